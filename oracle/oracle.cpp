@@ -1,0 +1,1137 @@
+// oracle.cpp — TEST INFRASTRUCTURE ONLY.
+//
+// A double-precision CPU restatement of the per-pixel Monte Carlo path of
+// BlackCloud37/rust-raytracer, used (a) as the checker in tests/ and
+// __graft_entry__.smoke() and (b) as the timed CPU baseline of bench.py
+// (`cpu_baseline`, `--impl reference`).  Nothing in the product path
+// (rust_raytracer_b200/) links, imports or executes this file.
+//
+// PARITY UNPINNED: the reference cannot be compiled here (no cargo/rustc) and
+// its own tests only pin Vec3 arithmetic (vec3.rs:425-564, restated in
+// tests/test_oracle_vec3.py).  Everything else follows the reference source
+// line by line; each block cites the file:line it restates (paths relative to
+// raytracer/src/).  Features the reference lacks (MovingSphere, Isotropic,
+// Perlin, MixturePDF, background) follow the public book series the reference's
+// README cites and are marked "absent upstream".
+//
+// Scene hand-off: the flat tables of include/b200rt.h (the public ABI structs);
+// this file rebuilds the reference's object graph (Arc<dyn Hitable> tree,
+// recursive BVHNode, Transform wrappers) from them.
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../include/b200rt.h"
+
+namespace oracle {
+
+static const double PI = 3.14159265358979323846;
+static const double INF = std::numeric_limits<double>::infinity();
+
+// ---------------------------------------------------------------- vec3.rs:14-422
+struct Vec3 {
+  double x = 0, y = 0, z = 0;
+  Vec3() {}
+  Vec3(double x_, double y_, double z_) : x(x_), y(y_), z(z_) {}
+  static Vec3 ones() { return Vec3(1, 1, 1); }
+  static Vec3 zero() { return Vec3(0, 0, 0); }
+  static Vec3 all(double v) { return Vec3(v, v, v); }
+  double operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
+  double max() const { return std::fmax(std::fmax(x, y), z); }
+  double squared_length() const { return x * x + y * y + z * z; }
+  double length() const { return std::sqrt(squared_length()); }
+  // vec3.rs:86-91 panics on the zero vector.
+  Vec3 unit() const {
+    double l = length();
+    if (l == 0.) throw std::runtime_error("unitizing zero vector");
+    return Vec3(x / l, y / l, z / l);
+  }
+  bool is_near_zero() const {  // vec3.rs:93-96
+    const double S = 1e-8;
+    return std::fabs(x) < S && std::fabs(y) < S && std::fabs(z) < S;
+  }
+};
+inline Vec3 operator+(Vec3 a, Vec3 b) { return Vec3(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline Vec3 operator+(Vec3 a, double b) { return Vec3(a.x + b, a.y + b, a.z + b); }
+inline Vec3 operator-(Vec3 a, Vec3 b) { return Vec3(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline Vec3 operator-(Vec3 a, double b) { return Vec3(a.x - b, a.y - b, a.z - b); }
+inline Vec3 operator-(Vec3 a) { return Vec3(-a.x, -a.y, -a.z); }
+// vec3.rs:335-341: `Vec3 * Vec3` is the DOT product.
+inline double operator*(Vec3 a, Vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline Vec3 operator*(Vec3 a, double b) { return Vec3(a.x * b, a.y * b, a.z * b); }
+inline Vec3 operator*(double b, Vec3 a) { return Vec3(a.x * b, a.y * b, a.z * b); }
+inline Vec3 operator/(Vec3 a, double b) { return Vec3(a.x / b, a.y / b, a.z / b); }
+inline Vec3 elemul(Vec3 a, Vec3 b) { return Vec3(a.x * b.x, a.y * b.y, a.z * b.z); }  // vec3.rs:66-72
+inline Vec3 cross(Vec3 l, Vec3 r) {                                                    // vec3.rs:74-80
+  return Vec3(l.y * r.z - l.z * r.y, l.z * r.x - l.x * r.z, l.x * r.y - l.y * r.x);
+}
+inline Vec3 reflect(Vec3 v, Vec3 n) { return v - 2. * (v * n) * n; }  // vec3.rs:163-165
+inline Vec3 refract(Vec3 uv, Vec3 n, double eta) {                    // vec3.rs:167-172
+  double cos_theta = std::fmin((-uv) * n, 1.0);
+  Vec3 perp = eta * (uv + cos_theta * n);
+  Vec3 par = -std::sqrt(std::fabs(1.0 - perp.squared_length())) * n;
+  return perp + par;
+}
+inline double degrees_to_radians(double d) { return d * PI / 180.; }  // vec3.rs:10-12
+
+// 3x4 affine matrix standing in for nalgebra::Matrix4 (vec3.rs:174-184, transform.rs:28-138).
+struct Mat34 {
+  double m[12];
+  Vec3 point(Vec3 p) const {
+    return Vec3(m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3], m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7],
+                m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11]);
+  }
+  Vec3 dir(Vec3 p) const {
+    return Vec3(m[0] * p.x + m[1] * p.y + m[2] * p.z, m[4] * p.x + m[5] * p.y + m[6] * p.z,
+                m[8] * p.x + m[9] * p.y + m[10] * p.z);
+  }
+  bool inverse(Mat34& out) const {  // try_inverse of the affine matrix
+    double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+    double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    if (det == 0. || !std::isfinite(det)) return false;
+    double id = 1.0 / det;
+    double r[9] = {(e * i - f * h) * id, (c * h - b * i) * id, (b * f - c * e) * id,
+                   (f * g - d * i) * id, (a * i - c * g) * id, (c * d - a * f) * id,
+                   (d * h - e * g) * id, (b * g - a * h) * id, (a * e - b * d) * id};
+    for (int row = 0; row < 3; ++row) {
+      out.m[row * 4 + 0] = r[row * 3 + 0];
+      out.m[row * 4 + 1] = r[row * 3 + 1];
+      out.m[row * 4 + 2] = r[row * 3 + 2];
+      out.m[row * 4 + 3] = -(r[row * 3 + 0] * m[3] + r[row * 3 + 1] * m[7] + r[row * 3 + 2] * m[11]);
+    }
+    return true;
+  }
+};
+
+// ---------------------------------------------------------------- RNG
+// The reference draws everything from rand::thread_rng() (OS-seeded ChaCha12;
+// rand 0.8.4 is not under /root/reference), so only distributions can be
+// compared.  Here every draw comes from an injected Philox4x32-10 stream
+// (Salmon et al., SC'11 — public algorithm) keyed per (seed, pixel, sample).
+struct Philox {
+  static inline void round(uint32_t c[4], const uint32_t k[2]) {
+    const uint64_t M0 = 0xD2511F53ull, M1 = 0xCD9E8D57ull;
+    uint64_t p0 = M0 * c[0], p1 = M1 * c[2];
+    uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0, hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
+    uint32_t n0 = hi1 ^ c[1] ^ k[0], n1 = lo1, n2 = hi0 ^ c[3] ^ k[1], n3 = lo0;
+    c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+  }
+  static inline void gen(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+    uint32_t c[4] = {ctr[0], ctr[1], ctr[2], ctr[3]};
+    uint32_t k[2] = {key[0], key[1]};
+    for (int i = 0; i < 10; ++i) {
+      round(c, k);
+      k[0] += 0x9E3779B9u;
+      k[1] += 0xBB67AE85u;
+    }
+    out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
+  }
+};
+
+struct Stream {
+  uint32_t key[2], ctr[4], buf[4];
+  int idx = 4;
+  Stream(uint64_t seed, uint32_t a, uint32_t b, uint32_t tag) {
+    key[0] = (uint32_t)seed; key[1] = (uint32_t)(seed >> 32);
+    ctr[0] = a; ctr[1] = b; ctr[2] = 0; ctr[3] = tag;
+  }
+  uint32_t next_u32() {
+    if (idx == 4) { Philox::gen(ctr, key, buf); ctr[2]++; idx = 0; }
+    return buf[idx++];
+  }
+  double next() {  // rng.gen::<f64>() : uniform [0,1), 53 bits
+    uint64_t a = next_u32() >> 5, b = next_u32() >> 6;
+    return (a * 67108864.0 + b) / 9007199254740992.0;
+  }
+  double range(double lo, double hi) { return lo + (hi - lo) * next(); }  // gen_range(lo..hi)
+  int range_int(int n) { return std::min(n - 1, (int)(next() * n)); }
+};
+
+// Shared with the device code by DEFINITION (both sides restate it): the draw
+// ConstantMedium::hit makes inside `hit` (medium.rs:37-38) as a pure function of
+// the ray's seed and the primitive index.
+static inline uint32_t pcg_hash(uint32_t v) {
+  uint32_t state = v * 747796405u + 2891336453u;
+  uint32_t word = ((state >> ((state >> 28u) + 4u)) ^ state) * 277803737u;
+  return (word >> 22u) ^ word;
+}
+static inline double medium_xi(uint32_t seed, uint32_t prim) {
+  uint32_t h = pcg_hash(seed ^ (prim * 0x9E3779B9u));
+  return ((double)(h >> 9) + 0.5) * (1.0 / 8388608.0);
+}
+
+// vec3.rs:111-129 — Marsaglia: returns a point ON the unit sphere.
+static Vec3 random_in_unit_sphere(Stream& rng) {
+  double u, v, r2;
+  for (;;) {
+    u = rng.range(-1., 1.);
+    v = rng.range(-1., 1.);
+    r2 = u * u + v * v;
+    if (r2 <= 1.) break;
+  }
+  return Vec3(2. * u * std::sqrt(1. - r2), 2. * v * std::sqrt(1. - r2), 1. - 2. * r2);
+}
+static Vec3 random_unit_vector(Stream& rng) { return random_in_unit_sphere(rng).unit(); }  // vec3.rs:140-142
+static Vec3 random_in_unit_disk(Stream& rng) {                                             // vec3.rs:153-162
+  for (;;) {
+    Vec3 p(rng.range(-1., 1.), rng.range(-1., 1.), 0.);
+    if (p.squared_length() >= 1.) continue;
+    return p;
+  }
+}
+
+// ---------------------------------------------------------------- ray.rs:3-15 (+ time, + medium seed)
+struct Ray {
+  Vec3 orig, dir;
+  double time = 0;     // absent upstream (MovingSphere)
+  uint32_t mseed = 0;  // injected draw for ConstantMedium::hit
+  Ray() {}
+  Ray(Vec3 o, Vec3 d, double t = 0, uint32_t s = 0) : orig(o), dir(d), time(t), mseed(s) {}
+  Vec3 at(double t) const { return orig + t * dir; }
+};
+
+struct Material;
+
+// ---------------------------------------------------------------- objects/hit.rs:7-48
+struct HitRecord {
+  Vec3 p, normal;
+  double t = 0;
+  bool front_face = false;
+  const Material* mat = nullptr;
+  double u = 0, v = 0;
+  int prim = -1;  // bookkeeping for parity tests only
+  HitRecord() {}
+  HitRecord(double t_, Vec3 outward_normal, const Ray& r, const Material* m, double u_, double v_, int prim_) {
+    p = r.at(t_);
+    front_face = r.dir * outward_normal < 0.;
+    Vec3 n = front_face ? outward_normal : -outward_normal;
+    normal = n.unit();
+    t = t_; mat = m; u = u_; v = v_; prim = prim_;
+  }
+  void set_face_normal(const Ray& r, Vec3 outward_normal) {  // hit.rs:41-48
+    front_face = r.dir * outward_normal < 0.;
+    normal = front_face ? outward_normal.unit() : -outward_normal.unit();
+  }
+};
+
+// ---------------------------------------------------------------- objects/aabb.rs:15-45
+struct AABB {
+  Vec3 minimum, maximum;
+  bool hit(const Ray& r, double t_min, double t_max) const {
+    double mn = t_min, mx = t_max;
+    for (int a = 0; a < 3; ++a) {
+      double inv_d = 1.0 / r.dir[a];
+      double t0 = (minimum[a] - r.orig[a]) * inv_d;
+      double t1 = (maximum[a] - r.orig[a]) * inv_d;
+      if (inv_d < 0.0) std::swap(t0, t1);
+      mn = std::fmax(mn, t0);  // f64::max returns the non-NaN operand, like fmax
+      mx = std::fmin(mx, t1);
+      if (mx <= mn) return false;
+    }
+    return true;
+  }
+  static AABB surrounding_box(const AABB& a, const AABB& b) {
+    AABB o;
+    o.minimum = Vec3(std::fmin(a.minimum.x, b.minimum.x), std::fmin(a.minimum.y, b.minimum.y), std::fmin(a.minimum.z, b.minimum.z));
+    o.maximum = Vec3(std::fmax(a.maximum.x, b.maximum.x), std::fmax(a.maximum.y, b.maximum.y), std::fmax(a.maximum.z, b.maximum.z));
+    return o;
+  }
+};
+
+// ---------------------------------------------------------------- objects/hit.rs:51-54
+struct Hitable {
+  virtual ~Hitable() {}
+  virtual bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const = 0;
+  virtual bool bounding_box(AABB& out) const = 0;
+};
+typedef std::shared_ptr<Hitable> HitablePtr;
+
+// hit.rs:56-92 — impl Hitable for Vec<Arc<dyn Hitable>>
+struct HitableList : Hitable {
+  std::vector<HitablePtr> items;
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override {
+    double closest = t_max;
+    bool any = false;
+    HitRecord tmp;
+    for (const auto& o : items)
+      if (o->hit(r, t_min, closest, tmp)) { closest = tmp.t; rec = tmp; any = true; }
+    return any;
+  }
+  bool bounding_box(AABB& out) const override {
+    if (items.empty()) return false;
+    bool first = true;
+    AABB tmp;
+    for (const auto& o : items) {
+      if (!o->bounding_box(tmp)) return false;
+      out = first ? tmp : AABB::surrounding_box(out, tmp);
+      first = false;
+    }
+    return true;
+  }
+};
+
+// ---------------------------------------------------------------- objects/bvh.rs:29-106
+struct BVHNode : Hitable {
+  HitablePtr left, right;
+  AABB box;
+  static int box_compare_less(const HitablePtr& a, const HitablePtr& b, int axis) {  // bvh.rs:34-44
+    AABB ba, bb;
+    if (!a->bounding_box(ba) || !b->bounding_box(bb)) throw std::runtime_error("No bounding box in bvh_node constructor.");
+    return ba.minimum[axis] < bb.minimum[axis];
+  }
+  static std::shared_ptr<BVHNode> construct(HitablePtr l, HitablePtr r) {  // bvh.rs:47-58
+    AABB bl, br;
+    if (!l->bounding_box(bl) || !r->bounding_box(br)) throw std::runtime_error("No bounding box in bvh_node constructor.");
+    auto n = std::make_shared<BVHNode>();
+    n->left = l; n->right = r; n->box = AABB::surrounding_box(bl, br);
+    return n;
+  }
+  static std::shared_ptr<BVHNode> make(std::vector<HitablePtr> objs, Stream& rng) {  // bvh.rs:60-83
+    int axis = rng.range_int(3);
+    size_t span = objs.size();
+    if (span == 0) throw std::runtime_error("BVHNode::new on an empty list");
+    if (span == 1) return construct(objs[0], objs[0]);
+    if (span == 2) {
+      // comparator(a,b).is_le(): the comparator never returns Equal, so "le" == "less"
+      if (box_compare_less(objs[0], objs[1], axis)) return construct(objs[0], objs[1]);
+      return construct(objs[1], objs[0]);
+    }
+    std::stable_sort(objs.begin(), objs.end(), [axis](const HitablePtr& a, const HitablePtr& b) { return box_compare_less(a, b, axis) != 0; });
+    size_t mid = span / 2;
+    auto l = make(std::vector<HitablePtr>(objs.begin(), objs.begin() + mid), rng);
+    auto r = make(std::vector<HitablePtr>(objs.begin() + mid, objs.end()), rng);
+    return construct(l, r);
+  }
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override {  // bvh.rs:86-102
+    if (!box.hit(r, t_min, t_max)) return false;
+    HitRecord lrec, rrec;
+    bool hl = left->hit(r, t_min, t_max, lrec);
+    double lmax = hl ? lrec.t : t_max;
+    bool hr = right->hit(r, t_min, lmax, rrec);
+    if (hr) { rec = rrec; return true; }
+    if (hl) { rec = lrec; return true; }
+    return false;
+  }
+  bool bounding_box(AABB& out) const override { out = box; return true; }
+};
+
+// ---------------------------------------------------------------- objects/sphere.rs:10-62
+struct Sphere : Hitable {
+  Vec3 center;
+  double radius;
+  const Material* material;
+  int prim;
+  static void get_uv(Vec3 p, double& u, double& v) {  // sphere.rs:16-20
+    double theta = std::acos(-p.y);
+    double phi = std::atan2(-p.z, p.x) + PI;
+    u = phi * (1.0 / PI) * 0.5;
+    v = theta * (1.0 / PI);
+  }
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override {  // sphere.rs:24-55
+    Vec3 oc = r.orig - center;
+    double a = r.dir.squared_length();
+    double half_b = oc * r.dir;
+    double c = oc.squared_length() - radius * radius;
+    double disc = half_b * half_b - a * c;
+    if (disc < 0.) return false;
+    double sqrt_d = std::sqrt(disc);
+    double root = (-half_b - sqrt_d) / a;
+    if (!(root >= t_min && root <= t_max)) {
+      root = (-half_b + sqrt_d) / a;
+      if (!(root >= t_min && root <= t_max)) return false;
+    }
+    Vec3 p = r.at(root);
+    Vec3 on = (p - center) / radius;
+    double u, v;
+    get_uv(on, u, v);
+    rec = HitRecord(root, on, r, material, u, v, prim);
+    return true;
+  }
+  bool bounding_box(AABB& out) const override {  // sphere.rs:56-61
+    out.minimum = center - Vec3::all(radius);
+    out.maximum = center + Vec3::all(radius);
+    return true;
+  }
+};
+
+// Absent upstream (Ray has no time, ray.rs:3-6).  Book-2 semantics: centre moves linearly over the shutter.
+struct MovingSphere : Hitable {
+  Vec3 c0, c1;
+  double time0, time1, radius;
+  const Material* material;
+  int prim;
+  Vec3 center(double time) const { return c0 + ((time - time0) / (time1 - time0)) * (c1 - c0); }
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override {
+    Vec3 ctr = center(r.time);
+    Vec3 oc = r.orig - ctr;
+    double a = r.dir.squared_length();
+    double half_b = oc * r.dir;
+    double c = oc.squared_length() - radius * radius;
+    double disc = half_b * half_b - a * c;
+    if (disc < 0.) return false;
+    double sqrt_d = std::sqrt(disc);
+    double root = (-half_b - sqrt_d) / a;
+    if (!(root >= t_min && root <= t_max)) {
+      root = (-half_b + sqrt_d) / a;
+      if (!(root >= t_min && root <= t_max)) return false;
+    }
+    Vec3 on = (r.at(root) - ctr) / radius;
+    double u, v;
+    Sphere::get_uv(on, u, v);
+    rec = HitRecord(root, on, r, material, u, v, prim);
+    return true;
+  }
+  bool bounding_box(AABB& out) const override {
+    AABB b0{c0 - Vec3::all(radius), c0 + Vec3::all(radius)}, b1{c1 - Vec3::all(radius), c1 + Vec3::all(radius)};
+    out = AABB::surrounding_box(b0, b1);
+    return true;
+  }
+};
+
+// ---------------------------------------------------------------- objects/rectangle.rs:7-117
+// axis: 2 = XYRectangle (k = z), 1 = XZRectangle (k = y), 0 = YZRectangle (k = x).
+struct AxisRect : Hitable {
+  int axis;
+  double a0, b0, a1, b1, k;
+  const Material* material;
+  int prim;
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override {
+    const int ia = axis == 0 ? 1 : 0;             // first in-plane coordinate
+    const int ib = axis == 2 ? 1 : 2;             // second in-plane coordinate
+    double t = (k - r.orig[axis]) / r.dir[axis];  // no guard for dir == 0 (rectangle.rs:19,57,94)
+    if (t < t_min || t > t_max) return false;
+    Vec3 p = r.at(t);
+    double a = p[ia], b = p[ib];
+    if (a < a0 || a > a1 || b < b0 || b > b1) return false;
+    Vec3 n(axis == 0 ? 1. : 0., axis == 1 ? 1. : 0., axis == 2 ? 1. : 0.);
+    rec = HitRecord(t, n, r, material, (a - a0) / (a1 - a0), (b - b0) / (b1 - b0), prim);
+    return true;
+  }
+  bool bounding_box(AABB& out) const override {  // rectangle.rs:35-41,73-79,110-116
+    const double BIAS = 0.0001;
+    double lo[3], hi[3];
+    const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
+    lo[ia] = a0; hi[ia] = a1; lo[ib] = b0; hi[ib] = b1; lo[axis] = k - BIAS; hi[axis] = k + BIAS;
+    out.minimum = Vec3(lo[0], lo[1], lo[2]);
+    out.maximum = Vec3(hi[0], hi[1], hi[2]);
+    return true;
+  }
+};
+
+// ---------------------------------------------------------------- objects/cube.rs:9-70
+struct Cube : Hitable {
+  Vec3 box_min, box_max;
+  HitableList sides;
+  Cube(Vec3 mn, Vec3 mx, const Material* m, int prim) : box_min(mn), box_max(mx) {
+    auto add = [&](int axis, double a0, double b0, double a1, double b1, double k) {
+      auto r = std::make_shared<AxisRect>();
+      r->axis = axis; r->a0 = a0; r->b0 = b0; r->a1 = a1; r->b1 = b1; r->k = k; r->material = m; r->prim = prim;
+      sides.items.push_back(r);
+    };
+    add(2, mn.x, mn.y, mx.x, mx.y, mn.z);  // cube.rs:18-29
+    add(2, mn.x, mn.y, mx.x, mx.y, mx.z);
+    add(1, mn.x, mn.z, mx.x, mx.z, mn.y);  // cube.rs:30-41
+    add(1, mn.x, mn.z, mx.x, mx.z, mx.y);
+    add(0, mn.y, mn.z, mx.y, mx.z, mn.x);  // cube.rs:42-53
+    add(0, mn.y, mn.z, mx.y, mx.z, mx.x);
+  }
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override { return sides.hit(r, t_min, t_max, rec); }
+  bool bounding_box(AABB& out) const override { out.minimum = box_min; out.maximum = box_max; return true; }
+};
+
+// ---------------------------------------------------------------- objects/mesh.rs:8-142
+struct Triangle : Hitable {
+  Vec3 pa, pb, pc, na, nb, nc;
+  const Material* material;
+  int prim;
+  bool hit(const Ray& ray, double t_min, double t_max, HitRecord& rec) const override {  // mesh.rs:56-137
+    Vec3 edge0 = pb - pa, edge1 = pc - pa;
+    Vec3 s0 = cross(ray.dir, edge1);
+    double d0 = s0 * edge0;
+    if (d0 == 0.0) return false;
+    double div = 1.0 / d0;
+    Vec3 d = ray.orig - pa;
+    double b1 = d * s0 * div;
+    if (b1 < 0.0 || b1 > 1.0) return false;
+    Vec3 s1 = cross(d, edge0);
+    double b2 = ray.dir * s1 * div;
+    if (b2 < 0.0 || b1 + b2 > 1.0) return false;
+    double t = edge1 * s1 * div;
+    if (t < t_min || t > t_max) return false;
+    double b0 = 1.0 - b1 - b2;
+    Vec3 n = (b0 * na + b1 * nb + b2 * nc).unit();
+    rec = HitRecord(t, n, ray, material, 0.0, 0.0, prim);
+    return true;
+  }
+  bool bounding_box(AABB& out) const override {  // mesh.rs:33-42 (padded by 0.1 on every axis)
+    out.maximum = Vec3(std::fmax(std::fmax(pa.x, pb.x), pc.x) + 0.1, std::fmax(std::fmax(pa.y, pb.y), pc.y) + 0.1, std::fmax(std::fmax(pa.z, pb.z), pc.z) + 0.1);
+    out.minimum = Vec3(std::fmin(std::fmin(pa.x, pb.x), pc.x) - 0.1, std::fmin(std::fmin(pa.y, pb.y), pc.y) - 0.1, std::fmin(std::fmin(pa.z, pb.z), pc.z) - 0.1);
+    return true;
+  }
+};
+
+// ---------------------------------------------------------------- objects/transform.rs:9-169
+struct Transform : Hitable {
+  HitablePtr obj;
+  Mat34 trans, inverse_trans;
+  bool has_box = false;
+  AABB box;
+  Transform(const Mat34& m, HitablePtr o) : obj(o), trans(m) {
+    AABB bb;
+    if (obj->bounding_box(bb)) {  // transform.rs:110-136
+      double mn[3] = {INF, INF, INF}, mx[3] = {-INF, -INF, -INF};
+      for (int i = 0; i < 2; ++i)
+        for (int j = 0; j < 2; ++j)
+          for (int k = 0; k < 2; ++k) {
+            Vec3 tester(i * bb.maximum.x + (1. - i) * bb.minimum.x, j * bb.maximum.y + (1. - j) * bb.minimum.y, k * bb.maximum.z + (1. - k) * bb.minimum.z);
+            tester = trans.point(tester);
+            for (int c = 0; c < 3; ++c) { mn[c] = std::fmin(mn[c], tester[c]); mx[c] = std::fmax(mx[c], tester[c]); }
+          }
+      box.minimum = Vec3(mn[0], mn[1], mn[2]);
+      box.maximum = Vec3(mx[0], mx[1], mx[2]);
+      has_box = true;
+    }
+    if (!trans.inverse(inverse_trans)) throw std::runtime_error("Invalid transform matrix");  // transform.rs:138-147
+  }
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override {  // transform.rs:151-165
+    Ray tr(inverse_trans.point(r.orig), inverse_trans.dir(r.dir), r.time, r.mseed);
+    if (!obj->hit(tr, t_min, t_max, rec)) return false;
+    Vec3 outward = trans.dir(rec.normal);  // M * n, not the inverse transpose
+    rec.p = trans.point(rec.p);
+    rec.set_face_normal(tr, outward);  // against the OBJECT-space ray
+    return true;
+  }
+  bool bounding_box(AABB& out) const override { if (!has_box) return false; out = box; return true; }
+};
+
+// ---------------------------------------------------------------- objects/medium.rs:9-57
+struct ConstantMedium : Hitable {
+  HitablePtr boundary;
+  const Material* phase_function;
+  double neg_inv_density;
+  int prim;
+  bool hit(const Ray& r, double t_min, double t_max, HitRecord& rec) const override {
+    HitRecord rec1, rec2;
+    if (!boundary->hit(r, -INF, INF, rec1)) return false;
+    if (!boundary->hit(r, rec1.t + 0.0001, INF, rec2)) return false;
+    rec1.t = std::fmax(rec1.t, t_min);
+    rec2.t = std::fmin(rec2.t, t_max);
+    if (rec1.t >= rec2.t) return false;
+    rec1.t = std::fmax(rec1.t, 0.);
+    double ray_length = r.dir.length();
+    double distance_inside = (rec2.t - rec1.t) * ray_length;
+    double hit_distance = neg_inv_density * std::log(medium_xi(r.mseed, (uint32_t)prim));  // medium.rs:37-38, injected draw
+    if (hit_distance > distance_inside) return false;
+    double t = rec1.t + hit_distance / ray_length;
+    rec = HitRecord(t, Vec3(1., 0., 0.), r, phase_function, 0.0, 0.0, prim);
+    return true;
+  }
+  bool bounding_box(AABB& out) const override { return boundary->bounding_box(out); }
+};
+
+// ---------------------------------------------------------------- material.rs:18-84 textures
+struct Scene;
+struct Texture {
+  int type = 0;
+  Vec3 c0, c1;
+  double scale = 1;
+  int img_w = 0, img_h = 0;
+  const uint8_t* img = nullptr;
+  const b200rt_perlin* perlin = nullptr;
+
+  double noise(Vec3 p) const {  // absent upstream; book-2 Perlin with hermite smoothing
+    double fx = std::floor(p.x), fy = std::floor(p.y), fz = std::floor(p.z);
+    double u = p.x - fx, v = p.y - fy, w = p.z - fz;
+    int i = (int)fx, j = (int)fy, k = (int)fz;
+    double uu = u * u * (3 - 2 * u), vv = v * v * (3 - 2 * v), ww = w * w * (3 - 2 * w);
+    double accum = 0;
+    for (int di = 0; di < 2; ++di)
+      for (int dj = 0; dj < 2; ++dj)
+        for (int dk = 0; dk < 2; ++dk) {
+          int idx = perlin->perm_x[(i + di) & 255] ^ perlin->perm_y[(j + dj) & 255] ^ perlin->perm_z[(k + dk) & 255];
+          Vec3 c(perlin->ranvec[idx][0], perlin->ranvec[idx][1], perlin->ranvec[idx][2]);
+          Vec3 wv(u - di, v - dj, w - dk);
+          accum += (di * uu + (1 - di) * (1 - uu)) * (dj * vv + (1 - dj) * (1 - vv)) * (dk * ww + (1 - dk) * (1 - ww)) * (c * wv);
+        }
+    return accum;
+  }
+  double turb(Vec3 p) const {
+    double accum = 0, weight = 1;
+    for (int i = 0; i < 7; ++i) { accum += weight * noise(p); weight *= 0.5; p = p * 2.; }
+    return std::fabs(accum);
+  }
+  Vec3 get_color(const HitRecord& rec) const {
+    switch (type) {
+      case B200RT_TEX_CONSTANT: return c0;  // material.rs:52-56
+      case B200RT_TEX_CHECKER: {            // material.rs:58-68
+        Vec3 p = rec.p;
+        double sines = std::sin(10. * p.x) * std::sin(10. * p.y) * std::sin(10. * p.z);
+        return sines < 0. ? c0 : c1;
+      }
+      case B200RT_TEX_IMAGE: {  // material.rs:70-84; index clamped (the reference would panic at u == 1, v == 0)
+        double u = std::fmin(std::fmax(rec.u, 0.), 1.), v = 1. - std::fmin(std::fmax(rec.v, 0.), 1.);
+        int x = (int)std::floor(img_w * u), y = (int)std::floor(img_h * v);
+        x = std::min(x, img_w - 1); y = std::min(y, img_h - 1);
+        const uint8_t* px = img + 3 * ((size_t)y * img_w + x);
+        return Vec3(px[0] / 255., px[1] / 255., px[2] / 255.);  // vec3.rs:233-238
+      }
+      case B200RT_TEX_NOISE: return Vec3::ones() * (0.5 * (1. + std::sin(scale * rec.p.z + 10. * turb(rec.p))));
+    }
+    return Vec3::zero();
+  }
+};
+
+// ---------------------------------------------------------------- material.rs:10-231
+enum Interaction { Diffuse, Specular, Absorb, Reflect, Refract };
+struct ScatterResult {
+  Interaction inter = Absorb;
+  bool has_ray = false;
+  Ray ray;
+  Vec3 attenuation;
+};
+struct Material {
+  int type = 0;
+  const Texture* tex = nullptr;
+  double param = 0;
+  static Vec3 scattered_direction(Vec3 n, Stream& rng) {  // material.rs:92-98
+    Vec3 d = n + random_unit_vector(rng);
+    if (d.is_near_zero()) d = n;
+    return d;
+  }
+  static double reflectance(double cosine, double ref_idx) {  // material.rs:150-154
+    double r0 = (1. - ref_idx) / (1. + ref_idx);
+    r0 = r0 * r0;
+    double m = 1. - cosine;
+    return r0 + (1. - r0) * (m * m * m * m * m);
+  }
+  Vec3 emitted(const HitRecord& rec) const {  // material.rs:24-26, 209-211
+    return type == B200RT_MAT_DIFFUSE_LIGHT ? tex->get_color(rec) : Vec3::zero();
+  }
+  bool is_diffuse() const { return type == B200RT_MAT_LAMBERTIAN || type == B200RT_MAT_ISOTROPIC; }
+  ScatterResult scatter(const Ray& r, const HitRecord& rec, Stream& rng) const {
+    ScatterResult s;
+    switch (type) {
+      case B200RT_MAT_LAMBERTIAN:  // material.rs:109-112
+        s.inter = Diffuse; s.has_ray = true;
+        s.ray = Ray(rec.p, scattered_direction(rec.normal, rng), r.time);
+        s.attenuation = tex->get_color(rec);
+        break;
+      case B200RT_MAT_METAL: {  // material.rs:130-138
+        Vec3 reflected = reflect(r.dir.unit(), rec.normal);
+        Vec3 dir = reflected + param * random_in_unit_sphere(rng);
+        if (dir * rec.normal > 0.) {
+          s.inter = Specular; s.has_ray = true; s.ray = Ray(rec.p, dir, r.time); s.attenuation = tex->get_color(rec);
+        }
+        break;
+      }
+      case B200RT_MAT_DIELECTRIC: {  // material.rs:161-187
+        s.attenuation = tex->get_color(rec);
+        double ratio = rec.front_face ? 1.0 / param : param;
+        Vec3 ud = r.dir.unit();
+        double cos_theta = std::fmin((-ud) * rec.normal, 1.0);
+        double sin_theta = std::sqrt(1.0 - cos_theta * cos_theta);
+        bool cannot_refract = ratio * sin_theta > 1.0;
+        Vec3 dir;
+        if (cannot_refract || reflectance(cos_theta, ratio) > rng.next()) { dir = reflect(ud, rec.normal); s.inter = Reflect; }
+        else { dir = refract(ud, rec.normal, ratio); s.inter = Refract; }
+        s.has_ray = true; s.ray = Ray(rec.p, dir, r.time);
+        break;
+      }
+      case B200RT_MAT_DIFFUSE_LIGHT:  // material.rs:201-208 (bsdf = 1/pi, scatters like Lambertian)
+        s.inter = Diffuse; s.has_ray = true;
+        s.ray = Ray(rec.p, scattered_direction(rec.normal, rng), r.time);
+        s.attenuation = Vec3::ones() * (1.0 / PI);
+        break;
+      case B200RT_MAT_ISOTROPIC:  // material.rs:213-231 (commented out upstream): albedo, random_in_unit_sphere()
+        s.inter = Diffuse; s.has_ray = true;
+        s.ray = Ray(rec.p, random_in_unit_sphere(rng), r.time);
+        s.attenuation = tex->get_color(rec);
+        break;
+    }
+    return s;
+  }
+};
+
+// ---------------------------------------------------------------- camera.rs:11-64
+struct Camera {
+  Vec3 origin, llc, horizontal, vertical, u, v, w;
+  double lens_radius, time0, time1;
+  Ray get_ray(double s, double t, Stream& rng) const {  // camera.rs:57-64
+    Vec3 rd = lens_radius * random_in_unit_disk(rng);
+    Vec3 offset = u * rd.x + v * rd.y;
+    double time = time0;
+    if (time1 > time0) time = rng.range(time0, time1);  // absent upstream
+    return Ray(origin + offset, llc + s * horizontal + t * vertical - origin - offset, time);
+  }
+};
+
+// ---------------------------------------------------------------- world.rs:9-30 + light list
+struct Light {  // book-3 HittablePDF target; absent upstream (nearest analogue light.rs:107-124,170-183)
+  int kind;     // 0 = sphere, 1 = axis rect
+  Vec3 center; double radius;
+  int axis; double a0, b0, a1, b1, k;
+  HitablePtr shape;
+  int prim;
+  double pdf_value(Vec3 o, Vec3 dir, double t_min) const {
+    HitRecord rec;
+    Ray r(o, dir);
+    if (!shape->hit(r, t_min, INF, rec)) return 0;
+    if (kind == 1) {
+      double area = (a1 - a0) * (b1 - b0);
+      double dist2 = rec.t * rec.t * dir.squared_length();
+      Vec3 n(axis == 0, axis == 1, axis == 2);
+      double cosine = std::fabs((dir * n) / dir.length());
+      return dist2 / (cosine * area);
+    }
+    double cos_max = std::sqrt(std::fmax(0., 1 - radius * radius / (center - o).squared_length()));
+    double solid = 2 * PI * (1 - cos_max);
+    return 1 / solid;
+  }
+  Vec3 random(Vec3 o, Stream& rng) const {
+    if (kind == 1) {
+      double a = rng.range(a0, a1), b = rng.range(b0, b1);
+      double c[3];
+      const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
+      c[ia] = a; c[ib] = b; c[axis] = k;
+      return Vec3(c[0], c[1], c[2]) - o;
+    }
+    Vec3 dirc = center - o;
+    double d2 = dirc.squared_length();
+    Vec3 w = dirc.unit();
+    Vec3 a = std::fabs(w.x) > 0.9 ? Vec3(0, 1, 0) : Vec3(1, 0, 0);
+    Vec3 v = cross(w, a).unit();
+    Vec3 u = cross(w, v);
+    double r1 = rng.next(), r2 = rng.next();
+    double z = 1 + r2 * (std::sqrt(std::fmax(0., 1 - radius * radius / d2)) - 1);
+    double phi = 2 * PI * r1;
+    double x = std::cos(phi) * std::sqrt(std::fmax(0., 1 - z * z)), y = std::sin(phi) * std::sqrt(std::fmax(0., 1 - z * z));
+    return x * u + y * v + z * w;
+  }
+};
+
+struct Scene {
+  std::vector<Material> materials;
+  std::vector<Texture> textures;
+  std::vector<uint8_t> image_data;
+  std::vector<b200rt_image> images;
+  b200rt_perlin perlin;
+  bool has_perlin = false;
+  HitablePtr world;  // BVHNode over the list (world.rs:21) or the bare list (flat mode)
+  std::vector<Light> lights;
+  std::vector<int> light_of_prim;
+  size_t n_prims = 0;
+
+  double light_pdf(Vec3 o, Vec3 dir, double t_min) const {
+    double s = 0;
+    for (const auto& l : lights) s += l.pdf_value(o, dir, t_min);
+    return s / (double)lights.size();
+  }
+};
+
+static Vec3 v3(const float* p) { return Vec3(p[0], p[1], p[2]); }
+
+static Scene* build_scene(const b200rt_scene_desc* d, uint64_t bvh_seed) {
+  std::unique_ptr<Scene> sc(new Scene());
+  sc->n_prims = d->n_prims;
+  if (d->image_bytes) sc->image_data.assign(d->image_rgb8, d->image_rgb8 + d->image_bytes);
+  sc->images.assign(d->images, d->images + d->n_images);
+  if (d->perlin) { sc->perlin = *d->perlin; sc->has_perlin = true; }
+  sc->textures.resize(d->n_textures);
+  for (uint32_t i = 0; i < d->n_textures; ++i) {
+    const b200rt_texture& t = d->textures[i];
+    Texture& o = sc->textures[i];
+    o.type = t.type; o.c0 = v3(t.c0); o.c1 = v3(t.c1); o.scale = t.scale;
+    if (t.type == B200RT_TEX_IMAGE) {
+      if (t.image < 0 || (uint32_t)t.image >= d->n_images) throw std::runtime_error("bad image index");
+      o.img_w = sc->images[t.image].width; o.img_h = sc->images[t.image].height;
+      o.img = sc->image_data.data() + sc->images[t.image].offset;
+    }
+    if (t.type == B200RT_TEX_NOISE) {
+      if (!sc->has_perlin) throw std::runtime_error("noise texture without perlin tables");
+      o.perlin = &sc->perlin;
+    }
+  }
+  sc->materials.resize(d->n_materials);
+  for (uint32_t i = 0; i < d->n_materials; ++i) {
+    const b200rt_material& m = d->materials[i];
+    if (m.texture < 0 || (uint32_t)m.texture >= d->n_textures) throw std::runtime_error("bad texture index");
+    sc->materials[i].type = m.type; sc->materials[i].tex = &sc->textures[m.texture]; sc->materials[i].param = m.param;
+  }
+  auto list = std::make_shared<HitableList>();
+  std::vector<HitablePtr> raw(d->n_prims);
+  for (uint32_t i = 0; i < d->n_prims; ++i) {
+    const b200rt_prim& p = d->prims[i];
+    if (p.material < 0 || (uint32_t)p.material >= d->n_materials) throw std::runtime_error("bad material index");
+    const Material* m = &sc->materials[p.material];
+    HitablePtr h;
+    switch (p.type) {
+      case B200RT_PRIM_SPHERE: {
+        auto s = std::make_shared<Sphere>();
+        s->center = v3(p.p); s->radius = p.p[3]; s->material = m; s->prim = (int)i; h = s;
+        break;
+      }
+      case B200RT_PRIM_MOVING_SPHERE: {
+        auto s = std::make_shared<MovingSphere>();
+        s->c0 = v3(p.p); s->radius = p.p[3]; s->c1 = v3(p.p + 4); s->time0 = p.p[7]; s->time1 = p.p[8]; s->material = m; s->prim = (int)i; h = s;
+        break;
+      }
+      case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
+        auto r = std::make_shared<AxisRect>();
+        r->axis = p.type == B200RT_PRIM_XY_RECT ? 2 : (p.type == B200RT_PRIM_XZ_RECT ? 1 : 0);
+        r->a0 = p.p[0]; r->b0 = p.p[1]; r->a1 = p.p[2]; r->b1 = p.p[3]; r->k = p.p[4]; r->material = m; r->prim = (int)i; h = r;
+        break;
+      }
+      case B200RT_PRIM_BOX: h = std::make_shared<Cube>(v3(p.p), v3(p.p + 3), m, (int)i); break;
+      case B200RT_PRIM_TRIANGLE: {
+        auto t = std::make_shared<Triangle>();
+        t->pa = v3(p.p); t->pb = v3(p.p + 3); t->pc = v3(p.p + 6);
+        if (p.aux < 0 || (uint32_t)p.aux >= d->n_tri_normals) throw std::runtime_error("triangle without normals (mesh.rs:62-64 would panic)");
+        const float* n = d->tri_normals + 9 * (size_t)p.aux;
+        t->na = v3(n); t->nb = v3(n + 3); t->nc = v3(n + 6); t->material = m; t->prim = (int)i; h = t;
+        break;
+      }
+      case B200RT_PRIM_MEDIUM_SPHERE: {
+        auto s = std::make_shared<Sphere>();
+        s->center = v3(p.p); s->radius = p.p[3]; s->material = m; s->prim = (int)i;
+        auto cm = std::make_shared<ConstantMedium>();
+        cm->boundary = s; cm->phase_function = m; cm->neg_inv_density = -1. / (double)p.p[4]; cm->prim = (int)i; h = cm;
+        break;
+      }
+      case B200RT_PRIM_MEDIUM_BOX: {
+        auto cm = std::make_shared<ConstantMedium>();
+        cm->boundary = std::make_shared<Cube>(v3(p.p), v3(p.p + 3), m, (int)i);
+        cm->phase_function = m; cm->neg_inv_density = -1. / (double)p.p[6]; cm->prim = (int)i; h = cm;
+        break;
+      }
+      default: throw std::runtime_error("unknown primitive type");
+    }
+    raw[i] = h;
+    if (p.instance >= 0) {
+      if ((uint32_t)p.instance >= d->n_instances) throw std::runtime_error("bad instance index");
+      Mat34 m34;
+      std::memcpy(m34.m, d->instances[p.instance].m, sizeof(m34.m));
+      h = std::make_shared<Transform>(m34, h);
+    }
+    list->items.push_back(h);
+  }
+  sc->light_of_prim.assign(d->n_prims, -1);
+  for (uint32_t i = 0; i < d->n_lights; ++i) {
+    int pi = d->light_prims[i];
+    if (pi < 0 || (uint32_t)pi >= d->n_prims) throw std::runtime_error("bad light index");
+    const b200rt_prim& p = d->prims[pi];
+    if (p.instance >= 0) throw std::runtime_error("transformed lights are not sampled");
+    Light l;
+    l.prim = pi; l.shape = raw[pi];
+    if (p.type == B200RT_PRIM_SPHERE) { l.kind = 0; l.center = v3(p.p); l.radius = p.p[3]; }
+    else if (p.type == B200RT_PRIM_XY_RECT || p.type == B200RT_PRIM_XZ_RECT || p.type == B200RT_PRIM_YZ_RECT) {
+      l.kind = 1; l.axis = p.type == B200RT_PRIM_XY_RECT ? 2 : (p.type == B200RT_PRIM_XZ_RECT ? 1 : 0);
+      l.a0 = p.p[0]; l.b0 = p.p[1]; l.a1 = p.p[2]; l.b1 = p.p[3]; l.k = p.p[4];
+    } else throw std::runtime_error("only sphere and axis-rect lights are sampled");
+    sc->light_of_prim[pi] = (int)sc->lights.size();
+    sc->lights.push_back(l);
+  }
+  if (d->flags & B200RT_SCENE_FLAT_LIST) sc->world = list;
+  else {
+    Stream rng(bvh_seed, 0xB0B0u, 0x1u, 0xBEEFu);
+    sc->world = BVHNode::make(list->items, rng);  // world.rs:21
+  }
+  return sc.release();
+}
+
+// ---------------------------------------------------------------- the per-sample loop
+struct Counters { uint64_t extend = 0, shadow = 0; };
+
+static Vec3 background(const b200rt_params& P, const Ray& r) {
+  Vec3 bg(P.background[0], P.background[1], P.background[2]);
+  if (P.background_mode == B200RT_BACKGROUND_SKY) {  // absent upstream (photon_mapper.rs:335,364 returns black on a miss)
+    double t = 0.5 * (r.dir.unit().y + 1.0);
+    return (1.0 - t) * Vec3::ones() + t * bg;
+  }
+  return bg;
+}
+
+static void onb(Vec3 n, Vec3& u, Vec3& v) {
+  Vec3 a = std::fabs(n.x) > 0.9 ? Vec3(0, 1, 0) : Vec3(1, 0, 0);
+  v = cross(n, a).unit();
+  u = cross(n, v);
+}
+
+// Loop skeleton photon_mapper.rs:327-365 (throughput/radiance, depth budget decremented per hit, t_min 0.001,
+// emission x throughput, miss ends the path) — continued after diffuse hits instead of the SPPM lookup.
+static Vec3 sample_ray(const Scene& sc, const b200rt_params& P, Ray ray, Stream& rng, Counters& cnt) {
+  Vec3 throughput = Vec3::ones(), radiance = Vec3::zero();
+  int depth = P.max_depth;
+  const double t_min = P.t_min;
+  const bool use_lights = !sc.lights.empty();
+  double prev_pdf_b = -1;  // NEE: pdf of the direction that produced `ray` (< 0: camera / specular)
+  HitRecord rec;
+  for (;;) {
+    ray.mseed = rng.next_u32();
+    cnt.extend++;
+    if (!sc.world->hit(ray, t_min, INF, rec)) { radiance = radiance + elemul(throughput, background(P, ray)); break; }
+    if (depth <= 0) break;
+    depth -= 1;
+    const Material* m = rec.mat;
+    Vec3 le = m->emitted(rec);
+    if (m->type == B200RT_MAT_DIFFUSE_LIGHT) {
+      double w = 1;
+      if (P.integrator == B200RT_INTEGRATOR_NEE && prev_pdf_b >= 0 && use_lights && sc.light_of_prim[rec.prim] >= 0) {
+        double pl = sc.lights[sc.light_of_prim[rec.prim]].pdf_value(ray.orig, ray.dir, t_min) / (double)sc.lights.size();
+        w = prev_pdf_b / (prev_pdf_b + pl);
+      }
+      radiance = radiance + elemul(throughput, le) * w;
+      if (!(P.flags & B200RT_FLAG_LIGHT_SCATTERS)) break;
+    }
+    if (m->is_diffuse() && P.integrator != B200RT_INTEGRATOR_PATH) {
+      Vec3 albedo = m->tex->get_color(rec);
+      const bool iso = m->type == B200RT_MAT_ISOTROPIC;
+      auto spdf = [&](Vec3 d) { return iso ? 1.0 / (4 * PI) : std::fmax(0., rec.normal * d.unit()) / PI; };
+      auto sample_bsdf = [&]() {
+        if (iso) return random_in_unit_sphere(rng);
+        Vec3 u, v;
+        onb(rec.normal, u, v);
+        double r1 = rng.next(), r2 = rng.next();
+        double phi = 2 * PI * r1;
+        return std::cos(phi) * std::sqrt(r2) * u + std::sin(phi) * std::sqrt(r2) * v + std::sqrt(1 - r2) * rec.normal;
+      };
+      if (P.integrator == B200RT_INTEGRATOR_MIXTURE) {
+        Vec3 dir;
+        if (use_lights && rng.next() < 0.5) dir = sc.lights[rng.range_int((int)sc.lights.size())].random(rec.p, rng);
+        else dir = sample_bsdf();
+        double pb = spdf(dir);
+        double pdf = use_lights ? 0.5 * sc.light_pdf(rec.p, dir, t_min) + 0.5 * pb : pb;
+        if (!(pdf > 0) || !(pb > 0)) break;
+        throughput = elemul(throughput, albedo) * (pb / pdf);
+        ray = Ray(rec.p, dir, ray.time);
+        prev_pdf_b = -1;
+        continue;
+      }
+      // NEE + MIS (balance heuristic), one light sample per diffuse hit.
+      if (use_lights) {
+        const Light& L = sc.lights[rng.range_int((int)sc.lights.size())];
+        Vec3 dl = L.random(rec.p, rng);
+        HitRecord lrec;
+        Ray sray(rec.p, dl, ray.time, rng.next_u32());
+        double pb = spdf(dl);
+        if (pb > 0 && L.shape->hit(sray, t_min, INF, lrec)) {
+          double pl = L.pdf_value(rec.p, dl, t_min) / (double)sc.lights.size();
+          HitRecord occ;
+          cnt.shadow++;
+          if (pl > 0 && !sc.world->hit(sray, t_min, lrec.t * (1 - 1e-4), occ)) {
+            Vec3 le2 = lrec.mat->emitted(lrec);
+            double w = pl / (pl + pb);
+            radiance = radiance + elemul(elemul(throughput, albedo), le2) * (pb / pl * w);
+          }
+        }
+      }
+      Vec3 dir = sample_bsdf();
+      double pb = spdf(dir);
+      if (!(pb > 0)) break;
+      throughput = elemul(throughput, albedo);
+      prev_pdf_b = pb;
+      ray = Ray(rec.p, dir, ray.time);
+      continue;
+    }
+    ScatterResult s = m->scatter(ray, rec, rng);
+    if (!s.has_ray) break;  // Absorb (photon_mapper.rs:358-361)
+    throughput = elemul(throughput, s.attenuation);
+    ray = s.ray;
+    prev_pdf_b = -1;
+    if (P.integrator == B200RT_INTEGRATOR_NEE && s.inter == Diffuse) {
+      // DiffuseLight re-scatter under LIGHT_SCATTERS: cosine lobe, no NEE
+      prev_pdf_b = -1;
+    }
+  }
+  return radiance;
+}
+
+static Camera make_camera(const b200rt_camera& c) {
+  Camera cam;
+  cam.origin = v3(c.origin); cam.llc = v3(c.lower_left_corner); cam.horizontal = v3(c.horizontal); cam.vertical = v3(c.vertical);
+  cam.u = v3(c.u); cam.v = v3(c.v); cam.w = v3(c.w);
+  cam.lens_radius = c.lens_radius; cam.time0 = c.time0; cam.time1 = c.time1;
+  return cam;
+}
+
+}  // namespace oracle
+
+// ======================================================================= C entry points (ctypes)
+using namespace oracle;
+
+static thread_local std::string g_err;
+
+extern "C" {
+
+struct oracle_hit {
+  double t;
+  double nx, ny, nz;
+  double u, v;
+  double px, py, pz;
+  int32_t prim;
+  int32_t front_face;
+};
+
+const char* oracle_last_error() { return g_err.c_str(); }
+
+void* oracle_scene_create(const b200rt_scene_desc* desc, uint64_t bvh_seed) {
+  try { return build_scene(desc, bvh_seed); }
+  catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
+void oracle_scene_destroy(void* s) { delete (Scene*)s; }
+
+// World::hit (world.rs:27-29) over a batch.  o_time: n x (ox,oy,oz,time), d_tmax: n x (dx,dy,dz,t_max).
+int oracle_hit_batch(void* scene, const float* o_time, const float* d_tmax, const uint32_t* mseed, uint64_t n, double t_min, oracle_hit* out) {
+  const Scene& sc = *(Scene*)scene;
+  try {
+    for (uint64_t i = 0; i < n; ++i) {
+      Ray r(Vec3(o_time[4 * i], o_time[4 * i + 1], o_time[4 * i + 2]), Vec3(d_tmax[4 * i], d_tmax[4 * i + 1], d_tmax[4 * i + 2]), o_time[4 * i + 3], mseed ? mseed[i] : 0u);
+      HitRecord rec;
+      oracle_hit& h = out[i];
+      if (sc.world->hit(r, t_min, (double)d_tmax[4 * i + 3], rec)) {
+        h.t = rec.t; h.nx = rec.normal.x; h.ny = rec.normal.y; h.nz = rec.normal.z; h.u = rec.u; h.v = rec.v;
+        h.px = rec.p.x; h.py = rec.p.y; h.pz = rec.p.z; h.prim = rec.prim; h.front_face = rec.front_face ? 1 : 0;
+      } else { std::memset(&h, 0, sizeof(h)); h.prim = -1; h.t = INF; }
+    }
+  } catch (const std::exception& e) { g_err = e.what(); return 1; }
+  return 0;
+}
+
+// Camera::capture_image (camera.rs:66-128): n_jobs row bands on a pool of n_threads workers, per-pixel
+// spp loop camera.rs:91-106 with u = (x+xi)/(w-1), v = (y+xi)/(h-1), get_ray(u, 1-v).
+// accum: width*height*3 doubles (sum of samples, NOT divided).  Returns elapsed seconds in *seconds.
+int oracle_render(void* scene, const b200rt_camera* cam_in, const b200rt_params* P, double* accum, int n_jobs, int n_threads, uint64_t* extend_rays, uint64_t* shadow_rays, double* seconds) {
+  const Scene& sc = *(Scene*)scene;
+  Camera cam = make_camera(*cam_in);
+  const int W = P->width, H = P->height;
+  std::atomic<int> next_job(0);
+  std::atomic<uint64_t> ext(0), shd(0);
+  std::atomic<bool> failed(false);
+  std::mutex err_mu;
+  std::string err;
+  if (n_jobs < 1) n_jobs = 64;     // main.rs:42
+  if (n_threads < 1) n_threads = 8;
+  auto t0 = std::chrono::steady_clock::now();
+  auto worker = [&]() {
+    Counters cnt;
+    try {
+      for (;;) {
+        int i = next_job.fetch_add(1);
+        if (i >= n_jobs) break;
+        int row_begin = (int)((long long)H * i / n_jobs), row_end = (int)((long long)H * (i + 1) / n_jobs);  // camera.rs:85-86
+        for (int x = 0; x < W; ++x)
+          for (int y = row_begin; y < row_end; ++y) {
+            Vec3 pixel = Vec3::zero();
+            for (int s = 0; s < P->spp_count; ++s) {
+              Stream rng(P->seed, (uint32_t)(y * W + x), (uint32_t)(P->spp_begin + s), 0x0AC1Eu);
+              double u = (x + rng.next()) / (double)(W - 1);
+              double v = (y + rng.next()) / (double)(H - 1);
+              Ray r = cam.get_ray(u, 1.0 - v, rng);
+              pixel = pixel + sample_ray(sc, *P, r, rng, cnt);
+            }
+            double* o = accum + 3 * ((size_t)y * W + x);
+            o[0] += pixel.x; o[1] += pixel.y; o[2] += pixel.z;
+          }
+      }
+    } catch (const std::exception& e) {
+      std::lock_guard<std::mutex> g(err_mu);
+      err = e.what(); failed = true;
+    }
+    ext += cnt.extend; shd += cnt.shadow;
+  };
+  std::vector<std::thread> pool;
+  for (int i = 0; i < n_threads; ++i) pool.emplace_back(worker);
+  for (auto& t : pool) t.join();
+  auto t1 = std::chrono::steady_clock::now();
+  if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+  if (extend_rays) *extend_rays = ext.load();
+  if (shadow_rays) *shadow_rays = shd.load();
+  if (failed) { g_err = err; return 1; }
+  return 0;
+}
+
+// From<Vec3> for Rgb<u8> (vec3.rs:223-231): floor(clamp(sqrt(c),0,1)*255); NaN -> 0 via `as u8`.
+void oracle_tonemap(const double* mean_rgb, uint64_t n_pixels, uint8_t* out) {
+  for (uint64_t i = 0; i < 3 * n_pixels; ++i) {
+    double c = std::sqrt(mean_rgb[i]);
+    c = c < 0. ? 0. : (c > 1. ? 1. : c);  // clamp; NaN falls through both comparisons
+    double f = std::floor(c * 255.);
+    out[i] = std::isnan(f) ? 0 : (uint8_t)f;
+  }
+}
+
+// Vec3 operator table for the known-answer tests of vec3.rs:425-564.
+// op: 0 add, 1 add scalar(b[0]), 2 sub, 3 sub scalar, 4 dot -> out[0], 5 mul scalar, 6 div scalar, 7 elemul,
+//     8 cross, 9 neg, 10 squared_length -> out[0], 11 length -> out[0], 12 unit (returns 1 on the zero vector "panic"),
+//     13 reflect(a, b), 14 refract(a, b, eta = out[0] on entry)
+int oracle_vec3_op(int op, const double* a, const double* b, double* out) {
+  Vec3 A(a[0], a[1], a[2]), B = b ? Vec3(b[0], b[1], b[2]) : Vec3();
+  Vec3 r;
+  try {
+    switch (op) {
+      case 0: r = A + B; break;
+      case 1: r = A + b[0]; break;
+      case 2: r = A - B; break;
+      case 3: r = A - b[0]; break;
+      case 4: out[0] = A * B; return 0;
+      case 5: r = A * b[0]; break;
+      case 6: r = A / b[0]; break;
+      case 7: r = elemul(A, B); break;
+      case 8: r = cross(A, B); break;
+      case 9: r = -A; break;
+      case 10: out[0] = A.squared_length(); return 0;
+      case 11: out[0] = A.length(); return 0;
+      case 12: r = A.unit(); break;
+      case 13: r = reflect(A, B); break;
+      case 14: r = refract(A, B, out[0]); break;
+      default: return 2;
+    }
+  } catch (const std::exception&) { return 1; }
+  out[0] = r.x; out[1] = r.y; out[2] = r.z;
+  return 0;
+}
+
+// Sphere::bounding_box + AABB::surrounding_box over every sphere of a desc (known answer: the
+// `bounding_box` stored in data/scene_*.json BVHNode entries).
+void oracle_sphere_union_box(const b200rt_prim* prims, uint32_t n, double* out6) {
+  AABB acc;
+  bool first = true;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (prims[i].type != B200RT_PRIM_SPHERE) continue;
+    Sphere s;
+    s.center = v3(prims[i].p); s.radius = prims[i].p[3];
+    AABB b;
+    s.bounding_box(b);
+    acc = first ? b : AABB::surrounding_box(acc, b);
+    first = false;
+  }
+  out6[0] = acc.minimum.x; out6[1] = acc.minimum.y; out6[2] = acc.minimum.z;
+  out6[3] = acc.maximum.x; out6[4] = acc.maximum.y; out6[5] = acc.maximum.z;
+}
+
+// Texture::get_color and Material::scatter probes (distribution tests).
+int oracle_texture_eval(void* scene, int tex, uint64_t n, const double* p_uv /* n x 5: px py pz u v */, double* rgb) {
+  const Scene& sc = *(Scene*)scene;
+  if (tex < 0 || (size_t)tex >= sc.textures.size()) return 1;
+  for (uint64_t i = 0; i < n; ++i) {
+    HitRecord rec;
+    rec.p = Vec3(p_uv[5 * i], p_uv[5 * i + 1], p_uv[5 * i + 2]); rec.u = p_uv[5 * i + 3]; rec.v = p_uv[5 * i + 4];
+    Vec3 c = sc.textures[tex].get_color(rec);
+    rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+  }
+  return 0;
+}
+
+int oracle_thread_count() { return (int)std::thread::hardware_concurrency(); }
+
+}  // extern "C"
