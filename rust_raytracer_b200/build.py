@@ -1,0 +1,71 @@
+"""In-tree build of the CUDA library (sm_100a) and, separately, of the CPU oracle.
+
+`build_library()` compiles rust_raytracer_b200/csrc into rust_raytracer_b200/libb200rt.so with nvcc
+(cross-compiles without a GPU).  `build_oracle()` compiles oracle/oracle.cpp into oracle/liboracle.so; the
+oracle is test infrastructure and is never loaded by the package itself.
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libb200rt.so")
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_LIB = os.path.join(ORACLE_DIR, "liboracle.so")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-shared", "-Xcompiler", "-fPIC,-O3,-Wall", "-Xptxas", "-v", "--use_fast_math=false",
+]
+SOURCES = ["api.cu", "builder.cpp", "loaders.cpp", "scenes.cpp", "scene_compile.cpp"]
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def _deps(directory, extra=()):
+    out = [os.path.join(directory, f) for f in os.listdir(directory) if f.endswith((".cu", ".cuh", ".cpp", ".hpp", ".h"))]
+    return out + list(extra)
+
+
+def build_library(force=False, verbose=False):
+    header = os.path.join(ROOT, "include", "b200rt.h")
+    if not force and not _newer(LIB, _deps(CSRC, [header])):
+        return LIB
+    nvcc = os.environ.get("NVCC", "nvcc")
+    flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"]
+    cmd = [nvcc] + flags + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    log = os.path.join(HERE, "build.log")
+    with open(log, "w") as f:
+        f.write(" ".join(cmd) + "\n" + res.stdout)
+    if verbose or res.returncode != 0:
+        sys.stderr.write(res.stdout)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed (see %s)" % log)
+    return LIB
+
+
+def build_oracle(force=False):
+    src = os.path.join(ORACLE_DIR, "oracle.cpp")
+    header = os.path.join(ROOT, "include", "b200rt.h")
+    if not force and not _newer(ORACLE_LIB, [src, header]):
+        return ORACLE_LIB
+    res = subprocess.run(["make", "-C", ORACLE_DIR, "-B"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout)
+        raise RuntimeError("oracle build failed")
+    return ORACLE_LIB
+
+
+if __name__ == "__main__":
+    build_library(force="--force" in sys.argv, verbose=True)
+    build_oracle(force="--force" in sys.argv)
+    print(LIB)
+    print(ORACLE_LIB)

@@ -1,0 +1,219 @@
+// api.cu — the C ABI of include/b200rt.h: context, scene upload, World::hit batch operator, capture_image
+// (wavefront and megakernel pipelines), tonemap.  Every entry point returns a status; nothing throws across the ABI.
+#include <cstdio>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "scene_compile.hpp"
+#include "wavefront.cuh"
+
+struct b200rt_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaDeviceProp prop;
+  std::string err;
+  // wavefront pool (allocated lazily, reused across renders)
+  WfBuffers wf{};
+  void* wf_block = nullptr;
+  size_t wf_bytes = 0;
+  MegaCounters* mega_cnt = nullptr;
+  WfCounters* host_cnt = nullptr;  // pinned
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+};
+
+struct b200rt_scene {
+  b200rt_ctx* ctx = nullptr;
+  DevScene dev{};
+  void* block = nullptr;  // one allocation holding every table
+  uint64_t h2d_bytes = 0;
+  uint32_t n_nodes = 0, n_prims = 0;
+};
+
+static thread_local std::string g_global_err;
+
+#define CU_CHECK(ctx, call)                                                                                      \
+  do {                                                                                                           \
+    cudaError_t e_ = (call);                                                                                     \
+    if (e_ != cudaSuccess) {                                                                                     \
+      (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                           \
+      return B200RT_ERR_CUDA;                                                                                    \
+    }                                                                                                            \
+  } while (0)
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+extern "C" {
+
+int b200rt_abi_version(void) { return B200RT_ABI_VERSION; }
+const char* b200rt_global_error(void) { return g_global_err.c_str(); }
+const char* b200rt_last_error(const b200rt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_global_err.c_str(); }
+
+int b200rt_device_count(int* count) {
+  if (!count) return B200RT_ERR_INVALID;
+  cudaError_t e = cudaGetDeviceCount(count);
+  if (e != cudaSuccess) { *count = 0; g_global_err = cudaGetErrorString(e); return B200RT_ERR_CUDA; }
+  return B200RT_OK;
+}
+
+int b200rt_ctx_create(int device, b200rt_ctx** out) {
+  if (!out) return B200RT_ERR_INVALID;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    g_global_err = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") + " (this library has no CPU fallback)";
+    return B200RT_ERR_CUDA;
+  }
+  if (device < 0 || device >= n) { g_global_err = "device index out of range"; return B200RT_ERR_INVALID; }
+  b200rt_ctx* c = new (std::nothrow) b200rt_ctx();
+  if (!c) return B200RT_ERR_NOMEM;
+  c->device = device;
+  if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&c->prop, device)) != cudaSuccess ||
+      (e = cudaMalloc(&c->mega_cnt, sizeof(MegaCounters))) != cudaSuccess || (e = cudaMallocHost(&c->host_cnt, sizeof(WfCounters))) != cudaSuccess ||
+      (e = cudaEventCreate(&c->ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev[1])) != cudaSuccess) {
+    g_global_err = std::string("ctx_create: ") + cudaGetErrorString(e);
+    delete c;
+    return B200RT_ERR_CUDA;
+  }
+  *out = c;
+  return B200RT_OK;
+}
+
+int b200rt_ctx_destroy(b200rt_ctx* c) {
+  if (!c) return B200RT_OK;
+  cudaSetDevice(c->device);
+  if (c->wf_block) cudaFree(c->wf_block);
+  if (c->mega_cnt) cudaFree(c->mega_cnt);
+  if (c->host_cnt) cudaFreeHost(c->host_cnt);
+  if (c->ev[0]) cudaEventDestroy(c->ev[0]);
+  if (c->ev[1]) cudaEventDestroy(c->ev[1]);
+  delete c;
+  return B200RT_OK;
+}
+
+int b200rt_ctx_set_stream(b200rt_ctx* c, void* s) {
+  if (!c) return B200RT_ERR_INVALID;
+  c->stream = (cudaStream_t)s;
+  return B200RT_OK;
+}
+
+int b200rt_ctx_device_info(const b200rt_ctx* c, int32_t* sm_count, int32_t* clock_khz, int64_t* l2_bytes, char* name, int name_len) {
+  if (!c) return B200RT_ERR_INVALID;
+  if (sm_count) *sm_count = c->prop.multiProcessorCount;
+  if (clock_khz) { int khz = 0; cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, c->device); *clock_khz = khz; }
+  if (l2_bytes) *l2_bytes = c->prop.l2CacheSize;
+  if (name && name_len > 0) { std::snprintf(name, (size_t)name_len, "%s", c->prop.name); }
+  return B200RT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ scene
+int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_scene** out) {
+  if (!ctx || !desc || !out) return B200RT_ERR_INVALID;
+  *out = nullptr;
+  b200rt::CompiledScene cs;
+  int rc = b200rt::compile_scene(desc, cs, ctx->err);
+  if (rc) return rc;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  struct Part { const void* src; size_t bytes; size_t off; };
+  Part parts[12] = {{cs.nodes.data(), cs.nodes.size() * 4, 0},           {cs.prim_data.data(), cs.prim_data.size() * 4, 0},
+                    {cs.prim_meta.data(), cs.prim_meta.size() * 4, 0},   {cs.tri_normals.data(), cs.tri_normals.size() * 4, 0},
+                    {cs.instances.data(), cs.instances.size() * 4, 0},   {cs.materials.data(), cs.materials.size() * 4, 0},
+                    {cs.textures.data(), cs.textures.size() * 4, 0},     {cs.images.data(), cs.images.size() * 4, 0},
+                    {cs.image_data.data(), cs.image_data.size(), 0},     {cs.perlin_vec.data(), cs.perlin_vec.size() * 4, 0},
+                    {cs.perlin_perm.data(), cs.perlin_perm.size() * 4, 0}, {cs.lights.data(), cs.lights.size() * 4, 0}};
+  size_t total = 0;
+  for (auto& p : parts) { p.off = total; total += align_up(std::max<size_t>(p.bytes, 16), 256); }
+  // stage everything in one pinned buffer -> one H2D copy
+  void* host = nullptr;
+  CU_CHECK(ctx, cudaMallocHost(&host, total));
+  std::memset(host, 0, total);
+  for (auto& p : parts) if (p.bytes) std::memcpy((char*)host + p.off, p.src, p.bytes);
+  b200rt_scene* sc = new (std::nothrow) b200rt_scene();
+  if (!sc) { cudaFreeHost(host); return B200RT_ERR_NOMEM; }
+  cudaError_t e = cudaMalloc(&sc->block, total);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(sc->block, host, total, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFreeHost(host);
+  if (e != cudaSuccess) {
+    ctx->err = std::string("scene upload: ") + cudaGetErrorString(e);
+    if (sc->block) cudaFree(sc->block);
+    delete sc;
+    return e == cudaErrorMemoryAllocation ? B200RT_ERR_NOMEM : B200RT_ERR_CUDA;
+  }
+  char* base = (char*)sc->block;
+  sc->ctx = ctx;
+  sc->dev.nodes = (const float4*)(base + parts[0].off);
+  sc->dev.prim_data = (const float4*)(base + parts[1].off);
+  sc->dev.prim_meta = (const int4*)(base + parts[2].off);
+  sc->dev.tri_normals = (const float4*)(base + parts[3].off);
+  sc->dev.instances = (const float4*)(base + parts[4].off);
+  sc->dev.materials = (const float4*)(base + parts[5].off);
+  sc->dev.textures = (const float4*)(base + parts[6].off);
+  sc->dev.images = (const int4*)(base + parts[7].off);
+  sc->dev.image_data = (const uint8_t*)(base + parts[8].off);
+  sc->dev.perlin_vec = (const float4*)(base + parts[9].off);
+  sc->dev.perlin_perm = (const int*)(base + parts[10].off);
+  sc->dev.lights = (const float4*)(base + parts[11].off);
+  sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0;
+  sc->h2d_bytes = total; sc->n_nodes = cs.n_nodes; sc->n_prims = cs.n_prims;
+  *out = sc;
+  return B200RT_OK;
+}
+
+int b200rt_scene_destroy(b200rt_scene* s) {
+  if (!s) return B200RT_OK;
+  cudaSetDevice(s->ctx->device);
+  if (s->block) cudaFree(s->block);
+  delete s;
+  return B200RT_OK;
+}
+
+int b200rt_scene_info(const b200rt_scene* s, uint64_t* h2d_bytes, uint32_t* bvh_nodes, uint32_t* device_prims) {
+  if (!s) return B200RT_ERR_INVALID;
+  if (h2d_bytes) *h2d_bytes = s->h2d_bytes;
+  if (bvh_nodes) *bvh_nodes = s->n_nodes;
+  if (device_prims) *device_prims = s->n_prims;
+  return B200RT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ World::hit
+int b200rt_intersect_batch_device(b200rt_scene* s, const float* o_time, const float* d_tmax, const uint32_t* medium_seed, uint64_t n, float t_min, b200rt_hit* out) {
+  if (!s || (n && (!o_time || !d_tmax || !out))) return B200RT_ERR_INVALID;
+  if (n == 0) return B200RT_OK;  // empty batch
+  b200rt_ctx* ctx = s->ctx;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  const int threads = 128;
+  unsigned long long want = (n + threads - 1) / threads;
+  unsigned long long cap = (unsigned long long)ctx->prop.multiProcessorCount * 64ull;
+  int blocks = (int)(want < cap ? want : cap);
+  k_intersect_batch<<<blocks, threads, 0, ctx->stream>>>(s->dev, (const float4*)o_time, (const float4*)d_tmax, medium_seed, n, t_min, out);
+  CU_CHECK(ctx, cudaGetLastError());
+  return B200RT_OK;
+}
+
+int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_tmax, const uint32_t* medium_seed, uint64_t n, float t_min, b200rt_hit* out) {
+  if (!s || (n && (!o_time || !d_tmax || !out))) return B200RT_ERR_INVALID;
+  if (n == 0) return B200RT_OK;
+  b200rt_ctx* ctx = s->ctx;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  float *d_o = nullptr, *d_d = nullptr;
+  uint32_t* d_s = nullptr;
+  b200rt_hit* d_h = nullptr;
+  int rc = B200RT_OK;
+  cudaError_t e;
+  auto fail = [&](cudaError_t er) { ctx->err = std::string("intersect_batch: ") + cudaGetErrorString(er); rc = er == cudaErrorMemoryAllocation ? B200RT_ERR_NOMEM : B200RT_ERR_CUDA; };
+  if ((e = cudaMalloc(&d_o, n * 16)) != cudaSuccess || (e = cudaMalloc(&d_d, n * 16)) != cudaSuccess || (e = cudaMalloc(&d_h, n * sizeof(b200rt_hit))) != cudaSuccess ||
+      (medium_seed && (e = cudaMalloc(&d_s, n * 4)) != cudaSuccess)) fail(e);
+  if (!rc && ((e = cudaMemcpyAsync(d_o, o_time, n * 16, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+              (e = cudaMemcpyAsync(d_d, d_tmax, n * 16, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+              (medium_seed && (e = cudaMemcpyAsync(d_s, medium_seed, n * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess))) fail(e);
+  if (!rc) rc = b200rt_intersect_batch_device(s, d_o, d_d, d_s, n, t_min, d_h);
+  if (!rc && ((e = cudaMemcpyAsync(out, d_h, n * sizeof(b200rt_hit), cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess || (e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess)) fail(e);
+  cudaFree(d_o); cudaFree(d_d); cudaFree(d_s); cudaFree(d_h);
+  return rc;
+}
+
+}  // extern "C"
+
+#include "api_render.cuh"

@@ -1,0 +1,207 @@
+// api_render.cuh — Camera::capture_image (camera.rs:66-128) on the device: the host-side control loop of the
+// wavefront pipeline, the megakernel launch, tonemap and the FP32 peak probe.  Included by api.cu.
+#pragma once
+
+static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool) {
+  if (ctx->wf_block && ctx->wf.pool == pool) return B200RT_OK;
+  if (ctx->wf_block) { cudaFree(ctx->wf_block); ctx->wf_block = nullptr; }
+  const size_t P = pool;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
+  size_t o_ray_o = take(P * 16), o_ray_d = take(P * 16), o_hit = take(P * 16), o_sta = take(P * 16), o_stb = take(P * 16);
+  size_t o_qe = take(P * 4), o_qn = take(P * 4), o_qf = take(P * 4), o_qc = take(P * 4 * WF_NCLASS);
+  size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4), o_cnt = take(sizeof(WfCounters));
+  CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
+  char* b = (char*)ctx->wf_block;
+  ctx->wf_bytes = off;
+  ctx->wf.ray_o = (float4*)(b + o_ray_o); ctx->wf.ray_d = (float4*)(b + o_ray_d); ctx->wf.hit = (uint4*)(b + o_hit);
+  ctx->wf.st_a = (float4*)(b + o_sta); ctx->wf.st_b = (uint4*)(b + o_stb);
+  ctx->wf.q_ext = (unsigned int*)(b + o_qe); ctx->wf.q_ext_next = (unsigned int*)(b + o_qn); ctx->wf.q_free = (unsigned int*)(b + o_qf);
+  ctx->wf.q_class = (unsigned int*)(b + o_qc);
+  ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
+  ctx->wf.cnt = (WfCounters*)(b + o_cnt);
+  ctx->wf.pool = pool;
+  return B200RT_OK;
+}
+
+static int validate_params(b200rt_ctx* ctx, const b200rt_params* p) {
+  if (p->width < 2 || p->height < 2) { ctx->err = "width and height must be >= 2 (camera.rs:97-98 divides by w-1, h-1)"; return B200RT_ERR_INVALID; }
+  if ((long long)p->width * p->height > (1ll << 30)) { ctx->err = "image too large"; return B200RT_ERR_INVALID; }
+  if (p->spp_count < 0 || p->spp_begin < 0 || p->max_depth < 0) { ctx->err = "negative spp / depth"; return B200RT_ERR_INVALID; }
+  if (p->integrator < 0 || p->integrator > B200RT_INTEGRATOR_NEE) { ctx->err = "unknown integrator"; return B200RT_ERR_INVALID; }
+  if (p->pipeline < 0 || p->pipeline > B200RT_PIPELINE_MEGAKERNEL) { ctx->err = "unknown pipeline"; return B200RT_ERR_INVALID; }
+  return B200RT_OK;
+}
+
+static RenderConst make_render_const(const b200rt_camera* cam, const b200rt_params* p) {
+  RenderConst P;
+  P.cam = *cam;
+  P.width = p->width; P.height = p->height; P.spp_begin = p->spp_begin; P.spp_count = p->spp_count;
+  P.max_depth = p->max_depth; P.integrator = p->integrator; P.background_mode = p->background_mode; P.flags = p->flags;
+  P.t_min = p->t_min; P.background = make_float3(p->background[0], p->background[1], p->background[2]);
+  P.key = make_uint2((uint32_t)p->seed, (uint32_t)(p->seed >> 32));
+  return P;
+}
+
+static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap& M, float* accum, b200rt_stats* st) {
+  b200rt_ctx* ctx = s->ctx;
+  cudaStream_t q = ctx->stream;
+  unsigned long long want = (M.total + 31ull) & ~31ull;
+  unsigned int pool = (unsigned int)(want < (1ull << 21) ? want : (1ull << 21));
+  int rc = wf_ensure_pool(ctx, pool);
+  if (rc) return rc;
+  WfBuffers B = ctx->wf;
+  CU_CHECK(ctx, cudaMemsetAsync(B.cnt, 0, sizeof(WfCounters), q));
+  const int sms = ctx->prop.multiProcessorCount;
+  int occ_ext = 1, occ_shadow = 1;
+  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend, 128, 0));
+  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow, 128, 0));
+  const int grid_ext = sms * (occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
+  const int grid_gen = sms * 8, grid_shade = sms * 16;
+  uint64_t launches = 0;
+  uint32_t iters = 0;
+  int first = 1;
+  for (;;) {
+    k_wf_control_generate<<<1, 1, 0, q>>>(B, M, first);
+    k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M, first);
+    std::swap(B.q_ext, B.q_ext_next);  // the queue filled by shade + generate becomes the one extend reads
+    k_wf_control_extend<<<1, 1, 0, q>>>(B);
+    k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
+    for (int c = 0; c < WF_NCLASS; ++c) k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, c, accum);
+    launches += 4 + WF_NCLASS;
+    if (P.integrator == B200RT_INTEGRATOR_NEE) {
+      k_wf_control_shadow<<<1, 1, 0, q>>>(B);
+      k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, P.t_min, accum);
+      launches += 2;
+    }
+    CU_CHECK(ctx, cudaGetLastError());
+    CU_CHECK(ctx, cudaMemcpyAsync(ctx->host_cnt, B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, q));
+    CU_CHECK(ctx, cudaStreamSynchronize(q));
+    first = 0;
+    iters++;
+    if (ctx->host_cnt->n_ext_next == 0 && ctx->host_cnt->next_path >= M.total) break;
+    if (iters > 100000000u) { ctx->err = "wavefront loop did not terminate"; return B200RT_ERR_CUDA; }
+  }
+  if (st) {
+    st->extend_rays = ctx->host_cnt->extend_rays; st->shadow_rays = ctx->host_cnt->shadow_rays;
+    st->kernel_launches = launches; st->wavefront_iterations = iters;
+  }
+  return B200RT_OK;
+}
+
+static int render_megakernel(b200rt_scene* s, const RenderConst& P, const PathMap& M, float* accum, b200rt_stats* st) {
+  b200rt_ctx* ctx = s->ctx;
+  cudaStream_t q = ctx->stream;
+  CU_CHECK(ctx, cudaMemsetAsync(ctx->mega_cnt, 0, sizeof(MegaCounters), q));
+  int occ = 1;
+  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_megakernel, 128, 0));
+  const int grid = ctx->prop.multiProcessorCount * (occ > 0 ? occ : 1);
+  k_megakernel<<<grid, 128, 0, q>>>(s->dev, P, M, accum, ctx->mega_cnt);
+  CU_CHECK(ctx, cudaGetLastError());
+  MegaCounters* hc = (MegaCounters*)ctx->host_cnt;
+  CU_CHECK(ctx, cudaMemcpyAsync(hc, ctx->mega_cnt, sizeof(MegaCounters), cudaMemcpyDeviceToHost, q));
+  CU_CHECK(ctx, cudaStreamSynchronize(q));
+  if (st) { st->extend_rays = hc->extend_rays; st->shadow_rays = hc->shadow_rays; st->kernel_launches = 1; st->wavefront_iterations = 0; }
+  return B200RT_OK;
+}
+
+extern "C" {
+
+int b200rt_render_device(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, float* accum_dev, b200rt_stats* stats) {
+  if (!s || !cam || !params || !accum_dev) return B200RT_ERR_INVALID;
+  b200rt_ctx* ctx = s->ctx;
+  int rc = validate_params(ctx, params);
+  if (rc) return rc;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  b200rt_stats local;
+  std::memset(&local, 0, sizeof(local));
+  const RenderConst P = make_render_const(cam, params);
+  const PathMap M = make_path_map(params->width, params->height, params->spp_count);
+  local.paths = M.total;
+  CU_CHECK(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+  if (M.total > 0) {
+    rc = params->pipeline == B200RT_PIPELINE_MEGAKERNEL ? render_megakernel(s, P, M, accum_dev, &local) : render_wavefront(s, P, M, accum_dev, &local);
+    if (rc) return rc;
+    const int npix = params->width * params->height;
+    k_add_count<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(accum_dev, npix, (float)params->spp_count);
+    local.kernel_launches += 1;
+    CU_CHECK(ctx, cudaGetLastError());
+  }
+  CU_CHECK(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  CU_CHECK(ctx, cudaEventSynchronize(ctx->ev[1]));
+  CU_CHECK(ctx, cudaEventElapsedTime(&local.ms_total, ctx->ev[0], ctx->ev[1]));
+  if (stats) *stats = local;
+  return B200RT_OK;
+}
+
+int b200rt_render(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, float* accum_host, b200rt_stats* stats) {
+  if (!s || !cam || !params || !accum_host) return B200RT_ERR_INVALID;
+  b200rt_ctx* ctx = s->ctx;
+  int rc = validate_params(ctx, params);
+  if (rc) return rc;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  const size_t bytes = (size_t)params->width * params->height * 16;
+  float* d = nullptr;
+  cudaError_t e = cudaMalloc(&d, bytes);
+  if (e != cudaSuccess) { ctx->err = std::string("render: ") + cudaGetErrorString(e); return B200RT_ERR_NOMEM; }
+  e = cudaMemsetAsync(d, 0, bytes, ctx->stream);
+  if (e == cudaSuccess) rc = b200rt_render_device(s, cam, params, d, stats);
+  if (e == cudaSuccess && !rc) e = cudaMemcpyAsync(accum_host, d, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && !rc) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) { ctx->err = std::string("render: ") + cudaGetErrorString(e); return B200RT_ERR_CUDA; }
+  return rc;
+}
+
+int b200rt_tonemap_rgb8_device(b200rt_ctx* ctx, const float* accum_dev, int32_t width, int32_t height, uint8_t* rgb_dev) {
+  if (!ctx || !accum_dev || !rgb_dev || width <= 0 || height <= 0) return B200RT_ERR_INVALID;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  const int n = width * height;
+  k_tonemap<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4*)accum_dev, n, rgb_dev);
+  CU_CHECK(ctx, cudaGetLastError());
+  return B200RT_OK;
+}
+
+int b200rt_tonemap_rgb8(b200rt_ctx* ctx, const float* accum_host, int32_t width, int32_t height, uint8_t* rgb_out) {
+  if (!ctx || !accum_host || !rgb_out || width <= 0 || height <= 0) return B200RT_ERR_INVALID;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  const size_t n = (size_t)width * height;
+  float* d = nullptr;
+  uint8_t* o = nullptr;
+  CU_CHECK(ctx, cudaMalloc(&d, n * 16));
+  cudaError_t e = cudaMalloc(&o, n * 3);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d, accum_host, n * 16, cudaMemcpyHostToDevice, ctx->stream);
+  int rc = B200RT_OK;
+  if (e == cudaSuccess) rc = b200rt_tonemap_rgb8_device(ctx, d, width, height, o);
+  if (e == cudaSuccess && !rc) e = cudaMemcpyAsync(rgb_out, o, n * 3, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && !rc) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d); cudaFree(o);
+  if (e != cudaSuccess) { ctx->err = std::string("tonemap: ") + cudaGetErrorString(e); return B200RT_ERR_CUDA; }
+  return rc;
+}
+
+int b200rt_measure_fp32_peak(b200rt_ctx* ctx, double* tflops, double* sm_mhz_effective) {
+  if (!ctx || !tflops) return B200RT_ERR_INVALID;
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  const int sms = ctx->prop.multiProcessorCount, blocks = sms * 8, threads = 256, iters = 4096;
+  float* out = nullptr;
+  CU_CHECK(ctx, cudaMalloc(&out, (size_t)blocks * threads * 4));
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(ctx->ev[0], ctx->stream);
+    k_fma_peak<<<blocks, threads, 0, ctx->stream>>>(out, iters, 1.0000001f, 1e-9f);
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    cudaEventSynchronize(ctx->ev[1]);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    if (rep > 0 && ms < best) best = ms;
+  }
+  cudaFree(out);
+  CU_CHECK(ctx, cudaGetLastError());
+  const double fma = (double)blocks * threads * (double)iters * 64.0;
+  *tflops = 2.0 * fma / (best * 1e-3) / 1e12;
+  if (sm_mhz_effective) *sm_mhz_effective = fma / (best * 1e-3) / ((double)sms * 128.0) / 1e6;
+  return B200RT_OK;
+}
+
+}  // extern "C"

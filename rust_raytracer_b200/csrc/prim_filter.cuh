@@ -1,0 +1,87 @@
+// prim_filter.cuh — f32 candidate filters: each returns true only when the primitive CERTAINLY does not
+// produce a hit in [t_min, t_best] (forward error bounds of the f32 evaluation are subtracted before every
+// comparison, u = 2^-24).  Survivors are decided by prim_exact.cuh.  This is where the FP32 pipe does the bulk
+// of the leaf work; the bounds are generous on purpose (a false "maybe" only costs one exact test).
+#pragma once
+#include "device_math.cuh"
+
+// Per-ray constants shared by all tests.
+struct RayF {
+  float3 o, d, inv;  // inv = 1/d with |d| clamped away from 0 (no NaN in the slab test)
+  float a;           // d . d
+  float time;
+};
+
+DEV float safe_rcp(float d) { return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
+
+// sphere.rs:24-43 in f32: disc error <= ~20u * a * (|oc|^2 + r^2)
+DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best) {
+  float3 oc = r.o - c;
+  float hb = dot(oc, r.d), oc2 = dot(oc, oc), r2 = radius * radius;
+  float cc = oc2 - r2;
+  float disc = hb * hb - r.a * cc;
+  float E = 2e-6f * r.a * (oc2 + r2);
+  if (disc < -E) return true;
+  if (disc > 4.0f * E) {
+    float s = sqrtf(disc), inva = 1.0f / r.a;
+    float dn = (6e-7f * sqrtf(oc2 * r.a) + E / s) * inva;
+    float t0 = (-hb - s) * inva, t1 = (-hb + s) * inva;
+    float e0 = dn + 4e-7f * fabsf(t0), e1 = dn + 4e-7f * fabsf(t1);
+    if (t0 - e0 > t_best) return true;                       // nearest root already beyond the best hit
+    if (t1 + e1 < t_min) return true;                        // sphere entirely behind t_min
+    if (t0 + e0 < t_min && t1 - e1 > t_best) return true;    // origin inside, exit beyond the best hit
+  }
+  return false;
+}
+
+// rectangle.rs:15-26 in f32
+DEV bool rect_reject(const RayF& r, int axis, float a0, float b0, float a1, float b1, float k, float t_min, float t_best) {
+  const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
+  float t = (k - comp(r.o, axis)) / comp(r.d, axis);
+  float e = 3e-7f * fabsf(t);
+  if (t + e < t_min || t - e > t_best) return true;
+  float oa = comp(r.o, ia), da = comp(r.d, ia), ob = comp(r.o, ib), db = comp(r.d, ib);
+  float x = fmaf(t, da, oa), y = fmaf(t, db, ob);
+  float ex = 4e-7f * (fabsf(oa) + fabsf(t * da)) + e * fabsf(da);
+  float ey = 4e-7f * (fabsf(ob) + fabsf(t * db)) + e * fabsf(db);
+  if (x < a0 - ex || x > a1 + ex || y < b0 - ey || y > b1 + ey) return true;
+  return false;  // includes the NaN / parallel case: the exact test decides
+}
+
+// Cube (cube.rs:63-66): the six rectangle hits are exactly the slab entry and exit points.
+DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best) {
+  float3 t0 = (mn - r.o) * r.inv, t1 = (mx - r.o) * r.inv;
+  float tn = fmaxf(fmaxf(fminf(t0.x, t1.x), fminf(t0.y, t1.y)), fminf(t0.z, t1.z));
+  float tf = fminf(fminf(fmaxf(t0.x, t1.x), fmaxf(t0.y, t1.y)), fmaxf(t0.z, t1.z));
+  float en = 1e-6f * fabsf(tn), ef = 1e-6f * fabsf(tf);
+  if (tn - en > tf + ef) return true;
+  if (tf + ef < t_min) return true;
+  if (tn - en > t_best) return true;
+  if (tn + en < t_min && tf - ef > t_best) return true;
+  return false;
+}
+
+// mesh.rs:56-101 in f32 with condition-number-scaled margins (q = |d||e0||e1| / |det|)
+DEV bool tri_reject(const RayF& r, float3 v0, float3 v1, float3 v2, float t_min, float t_best) {
+  float3 e0 = v1 - v0, e1 = v2 - v0;
+  float3 s0 = cross(r.d, e1);
+  float dd = dot(s0, e0);
+  float e0_2 = dot(e0, e0), e1_2 = dot(e1, e1);
+  float scale2 = r.a * e0_2 * e1_2;
+  if (!(dd * dd > 1e-8f * scale2)) return false;  // grazing or degenerate: let the exact test decide
+  float inv = 1.0f / dd;
+  float q = sqrtf(scale2) * fabsf(inv) * 1e-6f;
+  float3 dv = r.o - v0;
+  float dv2 = dot(dv, dv);
+  float b1 = dot(dv, s0) * inv;
+  float db1 = q * (sqrtf(dv2 / e0_2) + fabsf(b1));
+  if (b1 < -db1 || b1 > 1.0f + db1) return true;
+  float3 s1 = cross(dv, e0);
+  float b2 = dot(r.d, s1) * inv;
+  float db2 = q * (sqrtf(dv2 / e1_2) + fabsf(b2));
+  if (b2 < -db2 || b1 + b2 > 1.0f + db1 + db2) return true;
+  float t = dot(e1, s1) * inv;
+  float dt = q * (sqrtf(dv2 / r.a) + fabsf(t));
+  if (t + dt < t_min || t - dt > t_best) return true;
+  return false;
+}

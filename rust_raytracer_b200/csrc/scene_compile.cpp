@@ -1,0 +1,346 @@
+// scene_compile.cpp — host half of b200rt_scene_create: validates the flat tables, bakes instance transforms
+// into world-space primitives (objects/transform.rs:110-148 computes a transformed bounding box per object; here
+// the geometry itself is transformed once, in f64, so the device traverses a single-level BVH), and builds the
+// wide BVH that replaces BVHNode::new (objects/bvh.rs:60-83: random axis + median split).  The builder is a
+// binned-SAH binary build collapsed to 4-wide nodes; topology does not affect closest-hit results.
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <numeric>
+
+#include "scene_compile.hpp"
+
+namespace b200rt {
+
+namespace {
+
+struct Box {
+  float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  void grow(const Box& b) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+  void grow(D3 p) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], (float)std::nextafter((float)p[a], -FLT_MAX)); hi[a] = std::max(hi[a], (float)std::nextafter((float)p[a], FLT_MAX)); } }
+  float area() const {
+    float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    if (dx < 0 || dy < 0 || dz < 0) return 0;
+    return 2 * (dx * dy + dy * dz + dz * dx);
+  }
+  // Conservative padding: the f32 slab test and the f32 candidate filters carry ~1e-6 relative error, while
+  // rectangles/triangles touch their bounds exactly (the reference pads by 1e-4 / 0.1, rectangle.rs:36, mesh.rs:33).
+  void pad() {
+    float m = 0;
+    for (int a = 0; a < 3; ++a) m = std::max(m, std::max(std::fabs(lo[a]), std::fabs(hi[a])));
+    float e = 1e-5f * m + 1e-7f;
+    for (int a = 0; a < 3; ++a) { lo[a] -= e; hi[a] += e; }
+  }
+};
+
+struct BinNode {
+  Box box;
+  int left = -1, right = -1;  // children (binary) or -1
+  int first = 0, count = 0;   // leaf range
+};
+
+struct BinBuilder {
+  const std::vector<Box>& pb;
+  std::vector<D3> centroid;
+  std::vector<int> order;
+  std::vector<BinNode> nodes;
+  explicit BinBuilder(const std::vector<Box>& boxes) : pb(boxes) {
+    order.resize(pb.size());
+    std::iota(order.begin(), order.end(), 0);
+    centroid.resize(pb.size());
+    for (size_t i = 0; i < pb.size(); ++i) centroid[i] = D3(0.5 * ((double)pb[i].lo[0] + pb[i].hi[0]), 0.5 * ((double)pb[i].lo[1] + pb[i].hi[1]), 0.5 * ((double)pb[i].lo[2] + pb[i].hi[2]));
+  }
+  int build(int first, int count) {
+    int id = (int)nodes.size();
+    nodes.emplace_back();
+    Box box, cbox;
+    for (int i = first; i < first + count; ++i) { box.grow(pb[order[i]]); D3 c = centroid[order[i]]; for (int a = 0; a < 3; ++a) { cbox.lo[a] = std::min(cbox.lo[a], (float)c[a]); cbox.hi[a] = std::max(cbox.hi[a], (float)c[a]); } }
+    nodes[id].box = box;
+    if (count == 1) { nodes[id].first = first; nodes[id].count = count; return id; }
+    // binned SAH over the three axes
+    const int NB = 16;
+    float best_cost = FLT_MAX; int best_axis = -1, best_split = -1;
+    for (int axis = 0; axis < 3; ++axis) {
+      float ext = cbox.hi[axis] - cbox.lo[axis];
+      if (!(ext > 0)) continue;
+      Box bins[NB]; int cnt[NB] = {0};
+      float k = NB * (1 - 1e-6f) / ext;
+      for (int i = first; i < first + count; ++i) {
+        int bi = std::min(NB - 1, std::max(0, (int)(((float)centroid[order[i]][axis] - cbox.lo[axis]) * k)));
+        bins[bi].grow(pb[order[i]]); cnt[bi]++;
+      }
+      float right_area[NB]; int right_cnt[NB];
+      Box acc; int c = 0;
+      for (int i = NB - 1; i > 0; --i) { acc.grow(bins[i]); c += cnt[i]; right_area[i] = acc.area(); right_cnt[i] = c; }
+      Box lacc; int lc = 0;
+      for (int i = 0; i < NB - 1; ++i) {
+        lacc.grow(bins[i]); lc += cnt[i];
+        if (lc == 0 || right_cnt[i + 1] == 0) continue;
+        float cost = lacc.area() * lc + right_area[i + 1] * right_cnt[i + 1];
+        if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = i; }
+      }
+    }
+    float leaf_cost = box.area() * count;
+    if (count <= B200RT_MAX_LEAF && (best_axis < 0 || best_cost >= leaf_cost)) { nodes[id].first = first; nodes[id].count = count; return id; }
+    int mid;
+    if (best_axis < 0) {  // all centroids coincide: split the range in the middle
+      mid = first + count / 2;
+    } else {
+      float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
+      float k = NB * (1 - 1e-6f) / ext;
+      auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](int p) {
+        int bi = std::min(NB - 1, std::max(0, (int)(((float)centroid[p][best_axis] - cbox.lo[best_axis]) * k)));
+        return bi <= best_split;
+      });
+      mid = (int)(it - order.begin());
+      if (mid == first || mid == first + count) mid = first + count / 2;
+    }
+    int l = build(first, mid - first);
+    int r = build(mid, first + count - mid);
+    nodes[id].left = l; nodes[id].right = r;
+    return id;
+  }
+};
+
+void put4(std::vector<float>& v, size_t at, float a, float b, float c, float d) { v[at] = a; v[at + 1] = b; v[at + 2] = c; v[at + 3] = d; }
+float ibits(int32_t i) { float f; std::memcpy(&f, &i, 4); return f; }
+float ubits(uint32_t i) { float f; std::memcpy(&f, &i, 4); return f; }
+
+// Collapse the binary tree into BVH4 nodes (128 B each); returns the node index.
+int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out) {
+  int my = (int)(out.size() / 32);
+  out.resize(out.size() + 32, 0.f);
+  int kids[4]; int nk = 0;
+  const BinNode& root = bb.nodes[bin_id];
+  if (root.left < 0) { kids[nk++] = bin_id; }
+  else {
+    kids[nk++] = root.left; kids[nk++] = root.right;
+    while (nk < 4) {
+      int best = -1; float best_area = -1;
+      for (int i = 0; i < nk; ++i) {
+        const BinNode& c = bb.nodes[kids[i]];
+        if (c.left >= 0 && c.box.area() > best_area) { best_area = c.box.area(); best = i; }
+      }
+      if (best < 0) break;
+      int c = kids[best];
+      kids[best] = bb.nodes[c].left;
+      kids[nk++] = bb.nodes[c].right;
+    }
+  }
+  int32_t refs[4] = {B200RT_CHILD_EMPTY, B200RT_CHILD_EMPTY, B200RT_CHILD_EMPTY, B200RT_CHILD_EMPTY};
+  float lo[3][4], hi[3][4];
+  for (int a = 0; a < 3; ++a) for (int i = 0; i < 4; ++i) { lo[a][i] = FLT_MAX; hi[a][i] = -FLT_MAX; }
+  for (int i = 0; i < nk; ++i) {
+    const BinNode& c = bb.nodes[kids[i]];
+    for (int a = 0; a < 3; ++a) { lo[a][i] = c.box.lo[a]; hi[a][i] = c.box.hi[a]; }
+    if (c.left < 0) refs[i] = (int32_t)(B200RT_LEAF_BIT | ((uint32_t)(c.count - 1) << 27) | (uint32_t)c.first);
+    else refs[i] = collapse(bb, kids[i], out);
+  }
+  size_t at = (size_t)my * 32;
+  for (int a = 0; a < 3; ++a) { put4(out, at + 4 * a, lo[a][0], lo[a][1], lo[a][2], lo[a][3]); put4(out, at + 12 + 4 * a, hi[a][0], hi[a][1], hi[a][2], hi[a][3]); }
+  put4(out, at + 24, ibits(refs[0]), ibits(refs[1]), ibits(refs[2]), ibits(refs[3]));
+  return my;
+}
+
+}  // namespace
+
+int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& err) {
+  if (!d) { err = "null scene desc"; return B200RT_ERR_INVALID; }
+  if (d->n_prims == 0) { err = "scene has no primitives (BVHNode::new on an empty list)"; return B200RT_ERR_INVALID; }
+  if (d->n_prims >= (1u << 27)) { err = "too many primitives"; return B200RT_ERR_UNSUPPORTED; }
+  if (!d->prims || !d->materials || !d->textures) { err = "null table pointer"; return B200RT_ERR_INVALID; }
+  const uint32_t n = d->n_prims;
+  // ---- validate tables
+  for (uint32_t i = 0; i < d->n_textures; ++i) {
+    const b200rt_texture& t = d->textures[i];
+    if (t.type < 0 || t.type > B200RT_TEX_NOISE) { err = "unknown texture type"; return B200RT_ERR_INVALID; }
+    if (t.type == B200RT_TEX_IMAGE) {
+      if (t.image < 0 || (uint32_t)t.image >= d->n_images || !d->images || !d->image_rgb8) { err = "image index out of range"; return B200RT_ERR_INVALID; }
+      const b200rt_image& im = d->images[t.image];
+      if (im.width <= 0 || im.height <= 0 || im.offset < 0 || (uint64_t)im.offset + (uint64_t)3 * im.width * im.height > d->image_bytes) { err = "image outside the blob"; return B200RT_ERR_INVALID; }
+    }
+    if (t.type == B200RT_TEX_NOISE && !d->perlin) { err = "NOISE texture without perlin tables"; return B200RT_ERR_INVALID; }
+  }
+  for (uint32_t i = 0; i < d->n_materials; ++i) {
+    const b200rt_material& m = d->materials[i];
+    if (m.type < 0 || m.type > B200RT_MAT_ISOTROPIC) { err = "unknown material type"; return B200RT_ERR_INVALID; }
+    if (m.texture < 0 || (uint32_t)m.texture >= d->n_textures) { err = "texture index out of range"; return B200RT_ERR_INVALID; }
+  }
+  // ---- instances: linear parts of M and M^-1
+  std::vector<Affine> M(d->n_instances), Minv(d->n_instances);
+  cs.instances.assign((size_t)d->n_instances * 24, 0.f);
+  for (uint32_t i = 0; i < d->n_instances; ++i) {
+    std::memcpy(M[i].m, d->instances[i].m, sizeof(M[i].m));
+    if (!M[i].inverse(Minv[i])) { err = "Invalid transform matrix"; return B200RT_ERR_INVALID; }  // transform.rs:146
+    for (int r = 0; r < 3; ++r) {
+      put4(cs.instances, (size_t)i * 24 + 4 * r, (float)M[i].m[4 * r], (float)M[i].m[4 * r + 1], (float)M[i].m[4 * r + 2], 0);
+      put4(cs.instances, (size_t)i * 24 + 12 + 4 * r, (float)Minv[i].m[4 * r], (float)Minv[i].m[4 * r + 1], (float)Minv[i].m[4 * r + 2], 0);
+    }
+  }
+  // ---- bake primitives to world space
+  std::vector<float> data((size_t)n * 12, 0.f);
+  std::vector<Box> boxes(n);
+  for (uint32_t i = 0; i < n; ++i) {
+    const b200rt_prim& p = d->prims[i];
+    if (p.material < 0 || (uint32_t)p.material >= d->n_materials) { err = "material index out of range"; return B200RT_ERR_INVALID; }
+    if (p.instance >= (int32_t)d->n_instances) { err = "instance index out of range"; return B200RT_ERR_INVALID; }
+    const bool inst = p.instance >= 0;
+    const Affine A = inst ? M[p.instance] : Affine::identity();
+    float* o = &data[(size_t)i * 12];
+    Box& bx = boxes[i];
+    switch (p.type) {
+      case B200RT_PRIM_SPHERE: case B200RT_PRIM_MEDIUM_SPHERE: case B200RT_PRIM_MOVING_SPHERE: {
+        double s = inst ? A.similarity_scale() : 1.0;
+        if (s == 0) { err = "sphere under a non-similarity transform"; return B200RT_ERR_UNSUPPORTED; }
+        D3 c = A.point(D3(p.p));
+        double r = s * p.p[3];
+        if (!(r > 0)) { err = "sphere radius must be positive"; return B200RT_ERR_INVALID; }
+        o[0] = (float)c.x; o[1] = (float)c.y; o[2] = (float)c.z; o[3] = (float)r;
+        double rr = (double)o[3] * (1 + 1e-6);
+        bx.grow(D3(o[0] - rr, o[1] - rr, o[2] - rr)); bx.grow(D3(o[0] + rr, o[1] + rr, o[2] + rr));
+        if (p.type == B200RT_PRIM_MOVING_SPHERE) {
+          D3 c1 = A.point(D3(p.p + 4));
+          float c1f[3] = {(float)c1.x, (float)c1.y, (float)c1.z};
+          if (!(p.p[8] > p.p[7])) { err = "moving sphere needs time1 > time0"; return B200RT_ERR_INVALID; }
+          o[4] = c1f[0]; o[5] = c1f[1]; o[6] = c1f[2]; o[7] = p.p[7]; o[8] = p.p[8];
+          bx.grow(D3(c1f[0] - rr, c1f[1] - rr, c1f[2] - rr)); bx.grow(D3(c1f[0] + rr, c1f[1] + rr, c1f[2] + rr));
+        } else if (p.type == B200RT_PRIM_MEDIUM_SPHERE) {
+          if (!(p.p[4] > 0)) { err = "medium density must be positive"; return B200RT_ERR_INVALID; }
+          o[4] = (float)(-1.0 / ((double)p.p[4]));
+          // a distance of d object units is s*d world units: density scales by 1/s
+          if (inst) o[4] = (float)(-s / (double)p.p[4]);
+        }
+        break;
+      }
+      case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
+        if (inst && !A.is_positive_diagonal()) { err = "axis rectangle under a rotating transform (the builder emits triangles)"; return B200RT_ERR_UNSUPPORTED; }
+        const int axis = p.type == B200RT_PRIM_XY_RECT ? 2 : (p.type == B200RT_PRIM_XZ_RECT ? 1 : 0);
+        const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
+        double lo[3], hi[3];
+        lo[ia] = p.p[0]; lo[ib] = p.p[1]; hi[ia] = p.p[2]; hi[ib] = p.p[3]; lo[axis] = hi[axis] = p.p[4];
+        D3 l = A.point(D3(lo)), h = A.point(D3(hi));
+        o[0] = (float)l[ia]; o[1] = (float)l[ib]; o[2] = (float)h[ia]; o[3] = (float)h[ib]; o[4] = (float)l[axis];
+        if (!(o[2] > o[0]) || !(o[3] > o[1])) { err = "degenerate rectangle"; return B200RT_ERR_INVALID; }
+        double q0[3], q1[3];
+        q0[ia] = o[0]; q0[ib] = o[1]; q0[axis] = o[4]; q1[ia] = o[2]; q1[ib] = o[3]; q1[axis] = o[4];
+        bx.grow(D3(q0)); bx.grow(D3(q1));
+        break;
+      }
+      case B200RT_PRIM_BOX: case B200RT_PRIM_MEDIUM_BOX: {
+        if (inst && !A.is_positive_diagonal()) { err = "box under a rotating transform (the builder emits triangles)"; return B200RT_ERR_UNSUPPORTED; }
+        D3 l = A.point(D3(p.p)), h = A.point(D3(p.p + 3));
+        o[0] = (float)l.x; o[1] = (float)l.y; o[2] = (float)l.z; o[4] = (float)h.x; o[5] = (float)h.y; o[6] = (float)h.z;
+        if (!(o[4] > o[0]) || !(o[5] > o[1]) || !(o[6] > o[2])) { err = "degenerate box"; return B200RT_ERR_INVALID; }
+        if (p.type == B200RT_PRIM_MEDIUM_BOX) {
+          if (!(p.p[6] > 0)) { err = "medium density must be positive"; return B200RT_ERR_INVALID; }
+          if (inst && !(A.m[0] == A.m[5] && A.m[5] == A.m[10])) { err = "medium box under a non-uniform scale"; return B200RT_ERR_UNSUPPORTED; }
+          o[7] = (float)(-(inst ? A.m[0] : 1.0) / (double)p.p[6]);
+        }
+        bx.grow(D3(o[0], o[1], o[2])); bx.grow(D3(o[4], o[5], o[6]));
+        break;
+      }
+      case B200RT_PRIM_TRIANGLE: {
+        if (p.aux < 0 || (uint32_t)p.aux >= d->n_tri_normals || !d->tri_normals) { err = "triangle without vertex normals (mesh.rs:62-64 would panic)"; return B200RT_ERR_INVALID; }
+        for (int v = 0; v < 3; ++v) {
+          D3 w = A.point(D3(p.p + 3 * v));
+          o[4 * v] = (float)w.x; o[4 * v + 1] = (float)w.y; o[4 * v + 2] = (float)w.z;
+          bx.grow(D3(o[4 * v], o[4 * v + 1], o[4 * v + 2]));
+        }
+        break;
+      }
+      default: err = "unknown primitive type"; return B200RT_ERR_INVALID;
+    }
+    for (int a = 0; a < 3; ++a) if (!std::isfinite(bx.lo[a]) || !std::isfinite(bx.hi[a])) { err = "non-finite primitive"; return B200RT_ERR_INVALID; }
+    bx.pad();
+  }
+  // ---- BVH (skipped for the flat-list arm: hit.rs:56-67 scans linearly)
+  cs.flat = (d->flags & B200RT_SCENE_FLAT_LIST) != 0;
+  std::vector<int> order(n);
+  std::iota(order.begin(), order.end(), 0);
+  cs.nodes.clear();
+  if (!cs.flat) {
+    BinBuilder bb(boxes);
+    bb.nodes.reserve(2 * (size_t)n);
+    int root = bb.build(0, (int)n);
+    cs.nodes.reserve((size_t)n * 16);
+    collapse(bb, root, cs.nodes);
+    order = bb.order;
+  } else {
+    cs.nodes.assign(32, 0.f);
+  }
+  cs.n_nodes = (uint32_t)(cs.nodes.size() / 32);
+  cs.n_prims = n;
+  cs.prim_data.resize((size_t)n * 12);
+  cs.prim_meta.resize((size_t)n * 4);
+  std::vector<int> dev_of(n);
+  for (uint32_t k = 0; k < n; ++k) {
+    int i = order[k];
+    dev_of[i] = (int)k;
+    const b200rt_prim& p = d->prims[i];
+    const float* src = &data[(size_t)i * 12];
+    float* dst = &cs.prim_data[(size_t)k * 12];
+    switch (p.type) {
+      case B200RT_PRIM_SPHERE: put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]); break;
+      case B200RT_PRIM_MOVING_SPHERE:
+        put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]);
+        put4(cs.prim_data, (size_t)k * 12 + 4, src[4], src[5], src[6], 0);  // c1 (absolute)
+        dst[8] = src[7]; dst[9] = src[8];
+        break;
+      case B200RT_PRIM_MEDIUM_SPHERE: put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]); dst[4] = src[4]; break;
+      case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT:
+        put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]); dst[4] = src[4]; break;
+      case B200RT_PRIM_BOX: case B200RT_PRIM_MEDIUM_BOX:
+        put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], 0); put4(cs.prim_data, (size_t)k * 12 + 4, src[4], src[5], src[6], src[7]); break;
+      case B200RT_PRIM_TRIANGLE: std::memcpy(dst, src, 12 * sizeof(float)); break;
+    }
+    cs.prim_meta[(size_t)k * 4 + 0] = p.type | (p.material << 8);
+    cs.prim_meta[(size_t)k * 4 + 1] = i;
+    cs.prim_meta[(size_t)k * 4 + 2] = p.instance;
+    cs.prim_meta[(size_t)k * 4 + 3] = p.aux;
+  }
+  // ---- the remaining tables
+  cs.tri_normals.assign((size_t)std::max(1u, d->n_tri_normals) * 12, 0.f);
+  for (uint32_t i = 0; i < d->n_tri_normals; ++i)
+    for (int v = 0; v < 3; ++v) put4(cs.tri_normals, (size_t)i * 12 + 4 * v, d->tri_normals[9 * (size_t)i + 3 * v], d->tri_normals[9 * (size_t)i + 3 * v + 1], d->tri_normals[9 * (size_t)i + 3 * v + 2], 0);
+  cs.materials.assign((size_t)d->n_materials * 4, 0.f);
+  for (uint32_t i = 0; i < d->n_materials; ++i) put4(cs.materials, (size_t)i * 4, ibits(d->materials[i].type), ibits(d->materials[i].texture), d->materials[i].param, 0);
+  cs.textures.assign((size_t)d->n_textures * 12, 0.f);
+  for (uint32_t i = 0; i < d->n_textures; ++i) {
+    const b200rt_texture& t = d->textures[i];
+    put4(cs.textures, (size_t)i * 12, ibits(t.type), ibits(t.image), t.scale, 0);
+    put4(cs.textures, (size_t)i * 12 + 4, t.c0[0], t.c0[1], t.c0[2], 0);
+    put4(cs.textures, (size_t)i * 12 + 8, t.c1[0], t.c1[1], t.c1[2], 0);
+  }
+  cs.images.assign((size_t)std::max(1u, d->n_images) * 4, 0);
+  for (uint32_t i = 0; i < d->n_images; ++i) { cs.images[4 * i] = d->images[i].offset; cs.images[4 * i + 1] = d->images[i].width; cs.images[4 * i + 2] = d->images[i].height; }
+  cs.image_data.assign(d->image_rgb8, d->image_rgb8 + d->image_bytes);
+  if (cs.image_data.empty()) cs.image_data.resize(4, 0);
+  cs.perlin_vec.assign(256 * 4, 0.f);
+  cs.perlin_perm.assign(3 * 256, 0);
+  if (d->perlin) {
+    for (int i = 0; i < 256; ++i) put4(cs.perlin_vec, (size_t)i * 4, d->perlin->ranvec[i][0], d->perlin->ranvec[i][1], d->perlin->ranvec[i][2], 0);
+    for (int i = 0; i < 256; ++i) { cs.perlin_perm[i] = d->perlin->perm_x[i] & 255; cs.perlin_perm[256 + i] = d->perlin->perm_y[i] & 255; cs.perlin_perm[512 + i] = d->perlin->perm_z[i] & 255; }
+  }
+  cs.n_lights = d->n_lights;
+  cs.lights.assign((size_t)std::max(1u, d->n_lights) * 12, 0.f);
+  for (uint32_t i = 0; i < d->n_lights; ++i) {
+    int pi = d->light_prims[i];
+    if (pi < 0 || (uint32_t)pi >= n) { err = "light index out of range"; return B200RT_ERR_INVALID; }
+    const b200rt_prim& p = d->prims[pi];
+    if (p.instance >= 0) { err = "transformed lights are not sampled"; return B200RT_ERR_UNSUPPORTED; }
+    size_t at = (size_t)i * 12;
+    if (p.type == B200RT_PRIM_SPHERE) {
+      put4(cs.lights, at, ibits(0), ibits(pi), ibits(0), ibits(p.material));
+      put4(cs.lights, at + 4, p.p[0], p.p[1], p.p[2], p.p[3]);
+    } else if (p.type == B200RT_PRIM_XY_RECT || p.type == B200RT_PRIM_XZ_RECT || p.type == B200RT_PRIM_YZ_RECT) {
+      int axis = p.type == B200RT_PRIM_XY_RECT ? 2 : (p.type == B200RT_PRIM_XZ_RECT ? 1 : 0);
+      put4(cs.lights, at, ibits(1), ibits(pi), ibits(axis), ibits(p.material));
+      put4(cs.lights, at + 4, p.p[0], p.p[1], p.p[2], p.p[3]);
+      put4(cs.lights, at + 8, p.p[4], (p.p[2] - p.p[0]) * (p.p[3] - p.p[1]), 0, 0);
+    } else { err = "only sphere and axis-rectangle lights are sampled"; return B200RT_ERR_UNSUPPORTED; }
+  }
+  (void)ubits;
+  return B200RT_OK;
+}
+
+}  // namespace b200rt

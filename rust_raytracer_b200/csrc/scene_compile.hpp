@@ -1,0 +1,31 @@
+// scene_compile.hpp — host-side compiled scene (what b200rt_scene_create uploads).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "device_scene.h"
+#include "host_common.hpp"
+
+namespace b200rt {
+
+struct CompiledScene {
+  std::vector<float> nodes;        // 32 floats per BVH4 node
+  std::vector<float> prim_data;    // 12 floats per prim (leaf order)
+  std::vector<int32_t> prim_meta;  // 4 ints per prim
+  std::vector<float> tri_normals;  // 12 floats per entry
+  std::vector<float> instances;    // 24 floats per instance
+  std::vector<float> materials;    // 4 floats
+  std::vector<float> textures;     // 12 floats
+  std::vector<int32_t> images;     // 4 ints
+  std::vector<uint8_t> image_data;
+  std::vector<float> perlin_vec;   // 256 x 4
+  std::vector<int32_t> perlin_perm;  // 3 x 256
+  std::vector<float> lights;       // 12 floats per light
+  uint32_t n_prims = 0, n_nodes = 0, n_lights = 0;
+  bool flat = false;
+};
+
+// Validates, bakes and builds; returns a B200RT_* status and fills err.
+int compile_scene(const b200rt_scene_desc* d, CompiledScene& out, std::string& err);
+
+}  // namespace b200rt
