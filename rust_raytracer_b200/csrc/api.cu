@@ -20,6 +20,7 @@ struct b200rt_ctx {
   MegaCounters* mega_cnt = nullptr;
   WfCounters* host_cnt = nullptr;  // pinned
   cudaEvent_t ev[2] = {nullptr, nullptr};
+  cudaEvent_t sev[8] = {};  // stage events: generate, extend, shade, shadow (begin/end)
 };
 
 struct b200rt_scene {
@@ -76,6 +77,12 @@ int b200rt_ctx_create(int device, b200rt_ctx** out) {
     delete c;
     return B200RT_ERR_CUDA;
   }
+  for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->sev[i]);
+  if (e != cudaSuccess) {
+    g_global_err = std::string("ctx_create: ") + cudaGetErrorString(e);
+    delete c;
+    return B200RT_ERR_CUDA;
+  }
   *out = c;
   return B200RT_OK;
 }
@@ -88,6 +95,7 @@ int b200rt_ctx_destroy(b200rt_ctx* c) {
   if (c->host_cnt) cudaFreeHost(c->host_cnt);
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
+  for (int i = 0; i < 8; ++i) if (c->sev[i]) cudaEventDestroy(c->sev[i]);
   delete c;
   return B200RT_OK;
 }
@@ -116,12 +124,14 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
   if (rc) return rc;
   CU_CHECK(ctx, cudaSetDevice(ctx->device));
   struct Part { const void* src; size_t bytes; size_t off; };
-  Part parts[12] = {{cs.nodes.data(), cs.nodes.size() * 4, 0},           {cs.prim_data.data(), cs.prim_data.size() * 4, 0},
+  Part parts[15] = {{cs.nodes.data(), cs.nodes.size() * 4, 0},           {cs.prim_data.data(), cs.prim_data.size() * 4, 0},
                     {cs.prim_meta.data(), cs.prim_meta.size() * 4, 0},   {cs.tri_normals.data(), cs.tri_normals.size() * 4, 0},
                     {cs.instances.data(), cs.instances.size() * 4, 0},   {cs.materials.data(), cs.materials.size() * 4, 0},
                     {cs.textures.data(), cs.textures.size() * 4, 0},     {cs.images.data(), cs.images.size() * 4, 0},
                     {cs.image_data.data(), cs.image_data.size(), 0},     {cs.perlin_vec.data(), cs.perlin_vec.size() * 4, 0},
-                    {cs.perlin_perm.data(), cs.perlin_perm.size() * 4, 0}, {cs.lights.data(), cs.lights.size() * 4, 0}};
+                    {cs.perlin_perm.data(), cs.perlin_perm.size() * 4, 0}, {cs.lights.data(), cs.lights.size() * 4, 0},
+                    {cs.prim_obj.data(), cs.prim_obj.size() * 4, 0},     {cs.instances_d.data(), cs.instances_d.size() * 8, 0},
+                    {cs.inst_eps.data(), cs.inst_eps.size() * 4, 0}};
   size_t total = 0;
   for (auto& p : parts) { p.off = total; total += align_up(std::max<size_t>(p.bytes, 16), 256); }
   // stage everything in one pinned buffer -> one H2D copy
@@ -155,6 +165,9 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
   sc->dev.perlin_vec = (const float4*)(base + parts[9].off);
   sc->dev.perlin_perm = (const int*)(base + parts[10].off);
   sc->dev.lights = (const float4*)(base + parts[11].off);
+  sc->dev.prim_obj = (const float4*)(base + parts[12].off);
+  sc->dev.instances_d = (const double*)(base + parts[13].off);
+  sc->dev.inst_eps = (const float*)(base + parts[14].off);
   sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0;
   sc->h2d_bytes = total; sc->n_nodes = cs.n_nodes; sc->n_prims = cs.n_prims;
   *out = sc;

@@ -61,27 +61,42 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   uint64_t launches = 0;
   uint32_t iters = 0;
   int first = 1;
+  float ms_stage[4] = {0.f, 0.f, 0.f, 0.f};
+  const bool nee = P.integrator == B200RT_INTEGRATOR_NEE;
   for (;;) {
+    cudaEventRecord(ctx->sev[0], q);
     k_wf_control_generate<<<1, 1, 0, q>>>(B, M, first);
     k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M, first);
     std::swap(B.q_ext, B.q_ext_next);  // the queue filled by shade + generate becomes the one extend reads
     k_wf_control_extend<<<1, 1, 0, q>>>(B);
+    cudaEventRecord(ctx->sev[1], q);
+    cudaEventRecord(ctx->sev[2], q);
     k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
+    cudaEventRecord(ctx->sev[3], q);
+    cudaEventRecord(ctx->sev[4], q);
     for (int c = 0; c < WF_NCLASS; ++c) k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, c, accum);
+    cudaEventRecord(ctx->sev[5], q);
     launches += 4 + WF_NCLASS;
-    if (P.integrator == B200RT_INTEGRATOR_NEE) {
+    if (nee) {
+      cudaEventRecord(ctx->sev[6], q);
       k_wf_control_shadow<<<1, 1, 0, q>>>(B);
       k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, P.t_min, accum);
+      cudaEventRecord(ctx->sev[7], q);
       launches += 2;
     }
     CU_CHECK(ctx, cudaGetLastError());
     CU_CHECK(ctx, cudaMemcpyAsync(ctx->host_cnt, B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, q));
     CU_CHECK(ctx, cudaStreamSynchronize(q));
+    for (int k = 0; k < (nee ? 4 : 3); ++k) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, ctx->sev[2 * k], ctx->sev[2 * k + 1]) == cudaSuccess) ms_stage[k] += ms;
+    }
     first = 0;
     iters++;
     if (ctx->host_cnt->n_ext_next == 0 && ctx->host_cnt->next_path >= M.total) break;
     if (iters > 100000000u) { ctx->err = "wavefront loop did not terminate"; return B200RT_ERR_CUDA; }
   }
+  if (st) { st->ms_generate = ms_stage[0]; st->ms_extend = ms_stage[1]; st->ms_shade = ms_stage[2]; st->ms_shadow = ms_stage[3]; }
   if (st) {
     st->extend_rays = ctx->host_cnt->extend_rays; st->shadow_rays = ctx->host_cnt->shadow_rays;
     st->kernel_launches = launches; st->wavefront_iterations = iters;
@@ -130,6 +145,8 @@ int b200rt_render_device(b200rt_scene* s, const b200rt_camera* cam, const b200rt
   CU_CHECK(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
   CU_CHECK(ctx, cudaEventSynchronize(ctx->ev[1]));
   CU_CHECK(ctx, cudaEventElapsedTime(&local.ms_total, ctx->ev[0], ctx->ev[1]));
+  local.ms_other = local.ms_total - local.ms_generate - local.ms_extend - local.ms_shade - local.ms_shadow;
+  if (params->pipeline == B200RT_PIPELINE_MEGAKERNEL) { local.ms_extend = local.ms_total; local.ms_other = 0.f; }
   if (stats) *stats = local;
   return B200RT_OK;
 }

@@ -39,6 +39,9 @@ struct DevScene {
   const int4* prim_meta;
   const float4* tri_normals;
   const float4* instances;
+  const float4* prim_obj;     // 3 x float4 per prim: OBJECT-space data of instanced prims (same layout as prim_data)
+  const double* instances_d;  // 24 doubles per instance: M (3x4 row-major), M^-1 (3x4)
+  const float* inst_eps;      // per instance: absolute f32 rounding error of the baked world-space coordinates
   const float4* materials;
   const float4* textures;
   const int4* images;

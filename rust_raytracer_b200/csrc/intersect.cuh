@@ -43,64 +43,105 @@ DEV RayD make_rayd(const Ray& r) {
   return d;
 }
 
-// One leaf primitive: filter in f32, confirm in f64.  Updates h when the primitive hits in [t_min, h.t].
+// Transform::hit (transform.rs:152-155): the ray in OBJECT space, o' = M^-1 * o (point), d' = M^-1 * d (direction),
+// evaluated in f64 with the reference's operation order (nalgebra mat-vec, vec3.rs:174-184).
+DEV d3 affine_point(const double* m, d3 p) {
+  return D3(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(m[0], p.x), __dmul_rn(m[1], p.y)), __dmul_rn(m[2], p.z)), m[3]),
+            __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(m[4], p.x), __dmul_rn(m[5], p.y)), __dmul_rn(m[6], p.z)), m[7]),
+            __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(m[8], p.x), __dmul_rn(m[9], p.y)), __dmul_rn(m[10], p.z)), m[11]));
+}
+DEV d3 affine_dir(const double* m, d3 p) {
+  return D3(__dadd_rn(__dadd_rn(__dmul_rn(m[0], p.x), __dmul_rn(m[1], p.y)), __dmul_rn(m[2], p.z)),
+            __dadd_rn(__dadd_rn(__dmul_rn(m[4], p.x), __dmul_rn(m[5], p.y)), __dmul_rn(m[6], p.z)),
+            __dadd_rn(__dadd_rn(__dmul_rn(m[8], p.x), __dmul_rn(m[9], p.y)), __dmul_rn(m[10], p.z)));
+}
+DEV RayD to_object(const DevScene& S, int inst, const RayD& w) {
+  const double* minv = S.instances_d + 24 * (size_t)inst + 12;
+  RayD r;
+  r.o = affine_point(minv, w.o); r.d = affine_dir(minv, w.d); r.time = w.time;
+  return r;
+}
+
+// One leaf primitive: filter in f32 on the world-space (baked) record, confirm in f64 on the ORIGINAL record
+// (object space for instanced primitives, exactly like Transform::hit).  Updates h when the primitive hits in
+// [t_min, h.t].
 DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, float t_min, float& t_best32, HitRaw& h) {
   const int4 meta = __ldg(&S.prim_meta[k]);
   const int type = meta.x & 0xff;
+  const bool inst = meta.z >= 0;
+  const float eps = inst ? __ldg(&S.inst_eps[meta.z]) : 0.f;
   const float4 A = __ldg(&S.prim_data[3 * k]);
-  double t;
-  int aux = 0;
-  switch (type) {
-    case B200RT_PRIM_SPHERE: {
-      if (sphere_reject(rf, f3(A), A.w, t_min, t_best32)) return;
-      RayD rd = make_rayd(ray);
-      if (!sphere_exact(rd, D3(A), (double)A.w, (double)t_min, h.t, t)) return;
+  switch (type) {  // ---- f32 filter (certain misses only)
+    case B200RT_PRIM_SPHERE:
+      if (sphere_reject(rf, f3(A), A.w, t_min, t_best32, eps)) return;
       break;
-    }
-    case B200RT_PRIM_MOVING_SPHERE: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      const float4 C = __ldg(&S.prim_data[3 * k + 2]);
-      RayD rd = make_rayd(ray);
-      d3 c = moving_center(D3(A), D3(B), (double)C.x, (double)C.y, rd.time);
-      if (!sphere_exact(rd, c, (double)A.w, (double)t_min, h.t, t)) return;
-      break;
-    }
     case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
       const float4 B = __ldg(&S.prim_data[3 * k + 1]);
       const int axis = type == B200RT_PRIM_XY_RECT ? 2 : (type == B200RT_PRIM_XZ_RECT ? 1 : 0);
-      if (rect_reject(rf, axis, A.x, A.y, A.z, A.w, B.x, t_min, t_best32)) return;
-      RayD rd = make_rayd(ray);
-      double pa, pb;
-      if (!rect_exact(rd, axis, (double)A.x, (double)A.y, (double)A.z, (double)A.w, (double)B.x, (double)t_min, h.t, t, pa, pb)) return;
+      if (rect_reject(rf, axis, A.x, A.y, A.z, A.w, B.x, t_min, t_best32, eps)) return;
       break;
     }
     case B200RT_PRIM_BOX: {
       const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      if (box_reject(rf, f3(A), f3(B), t_min, t_best32)) return;
-      RayD rd = make_rayd(ray);
-      if (!cube_exact(rd, D3(A), D3(B), (double)t_min, h.t, t, aux)) return;
+      if (box_reject(rf, f3(A), f3(B), t_min, t_best32, eps)) return;
+      break;
+    }
+    case B200RT_PRIM_MEDIUM_BOX: {
+      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
+      if (box_reject(rf, f3(A), f3(B), -3.0e38f, t_best32, eps)) return;
       break;
     }
     case B200RT_PRIM_TRIANGLE: {
       const float4 B = __ldg(&S.prim_data[3 * k + 1]);
       const float4 C = __ldg(&S.prim_data[3 * k + 2]);
-      if (tri_reject(rf, f3(A), f3(B), f3(C), t_min, t_best32)) return;
-      RayD rd = make_rayd(ray);
+      if (tri_reject(rf, f3(A), f3(B), f3(C), t_min, t_best32, eps)) return;
+      break;
+    }
+    default: break;  // moving spheres and sphere media go straight to the exact test
+  }
+  // ---- f64 decision
+  RayD rd = make_rayd(ray);
+  const float4* rec = S.prim_data + 3 * (size_t)k;
+  if (inst) { rd = to_object(S, meta.z, rd); rec = S.prim_obj + 3 * (size_t)k; }
+  const float4 EA = inst ? __ldg(rec) : A;
+  double t;
+  int aux = 0;
+  switch (type) {
+    case B200RT_PRIM_SPHERE:
+      if (!sphere_exact(rd, D3(EA), (double)EA.w, (double)t_min, h.t, t)) return;
+      break;
+    case B200RT_PRIM_MOVING_SPHERE: {
+      const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
+      d3 c = moving_center(D3(EA), D3(B), (double)C.x, (double)C.y, rd.time);
+      if (!sphere_exact(rd, c, (double)EA.w, (double)t_min, h.t, t)) return;
+      break;
+    }
+    case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
+      const float4 B = __ldg(rec + 1);
+      const int axis = type == B200RT_PRIM_XY_RECT ? 2 : (type == B200RT_PRIM_XZ_RECT ? 1 : 0);
+      double pa, pb;
+      if (!rect_exact(rd, axis, (double)EA.x, (double)EA.y, (double)EA.z, (double)EA.w, (double)B.x, (double)t_min, h.t, t, pa, pb)) return;
+      break;
+    }
+    case B200RT_PRIM_BOX: {
+      const float4 B = __ldg(rec + 1);
+      if (!cube_exact(rd, D3(EA), D3(B), (double)t_min, h.t, t, aux)) return;
+      break;
+    }
+    case B200RT_PRIM_TRIANGLE: {
+      const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
       double b1, b2;
-      if (!tri_exact(rd, D3(A), D3(B), D3(C), (double)t_min, h.t, t, b1, b2)) return;
+      if (!tri_exact(rd, D3(EA), D3(B), D3(C), (double)t_min, h.t, t, b1, b2)) return;
       break;
     }
     case B200RT_PRIM_MEDIUM_SPHERE: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      RayD rd = make_rayd(ray);
-      if (!medium_exact(rd, 0, D3(A), D3(A), (double)A.w, (double)B.x, medium_xi(ray.mseed, (uint32_t)meta.y), (double)t_min, h.t, t)) return;
+      const float4 B = __ldg(rec + 1);
+      if (!medium_exact(rd, 0, D3(EA), D3(EA), (double)EA.w, (double)B.x, medium_xi(ray.mseed, (uint32_t)meta.y), (double)t_min, h.t, t)) return;
       break;
     }
     case B200RT_PRIM_MEDIUM_BOX: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      if (box_reject(rf, f3(A), f3(B), -3.0e38f, t_best32)) return;
-      RayD rd = make_rayd(ray);
-      if (!medium_exact(rd, 1, D3(A), D3(B), 0.0, (double)B.w, medium_xi(ray.mseed, (uint32_t)meta.y), (double)t_min, h.t, t)) return;
+      const float4 B = __ldg(rec + 1);
+      if (!medium_exact(rd, 1, D3(EA), D3(B), 0.0, (double)B.w, medium_xi(ray.mseed, (uint32_t)meta.y), (double)t_min, h.t, t)) return;
       break;
     }
     default: return;
@@ -168,35 +209,33 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
   }
 }
 
-DEV float3 mat3_mul(const float4* rows, float3 v) { return f3(dot(f3(__ldg(rows)), v), dot(f3(__ldg(rows + 1)), v), dot(f3(__ldg(rows + 2)), v)); }
-DEV float3 mat3_tmul(const float4* rows, float3 v) {
-  float3 r0 = f3(__ldg(rows)), r1 = f3(__ldg(rows + 1)), r2 = f3(__ldg(rows + 2));
-  return f3(r0.x * v.x + r1.x * v.y + r2.x * v.z, r0.y * v.x + r1.y * v.y + r2.y * v.z, r0.z * v.x + r1.z * v.y + r2.z * v.z);
-}
-
 DEV void sphere_uv(d3 n, float& u, float& v) {  // sphere.rs:16-20
   double theta = acos(-n.y), phi = atan2(-n.z, n.x) + PI_D;
   u = (float)(phi * (1.0 / PI_D) * 0.5);
   v = (float)(theta * (1.0 / PI_D));
 }
+DEV d3 dunit(d3 v) { return v / sqrt(ddot(v, v)); }  // Vec3::unit (vec3.rs:86-91)
 
 // HitRecord::new (hit.rs:17-39) for the winning primitive; WANT_UV = false skips the sphere uv (acos/atan2).
+// Instanced primitives follow Transform::hit (transform.rs:151-165): the record is built in OBJECT space, then
+// p = M p', n_out = M n' (not the inverse transpose) and front_face = d' . n_out < 0 with the OBJECT-space d'.
 DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo& out, const bool WANT_UV) {
   const int k = h.prim;
   const int4 meta = __ldg(&S.prim_meta[k]);
   const int type = meta.x & 0xff;
+  const bool inst = meta.z >= 0;
   out.type = type; out.material = meta.x >> 8; out.prim_orig = meta.y; out.t = (float)h.t;
   out.u = 0.f; out.v = 0.f;
-  const RayD rd = make_rayd(ray);
+  RayD rd = make_rayd(ray);
+  const float4* rec = S.prim_data + 3 * (size_t)k;
+  if (inst) { rd = to_object(S, meta.z, rd); rec = S.prim_obj + 3 * (size_t)k; }
   const d3 p = dat(rd.o, h.t, rd.d);
-  out.p = to_f3(p);
-  const float4 A = __ldg(&S.prim_data[3 * k]);
-  d3 on;  // outward normal in WORLD space (object space == world space unless instanced)
+  const float4 A = __ldg(rec);
+  d3 on;  // outward normal in the primitive's own space
   switch (type) {
     case B200RT_PRIM_SPHERE: on = (p - D3(A)) / (double)A.w; break;
     case B200RT_PRIM_MOVING_SPHERE: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      const float4 C = __ldg(&S.prim_data[3 * k + 2]);
+      const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
       on = (p - moving_center(D3(A), D3(B), (double)C.x, (double)C.y, rd.time)) / (double)A.w;
       break;
     }
@@ -209,7 +248,7 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
       break;
     }
     case B200RT_PRIM_BOX: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
+      const float4 B = __ldg(rec + 1);
       int axis; double a0, b0, a1, b1, kk;
       cube_side(h.aux, D3(A), D3(B), axis, a0, b0, a1, b1, kk);
       const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
@@ -219,40 +258,30 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
       break;
     }
     case B200RT_PRIM_TRIANGLE: {  // mesh.rs:102-104: normalised barycentric blend of the vertex normals
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      const float4 C = __ldg(&S.prim_data[3 * k + 2]);
+      const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
       double t, b1 = 0, b2 = 0;
       tri_exact(rd, D3(A), D3(B), D3(C), -DINF, DINF, t, b1, b2);
-      const double b0 = 1.0 - b1 - b2;
+      const double b0 = __dsub_rn(__dsub_rn(1.0, b1), b2);
       const float4* nn = S.tri_normals + 3 * (size_t)meta.w;
-      d3 n = b0 * D3(__ldg(nn)) + b1 * D3(__ldg(nn + 1)) + b2 * D3(__ldg(nn + 2));
-      on = n / sqrt(ddot(n, n));  // OBJECT space when instanced (handled below)
+      on = dunit(b0 * D3(__ldg(nn)) + b1 * D3(__ldg(nn + 1)) + b2 * D3(__ldg(nn + 2)));
       break;
     }
     default: on = D3(1., 0., 0.); break;  // ConstantMedium: arbitrary normal (medium.rs:47)
   }
-  if (meta.z < 0) {
-    const bool front = ddot(rd.d, on) < 0.;
-    d3 n = front ? on : -on;
-    n = n / sqrt(ddot(n, n));  // hit.rs:33
+  if (WANT_UV && (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE)) sphere_uv(on, out.u, out.v);
+  const bool front = ddot(rd.d, on) < 0.;  // hit.rs:25
+  d3 n = dunit(front ? on : -on);           // hit.rs:26-33
+  if (!inst) {
     out.front_face = front ? 1 : 0;
     out.n = to_f3(n);
-    if (WANT_UV && (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE)) sphere_uv(on, out.u, out.v);
+    out.p = to_f3(p);
     return;
   }
-  // Transform::hit (transform.rs:151-165): the child record is built against the OBJECT-space ray d' = M^-1 d,
-  // then n_out = M * n' (not the inverse transpose) and front_face = d' . n_out < 0.
-  const float4* Mrows = S.instances + 6 * (size_t)meta.z;
-  const float3 dprime = mat3_mul(Mrows + 3, ray.d);
-  float3 nobj;
-  if (type == B200RT_PRIM_TRIANGLE || type == B200RT_PRIM_MEDIUM_SPHERE || type == B200RT_PRIM_MEDIUM_BOX) nobj = to_f3(on);
-  else if (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE) nobj = normalize(mat3_tmul(Mrows, to_f3(on)));  // similarity: R^T n
-  else nobj = to_f3(on);  // axis shapes under a positive diagonal matrix keep their axis normal
-  if (WANT_UV && (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE)) sphere_uv(D3(nobj), out.u, out.v);
-  const bool front_obj = dot(dprime, nobj) < 0.f;
-  const float3 nff = front_obj ? nobj : -nobj;
-  const float3 outward = mat3_mul(Mrows, nff);
-  const bool front = dot(dprime, outward) < 0.f;
-  out.front_face = front ? 1 : 0;
-  out.n = front ? normalize(outward) : -normalize(outward);
+  const double* m = S.instances_d + 24 * (size_t)meta.z;
+  const d3 outward = affine_dir(m, n);  // transform.rs:158
+  out.p = to_f3(affine_point(m, p));    // transform.rs:159
+  const bool ff = ddot(rd.d, outward) < 0.;  // transform.rs:160 -> hit.rs:41-48, against the OBJECT-space ray
+  const d3 un = dunit(outward);
+  out.front_face = ff ? 1 : 0;
+  out.n = to_f3(ff ? un : -un);
 }

@@ -15,16 +15,18 @@ struct RayF {
 DEV float safe_rcp(float d) { return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
 
 // sphere.rs:24-43 in f32: disc error <= ~20u * a * (|oc|^2 + r^2)
-DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best) {
+// eps: absolute error of the baked world-space coordinates of an instanced primitive (0 when not instanced):
+// the exact test then runs in OBJECT space on the original values, so the filter must tolerate the baking error.
+DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best, float eps) {
   float3 oc = r.o - c;
   float hb = dot(oc, r.d), oc2 = dot(oc, oc), r2 = radius * radius;
   float cc = oc2 - r2;
   float disc = hb * hb - r.a * cc;
-  float E = 2e-6f * r.a * (oc2 + r2);
+  float E = 2e-6f * r.a * (oc2 + r2) + r.a * eps * (8.0f * sqrtf(oc2) + 4.0f * radius);
   if (disc < -E) return true;
   if (disc > 4.0f * E) {
     float s = sqrtf(disc), inva = 1.0f / r.a;
-    float dn = (6e-7f * sqrtf(oc2 * r.a) + E / s) * inva;
+    float dn = (6e-7f * sqrtf(oc2 * r.a) + E / s + 2.0f * eps * sqrtf(r.a)) * inva;
     float t0 = (-hb - s) * inva, t1 = (-hb + s) * inva;
     float e0 = dn + 4e-7f * fabsf(t0), e1 = dn + 4e-7f * fabsf(t1);
     if (t0 - e0 > t_best) return true;                       // nearest root already beyond the best hit
@@ -35,25 +37,26 @@ DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float
 }
 
 // rectangle.rs:15-26 in f32
-DEV bool rect_reject(const RayF& r, int axis, float a0, float b0, float a1, float b1, float k, float t_min, float t_best) {
+DEV bool rect_reject(const RayF& r, int axis, float a0, float b0, float a1, float b1, float k, float t_min, float t_best, float eps) {
   const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
   float t = (k - comp(r.o, axis)) / comp(r.d, axis);
-  float e = 3e-7f * fabsf(t);
+  float e = 3e-7f * fabsf(t) + 2.0f * eps / fabsf(comp(r.d, axis));
   if (t + e < t_min || t - e > t_best) return true;
   float oa = comp(r.o, ia), da = comp(r.d, ia), ob = comp(r.o, ib), db = comp(r.d, ib);
   float x = fmaf(t, da, oa), y = fmaf(t, db, ob);
-  float ex = 4e-7f * (fabsf(oa) + fabsf(t * da)) + e * fabsf(da);
-  float ey = 4e-7f * (fabsf(ob) + fabsf(t * db)) + e * fabsf(db);
+  float ex = 4e-7f * (fabsf(oa) + fabsf(t * da)) + e * fabsf(da) + 2.0f * eps;
+  float ey = 4e-7f * (fabsf(ob) + fabsf(t * db)) + e * fabsf(db) + 2.0f * eps;
   if (x < a0 - ex || x > a1 + ex || y < b0 - ey || y > b1 + ey) return true;
   return false;  // includes the NaN / parallel case: the exact test decides
 }
 
 // Cube (cube.rs:63-66): the six rectangle hits are exactly the slab entry and exit points.
-DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best) {
+DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best, float eps) {
   float3 t0 = (mn - r.o) * r.inv, t1 = (mx - r.o) * r.inv;
   float tn = fmaxf(fmaxf(fminf(t0.x, t1.x), fminf(t0.y, t1.y)), fminf(t0.z, t1.z));
   float tf = fminf(fminf(fmaxf(t0.x, t1.x), fmaxf(t0.y, t1.y)), fmaxf(t0.z, t1.z));
-  float en = 1e-6f * fabsf(tn), ef = 1e-6f * fabsf(tf);
+  float es = eps > 0.f ? 2.0f * eps * fmaxf(fabsf(r.inv.x), fmaxf(fabsf(r.inv.y), fabsf(r.inv.z))) : 0.f;
+  float en = 1e-6f * fabsf(tn) + es, ef = 1e-6f * fabsf(tf) + es;
   if (tn - en > tf + ef) return true;
   if (tf + ef < t_min) return true;
   if (tn - en > t_best) return true;
@@ -62,7 +65,7 @@ DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_be
 }
 
 // mesh.rs:56-101 in f32 with condition-number-scaled margins (q = |d||e0||e1| / |det|)
-DEV bool tri_reject(const RayF& r, float3 v0, float3 v1, float3 v2, float t_min, float t_best) {
+DEV bool tri_reject(const RayF& r, float3 v0, float3 v1, float3 v2, float t_min, float t_best, float eps) {
   float3 e0 = v1 - v0, e1 = v2 - v0;
   float3 s0 = cross(r.d, e1);
   float dd = dot(s0, e0);
@@ -70,7 +73,10 @@ DEV bool tri_reject(const RayF& r, float3 v0, float3 v1, float3 v2, float t_min,
   float scale2 = r.a * e0_2 * e1_2;
   if (!(dd * dd > 1e-8f * scale2)) return false;  // grazing or degenerate: let the exact test decide
   float inv = 1.0f / dd;
-  float q = sqrtf(scale2) * fabsf(inv) * 1e-6f;
+  float cond = sqrtf(scale2) * fabsf(inv);
+  float rel = eps * rsqrtf(fminf(e0_2, e1_2));  // baking error relative to the shorter edge
+  if (cond * rel > 0.05f) return false;
+  float q = cond * (1e-6f + 8.0f * rel);
   float3 dv = r.o - v0;
   float dv2 = dot(dv, dv);
   float b1 = dot(dv, s0) * inv;

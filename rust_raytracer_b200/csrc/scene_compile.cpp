@@ -168,17 +168,21 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
   }
   // ---- instances: linear parts of M and M^-1
   std::vector<Affine> M(d->n_instances), Minv(d->n_instances);
-  cs.instances.assign((size_t)d->n_instances * 24, 0.f);
+  cs.instances.assign((size_t)std::max(1u, d->n_instances) * 24, 0.f);
+  cs.instances_d.assign((size_t)std::max(1u, d->n_instances) * 24, 0.0);
+  cs.inst_eps.assign((size_t)std::max(1u, d->n_instances), 0.f);
   for (uint32_t i = 0; i < d->n_instances; ++i) {
     std::memcpy(M[i].m, d->instances[i].m, sizeof(M[i].m));
     if (!M[i].inverse(Minv[i])) { err = "Invalid transform matrix"; return B200RT_ERR_INVALID; }  // transform.rs:146
+    std::memcpy(&cs.instances_d[(size_t)i * 24], M[i].m, sizeof(M[i].m));
+    std::memcpy(&cs.instances_d[(size_t)i * 24 + 12], Minv[i].m, sizeof(Minv[i].m));
     for (int r = 0; r < 3; ++r) {
       put4(cs.instances, (size_t)i * 24 + 4 * r, (float)M[i].m[4 * r], (float)M[i].m[4 * r + 1], (float)M[i].m[4 * r + 2], 0);
       put4(cs.instances, (size_t)i * 24 + 12 + 4 * r, (float)Minv[i].m[4 * r], (float)Minv[i].m[4 * r + 1], (float)Minv[i].m[4 * r + 2], 0);
     }
   }
   // ---- bake primitives to world space
-  std::vector<float> data((size_t)n * 12, 0.f);
+  std::vector<float> data((size_t)n * 12, 0.f), objdata((size_t)n * 12, 0.f);
   std::vector<Box> boxes(n);
   for (uint32_t i = 0; i < n; ++i) {
     const b200rt_prim& p = d->prims[i];
@@ -251,6 +255,23 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
       default: err = "unknown primitive type"; return B200RT_ERR_INVALID;
     }
     for (int a = 0; a < 3; ++a) if (!std::isfinite(bx.lo[a]) || !std::isfinite(bx.hi[a])) { err = "non-finite primitive"; return B200RT_ERR_INVALID; }
+    if (inst) {
+      // object-space record in the same intermediate layout (the exact test runs there, on the original values)
+      float* q = &objdata[(size_t)i * 12];
+      switch (p.type) {
+        case B200RT_PRIM_SPHERE: case B200RT_PRIM_MOVING_SPHERE: for (int k = 0; k < 9; ++k) q[k] = p.p[k]; break;
+        case B200RT_PRIM_MEDIUM_SPHERE: for (int k = 0; k < 4; ++k) q[k] = p.p[k]; q[4] = (float)(-1.0 / (double)p.p[4]); break;
+        case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: for (int k = 0; k < 5; ++k) q[k] = p.p[k]; break;
+        case B200RT_PRIM_BOX: case B200RT_PRIM_MEDIUM_BOX:
+          q[0] = p.p[0]; q[1] = p.p[1]; q[2] = p.p[2]; q[4] = p.p[3]; q[5] = p.p[4]; q[6] = p.p[5];
+          if (p.type == B200RT_PRIM_MEDIUM_BOX) q[7] = (float)(-1.0 / (double)p.p[6]);
+          break;
+        case B200RT_PRIM_TRIANGLE: for (int v = 0; v < 3; ++v) for (int c = 0; c < 3; ++c) q[4 * v + c] = p.p[3 * v + c]; break;
+      }
+      float m = 0;
+      for (int a = 0; a < 3; ++a) m = std::max(m, std::max(std::fabs(bx.lo[a]), std::fabs(bx.hi[a])));
+      cs.inst_eps[p.instance] = std::max(cs.inst_eps[p.instance], 1.3e-7f * m);  // ~2u |coord|: rounding of M*x to f32 (+ f64 slop)
+    }
     bx.pad();
   }
   // ---- BVH (skipped for the flat-list arm: hit.rs:56-67 scans linearly)
@@ -270,29 +291,33 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
   }
   cs.n_nodes = (uint32_t)(cs.nodes.size() / 32);
   cs.n_prims = n;
-  cs.prim_data.resize((size_t)n * 12);
+  cs.prim_data.assign((size_t)n * 12, 0.f);
+  cs.prim_obj.assign(d->n_instances ? (size_t)n * 12 : 12, 0.f);
   cs.prim_meta.resize((size_t)n * 4);
   std::vector<int> dev_of(n);
+  auto pack = [](std::vector<float>& out, size_t k, int type, const float* src) {
+    float* dst = &out[k * 12];
+    switch (type) {
+      case B200RT_PRIM_SPHERE: put4(out, k * 12, src[0], src[1], src[2], src[3]); break;
+      case B200RT_PRIM_MOVING_SPHERE:
+        put4(out, k * 12, src[0], src[1], src[2], src[3]);
+        put4(out, k * 12 + 4, src[4], src[5], src[6], 0);  // c1 (absolute)
+        dst[8] = src[7]; dst[9] = src[8];
+        break;
+      case B200RT_PRIM_MEDIUM_SPHERE: put4(out, k * 12, src[0], src[1], src[2], src[3]); dst[4] = src[4]; break;
+      case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT:
+        put4(out, k * 12, src[0], src[1], src[2], src[3]); dst[4] = src[4]; break;
+      case B200RT_PRIM_BOX: case B200RT_PRIM_MEDIUM_BOX:
+        put4(out, k * 12, src[0], src[1], src[2], 0); put4(out, k * 12 + 4, src[4], src[5], src[6], src[7]); break;
+      case B200RT_PRIM_TRIANGLE: std::memcpy(dst, src, 12 * sizeof(float)); break;
+    }
+  };
   for (uint32_t k = 0; k < n; ++k) {
     int i = order[k];
     dev_of[i] = (int)k;
     const b200rt_prim& p = d->prims[i];
-    const float* src = &data[(size_t)i * 12];
-    float* dst = &cs.prim_data[(size_t)k * 12];
-    switch (p.type) {
-      case B200RT_PRIM_SPHERE: put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]); break;
-      case B200RT_PRIM_MOVING_SPHERE:
-        put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]);
-        put4(cs.prim_data, (size_t)k * 12 + 4, src[4], src[5], src[6], 0);  // c1 (absolute)
-        dst[8] = src[7]; dst[9] = src[8];
-        break;
-      case B200RT_PRIM_MEDIUM_SPHERE: put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]); dst[4] = src[4]; break;
-      case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT:
-        put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], src[3]); dst[4] = src[4]; break;
-      case B200RT_PRIM_BOX: case B200RT_PRIM_MEDIUM_BOX:
-        put4(cs.prim_data, (size_t)k * 12, src[0], src[1], src[2], 0); put4(cs.prim_data, (size_t)k * 12 + 4, src[4], src[5], src[6], src[7]); break;
-      case B200RT_PRIM_TRIANGLE: std::memcpy(dst, src, 12 * sizeof(float)); break;
-    }
+    pack(cs.prim_data, k, p.type, &data[(size_t)i * 12]);
+    if (p.instance >= 0) pack(cs.prim_obj, k, p.type, &objdata[(size_t)i * 12]);
     cs.prim_meta[(size_t)k * 4 + 0] = p.type | (p.material << 8);
     cs.prim_meta[(size_t)k * 4 + 1] = i;
     cs.prim_meta[(size_t)k * 4 + 2] = p.instance;

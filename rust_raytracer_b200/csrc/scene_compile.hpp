@@ -14,6 +14,9 @@ struct CompiledScene {
   std::vector<int32_t> prim_meta;  // 4 ints per prim
   std::vector<float> tri_normals;  // 12 floats per entry
   std::vector<float> instances;    // 24 floats per instance
+  std::vector<float> prim_obj;     // 12 floats per prim (object-space twin of prim_data; instanced scenes only)
+  std::vector<double> instances_d; // 24 doubles per instance: M, M^-1
+  std::vector<float> inst_eps;     // per instance
   std::vector<float> materials;    // 4 floats
   std::vector<float> textures;     // 12 floats
   std::vector<int32_t> images;     // 4 ints
