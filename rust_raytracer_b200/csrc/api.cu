@@ -1,6 +1,7 @@
 // api.cu — the C ABI of include/b200rt.h: context, scene upload, World::hit batch operator, capture_image
 // (wavefront and megakernel pipelines), tonemap.  Every entry point returns a status; nothing throws across the ABI.
 #include <cstdio>
+#include <cstdlib>
 #include <new>
 #include <string>
 #include <vector>
@@ -20,7 +21,7 @@ struct b200rt_ctx {
   MegaCounters* mega_cnt = nullptr;
   WfCounters* host_cnt = nullptr;  // pinned
   cudaEvent_t ev[2] = {nullptr, nullptr};
-  cudaEvent_t sev[8] = {};  // stage events: generate, extend, shade, shadow (begin/end)
+  cudaEvent_t sev[64] = {};  // stage events: up to 8 iterations in flight x (generate, extend, shade, shadow) x (begin, end)
 };
 
 struct b200rt_scene {
@@ -77,7 +78,7 @@ int b200rt_ctx_create(int device, b200rt_ctx** out) {
     delete c;
     return B200RT_ERR_CUDA;
   }
-  for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->sev[i]);
+  for (int i = 0; i < 64 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->sev[i]);
   if (e != cudaSuccess) {
     g_global_err = std::string("ctx_create: ") + cudaGetErrorString(e);
     delete c;
@@ -95,7 +96,7 @@ int b200rt_ctx_destroy(b200rt_ctx* c) {
   if (c->host_cnt) cudaFreeHost(c->host_cnt);
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
-  for (int i = 0; i < 8; ++i) if (c->sev[i]) cudaEventDestroy(c->sev[i]);
+  for (int i = 0; i < 64; ++i) if (c->sev[i]) cudaEventDestroy(c->sev[i]);
   delete c;
   return B200RT_OK;
 }
@@ -168,7 +169,7 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
   sc->dev.prim_obj = (const float4*)(base + parts[12].off);
   sc->dev.instances_d = (const double*)(base + parts[13].off);
   sc->dev.inst_eps = (const float*)(base + parts[14].off);
-  sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0;
+  sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_bvh_prims = (int)cs.n_bvh_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0;
   sc->h2d_bytes = total; sc->n_nodes = cs.n_nodes; sc->n_prims = cs.n_prims;
   *out = sc;
   return B200RT_OK;
@@ -228,5 +229,14 @@ int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_
 }
 
 }  // extern "C"
+
+#ifdef B200RT_COUNTERS
+extern "C" int b200rt_debug_counters(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, g_dbg, sizeof(unsigned long long) * 16);
+  if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_dbg, z, sizeof(z)); }
+  return 0;
+}
+#endif
 
 #include "api_render.cuh"

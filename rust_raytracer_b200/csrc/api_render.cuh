@@ -43,61 +43,78 @@ static RenderConst make_render_const(const b200rt_camera* cam, const b200rt_para
   return P;
 }
 
+static int env_int(const char* name, int dflt, int lo, int hi) {
+  const char* v = std::getenv(name);
+  if (!v || !*v) return dflt;
+  int x = std::atoi(v);
+  return x < lo ? lo : (x > hi ? hi : x);
+}
+
+// Host control loop of the wavefront pipeline.  Iterations are enqueued in batches (no host round trip inside a
+// batch: the control kernels turn the counters over on the device); the counters are polled once per batch.
 static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap& M, float* accum, b200rt_stats* st) {
   b200rt_ctx* ctx = s->ctx;
   cudaStream_t q = ctx->stream;
+  const unsigned long long cap = 1ull << env_int("B200RT_WF_POOL_LOG2", 21, 12, 24);
   unsigned long long want = (M.total + 31ull) & ~31ull;
-  unsigned int pool = (unsigned int)(want < (1ull << 21) ? want : (1ull << 21));
+  unsigned int pool = (unsigned int)(want < cap ? want : cap);
   int rc = wf_ensure_pool(ctx, pool);
   if (rc) return rc;
   WfBuffers B = ctx->wf;
   CU_CHECK(ctx, cudaMemsetAsync(B.cnt, 0, sizeof(WfCounters), q));
   const int sms = ctx->prop.multiProcessorCount;
-  int occ_ext = 1, occ_shadow = 1;
+  int occ_ext = 1, occ_shadow = 1, occ_shade = 1;
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend, 128, 0));
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow, 128, 0));
+  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade, 128, 0));
   const int grid_ext = sms * (occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
-  const int grid_gen = sms * 8, grid_shade = sms * 16;
+  const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", (occ_shade > 0 ? occ_shade : 1) * 2, 1, 64);
+  const int batch = env_int("B200RT_WF_BATCH", 4, 1, 8);
+  const bool shade_split = env_int("B200RT_WF_SHADE_SPLIT", 0, 0, 1) != 0;
   uint64_t launches = 0;
   uint32_t iters = 0;
   int first = 1;
   float ms_stage[4] = {0.f, 0.f, 0.f, 0.f};
   const bool nee = P.integrator == B200RT_INTEGRATOR_NEE;
   for (;;) {
-    cudaEventRecord(ctx->sev[0], q);
-    k_wf_control_generate<<<1, 1, 0, q>>>(B, M, first);
-    k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M, first);
-    std::swap(B.q_ext, B.q_ext_next);  // the queue filled by shade + generate becomes the one extend reads
-    k_wf_control_extend<<<1, 1, 0, q>>>(B);
-    cudaEventRecord(ctx->sev[1], q);
-    cudaEventRecord(ctx->sev[2], q);
-    k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
-    cudaEventRecord(ctx->sev[3], q);
-    cudaEventRecord(ctx->sev[4], q);
-    for (int c = 0; c < WF_NCLASS; ++c) k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, c, accum);
-    cudaEventRecord(ctx->sev[5], q);
-    launches += 4 + WF_NCLASS;
-    if (nee) {
-      cudaEventRecord(ctx->sev[6], q);
-      k_wf_control_shadow<<<1, 1, 0, q>>>(B);
-      k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, P.t_min, accum);
-      cudaEventRecord(ctx->sev[7], q);
-      launches += 2;
+    for (int b = 0; b < batch; ++b) {
+      cudaEvent_t* ev = ctx->sev + 8 * b;
+      cudaEventRecord(ev[0], q);
+      k_wf_control_generate<<<1, 1, 0, q>>>(B, M, first);
+      k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M, first);
+      std::swap(B.q_ext, B.q_ext_next);  // the queue filled by shade + generate becomes the one extend reads
+      k_wf_control_extend<<<1, 1, 0, q>>>(B);
+      cudaEventRecord(ev[1], q);
+      k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
+      cudaEventRecord(ev[2], q);
+      if (shade_split) { for (int c = 0; c < WF_NCLASS; ++c) k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum, c); launches += WF_NCLASS - 1; }
+      else k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum, -1);
+      cudaEventRecord(ev[3], q);
+      launches += 5;
+      if (nee) {
+        k_wf_control_shadow<<<1, 1, 0, q>>>(B);
+        k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, P.t_min, accum);
+        cudaEventRecord(ev[4], q);
+        launches += 2;
+      }
+      first = 0;
+      iters++;
     }
     CU_CHECK(ctx, cudaGetLastError());
     CU_CHECK(ctx, cudaMemcpyAsync(ctx->host_cnt, B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, q));
     CU_CHECK(ctx, cudaStreamSynchronize(q));
-    for (int k = 0; k < (nee ? 4 : 3); ++k) {
-      float ms = 0.f;
-      if (cudaEventElapsedTime(&ms, ctx->sev[2 * k], ctx->sev[2 * k + 1]) == cudaSuccess) ms_stage[k] += ms;
+    for (int b = 0; b < batch; ++b) {
+      cudaEvent_t* ev = ctx->sev + 8 * b;
+      for (int k = 0; k < (nee ? 4 : 3); ++k) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ev[k], ev[k + 1]) == cudaSuccess) ms_stage[k] += ms;
+      }
     }
-    first = 0;
-    iters++;
     if (ctx->host_cnt->n_ext_next == 0 && ctx->host_cnt->next_path >= M.total) break;
     if (iters > 100000000u) { ctx->err = "wavefront loop did not terminate"; return B200RT_ERR_CUDA; }
   }
-  if (st) { st->ms_generate = ms_stage[0]; st->ms_extend = ms_stage[1]; st->ms_shade = ms_stage[2]; st->ms_shadow = ms_stage[3]; }
   if (st) {
+    st->ms_generate = ms_stage[0]; st->ms_extend = ms_stage[1]; st->ms_shade = ms_stage[2]; st->ms_shadow = ms_stage[3];
     st->extend_rays = ctx->host_cnt->extend_rays; st->shadow_rays = ctx->host_cnt->shadow_rays;
     st->kernel_launches = launches; st->wavefront_iterations = iters;
   }

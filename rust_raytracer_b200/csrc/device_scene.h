@@ -50,6 +50,7 @@ struct DevScene {
   const int* perlin_perm;    // 3 x 256
   const float4* lights;      // 3 x float4 per light
   int n_prims;
+  int n_bvh_prims;  // prims [0, n_bvh_prims) are in the BVH; the rest (scene-enclosing) are tested after traversal
   int n_nodes;
   int n_lights;
   int flat;  // B200RT_SCENE_FLAT_LIST: linear scan, no BVH

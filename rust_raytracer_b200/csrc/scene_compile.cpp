@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <numeric>
 
 #include "scene_compile.hpp"
@@ -279,13 +280,26 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
   std::vector<int> order(n);
   std::iota(order.begin(), order.end(), 0);
   cs.nodes.clear();
+  cs.n_bvh_prims = n;
   if (!cs.flat) {
-    BinBuilder bb(boxes);
-    bb.nodes.reserve(2 * (size_t)n);
-    int root = bb.build(0, (int)n);
-    cs.nodes.reserve((size_t)n * 16);
+    // scene-enclosing primitives (box area > half of the scene box) stay out of the BVH: every ray hits their box at
+    // t_near = 0 anyway; the device tests them once, before the traversal, while the warp is convergent.
+    Box all;
+    for (uint32_t i = 0; i < n; ++i) all.grow(boxes[i]);
+    std::vector<int> in_idx, out_idx;
+    const bool no_outliers = true;  // the traversal in intersect.cuh tests every primitive through the BVH
+    for (uint32_t i = 0; i < n; ++i) ((!no_outliers && n >= 8 && boxes[i].area() > 0.5f * all.area()) ? out_idx : in_idx).push_back((int)i);
+    if (in_idx.empty() || out_idx.size() > 8) { in_idx.resize(n); std::iota(in_idx.begin(), in_idx.end(), 0); out_idx.clear(); }
+    std::vector<Box> inboxes(in_idx.size());
+    for (size_t k = 0; k < in_idx.size(); ++k) inboxes[k] = boxes[in_idx[k]];
+    BinBuilder bb(inboxes);
+    bb.nodes.reserve(2 * in_idx.size());
+    int root = bb.build(0, (int)in_idx.size());
+    cs.nodes.reserve(in_idx.size() * 16);
     collapse(bb, root, cs.nodes);
-    order = bb.order;
+    for (size_t k = 0; k < in_idx.size(); ++k) order[k] = in_idx[bb.order[k]];
+    for (size_t k = 0; k < out_idx.size(); ++k) order[in_idx.size() + k] = out_idx[k];
+    cs.n_bvh_prims = (uint32_t)in_idx.size();
   } else {
     cs.nodes.assign(32, 0.f);
   }

@@ -24,7 +24,7 @@ struct CompiledScene {
   std::vector<float> perlin_vec;   // 256 x 4
   std::vector<int32_t> perlin_perm;  // 3 x 256
   std::vector<float> lights;       // 12 floats per light
-  uint32_t n_prims = 0, n_nodes = 0, n_lights = 0;
+  uint32_t n_prims = 0, n_bvh_prims = 0, n_nodes = 0, n_lights = 0;
   bool flat = false;
 };
 

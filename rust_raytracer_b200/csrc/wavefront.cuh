@@ -102,7 +102,10 @@ DEV int class_of_material(const DevScene& S, int device_prim) {
 
 // extend: persistent warps fetch 32 rays at a time from the queue (warp-level work fetch), traverse, store the
 // hit and bin the slot by material class for the shade kernels.
-__global__ void __launch_bounds__(128) k_wf_extend(DevScene S, WfBuffers B, float t_min) {
+#ifndef B200RT_EXTEND_MINBLOCKS
+#define B200RT_EXTEND_MINBLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevScene S, WfBuffers B, float t_min) {
   const unsigned int n = B.cnt->n_ext;
   const unsigned lane = threadIdx.x & 31;
   for (;;) {
@@ -133,12 +136,20 @@ __global__ void __launch_bounds__(128) k_wf_extend(DevScene S, WfBuffers B, floa
   }
 }
 
-// shade: one launch per material class over that class's queue
-__global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, int cls, float* __restrict__ accum) {
-  const unsigned int n = B.cnt->n_class[cls];
-  const unsigned int* q = B.q_class + (size_t)cls * B.pool;
-  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < ((n + 31u) & ~31u); i += gridDim.x * blockDim.x) {
-    const bool active = i < n;
+// shade: ONE launch over all per-material queues.  Each queue is padded to a multiple of 32 in the index space, so
+// every warp works on a single material class (coherent branches) and the six classes run concurrently.
+__global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum, int only_cls) {
+  unsigned int off[WF_NCLASS + 1];
+  off[0] = 0;
+#pragma unroll
+  for (int c = 0; c < WF_NCLASS; ++c) off[c + 1] = off[c] + ((only_cls < 0 || only_cls == c) ? ((B.cnt->n_class[c] + 31u) & ~31u) : 0u);
+  for (unsigned int gi = blockIdx.x * blockDim.x + threadIdx.x; gi < off[WF_NCLASS]; gi += gridDim.x * blockDim.x) {
+    int cls = 0;
+#pragma unroll
+    for (int c = 1; c < WF_NCLASS; ++c) cls += (gi >= off[c]) ? 1 : 0;
+    const unsigned int i = gi - off[cls];
+    const unsigned int* q = B.q_class + (size_t)cls * B.pool;
+    const bool active = i < B.cnt->n_class[cls];
     bool cont = false, shadow = false;
     unsigned int slot = 0;
     Ray ray;
