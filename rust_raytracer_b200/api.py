@@ -69,6 +69,7 @@ class SceneBuilder:
     def desc(self):
         d = F.SceneDesc()
         self._ok(F.lib().b200rt_builder_finish(self._h, C.byref(d)))
+        d._builder = self  # the tables live in the builder: keep it alive as long as the desc
         return d
 
     def set_flags(self, flags):

@@ -1,0 +1,55 @@
+"""The C-ABI library loads and exports every symbol include/b200rt.h declares; without a GPU every compute entry
+point fails loudly (no CPU fallback).  No compute calls are made here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+import rust_raytracer_b200 as rt
+from rust_raytracer_b200 import _ffi as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200rt.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200rt_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported_and_bound(built):
+    syms = declared_symbols()
+    assert len(syms) >= 40
+    lib = C.CDLL(F.LIB_PATH)
+    missing = [s for s in syms if not hasattr(lib, s)]
+    assert not missing, missing
+    assert sorted(F.PROTOTYPES) == syms  # the ctypes table covers exactly the header
+    assert F.lib().b200rt_abi_version() == 1
+
+
+def test_struct_sizes_match_the_header(built):
+    assert C.sizeof(F.Prim) == 64 and C.sizeof(F.Material) == 16 and C.sizeof(F.Texture) == 48
+    assert C.sizeof(F.Image) == 16 and C.sizeof(F.Instance) == 96 and C.sizeof(F.Hit) == 32
+    assert C.sizeof(F.Perlin) == 256 * 16 + 3 * 256 * 4
+    assert C.sizeof(F.Camera) == 24 * 4 and C.sizeof(F.Params) == 64 and C.sizeof(F.Stats) == 64
+
+
+def test_no_cpu_fallback(built):
+    n = C.c_int(-1)
+    rc = F.lib().b200rt_device_count(C.byref(n))
+    if rc == 0 and n.value > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(rt.B200RTError) as e:
+        rt.Context(0)
+    assert e.value.status == F.ERR_CUDA and "no CPU fallback" in str(e.value)
+
+
+def test_package_does_not_touch_the_oracle():
+    """The product path may not import, link or execute anything under oracle/ (only tests/, smoke() and bench.py's CPU legs may)."""
+    pkg = os.path.join(ROOT, "rust_raytracer_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")) and f != "build.py":
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "liboracle" not in text and "oracle_ffi" not in text and "oracle/" not in text.replace("the oracle/", ""), os.path.join(dirpath, f)

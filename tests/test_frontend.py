@@ -1,0 +1,132 @@
+"""Host logic: the mirror of the reference's construction API flattens into the tables of include/b200rt.h."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import rust_raytracer_b200 as rt
+from rust_raytracer_b200 import _ffi as F
+from scenes_util import DATA, scene_builder
+
+
+def test_reference_cornell_scene_tables():
+    """scene.rs:16-112: 5 walls + light + 2 spheres + Transform(Mesh(cube.obj)) (12 triangles) + Cube."""
+    d = scene_builder("cornell_ref").desc()
+    types = [d.prims[i].type for i in range(d.n_prims)]
+    assert d.n_prims == 5 + 1 + 2 + 12 + 1
+    assert types.count(F.PRIM_TRIANGLE) == 12 and types.count(F.PRIM_BOX) == 1 and types.count(F.PRIM_SPHERE) == 2
+    assert d.n_instances == 1 and d.n_lights == 1
+    tri = [d.prims[i] for i in range(d.n_prims) if d.prims[i].type == F.PRIM_TRIANGLE]
+    assert all(t.instance == 0 for t in tri)
+    m = np.array(d.instances[0].m[:]).reshape(3, 4)  # M = T(100,50,100) * S(50)
+    np.testing.assert_allclose(m, [[50, 0, 0, 100], [0, 50, 0, 50], [0, 0, 50, 100]])
+    assert d.prims[d.light_prims[0]].type == F.PRIM_XZ_RECT
+    # one table row per Arc<dyn Material>: `white` is shared by three walls, the mesh and the cube
+    assert d.n_materials == 6
+
+
+def test_cube_obj_loader_matches_tobj_semantics():
+    """mesh.rs:148-199 on data/mesh/cube.obj: 12 triangles, 6 distinct (flat) normals, f32 positions."""
+    white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
+    w = rt.World(rt.HitableList([rt.Mesh.load_obj(os.path.join(DATA, "mesh", "cube.obj"), white)]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
+    d = w.builder.desc()
+    assert d.n_prims == 12 and d.n_tri_normals == 12
+    normals = {tuple(np.round(d.tri_normals[9 * i:9 * i + 3], 6)) for i in range(12)}
+    assert len(normals) == 6
+    pos = np.array([d.prims[i].p[:9] for i in range(12)])
+    assert np.abs(pos).max() <= 1.000002
+
+
+def test_obj_without_normals_is_an_error_like_the_reference_panic():
+    """bun315.obj has no vn lines: Triangle::hit would index an empty normals Vec (mesh.rs:62-64)."""
+    white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
+    with pytest.raises(rt.B200RTError) as e:
+        rt.World(rt.HitableList([rt.Mesh.load_obj(os.path.join(DATA, "mesh", "bun315.obj"), white)]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
+    assert "normals" in str(e.value)
+    w = rt.World(rt.HitableList([rt.Mesh.load_obj(os.path.join(DATA, "mesh", "bun315.obj"), white, make_normals=True)]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
+    assert w.builder.desc().n_prims == 4968
+    w = rt.World(rt.HitableList([rt.Mesh.load_obj(os.path.join(DATA, "mesh", "bun315.obj"), white, make_normals=True, subdivide=1)]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
+    assert w.builder.desc().n_prims == 4 * 4968
+
+
+def test_missing_obj_and_bad_ids():
+    white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
+    with pytest.raises(rt.B200RTError) as e:
+        rt.World(rt.HitableList([rt.Mesh.load_obj("/nonexistent.obj", white)]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
+    assert e.value.status == F.ERR_IO
+    sb = rt.SceneBuilder()
+    assert F.lib().b200rt_builder_sphere(sb.handle, F.d3((0, 0, 0)), 1.0, 7) < 0  # unknown material id
+    with pytest.raises(rt.B200RTError):
+        rt.Camera(((0, 0, 0), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1)  # look_from == look_at: unit() of a zero vector (vec3.rs:88)
+
+
+@pytest.mark.parametrize("name,n,flat", [("scene_10", 25, 0), ("scene_200_no_bvh", 405, 1), ("scene_500", 1005, 0)])
+def test_json_scenes(name, n, flat):
+    sb = rt.SceneBuilder().load_json(open(os.path.join(DATA, name + ".json")).read())
+    d = sb.desc()
+    assert d.n_prims == n and (d.flags & F.SCENE_FLAT_LIST) == flat
+    # the five fixed spheres of Appendix B
+    assert tuple(np.round(d.prims[0].p[:4], 4)) == (0.0, -100.5, -1.0, 100.0)
+    mats = [d.materials[d.prims[i].material].type for i in range(5)]
+    assert mats == [F.MAT_LAMBERTIAN, F.MAT_DIELECTRIC, F.MAT_DIFFUSE_LIGHT, F.MAT_METAL, F.MAT_DIELECTRIC]
+    assert d.textures[d.materials[d.prims[0].material].texture].type == F.TEX_CHECKER
+    cam = sb.camera
+    np.testing.assert_allclose(cam.origin[:], [-6, 2, -6])
+    assert abs(cam.lens_radius - 0.05) < 1e-7
+
+
+def test_json_errors():
+    with pytest.raises(rt.B200RTError) as e:
+        rt.SceneBuilder().load_json('{"objects": {"type": "Torus"}}')
+    assert e.value.status == F.ERR_PARSE
+    with pytest.raises(rt.B200RTError):
+        rt.SceneBuilder().load_json('{"objects": ')
+
+
+def test_transform_composition_and_rotated_shapes():
+    """M = T*S*Rx*Ry*Rz (transform.rs:28-106); a rotated Cube is emitted as 12 flat triangles, a rotated sphere stays a sphere."""
+    white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
+    items = rt.HitableList([
+        rt.Transform((10, 20, 30), (2, 2, 2), (1, 2, 3), rt.Sphere((0, 0, 0), 1, white)),
+        rt.Transform((0, 15, 0), (1, 1, 1), (265, 0, 295), rt.Cube((0, 0, 0), (165, 330, 165), white)),
+        rt.Transform((0, 0, 0), (2, 3, 4), (0, 0, 0), rt.Cube((0, 0, 0), (1, 1, 1), white)),
+    ])
+    d = rt.World(items, rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1)).builder.desc()
+    types = [d.prims[i].type for i in range(d.n_prims)]
+    assert types == [F.PRIM_SPHERE] + [F.PRIM_TRIANGLE] * 12 + [F.PRIM_BOX]
+    rx, ry, rz = np.radians([10, 20, 30])
+    Rx = np.array([[1, 0, 0], [0, np.cos(rx), -np.sin(rx)], [0, np.sin(rx), np.cos(rx)]])
+    Ry = np.array([[np.cos(ry), 0, np.sin(ry)], [0, 1, 0], [-np.sin(ry), 0, np.cos(ry)]])
+    Rz = np.array([[np.cos(rz), -np.sin(rz), 0], [np.sin(rz), np.cos(rz), 0], [0, 0, 1]])
+    want = np.hstack([2 * Rx @ Ry @ Rz, [[1], [2], [3]]])
+    np.testing.assert_allclose(np.array(d.instances[0].m[:]).reshape(3, 4), want, atol=1e-15)
+    with pytest.raises(rt.B200RTError) as e:  # ellipsoid
+        rt.World(rt.HitableList([rt.Transform((0, 0, 0), (1, 2, 1), (0, 0, 0), rt.Sphere((0, 0, 0), 1, white))]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
+    assert e.value.status == F.ERR_UNSUPPORTED
+
+
+def test_camera_new_matches_reference_formula():
+    """camera.rs:24-55 evaluated in numpy."""
+    c = rt.Camera(((13, 2, 3), (0, 0, 0)), (0, 1, 0), 20, 16 / 9, 0.1, 10.0).c
+    w = np.array([13, 2, 3.0]); w /= np.linalg.norm(w)
+    u = np.cross([0, 1, 0], w); u /= np.linalg.norm(u)
+    v = np.cross(w, u)
+    h = np.tan(np.radians(20) / 2)
+    hor, ver = 10 * (16 / 9) * 2 * h * u, 10 * 2 * h * v
+    np.testing.assert_allclose(c.horizontal[:], hor, rtol=1e-6)
+    np.testing.assert_allclose(c.vertical[:], ver, rtol=1e-6)
+    np.testing.assert_allclose(c.lower_left_corner[:], np.array([13, 2, 3]) - hor / 2 - ver / 2 - 10 * w, rtol=1e-6)
+    assert abs(c.lens_radius - 0.05) < 1e-8
+
+
+def test_canonical_scenes_are_deterministic_in_the_seed():
+    a, b, c = scene_builder("book1", 1).desc(), scene_builder("book1", 1).desc(), scene_builder("book1", 2).desc()
+    pa = np.array([a.prims[i].p[:4] for i in range(a.n_prims)])
+    pb = np.array([b.prims[i].p[:4] for i in range(b.n_prims)])
+    pc = np.array([c.prims[i].p[:4] for i in range(min(a.n_prims, c.n_prims))])
+    assert np.array_equal(pa, pb) and not np.array_equal(pa[:len(pc)], pc)
+    d = scene_builder("book2").desc()
+    types = [d.prims[i].type for i in range(d.n_prims)]
+    assert types.count(F.PRIM_BOX) == 400 and types.count(F.PRIM_MEDIUM_SPHERE) == 2 and types.count(F.PRIM_MOVING_SPHERE) == 1
+    assert sum(1 for i in range(d.n_prims) if d.prims[i].instance >= 0) == 1000 and d.perlin and d.n_images == 1
