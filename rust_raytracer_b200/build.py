@@ -52,6 +52,23 @@ def build_library(force=False, verbose=False):
     return LIB
 
 
+def build_variant(name, defines=(), out_dir=None):
+    """A/B or debug build of the same sources with extra -D flags (tools/dbg, profiling): loaded via B200RT_LIB."""
+    out_dir = out_dir or os.path.join(ROOT, "tools", "dbg")
+    os.makedirs(out_dir, exist_ok=True)
+    out = os.path.join(out_dir, "libb200rt_%s.so" % name)
+    nvcc = os.environ.get("NVCC", "nvcc")
+    flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"] + ["-D" + d for d in defines]
+    cmd = [nvcc] + flags + ["-o", out] + [os.path.join(CSRC, s) for s in SOURCES]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    with open(out + ".log", "w") as f:
+        f.write(" ".join(cmd) + "\n" + res.stdout)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout)
+        raise RuntimeError("nvcc failed for variant %s" % name)
+    return out
+
+
 def build_oracle(force=False):
     src = os.path.join(ORACLE_DIR, "oracle.cpp")
     header = os.path.join(ROOT, "include", "b200rt.h")

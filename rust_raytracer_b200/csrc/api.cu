@@ -45,6 +45,15 @@ static thread_local std::string g_global_err;
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+#ifdef B200RT_COUNTERS
+extern "C" int b200rt_debug_counters(unsigned long long* out, int reset) {  // debug builds only (tools/dbg)
+  cudaDeviceSynchronize();
+  if (out) cudaMemcpyFromSymbol(out, g_dbg, sizeof(g_dbg));
+  if (reset) { static unsigned long long z[64]; cudaMemcpyToSymbol(g_dbg, z, sizeof(z)); }
+  return 0;
+}
+#endif
+
 extern "C" {
 
 int b200rt_abi_version(void) { return B200RT_ABI_VERSION; }
@@ -229,14 +238,5 @@ int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_
 }
 
 }  // extern "C"
-
-#ifdef B200RT_COUNTERS
-extern "C" int b200rt_debug_counters(unsigned long long* out, int reset) {
-  cudaDeviceSynchronize();
-  cudaMemcpyFromSymbol(out, g_dbg, sizeof(unsigned long long) * 16);
-  if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_dbg, z, sizeof(z)); }
-  return 0;
-}
-#endif
 
 #include "api_render.cuh"

@@ -70,6 +70,11 @@ DEV double medium_xi(uint32_t seed, uint32_t prim) {
   return ((double)(h >> 9) + 0.5) * (1.0 / 8388608.0);
 }
 
+DEV float medium_xi_f32(uint32_t seed, uint32_t prim) {  // the same draw, exactly representable in f32
+  uint32_t h = pcg_hash(seed ^ (prim * 0x9E3779B9u));
+  return ((float)(h >> 9) + 0.5f) * (1.0f / 8388608.0f);
+}
+
 // ---- sampling transforms (distribution-equal to the reference's rejection loops, vec3.rs:111-162) -------------
 // uniform on the unit sphere == Vec3::random_in_unit_sphere() (Marsaglia, returns a point ON the sphere)
 DEV float3 sample_unit_sphere(float u1, float u2) {

@@ -5,6 +5,16 @@
 #include "prim_exact.cuh"
 #include "prim_filter.cuh"
 
+// Debug build (-DB200RT_COUNTERS, tools/dbg): per-ray work statistics of the traversal.
+#ifdef B200RT_COUNTERS
+__device__ unsigned long long g_dbg[64];
+#define DBG_INC(i) atomicAdd(&g_dbg[(i)], 1ull)
+#else
+#define DBG_INC(i)
+#endif
+// counter slots: 0 rays, 1 inner nodes visited, 2 leaves visited, 3 stack pushes, 4 pops culled, 5 to_object,
+// 10+type filter calls, 20+type exact calls, 30+type exact accepted
+
 struct Ray {
   float3 o;
   float time;
@@ -65,147 +75,210 @@ DEV RayD to_object(const DevScene& S, int inst, const RayD& w) {
 // One leaf primitive: filter in f32 on the world-space (baked) record, confirm in f64 on the ORIGINAL record
 // (object space for instanced primitives, exactly like Transform::hit).  Updates h when the primitive hits in
 // [t_min, h.t].
+//
+// Code size is a first-order cost here (the SM's L1.5 instruction cache is 32 KB and divergent warps walk
+// different parts of this function), so every heavy f64 sequence exists exactly ONCE: one quadratic-root site
+// serves Sphere, MovingSphere and the sphere ConstantMedium boundary; one rectangle site serves the three
+// rectangles, the Cube faces and the box ConstantMedium boundary; the medium tail (medium.rs:33-52) is shared.
 DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, float t_min, float& t_best32, HitRaw& h) {
   const int4 meta = __ldg(&S.prim_meta[k]);
   const int type = meta.x & 0xff;
   const bool inst = meta.z >= 0;
   const float eps = inst ? __ldg(&S.inst_eps[meta.z]) : 0.f;
   const float4 A = __ldg(&S.prim_data[3 * k]);
-  switch (type) {  // ---- f32 filter (certain misses only)
-    case B200RT_PRIM_SPHERE:
-      if (sphere_reject(rf, f3(A), A.w, t_min, t_best32, eps)) return;
-      break;
-    case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      const int axis = type == B200RT_PRIM_XY_RECT ? 2 : (type == B200RT_PRIM_XZ_RECT ? 1 : 0);
-      if (rect_reject(rf, axis, A.x, A.y, A.z, A.w, B.x, t_min, t_best32, eps)) return;
-      break;
-    }
-    case B200RT_PRIM_BOX: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      if (box_reject(rf, f3(A), f3(B), t_min, t_best32, eps)) return;
-      break;
-    }
-    case B200RT_PRIM_MEDIUM_BOX: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      if (box_reject(rf, f3(A), f3(B), -3.0e38f, t_best32, eps)) return;
-      break;
-    }
-    case B200RT_PRIM_TRIANGLE: {
-      const float4 B = __ldg(&S.prim_data[3 * k + 1]);
-      const float4 C = __ldg(&S.prim_data[3 * k + 2]);
-      if (tri_reject(rf, f3(A), f3(B), f3(C), t_min, t_best32, eps)) return;
-      break;
-    }
-    default: break;  // moving spheres and sphere media go straight to the exact test
-  }
+  const float4 WB = __ldg(&S.prim_data[3 * k + 1]);
+  const bool is_medium = type == B200RT_PRIM_MEDIUM_SPHERE || type == B200RT_PRIM_MEDIUM_BOX;
+  const bool is_rect = type == B200RT_PRIM_XY_RECT || type == B200RT_PRIM_XZ_RECT || type == B200RT_PRIM_YZ_RECT;
+  const int rect_axis = type == B200RT_PRIM_XY_RECT ? 2 : (type == B200RT_PRIM_XZ_RECT ? 1 : 0);
+  DBG_INC(10 + type);
+  uint32_t cand = 0x3fu;  // Cube faces to confirm: bits 0..5 near the slab entry, bits 8..13 near the exit
+  // ---- f32 filter (certain misses only)
+  if (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MEDIUM_SPHERE) {
+    const float xi = is_medium ? medium_xi_f32(ray.mseed, (uint32_t)meta.y) : 0.5f;
+    if (sphere_reject(rf, f3(A), A.w, t_min, t_best32, eps, is_medium, WB.x, xi)) return;
+  } else if (type == B200RT_PRIM_BOX || type == B200RT_PRIM_MEDIUM_BOX) {
+    const float xi = is_medium ? medium_xi_f32(ray.mseed, (uint32_t)meta.y) : 0.5f;
+    if (box_reject(rf, f3(A), f3(WB), t_min, t_best32, eps, is_medium ? nullptr : &cand, is_medium, WB.w, xi)) return;
+  } else if (is_rect) {
+    if (rect_reject(rf, rect_axis, A.x, A.y, A.z, A.w, WB.x, t_min, t_best32, eps)) return;
+    cand = 1u << (2 * (2 - rect_axis));  // the rectangle is the "min" side of a degenerate box on its axis
+  } else if (type == B200RT_PRIM_TRIANGLE) {
+    const float4 C = __ldg(&S.prim_data[3 * k + 2]);
+    if (tri_reject(rf, f3(A), f3(WB), f3(C), t_min, t_best32, eps)) return;
+  }  // moving spheres go straight to the exact test
   // ---- f64 decision
   RayD rd = make_rayd(ray);
   const float4* rec = S.prim_data + 3 * (size_t)k;
-  if (inst) { rd = to_object(S, meta.z, rd); rec = S.prim_obj + 3 * (size_t)k; }
+  if (inst) { rd = to_object(S, meta.z, rd); rec = S.prim_obj + 3 * (size_t)k; DBG_INC(5); }
+  DBG_INC(20 + type);
   const float4 EA = inst ? __ldg(rec) : A;
-  double t;
+  const float4 EB = inst ? __ldg(rec + 1) : WB;
+  const double tmin_d = (double)t_min, tmax_d = h.t;
+  double t_in = 0., t_out = 0.;  // surfaces: t_in is the hit; media: the boundary interval
   int aux = 0;
-  switch (type) {
-    case B200RT_PRIM_SPHERE:
-      if (!sphere_exact(rd, D3(EA), (double)EA.w, (double)t_min, h.t, t)) return;
-      break;
-    case B200RT_PRIM_MOVING_SPHERE: {
-      const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
-      d3 c = moving_center(D3(EA), D3(B), (double)C.x, (double)C.y, rd.time);
-      if (!sphere_exact(rd, c, (double)EA.w, (double)t_min, h.t, t)) return;
-      break;
+  if (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE || type == B200RT_PRIM_MEDIUM_SPHERE) {
+    // objects/sphere.rs:24-43 — nearest root in the CLOSED interval [t_min, t_max]; tangent rays hit.
+    // ConstantMedium (medium.rs:26-31): first root in (-inf, inf), then the next one in [first + 0.0001, inf).
+    d3 c = D3(EA);
+    if (type == B200RT_PRIM_MOVING_SPHERE) {
+      const float4 C = __ldg(rec + 2);
+      c = moving_center(c, D3(EB), (double)C.x, (double)C.y, rd.time);
     }
-    case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
-      const float4 B = __ldg(rec + 1);
-      const int axis = type == B200RT_PRIM_XY_RECT ? 2 : (type == B200RT_PRIM_XZ_RECT ? 1 : 0);
-      double pa, pb;
-      if (!rect_exact(rd, axis, (double)EA.x, (double)EA.y, (double)EA.z, (double)EA.w, (double)B.x, (double)t_min, h.t, t, pa, pb)) return;
-      break;
+    const double radius = (double)EA.w;
+    const d3 oc = rd.o - c;
+    const double a = ddot(rd.d, rd.d);
+    const double half_b = ddot(oc, rd.d);
+    const double cc = __dsub_rn(ddot(oc, oc), __dmul_rn(radius, radius));
+    const double disc = __dsub_rn(__dmul_rn(half_b, half_b), __dmul_rn(a, cc));
+    if (disc < 0.) return;
+    const double sqrt_d = sqrt(disc);
+    double lo = is_medium ? -DINF : tmin_d;
+    const double hi = is_medium ? DINF : tmax_d;
+    int found = 0;
+#pragma unroll 1
+    for (int i = 0; i < 2; ++i) {
+      const double root = __ddiv_rn(i == 0 ? __dsub_rn(-half_b, sqrt_d) : __dadd_rn(-half_b, sqrt_d), a);
+      if (root >= lo && root <= hi) {
+        if (found == 0) { t_in = root; found = 1; if (!is_medium) break; lo = __dadd_rn(root, 0.0001); }
+        else { t_out = root; found = 2; }
+      }
     }
-    case B200RT_PRIM_BOX: {
-      const float4 B = __ldg(rec + 1);
-      if (!cube_exact(rd, D3(EA), D3(B), (double)t_min, h.t, t, aux)) return;
-      break;
+    if (found == 0 || (is_medium && found != 2)) return;
+  } else if (type == B200RT_PRIM_TRIANGLE) {
+    const float4 C = __ldg(rec + 2);
+    double b1, b2;
+    if (!tri_exact(rd, D3(EA), D3(EB), D3(C), tmin_d, tmax_d, t_in, b1, b2)) return;
+  } else {
+    // Rectangles (rectangle.rs:15-34,53-72,90-109), Cube = closest of six rectangles (cube.rs:63-66), and the box
+    // ConstantMedium boundary: one pass over the candidate faces per boundary hit wanted.
+    d3 mn = D3(EA), mx = D3(EB);
+    if (is_rect) {  // A = (a0, b0, a1, b1), B.x = k
+      const double kk = (double)EB.x;
+      if (rect_axis == 2) { mn = D3((double)EA.x, (double)EA.y, kk); mx = D3((double)EA.z, (double)EA.w, kk); }
+      else if (rect_axis == 1) { mn = D3((double)EA.x, kk, (double)EA.y); mx = D3((double)EA.z, kk, (double)EA.w); }
+      else { mn = D3(kk, (double)EA.x, (double)EA.y); mx = D3(kk, (double)EA.z, (double)EA.w); }
     }
-    case B200RT_PRIM_TRIANGLE: {
-      const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
-      double b1, b2;
-      if (!tri_exact(rd, D3(EA), D3(B), D3(C), (double)t_min, h.t, t, b1, b2)) return;
-      break;
+    const float es = inst ? 2.0f * eps * fmaxf(fabsf(rf.inv.x), fmaxf(fabsf(rf.inv.y), fabsf(rf.inv.z))) : 0.f;
+    auto lower = [&](int s) { const float ts = box_side_t(rf, f3(A), f3(WB), s); return ts - (2e-6f * fabsf(ts) + es); };
+    double lo = is_medium ? -DINF : tmin_d;
+    const double hi = is_medium ? DINF : tmax_d;
+#pragma unroll 1
+    for (int pass = 0; pass < (is_medium ? 2 : 1); ++pass) {
+      double tt;
+      if (!cube_exact_cand(rd, mn, mx, lo, hi, cand, lower, tt, aux)) return;
+      if (pass == 0) { t_in = tt; lo = __dadd_rn(tt, 0.0001); } else t_out = tt;
     }
-    case B200RT_PRIM_MEDIUM_SPHERE: {
-      const float4 B = __ldg(rec + 1);
-      if (!medium_exact(rd, 0, D3(EA), D3(EA), (double)EA.w, (double)B.x, medium_xi(ray.mseed, (uint32_t)meta.y), (double)t_min, h.t, t)) return;
-      break;
-    }
-    case B200RT_PRIM_MEDIUM_BOX: {
-      const float4 B = __ldg(rec + 1);
-      if (!medium_exact(rd, 1, D3(EA), D3(B), 0.0, (double)B.w, medium_xi(ray.mseed, (uint32_t)meta.y), (double)t_min, h.t, t)) return;
-      break;
-    }
-    default: return;
+    if (type != B200RT_PRIM_BOX) aux = 0;  // only the Cube records which side was hit (finish_hit)
   }
+  double t = t_in;
+  if (is_medium) {  // medium.rs:33-52; xi is the injected draw
+    const double neg_inv_density = type == B200RT_PRIM_MEDIUM_SPHERE ? (double)EB.x : (double)EB.w;
+    double t1 = fmax(t_in, tmin_d);
+    const double t2 = fmin(t_out, tmax_d);
+    if (t1 >= t2) return;
+    t1 = fmax(t1, 0.);
+    const double ray_length = sqrt(ddot(rd.d, rd.d));
+    const double distance_inside = __dmul_rn(__dsub_rn(t2, t1), ray_length);
+    const double hit_distance = __dmul_rn(neg_inv_density, log(medium_xi(ray.mseed, (uint32_t)meta.y)));
+    if (hit_distance > distance_inside) return;
+    t = __dadd_rn(t1, __ddiv_rn(hit_distance, ray_length));
+    aux = 0;
+  }
+  DBG_INC(30 + type);
   h.t = t; h.prim = k; h.aux = aux;
   t_best32 = __double2float_ru(t);
 }
 
+// BVH4 node step: slab-tests the four children of inner node `cur` against [t_min, t_best32], pushes the far
+// hits (farthest first) and returns the nearest child reference, or B200RT_TRAV_DONE-style "none" via `any`.
+#define B200RT_TRAV_DONE 0xFFFFFFFFu  // leaf bit set with an impossible count: never a real child reference
+
+DEV uint32_t pop_next(const uint2* stack, int& sp, float t_best32) {
+  while (sp > 0) {
+    const uint2 e = stack[--sp];
+    if (__uint_as_float(e.y) <= t_best32) return e.x;
+    DBG_INC(4);
+  }
+  return B200RT_TRAV_DONE;
+}
+
+DEV uint32_t node_step(const DevScene& S, const RayF& rf, uint32_t cur, float t_min, float t_best32, uint2* stack, int& sp) {
+  DBG_INC(1);
+  const float4* nd = S.nodes + 8 * (size_t)cur;
+  const float4 lox = __ldg(nd + 0), loy = __ldg(nd + 1), loz = __ldg(nd + 2);
+  const float4 hix = __ldg(nd + 3), hiy = __ldg(nd + 4), hiz = __ldg(nd + 5);
+  const int4 ref = __ldg((const int4*)(nd + 6));
+  float tn[4];
+  uint32_t rr[4] = {(uint32_t)ref.x, (uint32_t)ref.y, (uint32_t)ref.z, (uint32_t)ref.w};
+  const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
+  const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float t0x = (lx[i] - rf.o.x) * rf.inv.x, t1x = (hx[i] - rf.o.x) * rf.inv.x;
+    float t0y = (ly[i] - rf.o.y) * rf.inv.y, t1y = (hy[i] - rf.o.y) * rf.inv.y;
+    float t0z = (lz[i] - rf.o.z) * rf.inv.z, t1z = (hz[i] - rf.o.z) * rf.inv.z;
+    float n = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), t_min));
+    float f = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), t_best32));
+    bool hit = (n <= f * 1.000001f) && (rr[i] != (uint32_t)B200RT_CHILD_EMPTY);
+    tn[i] = hit ? n : 3.0e38f;
+  }
+  // sort the four (tn, ref) pairs ascending (5-comparator network)
+#define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t tr = rr[a]; rr[a] = rr[b]; rr[b] = tr; }
+  CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2) CSWAP(1, 3) CSWAP(1, 2)
+#undef CSWAP
+  if (tn[3] < 3.0e38f) stack[sp++] = make_uint2(rr[3], __float_as_uint(tn[3]));
+  if (tn[2] < 3.0e38f) stack[sp++] = make_uint2(rr[2], __float_as_uint(tn[2]));
+  if (tn[1] < 3.0e38f) stack[sp++] = make_uint2(rr[1], __float_as_uint(tn[1]));
+  if (tn[0] < 3.0e38f) return rr[0];
+  return pop_next(stack, sp, t_best32);
+}
+
+#ifndef B200RT_TRAV_WW
+#define B200RT_TRAV_WW 1
+#endif
+
+
 // Closest hit in [t_min, ray.tmax] (ANY = false) or any hit (ANY = true: shadow rays, returns at the first hit).
+// "while-while" traversal: every lane first descends inner nodes until it holds a leaf (or is done), then the
+// warp runs the (expensive, f64-confirmed) leaf tests together.  Primitives outside the BVH — the scene-enclosing
+// ones the host kept out of it, or ALL of them for the flat-list arm (hit.rs:56-67, n_bvh_prims = 0) — are fed
+// through the same leaf code as pseudo-leaves of up to 16 after the traversal, when t_best already culls most of
+// their work: test_prim is instantiated once per kernel.
 template <bool ANY>
 DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
   h.t = (double)ray.tmax; h.prim = -1; h.aux = 0;
   float t_best32 = ray.tmax;
   const RayF rf = make_rayf(ray);
-  if (S.flat) {  // hit.rs:56-67: the brute-force arm (data/scene_200_no_bvh.json)
-    for (int k = 0; k < S.n_prims; ++k) {
-      test_prim(S, ray, rf, k, t_min, t_best32, h);
-      if (ANY && h.prim >= 0) return;
-    }
-    return;
-  }
+  DBG_INC(0);
   uint2 stack[B200RT_STACK];
   int sp = 0;
-  uint32_t cur = 0;  // root node
+  int tail = S.n_bvh_prims;                          // next primitive outside the BVH
+  // The tail is expensive (book-2's fog: an f64 medium test for half of the rays): run it once per warp, with
+  // all lanes converged, instead of once per group of lanes that happen to leave the BVH together.
+  const unsigned lanes = __activemask();
+  const bool wait_tail = !ANY && !S.flat && S.n_bvh_prims < S.n_prims;
+  uint32_t cur = S.flat ? B200RT_TRAV_DONE : 0u;  // root node
   for (;;) {
-    if (!(cur & B200RT_LEAF_BIT)) {
-      const float4* nd = S.nodes + 8 * (size_t)cur;
-      const float4 lox = __ldg(nd + 0), loy = __ldg(nd + 1), loz = __ldg(nd + 2);
-      const float4 hix = __ldg(nd + 3), hiy = __ldg(nd + 4), hiz = __ldg(nd + 5);
-      const int4 ref = __ldg((const int4*)(nd + 6));
-      float tn[4];
-      uint32_t rr[4] = {(uint32_t)ref.x, (uint32_t)ref.y, (uint32_t)ref.z, (uint32_t)ref.w};
-      const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
-      const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        float t0x = (lx[i] - rf.o.x) * rf.inv.x, t1x = (hx[i] - rf.o.x) * rf.inv.x;
-        float t0y = (ly[i] - rf.o.y) * rf.inv.y, t1y = (hy[i] - rf.o.y) * rf.inv.y;
-        float t0z = (lz[i] - rf.o.z) * rf.inv.z, t1z = (hz[i] - rf.o.z) * rf.inv.z;
-        float n = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), t_min));
-        float f = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), t_best32));
-        bool hit = (n <= f * 1.000001f) && (rr[i] != (uint32_t)B200RT_CHILD_EMPTY);
-        tn[i] = hit ? n : 3.0e38f;
-      }
-      // sort the four (tn, ref) pairs ascending (5-comparator network)
-#define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t tr = rr[a]; rr[a] = rr[b]; rr[b] = tr; }
-      CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2) CSWAP(1, 3) CSWAP(1, 2)
-#undef CSWAP
-      if (tn[3] < 3.0e38f) stack[sp++] = make_uint2(rr[3], __float_as_uint(tn[3]));
-      if (tn[2] < 3.0e38f) stack[sp++] = make_uint2(rr[2], __float_as_uint(tn[2]));
-      if (tn[1] < 3.0e38f) stack[sp++] = make_uint2(rr[1], __float_as_uint(tn[1]));
-      if (tn[0] < 3.0e38f) { cur = rr[0]; continue; }
-    } else {
-      const int first = (int)(cur & 0x07FFFFFFu), count = (int)((cur >> 27) & 15u) + 1;
-      for (int k = first; k < first + count; ++k) test_prim(S, ray, rf, k, t_min, t_best32, h);
-      if (ANY && h.prim >= 0) return;
+#if B200RT_TRAV_WW
+    while (!(cur & B200RT_LEAF_BIT)) cur = node_step(S, rf, cur, t_min, t_best32, stack, sp);
+#else
+    if (!(cur & B200RT_LEAF_BIT)) { cur = node_step(S, rf, cur, t_min, t_best32, stack, sp); continue; }
+#endif
+    if (wait_tail) {  // warp-uniform: the lanes that finished the BVH wait here until the whole warp has
+      const bool all_done = __all_sync(lanes, cur == B200RT_TRAV_DONE);
+      if (cur == B200RT_TRAV_DONE && !all_done) continue;
     }
-    // pop the next entry that can still beat the best hit
-    bool found = false;
-    while (sp > 0) {
-      uint2 e = stack[--sp];
-      if (__uint_as_float(e.y) <= t_best32) { cur = e.x; found = true; break; }
+    if (cur == B200RT_TRAV_DONE) {
+      if (tail >= S.n_prims) break;
+      const int c = min(16, S.n_prims - tail);
+      cur = B200RT_LEAF_BIT | ((uint32_t)(c - 1) << 27) | (uint32_t)tail;
+      tail += c;
     }
-    if (!found) return;
+    const int first = (int)(cur & 0x07FFFFFFu), count = (int)((cur >> 27) & 15u) + 1;
+    DBG_INC(2);
+    for (int k = first; k < first + count; ++k) test_prim(S, ray, rf, k, t_min, t_best32, h);
+    if (ANY && h.prim >= 0) return;
+    cur = pop_next(stack, sp, t_best32);
   }
 }
 

@@ -65,6 +65,35 @@ DEV bool cube_exact(const RayD& r, d3 mn, d3 mx, double t_min, double t_max, dou
   return any;
 }
 
+// The same closest-of-six result from the candidate faces only (prim_filter.cuh box_reject): entry-side
+// candidates first; an exit-side candidate is skipped when its f32 plane parameter is certainly beyond the hit
+// already accepted.  The accept rule (smaller t, or equal t and a later side) is cube.rs:63-66 -> hit.rs:56-67
+// made order-independent, so skipping certain misses cannot change the winner.
+template <typename SideLB>
+DEV bool cube_exact_cand(const RayD& r, d3 mn, d3 mx, double t_min, double t_max, uint32_t cand, SideLB side_lower_bound32, double& t, int& side_out) {
+  double best = t_max;
+  int side = -1;
+  uint32_t m = cand & 0x3fu;
+  for (int pass = 0; pass < 2; ++pass) {
+    while (m) {
+      const int s = __ffs((int)m) - 1;
+      m &= m - 1u;
+      if (pass == 1 && side >= 0) {
+        if ((double)side_lower_bound32(s) > best) continue;
+      }
+      int axis; double a0, b0, a1, b1, k, tt, pa, pb;
+      cube_side(s, mn, mx, axis, a0, b0, a1, b1, k);
+      if (rect_exact(r, axis, a0, b0, a1, b1, k, t_min, t_max, tt, pa, pb)) {
+        if (side < 0 || tt < best || (tt == best && s > side)) { best = tt; side = s; }
+      }
+    }
+    m = (cand >> 8) & 0x3fu;
+  }
+  if (side < 0) return false;
+  t = best; side_out = side;
+  return true;
+}
+
 // objects/mesh.rs:56-101 (Moeller-Trumbore, two-sided, inclusive bounds)
 DEV bool tri_exact(const RayD& r, d3 pa, d3 pb, d3 pc, double t_min, double t_max, double& t, double& b1, double& b2) {
   d3 e0 = pb - pa, e1 = pc - pa;

@@ -14,10 +14,25 @@ struct RayF {
 
 DEV float safe_rcp(float d) { return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
 
+// ConstantMedium::hit (medium.rs:25-53) in f32.  [t_in, t_out] is the boundary interval (errors e_in, e_out):
+// distance_inside <= (min(t_out, t_best) - max(t_in, t_min, 0)) * |d|; the scattering distance
+// hit_distance = -1/density * ln(xi) is known to ~3 ulp, so when it exceeds that upper bound the medium is a
+// certain miss and the f64 boundary roots / log never run.
+DEV bool medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, float e_out, float neg_inv_density, float xi, float t_min, float t_best) {
+  const float lo = fmaxf(fmaxf(t_in - e_in, t_min), 0.f);
+  const float hi = fminf(t_out + e_out, t_best);
+  const float len = sqrtf(r.a);
+  float upper = fmaxf(hi - lo, 0.f) + 2e-7f * (fabsf(hi) + fabsf(lo));
+  upper = upper * len * (1.0f + 2e-6f);
+  const float hd = neg_inv_density * logf(xi);  // >= 0
+  return hd * (1.0f - 2e-6f) > upper;           // NaN/inf upper (t_best = inf, unbounded boundary) never rejects
+}
+
 // sphere.rs:24-43 in f32: disc error <= ~20u * a * (|oc|^2 + r^2)
 // eps: absolute error of the baked world-space coordinates of an instanced primitive (0 when not instanced):
 // the exact test then runs in OBJECT space on the original values, so the filter must tolerate the baking error.
-DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best, float eps) {
+// medium = true: the sphere is a ConstantMedium boundary (both roots matter, then the distance test).
+DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best, float eps, bool medium = false, float neg_inv_density = 0.f, float xi = 0.5f) {
   float3 oc = r.o - c;
   float hb = dot(oc, r.d), oc2 = dot(oc, oc), r2 = radius * radius;
   float cc = oc2 - r2;
@@ -31,6 +46,7 @@ DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float
     float e0 = dn + 4e-7f * fabsf(t0), e1 = dn + 4e-7f * fabsf(t1);
     if (t0 - e0 > t_best) return true;                       // nearest root already beyond the best hit
     if (t1 + e1 < t_min) return true;                        // sphere entirely behind t_min
+    if (medium) return medium_far_reject(r, t0, e0, t1, e1, neg_inv_density, xi, t_min, t_best);
     if (t0 + e0 < t_min && t1 - e1 > t_best) return true;    // origin inside, exit beyond the best hit
   }
   return false;
@@ -51,7 +67,12 @@ DEV bool rect_reject(const RayF& r, int axis, float a0, float b0, float a1, floa
 }
 
 // Cube (cube.rs:63-66): the six rectangle hits are exactly the slab entry and exit points.
-DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best, float eps) {
+// `cand` (optional) returns the faces that can produce the closest valid hit: bits 0..5 = sides whose plane
+// parameter lies within the f32 error of the slab ENTRY point, bits 8..13 = sides near the EXIT point (side
+// numbering of cube_side: XY@min.z, XY@max.z, XZ@min.y, XZ@max.y, YZ@min.x, YZ@max.x).  A face whose plane hit
+// is neither is out of its rectangle bounds for certain, so the exact test may skip it.
+DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best, float eps, uint32_t* cand = nullptr, bool medium = false, float neg_inv_density = 0.f,
+                    float xi = 0.5f) {
   float3 t0 = (mn - r.o) * r.inv, t1 = (mx - r.o) * r.inv;
   float tn = fmaxf(fmaxf(fminf(t0.x, t1.x), fminf(t0.y, t1.y)), fminf(t0.z, t1.z));
   float tf = fminf(fminf(fmaxf(t0.x, t1.x), fmaxf(t0.y, t1.y)), fmaxf(t0.z, t1.z));
@@ -60,8 +81,29 @@ DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_be
   if (tn - en > tf + ef) return true;
   if (tf + ef < t_min) return true;
   if (tn - en > t_best) return true;
+  if (medium) return medium_far_reject(r, tn, en, tf, ef, neg_inv_density, xi, t_min, t_best);  // ConstantMedium boundary
   if (tn + en < t_min && tf - ef > t_best) return true;
+  if (cand) {
+    const float ts[6] = {t0.z, t1.z, t0.y, t1.y, t0.x, t1.x};
+    uint32_t cn = 0, cf = 0;
+#pragma unroll
+    for (int s = 0; s < 6; ++s) {
+      const float e = 1e-6f * fabsf(ts[s]) + es;
+      const bool in_range = (ts[s] + e >= t_min) && (ts[s] - e <= t_best);
+      const bool near_n = fabsf(ts[s] - tn) <= 2.0f * (e + en), near_f = fabsf(ts[s] - tf) <= 2.0f * (e + ef);
+      if (in_range && near_n) cn |= 1u << s;
+      else if (in_range && near_f) cf |= 1u << s;
+    }
+    if (!(cn | cf)) return true;
+    *cand = cn | (cf << 8);
+  }
   return false;
+}
+// f32 plane parameter of one cube side (for ordering decisions in the exact stage)
+DEV float box_side_t(const RayF& r, float3 mn, float3 mx, int side) {
+  const int axis = 2 - (side >> 1);
+  const float k = (side & 1) ? comp(mx, axis) : comp(mn, axis);
+  return (k - comp(r.o, axis)) * comp(r.inv, axis);
 }
 
 // mesh.rs:56-101 in f32 with condition-number-scaled margins (q = |d||e0||e1| / |det|)

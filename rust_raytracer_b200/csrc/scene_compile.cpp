@@ -283,11 +283,16 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
   cs.n_bvh_prims = n;
   if (!cs.flat) {
     // scene-enclosing primitives (box area > half of the scene box) stay out of the BVH: every ray hits their box at
-    // t_near = 0 anyway; the device tests them once, before the traversal, while the warp is convergent.
+    // t_near = 0 anyway; the device tests them once, AFTER the traversal, when the closest hit found so far lets
+    // the f32 filters reject most of them (book-2's fog sphere: ~95 % of the rays).
     Box all;
     for (uint32_t i = 0; i < n; ++i) all.grow(boxes[i]);
     std::vector<int> in_idx, out_idx;
-    const bool no_outliers = true;  // the traversal in intersect.cuh tests every primitive through the BVH
+#ifdef B200RT_NO_OUTLIERS
+    const bool no_outliers = true;
+#else
+    const bool no_outliers = false;
+#endif
     for (uint32_t i = 0; i < n; ++i) ((!no_outliers && n >= 8 && boxes[i].area() > 0.5f * all.area()) ? out_idx : in_idx).push_back((int)i);
     if (in_idx.empty() || out_idx.size() > 8) { in_idx.resize(n); std::iota(in_idx.begin(), in_idx.end(), 0); out_idx.clear(); }
     std::vector<Box> inboxes(in_idx.size());
@@ -302,6 +307,7 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     cs.n_bvh_prims = (uint32_t)in_idx.size();
   } else {
     cs.nodes.assign(32, 0.f);
+    cs.n_bvh_prims = 0;  // the device feeds every primitive through the linear tail of trace()
   }
   cs.n_nodes = (uint32_t)(cs.nodes.size() / 32);
   cs.n_prims = n;

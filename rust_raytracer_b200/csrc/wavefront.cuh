@@ -128,11 +128,14 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
       B.hit[slot] = make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), (unsigned int)h.prim, (unsigned int)h.aux);
       cls = h.prim < 0 ? WF_MISS : class_of_material(S, h.prim);
     }
-#pragma unroll
-    for (int c = 0; c < WF_NCLASS; ++c) {
-      unsigned int pos = warp_append(&B.cnt->n_class[c], active && cls == c);
-      if (active && cls == c) B.q_class[(size_t)c * B.pool + pos] = slot;
-    }
+    // bin by material class: the leader lane of every class present in the warp issues its atomic in the same
+    // instruction, so the warp pays one atomic round trip instead of one per class
+    const unsigned peers = __match_any_sync(0xffffffffu, active ? (unsigned)cls : (unsigned)WF_NCLASS);
+    const int leader = __ffs((int)peers) - 1;
+    unsigned int cbase = 0;
+    if (active && (int)lane == leader) cbase = atomicAdd(&B.cnt->n_class[cls], (unsigned)__popc(peers));
+    cbase = __shfl_sync(0xffffffffu, cbase, leader);
+    if (active) B.q_class[(size_t)cls * B.pool + cbase + __popc(peers & ((1u << lane) - 1u))] = slot;
   }
 }
 
