@@ -8,15 +8,16 @@ static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool) {
   const size_t P = pool;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
-  size_t o_ray_o = take(P * 16), o_ray_d = take(P * 16), o_hit = take(P * 16), o_sta = take(P * 16), o_stb = take(P * 16);
-  size_t o_qe = take(P * 4), o_qn = take(P * 4), o_qf = take(P * 4), o_qc = take(P * 4 * WF_NCLASS);
+  size_t o_set[2][4];
+  for (int k = 0; k < 2; ++k) for (int j = 0; j < 4; ++j) o_set[k][j] = take(P * 16);  // ray_o, ray_d, st_a, st_b, twice
+  size_t o_hit = take(P * 16), o_qc = take(P * 4 * WF_NCLASS);
   size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4), o_cnt = take(sizeof(WfCounters));
   CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
   char* b = (char*)ctx->wf_block;
   ctx->wf_bytes = off;
-  ctx->wf.ray_o = (float4*)(b + o_ray_o); ctx->wf.ray_d = (float4*)(b + o_ray_d); ctx->wf.hit = (uint4*)(b + o_hit);
-  ctx->wf.st_a = (float4*)(b + o_sta); ctx->wf.st_b = (uint4*)(b + o_stb);
-  ctx->wf.q_ext = (unsigned int*)(b + o_qe); ctx->wf.q_ext_next = (unsigned int*)(b + o_qn); ctx->wf.q_free = (unsigned int*)(b + o_qf);
+  ctx->wf.ray_o = (float4*)(b + o_set[0][0]); ctx->wf.ray_d = (float4*)(b + o_set[0][1]); ctx->wf.st_a = (float4*)(b + o_set[0][2]); ctx->wf.st_b = (uint4*)(b + o_set[0][3]);
+  ctx->wf.ray_o_n = (float4*)(b + o_set[1][0]); ctx->wf.ray_d_n = (float4*)(b + o_set[1][1]); ctx->wf.st_a_n = (float4*)(b + o_set[1][2]); ctx->wf.st_b_n = (uint4*)(b + o_set[1][3]);
+  ctx->wf.hit = (uint4*)(b + o_hit);
   ctx->wf.q_class = (unsigned int*)(b + o_qc);
   ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
   ctx->wf.cnt = (WfCounters*)(b + o_cnt);
@@ -73,31 +74,29 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   const bool shade_split = env_int("B200RT_WF_SHADE_SPLIT", 0, 0, 1) != 0;
   uint64_t launches = 0;
   uint32_t iters = 0;
-  int first = 1;
   float ms_stage[4] = {0.f, 0.f, 0.f, 0.f};
   const bool nee = P.integrator == B200RT_INTEGRATOR_NEE;
   for (;;) {
     for (int b = 0; b < batch; ++b) {
       cudaEvent_t* ev = ctx->sev + 8 * b;
       cudaEventRecord(ev[0], q);
-      k_wf_control_generate<<<1, 1, 0, q>>>(B, M, first);
-      k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M, first);
-      std::swap(B.q_ext, B.q_ext_next);  // the queue filled by shade + generate becomes the one extend reads
-      k_wf_control_extend<<<1, 1, 0, q>>>(B);
+      // the set shade just compacted the survivors into becomes the current one; generate appends behind them
+      std::swap(B.ray_o, B.ray_o_n); std::swap(B.ray_d, B.ray_d_n); std::swap(B.st_a, B.st_a_n); std::swap(B.st_b, B.st_b_n);
+      k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M);
+      k_wf_control<<<1, 1, 0, q>>>(B, M);
       cudaEventRecord(ev[1], q);
       k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
       cudaEventRecord(ev[2], q);
       if (shade_split) { for (int c = 0; c < WF_NCLASS; ++c) k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum, c); launches += WF_NCLASS - 1; }
       else k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum, -1);
       cudaEventRecord(ev[3], q);
-      launches += 5;
+      launches += 4;
       if (nee) {
         k_wf_control_shadow<<<1, 1, 0, q>>>(B);
         k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, P.t_min, accum);
         cudaEventRecord(ev[4], q);
         launches += 2;
       }
-      first = 0;
       iters++;
     }
     CU_CHECK(ctx, cudaGetLastError());

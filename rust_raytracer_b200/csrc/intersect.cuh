@@ -189,8 +189,6 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
   t_best32 = __double2float_ru(t);
 }
 
-// BVH4 node step: slab-tests the four children of inner node `cur` against [t_min, t_best32], pushes the far
-// hits (farthest first) and returns the nearest child reference, or B200RT_TRAV_DONE-style "none" via `any`.
 #define B200RT_TRAV_DONE 0xFFFFFFFFu  // leaf bit set with an impossible count: never a real child reference
 
 DEV uint32_t pop_next(const uint2* stack, int& sp, float t_best32) {
@@ -202,13 +200,59 @@ DEV uint32_t pop_next(const uint2* stack, int& sp, float t_best32) {
   return B200RT_TRAV_DONE;
 }
 
-DEV uint32_t node_step(const DevScene& S, const RayF& rf, uint32_t cur, float t_min, float t_best32, uint2* stack, int& sp) {
+#ifndef B200RT_NODE_FAST
+#define B200RT_NODE_FAST 1
+#endif
+#ifndef B200RT_NODE_FULLSORT
+#define B200RT_NODE_FULLSORT 0
+#endif
+
+// Per-ray constants of the node test.  t = plane * inv - o * inv is one FFMA per plane; the near / far plane of
+// every axis is chosen by ADDRESS (the node stores lo.x|lo.y|lo.z|hi.x|hi.y|hi.z as six float4 rows, so the
+// direction sign picks row a or row a + 3), which removes the per-child min/max pairs.  The rounding error of
+// o * inv (the only term the fused form adds over (plane - o) * inv) is folded into the two constants so the
+// test stays conservative: near parameters are lowered, far parameters raised by |o * inv| * 2^-22.
+struct RayT {
+  float3 inv, oin, oif;  // 1/d, o/d + e (near planes), o/d - e (far planes)
+  int nx, ny, nz;        // byte offset of the near-plane row of each axis: 0 or 48
+};
+DEV RayT make_rayt(const RayF& rf) {
+  RayT t;
+  t.inv = rf.inv;
+  const float3 oi = rf.o * rf.inv;
+  const float k = 2.3841858e-7f;  // 2^-22
+  t.oin = f3(oi.x + fabsf(oi.x) * k, oi.y + fabsf(oi.y) * k, oi.z + fabsf(oi.z) * k);
+  t.oif = f3(oi.x - fabsf(oi.x) * k, oi.y - fabsf(oi.y) * k, oi.z - fabsf(oi.z) * k);
+  t.nx = rf.inv.x < 0.f ? 48 : 0; t.ny = rf.inv.y < 0.f ? 48 : 0; t.nz = rf.inv.z < 0.f ? 48 : 0;
+  return t;
+}
+
+// BVH4 node step: slab-tests the four children of inner node `cur` against [t_min, t_best32], pushes the far
+// hits and returns the nearest child reference (or the next stack entry when no child is hit).
+DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32_t cur, float t_min, float t_best32, uint2* stack, int& sp) {
   DBG_INC(1);
+  float tn[4];
+#if B200RT_NODE_FAST
+  const char* nb = reinterpret_cast<const char*>(S.nodes) + ((size_t)cur << 7);
+  const float4 nxv = __ldg(reinterpret_cast<const float4*>(nb + rt.nx)), fxv = __ldg(reinterpret_cast<const float4*>(nb + 48 - rt.nx));
+  const float4 nyv = __ldg(reinterpret_cast<const float4*>(nb + 16 + rt.ny)), fyv = __ldg(reinterpret_cast<const float4*>(nb + 64 - rt.ny));
+  const float4 nzv = __ldg(reinterpret_cast<const float4*>(nb + 32 + rt.nz)), fzv = __ldg(reinterpret_cast<const float4*>(nb + 80 - rt.nz));
+  const int4 ref = __ldg(reinterpret_cast<const int4*>(nb + 96));
+  uint32_t rr[4] = {(uint32_t)ref.x, (uint32_t)ref.y, (uint32_t)ref.z, (uint32_t)ref.w};
+  const float ax[4] = {nxv.x, nxv.y, nxv.z, nxv.w}, ay[4] = {nyv.x, nyv.y, nyv.z, nyv.w}, az[4] = {nzv.x, nzv.y, nzv.z, nzv.w};
+  const float bx[4] = {fxv.x, fxv.y, fxv.z, fxv.w}, by[4] = {fyv.x, fyv.y, fyv.z, fyv.w}, bz[4] = {fzv.x, fzv.y, fzv.z, fzv.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float n = fmaxf(fmaxf(fmaf(ax[i], rt.inv.x, -rt.oin.x), fmaf(ay[i], rt.inv.y, -rt.oin.y)), fmaxf(fmaf(az[i], rt.inv.z, -rt.oin.z), t_min));
+    const float f = fminf(fminf(fmaf(bx[i], rt.inv.x, -rt.oif.x), fmaf(by[i], rt.inv.y, -rt.oif.y)), fminf(fmaf(bz[i], rt.inv.z, -rt.oif.z), t_best32));
+    const bool hit = (n <= f * 1.000001f) && (rr[i] != (uint32_t)B200RT_CHILD_EMPTY);
+    tn[i] = hit ? n : 3.0e38f;
+  }
+#else
   const float4* nd = S.nodes + 8 * (size_t)cur;
   const float4 lox = __ldg(nd + 0), loy = __ldg(nd + 1), loz = __ldg(nd + 2);
   const float4 hix = __ldg(nd + 3), hiy = __ldg(nd + 4), hiz = __ldg(nd + 5);
   const int4 ref = __ldg((const int4*)(nd + 6));
-  float tn[4];
   uint32_t rr[4] = {(uint32_t)ref.x, (uint32_t)ref.y, (uint32_t)ref.z, (uint32_t)ref.w};
   const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
   const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
@@ -222,9 +266,14 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, uint32_t cur, float t_
     bool hit = (n <= f * 1.000001f) && (rr[i] != (uint32_t)B200RT_CHILD_EMPTY);
     tn[i] = hit ? n : 3.0e38f;
   }
-  // sort the four (tn, ref) pairs ascending (5-comparator network)
+#endif
+  // Nearest child into slot 0 (three comparators); the full 5-comparator sort of the rest only matters when three
+  // or four children are hit (rare: ~1.4 hits per visited node on book-2), and pop_next culls by the stored tn anyway.
 #define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t tr = rr[a]; rr[a] = rr[b]; rr[b] = tr; }
-  CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2) CSWAP(1, 3) CSWAP(1, 2)
+  CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2)
+#if B200RT_NODE_FULLSORT
+  CSWAP(1, 3) CSWAP(1, 2)
+#endif
 #undef CSWAP
   if (tn[3] < 3.0e38f) stack[sp++] = make_uint2(rr[3], __float_as_uint(tn[3]));
   if (tn[2] < 3.0e38f) stack[sp++] = make_uint2(rr[2], __float_as_uint(tn[2]));
@@ -249,6 +298,7 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
   h.t = (double)ray.tmax; h.prim = -1; h.aux = 0;
   float t_best32 = ray.tmax;
   const RayF rf = make_rayf(ray);
+  const RayT rt = make_rayt(rf);
   DBG_INC(0);
   uint2 stack[B200RT_STACK];
   int sp = 0;
@@ -260,9 +310,9 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
   uint32_t cur = S.flat ? B200RT_TRAV_DONE : 0u;  // root node
   for (;;) {
 #if B200RT_TRAV_WW
-    while (!(cur & B200RT_LEAF_BIT)) cur = node_step(S, rf, cur, t_min, t_best32, stack, sp);
+    while (!(cur & B200RT_LEAF_BIT)) cur = node_step(S, rf, rt, cur, t_min, t_best32, stack, sp);
 #else
-    if (!(cur & B200RT_LEAF_BIT)) { cur = node_step(S, rf, cur, t_min, t_best32, stack, sp); continue; }
+    if (!(cur & B200RT_LEAF_BIT)) { cur = node_step(S, rf, rt, cur, t_min, t_best32, stack, sp); continue; }
 #endif
     if (wait_tail) {  // warp-uniform: the lanes that finished the BVH wait here until the whole warp has
       const bool all_done = __all_sync(lanes, cur == B200RT_TRAV_DONE);

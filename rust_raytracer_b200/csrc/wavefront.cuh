@@ -1,13 +1,14 @@
 // wavefront.cuh — the wavefront pipeline over SoA float4 ray queues (north_star): generate -> extend ->
-// per-material shade -> light-sample/shadow, with queue compaction by warp-aggregated atomics and in-place
-// regeneration of terminated paths so the pool stays full.
+// per-material shade -> light-sample/shadow, with stream compaction by warp-aggregated atomics.
 //
-// Per path slot (HBM, SoA, one float4/uint4 per array => fully coalesced 16-byte accesses):
-//   ray_o   (o.xyz, time)            ray_d  (d.xyz, t_max)
-//   hit     (t as 2 x u32 [f64], device prim, aux)
-//   st_a    (throughput.rgb, prev_pdf_b)
-//   st_b    (pixel, sample, bounce, medium seed)
-// Queues hold slot indices (u32).  Shadow requests are stored by queue position: sh_o, sh_d, sh_c(contrib.rgb, pixel).
+// The queues hold the ray PAYLOAD, not indices: queue position i of the current set is
+//   ray_o[i] (o.xyz, time)          ray_d[i] (d.xyz, medium seed bits; t_max of an extend ray is always +inf)
+//   st_a[i]  (throughput.rgb, prev_pdf_b)      st_b[i] (pixel, sample, bounce, 0)
+//   hit[i]   (t as 2 x u32 [f64], device prim, aux) written by extend
+// Shade compacts the surviving paths straight into the NEXT set (one warp-aggregated atomic per warp, then
+// coalesced 16-byte stores); generate appends freshly started paths behind them, so extend and generate touch
+// memory strictly in order and shade reads are sequential within a material class.  The two sets are swapped
+// by the host between iterations.  Shadow requests are stored by queue position: sh_o, sh_d, sh_c, sh_seed.
 #pragma once
 #include "kernels.cuh"
 
@@ -17,21 +18,20 @@
 struct WfCounters {
   unsigned long long next_path;     // next path id to generate
   unsigned long long extend_rays, shadow_rays, paths_done;
-  unsigned int n_ext;               // size of the current extend queue
-  unsigned int n_ext_next;          // size of the queue being filled by shade/generate
-  unsigned int n_free;              // slots released by shade this iteration
+  unsigned int n_ext;               // rays in the current set (extend + shade work list)
+  unsigned int n_ext_next;          // survivors appended to the next set by shade
   unsigned int n_shadow;            // shadow requests this iteration
   unsigned int n_class[WF_NCLASS];  // per-material shade queues
   unsigned int ext_cursor;          // work-fetch cursor of the persistent extend kernel
   unsigned int shadow_cursor;
-  unsigned int n_new;               // paths to generate this iteration
-  unsigned int pad;
-  unsigned long long gen_base;      // first path id of this iteration's generation
+  unsigned int pad[3];
 };
 
 struct WfBuffers {
-  float4* ray_o; float4* ray_d; uint4* hit; float4* st_a; uint4* st_b;
-  unsigned int* q_ext; unsigned int* q_ext_next; unsigned int* q_free; unsigned int* q_class;  // q_class: WF_NCLASS x pool
+  float4* ray_o; float4* ray_d; float4* st_a; uint4* st_b;          // current set
+  float4* ray_o_n; float4* ray_d_n; float4* st_a_n; uint4* st_b_n;  // next set
+  uint4* hit;
+  unsigned int* q_class;  // WF_NCLASS x pool queue positions
   float4* sh_o; float4* sh_d; float4* sh_c; unsigned int* sh_seed;
   WfCounters* cnt;
   unsigned int pool;
@@ -49,23 +49,39 @@ DEV unsigned int warp_append(unsigned int* counter, bool pred) {
   return base + __popc(mask & ((1u << lane) - 1u));
 }
 
-// Between stages: one thread turns the counters over (no host round trip inside an iteration).
-// phase 0: before generate  (decide how many paths to start, from the free list or the whole pool on the first pass)
-__global__ void k_wf_control_generate(WfBuffers B, PathMap M, int first_pass) {
-  WfCounters* c = B.cnt;
-  unsigned long long remaining = M.total - c->next_path;
-  unsigned int avail = first_pass ? B.pool : c->n_free;
-  unsigned int n_new = (unsigned int)(remaining < (unsigned long long)avail ? remaining : (unsigned long long)avail);
-  c->n_new = n_new;
-  c->gen_base = c->next_path;
-  c->next_path += n_new;
+// How many paths this iteration starts: the room left behind the survivors, capped by the paths that remain.
+// generate and the control kernel evaluate the same expression on the same (not yet updated) counters.
+DEV unsigned int wf_new_paths(const WfCounters* c, const PathMap& M, unsigned int pool) {
+  const unsigned long long remaining = M.total - c->next_path;
+  const unsigned int room = pool - c->n_ext_next;
+  return (unsigned int)(remaining < (unsigned long long)room ? remaining : (unsigned long long)room);
 }
-// phase 1: before extend (the queue filled by shade + generate becomes the current one; class queues reset)
-__global__ void k_wf_control_extend(WfBuffers B) {
+
+// generate: Camera::get_ray for new paths (camera.rs:57-64, 97-99), appended behind the survivors of the last
+// shade pass.  Path ids are consecutive, so a warp's primary rays cover an 8x4 pixel tile (coherent traversal).
+__global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P, PathMap M) {
+  const unsigned int n_new = wf_new_paths(B.cnt, M, B.pool);
+  const unsigned long long base = B.cnt->next_path;
+  const unsigned int off = B.cnt->n_ext_next;
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_new; i += gridDim.x * blockDim.x) {
+    uint32_t pixel, sample;
+    path_to_pixel(M, P, base + i, pixel, sample);
+    const Ray r = camera_ray(P, pixel, sample);
+    const unsigned int pos = off + i;
+    B.ray_o[pos] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+    B.ray_d[pos] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed));
+    B.st_a[pos] = make_float4(1.f, 1.f, 1.f, -1.f);
+    B.st_b[pos] = make_uint4(pixel, sample, 0u, 0u);
+  }
+}
+
+// One thread turns the counters over between generate and extend (no host round trip inside an iteration).
+__global__ void k_wf_control(WfBuffers B, PathMap M) {
   WfCounters* c = B.cnt;
-  c->n_ext = c->n_ext_next;
+  const unsigned int n_new = wf_new_paths(c, M, B.pool);
+  c->next_path += n_new;
+  c->n_ext = c->n_ext_next + n_new;
   c->n_ext_next = 0;
-  c->n_free = 0;
   c->n_shadow = 0;
   c->ext_cursor = 0;
   c->shadow_cursor = 0;
@@ -74,34 +90,13 @@ __global__ void k_wf_control_extend(WfBuffers B) {
 }
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
 
-// generate: Camera::get_ray for new paths (camera.rs:57-64, 97-99) into free slots
-__global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P, PathMap M, int first_pass) {
-  const unsigned int n_new = B.cnt->n_new;
-  const unsigned long long base = B.cnt->gen_base;
-  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_new; i += gridDim.x * blockDim.x) {
-    const unsigned int slot = first_pass ? i : B.q_free[i];
-    uint32_t pixel, sample;
-    const bool valid = true;
-    path_to_pixel(M, P, base + i, pixel, sample);
-    {
-      Ray r = camera_ray(P, pixel, sample);
-      B.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-      B.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, r.tmax);
-      B.st_a[slot] = make_float4(1.f, 1.f, 1.f, -1.f);
-      B.st_b[slot] = make_uint4(pixel, sample, 0u, r.mseed);
-    }
-    unsigned int pos = warp_append(&B.cnt->n_ext_next, valid);
-    if (valid) B.q_ext_next[pos] = slot;
-  }
-}
-
 DEV int class_of_material(const DevScene& S, int device_prim) {
   const int4 meta = __ldg(&S.prim_meta[device_prim]);
   return 1 + __float_as_int(__ldg(&S.materials[meta.x >> 8]).x);
 }
 
-// extend: persistent warps fetch 32 rays at a time from the queue (warp-level work fetch), traverse, store the
-// hit and bin the slot by material class for the shade kernels.
+// extend: persistent warps fetch 32 consecutive rays at a time (warp-level work fetch: coalesced 512-byte
+// reads of ray_o / ray_d), traverse, store the hit and bin the queue position by material class for shade.
 #ifndef B200RT_EXTEND_MINBLOCKS
 #define B200RT_EXTEND_MINBLOCKS 6
 #endif
@@ -116,16 +111,14 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     const unsigned int i = base + lane;
     const bool active = i < n;
     int cls = WF_MISS;
-    unsigned int slot = 0;
     if (active) {
-      slot = B.q_ext[i];
-      const float4 o = B.ray_o[slot], d = B.ray_d[slot];
+      const float4 o = B.ray_o[i], d = B.ray_d[i];
       Ray r;
-      r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = d.w; r.mseed = B.st_b[slot].w;
+      r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = __int_as_float(0x7f800000); r.mseed = __float_as_uint(d.w);
       HitRaw h;
       trace<false>(S, r, t_min, h);
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
-      B.hit[slot] = make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), (unsigned int)h.prim, (unsigned int)h.aux);
+      B.hit[i] = make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), (unsigned int)h.prim, (unsigned int)h.aux);
       cls = h.prim < 0 ? WF_MISS : class_of_material(S, h.prim);
     }
     // bin by material class: the leader lane of every class present in the warp issues its atomic in the same
@@ -135,12 +128,13 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     unsigned int cbase = 0;
     if (active && (int)lane == leader) cbase = atomicAdd(&B.cnt->n_class[cls], (unsigned)__popc(peers));
     cbase = __shfl_sync(0xffffffffu, cbase, leader);
-    if (active) B.q_class[(size_t)cls * B.pool + cbase + __popc(peers & ((1u << lane) - 1u))] = slot;
+    if (active) B.q_class[(size_t)cls * B.pool + cbase + __popc(peers & ((1u << lane) - 1u))] = i;
   }
 }
 
 // shade: ONE launch over all per-material queues.  Each queue is padded to a multiple of 32 in the index space, so
 // every warp works on a single material class (coherent branches) and the six classes run concurrently.
+// Survivors are written to the next set at their compacted position.
 __global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum, int only_cls) {
   unsigned int off[WF_NCLASS + 1];
   off[0] = 0;
@@ -154,39 +148,36 @@ __global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, Rende
     const unsigned int* q = B.q_class + (size_t)cls * B.pool;
     const bool active = i < B.cnt->n_class[cls];
     bool cont = false, shadow = false;
-    unsigned int slot = 0;
     Ray ray;
     PathState ps;
     ShadowReq sr;
     sr.valid = false;
     if (active) {
-      slot = q[i];
-      const float4 o = B.ray_o[slot], d = B.ray_d[slot], sa = B.st_a[slot];
-      const uint4 sb = B.st_b[slot], hh = B.hit[slot];
-      ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = d.w; ray.mseed = sb.w;
+      const unsigned int src = q[i];
+      const float4 o = B.ray_o[src], d = B.ray_d[src], sa = B.st_a[src];
+      const uint4 sb = B.st_b[src];
+      ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
       ps.throughput = f3(sa); ps.prev_pdf_b = sa.w; ps.radiance = f3(0, 0, 0);
       ps.pixel = sb.x; ps.sample = sb.y; ps.bounce = (int)sb.z;
       if (cls == WF_MISS) {
         ps.radiance = ps.throughput * background_color(P, ray.d);
       } else if (ps.bounce < P.max_depth) {  // photon_mapper.rs:336-339: the depth budget is checked after the hit
+        const uint4 hh = B.hit[src];
         HitRaw h;
         h.t = __longlong_as_double((long long)(((unsigned long long)hh.y << 32) | hh.x)); h.prim = (int)hh.z; h.aux = (int)hh.w;
         cont = shade_hit(S, P, ray, h, ps, sr);
         shadow = sr.valid;
       }
       accum_add(accum, ps.pixel, ps.radiance);
-      if (cont) {
-        B.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
-        B.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __int_as_float(0x7f800000));
-        B.st_a[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
-        B.st_b[slot] = make_uint4(ps.pixel, ps.sample, (unsigned int)ps.bounce, ray.mseed);
-      }
     }
-    unsigned int pe = warp_append(&B.cnt->n_ext_next, active && cont);
-    if (active && cont) B.q_ext_next[pe] = slot;
-    unsigned int pf = warp_append(&B.cnt->n_free, active && !cont);
-    if (active && !cont) B.q_free[pf] = slot;
-    unsigned int pq = warp_append(&B.cnt->n_shadow, shadow);
+    const unsigned int pe = warp_append(&B.cnt->n_ext_next, active && cont);
+    if (active && cont) {
+      B.ray_o_n[pe] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
+      B.ray_d_n[pe] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed));
+      B.st_a_n[pe] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
+      B.st_b_n[pe] = make_uint4(ps.pixel, ps.sample, (unsigned int)ps.bounce, 0u);
+    }
+    const unsigned int pq = warp_append(&B.cnt->n_shadow, shadow);
     if (shadow) {
       B.sh_o[pq] = make_float4(sr.ray.o.x, sr.ray.o.y, sr.ray.o.z, sr.ray.time);
       B.sh_d[pq] = make_float4(sr.ray.d.x, sr.ray.d.y, sr.ray.d.z, sr.ray.tmax);
