@@ -10,7 +10,7 @@ static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool) {
   auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
   size_t o_set[2][4];
   for (int k = 0; k < 2; ++k) for (int j = 0; j < 4; ++j) o_set[k][j] = take(P * 16);  // ray_o, ray_d, st_a, st_b, twice
-  size_t o_hit = take(P * 16), o_qc = take(P * 4 * WF_NCLASS);
+  size_t o_hit = take(P * 16), o_qc = take(P * 4 * WF_NBINS), o_bc = take(4 * WF_NBINS), o_bo = take(4 * (WF_NBINS + 1));
   size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4), o_cnt = take(sizeof(WfCounters));
   CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
   char* b = (char*)ctx->wf_block;
@@ -18,7 +18,7 @@ static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool) {
   ctx->wf.ray_o = (float4*)(b + o_set[0][0]); ctx->wf.ray_d = (float4*)(b + o_set[0][1]); ctx->wf.st_a = (float4*)(b + o_set[0][2]); ctx->wf.st_b = (uint4*)(b + o_set[0][3]);
   ctx->wf.ray_o_n = (float4*)(b + o_set[1][0]); ctx->wf.ray_d_n = (float4*)(b + o_set[1][1]); ctx->wf.st_a_n = (float4*)(b + o_set[1][2]); ctx->wf.st_b_n = (uint4*)(b + o_set[1][3]);
   ctx->wf.hit = (uint4*)(b + o_hit);
-  ctx->wf.q_class = (unsigned int*)(b + o_qc);
+  ctx->wf.q_bin = (unsigned int*)(b + o_qc); ctx->wf.bin_count = (unsigned int*)(b + o_bc); ctx->wf.bin_off = (unsigned int*)(b + o_bo);
   ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
   ctx->wf.cnt = (WfCounters*)(b + o_cnt);
   ctx->wf.pool = pool;
@@ -62,6 +62,10 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   int rc = wf_ensure_pool(ctx, pool);
   if (rc) return rc;
   WfBuffers B = ctx->wf;
+  {  // bin = 1 + umulhi(prim, bin_mul) maps [0, n_prims) onto bins 1 .. WF_NBINS - 1 (identity for tiny scenes)
+    const unsigned long long m = (((unsigned long long)(WF_NBINS - 1)) << 32) / (unsigned long long)(s->n_prims > 0 ? s->n_prims : 1);
+    B.bin_mul = m > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)m;
+  }
   CU_CHECK(ctx, cudaMemsetAsync(B.cnt, 0, sizeof(WfCounters), q));
   const int sms = ctx->prop.multiProcessorCount;
   int occ_ext = 1, occ_shadow = 1, occ_shade = 1;
@@ -71,7 +75,6 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   const int grid_ext = sms * (occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
   const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", (occ_shade > 0 ? occ_shade : 1) * 2, 1, 64);
   const int batch = env_int("B200RT_WF_BATCH", 4, 1, 8);
-  const bool shade_split = env_int("B200RT_WF_SHADE_SPLIT", 0, 0, 1) != 0;
   uint64_t launches = 0;
   uint32_t iters = 0;
   float ms_stage[4] = {0.f, 0.f, 0.f, 0.f};
@@ -87,10 +90,10 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
       cudaEventRecord(ev[1], q);
       k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
       cudaEventRecord(ev[2], q);
-      if (shade_split) { for (int c = 0; c < WF_NCLASS; ++c) k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum, c); launches += WF_NCLASS - 1; }
-      else k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum, -1);
+      k_wf_control_shade<<<1, 1, 0, q>>>(B);
+      k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
       cudaEventRecord(ev[3], q);
-      launches += 4;
+      launches += 5;
       if (nee) {
         k_wf_control_shadow<<<1, 1, 0, q>>>(B);
         k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, P.t_min, accum);

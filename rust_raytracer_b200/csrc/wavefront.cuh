@@ -12,8 +12,14 @@
 #pragma once
 #include "kernels.cuh"
 
-#define WF_NCLASS 6  // 0 miss, 1 Lambertian, 2 Metal, 3 Dielectric, 4 DiffuseLight, 5 Isotropic
-#define WF_MISS 0
+// Shade work is binned by WHERE the ray ended: bin 0 = miss, bins 1.. = the hit primitive's index in BVH leaf order
+// (spatially coherent, and one primitive has one material) scaled to WF_NBINS - 1 bins.  Shade walks the bins in
+// order, so (a) its warps are material-coherent and (b) the survivors land in the next queue grouped by origin
+// region and by expected traversal cost (fog-born rays together, ground-box rays together, ...), which is what
+// keeps the extend warps converged.  Bin storage is WF_NBINS x pool indices: HBM is plentiful (180 GB).
+#ifndef WF_NBINS
+#define WF_NBINS 256
+#endif
 
 struct WfCounters {
   unsigned long long next_path;     // next path id to generate
@@ -21,17 +27,20 @@ struct WfCounters {
   unsigned int n_ext;               // rays in the current set (extend + shade work list)
   unsigned int n_ext_next;          // survivors appended to the next set by shade
   unsigned int n_shadow;            // shadow requests this iteration
-  unsigned int n_class[WF_NCLASS];  // per-material shade queues
   unsigned int ext_cursor;          // work-fetch cursor of the persistent extend kernel
   unsigned int shadow_cursor;
-  unsigned int pad[3];
+  unsigned int n_work;              // shade index space: sum of the bin sizes, each padded to a multiple of 32
+  unsigned int pad[2];
 };
 
 struct WfBuffers {
   float4* ray_o; float4* ray_d; float4* st_a; uint4* st_b;          // current set
   float4* ray_o_n; float4* ray_d_n; float4* st_a_n; uint4* st_b_n;  // next set
   uint4* hit;
-  unsigned int* q_class;  // WF_NCLASS x pool queue positions
+  unsigned int* q_bin;    // WF_NBINS x pool queue positions
+  unsigned int* bin_count;  // WF_NBINS
+  unsigned int* bin_off;    // WF_NBINS + 1: start of every bin in the padded shade index space
+  unsigned int bin_mul;     // bin = 1 + umulhi(prim, bin_mul)
   float4* sh_o; float4* sh_d; float4* sh_c; unsigned int* sh_seed;
   WfCounters* cnt;
   unsigned int pool;
@@ -86,14 +95,16 @@ __global__ void k_wf_control(WfBuffers B, PathMap M) {
   c->ext_cursor = 0;
   c->shadow_cursor = 0;
   c->extend_rays += c->n_ext;
-  for (int i = 0; i < WF_NCLASS; ++i) c->n_class[i] = 0;
+  for (int i = 0; i < WF_NBINS; ++i) B.bin_count[i] = 0;
+}
+// after extend: the padded prefix sum of the bin sizes (shade's index space)
+__global__ void k_wf_control_shade(WfBuffers B) {
+  unsigned int off = 0;
+  for (int i = 0; i < WF_NBINS; ++i) { B.bin_off[i] = off; off += (B.bin_count[i] + 31u) & ~31u; }
+  B.bin_off[WF_NBINS] = off;
+  B.cnt->n_work = off;
 }
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
-
-DEV int class_of_material(const DevScene& S, int device_prim) {
-  const int4 meta = __ldg(&S.prim_meta[device_prim]);
-  return 1 + __float_as_int(__ldg(&S.materials[meta.x >> 8]).x);
-}
 
 // extend: persistent warps fetch 32 consecutive rays at a time (warp-level work fetch: coalesced 512-byte
 // reads of ray_o / ray_d), traverse, store the hit and bin the queue position by material class for shade.
@@ -110,7 +121,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     if (base >= n) break;
     const unsigned int i = base + lane;
     const bool active = i < n;
-    int cls = WF_MISS;
+    unsigned int bin = 0;
     if (active) {
       const float4 o = B.ray_o[i], d = B.ray_d[i];
       Ray r;
@@ -119,34 +130,33 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
       trace<false>(S, r, t_min, h);
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
       B.hit[i] = make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), (unsigned int)h.prim, (unsigned int)h.aux);
-      cls = h.prim < 0 ? WF_MISS : class_of_material(S, h.prim);
+      bin = h.prim < 0 ? 0u : 1u + __umulhi((unsigned int)h.prim, B.bin_mul);
     }
-    // bin by material class: the leader lane of every class present in the warp issues its atomic in the same
-    // instruction, so the warp pays one atomic round trip instead of one per class
-    const unsigned peers = __match_any_sync(0xffffffffu, active ? (unsigned)cls : (unsigned)WF_NCLASS);
+    // the leader lane of every bin present in the warp issues its atomic in the same instruction: one atomic
+    // round trip per warp, whatever the number of bins
+    const unsigned peers = __match_any_sync(0xffffffffu, active ? bin : (unsigned)WF_NBINS);
     const int leader = __ffs((int)peers) - 1;
     unsigned int cbase = 0;
-    if (active && (int)lane == leader) cbase = atomicAdd(&B.cnt->n_class[cls], (unsigned)__popc(peers));
+    if (active && (int)lane == leader) cbase = atomicAdd(&B.bin_count[bin], (unsigned)__popc(peers));
     cbase = __shfl_sync(0xffffffffu, cbase, leader);
-    if (active) B.q_class[(size_t)cls * B.pool + cbase + __popc(peers & ((1u << lane) - 1u))] = i;
+    if (active) B.q_bin[(size_t)bin * B.pool + cbase + __popc(peers & ((1u << lane) - 1u))] = i;
   }
 }
 
-// shade: ONE launch over all per-material queues.  Each queue is padded to a multiple of 32 in the index space, so
-// every warp works on a single material class (coherent branches) and the six classes run concurrently.
-// Survivors are written to the next set at their compacted position.
-__global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum, int only_cls) {
-  unsigned int off[WF_NCLASS + 1];
-  off[0] = 0;
-#pragma unroll
-  for (int c = 0; c < WF_NCLASS; ++c) off[c + 1] = off[c] + ((only_cls < 0 || only_cls == c) ? ((B.cnt->n_class[c] + 31u) & ~31u) : 0u);
-  for (unsigned int gi = blockIdx.x * blockDim.x + threadIdx.x; gi < off[WF_NCLASS]; gi += gridDim.x * blockDim.x) {
-    int cls = 0;
-#pragma unroll
-    for (int c = 1; c < WF_NCLASS; ++c) cls += (gi >= off[c]) ? 1 : 0;
-    const unsigned int i = gi - off[cls];
-    const unsigned int* q = B.q_class + (size_t)cls * B.pool;
-    const bool active = i < B.cnt->n_class[cls];
+// shade: ONE launch over all bins.  Each bin is padded to a multiple of 32 in the index space, so every warp
+// works on a single bin (one or a few neighbouring primitives: coherent material branches).  Survivors are
+// written to the next set at their compacted position.
+__global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
+  __shared__ unsigned int s_off[WF_NBINS + 1];
+  for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) s_off[k] = B.bin_off[k];
+  __syncthreads();
+  const unsigned int n_work = s_off[WF_NBINS];
+  for (unsigned int gi = blockIdx.x * blockDim.x + threadIdx.x; gi < n_work; gi += gridDim.x * blockDim.x) {
+    int lo = 0, hi = WF_NBINS;  // the bin with s_off[bin] <= gi < s_off[bin + 1] (warp-uniform: bins are 32-aligned)
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (gi >= s_off[mid]) lo = mid; else hi = mid; }
+    const unsigned int i = gi - s_off[lo];
+    const unsigned int* q = B.q_bin + (size_t)lo * B.pool;
+    const bool active = i < B.bin_count[lo];
     bool cont = false, shadow = false;
     Ray ray;
     PathState ps;
@@ -155,14 +165,13 @@ __global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, Rende
     if (active) {
       const unsigned int src = q[i];
       const float4 o = B.ray_o[src], d = B.ray_d[src], sa = B.st_a[src];
-      const uint4 sb = B.st_b[src];
+      const uint4 sb = B.st_b[src], hh = B.hit[src];
       ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
       ps.throughput = f3(sa); ps.prev_pdf_b = sa.w; ps.radiance = f3(0, 0, 0);
       ps.pixel = sb.x; ps.sample = sb.y; ps.bounce = (int)sb.z;
-      if (cls == WF_MISS) {
+      if ((int)hh.z < 0) {  // miss
         ps.radiance = ps.throughput * background_color(P, ray.d);
       } else if (ps.bounce < P.max_depth) {  // photon_mapper.rs:336-339: the depth budget is checked after the hit
-        const uint4 hh = B.hit[src];
         HitRaw h;
         h.t = __longlong_as_double((long long)(((unsigned long long)hh.y << 32) | hh.x)); h.prim = (int)hh.z; h.aux = (int)hh.w;
         cont = shade_hit(S, P, ray, h, ps, sr);

@@ -1,11 +1,15 @@
 """Per-source-line warp-instruction counts (aggregated over inlined copies). usage: ncu -i rep --page source --csv --print-source cuda,sass | python tools/ncu_source_by_inst.py [top]"""
 import csv, sys, collections
 top = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+want = sys.argv[2] if len(sys.argv) > 2 else None  # optional kernel-name substring filter
+keep = True
 rows = list(csv.reader(sys.stdin))
 cur, hdr = None, None
 agg = collections.defaultdict(lambda: [0, 0, 0, ""])
 for r in rows:
     if not r: continue
+    if r[0] == "Kernel Name": keep = (want is None) or (want in r[1])
+    if not keep: continue
     if r[0] == "File Path": cur = r[1].split("/")[-1]
     elif r[0] == "Line No": hdr = r
     elif hdr and r[0].isdigit():
