@@ -26,8 +26,8 @@ SPP_PER_STEP = 128          # per GPU and step; the full job is 10,000 spp (Mpat
 FULL_JOB_SPP = 10000
 METRIC = "Mpaths/s (device-timed) on book-2 final scene"
 UNIT = "Mpaths/s"
-# extend kernel, per ray: ray_o 16 + ray_d 16 + st_b 16 (medium seed) + queue index 4 read; hit 16 + class queue 4 written
-EXTEND_BYTES_PER_RAY = 72
+# extend kernel, per ray: ray_o 16 + ray_d 16 read (the medium seed rides in ray_d.w); hit 16 + bin queue index 4 written
+EXTEND_BYTES_PER_RAY = 52
 SEGMENT_BYTES_PIPELINE = 128  # ray 32 + hit 16 + state 16, written once and read once
 
 
@@ -289,7 +289,7 @@ def main():
             "config": {"workload": "book-2 final scene 800x800 (BASELINE.json configs[3]): 1409 primitives incl. 400 boxes, 1000 instanced spheres, moving sphere, 2 constant media, Perlin + earthmap textures",
                        "spp_per_step_per_gpu": spp, "full_job_spp": FULL_JOB_SPP, "max_depth": 50, "integrator": "path", "pipeline": args.pipeline,
                        "sharding": "spp ranges per rank + NCCL sum-reduce of the accumulation buffer per step",
-                       "l2": "256 MB write between timed steps; wavefront queue state (%d MB) exceeds L2" % (168 * (1 << 21) >> 20)},
+                       "l2": "256 MB write between timed steps; the wavefront queues (2^24 path slots x 196 B of ray/state/hit payload = 3.3 GB, plus bin index space) exceed L2"},
             "mrays_per_s": mrays, "rays_per_path": (ext + shd) / paths,
             "stage_ms_per_step": {k: stats[k] / args.steps for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total")},
             "wavefront_iterations_per_step": stats["wavefront_iterations"] / args.steps,

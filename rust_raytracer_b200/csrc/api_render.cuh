@@ -56,7 +56,7 @@ static int env_int(const char* name, int dflt, int lo, int hi) {
 static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap& M, float* accum, b200rt_stats* st) {
   b200rt_ctx* ctx = s->ctx;
   cudaStream_t q = ctx->stream;
-  const unsigned long long cap = 1ull << env_int("B200RT_WF_POOL_LOG2", 21, 12, 24);
+  const unsigned long long cap = 1ull << env_int("B200RT_WF_POOL_LOG2", 24, 12, 26);
   unsigned long long want = (M.total + 31ull) & ~31ull;
   unsigned int pool = (unsigned int)(want < cap ? want : cap);
   int rc = wf_ensure_pool(ctx, pool);

@@ -23,7 +23,9 @@
 
 #define B200RT_CHILD_EMPTY 0x7FFFFFFF
 #define B200RT_LEAF_BIT 0x80000000u
+#ifndef B200RT_MAX_LEAF
 #define B200RT_MAX_LEAF 4
+#endif
 #define B200RT_STACK 64
 
 #ifdef __CUDACC__

@@ -14,25 +14,39 @@ struct RayF {
 
 DEV float safe_rcp(float d) { return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
 
+// Filter verdicts
+#define FILTER_MAYBE 0        // the exact test decides
+#define FILTER_REJECT 1       // certain miss
+#define FILTER_MEDIUM_HIT 2   // ConstantMedium only: certain scatter before the boundary exit / the best hit, origin inside
+
 // ConstantMedium::hit (medium.rs:25-53) in f32.  [t_in, t_out] is the boundary interval (errors e_in, e_out):
 // distance_inside <= (min(t_out, t_best) - max(t_in, t_min, 0)) * |d|; the scattering distance
 // hit_distance = -1/density * ln(xi) is known to ~3 ulp, so when it exceeds that upper bound the medium is a
-// certain miss and the f64 boundary roots / log never run.
-DEV bool medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, float e_out, float neg_inv_density, float xi, float t_min, float t_best) {
+// certain miss and the f64 boundary roots / log never run.  Conversely, when the ray certainly starts inside
+// (t_in < t_min) and hit_distance is certainly below the LOWER bound of distance_inside, the outcome is a hit at
+// t = max(t_min, 0) + hit_distance / |d| whatever the exact boundary roots are: the exact stage then skips them.
+DEV int medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, float e_out, float neg_inv_density, float xi, float t_min, float t_best) {
   const float lo = fmaxf(fmaxf(t_in - e_in, t_min), 0.f);
   const float hi = fminf(t_out + e_out, t_best);
   const float len = sqrtf(r.a);
   float upper = fmaxf(hi - lo, 0.f) + 2e-7f * (fabsf(hi) + fabsf(lo));
   upper = upper * len * (1.0f + 2e-6f);
   const float hd = neg_inv_density * logf(xi);  // >= 0
-  return hd * (1.0f - 2e-6f) > upper;           // NaN/inf upper (t_best = inf, unbounded boundary) never rejects
+  if (hd * (1.0f - 2e-6f) > upper) return FILTER_REJECT;  // NaN/inf upper (t_best = inf, unbounded boundary) never rejects
+  if (t_in + e_in < t_min) {
+    const float lo1 = fmaxf(t_min, 0.f);                                    // exact: t1 after both clamps
+    const float hi1 = fminf(t_out - e_out, t_best * (1.0f - 2.4e-7f));      // lower bound of min(t_out, t_max); t_best is rounded up
+    const float lower = ((hi1 - lo1) - 2e-7f * (fabsf(hi1) + fabsf(lo1))) * len * (1.0f - 2e-6f);
+    if (hi1 > lo1 * (1.0f + 1e-6f) + 1e-30f && hd * (1.0f + 2e-6f) < lower) return FILTER_MEDIUM_HIT;
+  }
+  return FILTER_MAYBE;
 }
 
 // sphere.rs:24-43 in f32: disc error <= ~20u * a * (|oc|^2 + r^2)
 // eps: absolute error of the baked world-space coordinates of an instanced primitive (0 when not instanced):
 // the exact test then runs in OBJECT space on the original values, so the filter must tolerate the baking error.
 // medium = true: the sphere is a ConstantMedium boundary (both roots matter, then the distance test).
-DEV bool sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best, float eps, bool medium = false, float neg_inv_density = 0.f, float xi = 0.5f) {
+DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best, float eps, bool medium = false, float neg_inv_density = 0.f, float xi = 0.5f) {
   float3 oc = r.o - c;
   float hb = dot(oc, r.d), oc2 = dot(oc, oc), r2 = radius * radius;
   float cc = oc2 - r2;
@@ -71,7 +85,7 @@ DEV bool rect_reject(const RayF& r, int axis, float a0, float b0, float a1, floa
 // parameter lies within the f32 error of the slab ENTRY point, bits 8..13 = sides near the EXIT point (side
 // numbering of cube_side: XY@min.z, XY@max.z, XZ@min.y, XZ@max.y, YZ@min.x, YZ@max.x).  A face whose plane hit
 // is neither is out of its rectangle bounds for certain, so the exact test may skip it.
-DEV bool box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best, float eps, uint32_t* cand = nullptr, bool medium = false, float neg_inv_density = 0.f,
+DEV int box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best, float eps, uint32_t* cand = nullptr, bool medium = false, float neg_inv_density = 0.f,
                     float xi = 0.5f) {
   float3 t0 = (mn - r.o) * r.inv, t1 = (mx - r.o) * r.inv;
   float tn = fmaxf(fmaxf(fminf(t0.x, t1.x), fminf(t0.y, t1.y)), fminf(t0.z, t1.z));

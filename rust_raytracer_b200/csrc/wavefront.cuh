@@ -107,7 +107,10 @@ __global__ void k_wf_control_shade(WfBuffers B) {
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
 
 // extend: persistent warps fetch 32 consecutive rays at a time (warp-level work fetch: coalesced 512-byte
-// reads of ray_o / ray_d), traverse, store the hit and bin the queue position by material class for shade.
+// reads of ray_o / ray_d), traverse, store the hit and bin the queue position for shade.
+// (Measured and rejected: per-lane ray replacement a la Aila & Laine's dynamic fetch.  Refilling idle lanes from
+// the queue mixes rays of different bins in one warp and loses the converged out-of-BVH tail: 60 ms -> 74..99 ms
+// of extend per step on book-2 for refill thresholds 16..28, profiles/r1_experiments.md.)
 #ifndef B200RT_EXTEND_MINBLOCKS
 #define B200RT_EXTEND_MINBLOCKS 6
 #endif
@@ -146,7 +149,10 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
 // shade: ONE launch over all bins.  Each bin is padded to a multiple of 32 in the index space, so every warp
 // works on a single bin (one or a few neighbouring primitives: coherent material branches).  Survivors are
 // written to the next set at their compacted position.
-__global__ void __launch_bounds__(128) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
+#ifndef B200RT_SHADE_MINBLOCKS
+#define B200RT_SHADE_MINBLOCKS 4
+#endif
+__global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   __shared__ unsigned int s_off[WF_NBINS + 1];
   for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) s_off[k] = B.bin_off[k];
   __syncthreads();
