@@ -71,9 +71,13 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   int occ_ext = 1, occ_shadow = 1, occ_shade = 1;
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend, 128, 0));
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow, 128, 0));
-  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade, 128, 0));
+  CU_CHECK(ctx, P.integrator == B200RT_INTEGRATOR_PATH ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_PATH>, 128, 0)
+                : P.integrator == B200RT_INTEGRATOR_MIXTURE ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_MIXTURE>, 128, 0)
+                                                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_NEE>, 128, 0));
   const int grid_ext = sms * (occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
-  const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", (occ_shade > 0 ? occ_shade : 1) * 2, 1, 64);
+  const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", occ_shade > 4 ? 4 : (occ_shade > 0 ? occ_shade : 1), 1, 64);
+  // (4 resident shade blocks per SM: a larger grid widens the window of queue positions in flight, which interleaves
+  //  the bins in the compacted output and costs the next extend pass ~5 %; measured in profiles/r1_experiments.md)
   const int batch = env_int("B200RT_WF_BATCH", 4, 1, 8);
   uint64_t launches = 0;
   uint32_t iters = 0;
@@ -91,7 +95,9 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
       k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
       cudaEventRecord(ev[2], q);
       k_wf_control_shade<<<1, 1, 0, q>>>(B);
-      k_wf_shade<<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
+      if (P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
+      else if (P.integrator == B200RT_INTEGRATOR_MIXTURE) k_wf_shade<B200RT_INTEGRATOR_MIXTURE><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
+      else k_wf_shade<B200RT_INTEGRATOR_NEE><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
       cudaEventRecord(ev[3], q);
       launches += 5;
       if (nee) {

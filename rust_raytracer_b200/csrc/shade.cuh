@@ -175,7 +175,11 @@ DEV float3 refract3(float3 uv, float3 n, float eta) {                        // 
 
 // Processes the hit `h` of `ray`: adds emission, samples the next direction.  Returns true when the path
 // continues (ray is replaced).  depth bookkeeping (photon_mapper.rs:334-339) is done by the caller.
+// INTEG >= 0 fixes the integrator at compile time (the wavefront shade kernel is instantiated per integrator, so
+// the PATH build carries no light-sampling code: fewer registers, a third of the instructions); -1 reads P.integrator.
+template <int INTEG = -1>
 DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitRaw& hr, PathState& ps, ShadowReq& sreq) {
+  const int integrator = INTEG >= 0 ? INTEG : P.integrator;
   sreq.valid = false;
   const int4 meta = __ldg(&S.prim_meta[hr.prim]);
   const float4 mat = __ldg(&S.materials[meta.x >> 8]);
@@ -190,7 +194,7 @@ DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitR
 
   if (mtype == B200RT_MAT_DIFFUSE_LIGHT) {  // emitted = emit.get_color(rec), both faces (material.rs:209-211)
     float w = 1.f;
-    if (P.integrator == B200RT_INTEGRATOR_NEE && ps.prev_pdf_b >= 0.f && S.n_lights > 0) {
+    if (integrator == B200RT_INTEGRATOR_NEE && ps.prev_pdf_b >= 0.f && S.n_lights > 0) {
       int li = light_index_of_prim(S, h.prim_orig);
       if (li >= 0) {
         float pl = light_pdf_one(S, li, ray.o, ray.d, P.t_min) / (float)S.n_lights;
@@ -208,10 +212,10 @@ DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitR
     return true;
   }
   const bool diffuse = mtype == B200RT_MAT_LAMBERTIAN || mtype == B200RT_MAT_ISOTROPIC;
-  if (diffuse && P.integrator != B200RT_INTEGRATOR_PATH) {
+  if (diffuse && integrator != B200RT_INTEGRATOR_PATH) {
     const bool iso = mtype == B200RT_MAT_ISOTROPIC;
     const bool use_lights = S.n_lights > 0;
-    if (P.integrator == B200RT_INTEGRATOR_MIXTURE) {  // MixturePDF: 1/2 lights + 1/2 bsdf lobe
+    if (integrator == B200RT_INTEGRATOR_MIXTURE) {  // MixturePDF: 1/2 lights + 1/2 bsdf lobe
       float3 dir;
       if (use_lights && u3 < 0.5f) {
         const uint4 r2 = philox4x32(make_uint4(ps.pixel, ps.sample, (uint32_t)ps.bounce, 1u), P.key);

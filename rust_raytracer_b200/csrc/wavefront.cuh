@@ -112,7 +112,7 @@ __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->
 // the queue mixes rays of different bins in one warp and loses the converged out-of-BVH tail: 60 ms -> 74..99 ms
 // of extend per step on book-2 for refill thresholds 16..28, profiles/r1_experiments.md.)
 #ifndef B200RT_EXTEND_MINBLOCKS
-#define B200RT_EXTEND_MINBLOCKS 6
+#define B200RT_EXTEND_MINBLOCKS 8
 #endif
 __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevScene S, WfBuffers B, float t_min) {
   const unsigned int n = B.cnt->n_ext;
@@ -152,6 +152,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
 #ifndef B200RT_SHADE_MINBLOCKS
 #define B200RT_SHADE_MINBLOCKS 4
 #endif
+template <int INTEG>
 __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   __shared__ unsigned int s_off[WF_NBINS + 1];
   for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) s_off[k] = B.bin_off[k];
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevSce
       } else if (ps.bounce < P.max_depth) {  // photon_mapper.rs:336-339: the depth budget is checked after the hit
         HitRaw h;
         h.t = __longlong_as_double((long long)(((unsigned long long)hh.y << 32) | hh.x)); h.prim = (int)hh.z; h.aux = (int)hh.w;
-        cont = shade_hit(S, P, ray, h, ps, sr);
+        cont = shade_hit<INTEG>(S, P, ray, h, ps, sr);
         shadow = sr.valid;
       }
       accum_add(accum, ps.pixel, ps.radiance);
@@ -192,6 +193,7 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevSce
       B.st_a_n[pe] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
       B.st_b_n[pe] = make_uint4(ps.pixel, ps.sample, (unsigned int)ps.bounce, 0u);
     }
+    if (INTEG != B200RT_INTEGRATOR_NEE) continue;  // only the NEE integrator produces shadow requests
     const unsigned int pq = warp_append(&B.cnt->n_shadow, shadow);
     if (shadow) {
       B.sh_o[pq] = make_float4(sr.ray.o.x, sr.ray.o.y, sr.ray.o.z, sr.ray.time);
