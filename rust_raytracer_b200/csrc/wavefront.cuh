@@ -1,14 +1,15 @@
 // wavefront.cuh — the wavefront pipeline over SoA float4 ray queues (north_star): generate -> extend ->
 // per-material shade -> light-sample/shadow, with stream compaction by warp-aggregated atomics.
 //
-// The queues hold the ray PAYLOAD, not indices: queue position i of the current set is
-//   ray_o[i] (o.xyz, time)          ray_d[i] (d.xyz, medium seed bits; t_max of an extend ray is always +inf)
-//   st_a[i]  (throughput.rgb, prev_pdf_b)      st_b[i] (pixel, sample, bounce, 0)
-//   hit[i]   (t as 2 x u32 [f64], device prim, aux) written by extend
-// Shade compacts the surviving paths straight into the NEXT set (one warp-aggregated atomic per warp, then
-// coalesced 16-byte stores); generate appends freshly started paths behind them, so extend and generate touch
-// memory strictly in order and shade reads are sequential within a material class.  The two sets are swapped
-// by the host between iterations.  Shadow requests are stored by queue position: sh_o, sh_d, sh_c, sh_seed.
+// The queues hold the ray PAYLOAD, not indices, as one 96-byte record (three 32-byte DRAM sectors) per position:
+//   sector 0: (o.xyz, time) (d.xyz, medium seed bits; t_max of an extend ray is always +inf)   read by extend + shade
+//   sector 1: (throughput.rgb, prev_pdf_b) (pixel, sample, bounce, 0)                           read by shade
+//   sector 2: (t as 2 x u32 [f64], device prim, aux) (spare)                                    written by extend
+// Shade gathers whole records (every sector it touches is fully used: the SoA version of this layout read 154 B
+// per ray from DRAM for 84 B of payload), compacts the surviving paths straight into the NEXT set (one
+// warp-aggregated atomic per warp, then 64 contiguous bytes per lane); generate appends freshly started paths
+// behind them, so extend and generate touch memory strictly in order.  The two sets are swapped by the host
+// between iterations.  Shadow requests are stored by queue position: sh_o, sh_d, sh_c, sh_seed.
 #pragma once
 #include "kernels.cuh"
 
@@ -17,6 +18,7 @@
 // order, so (a) its warps are material-coherent and (b) the survivors land in the next queue grouped by origin
 // region and by expected traversal cost (fog-born rays together, ground-box rays together, ...), which is what
 // keeps the extend warps converged.  Bin storage is WF_NBINS x pool indices: HBM is plentiful (180 GB).
+#define WF_REC 6  // float4 per queue record (96 bytes)
 #ifndef WF_NBINS
 #define WF_NBINS 256
 #endif
@@ -34,9 +36,8 @@ struct WfCounters {
 };
 
 struct WfBuffers {
-  float4* ray_o; float4* ray_d; float4* st_a; uint4* st_b;          // current set
-  float4* ray_o_n; float4* ray_d_n; float4* st_a_n; uint4* st_b_n;  // next set
-  uint4* hit;
+  float4* rec;    // current set: WF_REC float4 per queue position
+  float4* rec_n;  // next set
   unsigned int* q_bin;    // WF_NBINS x pool queue positions
   unsigned int* bin_count;  // WF_NBINS
   unsigned int* bin_off;    // WF_NBINS + 1: start of every bin in the padded shade index space
@@ -76,11 +77,11 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P,
     uint32_t pixel, sample;
     path_to_pixel(M, P, base + i, pixel, sample);
     const Ray r = camera_ray(P, pixel, sample);
-    const unsigned int pos = off + i;
-    B.ray_o[pos] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-    B.ray_d[pos] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed));
-    B.st_a[pos] = make_float4(1.f, 1.f, 1.f, -1.f);
-    B.st_b[pos] = make_uint4(pixel, sample, 0u, 0u);
+    float4* rec = B.rec + (size_t)WF_REC * (off + i);
+    rec[0] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+    rec[1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed));
+    rec[2] = make_float4(1.f, 1.f, 1.f, -1.f);
+    rec[3] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), 0.f, 0.f);
   }
 }
 
@@ -126,13 +127,15 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     const bool active = i < n;
     unsigned int bin = 0;
     if (active) {
-      const float4 o = B.ray_o[i], d = B.ray_d[i];
+      float4* rec = B.rec + (size_t)WF_REC * i;
+      const float4 o = rec[0], d = rec[1];
       Ray r;
       r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = __int_as_float(0x7f800000); r.mseed = __float_as_uint(d.w);
       HitRaw h;
       trace<false>(S, r, t_min, h);
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
-      B.hit[i] = make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), (unsigned int)h.prim, (unsigned int)h.aux);
+      rec[4] = make_float4(__uint_as_float((unsigned int)tb), __uint_as_float((unsigned int)(tb >> 32)), __int_as_float(h.prim), __int_as_float(h.aux));
+      rec[5] = make_float4(0.f, 0.f, 0.f, 0.f);  // the whole 32-byte sector is written: no read-modify-write
       bin = h.prim < 0 ? 0u : 1u + __umulhi((unsigned int)h.prim, B.bin_mul);
     }
     // the leader lane of every bin present in the warp issues its atomic in the same instruction: one atomic
@@ -155,24 +158,46 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
 template <int INTEG>
 __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   __shared__ unsigned int s_off[WF_NBINS + 1];
-  for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) s_off[k] = B.bin_off[k];
+  __shared__ unsigned int s_cnt[WF_NBINS];
+  for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) { s_off[k] = B.bin_off[k]; if (k < WF_NBINS) s_cnt[k] = B.bin_count[k]; }
   __syncthreads();
   const unsigned int n_work = s_off[WF_NBINS];
-  for (unsigned int gi = blockIdx.x * blockDim.x + threadIdx.x; gi < n_work; gi += gridDim.x * blockDim.x) {
-    int lo = 0, hi = WF_NBINS;  // the bin with s_off[bin] <= gi < s_off[bin + 1] (warp-uniform: bins are 32-aligned)
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (gi >= s_off[mid]) lo = mid; else hi = mid; }
-    const unsigned int i = gi - s_off[lo];
-    const unsigned int* q = B.q_bin + (size_t)lo * B.pool;
-    const bool active = i < B.bin_count[lo];
+  const unsigned int stride = gridDim.x * blockDim.x;
+  // queue position of work item g (bins are 32-aligned in the index space, so the lookup is warp-uniform)
+  auto fetch_src = [&](unsigned int g, bool& act, unsigned int& src) {
+    act = false; src = 0u;
+    if (g >= n_work) return;
+    int lo = 0, hi = WF_NBINS;  // the bin with s_off[bin] <= g < s_off[bin + 1]
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (g >= s_off[mid]) lo = mid; else hi = mid; }
+    const unsigned int i = g - s_off[lo];
+    act = i < s_cnt[lo];
+    if (act) src = B.q_bin[(size_t)lo * B.pool + i];
+  };
+  // Software pipeline over the grid-stride loop: the gathers are latency-bound (two dependent levels, random
+  // 16-byte reads), so the payload of the NEXT work item and the queue index of the one after it are in flight
+  // while the current item is shaded.
+  const unsigned int g0 = blockIdx.x * blockDim.x + threadIdx.x;
+  bool a1, a2;
+  unsigned int s1, s2;
+  float4 n_o, n_d, n_sa, n_sb, n_hh;
+  fetch_src(g0, a1, s1);
+  fetch_src(g0 + stride, a2, s2);
+  auto load_rec = [&](unsigned int src) { const float4* r = B.rec + (size_t)WF_REC * src; n_o = r[0]; n_d = r[1]; n_sa = r[2]; n_sb = r[3]; n_hh = r[4]; };
+  if (a1) load_rec(s1);
+  for (unsigned int gi = g0; gi < n_work; gi += stride) {
+    const bool active = a1;
+    const float4 o = n_o, d = n_d, sa = n_sa;
+    const uint4 sb = make_uint4(__float_as_uint(n_sb.x), __float_as_uint(n_sb.y), __float_as_uint(n_sb.z), 0u);
+    const uint4 hh = make_uint4(__float_as_uint(n_hh.x), __float_as_uint(n_hh.y), __float_as_uint(n_hh.z), __float_as_uint(n_hh.w));
+    a1 = a2; s1 = s2;
+    if (a1) load_rec(s1);
+    fetch_src(gi + 2u * stride, a2, s2);
     bool cont = false, shadow = false;
     Ray ray;
     PathState ps;
     ShadowReq sr;
     sr.valid = false;
     if (active) {
-      const unsigned int src = q[i];
-      const float4 o = B.ray_o[src], d = B.ray_d[src], sa = B.st_a[src];
-      const uint4 sb = B.st_b[src], hh = B.hit[src];
       ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
       ps.throughput = f3(sa); ps.prev_pdf_b = sa.w; ps.radiance = f3(0, 0, 0);
       ps.pixel = sb.x; ps.sample = sb.y; ps.bounce = (int)sb.z;
@@ -188,10 +213,11 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevSce
     }
     const unsigned int pe = warp_append(&B.cnt->n_ext_next, active && cont);
     if (active && cont) {
-      B.ray_o_n[pe] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
-      B.ray_d_n[pe] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed));
-      B.st_a_n[pe] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
-      B.st_b_n[pe] = make_uint4(ps.pixel, ps.sample, (unsigned int)ps.bounce, 0u);
+      float4* out = B.rec_n + (size_t)WF_REC * pe;
+      out[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
+      out[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed));
+      out[2] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
+      out[3] = make_float4(__uint_as_float(ps.pixel), __uint_as_float(ps.sample), __uint_as_float((unsigned int)ps.bounce), 0.f);
     }
     if (INTEG != B200RT_INTEGRATOR_NEE) continue;  // only the NEE integrator produces shadow requests
     const unsigned int pq = warp_append(&B.cnt->n_shadow, shadow);
