@@ -10,13 +10,13 @@ static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool) {
   auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
   size_t o_set[2];
   for (int k = 0; k < 2; ++k) o_set[k] = take(P * 16 * WF_REC);  // the two record sets (96 B per queue position)
-  size_t o_qc = take(P * 4 * WF_NBINS), o_bc = take(4 * WF_NBINS), o_bo = take(4 * (WF_NBINS + 1));
+  size_t o_bc = take(4 * WF_NBINS), o_bo = take(4 * (WF_NBINS + 1));
   size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4), o_cnt = take(sizeof(WfCounters));
   CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
   char* b = (char*)ctx->wf_block;
   ctx->wf_bytes = off;
   ctx->wf.rec = (float4*)(b + o_set[0]); ctx->wf.rec_n = (float4*)(b + o_set[1]);
-  ctx->wf.q_bin = (unsigned int*)(b + o_qc); ctx->wf.bin_count = (unsigned int*)(b + o_bc); ctx->wf.bin_off = (unsigned int*)(b + o_bo);
+  ctx->wf.bin_count = (unsigned int*)(b + o_bc); ctx->wf.bin_off = (unsigned int*)(b + o_bo);
   ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
   ctx->wf.cnt = (WfCounters*)(b + o_cnt);
   ctx->wf.pool = pool;
@@ -90,7 +90,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
       k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M);
       k_wf_control<<<1, 1, 0, q>>>(B, M);
       cudaEventRecord(ev[1], q);
-      k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min);
+      k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min, (P.flags & B200RT_FLAG_LIGHT_SCATTERS) ? 1 : 0);
       cudaEventRecord(ev[2], q);
       k_wf_control_shade<<<1, 1, 0, q>>>(B);
       if (P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
@@ -121,7 +121,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   }
   if (st) {
     st->ms_generate = ms_stage[0]; st->ms_extend = ms_stage[1]; st->ms_shade = ms_stage[2]; st->ms_shadow = ms_stage[3];
-    st->extend_rays = ctx->host_cnt->extend_rays; st->shadow_rays = ctx->host_cnt->shadow_rays;
+    st->extend_rays = ctx->host_cnt->extend_rays - ctx->host_cnt->dead_rays; st->shadow_rays = ctx->host_cnt->shadow_rays;
     st->kernel_launches = launches; st->wavefront_iterations = iters;
   }
   return B200RT_OK;

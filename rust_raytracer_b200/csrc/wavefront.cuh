@@ -4,20 +4,22 @@
 // The queues hold the ray PAYLOAD, not indices, as one 96-byte record (three 32-byte DRAM sectors) per position:
 //   sector 0: (o.xyz, time) (d.xyz, medium seed bits; t_max of an extend ray is always +inf)   read by extend + shade
 //   sector 1: (throughput.rgb, prev_pdf_b) (pixel, sample, bounce, 0)                           read by shade
-//   sector 2: (t as 2 x u32 [f64], device prim, aux) (spare)                                    written by extend
-// Shade gathers whole records (every sector it touches is fully used: the SoA version of this layout read 154 B
-// per ray from DRAM for 84 B of payload), compacts the surviving paths straight into the NEXT set (one
-// warp-aggregated atomic per warp, then 64 contiguous bytes per lane); generate appends freshly started paths
-// behind them, so extend and generate touch memory strictly in order.  The two sets are swapped by the host
+//   sector 2: (t as 2 x u32 [f64], device prim, aux) (bin, rank in bin, 0, 0)                   written by extend
+// Extend, shade and generate all read and write their queue strictly in order; the only scattered traffic is the
+// 64-byte store of a surviving path into its bin of the NEXT set (stores do not stall the warp the way the
+// gathers of an index-sorted shade did: 154 B read per ray for 84 B of payload, latency-bound at 28 % issue).  The two sets are swapped by the host
 // between iterations.  Shadow requests are stored by queue position: sh_o, sh_d, sh_c, sh_seed.
 #pragma once
 #include "kernels.cuh"
 
-// Shade work is binned by WHERE the ray ended: bin 0 = miss, bins 1.. = the hit primitive's index in BVH leaf order
-// (spatially coherent, and one primitive has one material) scaled to WF_NBINS - 1 bins.  Shade walks the bins in
-// order, so (a) its warps are material-coherent and (b) the survivors land in the next queue grouped by origin
-// region and by expected traversal cost (fog-born rays together, ground-box rays together, ...), which is what
-// keeps the extend warps converged.  Bin storage is WF_NBINS x pool indices: HBM is plentiful (180 GB).
+// The NEXT queue is ordered by WHERE each ray starts: bin = the hit primitive's index in BVH leaf order (spatially
+// coherent) scaled to WF_NBINS - 1 bins.  Extend knows the bin of every ray that will go on (hit, and the material
+// scatters) and takes its rank inside the bin with one warp-aggregated atomic; a one-thread kernel turns the bin
+// sizes into offsets; shade then walks the current queue IN ORDER (pure streaming reads of whole records) and
+// writes each surviving path at offset[bin] + rank of the next set.  Extend warps therefore receive rays that left
+// neighbouring primitives, with similar traversal cost (fog-born rays together, ground-box rays together, ...).
+// A path that was predicted to go on but ended in shade (metal absorption, zero pdf, depth budget) leaves a dead
+// record (zero direction) that extend skips.
 #define WF_REC 6  // float4 per queue record (96 bytes)
 #ifndef WF_NBINS
 #define WF_NBINS 256
@@ -31,16 +33,15 @@ struct WfCounters {
   unsigned int n_shadow;            // shadow requests this iteration
   unsigned int ext_cursor;          // work-fetch cursor of the persistent extend kernel
   unsigned int shadow_cursor;
-  unsigned int n_work;              // shade index space: sum of the bin sizes, each padded to a multiple of 32
+  unsigned int dead_rays;           // dead records met by extend (not rays: subtracted from the statistics)
   unsigned int pad[2];
 };
 
 struct WfBuffers {
   float4* rec;    // current set: WF_REC float4 per queue position
   float4* rec_n;  // next set
-  unsigned int* q_bin;    // WF_NBINS x pool queue positions
-  unsigned int* bin_count;  // WF_NBINS
-  unsigned int* bin_off;    // WF_NBINS + 1: start of every bin in the padded shade index space
+  unsigned int* bin_count;  // WF_NBINS: continuing rays per bin (filled by extend)
+  unsigned int* bin_off;    // WF_NBINS + 1: start of every bin in the next set
   unsigned int bin_mul;     // bin = 1 + umulhi(prim, bin_mul)
   float4* sh_o; float4* sh_d; float4* sh_c; unsigned int* sh_seed;
   WfCounters* cnt;
@@ -98,12 +99,12 @@ __global__ void k_wf_control(WfBuffers B, PathMap M) {
   c->extend_rays += c->n_ext;
   for (int i = 0; i < WF_NBINS; ++i) B.bin_count[i] = 0;
 }
-// after extend: the padded prefix sum of the bin sizes (shade's index space)
+// after extend: bin sizes -> offsets in the next set; their total is the number of records shade will write
 __global__ void k_wf_control_shade(WfBuffers B) {
   unsigned int off = 0;
-  for (int i = 0; i < WF_NBINS; ++i) { B.bin_off[i] = off; off += (B.bin_count[i] + 31u) & ~31u; }
+  for (int i = 0; i < WF_NBINS; ++i) { B.bin_off[i] = off; off += B.bin_count[i]; }
   B.bin_off[WF_NBINS] = off;
-  B.cnt->n_work = off;
+  B.cnt->n_ext_next = off;
 }
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
 
@@ -115,7 +116,9 @@ __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->
 #ifndef B200RT_EXTEND_MINBLOCKS
 #define B200RT_EXTEND_MINBLOCKS 8
 #endif
-__global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevScene S, WfBuffers B, float t_min) {
+#define WF_PRIM_DEAD (-2)
+#define WF_NO_RANK 0xffffffffu
+__global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevScene S, WfBuffers B, float t_min, int light_scatters) {
   const unsigned int n = B.cnt->n_ext;
   const unsigned lane = threadIdx.x & 31;
   for (;;) {
@@ -125,73 +128,67 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     if (base >= n) break;
     const unsigned int i = base + lane;
     const bool active = i < n;
-    unsigned int bin = 0;
+    float4* rec = B.rec + (size_t)WF_REC * i;
+    unsigned int bin = (unsigned)WF_NBINS;  // WF_NBINS = "does not go on"
+    HitRaw h;
+    h.t = 0.; h.prim = WF_PRIM_DEAD; h.aux = 0;
+    bool dead = false;
     if (active) {
-      float4* rec = B.rec + (size_t)WF_REC * i;
       const float4 o = rec[0], d = rec[1];
-      Ray r;
-      r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = __int_as_float(0x7f800000); r.mseed = __float_as_uint(d.w);
-      HitRaw h;
-      trace<false>(S, r, t_min, h);
+      dead = d.x == 0.f && d.y == 0.f && d.z == 0.f;
+      if (!dead) {
+        Ray r;
+        r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = __int_as_float(0x7f800000); r.mseed = __float_as_uint(d.w);
+        trace<false>(S, r, t_min, h);
+        if (h.prim >= 0) {  // will the path go on?  Every material scatters except DiffuseLight (material.rs:201-212 behind a flag)
+          const int4 meta = __ldg(&S.prim_meta[h.prim]);
+          const int mtype = __float_as_int(__ldg(&S.materials[meta.x >> 8]).x);
+          if (mtype != B200RT_MAT_DIFFUSE_LIGHT || light_scatters) bin = 1u + __umulhi((unsigned int)h.prim, B.bin_mul);
+        }
+      }
+    }
+    // rank inside the bin: the leader lane of every bin present in the warp issues its atomic in the same
+    // instruction, so the warp pays one atomic round trip whatever the number of bins
+    const unsigned peers = __match_any_sync(0xffffffffu, bin);
+    const int leader = __ffs((int)peers) - 1;
+    const bool goes_on = bin != (unsigned)WF_NBINS;
+    unsigned int rank = 0;
+    if (goes_on && (int)lane == leader) rank = atomicAdd(&B.bin_count[bin], (unsigned)__popc(peers));
+    rank = __shfl_sync(0xffffffffu, rank, leader) + __popc(peers & ((1u << lane) - 1u));
+    const unsigned n_dead = __popc(__ballot_sync(0xffffffffu, dead));
+    if (n_dead && lane == 0) atomicAdd(&B.cnt->dead_rays, n_dead);
+    if (active) {
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
       rec[4] = make_float4(__uint_as_float((unsigned int)tb), __uint_as_float((unsigned int)(tb >> 32)), __int_as_float(h.prim), __int_as_float(h.aux));
-      rec[5] = make_float4(0.f, 0.f, 0.f, 0.f);  // the whole 32-byte sector is written: no read-modify-write
-      bin = h.prim < 0 ? 0u : 1u + __umulhi((unsigned int)h.prim, B.bin_mul);
+      rec[5] = make_float4(__uint_as_float(bin), __uint_as_float(goes_on ? rank : WF_NO_RANK), 0.f, 0.f);  // full 32-byte sector: no read-modify-write
     }
-    // the leader lane of every bin present in the warp issues its atomic in the same instruction: one atomic
-    // round trip per warp, whatever the number of bins
-    const unsigned peers = __match_any_sync(0xffffffffu, active ? bin : (unsigned)WF_NBINS);
-    const int leader = __ffs((int)peers) - 1;
-    unsigned int cbase = 0;
-    if (active && (int)lane == leader) cbase = atomicAdd(&B.bin_count[bin], (unsigned)__popc(peers));
-    cbase = __shfl_sync(0xffffffffu, cbase, leader);
-    if (active) B.q_bin[(size_t)bin * B.pool + cbase + __popc(peers & ((1u << lane) - 1u))] = i;
   }
 }
 
-// shade: ONE launch over all bins.  Each bin is padded to a multiple of 32 in the index space, so every warp
-// works on a single bin (one or a few neighbouring primitives: coherent material branches).  Survivors are
-// written to the next set at their compacted position.
+// shade: walks the current queue in order (streaming reads of whole records, the next record prefetched while the
+// current one is shaded) and stores every surviving path at its place in the next set.
 #ifndef B200RT_SHADE_MINBLOCKS
 #define B200RT_SHADE_MINBLOCKS 4
 #endif
 template <int INTEG>
 __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   __shared__ unsigned int s_off[WF_NBINS + 1];
-  __shared__ unsigned int s_cnt[WF_NBINS];
-  for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) { s_off[k] = B.bin_off[k]; if (k < WF_NBINS) s_cnt[k] = B.bin_count[k]; }
+  for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) s_off[k] = B.bin_off[k];
   __syncthreads();
-  const unsigned int n_work = s_off[WF_NBINS];
+  const unsigned int n_ext = B.cnt->n_ext;
+  const unsigned int n_work = (n_ext + 31u) & ~31u;  // whole warps stay in the loop (warp-aggregated appends below)
   const unsigned int stride = gridDim.x * blockDim.x;
-  // queue position of work item g (bins are 32-aligned in the index space, so the lookup is warp-uniform)
-  auto fetch_src = [&](unsigned int g, bool& act, unsigned int& src) {
-    act = false; src = 0u;
-    if (g >= n_work) return;
-    int lo = 0, hi = WF_NBINS;  // the bin with s_off[bin] <= g < s_off[bin + 1]
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (g >= s_off[mid]) lo = mid; else hi = mid; }
-    const unsigned int i = g - s_off[lo];
-    act = i < s_cnt[lo];
-    if (act) src = B.q_bin[(size_t)lo * B.pool + i];
-  };
-  // Software pipeline over the grid-stride loop: the gathers are latency-bound (two dependent levels, random
-  // 16-byte reads), so the payload of the NEXT work item and the queue index of the one after it are in flight
-  // while the current item is shaded.
   const unsigned int g0 = blockIdx.x * blockDim.x + threadIdx.x;
-  bool a1, a2;
-  unsigned int s1, s2;
-  float4 n_o, n_d, n_sa, n_sb, n_hh;
-  fetch_src(g0, a1, s1);
-  fetch_src(g0 + stride, a2, s2);
-  auto load_rec = [&](unsigned int src) { const float4* r = B.rec + (size_t)WF_REC * src; n_o = r[0]; n_d = r[1]; n_sa = r[2]; n_sb = r[3]; n_hh = r[4]; };
-  if (a1) load_rec(s1);
+  float4 n_o, n_d, n_sa, n_sb, n_hh, n_br;
+  auto load_rec = [&](unsigned int src) { const float4* r = B.rec + (size_t)WF_REC * src; n_o = r[0]; n_d = r[1]; n_sa = r[2]; n_sb = r[3]; n_hh = r[4]; n_br = r[5]; };
+  if (g0 < n_ext) load_rec(g0);
   for (unsigned int gi = g0; gi < n_work; gi += stride) {
-    const bool active = a1;
     const float4 o = n_o, d = n_d, sa = n_sa;
     const uint4 sb = make_uint4(__float_as_uint(n_sb.x), __float_as_uint(n_sb.y), __float_as_uint(n_sb.z), 0u);
     const uint4 hh = make_uint4(__float_as_uint(n_hh.x), __float_as_uint(n_hh.y), __float_as_uint(n_hh.z), __float_as_uint(n_hh.w));
-    a1 = a2; s1 = s2;
-    if (a1) load_rec(s1);
-    fetch_src(gi + 2u * stride, a2, s2);
+    const unsigned int bin = __float_as_uint(n_br.x), rank = __float_as_uint(n_br.y);
+    if (gi + stride < n_ext) load_rec(gi + stride);
+    const bool active = gi < n_ext && (int)hh.z != WF_PRIM_DEAD;
     bool cont = false, shadow = false;
     Ray ray;
     PathState ps;
@@ -211,13 +208,17 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevSce
       }
       accum_add(accum, ps.pixel, ps.radiance);
     }
-    const unsigned int pe = warp_append(&B.cnt->n_ext_next, active && cont);
-    if (active && cont) {
-      float4* out = B.rec_n + (size_t)WF_REC * pe;
-      out[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
-      out[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed));
-      out[2] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
-      out[3] = make_float4(__uint_as_float(ps.pixel), __uint_as_float(ps.sample), __uint_as_float((unsigned int)ps.bounce), 0.f);
+    if (active && rank != WF_NO_RANK) {  // the place extend reserved in the next set: the new ray, or a dead record
+      float4* out = B.rec_n + (size_t)WF_REC * (s_off[bin] + rank);
+      if (cont) {
+        out[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
+        out[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed));
+        out[2] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
+        out[3] = make_float4(__uint_as_float(ps.pixel), __uint_as_float(ps.sample), __uint_as_float((unsigned int)ps.bounce), 0.f);
+      } else {
+        out[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+        out[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
     }
     if (INTEG != B200RT_INTEGRATOR_NEE) continue;  // only the NEE integrator produces shadow requests
     const unsigned int pq = warp_append(&B.cnt->n_shadow, shadow);
