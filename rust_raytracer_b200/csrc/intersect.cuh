@@ -252,8 +252,7 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32
   for (int i = 0; i < 4; ++i) {
     const float n = fmaxf(fmaxf(fmaf(ax[i], rt.inv.x, -rt.oin.x), fmaf(ay[i], rt.inv.y, -rt.oin.y)), fmaxf(fmaf(az[i], rt.inv.z, -rt.oin.z), t_min));
     const float f = fminf(fminf(fmaf(bx[i], rt.inv.x, -rt.oif.x), fmaf(by[i], rt.inv.y, -rt.oif.y)), fminf(fmaf(bz[i], rt.inv.z, -rt.oif.z), t_best32));
-    const bool hit = (n <= f * 1.000001f) && (rr[i] != (uint32_t)B200RT_CHILD_EMPTY);
-    tn[i] = hit ? n : 3.0e38f;
+    tn[i] = (n <= f * 1.000001f) ? n : 3.0e38f;  // empty slots hold an inverted infinite box: never hit
   }
 #else
   const float4* nd = S.nodes + 8 * (size_t)cur;

@@ -130,7 +130,7 @@ int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out) {
   }
   int32_t refs[4] = {B200RT_CHILD_EMPTY, B200RT_CHILD_EMPTY, B200RT_CHILD_EMPTY, B200RT_CHILD_EMPTY};
   float lo[3][4], hi[3][4];
-  for (int a = 0; a < 3; ++a) for (int i = 0; i < 4; ++i) { lo[a][i] = FLT_MAX; hi[a][i] = -FLT_MAX; }
+  for (int a = 0; a < 3; ++a) for (int i = 0; i < 4; ++i) { lo[a][i] = INFINITY; hi[a][i] = -INFINITY; }  // empty slot: near = +inf, far = -inf for any finite ray, never hit
   for (int i = 0; i < nk; ++i) {
     const BinNode& c = bb.nodes[kids[i]];
     for (int a = 0; a < 3; ++a) { lo[a][i] = c.box.lo[a]; hi[a][i] = c.box.hi[a]; }
