@@ -88,11 +88,11 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
       // the set shade just compacted the survivors into becomes the current one; generate appends behind them
       std::swap(B.rec, B.rec_n);
       k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M);
-      k_wf_control<<<1, 1, 0, q>>>(B, M);
+      k_wf_control<<<1, WF_NBINS, 0, q>>>(B, M);
       cudaEventRecord(ev[1], q);
       k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min, (P.flags & B200RT_FLAG_LIGHT_SCATTERS) ? 1 : 0);
       cudaEventRecord(ev[2], q);
-      k_wf_control_shade<<<1, 1, 0, q>>>(B);
+      k_wf_control_shade<<<1, WF_NBINS, 0, q>>>(B);
       if (P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
       else if (P.integrator == B200RT_INTEGRATOR_MIXTURE) k_wf_shade<B200RT_INTEGRATOR_MIXTURE><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
       else k_wf_shade<B200RT_INTEGRATOR_NEE><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);

@@ -198,9 +198,42 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
 
 #define B200RT_TRAV_DONE 0xFFFFFFFFu  // leaf bit set with an impossible count: never a real child reference
 
-DEV uint32_t pop_next(const uint2* stack, int& sp, float t_best32) {
+// Traversal stack.  north_star asks for a shared-memory short stack; it is implemented (the first B200RT_SSTACK
+// entries of every thread in shared memory, entry-major so a warp's 8-byte accesses are conflict-free, deeper
+// entries overflowing to a per-thread local array) and was measured on book-2: 8 / 16 / 24 shared entries cost
+// 66.7 / 70.1 / 82.4 ms of extend per step against 56.2 ms for the plain local-memory stack — the carve-out takes
+// L1 capacity away from the node / primitive / spill traffic, and the two-way push/pop adds instructions.  The
+// default is therefore 0 (local memory, L1-resident); profiles/r1_experiments.md.
+#ifndef B200RT_SSTACK
+#define B200RT_SSTACK 0
+#endif
+#define B200RT_BLOCK 128  // every kernel that traverses runs 128-thread blocks
+struct TStack {
+#if B200RT_SSTACK > 0
+  uint2* sm;  // &shared[threadIdx.x]; entry k at sm[k * B200RT_BLOCK]
+#endif
+  uint2 loc[B200RT_STACK - B200RT_SSTACK];
+  DEV void push(int& sp, uint2 v) {
+#if B200RT_SSTACK > 0
+    if (sp < B200RT_SSTACK) sm[sp * B200RT_BLOCK] = v; else loc[sp - B200RT_SSTACK] = v;
+#else
+    loc[sp] = v;
+#endif
+    ++sp;
+  }
+  DEV uint2 pop(int& sp) {
+    --sp;
+#if B200RT_SSTACK > 0
+    return sp < B200RT_SSTACK ? sm[sp * B200RT_BLOCK] : loc[sp - B200RT_SSTACK];
+#else
+    return loc[sp];
+#endif
+  }
+};
+
+DEV uint32_t pop_next(TStack& stack, int& sp, float t_best32) {
   while (sp > 0) {
-    const uint2 e = stack[--sp];
+    const uint2 e = stack.pop(sp);
     if (__uint_as_float(e.y) <= t_best32) return e.x;
     DBG_INC(4);
   }
@@ -236,7 +269,7 @@ DEV RayT make_rayt(const RayF& rf) {
 
 // BVH4 node step: slab-tests the four children of inner node `cur` against [t_min, t_best32], pushes the far
 // hits and returns the nearest child reference (or the next stack entry when no child is hit).
-DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32_t cur, float t_min, float t_best32, uint2* stack, int& sp) {
+DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32_t cur, float t_min, float t_best32, TStack& stack, int& sp) {
   DBG_INC(1);
   float tn[4];
 #if B200RT_NODE_FAST
@@ -281,9 +314,9 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32
   CSWAP(1, 3) CSWAP(1, 2)
 #endif
 #undef CSWAP
-  if (tn[3] < 3.0e38f) stack[sp++] = make_uint2(rr[3], __float_as_uint(tn[3]));
-  if (tn[2] < 3.0e38f) stack[sp++] = make_uint2(rr[2], __float_as_uint(tn[2]));
-  if (tn[1] < 3.0e38f) stack[sp++] = make_uint2(rr[1], __float_as_uint(tn[1]));
+  if (tn[3] < 3.0e38f) stack.push(sp, make_uint2(rr[3], __float_as_uint(tn[3])));
+  if (tn[2] < 3.0e38f) stack.push(sp, make_uint2(rr[2], __float_as_uint(tn[2])));
+  if (tn[1] < 3.0e38f) stack.push(sp, make_uint2(rr[1], __float_as_uint(tn[1])));
   if (tn[0] < 3.0e38f) return rr[0];
   return pop_next(stack, sp, t_best32);
 }
@@ -306,7 +339,11 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
   const RayF rf = make_rayf(ray);
   const RayT rt = make_rayt(rf);
   DBG_INC(0);
-  uint2 stack[B200RT_STACK];
+  TStack stack;
+#if B200RT_SSTACK > 0
+  __shared__ uint2 s_stack[B200RT_SSTACK * B200RT_BLOCK];
+  stack.sm = s_stack + threadIdx.x;
+#endif
   int sp = 0;
   int tail = S.n_bvh_prims;                          // next primitive outside the BVH
   // The tail is expensive (book-2's fog: an f64 medium test for half of the rays): run it once per warp, with

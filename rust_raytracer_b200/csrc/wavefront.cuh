@@ -87,7 +87,9 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P,
 }
 
 // One thread turns the counters over between generate and extend (no host round trip inside an iteration).
-__global__ void k_wf_control(WfBuffers B, PathMap M) {
+__global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, WF_NBINS>>>
+  B.bin_count[threadIdx.x] = 0;
+  if (threadIdx.x != 0) return;
   WfCounters* c = B.cnt;
   const unsigned int n_new = wf_new_paths(c, M, B.pool);
   c->next_path += n_new;
@@ -97,14 +99,24 @@ __global__ void k_wf_control(WfBuffers B, PathMap M) {
   c->ext_cursor = 0;
   c->shadow_cursor = 0;
   c->extend_rays += c->n_ext;
-  for (int i = 0; i < WF_NBINS; ++i) B.bin_count[i] = 0;
 }
-// after extend: bin sizes -> offsets in the next set; their total is the number of records shade will write
+// after extend: bin sizes -> offsets in the next set; their total is the number of records shade will write.
+// One block of WF_NBINS threads (Hillis-Steele scan in shared memory).
 __global__ void k_wf_control_shade(WfBuffers B) {
-  unsigned int off = 0;
-  for (int i = 0; i < WF_NBINS; ++i) { B.bin_off[i] = off; off += B.bin_count[i]; }
-  B.bin_off[WF_NBINS] = off;
-  B.cnt->n_ext_next = off;
+  __shared__ unsigned int sc[2][WF_NBINS];
+  const int t = threadIdx.x;
+  const unsigned int mine = B.bin_count[t];
+  sc[0][t] = mine;
+  __syncthreads();
+  int cur = 0;
+  for (int d = 1; d < WF_NBINS; d <<= 1) {
+    sc[cur ^ 1][t] = sc[cur][t] + (t >= d ? sc[cur][t - d] : 0u);
+    cur ^= 1;
+    __syncthreads();
+  }
+  const unsigned int incl = sc[cur][t];
+  B.bin_off[t] = incl - mine;
+  if (t == WF_NBINS - 1) { B.bin_off[WF_NBINS] = incl; B.cnt->n_ext_next = incl; }
 }
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
 
