@@ -29,6 +29,12 @@ UNIT = "Mpaths/s"
 # extend kernel, per ray: ray_o 16 + ray_d 16 read (the medium seed rides in ray_d.w); hit 16 + bin queue index 4 written
 EXTEND_BYTES_PER_RAY = 52
 SEGMENT_BYTES_PIPELINE = 128  # ray 32 + hit 16 + state 16, written once and read once
+# ncu --set full, k_wf_extend, full-pool launch (16,777,216 rays): dram__bytes_read.sum 1.661 GB + dram__bytes_write.sum
+# 0.820 GB (profiles/r1_final_extend_shade_full.txt) -> DRAM bytes per ray; issue/lane figures from the same capture
+EXTEND_DRAM_BYTES_PER_RAY_NCU = (1.660982e9 + 820.366592e6) / 16777216
+EXTEND_NCU = {"issue_active_pct": 73.0, "alu_pipe_pct": 51.9, "fma_pipe_pct": 22.8, "fp64_pipe_pct": 7.1, "lanes_per_instruction": 14.2,
+              "l1_hit_pct": 78.5, "l2_hit_pct": 70.0, "dram_pct_of_peak": 12.9, "shade_issue_active_pct": 48.9, "shade_dram_pct_of_peak": 37.2,
+              "source": "profiles/r1_final_extend_shade_full.txt"}
 
 
 def earth_image():
@@ -271,10 +277,13 @@ def main():
         roofline = {
             "bound": "hbm", "kernel": "k_wf_extend" if args.pipeline == "wavefront" else "k_megakernel",
             "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (achieved / peaks["hbm_gbs"]) if achieved else None,
-            "peak_source": "MEASURED_PEAKS.json (%s)" % peak_kind, "traffic": None,
+            "peak_source": "MEASURED_PEAKS.json (%s)" % peak_kind,
+            "traffic": EXTEND_DRAM_BYTES_PER_RAY_NCU * rays_per_launch if args.pipeline == "wavefront" else None,
+            "traffic_note": "ncu dram bytes per ray of a full-pool launch (%.0f B: 64-byte fills at the 96-byte record stride + local-memory stack/spill traffic) x rays of the average launch" % EXTEND_DRAM_BYTES_PER_RAY_NCU,
             "bytes_per_ray": EXTEND_BYTES_PER_RAY, "rays_per_launch": rays_per_launch, "launches": n_ext_launches,
             "avg_launch_ms": ext_ms / n_ext_launches, "kernel_share_of_step": ext_ms / max(stats["ms_total"], 1e-9),
-            "note": "BVH traversal is FP32-issue/latency bound, not HBM bound (scene is L2-resident): see fp32 and DESIGN.md",
+            "note": "BVH traversal is instruction-issue bound under divergence, not HBM bound (scene is L2-resident): see issue, fp32 and DESIGN.md",
+            "issue": EXTEND_NCU,
             "pipeline_bytes_per_segment": SEGMENT_BYTES_PIPELINE,
             "pipeline_hbm_frac": SEGMENT_BYTES_PIPELINE * (ext + shd) / total_s / 1e9 / peaks["hbm_gbs"],
         }

@@ -66,6 +66,13 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   }
   CU_CHECK(ctx, cudaMemsetAsync(B.cnt, 0, sizeof(WfCounters), q));
   const int sms = ctx->prop.multiProcessorCount;
+  {  // traversal lives in L1 (nodes, primitive records, the local-memory stack): ask for the smallest shared-memory carve-out
+    const int carve = env_int("B200RT_CARVEOUT", 0, -1, 100);
+    if (carve >= 0) {
+      cudaFuncSetAttribute(k_wf_extend, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+      cudaFuncSetAttribute(k_wf_shadow, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+    }
+  }
   int occ_ext = 1, occ_shadow = 1, occ_shade = 1;
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend, 128, 0));
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow, 128, 0));
