@@ -12,7 +12,13 @@ struct RayF {
   float time;
 };
 
-DEV float safe_rcp(float d) { return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
+// Approximate unit operations (MUFU.RCP / MUFU.RSQ, <= 2 ulp) for the FILTERS only: every comparison below carries
+// an explicit error margin several ulp wide, and a wrong "maybe" only costs one exact test.  The IEEE-rounded
+// forms cost ~8 instructions each and sat on every ray's critical path (three reciprocals in make_rayf).
+DEV float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+DEV float rsqrt_fast(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+DEV float sqrt_fast(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+DEV float safe_rcp(float d) { return rcp_fast(fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
 
 // Filter verdicts
 #define FILTER_MAYBE 0        // the exact test decides
@@ -28,7 +34,7 @@ DEV float safe_rcp(float d) { return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1
 DEV int medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, float e_out, float neg_inv_density, float xi, float t_min, float t_best) {
   const float lo = fmaxf(fmaxf(t_in - e_in, t_min), 0.f);
   const float hi = fminf(t_out + e_out, t_best);
-  const float len = sqrtf(r.a);
+  const float len = sqrt_fast(r.a);  // <= 2 ulp, inside the 2e-6 margins below
   float upper = fmaxf(hi - lo, 0.f) + 2e-7f * (fabsf(hi) + fabsf(lo));
   upper = upper * len * (1.0f + 2e-6f);
   const float hd = neg_inv_density * logf(xi);  // >= 0
@@ -51,13 +57,16 @@ DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float 
   float hb = dot(oc, r.d), oc2 = dot(oc, oc), r2 = radius * radius;
   float cc = oc2 - r2;
   float disc = hb * hb - r.a * cc;
-  float E = 2e-6f * r.a * (oc2 + r2) + r.a * eps * (8.0f * sqrtf(oc2) + 4.0f * radius);
+  float E = 2e-6f * r.a * (oc2 + r2);
+  if (eps > 0.f) E += r.a * eps * (8.2f * sqrt_fast(oc2) + 4.0f * radius);
   if (disc < -E) return true;
   if (disc > 4.0f * E) {
-    float s = sqrtf(disc), inva = 1.0f / r.a;
-    float dn = (6e-7f * sqrtf(oc2 * r.a) + E / s + 2.0f * eps * sqrtf(r.a)) * inva;
+    const float rs = rsqrt_fast(disc), s = disc * rs, inva = rcp_fast(r.a);  // s, inva: <= 3 ulp
+    float dn = 6.2e-7f * sqrt_fast(oc2 * r.a) + 1.01f * E * rs;
+    if (eps > 0.f) dn += 2.05f * eps * sqrt_fast(r.a);
+    dn *= inva;
     float t0 = (-hb - s) * inva, t1 = (-hb + s) * inva;
-    float e0 = dn + 4e-7f * fabsf(t0), e1 = dn + 4e-7f * fabsf(t1);
+    float e0 = dn + 1e-6f * fabsf(t0), e1 = dn + 1e-6f * fabsf(t1);
     if (t0 - e0 > t_best) return true;                       // nearest root already beyond the best hit
     if (t1 + e1 < t_min) return true;                        // sphere entirely behind t_min
     if (medium) return medium_far_reject(r, t0, e0, t1, e1, neg_inv_density, xi, t_min, t_best);
@@ -69,8 +78,9 @@ DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float 
 // rectangle.rs:15-26 in f32
 DEV bool rect_reject(const RayF& r, int axis, float a0, float b0, float a1, float b1, float k, float t_min, float t_best, float eps) {
   const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
-  float t = (k - comp(r.o, axis)) / comp(r.d, axis);
-  float e = 3e-7f * fabsf(t) + 2.0f * eps / fabsf(comp(r.d, axis));
+  const float inv = comp(r.inv, axis);
+  float t = (k - comp(r.o, axis)) * inv;
+  float e = 6e-7f * fabsf(t) + 2.0f * eps * fabsf(inv);
   if (t + e < t_min || t - e > t_best) return true;
   float oa = comp(r.o, ia), da = comp(r.d, ia), ob = comp(r.o, ib), db = comp(r.d, ib);
   float x = fmaf(t, da, oa), y = fmaf(t, db, ob);
@@ -128,22 +138,22 @@ DEV bool tri_reject(const RayF& r, float3 v0, float3 v1, float3 v2, float t_min,
   float e0_2 = dot(e0, e0), e1_2 = dot(e1, e1);
   float scale2 = r.a * e0_2 * e1_2;
   if (!(dd * dd > 1e-8f * scale2)) return false;  // grazing or degenerate: let the exact test decide
-  float inv = 1.0f / dd;
-  float cond = sqrtf(scale2) * fabsf(inv);
-  float rel = eps * rsqrtf(fminf(e0_2, e1_2));  // baking error relative to the shorter edge
+  float inv = rcp_fast(dd);
+  float cond = sqrt_fast(scale2) * fabsf(inv);
+  float rel = eps * rsqrt_fast(fminf(e0_2, e1_2));  // baking error relative to the shorter edge
   if (cond * rel > 0.05f) return false;
-  float q = cond * (1e-6f + 8.0f * rel);
+  float q = cond * (1.5e-6f + 8.0f * rel);
   float3 dv = r.o - v0;
   float dv2 = dot(dv, dv);
   float b1 = dot(dv, s0) * inv;
-  float db1 = q * (sqrtf(dv2 / e0_2) + fabsf(b1));
+  float db1 = q * (sqrt_fast(dv2 * rcp_fast(e0_2)) + fabsf(b1));
   if (b1 < -db1 || b1 > 1.0f + db1) return true;
   float3 s1 = cross(dv, e0);
   float b2 = dot(r.d, s1) * inv;
-  float db2 = q * (sqrtf(dv2 / e1_2) + fabsf(b2));
+  float db2 = q * (sqrt_fast(dv2 * rcp_fast(e1_2)) + fabsf(b2));
   if (b2 < -db2 || b1 + b2 > 1.0f + db1 + db2) return true;
   float t = dot(e1, s1) * inv;
-  float dt = q * (sqrtf(dv2 / r.a) + fabsf(t));
+  float dt = q * (sqrt_fast(dv2 * rcp_fast(r.a)) + fabsf(t));
   if (t + dt < t_min || t - dt > t_best) return true;
   return false;
 }
