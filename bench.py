@@ -245,6 +245,7 @@ def main():
     # ---- end to end through the public API with HOST buffers: scene tables H2D + render + reduce + image D2H
     host_img = torch.empty((HEIGHT, WIDTH, 4), dtype=torch.float32).pin_memory()
     e2e_steps = max(3, min(args.steps, 5))
+    e2e_marks = []
     sync_all()
     t0 = time.perf_counter()
     for i in range(-1, e2e_steps):
@@ -260,6 +261,7 @@ def main():
             host_img.copy_(accum, non_blocking=True)
         torch.cuda.synchronize()
         sc2.close()
+        e2e_marks.append(time.perf_counter())
     sync_all()
     e2e_s = time.perf_counter() - t0
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -310,6 +312,7 @@ def main():
             "fp32": {"peak_tflops_measured": fp32_tflops, "effective_sm_mhz": eff_mhz, "how": "k_fma_peak: 8 independent FMA chains/thread, 8 blocks x 256 threads per SM"},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": info["h2d_bytes"], "d2h_bytes_per_step": WIDTH * HEIGHT * 16, "steps": e2e_steps,
+                    "ms_per_step_list": [round((b - a) * 1e3, 2) for a, b in zip(e2e_marks[:-1], e2e_marks[1:])],
                     "what": "World::new (validate + bake + BVH build + upload) + capture_image + reduce + image D2H to pinned host"},
             "gpu_launches": int(stats["kernel_launches"]),
             "clocks": sampler.summary(),

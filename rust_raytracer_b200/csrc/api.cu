@@ -21,6 +21,13 @@ struct b200rt_ctx {
   MegaCounters* mega_cnt = nullptr;
   WfCounters* host_cnt = nullptr;  // pinned
   cudaEvent_t ev[2] = {nullptr, nullptr};
+  // World::new staging: one grow-only pinned buffer and one recycled device block per context, so that rebuilding
+  // a scene (the e2e path of bench.py) pays no cudaMallocHost / cudaMalloc / cudaFree (each of which can stall
+  // for hundreds of ms on a busy driver)
+  void* stage_host = nullptr;
+  size_t stage_bytes = 0;
+  void* spare_block = nullptr;
+  size_t spare_bytes = 0;
   cudaEvent_t sev[64] = {};  // stage events: up to 8 iterations in flight x (generate, extend, shade, shadow) x (begin, end)
 };
 
@@ -28,6 +35,7 @@ struct b200rt_scene {
   b200rt_ctx* ctx = nullptr;
   DevScene dev{};
   void* block = nullptr;  // one allocation holding every table
+  size_t block_bytes = 0;
   uint64_t h2d_bytes = 0;
   uint32_t n_nodes = 0, n_prims = 0;
 };
@@ -101,6 +109,8 @@ int b200rt_ctx_destroy(b200rt_ctx* c) {
   if (!c) return B200RT_OK;
   cudaSetDevice(c->device);
   if (c->wf_block) cudaFree(c->wf_block);
+  if (c->spare_block) cudaFree(c->spare_block);
+  if (c->stage_host) cudaFreeHost(c->stage_host);
   if (c->mega_cnt) cudaFree(c->mega_cnt);
   if (c->host_cnt) cudaFreeHost(c->host_cnt);
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
@@ -145,16 +155,27 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
   size_t total = 0;
   for (auto& p : parts) { p.off = total; total += align_up(std::max<size_t>(p.bytes, 16), 256); }
   // stage everything in one pinned buffer -> one H2D copy
-  void* host = nullptr;
-  CU_CHECK(ctx, cudaMallocHost(&host, total));
+  if (ctx->stage_bytes < total) {
+    if (ctx->stage_host) cudaFreeHost(ctx->stage_host);
+    ctx->stage_host = nullptr; ctx->stage_bytes = 0;
+    CU_CHECK(ctx, cudaMallocHost(&ctx->stage_host, total));
+    ctx->stage_bytes = total;
+  }
+  void* host = ctx->stage_host;
   std::memset(host, 0, total);
   for (auto& p : parts) if (p.bytes) std::memcpy((char*)host + p.off, p.src, p.bytes);
   b200rt_scene* sc = new (std::nothrow) b200rt_scene();
-  if (!sc) { cudaFreeHost(host); return B200RT_ERR_NOMEM; }
-  cudaError_t e = cudaMalloc(&sc->block, total);
+  if (!sc) return B200RT_ERR_NOMEM;
+  cudaError_t e = cudaSuccess;
+  if (ctx->spare_block && ctx->spare_bytes >= total && ctx->spare_bytes <= 2 * total + (1u << 20)) {
+    sc->block = ctx->spare_block; sc->block_bytes = ctx->spare_bytes;
+    ctx->spare_block = nullptr; ctx->spare_bytes = 0;
+  } else {
+    e = cudaMalloc(&sc->block, total);
+    sc->block_bytes = total;
+  }
   if (e == cudaSuccess) e = cudaMemcpyAsync(sc->block, host, total, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-  cudaFreeHost(host);
   if (e != cudaSuccess) {
     ctx->err = std::string("scene upload: ") + cudaGetErrorString(e);
     if (sc->block) cudaFree(sc->block);
@@ -186,8 +207,13 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
 
 int b200rt_scene_destroy(b200rt_scene* s) {
   if (!s) return B200RT_OK;
-  cudaSetDevice(s->ctx->device);
-  if (s->block) cudaFree(s->block);
+  b200rt_ctx* ctx = s->ctx;
+  cudaSetDevice(ctx->device);
+  if (s->block) {
+    cudaStreamSynchronize(ctx->stream);  // nothing in flight may still read the tables
+    if (!ctx->spare_block) { ctx->spare_block = s->block; ctx->spare_bytes = s->block_bytes; }
+    else cudaFree(s->block);
+  }
   delete s;
   return B200RT_OK;
 }

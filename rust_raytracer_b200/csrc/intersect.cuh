@@ -250,19 +250,18 @@ DEV uint32_t pop_next(TStack& stack, int& sp, float t_best32) {
 // Per-ray constants of the node test.  t = plane * inv - o * inv is one FFMA per plane; the near / far plane of
 // every axis is chosen by ADDRESS (the node stores lo.x|lo.y|lo.z|hi.x|hi.y|hi.z as six float4 rows, so the
 // direction sign picks row a or row a + 3), which removes the per-child min/max pairs.  The rounding error of
-// o * inv (the only term the fused form adds over (plane - o) * inv) is folded into the two constants so the
-// test stays conservative: near parameters are lowered, far parameters raised by |o * inv| * 2^-22.
+// o * inv (the only term the fused form adds over (plane - o) * inv) is covered so the
+// test stays conservative through one per-ray slack term on the comparison (2 * max|o * inv| * 2^-22).
 struct RayT {
-  float3 inv, oin, oif;  // 1/d, o/d + e (near planes), o/d - e (far planes)
-  int nx, ny, nz;        // byte offset of the near-plane row of each axis: 0 or 48
+  float3 inv, oi;  // 1/d, o/d
+  float slack;     // 2 * max_axis |o/d| * 2^-22: absolute error budget of (near - far) from rounding o/d
+  int nx, ny, nz;  // byte offset of the near-plane row of each axis: 0 or 48
 };
 DEV RayT make_rayt(const RayF& rf) {
   RayT t;
   t.inv = rf.inv;
-  const float3 oi = rf.o * rf.inv;
-  const float k = 2.3841858e-7f;  // 2^-22
-  t.oin = f3(oi.x + fabsf(oi.x) * k, oi.y + fabsf(oi.y) * k, oi.z + fabsf(oi.z) * k);
-  t.oif = f3(oi.x - fabsf(oi.x) * k, oi.y - fabsf(oi.y) * k, oi.z - fabsf(oi.z) * k);
+  t.oi = rf.o * rf.inv;
+  t.slack = 4.7683716e-7f * fmaxf(fabsf(t.oi.x), fmaxf(fabsf(t.oi.y), fabsf(t.oi.z)));  // 2 * 2^-22
   t.nx = rf.inv.x < 0.f ? 48 : 0; t.ny = rf.inv.y < 0.f ? 48 : 0; t.nz = rf.inv.z < 0.f ? 48 : 0;
   return t;
 }
@@ -283,9 +282,9 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32
   const float bx[4] = {fxv.x, fxv.y, fxv.z, fxv.w}, by[4] = {fyv.x, fyv.y, fyv.z, fyv.w}, bz[4] = {fzv.x, fzv.y, fzv.z, fzv.w};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const float n = fmaxf(fmaxf(fmaf(ax[i], rt.inv.x, -rt.oin.x), fmaf(ay[i], rt.inv.y, -rt.oin.y)), fmaxf(fmaf(az[i], rt.inv.z, -rt.oin.z), t_min));
-    const float f = fminf(fminf(fmaf(bx[i], rt.inv.x, -rt.oif.x), fmaf(by[i], rt.inv.y, -rt.oif.y)), fminf(fmaf(bz[i], rt.inv.z, -rt.oif.z), t_best32));
-    tn[i] = (n <= f * 1.000001f) ? n : 3.0e38f;  // empty slots hold an inverted infinite box: never hit
+    const float n = fmaxf(fmaxf(fmaf(ax[i], rt.inv.x, -rt.oi.x), fmaf(ay[i], rt.inv.y, -rt.oi.y)), fmaxf(fmaf(az[i], rt.inv.z, -rt.oi.z), t_min));
+    const float f = fminf(fminf(fmaf(bx[i], rt.inv.x, -rt.oi.x), fmaf(by[i], rt.inv.y, -rt.oi.y)), fminf(fmaf(bz[i], rt.inv.z, -rt.oi.z), t_best32));
+    tn[i] = (n <= fmaf(f, 1.000001f, rt.slack)) ? n : 3.0e38f;  // empty slots hold an inverted infinite box: never hit (inf <= -inf is false)
   }
 #else
   const float4* nd = S.nodes + 8 * (size_t)cur;
@@ -380,9 +379,6 @@ DEV void sphere_uv(d3 n, float& u, float& v) {  // sphere.rs:16-20
   u = (float)(phi * (1.0 / PI_D) * 0.5);
   v = (float)(theta * (1.0 / PI_D));
 }
-// Vec3::unit (vec3.rs:86-91).  One reciprocal instead of three divisions: the result differs from v / |v| by
-// <= 1 ulp of f64 and is rounded to f32 right after.
-DEV d3 dunit(d3 v) { return v * (1.0 / sqrt(ddot(v, v))); }
 
 // HitRecord::new (hit.rs:17-39) for the winning primitive; WANT_UV = false skips the sphere uv (acos/atan2).
 // Instanced primitives follow Transform::hit (transform.rs:151-165): the record is built in OBJECT space, then
@@ -401,10 +397,10 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
   const float4 A = __ldg(rec);
   d3 on;  // outward normal in the primitive's own space
   switch (type) {
-    case B200RT_PRIM_SPHERE: on = (p - D3(A)) * (1.0 / (double)A.w); break;
+    case B200RT_PRIM_SPHERE: on = p - D3(A); break;  // (p - c) / r: the positive scale drops out below
     case B200RT_PRIM_MOVING_SPHERE: {
       const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
-      on = (p - moving_center(D3(A), D3(B), (double)C.x, (double)C.y, rd.time)) * (1.0 / (double)A.w);
+      on = p - moving_center(D3(A), D3(B), (double)C.x, (double)C.y, rd.time);
       break;
     }
     case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
@@ -431,17 +427,20 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
       tri_exact(rd, D3(A), D3(B), D3(C), -DINF, DINF, t, b1, b2);
       const double b0 = __dsub_rn(__dsub_rn(1.0, b1), b2);
       const float4* nn = S.tri_normals + 3 * (size_t)meta.w;
-      on = dunit(b0 * D3(__ldg(nn)) + b1 * D3(__ldg(nn + 1)) + b2 * D3(__ldg(nn + 2)));
+      on = b0 * D3(__ldg(nn)) + b1 * D3(__ldg(nn + 1)) + b2 * D3(__ldg(nn + 2));
       break;
     }
     default: on = D3(1., 0., 0.); break;  // ConstantMedium: arbitrary normal (medium.rs:47)
   }
-  if (WANT_UV && (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE)) sphere_uv(on, out.u, out.v);
+  // `on` is the outward normal up to a positive scale.  The cancellation-prone parts (p, p - c, the sign tests of
+  // hit.rs:25 / transform.rs:160) stay in f64; Vec3::unit (hit.rs:33) is taken in f32 after the final rounding
+  // (2e-7 relative against the 1e-5 tolerance; three f64 divisions and a square root less per hit).
+  if (WANT_UV && (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE)) sphere_uv(on * (1.0 / (double)A.w), out.u, out.v);
   const bool front = ddot(rd.d, on) < 0.;  // hit.rs:25
-  d3 n = dunit(front ? on : -on);           // hit.rs:26-33
+  const d3 n = front ? on : -on;            // hit.rs:26-33
   if (!inst) {
     out.front_face = front ? 1 : 0;
-    out.n = to_f3(n);
+    out.n = normalize(to_f3(n));
     out.p = to_f3(p);
     return;
   }
@@ -449,7 +448,6 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
   const d3 outward = affine_dir(m, n);  // transform.rs:158
   out.p = to_f3(affine_point(m, p));    // transform.rs:159
   const bool ff = ddot(rd.d, outward) < 0.;  // transform.rs:160 -> hit.rs:41-48, against the OBJECT-space ray
-  const d3 un = dunit(outward);
   out.front_face = ff ? 1 : 0;
-  out.n = to_f3(ff ? un : -un);
+  out.n = normalize(to_f3(ff ? outward : -outward));
 }
