@@ -93,14 +93,15 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
   DBG_INC(10 + type);
   uint32_t cand = 0x3fu;  // Cube faces to confirm: bits 0..5 near the slab entry, bits 8..13 near the exit
   int verdict = FILTER_MAYBE;
+  float t_medium = 0.f;
   // ---- f32 filter (certain misses only)
   if (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MEDIUM_SPHERE) {
     const float xi = is_medium ? medium_xi_f32(ray.mseed, (uint32_t)meta.y) : 0.5f;
-    verdict = sphere_reject(rf, f3(A), A.w, t_min, t_best32, eps, is_medium, WB.x, xi);
+    verdict = sphere_reject(rf, f3(A), A.w, t_min, t_best32, eps, is_medium, WB.x, xi, &t_medium);
     if (verdict == FILTER_REJECT) return;
   } else if (type == B200RT_PRIM_BOX || type == B200RT_PRIM_MEDIUM_BOX) {
     const float xi = is_medium ? medium_xi_f32(ray.mseed, (uint32_t)meta.y) : 0.5f;
-    verdict = box_reject(rf, f3(A), f3(WB), t_min, t_best32, eps, is_medium ? nullptr : &cand, is_medium, WB.w, xi);
+    verdict = box_reject(rf, f3(A), f3(WB), t_min, t_best32, eps, is_medium ? nullptr : &cand, is_medium, WB.w, xi, &t_medium);
     if (verdict == FILTER_REJECT) return;
   } else if (is_rect) {
     if (rect_reject(rf, rect_axis, A.x, A.y, A.z, A.w, WB.x, t_min, t_best32, eps)) return;
@@ -109,6 +110,12 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
     const float4 C = __ldg(&S.prim_data[3 * k + 2]);
     if (tri_reject(rf, f3(A), f3(WB), f3(C), t_min, t_best32, eps)) return;
   }  // moving spheres go straight to the exact test
+  if (verdict == FILTER_MEDIUM_HIT) {  // certain interior scatter, certainly the closest hit so far: t in f32
+    DBG_INC(30 + type);
+    h.t = (double)t_medium; h.prim = k; h.aux = 0;
+    t_best32 = t_medium;
+    return;
+  }
   // ---- f64 decision
   RayD rd = make_rayd(ray);
   const float4* rec = S.prim_data + 3 * (size_t)k;
@@ -119,11 +126,7 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
   const double tmin_d = (double)t_min, tmax_d = h.t;
   double t_in = 0., t_out = 0.;  // surfaces: t_in is the hit; media: the boundary interval
   int aux = 0;
-  if (verdict == FILTER_MEDIUM_HIT) {
-    // certain interior scatter: t1 = max(t_min, 0) and the comparison of medium.rs:44 is decided, so the boundary
-    // roots are not needed (any t_in < t_min, t_out >= t_max gives the reference's own t below)
-    t_in = -DINF; t_out = DINF;
-  } else if (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE || type == B200RT_PRIM_MEDIUM_SPHERE) {
+  if (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE || type == B200RT_PRIM_MEDIUM_SPHERE) {
     // objects/sphere.rs:24-43 — nearest root in the CLOSED interval [t_min, t_max]; tangent rays hit.
     // ConstantMedium (medium.rs:26-31): first root in (-inf, inf), then the next one in [first + 0.0001, inf).
     d3 c = D3(EA);

@@ -30,8 +30,10 @@ DEV float safe_rcp(float d) { return rcp_fast(fabsf(d) > 1e-30f ? d : copysignf(
 // hit_distance = -1/density * ln(xi) is known to ~3 ulp, so when it exceeds that upper bound the medium is a
 // certain miss and the f64 boundary roots / log never run.  Conversely, when the ray certainly starts inside
 // (t_in < t_min) and hit_distance is certainly below the LOWER bound of distance_inside, the outcome is a hit at
-// t = max(t_min, 0) + hit_distance / |d| whatever the exact boundary roots are: the exact stage then skips them.
-DEV int medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, float e_out, float neg_inv_density, float xi, float t_min, float t_best) {
+// t = max(t_min, 0) + hit_distance / |d| whatever the exact boundary roots are, and certainly closer than the best
+// hit so far: no decision depends on its low bits, so t itself is taken in f32 (north_star: t within 1e-5) and the
+// whole f64 stage (boundary roots, f64 log / sqrt / division) is skipped for half of all book-2 rays.
+DEV int medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, float e_out, float neg_inv_density, float xi, float t_min, float t_best, float* t_hit) {
   const float lo = fmaxf(fmaxf(t_in - e_in, t_min), 0.f);
   const float hi = fminf(t_out + e_out, t_best);
   const float len = sqrt_fast(r.a);  // <= 2 ulp, inside the 2e-6 margins below
@@ -43,7 +45,10 @@ DEV int medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, fl
     const float lo1 = fmaxf(t_min, 0.f);                                    // exact: t1 after both clamps
     const float hi1 = fminf(t_out - e_out, t_best * (1.0f - 2.4e-7f));      // lower bound of min(t_out, t_max); t_best is rounded up
     const float lower = ((hi1 - lo1) - 2e-7f * (fabsf(hi1) + fabsf(lo1))) * len * (1.0f - 2e-6f);
-    if (hi1 > lo1 * (1.0f + 1e-6f) + 1e-30f && hd * (1.0f + 2e-6f) < lower) return FILTER_MEDIUM_HIT;
+    if (hi1 > lo1 * (1.0f + 1e-6f) + 1e-30f && hd * (1.0f + 2e-6f) < lower) {
+      *t_hit = lo1 + hd / sqrtf(r.a);  // medium.rs:52 in f32: ~4 ulp, against the 1e-5 tolerance on t
+      return FILTER_MEDIUM_HIT;
+    }
   }
   return FILTER_MAYBE;
 }
@@ -52,7 +57,7 @@ DEV int medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, fl
 // eps: absolute error of the baked world-space coordinates of an instanced primitive (0 when not instanced):
 // the exact test then runs in OBJECT space on the original values, so the filter must tolerate the baking error.
 // medium = true: the sphere is a ConstantMedium boundary (both roots matter, then the distance test).
-DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best, float eps, bool medium = false, float neg_inv_density = 0.f, float xi = 0.5f) {
+DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float t_best, float eps, bool medium = false, float neg_inv_density = 0.f, float xi = 0.5f, float* t_hit = nullptr) {
   float3 oc = r.o - c;
   float hb = dot(oc, r.d), oc2 = dot(oc, oc), r2 = radius * radius;
   float cc = oc2 - r2;
@@ -69,7 +74,7 @@ DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float 
     float e0 = dn + 1e-6f * fabsf(t0), e1 = dn + 1e-6f * fabsf(t1);
     if (t0 - e0 > t_best) return true;                       // nearest root already beyond the best hit
     if (t1 + e1 < t_min) return true;                        // sphere entirely behind t_min
-    if (medium) return medium_far_reject(r, t0, e0, t1, e1, neg_inv_density, xi, t_min, t_best);
+    if (medium) return medium_far_reject(r, t0, e0, t1, e1, neg_inv_density, xi, t_min, t_best, t_hit);
     if (t0 + e0 < t_min && t1 - e1 > t_best) return true;    // origin inside, exit beyond the best hit
   }
   return false;
@@ -96,7 +101,7 @@ DEV bool rect_reject(const RayF& r, int axis, float a0, float b0, float a1, floa
 // numbering of cube_side: XY@min.z, XY@max.z, XZ@min.y, XZ@max.y, YZ@min.x, YZ@max.x).  A face whose plane hit
 // is neither is out of its rectangle bounds for certain, so the exact test may skip it.
 DEV int box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_best, float eps, uint32_t* cand = nullptr, bool medium = false, float neg_inv_density = 0.f,
-                    float xi = 0.5f) {
+                   float xi = 0.5f, float* t_hit = nullptr) {
   float3 t0 = (mn - r.o) * r.inv, t1 = (mx - r.o) * r.inv;
   float tn = fmaxf(fmaxf(fminf(t0.x, t1.x), fminf(t0.y, t1.y)), fminf(t0.z, t1.z));
   float tf = fminf(fminf(fmaxf(t0.x, t1.x), fmaxf(t0.y, t1.y)), fmaxf(t0.z, t1.z));
@@ -105,7 +110,7 @@ DEV int box_reject(const RayF& r, float3 mn, float3 mx, float t_min, float t_bes
   if (tn - en > tf + ef) return true;
   if (tf + ef < t_min) return true;
   if (tn - en > t_best) return true;
-  if (medium) return medium_far_reject(r, tn, en, tf, ef, neg_inv_density, xi, t_min, t_best);  // ConstantMedium boundary
+  if (medium) return medium_far_reject(r, tn, en, tf, ef, neg_inv_density, xi, t_min, t_best, t_hit);  // ConstantMedium boundary
   if (tn + en < t_min && tf - ef > t_best) return true;
   if (cand) {
     const float ts[6] = {t0.z, t1.z, t0.y, t1.y, t0.x, t1.x};

