@@ -319,6 +319,8 @@ int b200rt_builder_set_flags(b200rt_builder* b, uint32_t flags);
 int b200rt_builder_seed_perlin(b200rt_builder* b, uint64_t seed);
 /* Appendix-B JSON scene (data/scene_*.json): fills the builder and the camera. */
 int b200rt_builder_load_json(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out);
+/* The YAML twins (data/scene_*.yaml, README.md:86-89: same objects as the JSON files; block-style subset). */
+int b200rt_builder_load_yaml(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out);
 /* Canonical workloads C1..C5: "book1", "cornell_ref", "cornell_book3", "book2", "mesh".
  * aux_path: OBJ path for "mesh"/"cornell_ref"; earth_*: decoded earthmap for "book2" (may be NULL). */
 int b200rt_builder_make_scene(b200rt_builder* b, const char* name, uint64_t seed, const char* aux_path,

@@ -123,6 +123,7 @@ PROTOTYPES = {
     "b200rt_builder_set_flags": (C.c_int, [VP, C.c_uint32]),
     "b200rt_builder_seed_perlin": (C.c_int, [VP, C.c_uint64]),
     "b200rt_builder_load_json": (C.c_int, [VP, C.c_char_p, C.c_uint64, C.POINTER(Camera)]),
+    "b200rt_builder_load_yaml": (C.c_int, [VP, C.c_char_p, C.c_uint64, C.POINTER(Camera)]),
     "b200rt_builder_make_scene": (C.c_int, [VP, C.c_char_p, C.c_uint64, C.c_char_p, VP, C.c_int32, C.c_int32, C.c_double, C.POINTER(Camera), C.POINTER(Params)]),
     "b200rt_builder_finish": (C.c_int, [VP, C.POINTER(SceneDesc)]),
 }

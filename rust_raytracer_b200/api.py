@@ -80,6 +80,11 @@ class SceneBuilder:
         self._ok(F.lib().b200rt_builder_load_json(self._h, data, len(data), C.byref(self.camera)))
         return self
 
+    def load_yaml(self, text):
+        data = text.encode() if isinstance(text, str) else bytes(text)
+        self._ok(F.lib().b200rt_builder_load_yaml(self._h, data, len(data), C.byref(self.camera)))
+        return self
+
     def make_scene(self, name, seed=1, aux_path=None, earth=None, aspect=0.0):
         ptr, w, h = None, 0, 0
         if earth is not None:

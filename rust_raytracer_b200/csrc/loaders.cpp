@@ -197,6 +197,89 @@ struct JParser {
   }
 };
 
+// ---------------------------------------------------------------- YAML (the block-style subset serde_yaml emits for
+// data/scene_*.yaml: nested mappings, "- " sequences of mappings, plain scalars; README.md:86-89 says the YAML twins
+// carry the same objects as the JSON files).  Parsed into the same JValue tree, so one scene walker serves both.
+struct YLine { int indent; bool dash; std::string key, val; bool has_val; };
+struct YParser {
+  std::vector<YLine> lines;
+  std::string err;
+  size_t at = 0;
+  static std::string trim(const std::string& s) {
+    size_t a = s.find_first_not_of(" \t\r"), b = s.find_last_not_of(" \t\r");
+    return a == std::string::npos ? std::string() : s.substr(a, b - a + 1);
+  }
+  bool tokenize(const char* p, const char* end) {
+    while (p < end) {
+      const char* e = (const char*)std::memchr(p, '\n', end - p);
+      if (!e) e = end;
+      std::string raw(p, e);
+      p = e < end ? e + 1 : end;
+      size_t hash = raw.find(" #");
+      if (hash != std::string::npos) raw.resize(hash);
+      if (trim(raw).empty() || trim(raw)[0] == '#' || trim(raw) == "---") continue;
+      int ind = 0;
+      while (ind < (int)raw.size() && raw[ind] == ' ') ++ind;
+      std::string body = raw.substr(ind);
+      while (body.size() >= 2 && body[0] == '-' && body[1] == ' ') {  // "- key: v" = a dash marker + the mapping's first line
+        lines.push_back({ind, true, "", "", false});
+        size_t skip = 2;
+        while (skip < body.size() && body[skip] == ' ') ++skip;
+        ind += (int)skip; body = body.substr(skip);
+      }
+      if (body == "-") { lines.push_back({ind, true, "", "", false}); continue; }
+      size_t colon = body.find(':');
+      if (colon == std::string::npos) { err = "YAML: expected 'key: value' in '" + body + "'"; return false; }
+      YLine l{ind, false, trim(body.substr(0, colon)), trim(body.substr(colon + 1)), false};
+      if (l.key.size() >= 2 && (l.key[0] == '"' || l.key[0] == '\'')) l.key = l.key.substr(1, l.key.size() - 2);
+      l.has_val = !l.val.empty();
+      lines.push_back(l);
+    }
+    return true;
+  }
+  std::unique_ptr<JValue> scalar(std::string v) {
+    std::unique_ptr<JValue> j(new JValue());
+    if (v.size() >= 2 && (v[0] == '"' || v[0] == '\'')) { j->kind = JValue::Str; j->str = v.substr(1, v.size() - 2); return j; }
+    if (v == "~" || v == "null") return j;
+    if (v == "true" || v == "false") { j->kind = JValue::Bool; j->num = v == "true"; return j; }
+    char* e;
+    double d = std::strtod(v.c_str(), &e);
+    if (e != v.c_str() && *e == 0) { j->kind = JValue::Num; j->num = d; return j; }
+    j->kind = JValue::Str; j->str = v;
+    return j;
+  }
+  // the block starting at lines[at], whose lines sit at exactly `indent`
+  std::unique_ptr<JValue> block(int indent, int depth) {
+    std::unique_ptr<JValue> v(new JValue());
+    if (depth > 4096) { err = "YAML: nesting too deep"; return nullptr; }
+    if (at >= lines.size()) return v;
+    if (lines[at].dash) {
+      v->kind = JValue::Arr;
+      while (at < lines.size() && lines[at].dash && lines[at].indent == indent) {
+        ++at;
+        if (at >= lines.size() || lines[at].indent <= indent) { v->arr.emplace_back(new JValue()); continue; }
+        auto c = block(lines[at].indent, depth + 1);
+        if (!c) return nullptr;
+        v->arr.push_back(std::move(c));
+      }
+      return v;
+    }
+    v->kind = JValue::Obj;
+    while (at < lines.size() && !lines[at].dash && lines[at].indent == indent) {
+      const YLine l = lines[at++];
+      if (l.has_val) { v->obj.emplace_back(l.key, scalar(l.val)); continue; }
+      // nested block: deeper mapping, or a sequence (serde_yaml indents it, plain YAML may keep it at the key's indent)
+      if (at < lines.size() && (lines[at].indent > indent || (lines[at].dash && lines[at].indent == indent))) {
+        auto c = block(lines[at].indent, depth + 1);
+        if (!c) return nullptr;
+        v->obj.emplace_back(l.key, std::move(c));
+      } else v->obj.emplace_back(l.key, std::unique_ptr<JValue>(new JValue()));
+    }
+    if (at < lines.size() && lines[at].indent > indent) { err = "YAML: bad indentation near key '" + lines[at].key + "'"; return nullptr; }
+    return v;
+  }
+};
+
 bool jnum(const JValue* v, const char* k, double& out) {
   const JValue* c = v ? v->get(k) : nullptr;
   if (!c || c->kind != JValue::Num) return false;
@@ -306,14 +389,30 @@ int b200rt_builder_mesh_obj(b200rt_builder* b, const char* path, int32_t materia
   return first;
 }
 
+static int load_scene_tree(b200rt_builder* b, const JValue* root, b200rt_camera* cam_out);
+
 int b200rt_builder_load_json(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out) {
   if (!b || !text) return B200RT_ERR_INVALID;
   JParser jp;
   jp.p = text; jp.end = text + len;
   auto root = jp.parse();
   if (!root) { b->err = "JSON: " + jp.err; return B200RT_ERR_PARSE; }
+  return load_scene_tree(b, root.get(), cam_out);
+}
+
+int b200rt_builder_load_yaml(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out) {
+  if (!b || !text) return B200RT_ERR_INVALID;
+  YParser yp;
+  if (!yp.tokenize(text, text + len)) { b->err = yp.err; return B200RT_ERR_PARSE; }
+  if (yp.lines.empty()) { b->err = "YAML: empty document"; return B200RT_ERR_PARSE; }
+  auto root = yp.block(yp.lines[0].indent, 0);
+  if (!root || yp.at != yp.lines.size()) { b->err = yp.err.empty() ? "YAML: trailing content / bad indentation" : yp.err; return B200RT_ERR_PARSE; }
+  return load_scene_tree(b, root.get(), cam_out);
+}
+
+static int load_scene_tree(b200rt_builder* b, const JValue* root, b200rt_camera* cam_out) {
   const JValue* objects = root->get("objects");
-  if (!objects) { b->err = "JSON: no 'objects'"; return B200RT_ERR_PARSE; }
+  if (!objects) { b->err = "scene file: no 'objects'"; return B200RT_ERR_PARSE; }
   bool flat = jtype(objects) == "HitableList";
   if (flat) {  // a BVHNode anywhere below makes it the BVH arm
     const JValue* items = objects->get("items");

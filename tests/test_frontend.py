@@ -76,6 +76,44 @@ def test_json_scenes(name, n, flat):
     assert abs(cam.lens_radius - 0.05) < 1e-7
 
 
+@pytest.mark.parametrize("name", ["scene_10", "scene_200_no_bvh"])
+def test_yaml_twin_builds_the_same_tables(name):
+    """README.md:86-89: the .yaml files carry the same objects as the .json files -> identical flat tables and camera."""
+    a = rt.SceneBuilder().load_json(open(os.path.join(DATA, name + ".json")).read())
+    b = rt.SceneBuilder().load_yaml(open(os.path.join(DATA, name + ".yaml")).read())
+    da, db = a.desc(), b.desc()
+    assert (da.n_prims, da.n_materials, da.n_textures, da.flags) == (db.n_prims, db.n_materials, db.n_textures, db.flags)
+    for i in range(da.n_prims):
+        pa, pb = da.prims[i], db.prims[i]
+        assert (pa.type, pa.material, pa.instance) == (pb.type, pb.material, pb.instance)
+        assert list(pa.p) == list(pb.p)
+    for i in range(da.n_materials):
+        assert (da.materials[i].type, da.materials[i].texture, da.materials[i].param) == (db.materials[i].type, db.materials[i].texture, db.materials[i].param)
+    for i in range(da.n_textures):
+        assert (da.textures[i].type, list(da.textures[i].c0), list(da.textures[i].c1)) == (db.textures[i].type, list(db.textures[i].c0), list(db.textures[i].c1))
+    for f in ("origin", "lower_left_corner", "horizontal", "vertical"):
+        assert list(getattr(a.camera, f)) == list(getattr(b.camera, f))
+    assert a.camera.lens_radius == b.camera.lens_radius
+
+
+def test_yaml_errors_and_plain_style():
+    with pytest.raises(rt.B200RTError) as e:
+        rt.SceneBuilder().load_yaml("objects:\n  type: Torus\n")
+    assert e.value.status == F.ERR_PARSE
+    with pytest.raises(rt.B200RTError):
+        rt.SceneBuilder().load_yaml("objects\n")
+    # a sequence kept at its key's indentation (plain YAML style) and a comment line
+    text = "\n".join([
+        "# one sphere", "objects:", "  type: HitableList", "  items:", "  - type: Sphere", "    center: {}".replace("{}", ""),
+        "      x: 0", "      y: 0", "      z: -1", "    radius: 0.5", "    material:", "      type: Dielectric", "      ref_idx: 1.5",
+        "camera:", "  look_from:", "    x: 0", "    y: 0", "    z: 3", "  look_at:", "    x: 0", "    y: 0", "    z: 0", "  vup:", "    x: 0", "    y: 1", "    z: 0",
+        "  vfov: 40", "  aspect: 1", "  aperture: 0", "  focus_dist: 3", ""])
+    sb = rt.SceneBuilder().load_yaml(text)
+    d = sb.desc()
+    assert d.n_prims == 1 and tuple(d.prims[0].p[:4]) == (0.0, 0.0, -1.0, 0.5)
+    assert d.materials[d.prims[0].material].type == F.MAT_DIELECTRIC
+
+
 def test_json_errors():
     with pytest.raises(rt.B200RTError) as e:
         rt.SceneBuilder().load_json('{"objects": {"type": "Torus"}}')
