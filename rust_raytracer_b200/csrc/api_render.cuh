@@ -80,8 +80,8 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
                 : P.integrator == B200RT_INTEGRATOR_MIXTURE ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_MIXTURE>, 128, 0)
                                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_NEE>, 128, 0));
   const int grid_ext = sms * (occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
-  const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", occ_shade > 4 ? 4 : (occ_shade > 0 ? occ_shade : 1), 1, 64);
-  // (4 resident shade blocks per SM: a larger grid widens the window of queue positions in flight, which interleaves
+  const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", occ_shade > 5 ? 5 : (occ_shade > 0 ? occ_shade : 1), 1, 64);
+  // (one resident wave of shade blocks: a larger grid widens the window of queue positions in flight, which interleaves
   //  the bins in the compacted output and costs the next extend pass ~5 %; measured in profiles/r1_experiments.md)
   const int batch = env_int("B200RT_WF_BATCH", 4, 1, 8);
   uint64_t launches = 0;

@@ -177,13 +177,17 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
   }
 }
 
-// shade: walks the current queue in order (streaming reads of whole records, the next record prefetched while the
-// current one is shaded) and stores every surviving path at its place in the next set.
-#ifndef B200RT_SHADE_MINBLOCKS
+// shade: walks the current queue in order (streaming reads of whole records) and stores every surviving path at
+// its place in the next set.
+#ifndef B200RT_SHADE_MINBLOCKS_PATH  // the PATH instantiation fits 96 registers without spilling (5 blocks/SM) ...
+#define B200RT_SHADE_MINBLOCKS_PATH 5
+#endif
+#ifndef B200RT_SHADE_MINBLOCKS  // ... MIXTURE / NEE need 120 / 126
 #define B200RT_SHADE_MINBLOCKS 4
 #endif
 template <int INTEG>
-__global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
+__global__ void __launch_bounds__(128, INTEG == B200RT_INTEGRATOR_PATH ? B200RT_SHADE_MINBLOCKS_PATH : B200RT_SHADE_MINBLOCKS)
+k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   __shared__ unsigned int s_off[WF_NBINS + 1];
   for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) s_off[k] = B.bin_off[k];
   __syncthreads();
@@ -193,13 +197,23 @@ __global__ void __launch_bounds__(128, B200RT_SHADE_MINBLOCKS) k_wf_shade(DevSce
   const unsigned int g0 = blockIdx.x * blockDim.x + threadIdx.x;
   float4 n_o, n_d, n_sa, n_sb, n_hh, n_br;
   auto load_rec = [&](unsigned int src) { const float4* r = B.rec + (size_t)WF_REC * src; n_o = r[0]; n_d = r[1]; n_sa = r[2]; n_sb = r[3]; n_hh = r[4]; n_br = r[5]; };
+#ifndef B200RT_SHADE_PREFETCH  // measured: with streaming reads the explicit prefetch only costs registers (18.3 ms vs 17.2 ms at 96 regs)
+#define B200RT_SHADE_PREFETCH 0
+#endif
+#if B200RT_SHADE_PREFETCH
   if (g0 < n_ext) load_rec(g0);
+#endif
   for (unsigned int gi = g0; gi < n_work; gi += stride) {
+#if !B200RT_SHADE_PREFETCH
+    if (gi < n_ext) load_rec(gi);
+#endif
     const float4 o = n_o, d = n_d, sa = n_sa;
     const uint4 sb = make_uint4(__float_as_uint(n_sb.x), __float_as_uint(n_sb.y), __float_as_uint(n_sb.z), 0u);
     const uint4 hh = make_uint4(__float_as_uint(n_hh.x), __float_as_uint(n_hh.y), __float_as_uint(n_hh.z), __float_as_uint(n_hh.w));
     const unsigned int bin = __float_as_uint(n_br.x), rank = __float_as_uint(n_br.y);
+#if B200RT_SHADE_PREFETCH
     if (gi + stride < n_ext) load_rec(gi + stride);
+#endif
     const bool active = gi < n_ext && (int)hh.z != WF_PRIM_DEAD;
     bool cont = false, shadow = false;
     Ray ray;
