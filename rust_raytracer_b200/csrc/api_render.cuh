@@ -8,14 +8,17 @@ static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool) {
   const size_t P = pool;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
-  size_t o_set[2];
-  for (int k = 0; k < 2; ++k) o_set[k] = take(P * 16 * WF_REC);  // the two record sets (96 B per queue position)
+  size_t o_ray[2], o_st[2];
+  for (int k = 0; k < 2; ++k) { o_ray[k] = take(P * 32); o_st[k] = take(P * 32); }  // the two ray / state sets
+  size_t o_hit = take(P * 16);
   size_t o_bc = take(4 * WF_NBINS), o_bo = take(4 * (WF_NBINS + 1));
   size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4), o_cnt = take(sizeof(WfCounters));
   CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
   char* b = (char*)ctx->wf_block;
   ctx->wf_bytes = off;
-  ctx->wf.rec = (float4*)(b + o_set[0]); ctx->wf.rec_n = (float4*)(b + o_set[1]);
+  ctx->wf.ray = (float4*)(b + o_ray[0]); ctx->wf.ray_n = (float4*)(b + o_ray[1]);
+  ctx->wf.st = (float4*)(b + o_st[0]); ctx->wf.st_n = (float4*)(b + o_st[1]);
+  ctx->wf.hit = (uint4*)(b + o_hit);
   ctx->wf.bin_count = (unsigned int*)(b + o_bc); ctx->wf.bin_off = (unsigned int*)(b + o_bo);
   ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
   ctx->wf.cnt = (WfCounters*)(b + o_cnt);
@@ -93,7 +96,8 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
       cudaEvent_t* ev = ctx->sev + 8 * b;
       cudaEventRecord(ev[0], q);
       // the set shade just compacted the survivors into becomes the current one; generate appends behind them
-      std::swap(B.rec, B.rec_n);
+      std::swap(B.ray, B.ray_n);
+      std::swap(B.st, B.st_n);
       k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M);
       k_wf_control<<<1, WF_NBINS, 0, q>>>(B, M);
       cudaEventRecord(ev[1], q);

@@ -1,14 +1,15 @@
 // wavefront.cuh — the wavefront pipeline over SoA float4 ray queues (north_star): generate -> extend ->
 // per-material shade -> light-sample/shadow, with stream compaction by warp-aggregated atomics.
 //
-// The queues hold the ray PAYLOAD, not indices, as one 96-byte record (three 32-byte DRAM sectors) per position:
-//   sector 0: (o.xyz, time) (d.xyz, medium seed bits; t_max of an extend ray is always +inf)   read by extend + shade
-//   sector 1: (throughput.rgb, prev_pdf_b) (pixel, sample, bounce, 0)                           read by shade
-//   sector 2: (t as 2 x u32 [f64], device prim, aux) (bin, rank in bin, 0, 0)                   written by extend
-// Extend, shade and generate all read and write their queue strictly in order; the only scattered traffic is the
-// 64-byte store of a surviving path into its bin of the NEXT set (stores do not stall the warp the way the
-// gathers of an index-sorted shade did: 154 B read per ray for 84 B of payload, latency-bound at 28 % issue).  The two sets are swapped by the host
-// between iterations.  Shadow requests are stored by queue position: sh_o, sh_d, sh_c, sh_seed.
+// The queues hold the ray PAYLOAD, not indices, as three streams per queue position (80 bytes):
+//   ray   32 B: (o.xyz, time) (d.xyz, medium seed bits; t_max of an extend ray is always +inf)   read by extend + shade
+//   state 32 B: (throughput.rgb, prev_pdf_b) (pixel, sample, bounce, 0)                           read by shade
+//   hit   16 B: (t as 2 x u32 [f64], device prim + 2 | Cube side << 28, rank in bin)             extend -> shade
+// Extend, shade and generate all read and write their streams strictly in order (every fetched DRAM sector is
+// used whole: extend reads nothing but the ray stream); the only scattered traffic is the two 32-byte stores of
+// a surviving path into its bin of the NEXT ray / state set (stores do not stall the warp the way the gathers of
+// an index-sorted shade did: 154 B read per ray for 84 B of payload, latency-bound at 28 % issue).  The two sets
+// are swapped by the host between iterations.  Shadow requests are stored by queue position: sh_o, sh_d, sh_c, sh_seed.
 #pragma once
 #include "kernels.cuh"
 
@@ -20,7 +21,7 @@
 // neighbouring primitives, with similar traversal cost (fog-born rays together, ground-box rays together, ...).
 // A path that was predicted to go on but ended in shade (metal absorption, zero pdf, depth budget) leaves a dead
 // record (zero direction) that extend skips.
-#define WF_REC 6  // float4 per queue record (96 bytes)
+#define WF_POS_BYTES 144  // device bytes per queue position: 2 sets x (ray 32 + state 32) + hit 16
 #ifndef WF_NBINS
 #define WF_NBINS 256
 #endif
@@ -38,8 +39,11 @@ struct WfCounters {
 };
 
 struct WfBuffers {
-  float4* rec;    // current set: WF_REC float4 per queue position
-  float4* rec_n;  // next set
+  float4* ray;    // current set: 2 float4 per queue position
+  float4* ray_n;  // next set
+  float4* st;     // path state, current set: 2 float4 per queue position
+  float4* st_n;
+  uint4* hit;     // hit of the current set, written by extend: 1 uint4 per queue position
   unsigned int* bin_count;  // WF_NBINS: continuing rays per bin (filled by extend)
   unsigned int* bin_off;    // WF_NBINS + 1: start of every bin in the next set
   unsigned int bin_mul;     // bin = 1 + umulhi(prim, bin_mul)
@@ -78,11 +82,12 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P,
     uint32_t pixel, sample;
     path_to_pixel(M, P, base + i, pixel, sample);
     const Ray r = camera_ray(P, pixel, sample);
-    float4* rec = B.rec + (size_t)WF_REC * (off + i);
-    rec[0] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-    rec[1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed));
-    rec[2] = make_float4(1.f, 1.f, 1.f, -1.f);
-    rec[3] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), 0.f, 0.f);
+    float4* ray = B.ray + 2 * (size_t)(off + i);
+    float4* st = B.st + 2 * (size_t)(off + i);
+    ray[0] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+    ray[1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed));
+    st[0] = make_float4(1.f, 1.f, 1.f, -1.f);
+    st[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), 0.f, 0.f);
   }
 }
 
@@ -120,8 +125,8 @@ __global__ void k_wf_control_shade(WfBuffers B) {
 }
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
 
-// extend: persistent warps fetch 32 consecutive rays at a time (warp-level work fetch: coalesced 512-byte
-// reads of ray_o / ray_d), traverse, store the hit and bin the queue position for shade.
+// extend: persistent warps fetch 32 consecutive rays at a time (warp-level work fetch: one coalesced 1 KB read of
+// the ray stream), traverse, store the hit and rank the queue position inside its bin for shade.
 // (Measured and rejected: per-lane ray replacement a la Aila & Laine's dynamic fetch.  Refilling idle lanes from
 // the queue mixes rays of different bins in one warp and loses the converged out-of-BVH tail: 60 ms -> 74..99 ms
 // of extend per step on book-2 for refill thresholds 16..28, profiles/r1_experiments.md.)
@@ -130,6 +135,10 @@ __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->
 #endif
 #define WF_PRIM_DEAD (-2)
 #define WF_NO_RANK 0xffffffffu
+// hit.z: device primitive (-2 dead, -1 miss, else < 2^27) biased by 2, Cube side in the top bits
+DEV unsigned int wf_pack_prim(int prim, int aux) { return (unsigned int)(prim + 2) | ((unsigned int)aux << 28); }
+DEV int wf_unpack_prim(unsigned int w) { return (int)(w & 0x0FFFFFFFu) - 2; }
+DEV int wf_unpack_aux(unsigned int w) { return (int)(w >> 28); }
 __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevScene S, WfBuffers B, float t_min, int light_scatters) {
   const unsigned int n = B.cnt->n_ext;
   const unsigned lane = threadIdx.x & 31;
@@ -140,13 +149,13 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     if (base >= n) break;
     const unsigned int i = base + lane;
     const bool active = i < n;
-    float4* rec = B.rec + (size_t)WF_REC * i;
+    const float4* ray = B.ray + 2 * (size_t)i;
     unsigned int bin = (unsigned)WF_NBINS;  // WF_NBINS = "does not go on"
     HitRaw h;
     h.t = 0.; h.prim = WF_PRIM_DEAD; h.aux = 0;
     bool dead = false;
     if (active) {
-      const float4 o = rec[0], d = rec[1];
+      const float4 o = ray[0], d = ray[1];
       dead = d.x == 0.f && d.y == 0.f && d.z == 0.f;
       if (!dead) {
         Ray r;
@@ -171,8 +180,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     if (n_dead && lane == 0) atomicAdd(&B.cnt->dead_rays, n_dead);
     if (active) {
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
-      rec[4] = make_float4(__uint_as_float((unsigned int)tb), __uint_as_float((unsigned int)(tb >> 32)), __int_as_float(h.prim), __int_as_float(h.aux));
-      rec[5] = make_float4(__uint_as_float(bin), __uint_as_float(goes_on ? rank : WF_NO_RANK), 0.f, 0.f);  // full 32-byte sector: no read-modify-write
+      B.hit[i] = make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), wf_pack_prim(h.prim, h.aux), goes_on ? rank : WF_NO_RANK);
     }
   }
 }
@@ -195,8 +203,13 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   const unsigned int n_work = (n_ext + 31u) & ~31u;  // whole warps stay in the loop (warp-aggregated appends below)
   const unsigned int stride = gridDim.x * blockDim.x;
   const unsigned int g0 = blockIdx.x * blockDim.x + threadIdx.x;
-  float4 n_o, n_d, n_sa, n_sb, n_hh, n_br;
-  auto load_rec = [&](unsigned int src) { const float4* r = B.rec + (size_t)WF_REC * src; n_o = r[0]; n_d = r[1]; n_sa = r[2]; n_sb = r[3]; n_hh = r[4]; n_br = r[5]; };
+  float4 n_o, n_d, n_sa, n_sb;
+  uint4 n_hh;
+  auto load_rec = [&](unsigned int src) {
+    const float4* r = B.ray + 2 * (size_t)src;
+    const float4* t = B.st + 2 * (size_t)src;
+    n_o = r[0]; n_d = r[1]; n_sa = t[0]; n_sb = t[1]; n_hh = B.hit[src];
+  };
 #ifndef B200RT_SHADE_PREFETCH  // measured: with streaming reads the explicit prefetch only costs registers (18.3 ms vs 17.2 ms at 96 regs)
 #define B200RT_SHADE_PREFETCH 0
 #endif
@@ -209,12 +222,13 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
 #endif
     const float4 o = n_o, d = n_d, sa = n_sa;
     const uint4 sb = make_uint4(__float_as_uint(n_sb.x), __float_as_uint(n_sb.y), __float_as_uint(n_sb.z), 0u);
-    const uint4 hh = make_uint4(__float_as_uint(n_hh.x), __float_as_uint(n_hh.y), __float_as_uint(n_hh.z), __float_as_uint(n_hh.w));
-    const unsigned int bin = __float_as_uint(n_br.x), rank = __float_as_uint(n_br.y);
+    const uint4 hh = n_hh;
+    const int hprim = wf_unpack_prim(hh.z);
+    const unsigned int rank = hh.w;
 #if B200RT_SHADE_PREFETCH
     if (gi + stride < n_ext) load_rec(gi + stride);
 #endif
-    const bool active = gi < n_ext && (int)hh.z != WF_PRIM_DEAD;
+    const bool active = gi < n_ext && hprim != WF_PRIM_DEAD;
     bool cont = false, shadow = false;
     Ray ray;
     PathState ps;
@@ -224,23 +238,25 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
       ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
       ps.throughput = f3(sa); ps.prev_pdf_b = sa.w; ps.radiance = f3(0, 0, 0);
       ps.pixel = sb.x; ps.sample = sb.y; ps.bounce = (int)sb.z;
-      if ((int)hh.z < 0) {  // miss
+      if (hprim < 0) {  // miss
         ps.radiance = ps.throughput * background_color(P, ray.d);
       } else if (ps.bounce < P.max_depth) {  // photon_mapper.rs:336-339: the depth budget is checked after the hit
         HitRaw h;
-        h.t = __longlong_as_double((long long)(((unsigned long long)hh.y << 32) | hh.x)); h.prim = (int)hh.z; h.aux = (int)hh.w;
+        h.t = __longlong_as_double((long long)(((unsigned long long)hh.y << 32) | hh.x)); h.prim = hprim; h.aux = wf_unpack_aux(hh.z);
         cont = shade_hit<INTEG>(S, P, ray, h, ps, sr);
         shadow = sr.valid;
       }
       accum_add(accum, ps.pixel, ps.radiance);
     }
     if (active && rank != WF_NO_RANK) {  // the place extend reserved in the next set: the new ray, or a dead record
-      float4* out = B.rec_n + (size_t)WF_REC * (s_off[bin] + rank);
+      const size_t dst = 2 * (size_t)(s_off[1u + __umulhi((unsigned int)hprim, B.bin_mul)] + rank);  // the bin extend ranked it in
+      float4* out = B.ray_n + dst;
       if (cont) {
+        float4* out_s = B.st_n + dst;
         out[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
         out[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed));
-        out[2] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
-        out[3] = make_float4(__uint_as_float(ps.pixel), __uint_as_float(ps.sample), __uint_as_float((unsigned int)ps.bounce), 0.f);
+        out_s[0] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
+        out_s[1] = make_float4(__uint_as_float(ps.pixel), __uint_as_float(ps.sample), __uint_as_float((unsigned int)ps.bounce), 0.f);
       } else {
         out[0] = make_float4(0.f, 0.f, 0.f, 0.f);
         out[1] = make_float4(0.f, 0.f, 0.f, 0.f);
