@@ -17,6 +17,7 @@ struct b200rt_ctx {
   // wavefront pool (allocated lazily, reused across renders)
   WfBuffers wf{};
   void* wf_block = nullptr;
+  void* wf_shadow_block = nullptr;
   size_t wf_bytes = 0;
   MegaCounters* mega_cnt = nullptr;
   WfCounters* host_cnt = nullptr;  // pinned
@@ -109,6 +110,7 @@ int b200rt_ctx_destroy(b200rt_ctx* c) {
   if (!c) return B200RT_OK;
   cudaSetDevice(c->device);
   if (c->wf_block) cudaFree(c->wf_block);
+  if (c->wf_shadow_block) cudaFree(c->wf_shadow_block);
   if (c->spare_block) cudaFree(c->spare_block);
   if (c->stage_host) cudaFreeHost(c->stage_host);
   if (c->mega_cnt) cudaFree(c->mega_cnt);

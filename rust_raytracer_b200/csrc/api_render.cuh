@@ -2,27 +2,36 @@
 // wavefront pipeline, the megakernel launch, tonemap and the FP32 peak probe.  Included by api.cu.
 #pragma once
 
-static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool) {
-  if (ctx->wf_block && ctx->wf.pool == pool) return B200RT_OK;
-  if (ctx->wf_block) { cudaFree(ctx->wf_block); ctx->wf_block = nullptr; }
+static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool, bool shadow) {
   const size_t P = pool;
-  size_t off = 0;
-  auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
-  size_t o_ray[2], o_st[2];
-  for (int k = 0; k < 2; ++k) { o_ray[k] = take(P * 32); o_st[k] = take(P * 32); }  // the two ray / state sets
-  size_t o_hit = take(P * 16);
-  size_t o_bc = take(4 * WF_NBINS), o_bo = take(4 * (WF_NBINS + 1));
-  size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4), o_cnt = take(sizeof(WfCounters));
-  CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
-  char* b = (char*)ctx->wf_block;
-  ctx->wf_bytes = off;
-  ctx->wf.ray = (float4*)(b + o_ray[0]); ctx->wf.ray_n = (float4*)(b + o_ray[1]);
-  ctx->wf.st = (float4*)(b + o_st[0]); ctx->wf.st_n = (float4*)(b + o_st[1]);
-  ctx->wf.hit = (uint4*)(b + o_hit);
-  ctx->wf.bin_count = (unsigned int*)(b + o_bc); ctx->wf.bin_off = (unsigned int*)(b + o_bo);
-  ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
-  ctx->wf.cnt = (WfCounters*)(b + o_cnt);
-  ctx->wf.pool = pool;
+  if (!(ctx->wf_block && ctx->wf.pool == pool)) {
+    if (ctx->wf_block) { cudaFree(ctx->wf_block); ctx->wf_block = nullptr; }
+    if (ctx->wf_shadow_block) { cudaFree(ctx->wf_shadow_block); ctx->wf_shadow_block = nullptr; }
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
+    size_t o_ray[2], o_st[2];
+    for (int k = 0; k < 2; ++k) { o_ray[k] = take(P * 32); o_st[k] = take(P * 32); }  // the two ray / state sets
+    size_t o_hit = take(P * 16);
+    size_t o_bc = take(4 * WF_NBINS), o_bo = take(4 * (WF_NBINS + 1)), o_cnt = take(sizeof(WfCounters));
+    CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
+    char* b = (char*)ctx->wf_block;
+    ctx->wf_bytes = off;
+    ctx->wf.ray = (float4*)(b + o_ray[0]); ctx->wf.ray_n = (float4*)(b + o_ray[1]);
+    ctx->wf.st = (float4*)(b + o_st[0]); ctx->wf.st_n = (float4*)(b + o_st[1]);
+    ctx->wf.hit = (uint4*)(b + o_hit);
+    ctx->wf.bin_count = (unsigned int*)(b + o_bc); ctx->wf.bin_off = (unsigned int*)(b + o_bo);
+    ctx->wf.cnt = (WfCounters*)(b + o_cnt);
+    ctx->wf.sh_o = ctx->wf.sh_d = ctx->wf.sh_c = nullptr; ctx->wf.sh_seed = nullptr;
+    ctx->wf.pool = pool;
+  }
+  if (shadow && !ctx->wf_shadow_block) {  // shadow requests (52 B per queue position): only the NEE integrator produces them
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
+    size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4);
+    CU_CHECK(ctx, cudaMalloc(&ctx->wf_shadow_block, off));
+    char* b = (char*)ctx->wf_shadow_block;
+    ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
+  }
   return B200RT_OK;
 }
 
@@ -57,10 +66,12 @@ static int env_int(const char* name, int dflt, int lo, int hi) {
 static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap& M, float* accum, b200rt_stats* st) {
   b200rt_ctx* ctx = s->ctx;
   cudaStream_t q = ctx->stream;
-  const unsigned long long cap = 1ull << env_int("B200RT_WF_POOL_LOG2", 24, 12, 26);
+  // queue positions in flight: 144 B each (9.7 GB at 2^26 — HBM is plentiful, and a larger pool means fewer, fuller
+  // launches: 2^21 -> 2^24 -> 2^26 is +17 % -> +4 % on book-2, profiles/r1_experiments.md)
+  const unsigned long long cap = 1ull << env_int("B200RT_WF_POOL_LOG2", 26, 12, 28);
   unsigned long long want = (M.total + 31ull) & ~31ull;
   unsigned int pool = (unsigned int)(want < cap ? want : cap);
-  int rc = wf_ensure_pool(ctx, pool);
+  int rc = wf_ensure_pool(ctx, pool, P.integrator == B200RT_INTEGRATOR_NEE);
   if (rc) return rc;
   WfBuffers B = ctx->wf;
   {  // bin = 1 + umulhi(prim, bin_mul) maps [0, n_prims) onto bins 1 .. WF_NBINS - 1 (identity for tiny scenes)

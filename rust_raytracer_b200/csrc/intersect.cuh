@@ -251,21 +251,21 @@ DEV uint32_t pop_next(TStack& stack, int& sp, float t_best32) {
 #endif
 
 // Per-ray constants of the node test.  t = plane * inv - o * inv is one FFMA per plane; the near / far plane of
-// every axis is chosen by ADDRESS (the node stores lo.x|lo.y|lo.z|hi.x|hi.y|hi.z as six float4 rows, so the
-// direction sign picks row a or row a + 3), which removes the per-child min/max pairs.  The rounding error of
+// every axis is chosen by ADDRESS (the node stores lo.x|hi.x|lo.y|hi.y|lo.z|hi.z as six float4 rows, so the
+// direction's sign bit picks row 2a or row 2a + 1), which removes the per-child min/max pairs.  The rounding error of
 // o * inv (the only term the fused form adds over (plane - o) * inv) is covered so the
 // test stays conservative through one per-ray slack term on the comparison (2 * max|o * inv| * 2^-22).
 struct RayT {
   float3 inv, oi;  // 1/d, o/d
   float slack;     // 2 * max_axis |o/d| * 2^-22: absolute error budget of (near - far) from rounding o/d
-  int nx, ny, nz;  // byte offset of the near-plane row of each axis: 0 or 48
+  const float4* nodes;   // S.nodes, laundered through a register pair (see node_step)
 };
-DEV RayT make_rayt(const RayF& rf) {
+DEV RayT make_rayt(const DevScene& S, const RayF& rf) {
   RayT t;
+  asm("mov.b64 %0, %1;" : "=l"(t.nodes) : "l"(S.nodes));
   t.inv = rf.inv;
   t.oi = rf.o * rf.inv;
   t.slack = 4.7683716e-7f * fmaxf(fabsf(t.oi.x), fmaxf(fabsf(t.oi.y), fabsf(t.oi.z)));  // 2 * 2^-22
-  t.nx = rf.inv.x < 0.f ? 48 : 0; t.ny = rf.inv.y < 0.f ? 48 : 0; t.nz = rf.inv.z < 0.f ? 48 : 0;
   return t;
 }
 
@@ -275,11 +275,18 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32
   DBG_INC(1);
   float tn[4];
 #if B200RT_NODE_FAST
-  const char* nb = reinterpret_cast<const char*>(S.nodes) + ((size_t)cur << 7);
-  const float4 nxv = __ldg(reinterpret_cast<const float4*>(nb + rt.nx)), fxv = __ldg(reinterpret_cast<const float4*>(nb + 48 - rt.nx));
-  const float4 nyv = __ldg(reinterpret_cast<const float4*>(nb + 16 + rt.ny)), fyv = __ldg(reinterpret_cast<const float4*>(nb + 64 - rt.ny));
-  const float4 nzv = __ldg(reinterpret_cast<const float4*>(nb + 32 + rt.nz)), fzv = __ldg(reinterpret_cast<const float4*>(nb + 80 - rt.nz));
-  const int4 ref = __ldg(reinterpret_cast<const int4*>(nb + 96));
+  // 32-bit row indices off a base pointer the compiler cannot see through: the near row of an axis is
+  // c8 + (sign bit of 1/d) (one LEA.HI), the far row its xor 1, the address one IMAD.WIDE (FMA pipe) with the axis
+  // in the load's immediate offset — instead of select + or + add + add-with-carry per row against a uniform base.
+  const uint32_t c8 = cur << 3;
+  uint32_t sx, sy, sz;  // opaque sign bits: keeps the far index an independent 32-bit sum (one IADD3 + one IMAD.WIDE)
+  asm("shr.u32 %0, %1, 31;" : "=r"(sx) : "r"(__float_as_uint(rt.inv.x)));
+  asm("shr.u32 %0, %1, 31;" : "=r"(sy) : "r"(__float_as_uint(rt.inv.y)));
+  asm("shr.u32 %0, %1, 31;" : "=r"(sz) : "r"(__float_as_uint(rt.inv.z)));
+  const float4 nxv = __ldg(rt.nodes + (c8 + sx)), fxv = __ldg(rt.nodes + (c8 + 1u - sx));
+  const float4 nyv = __ldg(rt.nodes + (c8 + 2u + sy)), fyv = __ldg(rt.nodes + (c8 + 3u - sy));
+  const float4 nzv = __ldg(rt.nodes + (c8 + 4u + sz)), fzv = __ldg(rt.nodes + (c8 + 5u - sz));
+  const int4 ref = __ldg(reinterpret_cast<const int4*>(rt.nodes + c8) + 6);
   uint32_t rr[4] = {(uint32_t)ref.x, (uint32_t)ref.y, (uint32_t)ref.z, (uint32_t)ref.w};
   const float ax[4] = {nxv.x, nxv.y, nxv.z, nxv.w}, ay[4] = {nyv.x, nyv.y, nyv.z, nyv.w}, az[4] = {nzv.x, nzv.y, nzv.z, nzv.w};
   const float bx[4] = {fxv.x, fxv.y, fxv.z, fxv.w}, by[4] = {fyv.x, fyv.y, fyv.z, fyv.w}, bz[4] = {fzv.x, fzv.y, fzv.z, fzv.w};
@@ -291,8 +298,8 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32
   }
 #else
   const float4* nd = S.nodes + 8 * (size_t)cur;
-  const float4 lox = __ldg(nd + 0), loy = __ldg(nd + 1), loz = __ldg(nd + 2);
-  const float4 hix = __ldg(nd + 3), hiy = __ldg(nd + 4), hiz = __ldg(nd + 5);
+  const float4 lox = __ldg(nd + 0), loy = __ldg(nd + 2), loz = __ldg(nd + 4);
+  const float4 hix = __ldg(nd + 1), hiy = __ldg(nd + 3), hiz = __ldg(nd + 5);
   const int4 ref = __ldg((const int4*)(nd + 6));
   uint32_t rr[4] = {(uint32_t)ref.x, (uint32_t)ref.y, (uint32_t)ref.z, (uint32_t)ref.w};
   const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
@@ -339,7 +346,7 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
   h.t = (double)ray.tmax; h.prim = -1; h.aux = 0;
   float t_best32 = ray.tmax;
   const RayF rf = make_rayf(ray);
-  const RayT rt = make_rayt(rf);
+  const RayT rt = make_rayt(S, rf);
   DBG_INC(0);
   TStack stack;
 #if B200RT_SSTACK > 0

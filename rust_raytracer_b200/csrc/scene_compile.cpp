@@ -138,7 +138,8 @@ int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out) {
     else refs[i] = collapse(bb, kids[i], out);
   }
   size_t at = (size_t)my * 32;
-  for (int a = 0; a < 3; ++a) { put4(out, at + 4 * a, lo[a][0], lo[a][1], lo[a][2], lo[a][3]); put4(out, at + 12 + 4 * a, hi[a][0], hi[a][1], hi[a][2], hi[a][3]); }
+  // rows: lo.x hi.x lo.y hi.y lo.z hi.z refs (pad) — the near plane of an axis is row 2a + sign(d_a), the far one its xor 1
+  for (int a = 0; a < 3; ++a) { put4(out, at + 8 * a, lo[a][0], lo[a][1], lo[a][2], lo[a][3]); put4(out, at + 8 * a + 4, hi[a][0], hi[a][1], hi[a][2], hi[a][3]); }
   put4(out, at + 24, ibits(refs[0]), ibits(refs[1]), ibits(refs[2]), ibits(refs[3]));
   return my;
 }
