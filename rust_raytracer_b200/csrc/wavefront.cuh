@@ -21,6 +21,18 @@
 // neighbouring primitives, with similar traversal cost (fog-born rays together, ground-box rays together, ...).
 // A path that was predicted to go on but ended in shade (metal absorption, zero pdf, depth budget) leaves a dead
 // record (zero direction) that extend skips.
+// The queue streams are touched once per iteration and never fit L2 (GBs): streaming (evict-first) loads and
+// stores keep them from displacing the scene tables there.
+#ifndef B200RT_WF_STREAMING
+#define B200RT_WF_STREAMING 1
+#endif
+#if B200RT_WF_STREAMING
+#define WF_LD(p) __ldcs(p)
+#define WF_ST(p, v) __stcs(p, v)
+#else
+#define WF_LD(p) (*(p))
+#define WF_ST(p, v) (*(p) = (v))
+#endif
 #define WF_POS_BYTES 144  // device bytes per queue position: 2 sets x (ray 32 + state 32) + hit 16
 #ifndef WF_NBINS
 #define WF_NBINS 256
@@ -84,10 +96,10 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P,
     const Ray r = camera_ray(P, pixel, sample);
     float4* ray = B.ray + 2 * (size_t)(off + i);
     float4* st = B.st + 2 * (size_t)(off + i);
-    ray[0] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-    ray[1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed));
-    st[0] = make_float4(1.f, 1.f, 1.f, -1.f);
-    st[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), 0.f, 0.f);
+    WF_ST(ray + 0, make_float4(r.o.x, r.o.y, r.o.z, r.time));
+    WF_ST(ray + 1, make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed)));
+    WF_ST(st + 0, make_float4(1.f, 1.f, 1.f, -1.f));
+    WF_ST(st + 1, make_float4(__uint_as_float(pixel), __uint_as_float(sample), 0.f, 0.f));
   }
 }
 
@@ -155,7 +167,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     h.t = 0.; h.prim = WF_PRIM_DEAD; h.aux = 0;
     bool dead = false;
     if (active) {
-      const float4 o = ray[0], d = ray[1];
+      const float4 o = WF_LD(ray + 0), d = WF_LD(ray + 1);
       dead = d.x == 0.f && d.y == 0.f && d.z == 0.f;
       if (!dead) {
         Ray r;
@@ -180,7 +192,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     if (n_dead && lane == 0) atomicAdd(&B.cnt->dead_rays, n_dead);
     if (active) {
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
-      B.hit[i] = make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), wf_pack_prim(h.prim, h.aux), goes_on ? rank : WF_NO_RANK);
+      WF_ST(B.hit + i, make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), wf_pack_prim(h.prim, h.aux), goes_on ? rank : WF_NO_RANK));
     }
   }
 }
@@ -208,7 +220,7 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   auto load_rec = [&](unsigned int src) {
     const float4* r = B.ray + 2 * (size_t)src;
     const float4* t = B.st + 2 * (size_t)src;
-    n_o = r[0]; n_d = r[1]; n_sa = t[0]; n_sb = t[1]; n_hh = B.hit[src];
+    n_o = WF_LD(r + 0); n_d = WF_LD(r + 1); n_sa = WF_LD(t + 0); n_sb = WF_LD(t + 1); n_hh = WF_LD(B.hit + src);
   };
 #ifndef B200RT_SHADE_PREFETCH  // measured: with streaming reads the explicit prefetch only costs registers (18.3 ms vs 17.2 ms at 96 regs)
 #define B200RT_SHADE_PREFETCH 0
@@ -253,13 +265,13 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
       float4* out = B.ray_n + dst;
       if (cont) {
         float4* out_s = B.st_n + dst;
-        out[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
-        out[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed));
-        out_s[0] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b);
-        out_s[1] = make_float4(__uint_as_float(ps.pixel), __uint_as_float(ps.sample), __uint_as_float((unsigned int)ps.bounce), 0.f);
+        WF_ST(out + 0, make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time));
+        WF_ST(out + 1, make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ray.mseed)));
+        WF_ST(out_s + 0, make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_pdf_b));
+        WF_ST(out_s + 1, make_float4(__uint_as_float(ps.pixel), __uint_as_float(ps.sample), __uint_as_float((unsigned int)ps.bounce), 0.f));
       } else {
-        out[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-        out[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        WF_ST(out + 0, make_float4(0.f, 0.f, 0.f, 0.f));
+        WF_ST(out + 1, make_float4(0.f, 0.f, 0.f, 0.f));
       }
     }
     if (INTEG != B200RT_INTEGRATOR_NEE) continue;  // only the NEE integrator produces shadow requests
