@@ -14,7 +14,7 @@
 #include "kernels.cuh"
 
 // The NEXT queue is ordered by WHERE each ray starts: bin = the hit primitive's index in BVH leaf order (spatially
-// coherent) scaled to WF_NBINS - 1 bins.  Extend knows the bin of every ray that will go on (hit, and the material
+// coherent) scaled to n_bins - 1 bins.  Extend knows the bin of every ray that will go on (hit, and the material
 // scatters) and takes its rank inside the bin with one warp-aggregated atomic; a one-thread kernel turns the bin
 // sizes into offsets; shade then walks the current queue IN ORDER (pure streaming reads of whole records) and
 // writes each surviving path at offset[bin] + rank of the next set.  Extend warps therefore receive rays that left
@@ -34,9 +34,9 @@
 #define WF_ST(p, v) (*(p) = (v))
 #endif
 #define WF_POS_BYTES 144  // device bytes per queue position: 2 sets x (ray 32 + state 32) + hit 16
-#ifndef WF_NBINS
-#define WF_NBINS 256
-#endif
+#define WF_MAX_BINS 16384    // capacity of the bin tables; the number of bins in use is WfBuffers::n_bins
+#define WF_SMEM_BINS 2048    // shade keeps the offsets in shared memory up to this many bins
+#define WF_NO_BIN 0xffffffffu
 
 struct WfCounters {
   unsigned long long next_path;     // next path id to generate
@@ -56,9 +56,10 @@ struct WfBuffers {
   float4* st;     // path state, current set: 2 float4 per queue position
   float4* st_n;
   uint4* hit;     // hit of the current set, written by extend: 1 uint4 per queue position
-  unsigned int* bin_count;  // WF_NBINS: continuing rays per bin (filled by extend)
-  unsigned int* bin_off;    // WF_NBINS + 1: start of every bin in the next set
+  unsigned int* bin_count;  // n_bins: continuing rays per bin (filled by extend)
+  unsigned int* bin_off;    // n_bins + 1: start of every bin in the next set
   unsigned int bin_mul;     // bin = 1 + umulhi(prim, bin_mul)
+  unsigned int n_bins;      // multiple of 1024 (the control kernels run one 1024-thread block), <= WF_MAX_BINS
   float4* sh_o; float4* sh_d; float4* sh_c; unsigned int* sh_seed;
   WfCounters* cnt;
   unsigned int pool;
@@ -103,9 +104,9 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P,
   }
 }
 
-// One thread turns the counters over between generate and extend (no host round trip inside an iteration).
-__global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, WF_NBINS>>>
-  B.bin_count[threadIdx.x] = 0;
+// One block turns the counters over between generate and extend (no host round trip inside an iteration).
+__global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, 1024>>>
+  for (unsigned int k = threadIdx.x; k < B.n_bins; k += blockDim.x) B.bin_count[k] = 0;
   if (threadIdx.x != 0) return;
   WfCounters* c = B.cnt;
   const unsigned int n_new = wf_new_paths(c, M, B.pool);
@@ -118,22 +119,26 @@ __global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, WF_NBINS>>>
   c->extend_rays += c->n_ext;
 }
 // after extend: bin sizes -> offsets in the next set; their total is the number of records shade will write.
-// One block of WF_NBINS threads (Hillis-Steele scan in shared memory).
-__global__ void k_wf_control_shade(WfBuffers B) {
-  __shared__ unsigned int sc[2][WF_NBINS];
+// One block of 1024 threads: every thread owns n_bins / 1024 consecutive bins, the per-thread sums are scanned
+// in shared memory (Hillis-Steele).
+__global__ void k_wf_control_shade(WfBuffers B) {  // <<<1, 1024>>>
+  __shared__ unsigned int sc[2][1024];
   const int t = threadIdx.x;
-  const unsigned int mine = B.bin_count[t];
+  const unsigned int per = B.n_bins >> 10, first = (unsigned int)t * per;
+  unsigned int mine = 0;
+  for (unsigned int k = 0; k < per; ++k) mine += B.bin_count[first + k];
   sc[0][t] = mine;
   __syncthreads();
   int cur = 0;
-  for (int d = 1; d < WF_NBINS; d <<= 1) {
+  for (int d = 1; d < 1024; d <<= 1) {
     sc[cur ^ 1][t] = sc[cur][t] + (t >= d ? sc[cur][t - d] : 0u);
     cur ^= 1;
     __syncthreads();
   }
   const unsigned int incl = sc[cur][t];
-  B.bin_off[t] = incl - mine;
-  if (t == WF_NBINS - 1) { B.bin_off[WF_NBINS] = incl; B.cnt->n_ext_next = incl; }
+  unsigned int run = incl - mine;
+  for (unsigned int k = 0; k < per; ++k) { B.bin_off[first + k] = run; run += B.bin_count[first + k]; }
+  if (t == 1023) { B.bin_off[B.n_bins] = incl; B.cnt->n_ext_next = incl; }
 }
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
 
@@ -162,7 +167,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     const unsigned int i = base + lane;
     const bool active = i < n;
     const float4* ray = B.ray + 2 * (size_t)i;
-    unsigned int bin = (unsigned)WF_NBINS;  // WF_NBINS = "does not go on"
+    unsigned int bin = WF_NO_BIN;  // "does not go on"
     HitRaw h;
     h.t = 0.; h.prim = WF_PRIM_DEAD; h.aux = 0;
     bool dead = false;
@@ -184,7 +189,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     // instruction, so the warp pays one atomic round trip whatever the number of bins
     const unsigned peers = __match_any_sync(0xffffffffu, bin);
     const int leader = __ffs((int)peers) - 1;
-    const bool goes_on = bin != (unsigned)WF_NBINS;
+    const bool goes_on = bin != WF_NO_BIN;
     unsigned int rank = 0;
     if (goes_on && (int)lane == leader) rank = atomicAdd(&B.bin_count[bin], (unsigned)__popc(peers));
     rank = __shfl_sync(0xffffffffu, rank, leader) + __popc(peers & ((1u << lane) - 1u));
@@ -208,8 +213,9 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
 template <int INTEG>
 __global__ void __launch_bounds__(128, INTEG == B200RT_INTEGRATOR_PATH ? B200RT_SHADE_MINBLOCKS_PATH : B200RT_SHADE_MINBLOCKS)
 k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
-  __shared__ unsigned int s_off[WF_NBINS + 1];
-  for (int k = threadIdx.x; k <= WF_NBINS; k += blockDim.x) s_off[k] = B.bin_off[k];
+  __shared__ unsigned int s_off[WF_SMEM_BINS + 1];
+  const bool off_in_smem = B.n_bins <= WF_SMEM_BINS;
+  if (off_in_smem) for (unsigned int k = threadIdx.x; k <= B.n_bins; k += blockDim.x) s_off[k] = B.bin_off[k];
   __syncthreads();
   const unsigned int n_ext = B.cnt->n_ext;
   const unsigned int n_work = (n_ext + 31u) & ~31u;  // whole warps stay in the loop (warp-aggregated appends below)
@@ -261,7 +267,8 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
       accum_add(accum, ps.pixel, ps.radiance);
     }
     if (active && rank != WF_NO_RANK) {  // the place extend reserved in the next set: the new ray, or a dead record
-      const size_t dst = 2 * (size_t)(s_off[1u + __umulhi((unsigned int)hprim, B.bin_mul)] + rank);  // the bin extend ranked it in
+      const unsigned int bin = 1u + __umulhi((unsigned int)hprim, B.bin_mul);  // the bin extend ranked it in
+      const size_t dst = 2 * (size_t)((off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank);
       float4* out = B.ray_n + dst;
       if (cont) {
         float4* out_s = B.st_n + dst;
