@@ -26,15 +26,16 @@ SPP_PER_STEP = 128          # per GPU and step; the full job is 10,000 spp (Mpat
 FULL_JOB_SPP = 10000
 METRIC = "Mpaths/s (device-timed) on book-2 final scene"
 UNIT = "Mpaths/s"
-# extend kernel, per ray: ray_o 16 + ray_d 16 read (the medium seed rides in ray_d.w); hit 16 + bin queue index 4 written
-EXTEND_BYTES_PER_RAY = 52
+# extend kernel, per ray: the 32-byte ray stream read (o, time | d, medium seed) + the 16-byte hit written (t as f64, prim, rank)
+EXTEND_BYTES_PER_RAY = 48
 SEGMENT_BYTES_PIPELINE = 128  # ray 32 + hit 16 + state 16, written once and read once
-# ncu --set full, k_wf_extend, full-pool launch (16,777,216 rays): dram__bytes_read.sum 1.661 GB + dram__bytes_write.sum
-# 0.820 GB (profiles/r1_final_extend_shade_full.txt) -> DRAM bytes per ray; issue/lane figures from the same capture
-EXTEND_DRAM_BYTES_PER_RAY_NCU = (1.660982e9 + 820.366592e6) / 16777216
-EXTEND_NCU = {"issue_active_pct": 73.0, "alu_pipe_pct": 51.9, "fma_pipe_pct": 22.8, "fp64_pipe_pct": 7.1, "lanes_per_instruction": 14.2,
-              "l1_hit_pct": 78.5, "l2_hit_pct": 70.0, "dram_pct_of_peak": 12.9, "shade_issue_active_pct": 48.9, "shade_dram_pct_of_peak": 37.2,
-              "source": "profiles/r1_final_extend_shade_full.txt"}
+# ncu --set full, k_wf_extend, launch of 18,292,061 rays: dram__bytes_read.sum 0.5996 GB + dram__bytes_write.sum 0.3108 GB
+# (profiles/r1_final2_extend_shade_full.txt) -> DRAM bytes per ray; issue/lane figures from the same capture
+EXTEND_DRAM_BYTES_PER_RAY_NCU = (0.599593e9 + 310.840576e6) / 18292061
+EXTEND_NCU = {"issue_active_pct": 76.4, "alu_pipe_pct": 48.6, "fma_pipe_pct": 27.3, "fp64_pipe_pct": 6.3, "lanes_per_instruction": 14.4,
+              "warp_instructions_per_32_rays": 3144, "l1_hit_pct": 86.3, "l2_hit_pct": 73.6, "dram_pct_of_peak": 5.4,
+              "shade_issue_active_pct": 50.8, "shade_dram_pct_of_peak": 36.0, "shade_dram_bytes_per_ray": 125.2,
+              "source": "profiles/r1_final2_extend_shade_full.txt"}
 
 
 def earth_image():
@@ -281,7 +282,7 @@ def main():
             "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (achieved / peaks["hbm_gbs"]) if achieved else None,
             "peak_source": "MEASURED_PEAKS.json (%s)" % peak_kind,
             "traffic": EXTEND_DRAM_BYTES_PER_RAY_NCU * rays_per_launch if args.pipeline == "wavefront" else None,
-            "traffic_note": "ncu dram bytes per ray of a full-pool launch (%.0f B: 64-byte fills at the 96-byte record stride + local-memory stack/spill traffic) x rays of the average launch" % EXTEND_DRAM_BYTES_PER_RAY_NCU,
+            "traffic_note": "ncu dram bytes per ray of one launch (%.1f B against %d algorithmic: the ray stream is read whole, the rest is local-memory stack traffic) x rays of the average launch" % (EXTEND_DRAM_BYTES_PER_RAY_NCU, EXTEND_BYTES_PER_RAY),
             "bytes_per_ray": EXTEND_BYTES_PER_RAY, "rays_per_launch": rays_per_launch, "launches": n_ext_launches,
             "avg_launch_ms": ext_ms / n_ext_launches, "kernel_share_of_step": ext_ms / max(stats["ms_total"], 1e-9),
             "note": "BVH traversal is instruction-issue bound under divergence, not HBM bound (scene is L2-resident): see issue, fp32 and DESIGN.md",
@@ -304,7 +305,7 @@ def main():
             "config": {"workload": "book-2 final scene 800x800 (BASELINE.json configs[3]): 1409 primitives incl. 400 boxes, 1000 instanced spheres, moving sphere, 2 constant media, Perlin + earthmap textures",
                        "spp_per_step_per_gpu": spp, "full_job_spp": FULL_JOB_SPP, "max_depth": 50, "integrator": "path", "pipeline": args.pipeline,
                        "sharding": "spp ranges per rank + NCCL sum-reduce of the accumulation buffer per step",
-                       "l2": "256 MB write between timed steps; the wavefront queues (2^24 path slots x 196 B of ray/state/hit payload = 3.3 GB, plus bin index space) exceed L2"},
+                       "l2": "256 MB write between timed steps; the wavefront queues (2^26 positions x 144 B of ray/state/hit streams = 9.7 GB) exceed L2"},
             "mrays_per_s": mrays, "rays_per_path": (ext + shd) / paths,
             "stage_ms_per_step": {k: stats[k] / args.steps for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total")},
             "wavefront_iterations_per_step": stats["wavefront_iterations"] / args.steps,
