@@ -273,6 +273,9 @@ int b200rt_render(b200rt_scene* scene, const b200rt_camera* cam, const b200rt_pa
 int b200rt_tonemap_rgb8(b200rt_ctx* ctx, const float* accum_host, int32_t width, int32_t height, uint8_t* rgb_out);
 int b200rt_tonemap_rgb8_device(b200rt_ctx* ctx, const float* accum_dev, int32_t width, int32_t height, uint8_t* rgb_dev);
 
+/* RgbImage::save (main.rs:54: `result.save("output/test.png")`): 8-bit RGB PNG, host only, no dependency. */
+int b200rt_write_png(const char* path, const uint8_t* rgb8, int32_t width, int32_t height);
+
 /* Camera::new (camera.rs:24-55), computed in f64 then rounded. */
 int b200rt_camera_make(const double look_from[3], const double look_at[3], const double vup[3], double vfov_deg,
                        double aspect, double aperture, double focus_dist, double time0, double time1,

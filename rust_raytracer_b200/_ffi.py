@@ -99,6 +99,7 @@ PROTOTYPES = {
     "b200rt_render": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, C.POINTER(Stats)]),
     "b200rt_tonemap_rgb8": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),
     "b200rt_tonemap_rgb8_device": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),
+    "b200rt_write_png": (C.c_int, [C.c_char_p, VP, C.c_int32, C.c_int32]),
     "b200rt_camera_make": (C.c_int, [D3, D3, D3, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(Camera)]),
     "b200rt_measure_fp32_peak": (C.c_int, [VP, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "b200rt_builder_create": (C.c_int, [C.POINTER(VP)]),

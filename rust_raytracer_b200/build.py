@@ -19,7 +19,8 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-shared", "-Xcompiler", "-fPIC,-O3,-Wall", "-Xptxas", "-v", "--use_fast_math=false",
 ]
-SOURCES = ["api.cu", "builder.cpp", "loaders.cpp", "scenes.cpp", "scene_compile.cpp"]
+SOURCES = ["api.cu", "builder.cpp", "loaders.cpp", "scenes.cpp", "scene_compile.cpp", "png_out.cpp"]
+CLI = os.path.join(HERE, "b200rt_render")  # the reference's `main` over the C ABI (csrc/cli_main.cpp)
 
 
 def _newer(target, deps):
@@ -37,6 +38,8 @@ def _deps(directory, extra=()):
 def build_library(force=False, verbose=False):
     header = os.path.join(ROOT, "include", "b200rt.h")
     if not force and not _newer(LIB, _deps(CSRC, [header])):
+        if not os.path.exists(CLI):
+            build_cli()
         return LIB
     nvcc = os.environ.get("NVCC", "nvcc")
     flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"]
@@ -49,7 +52,19 @@ def build_library(force=False, verbose=False):
         sys.stderr.write(res.stdout)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed (see %s)" % log)
+    build_cli()
     return LIB
+
+
+def build_cli():
+    """g++ build of the command-line driver against the in-tree library (rpath $ORIGIN)."""
+    src = os.path.join(CSRC, "cli_main.cpp")
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-pthread", "-o", CLI, src, "-L" + HERE, "-lb200rt", "-Wl,-rpath,$ORIGIN"]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout)
+        raise RuntimeError("g++ failed for b200rt_render")
+    return CLI
 
 
 def build_variant(name, defines=(), out_dir=None):

@@ -1,0 +1,182 @@
+// cli_main.cpp — the reference's `main` (main.rs:49-72) over the C ABI: pick a scene, render, save a PNG, print the
+// timing lines in the reference's form.  Host C++ only; every GPU call goes through include/b200rt.h.
+//
+//   b200rt_render --scene book2|book1|cornell_book3|cornell_ref|mesh|<file.json>|<file.yaml> [--obj path.obj]
+//                 [--earth earth.ppm] [--width W] [--height H] [--spp N] [--depth D] [--integrator path|mixture|nee]
+//                 [--seed S] [--gpus G] [--out output/test.png]
+//
+// --gpus G shards the samples over G devices (one context and one host thread per device, the reference's own
+// decomposition is row bands over a thread pool, camera.rs:74-111) and sums the accumulation images on the host.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/b200rt.h"
+
+namespace {
+
+bool ends_with(const std::string& s, const char* suf) {
+  const size_t n = std::strlen(suf);
+  return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+
+bool read_file(const std::string& path, std::string& out) {
+  std::ifstream f(path, std::ios::binary);
+  if (!f) return false;
+  std::ostringstream ss;
+  ss << f.rdbuf();
+  out = ss.str();
+  return true;
+}
+
+// binary PPM (P6, maxval 255): the decoded earthmap for book-2 (there is no JPEG decoder on this side of the ABI)
+bool read_ppm(const std::string& path, std::vector<uint8_t>& rgb, int& w, int& h) {
+  std::string s;
+  if (!read_file(path, s) || s.size() < 11 || s[0] != 'P' || s[1] != '6') return false;
+  size_t p = 2;
+  int vals[3], k = 0;
+  while (k < 3 && p < s.size()) {
+    while (p < s.size() && (s[p] == ' ' || s[p] == '\n' || s[p] == '\r' || s[p] == '\t')) ++p;
+    if (p < s.size() && s[p] == '#') { while (p < s.size() && s[p] != '\n') ++p; continue; }
+    int v = 0, d = 0;
+    while (p < s.size() && s[p] >= '0' && s[p] <= '9') { v = v * 10 + (s[p] - '0'); ++p; ++d; }
+    if (!d) return false;
+    vals[k++] = v;
+  }
+  if (k < 3 || vals[2] != 255) return false;
+  ++p;  // the single whitespace byte after maxval
+  w = vals[0]; h = vals[1];
+  const size_t n = (size_t)w * h * 3;
+  if (w <= 0 || h <= 0 || s.size() < p + n) return false;
+  rgb.assign(s.begin() + p, s.begin() + p + n);
+  return true;
+}
+
+struct Shard {
+  int device = 0, spp_begin = 0, spp_count = 0, rc = 0;
+  std::string err;
+  std::vector<float> accum;
+  b200rt_stats st{};
+};
+
+void render_shard(const b200rt_scene_desc* desc, const b200rt_camera* cam, b200rt_params params, Shard* sh) {
+  b200rt_ctx* ctx = nullptr;
+  sh->rc = b200rt_ctx_create(sh->device, &ctx);
+  if (sh->rc) { sh->err = "no CUDA device " + std::to_string(sh->device) + " (there is no CPU fallback)"; return; }
+  b200rt_scene* scene = nullptr;
+  sh->rc = b200rt_scene_create(ctx, desc, &scene);
+  if (!sh->rc) {
+    params.spp_begin = sh->spp_begin; params.spp_count = sh->spp_count;
+    sh->accum.assign((size_t)params.width * params.height * 4, 0.f);
+    sh->rc = b200rt_render(scene, cam, &params, sh->accum.data(), &sh->st);
+  }
+  if (sh->rc) sh->err = b200rt_last_error(ctx);
+  if (scene) b200rt_scene_destroy(scene);
+  b200rt_ctx_destroy(ctx);
+}
+
+double seconds_since(std::chrono::steady_clock::time_point t0) {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  std::string scene = "book2", obj, earth, out = "output/test.png", integ = "path";
+  int width = 0, height = 0, spp = 64, depth = 50, gpus = 1;
+  unsigned long long seed = 1;
+  for (int i = 1; i < argc; ++i) {
+    const std::string a = argv[i];
+    auto next = [&](const char* what) -> const char* {
+      if (i + 1 >= argc) { std::fprintf(stderr, "missing value for %s\n", what); std::exit(2); }
+      return argv[++i];
+    };
+    if (a == "--scene") scene = next("--scene");
+    else if (a == "--obj") obj = next("--obj");
+    else if (a == "--earth") earth = next("--earth");
+    else if (a == "--out") out = next("--out");
+    else if (a == "--integrator") integ = next("--integrator");
+    else if (a == "--width") width = std::atoi(next("--width"));
+    else if (a == "--height") height = std::atoi(next("--height"));
+    else if (a == "--spp") spp = std::atoi(next("--spp"));
+    else if (a == "--depth") depth = std::atoi(next("--depth"));
+    else if (a == "--gpus") gpus = std::atoi(next("--gpus"));
+    else if (a == "--seed") seed = std::strtoull(next("--seed"), nullptr, 10);
+    else { std::fprintf(stderr, "unknown argument %s\n", a.c_str()); return 2; }
+  }
+  if (spp < 1 || gpus < 1 || depth < 0) { std::fprintf(stderr, "spp, gpus must be >= 1, depth >= 0\n"); return 2; }
+
+  const auto t_start = std::chrono::steady_clock::now();
+  b200rt_builder* b = nullptr;
+  if (b200rt_builder_create(&b)) { std::fprintf(stderr, "builder_create failed\n"); return 1; }
+  b200rt_camera cam{};
+  b200rt_params params{};
+  int rc;
+  const bool from_file = ends_with(scene, ".json") || ends_with(scene, ".yaml") || ends_with(scene, ".yml");
+  if (from_file) {
+    std::string text;
+    if (!read_file(scene, text)) { std::fprintf(stderr, "cannot read %s\n", scene.c_str()); return 1; }
+    rc = ends_with(scene, ".json") ? b200rt_builder_load_json(b, text.data(), text.size(), &cam)
+                                   : b200rt_builder_load_yaml(b, text.data(), text.size(), &cam);
+    params.width = 400; params.height = 400; params.max_depth = 50; params.t_min = 0.001f;  // photon_mapper.rs:333-339
+    params.integrator = B200RT_INTEGRATOR_PATH; params.pipeline = B200RT_PIPELINE_WAVEFRONT;
+  } else {
+    std::vector<uint8_t> rgb;
+    int ew = 0, eh = 0;
+    if (!earth.empty() && !read_ppm(earth, rgb, ew, eh)) { std::fprintf(stderr, "cannot read PPM %s\n", earth.c_str()); return 1; }
+    const double aspect = (width > 0 && height > 0) ? (double)width / height : 0.0;
+    rc = b200rt_builder_make_scene(b, scene.c_str(), seed, obj.empty() ? nullptr : obj.c_str(), rgb.empty() ? nullptr : rgb.data(), ew, eh,
+                                   aspect, &cam, &params);
+  }
+  if (rc) { std::fprintf(stderr, "scene: %s\n", b200rt_builder_error(b)); return 1; }
+  if (width > 0) params.width = width;
+  if (height > 0) params.height = height;
+  params.max_depth = depth; params.seed = seed;
+  if (integ == "path") params.integrator = B200RT_INTEGRATOR_PATH;
+  else if (integ == "mixture") params.integrator = B200RT_INTEGRATOR_MIXTURE;
+  else if (integ == "nee") params.integrator = B200RT_INTEGRATOR_NEE;
+  else { std::fprintf(stderr, "unknown integrator %s\n", integ.c_str()); return 2; }
+  b200rt_scene_desc desc{};
+  if (b200rt_builder_finish(b, &desc)) { std::fprintf(stderr, "scene: %s\n", b200rt_builder_error(b)); return 1; }
+
+  const auto t_rt = std::chrono::steady_clock::now();
+  if (gpus > spp) gpus = spp;
+  std::vector<Shard> shards(gpus);
+  std::vector<std::thread> threads;
+  for (int g = 0; g < gpus; ++g) {
+    shards[g].device = g;
+    shards[g].spp_begin = (int)((long long)spp * g / gpus);
+    shards[g].spp_count = (int)((long long)spp * (g + 1) / gpus) - shards[g].spp_begin;
+    threads.emplace_back(render_shard, &desc, &cam, params, &shards[g]);
+  }
+  for (auto& t : threads) t.join();
+  unsigned long long rays = 0;
+  for (int g = 0; g < gpus; ++g) {
+    if (shards[g].rc) { std::fprintf(stderr, "render on device %d: %s\n", g, shards[g].err.c_str()); return 1; }
+    rays += shards[g].st.extend_rays + shards[g].st.shadow_rays;
+    if (g) for (size_t k = 0; k < shards[0].accum.size(); ++k) shards[0].accum[k] += shards[g].accum[k];
+  }
+  // tonemap on device 0 (vec3.rs:223-231) and save
+  std::vector<uint8_t> rgb8((size_t)params.width * params.height * 3);
+  b200rt_ctx* ctx = nullptr;
+  if (b200rt_ctx_create(0, &ctx)) { std::fprintf(stderr, "no CUDA device\n"); return 1; }
+  rc = b200rt_tonemap_rgb8(ctx, shards[0].accum.data(), params.width, params.height, rgb8.data());
+  if (rc) { std::fprintf(stderr, "tonemap: %s\n", b200rt_last_error(ctx)); return 1; }
+  b200rt_ctx_destroy(ctx);
+  b200rt_builder_destroy(b);
+  const double rt_s = seconds_since(t_rt);
+  rc = b200rt_write_png(out.c_str(), rgb8.data(), params.width, params.height);
+  if (rc) { std::fprintf(stderr, "cannot write %s\n", out.c_str()); return 1; }
+  // main.rs:56-71 prints "Total / SPPM / RT"; there is no photon pass on this path
+  std::printf("Total: %.3fs\n\tSPPM: %.3fs\n\tRT: %.3fs\n", seconds_since(t_start), 0.0, rt_s);
+  const double paths = (double)params.width * params.height * spp;
+  std::printf("%dx%d, %d spp on %d GPU(s): %.1f Mpaths/s, %.1f Mrays/s (host-timed, scene upload included) -> %s\n", params.width, params.height, spp,
+              gpus, paths / rt_s / 1e6, (double)rays / rt_s / 1e6, out.c_str());
+  return 0;
+}

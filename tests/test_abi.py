@@ -53,3 +53,32 @@ def test_package_does_not_touch_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")) and f != "build.py":
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "liboracle" not in text and "oracle_ffi" not in text and "oracle/" not in text.replace("the oracle/", ""), os.path.join(dirpath, f)
+
+
+def test_write_png_round_trip(built, tmp_path):
+    """RgbImage::save (main.rs:54): the dependency-free PNG writer decodes to the same pixels (PIL as the checker)."""
+    import numpy as np
+    from PIL import Image
+    rng = np.random.default_rng(7)
+    for (w, h) in ((1, 1), (37, 19), (300, 221)):  # 300x221x3+221 bytes: more than one 65535-byte stored block
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        path = str(tmp_path / ("t_%dx%d.png" % (w, h)))
+        assert F.lib().b200rt_write_png(path.encode(), img.ctypes.data_as(C.c_void_p), w, h) == 0
+        back = np.asarray(Image.open(path).convert("RGB"))
+        assert back.shape == img.shape and (back == img).all()
+    assert F.lib().b200rt_write_png(b"/nonexistent_dir/x.png", img.ctypes.data_as(C.c_void_p), 300, 221) == F.ERR_IO
+    assert F.lib().b200rt_write_png(b"x.png", None, 4, 4) == F.ERR_INVALID
+
+
+def test_cli_fails_loudly_without_a_device(built, tmp_path):
+    """b200rt_render (the reference's main over the C ABI) has no CPU fallback either."""
+    import subprocess
+    n = C.c_int(-1)
+    if F.lib().b200rt_device_count(C.byref(n)) == 0 and n.value > 0:
+        pytest.skip("a CUDA device is present")
+    from rust_raytracer_b200.build import CLI
+    scene = os.path.join(ROOT, "data", "scene_10.json")
+    r = subprocess.run([CLI, "--scene", scene, "--spp", "1", "--out", str(tmp_path / "o.png")], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1 and "no CPU fallback" in r.stderr and not (tmp_path / "o.png").exists()
+    r = subprocess.run([CLI, "--scene", "no_such_scene"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1 and "scene" in r.stderr

@@ -3,6 +3,8 @@
 Ray batches: hit/miss and primitive identical, t and normal within 1e-5 relative (north_star).
 Images: per-channel mean within 1 % of the oracle and tile-wise error inside the oracle's own two-seed envelope.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -10,6 +12,8 @@ import rust_raytracer_b200 as rt
 from rust_raytracer_b200 import _ffi as F
 from oracle_ffi import OracleScene
 from scenes_util import scene_builder, ray_batch, compare_hits
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 pytestmark = pytest.mark.gpu
 
@@ -202,3 +206,24 @@ def test_tonemap_matches_reference_formula(ctx):
     olib().oracle_tonemap(mean.ctypes.data_as(C.c_void_p), 256, want.ctypes.data_as(C.c_void_p))
     assert np.abs(got.astype(int) - want.astype(int)).max() <= 1  # f32 vs f64 sqrt at a bin edge
     assert tuple(got[0, 0]) == (0, 0, 255)
+
+
+@pytest.mark.gpu
+def test_cli_renders_the_json_scene_to_png(ctx, tmp_path):
+    """main.rs:49-72 over the C ABI: the PNG the command-line driver writes is the tonemapped image of the same
+    render through the Python mirror (same Philox keys; float summation order differs across atomics)."""
+    import subprocess
+    from PIL import Image
+    from rust_raytracer_b200.build import CLI
+    path = os.path.join(ROOT, "data", "scene_10.json")
+    out = str(tmp_path / "cli.png")
+    r = subprocess.run([CLI, "--scene", path, "--width", "96", "--height", "64", "--spp", "16", "--out", out], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Total:" in r.stdout and "RT:" in r.stdout
+    img = np.asarray(Image.open(out).convert("RGB")).astype(np.int32)
+    assert img.shape == (64, 96, 3)
+    sb = rt.SceneBuilder().load_json(open(path).read())
+    scene = rt.Scene(ctx, sb)
+    acc, _ = scene.render(sb.camera, rt.make_params(96, 64, 16))
+    ref = ctx.tonemap(acc).astype(np.int32)
+    assert np.abs(img - ref).max() <= 1 and (img != ref).mean() < 0.01
