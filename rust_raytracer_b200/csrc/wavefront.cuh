@@ -147,6 +147,9 @@ __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->
 // (Measured and rejected: per-lane ray replacement a la Aila & Laine's dynamic fetch.  Refilling idle lanes from
 // the queue mixes rays of different bins in one warp and loses the converged out-of-BVH tail: 60 ms -> 74..99 ms
 // of extend per step on book-2 for refill thresholds 16..28, profiles/r1_experiments.md.)
+#ifndef B200RT_EXTEND_BATCHES  // 32-ray batches a warp takes per cursor atomic (the later ones prefetched into L2)
+#define B200RT_EXTEND_BATCHES 1
+#endif
 #ifndef B200RT_EXTEND_MINBLOCKS
 #define B200RT_EXTEND_MINBLOCKS 8
 #endif
@@ -160,10 +163,20 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
   const unsigned int n = B.cnt->n_ext;
   const unsigned lane = threadIdx.x & 31;
   for (;;) {
-    unsigned int base = 0;
-    if (lane == 0) base = atomicAdd(&B.cnt->ext_cursor, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
+    unsigned int base0 = 0;
+    if (lane == 0) base0 = atomicAdd(&B.cnt->ext_cursor, 32u * B200RT_EXTEND_BATCHES);
+    base0 = __shfl_sync(0xffffffffu, base0, 0);
+    if (base0 >= n) break;
+#if B200RT_EXTEND_BATCHES > 1
+#pragma unroll 1
+   for (unsigned int hb = 0; hb < B200RT_EXTEND_BATCHES; ++hb) {
+    const unsigned int base = base0 + 32u * hb;
     if (base >= n) break;
+    if (hb + 1 < B200RT_EXTEND_BATCHES && base + 32u + lane < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(B.ray + 2 * (size_t)(base + 32u + lane)));
+#else
+   {
+    const unsigned int base = base0;
+#endif
     const unsigned int i = base + lane;
     const bool active = i < n;
     const float4* ray = B.ray + 2 * (size_t)i;
@@ -199,6 +212,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
       WF_ST(B.hit + i, make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), wf_pack_prim(h.prim, h.aux), goes_on ? rank : WF_NO_RANK));
     }
+   }
   }
 }
 
@@ -228,6 +242,12 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
     const float4* t = B.st + 2 * (size_t)src;
     n_o = WF_LD(r + 0); n_d = WF_LD(r + 1); n_sa = WF_LD(t + 0); n_sb = WF_LD(t + 1); n_hh = WF_LD(B.hit + src);
   };
+#ifndef B200RT_SHADE_L2PF  // iterations ahead whose records shade pulls into L2 (15.9 -> 14.5 ms of shade per step at 1; 14.7 at 2)
+#define B200RT_SHADE_L2PF 1
+#endif
+#ifndef B200RT_SHADE_PF_LEVEL
+#define B200RT_SHADE_PF_LEVEL "L2"
+#endif
 #ifndef B200RT_SHADE_PREFETCH  // measured: with streaming reads the explicit prefetch only costs registers (18.3 ms vs 17.2 ms at 96 regs)
 #define B200RT_SHADE_PREFETCH 0
 #endif
@@ -236,6 +256,14 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
 #endif
   for (unsigned int gi = g0; gi < n_work; gi += stride) {
 #if !B200RT_SHADE_PREFETCH
+#if B200RT_SHADE_L2PF
+    if (gi + B200RT_SHADE_L2PF * stride < n_ext) {  // pull a later iteration's records into L2: costs no registers
+      const unsigned int nx = gi + B200RT_SHADE_L2PF * stride;
+      asm volatile("prefetch.global." B200RT_SHADE_PF_LEVEL " [%0];" ::"l"(B.ray + 2 * (size_t)nx));
+      asm volatile("prefetch.global." B200RT_SHADE_PF_LEVEL " [%0];" ::"l"(B.st + 2 * (size_t)nx));
+      asm volatile("prefetch.global." B200RT_SHADE_PF_LEVEL " [%0];" ::"l"(B.hit + nx));
+    }
+#endif
     if (gi < n_ext) load_rec(gi);
 #endif
     const float4 o = n_o, d = n_d, sa = n_sa;
