@@ -269,6 +269,36 @@ int b200rt_render_device(b200rt_scene* scene, const b200rt_camera* cam, const b2
                          b200rt_stats* stats);
 int b200rt_render(b200rt_scene* scene, const b200rt_camera* cam, const b200rt_params* params, float* accum_host,
                   b200rt_stats* stats);
+/* ---- SPPMIntegrator (integrator/photon_mapper.rs:17-366) ---- */
+typedef struct b200rt_sppm_params {
+  int32_t iterations;       /* max_iter_cnt = 50 (photon_mapper.rs:151) */
+  int32_t photons_per_iter; /* photon_per_iter = 500000 (photon_mapper.rs:152) */
+  int32_t k_global;         /* GLOBAL_INIT_PHOTONS = 100 (photon_mapper.rs:18); <= 128 */
+  int32_t k_caustic;        /* CAUSTIC_INIT_PHOTONS = 50 (photon_mapper.rs:19); <= 128 */
+  double alpha;             /* ALPHA = 0.7 (photon_mapper.rs:17) */
+  double light_scale;       /* `scale` of XZRectLight::new / SphereDiffuseLight::new (1e6 in scene.rs:26-32) */
+} b200rt_sppm_params;
+typedef struct b200rt_sppm_stats {
+  uint64_t global_photons; /* stored over all iterations */
+  uint64_t caustic_photons;
+  uint64_t photon_rays;
+  uint64_t eye_rays; /* eye passes + final pass */
+  float ms_total;    /* CUDA events on the context stream */
+  float ms_photons;
+  float ms_grid;
+  float ms_eye;
+  float ms_final;
+  uint32_t pad;
+} b200rt_sppm_stats;
+/* SPPMIntegrator::new(world) followed by Camera::capture_image(integrator) (main.rs:51-53): `iterations` rounds of
+ * photon map + one eye ray per pixel (SPPM::update), then spp_count samples per pixel of SPPMIntegrator::sample_ray.
+ * The lights are the scene's marked lights (World::new's light list); rectangle lights emit towards the negative
+ * axis like XZRectLight (light.rs:157-165).  accum_host: width*height float4 (r,g,b sums and sample count);
+ * pixel_stats_host (may be NULL): width*height x 10 floats: global flux rgb, radius2, photons, caustic ditto. */
+int b200rt_render_sppm(b200rt_scene* scene, const b200rt_camera* cam, const b200rt_params* params,
+                       const b200rt_sppm_params* sppm, float* accum_host, float* pixel_stats_host,
+                       b200rt_sppm_stats* stats);
+
 /* From<Vec3> for Rgb<u8> (vec3.rs:223-231): floor(clamp(sqrt(sum/count),0,1)*255). Device kernel; host buffers. */
 int b200rt_tonemap_rgb8(b200rt_ctx* ctx, const float* accum_host, int32_t width, int32_t height, uint8_t* rgb_out);
 int b200rt_tonemap_rgb8_device(b200rt_ctx* ctx, const float* accum_dev, int32_t width, int32_t height, uint8_t* rgb_dev);

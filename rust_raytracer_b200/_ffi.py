@@ -73,6 +73,17 @@ class Stats(C.Structure):
                 ("ms_other", C.c_float), ("wavefront_iterations", C.c_uint32), ("pad", C.c_uint32)]
 
 
+class SppmParams(C.Structure):
+    _fields_ = [("iterations", C.c_int32), ("photons_per_iter", C.c_int32), ("k_global", C.c_int32), ("k_caustic", C.c_int32),
+                ("alpha", C.c_double), ("light_scale", C.c_double)]
+
+
+class SppmStats(C.Structure):
+    _fields_ = [("global_photons", C.c_uint64), ("caustic_photons", C.c_uint64), ("photon_rays", C.c_uint64), ("eye_rays", C.c_uint64),
+                ("ms_total", C.c_float), ("ms_photons", C.c_float), ("ms_grid", C.c_float), ("ms_eye", C.c_float), ("ms_final", C.c_float),
+                ("pad", C.c_uint32)]
+
+
 class Hit(C.Structure):
     _fields_ = [("t", C.c_float), ("prim", C.c_int32), ("nx", C.c_float), ("ny", C.c_float), ("nz", C.c_float), ("front_face", C.c_int32),
                 ("u", C.c_float), ("v", C.c_float)]
@@ -100,6 +111,7 @@ PROTOTYPES = {
     "b200rt_tonemap_rgb8": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),
     "b200rt_tonemap_rgb8_device": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),
     "b200rt_write_png": (C.c_int, [C.c_char_p, VP, C.c_int32, C.c_int32]),
+    "b200rt_render_sppm": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, VP, VP, VP]),
     "b200rt_camera_make": (C.c_int, [D3, D3, D3, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(Camera)]),
     "b200rt_measure_fp32_peak": (C.c_int, [VP, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "b200rt_builder_create": (C.c_int, [C.POINTER(VP)]),

@@ -268,3 +268,4 @@ int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_
 }  // extern "C"
 
 #include "api_render.cuh"
+#include "api_sppm.cuh"

@@ -1,0 +1,168 @@
+// api_sppm.cuh — SPPMIntegrator::new + capture_image (photon_mapper.rs:139-236, main.rs:51-53) on the device: the
+// host loop over the SPPM iterations (photon pass -> grid build for both maps -> eye pass) and the final pass.
+// Included by api.cu after api_render.cuh.
+#pragma once
+#include "sppm.cuh"
+
+namespace {
+
+struct SppmBuffers {
+  float4 *pg = nullptr, *pc = nullptr;
+  uint32_t *cell_count = nullptr, *start_g = nullptr, *start_c = nullptr, *cursor = nullptr, *index_g = nullptr, *index_c = nullptr;
+  float4 *px_g = nullptr, *px_c = nullptr;
+  uint2* px_n = nullptr;
+  SppmCounters* cnt = nullptr;
+  float* accum = nullptr;
+  void release() {
+    void* all[] = {pg, pc, cell_count, start_g, start_c, cursor, index_g, index_c, px_g, px_c, px_n, cnt, accum};
+    for (void* p : all) if (p) cudaFree(p);
+  }
+};
+
+const int SPPM_MAX_RES = 128;
+
+// grid resolution and placement for a map of n photons inside the photon bounding box [lo, hi]
+SppmGrid sppm_make_grid(const float4* photons, const uint32_t* start, const uint32_t* index, uint32_t n, const float lo[3], const float hi[3]) {
+  SppmGrid G;
+  G.photons = photons; G.cell_start = start; G.index = index; G.n = n;
+  int res = (int)std::cbrt((double)n / 2.0) + 1;
+  G.res = res < 1 ? 1 : (res > SPPM_MAX_RES ? SPPM_MAX_RES : res);
+  float ext = std::fmax(hi[0] - lo[0], std::fmax(hi[1] - lo[1], hi[2] - lo[2]));
+  if (!(ext > 0.f)) ext = 1.f;
+  G.cell = ext * 1.0001f / (float)G.res;
+  G.inv_cell = 1.0f / G.cell;
+  G.lo = make_float3(lo[0], lo[1], lo[2]);
+  return G;
+}
+
+int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, const SppmGrid& G, uint32_t* start, uint32_t* index) {
+  cudaStream_t q = ctx->stream;
+  const uint32_t n_cells = (uint32_t)G.res * G.res * G.res;
+  CU_CHECK(ctx, cudaMemsetAsync(B.cell_count, 0, sizeof(uint32_t) * n_cells, q));
+  const int blocks = ctx->prop.multiProcessorCount * 4;
+  if (G.n) k_sppm_grid_count<<<blocks, 256, 0, q>>>(G.photons, G.n, G.lo, G.inv_cell, G.res, B.cell_count);
+  k_sppm_grid_scan<<<1, 1024, 0, q>>>(B.cell_count, n_cells, start, B.cursor);
+  if (G.n) k_sppm_grid_fill<<<blocks, 256, 0, q>>>(G.photons, G.n, G.lo, G.inv_cell, G.res, B.cursor, index);
+  CU_CHECK(ctx, cudaGetLastError());
+  return B200RT_OK;
+}
+
+}  // namespace
+
+extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, const b200rt_sppm_params* sppm,
+                                  float* accum_host, float* pixel_stats_host, b200rt_sppm_stats* stats) {
+  if (!s || !cam || !params || !sppm || !accum_host) return B200RT_ERR_INVALID;
+  b200rt_ctx* ctx = s->ctx;
+  int rc = validate_params(ctx, params);
+  if (rc) return rc;
+  if (sppm->iterations < 1 || sppm->photons_per_iter < 1 || sppm->k_global < 1 || sppm->k_caustic < 1 || sppm->k_global > SPPM_MAX_K ||
+      sppm->k_caustic > SPPM_MAX_K || !(sppm->alpha > 0.0) || !(sppm->light_scale > 0.0) || sppm->photons_per_iter > (1 << 26)) {
+    ctx->err = "sppm: iterations, photons_per_iter >= 1, 1 <= k <= 128, alpha > 0, light_scale > 0";
+    return B200RT_ERR_INVALID;
+  }
+  if (s->dev.n_lights < 1) { ctx->err = "sppm: the scene has no marked light (World::new takes a light list, world.rs:15-25)"; return B200RT_ERR_INVALID; }
+  CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t q = ctx->stream;
+  const uint32_t n_pix = (uint32_t)params->width * params->height;
+  const unsigned int cap = (unsigned int)sppm->photons_per_iter * 16u;  // stored photons per iteration (~1.5 per emitted photon in a Cornell box)
+  const uint32_t max_cells = (uint32_t)SPPM_MAX_RES * SPPM_MAX_RES * SPPM_MAX_RES;
+  SppmBuffers B;
+  cudaError_t e = cudaSuccess;
+  auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
+  alloc((void**)&B.pg, (size_t)cap * 64); alloc((void**)&B.pc, (size_t)cap * 64);
+  alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
+  alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
+  alloc((void**)&B.index_g, 4 * (size_t)cap); alloc((void**)&B.index_c, 4 * (size_t)cap);
+  alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
+  alloc((void**)&B.cnt, sizeof(SppmCounters)); alloc((void**)&B.accum, 16 * (size_t)n_pix);
+  if (e != cudaSuccess) { B.release(); ctx->err = std::string("sppm: ") + cudaGetErrorString(e); return B200RT_ERR_NOMEM; }
+  auto fail = [&](int code) { B.release(); return code; };
+#define SPPM_CHECK(call)                                                                          \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess) { ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(B200RT_ERR_CUDA); } \
+  } while (0)
+  SPPM_CHECK(cudaMemsetAsync(B.px_g, 0, 16 * (size_t)n_pix, q));
+  SPPM_CHECK(cudaMemsetAsync(B.px_c, 0, 16 * (size_t)n_pix, q));
+  SPPM_CHECK(cudaMemsetAsync(B.px_n, 0, 8 * (size_t)n_pix, q));
+  SPPM_CHECK(cudaMemsetAsync(B.accum, 0, 16 * (size_t)n_pix, q));
+
+  b200rt_sppm_stats local;
+  std::memset(&local, 0, sizeof(local));
+  SppmConst sp;
+  sp.iterations = sppm->iterations; sp.photons_per_iter = sppm->photons_per_iter; sp.k_global = sppm->k_global; sp.k_caustic = sppm->k_caustic;
+  sp.alpha = sppm->alpha; sp.light_scale = (float)sppm->light_scale;
+  RenderConst P = make_render_const(cam, params);
+  RenderConst Peye = P;
+  Peye.key.y ^= 0x5EE05EE0u;  // the eye pass draws its own jitter, independent of the final pass
+  const SppmPixels px{B.px_g, B.px_c, B.px_n};
+  const int sms = ctx->prop.multiProcessorCount;
+  float ms = 0.f;
+  SPPM_CHECK(cudaEventRecord(ctx->ev[0], q));
+  for (int it = 0; it < sp.iterations; ++it) {
+    SppmCounters h;
+    std::memset(&h, 0, sizeof(h));
+    for (int a = 0; a < 3; ++a) { h.lo[a] = 0xffffffffu; h.hi[a] = 0u; }
+    SPPM_CHECK(cudaMemcpyAsync(B.cnt, &h, sizeof(h), cudaMemcpyHostToDevice, q));
+    SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
+    k_sppm_photons<<<sms * 4, 128, 0, q>>>(s->dev, sp, P.key, it, B.pg, B.pc, cap, B.cnt);
+    SPPM_CHECK(cudaEventRecord(ctx->sev[1], q));
+    SPPM_CHECK(cudaMemcpyAsync(&h, B.cnt, sizeof(h), cudaMemcpyDeviceToHost, q));
+    SPPM_CHECK(cudaStreamSynchronize(q));
+    if (h.overflow) { ctx->err = "sppm: photon buffer overflow (more than 16 stored photons per emitted photon)"; return fail(B200RT_ERR_NOMEM); }
+    float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+    if (h.n_global) for (int a = 0; a < 3; ++a) { lo[a] = sppm_unord(h.lo[a]); hi[a] = sppm_unord(h.hi[a]); }
+    const SppmGrid Gg = sppm_make_grid(B.pg, B.start_g, B.index_g, h.n_global, lo, hi);
+    const SppmGrid Gc = sppm_make_grid(B.pc, B.start_c, B.index_c, h.n_caustic, lo, hi);
+    if ((rc = sppm_build_grid(ctx, B, Gg, B.start_g, B.index_g)) != 0) return fail(rc);
+    if ((rc = sppm_build_grid(ctx, B, Gc, B.start_c, B.index_c)) != 0) return fail(rc);
+    SPPM_CHECK(cudaEventRecord(ctx->sev[2], q));
+    k_sppm_eye<<<sms * 4, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt);
+    SPPM_CHECK(cudaEventRecord(ctx->sev[3], q));
+    SPPM_CHECK(cudaMemcpyAsync(&h, B.cnt, sizeof(h), cudaMemcpyDeviceToHost, q));
+    SPPM_CHECK(cudaStreamSynchronize(q));
+    local.global_photons += h.n_global; local.caustic_photons += h.n_caustic;
+    local.photon_rays += h.photon_rays; local.eye_rays += h.eye_rays;
+    if (cudaEventElapsedTime(&ms, ctx->sev[0], ctx->sev[1]) == cudaSuccess) local.ms_photons += ms;
+    if (cudaEventElapsedTime(&ms, ctx->sev[1], ctx->sev[2]) == cudaSuccess) local.ms_grid += ms;
+    if (cudaEventElapsedTime(&ms, ctx->sev[2], ctx->sev[3]) == cudaSuccess) local.ms_eye += ms;
+  }
+  // final pass: capture_image over the SPPM integrator (photon_mapper.rs:327-365)
+  const PathMap M = make_path_map(params->width, params->height, params->spp_count);
+  const float n_emitted = (float)((double)sp.iterations * (double)sp.photons_per_iter);  // photon_mapper.rs:229-230
+  SppmCounters h;
+  std::memset(&h, 0, sizeof(h));
+  SPPM_CHECK(cudaMemcpyAsync(B.cnt, &h, sizeof(h), cudaMemcpyHostToDevice, q));
+  SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
+  if (M.total > 0) {
+    k_sppm_final<<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt);
+    k_add_count<<<(n_pix + 255) / 256, 256, 0, q>>>(B.accum, (int)n_pix, (float)params->spp_count);
+  }
+  SPPM_CHECK(cudaEventRecord(ctx->sev[1], q));
+  SPPM_CHECK(cudaEventRecord(ctx->ev[1], q));
+  SPPM_CHECK(cudaMemcpyAsync(&h, B.cnt, sizeof(h), cudaMemcpyDeviceToHost, q));
+  SPPM_CHECK(cudaMemcpyAsync(accum_host, B.accum, 16 * (size_t)n_pix, cudaMemcpyDeviceToHost, q));
+  std::vector<float4> hg, hc;
+  std::vector<uint2> hn;
+  if (pixel_stats_host) {
+    hg.resize(n_pix); hc.resize(n_pix); hn.resize(n_pix);
+    SPPM_CHECK(cudaMemcpyAsync(hg.data(), B.px_g, 16 * (size_t)n_pix, cudaMemcpyDeviceToHost, q));
+    SPPM_CHECK(cudaMemcpyAsync(hc.data(), B.px_c, 16 * (size_t)n_pix, cudaMemcpyDeviceToHost, q));
+    SPPM_CHECK(cudaMemcpyAsync(hn.data(), B.px_n, 8 * (size_t)n_pix, cudaMemcpyDeviceToHost, q));
+  }
+  SPPM_CHECK(cudaStreamSynchronize(q));
+  SPPM_CHECK(cudaGetLastError());
+  if (pixel_stats_host)
+    for (uint32_t i = 0; i < n_pix; ++i) {
+      float* o = pixel_stats_host + 10 * (size_t)i;
+      o[0] = hg[i].x; o[1] = hg[i].y; o[2] = hg[i].z; o[3] = hg[i].w; o[4] = (float)hn[i].x;
+      o[5] = hc[i].x; o[6] = hc[i].y; o[7] = hc[i].z; o[8] = hc[i].w; o[9] = (float)hn[i].y;
+    }
+  local.eye_rays += h.eye_rays;
+  if (cudaEventElapsedTime(&ms, ctx->sev[0], ctx->sev[1]) == cudaSuccess) local.ms_final = ms;
+  if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) local.ms_total = ms;
+#undef SPPM_CHECK
+  B.release();
+  if (stats) *stats = local;
+  return B200RT_OK;
+}

@@ -2,8 +2,10 @@
 // timing lines in the reference's form.  Host C++ only; every GPU call goes through include/b200rt.h.
 //
 //   b200rt_render --scene book2|book1|cornell_book3|cornell_ref|mesh|<file.json>|<file.yaml> [--obj path.obj]
-//                 [--earth earth.ppm] [--width W] [--height H] [--spp N] [--depth D] [--integrator path|mixture|nee]
-//                 [--seed S] [--gpus G] [--out output/test.png]
+//                 [--earth earth.ppm] [--width W] [--height H] [--spp N] [--depth D] [--integrator path|mixture|nee|sppm]
+//                 [--iterations 50] [--photons 500000] [--light-scale 1e6] [--seed S] [--gpus G] [--out output/test.png]
+//
+// --integrator sppm is what the reference's main renders (SPPMIntegrator::new + capture_image, main.rs:51-53; one GPU).
 //
 // --gpus G shards the samples over G devices (one context and one host thread per device, the reference's own
 // decomposition is row bands over a thread pool, camera.rs:74-111) and sums the accumulation images on the host.
@@ -89,7 +91,8 @@ double seconds_since(std::chrono::steady_clock::time_point t0) {
 
 int main(int argc, char** argv) {
   std::string scene = "book2", obj, earth, out = "output/test.png", integ = "path";
-  int width = 0, height = 0, spp = 64, depth = 50, gpus = 1;
+  int width = 0, height = 0, spp = 64, depth = 50, gpus = 1, iterations = 50, photons = 500000;
+  double light_scale = 1e6;
   unsigned long long seed = 1;
   for (int i = 1; i < argc; ++i) {
     const std::string a = argv[i];
@@ -107,6 +110,9 @@ int main(int argc, char** argv) {
     else if (a == "--spp") spp = std::atoi(next("--spp"));
     else if (a == "--depth") depth = std::atoi(next("--depth"));
     else if (a == "--gpus") gpus = std::atoi(next("--gpus"));
+    else if (a == "--iterations") iterations = std::atoi(next("--iterations"));
+    else if (a == "--photons") photons = std::atoi(next("--photons"));
+    else if (a == "--light-scale") light_scale = std::atof(next("--light-scale"));
     else if (a == "--seed") seed = std::strtoull(next("--seed"), nullptr, 10);
     else { std::fprintf(stderr, "unknown argument %s\n", a.c_str()); return 2; }
   }
@@ -141,10 +147,35 @@ int main(int argc, char** argv) {
   if (integ == "path") params.integrator = B200RT_INTEGRATOR_PATH;
   else if (integ == "mixture") params.integrator = B200RT_INTEGRATOR_MIXTURE;
   else if (integ == "nee") params.integrator = B200RT_INTEGRATOR_NEE;
+  else if (integ == "sppm") params.integrator = B200RT_INTEGRATOR_PATH;  // the final pass has its own loop (photon_mapper.rs:327-365)
   else { std::fprintf(stderr, "unknown integrator %s\n", integ.c_str()); return 2; }
   b200rt_scene_desc desc{};
   if (b200rt_builder_finish(b, &desc)) { std::fprintf(stderr, "scene: %s\n", b200rt_builder_error(b)); return 1; }
 
+  if (integ == "sppm") {  // main.rs:51-53: SPPMIntegrator::new(world) then capture_image(integrator)
+    b200rt_ctx* ctx = nullptr;
+    if (b200rt_ctx_create(0, &ctx)) { std::fprintf(stderr, "no CUDA device (there is no CPU fallback)\n"); return 1; }
+    b200rt_scene* sc = nullptr;
+    if (b200rt_scene_create(ctx, &desc, &sc)) { std::fprintf(stderr, "scene: %s\n", b200rt_last_error(ctx)); return 1; }
+    params.spp_begin = 0; params.spp_count = spp;
+    b200rt_sppm_params sp{};
+    sp.iterations = iterations; sp.photons_per_iter = photons; sp.k_global = 100; sp.k_caustic = 50; sp.alpha = 0.7; sp.light_scale = light_scale;
+    b200rt_sppm_stats st{};
+    std::vector<float> accum((size_t)params.width * params.height * 4, 0.f);
+    if (b200rt_render_sppm(sc, &cam, &params, &sp, accum.data(), nullptr, &st)) { std::fprintf(stderr, "sppm: %s\n", b200rt_last_error(ctx)); return 1; }
+    std::vector<uint8_t> rgb8((size_t)params.width * params.height * 3);
+    if (b200rt_tonemap_rgb8(ctx, accum.data(), params.width, params.height, rgb8.data())) { std::fprintf(stderr, "tonemap: %s\n", b200rt_last_error(ctx)); return 1; }
+    b200rt_scene_destroy(sc);
+    b200rt_ctx_destroy(ctx);
+    b200rt_builder_destroy(b);
+    if (b200rt_write_png(out.c_str(), rgb8.data(), params.width, params.height)) { std::fprintf(stderr, "cannot write %s\n", out.c_str()); return 1; }
+    const double sppm_s = (st.ms_photons + st.ms_grid + st.ms_eye) * 1e-3, rt_s = st.ms_final * 1e-3;
+    std::printf("Total: %.3fs\n\tSPPM: %.3fs\n\tRT: %.3fs\n", seconds_since(t_start), sppm_s, rt_s);
+    std::printf("%dx%d, %d iterations x %d photons (%llu global, %llu caustic stored), %d spp: photons %.1f ms, grid %.1f ms, eye %.1f ms, final %.1f ms -> %s\n",
+                params.width, params.height, iterations, photons, (unsigned long long)st.global_photons, (unsigned long long)st.caustic_photons, spp,
+                st.ms_photons, st.ms_grid, st.ms_eye, st.ms_final, out.c_str());
+    return 0;
+  }
   const auto t_rt = std::chrono::steady_clock::now();
   if (gpus > spp) gpus = spp;
   std::vector<Shard> shards(gpus);

@@ -107,6 +107,18 @@ class Scene:
         self.ctx._ok(F.lib().b200rt_render(self._h, C.byref(camera), C.byref(params), accum.ctypes.data_as(C.c_void_p), C.byref(st)))
         return accum, st
 
+    def render_sppm(self, camera, params, iterations=50, photons_per_iter=500000, k_global=100, k_caustic=50, alpha=0.7, light_scale=1e6,
+                    want_pixel_stats=False):
+        """SPPMIntegrator::new + capture_image (photon_mapper.rs:139-236, main.rs:51-53): returns (accum[h,w,4], SppmStats) or,
+        with want_pixel_stats, (accum, per-pixel stats [h,w,10], SppmStats)."""
+        accum = np.zeros((params.height, params.width, 4), np.float32)
+        px = np.zeros((params.height, params.width, 10), np.float32) if want_pixel_stats else None
+        sp = F.SppmParams(iterations, photons_per_iter, k_global, k_caustic, alpha, light_scale)
+        st = F.SppmStats()
+        self.ctx._ok(F.lib().b200rt_render_sppm(self._h, C.byref(camera), C.byref(params), C.byref(sp), accum.ctypes.data_as(C.c_void_p),
+                                                px.ctypes.data_as(C.c_void_p) if want_pixel_stats else None, C.byref(st)))
+        return (accum, px, st) if want_pixel_stats else (accum, st)
+
     def render_device(self, camera, params, accum_ptr):
         st = F.Stats()
         self.ctx._ok(F.lib().b200rt_render_device(self._h, C.byref(camera), C.byref(params), C.c_void_p(accum_ptr), C.byref(st)))

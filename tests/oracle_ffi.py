@@ -32,6 +32,8 @@ def lib():
         h.oracle_vec3_op.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         h.oracle_sphere_union_box.argtypes = [C.POINTER(F.Prim), C.c_uint32, C.c_void_p]
         h.oracle_texture_eval.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p]
+        h.oracle_sppm_render.argtypes = [C.c_void_p, C.POINTER(F.Camera), C.POINTER(F.Params), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_int]
         _lib = h
     return _lib
 
@@ -74,6 +76,19 @@ class OracleScene:
         if rc:
             raise RuntimeError("oracle: " + lib().oracle_last_error().decode())
         return acc, ext.value, shd.value, sec.value
+
+    def sppm_render(self, camera, params, iterations, photons_per_iter, k_global=100, k_caustic=50, alpha=0.7, light_scale=1e6, n_threads=8):
+        """SPPMIntegrator::new + capture_image.  Returns (sum image [h,w,3], per-pixel stats [h,w,10], (global, caustic) photon counts)."""
+        acc = np.zeros((params.height, params.width, 3), np.float64)
+        stats = np.zeros((params.height, params.width, 10), np.float64)
+        counts = np.zeros(2, np.uint64)
+        sp_i = np.array([iterations, photons_per_iter, k_global, k_caustic], np.int32)
+        sp_d = np.array([alpha, light_scale], np.float64)
+        rc = lib().oracle_sppm_render(self._h, C.byref(camera), C.byref(params), sp_i.ctypes.data_as(C.c_void_p), sp_d.ctypes.data_as(C.c_void_p),
+                                      acc.ctypes.data_as(C.c_void_p), stats.ctypes.data_as(C.c_void_p), counts.ctypes.data_as(C.c_void_p), n_threads)
+        if rc:
+            raise RuntimeError("oracle: " + lib().oracle_last_error().decode())
+        return acc, stats, (int(counts[0]), int(counts[1]))
 
     def texture_eval(self, tex, p_uv):
         p = np.ascontiguousarray(p_uv, dtype=np.float64).reshape(-1, 5)

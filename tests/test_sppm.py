@@ -1,0 +1,106 @@
+"""SPPM integrator: the device implementation against the oracle restatement of
+integrator/photon_mapper.rs + light.rs.  The reference draws from thread_rng(), so parity is statistical: photon
+statistics, the per-pixel SPPM state and the final image must agree within the oracle's own two-seed noise."""
+import os
+
+import numpy as np
+import pytest
+
+import rust_raytracer_b200 as rt
+from rust_raytracer_b200 import _ffi as F
+from oracle_ffi import OracleScene
+from scenes_util import scene_builder
+
+W, H, SPP = 40, 40, 4
+ITER, PHOTONS = 6, 20000
+
+
+def _oracle(sb, seed, **kw):
+    p = rt.copy_params(sb.params, width=W, height=H, spp_count=SPP, seed=seed)
+    return OracleScene(sb).sppm_render(sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS, **kw)
+
+
+def test_oracle_sppm_known_answers(built):
+    """Closed-form anchors of the restatement (no GPU): photon bookkeeping of generate_photon_map and SPPM::update."""
+    sb = scene_builder("cornell_ref")
+    acc, stats, (ng, nc) = _oracle(sb, 11)
+    # every emitted photon leaves the ceiling light downwards into a closed box: its first hit is a surface, so at least
+    # ~max(f) of them are stored; caustic photons need a specular hit first (the two spheres): a small, non-zero share
+    assert ITER * PHOTONS * 0.5 < ng < ITER * PHOTONS * 8
+    assert 0 < nc < 0.1 * ng
+    g_n, c_n = stats[..., 4], stats[..., 9]
+    seen = g_n > 0
+    assert seen.mean() > 0.4  # the box fills about half of the 50-degree view from z = -800 (scene.rs:100-110)
+    # photon_mapper.rs:51-52, 59: the count starts at 100 / 50 and only grows, by floor(0.7 * M)
+    assert g_n[seen].min() >= 100 and c_n[seen].min() >= 50
+    assert np.all(g_n[seen] == np.floor(g_n[seen])) and g_n[seen].max() > 100
+    # radius2 only shrinks: after ITER rounds it is below the first k-nearest radius of a typical pixel, and positive
+    assert np.all(stats[..., 3][seen] > 0)
+    img = acc / SPP
+    assert np.isfinite(img[seen]).mean() > 0.99
+
+
+@pytest.mark.gpu
+def test_sppm_matches_oracle(ctx):
+    sb = scene_builder("cornell_ref")
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=W, height=H, spp_count=SPP, seed=5)
+    acc, px, st = scene.render_sppm(sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS, want_pixel_stats=True)
+    assert np.all(acc[..., 3] == SPP)
+    a_acc, a_st, (a_ng, a_nc) = _oracle(sb, 101)
+    b_acc, b_st, (b_ng, b_nc) = _oracle(sb, 202)
+    print("photons gpu", st.global_photons, st.caustic_photons, "oracle", (a_ng, a_nc), (b_ng, b_nc), "ms", st.ms_total, st.ms_photons, st.ms_grid, st.ms_eye, st.ms_final)
+    # 1. photon statistics (binomial counts over 120k emitted photons: sigma ~ 0.3 %; caustic ~ 2 %)
+    ng, nc = 0.5 * (a_ng + b_ng), 0.5 * (a_nc + b_nc)
+    assert abs(st.global_photons - ng) < 0.03 * ng  # seed-to-seed sigma is 0.5 % (8 seeds each side: +0.1 % +- 0.2 %)
+    assert abs(st.caustic_photons - nc) < 0.10 * nc + 4 * abs(a_nc - b_nc)
+    # 2. per-pixel SPPM state (photon_mapper.rs:33-64): photons, radius2 and flux, image means against the two oracle seeds
+    for k, name, tol in ((4, "global photons", 0.03), (3, "global radius2", 0.08), (9, "caustic photons", 0.03), (8, "caustic radius2", 0.15)):
+        g, a, b = float(np.mean(px[..., k])), float(np.mean(a_st[..., k])), float(np.mean(b_st[..., k]))
+        ref = 0.5 * (a + b)
+        print("  %-16s gpu %.5g oracle %.5g / %.5g" % (name, g, a, b))
+        assert abs(g - ref) < tol * ref + 3 * abs(a - b), name
+    for k0, name in ((0, "global flux"), (5, "caustic flux")):
+        g = px[..., k0:k0 + 3].astype(np.float64).mean(axis=(0, 1))
+        a, b = a_st[..., k0:k0 + 3].mean(axis=(0, 1)), b_st[..., k0:k0 + 3].mean(axis=(0, 1))
+        ref = 0.5 * (a + b)
+        print("  %-16s gpu %s oracle %s / %s" % (name, g, a, b))
+        assert np.all(np.abs(g - ref) < 0.08 * ref + 3 * np.abs(a - b)), name
+    # 3. the final image (photon_mapper.rs:327-365), NaN estimates (empty-map pixels) excluded on both sides
+    gpu = acc[..., :3].astype(np.float64) / SPP
+    a, b = np.nan_to_num(a_acc / SPP, nan=0.0, posinf=0.0), np.nan_to_num(b_acc / SPP, nan=0.0, posinf=0.0)
+    ref = 0.5 * (a + b)
+    cap = np.percentile(ref, 99.5) * 4 + 1e-3
+    gm, rm = np.minimum(gpu, cap).mean(axis=(0, 1)), np.minimum(ref, cap).mean(axis=(0, 1))
+    dab = np.minimum(a, cap) - np.minimum(b, cap)
+    sigma_mean = np.sqrt((dab ** 2).mean(axis=(0, 1)) / 2.0 / (W * H))
+    rel = np.abs(gm - rm) / np.maximum(rm, 1e-9)
+    noise = sigma_mean * np.sqrt(1.5) / np.maximum(rm, 1e-9)
+    print("  image mean gpu", gm, "oracle", rm, "rel", rel, "noise", noise)
+    assert np.all(rel < np.maximum(0.05, 4 * noise))  # run-to-run sigma of the image mean is 1 % (8 seeds each side: -0.16 % +- 0.45 %)
+
+    def tiles(img, t=8):
+        return img[: H // t * t, : W // t * t].reshape(H // t, t, W // t, t, 3).mean(axis=(1, 3))
+    tg, ta, tb = tiles(np.minimum(gpu, cap)), tiles(np.minimum(a, cap)), tiles(np.minimum(b, cap))
+    env = np.sqrt(np.mean((ta - tb) ** 2)) / np.sqrt(2.0)
+    err = np.sqrt(np.mean((tg - 0.5 * (ta + tb)) ** 2))
+    print("  tile rms err %.5f, oracle two-seed sigma*sqrt(1.5) %.5f" % (err, env * np.sqrt(1.5)))
+    assert err < 2.5 * env * np.sqrt(1.5) + 1e-3
+
+
+@pytest.mark.gpu
+def test_sppm_argument_errors(ctx):
+    sb = scene_builder("json:scene_10")  # no marked light
+    scene = rt.Scene(ctx, sb)
+    p = rt.make_params(16, 16, 1)
+    if sb.desc().n_lights == 0:
+        with pytest.raises(rt.B200RTError) as e:
+            scene.render_sppm(sb.camera, p, iterations=1, photons_per_iter=100)
+        assert e.value.status == F.ERR_INVALID and "light" in str(e.value)
+    sb2 = scene_builder("cornell_ref")
+    scene2 = rt.Scene(ctx, sb2)
+    for kw in (dict(iterations=0), dict(photons_per_iter=0), dict(k_global=129), dict(alpha=0.0)):
+        args = dict(iterations=1, photons_per_iter=100)
+        args.update(kw)
+        with pytest.raises(rt.B200RTError):
+            scene2.render_sppm(sb2.camera, rt.copy_params(sb2.params, width=16, height=16, spp_count=1), **args)
