@@ -269,6 +269,31 @@ int b200rt_render_device(b200rt_scene* scene, const b200rt_camera* cam, const b2
                          b200rt_stats* stats);
 int b200rt_render(b200rt_scene* scene, const b200rt_camera* cam, const b200rt_params* params, float* accum_host,
                   b200rt_stats* stats);
+/* ---- capture_image over several GPUs of one node ---- */
+#define B200RT_REDUCE_NONE 0 /* one device: nothing to sum */
+#define B200RT_REDUCE_NCCL 1 /* ncclReduce over NVLink (libnccl.so.2 loaded at run time) */
+#define B200RT_REDUCE_PEER 2 /* the root GPU loads the peers' buffers over NVLink (P2P) and adds them */
+typedef struct b200rt_multi_stats {
+  uint64_t paths;       /* over all devices */
+  uint64_t extend_rays;
+  uint64_t shadow_rays;
+  float ms_render_max;  /* slowest device's CUDA-event render time */
+  float ms_reduce;      /* CUDA events on the root stream around the sum-reduce */
+  float ms_wall;        /* host clock around the whole call (first call: includes ncclCommInitAll) */
+  int32_t reduce_path;  /* B200RT_REDUCE_* */
+  int32_t n_dev;
+  uint32_t pad;
+} b200rt_multi_stats;
+/* Camera::capture_image (camera.rs:66-128) sharded over n_dev GPUs: scenes[g] is the same scene created on n_dev
+ * different devices (one context each); device g renders the g-th contiguous part of the global sample range
+ * [spp_begin, spp_begin + spp_count) of every pixel — the reference's own decomposition is row bands over a thread
+ * pool (camera.rs:74-111) — on its own host thread, then the W x H float4 accumulation buffers are summed onto
+ * scenes[0]'s device with ONE reduce (peer-memory loads over NVLink; NCCL without peer access or with B200RT_MULTI_REDUCE=nccl)
+ * and copied into accum_host.  The union equals the one-device render up to float summation order (the Philox
+ * counter carries the global sample index).  stats_per_device (n_dev entries) and multi may be NULL. */
+int b200rt_render_multi(int32_t n_dev, b200rt_scene* const* scenes, const b200rt_camera* cam,
+                        const b200rt_params* params, float* accum_host, b200rt_stats* stats_per_device,
+                        b200rt_multi_stats* multi);
 /* ---- SPPMIntegrator (integrator/photon_mapper.rs:17-366) ---- */
 typedef struct b200rt_sppm_params {
   int32_t iterations;       /* max_iter_cnt = 50 (photon_mapper.rs:151) */

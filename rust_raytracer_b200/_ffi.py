@@ -84,6 +84,14 @@ class SppmStats(C.Structure):
                 ("pad", C.c_uint32)]
 
 
+class MultiStats(C.Structure):
+    _fields_ = [("paths", C.c_uint64), ("extend_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("ms_render_max", C.c_float),
+                ("ms_reduce", C.c_float), ("ms_wall", C.c_float), ("reduce_path", C.c_int32), ("n_dev", C.c_int32), ("pad", C.c_uint32)]
+
+
+REDUCE_NONE, REDUCE_NCCL, REDUCE_PEER = 0, 1, 2
+
+
 class Hit(C.Structure):
     _fields_ = [("t", C.c_float), ("prim", C.c_int32), ("nx", C.c_float), ("ny", C.c_float), ("nz", C.c_float), ("front_face", C.c_int32),
                 ("u", C.c_float), ("v", C.c_float)]
@@ -111,6 +119,7 @@ PROTOTYPES = {
     "b200rt_tonemap_rgb8": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),
     "b200rt_tonemap_rgb8_device": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),
     "b200rt_write_png": (C.c_int, [C.c_char_p, VP, C.c_int32, C.c_int32]),
+    "b200rt_render_multi": (C.c_int, [C.c_int32, C.POINTER(VP), C.POINTER(Camera), C.POINTER(Params), VP, C.POINTER(Stats), C.POINTER(MultiStats)]),
     "b200rt_render_sppm": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, VP, VP, VP]),
     "b200rt_camera_make": (C.c_int, [D3, D3, D3, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(Camera)]),
     "b200rt_measure_fp32_peak": (C.c_int, [VP, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

@@ -269,3 +269,4 @@ int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_
 
 #include "api_render.cuh"
 #include "api_sppm.cuh"
+#include "api_multi.cuh"

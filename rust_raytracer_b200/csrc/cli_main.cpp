@@ -7,8 +7,9 @@
 //
 // --integrator sppm is what the reference's main renders (SPPMIntegrator::new + capture_image, main.rs:51-53; one GPU).
 //
-// --gpus G shards the samples over G devices (one context and one host thread per device, the reference's own
-// decomposition is row bands over a thread pool, camera.rs:74-111) and sums the accumulation images on the host.
+// --gpus G shards the samples over G devices (b200rt_render_multi: one context and one host thread per device -- the
+// reference's own decomposition is row bands over a thread pool, camera.rs:74-111 -- and one NCCL or peer-memory
+// sum-reduce of the accumulation buffers onto device 0).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -60,27 +61,19 @@ bool read_ppm(const std::string& path, std::vector<uint8_t>& rgb, int& w, int& h
   return true;
 }
 
+// World::new on one device (scene upload happens on the device's own host thread, like the render)
 struct Shard {
-  int device = 0, spp_begin = 0, spp_count = 0, rc = 0;
+  int device = 0, rc = 0;
   std::string err;
-  std::vector<float> accum;
-  b200rt_stats st{};
+  b200rt_ctx* ctx = nullptr;
+  b200rt_scene* scene = nullptr;
 };
 
-void render_shard(const b200rt_scene_desc* desc, const b200rt_camera* cam, b200rt_params params, Shard* sh) {
-  b200rt_ctx* ctx = nullptr;
-  sh->rc = b200rt_ctx_create(sh->device, &ctx);
+void create_shard(const b200rt_scene_desc* desc, Shard* sh) {
+  sh->rc = b200rt_ctx_create(sh->device, &sh->ctx);
   if (sh->rc) { sh->err = "no CUDA device " + std::to_string(sh->device) + " (there is no CPU fallback)"; return; }
-  b200rt_scene* scene = nullptr;
-  sh->rc = b200rt_scene_create(ctx, desc, &scene);
-  if (!sh->rc) {
-    params.spp_begin = sh->spp_begin; params.spp_count = sh->spp_count;
-    sh->accum.assign((size_t)params.width * params.height * 4, 0.f);
-    sh->rc = b200rt_render(scene, cam, &params, sh->accum.data(), &sh->st);
-  }
-  if (sh->rc) sh->err = b200rt_last_error(ctx);
-  if (scene) b200rt_scene_destroy(scene);
-  b200rt_ctx_destroy(ctx);
+  sh->rc = b200rt_scene_create(sh->ctx, desc, &sh->scene);
+  if (sh->rc) sh->err = b200rt_last_error(sh->ctx);
 }
 
 double seconds_since(std::chrono::steady_clock::time_point t0) {
@@ -179,27 +172,28 @@ int main(int argc, char** argv) {
   const auto t_rt = std::chrono::steady_clock::now();
   if (gpus > spp) gpus = spp;
   std::vector<Shard> shards(gpus);
-  std::vector<std::thread> threads;
-  for (int g = 0; g < gpus; ++g) {
-    shards[g].device = g;
-    shards[g].spp_begin = (int)((long long)spp * g / gpus);
-    shards[g].spp_count = (int)((long long)spp * (g + 1) / gpus) - shards[g].spp_begin;
-    threads.emplace_back(render_shard, &desc, &cam, params, &shards[g]);
+  {
+    std::vector<std::thread> threads;
+    for (int g = 0; g < gpus; ++g) { shards[g].device = g; threads.emplace_back(create_shard, &desc, &shards[g]); }
+    for (auto& t : threads) t.join();
   }
-  for (auto& t : threads) t.join();
-  unsigned long long rays = 0;
+  std::vector<b200rt_scene*> scenes(gpus);
   for (int g = 0; g < gpus; ++g) {
-    if (shards[g].rc) { std::fprintf(stderr, "render on device %d: %s\n", g, shards[g].err.c_str()); return 1; }
-    rays += shards[g].st.extend_rays + shards[g].st.shadow_rays;
-    if (g) for (size_t k = 0; k < shards[0].accum.size(); ++k) shards[0].accum[k] += shards[g].accum[k];
+    if (shards[g].rc) { std::fprintf(stderr, "scene on device %d: %s\n", g, shards[g].err.c_str()); return 1; }
+    scenes[g] = shards[g].scene;
   }
+  // capture_image: sample ranges per device + one NCCL / peer-memory sum-reduce onto device 0 (b200rt_render_multi)
+  params.spp_begin = 0; params.spp_count = spp;
+  std::vector<float> accum((size_t)params.width * params.height * 4, 0.f);
+  b200rt_multi_stats ms{};
+  rc = b200rt_render_multi(gpus, scenes.data(), &cam, &params, accum.data(), nullptr, &ms);
+  if (rc) { std::fprintf(stderr, "render: %s\n", b200rt_last_error(shards[0].ctx)); return 1; }
+  const unsigned long long rays = ms.extend_rays + ms.shadow_rays;
   // tonemap on device 0 (vec3.rs:223-231) and save
   std::vector<uint8_t> rgb8((size_t)params.width * params.height * 3);
-  b200rt_ctx* ctx = nullptr;
-  if (b200rt_ctx_create(0, &ctx)) { std::fprintf(stderr, "no CUDA device\n"); return 1; }
-  rc = b200rt_tonemap_rgb8(ctx, shards[0].accum.data(), params.width, params.height, rgb8.data());
-  if (rc) { std::fprintf(stderr, "tonemap: %s\n", b200rt_last_error(ctx)); return 1; }
-  b200rt_ctx_destroy(ctx);
+  rc = b200rt_tonemap_rgb8(shards[0].ctx, accum.data(), params.width, params.height, rgb8.data());
+  if (rc) { std::fprintf(stderr, "tonemap: %s\n", b200rt_last_error(shards[0].ctx)); return 1; }
+  for (int g = 0; g < gpus; ++g) { b200rt_scene_destroy(shards[g].scene); b200rt_ctx_destroy(shards[g].ctx); }
   b200rt_builder_destroy(b);
   const double rt_s = seconds_since(t_rt);
   rc = b200rt_write_png(out.c_str(), rgb8.data(), params.width, params.height);
@@ -207,7 +201,8 @@ int main(int argc, char** argv) {
   // main.rs:56-71 prints "Total / SPPM / RT"; there is no photon pass on this path
   std::printf("Total: %.3fs\n\tSPPM: %.3fs\n\tRT: %.3fs\n", seconds_since(t_start), 0.0, rt_s);
   const double paths = (double)params.width * params.height * spp;
-  std::printf("%dx%d, %d spp on %d GPU(s): %.1f Mpaths/s, %.1f Mrays/s (host-timed, scene upload included) -> %s\n", params.width, params.height, spp,
-              gpus, paths / rt_s / 1e6, (double)rays / rt_s / 1e6, out.c_str());
+  std::printf("%dx%d, %d spp on %d GPU(s): %.1f Mpaths/s, %.1f Mrays/s (host-timed, scene upload included); device: render %.1f ms + %s reduce %.2f ms -> %s\n",
+              params.width, params.height, spp, gpus, paths / rt_s / 1e6, (double)rays / rt_s / 1e6, ms.ms_render_max,
+              ms.reduce_path == B200RT_REDUCE_NCCL ? "NCCL" : (ms.reduce_path == B200RT_REDUCE_PEER ? "peer-memory" : "no"), ms.ms_reduce, out.c_str());
   return 0;
 }

@@ -125,6 +125,19 @@ class Scene:
         return st
 
 
+def render_multi(scenes, camera, params):
+    """capture_image sharded by sample index over the devices of `scenes` (the same scene created on one Context per GPU) with
+    one NCCL / peer-memory sum-reduce onto scenes[0]'s device (b200rt_render_multi).
+    Returns (accum[h,w,4], [Stats per device], MultiStats)."""
+    n = len(scenes)
+    handles = (C.c_void_p * n)(*[s._h for s in scenes])
+    accum = np.zeros((params.height, params.width, 4), np.float32)
+    st = (F.Stats * n)()
+    ms = F.MultiStats()
+    scenes[0].ctx._ok(F.lib().b200rt_render_multi(n, handles, C.byref(camera), C.byref(params), accum.ctypes.data_as(C.c_void_p), st, C.byref(ms)))
+    return accum, list(st), ms
+
+
 def make_params(width, height, spp, integrator=F.INTEGRATOR_PATH, pipeline=F.PIPELINE_WAVEFRONT, max_depth=50, t_min=0.001,
                 background=(0.0, 0.0, 0.0), background_mode=F.BACKGROUND_CONSTANT, seed=1, spp_begin=0, flags=0):
     p = F.Params()

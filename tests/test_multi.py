@@ -1,0 +1,86 @@
+"""b200rt_render_multi: capture_image sharded by sample index over the GPUs of one node with
+one NCCL (or peer-memory) sum-reduce, inside the C ABI.  The 2-GPU cases need `gpurun --gpus 2`; on a one-GPU box
+they skip and the one-device identities still run."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import rust_raytracer_b200 as rt
+from rust_raytracer_b200 import _ffi as F
+from scenes_util import scene_builder
+
+
+def test_multi_split_matches_sharding_py():
+    """The C split of the sample range (api_multi.cuh multi_spp_range) is restated here and must equal sharding.spp_range."""
+    from rust_raytracer_b200.sharding import spp_range
+    for world in (1, 2, 3, 4, 8):
+        for spp in (0, 1, 7, 8, 100, 10000):
+            for begin in (0, 5):
+                got = []
+                for rank in range(world):
+                    base, rem = divmod(spp, world)
+                    got.append((begin + rank * base + min(rank, rem), base + (1 if rank < rem else 0)))
+                assert got == [spp_range(r, world, spp, begin) for r in range(world)]
+                assert sum(c for _, c in got) == spp
+
+
+def _n_devices():
+    n = C.c_int(0)
+    F.lib().b200rt_device_count(C.byref(n))
+    return n.value
+
+
+@pytest.mark.gpu
+def test_render_multi_one_device_is_render(ctx):
+    sb = scene_builder("cornell_book3")
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=48, height=40, spp_count=6, spp_begin=3)
+    want, st1 = scene.render(sb.camera, p)
+    got, st, ms = rt.render_multi([scene], sb.camera, p)
+    np.testing.assert_allclose(got, want, rtol=1e-4, atol=1e-4)  # per-pixel float atomics: the order of the adds is free
+    assert ms.n_dev == 1 and ms.reduce_path == F.REDUCE_NONE and ms.paths == 48 * 40 * 6 == st[0].paths
+    assert ms.extend_rays == st1.extend_rays
+
+
+@pytest.mark.gpu
+def test_render_multi_argument_errors(ctx):
+    sb = scene_builder("cornell_book3")
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=16, height=16, spp_count=2)
+    with pytest.raises(rt.B200RTError) as e:
+        rt.render_multi([scene, scene], sb.camera, p)  # two shards on one device
+    assert e.value.status == F.ERR_INVALID and "own device" in str(e.value)
+    with pytest.raises(rt.B200RTError):
+        rt.render_multi([scene], sb.camera, rt.copy_params(p, width=0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", ["nccl", "peer"])
+def test_render_multi_two_devices(ctx, path):
+    if _n_devices() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    sb = scene_builder("book2")
+    ctx1 = rt.Context(1)
+    s0, s1 = rt.Scene(ctx, sb), rt.Scene(ctx1, sb)
+    p = rt.copy_params(sb.params, width=96, height=96, spp_count=9)  # odd: 5 + 4
+    full, _ = s0.render(sb.camera, p)
+    lo, _ = s0.render(sb.camera, rt.copy_params(p, spp_begin=0, spp_count=5))
+    hi, _ = s0.render(sb.camera, rt.copy_params(p, spp_begin=5, spp_count=4))
+    old = os.environ.get("B200RT_MULTI_REDUCE")
+    os.environ["B200RT_MULTI_REDUCE"] = path
+    try:
+        got, st, ms = rt.render_multi([s0, s1], sb.camera, p)
+    finally:
+        if old is None:
+            del os.environ["B200RT_MULTI_REDUCE"]
+        else:
+            os.environ["B200RT_MULTI_REDUCE"] = old
+    assert ms.n_dev == 2 and ms.reduce_path == (F.REDUCE_NCCL if path == "nccl" else F.REDUCE_PEER)
+    assert st[0].paths == 96 * 96 * 5 and st[1].paths == 96 * 96 * 4 and ms.paths == 96 * 96 * 9
+    # device 1 rendered what device 0 renders for the same sample range (up to the order of the per-pixel float adds)
+    np.testing.assert_allclose(got, lo + hi, rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(got, full, rtol=1e-4, atol=1e-4)
+    assert np.all(got[..., 3] == 9)
+    print("render_multi[%s]: render %.2f ms, reduce %.3f ms, wall %.1f ms" % (path, ms.ms_render_max, ms.ms_reduce, ms.ms_wall))

@@ -1,0 +1,82 @@
+"""SPPM integrator at the reference's own configuration: main.rs:33-53 renders
+scene.rs:16-112 (cornell_ref) at 800x800, SPPMIntegrator::new runs 50 iterations x 500,000 photons
+(photon_mapper.rs:148-149), capture_image takes 256 samples per pixel (camera.rs:73).  The device run is timed by
+CUDA events inside b200rt_render_sppm.  The CPU restatement (oracle/, all host threads) would take hours on the full
+job (its k-nearest query costs ~1 ms per pixel and iteration), so it is timed on three bounded samples -- one
+iteration at 100x100 and at 200x200 pixels, and 200x200 with 4 more samples per pixel -- that separate the cost per
+iteration (photon pass + kd-tree), per pixel and iteration (eye pass + k-nearest), and per final-pass sample; the
+full job is those three costs scaled, which is exact for this algorithm (every iteration, pixel and sample costs
+the same on average).  --no-gpu times only the CPU leg (it needs no GPU: can run in the build container).
+usage: python tools/bench_sppm.py [--iterations 50] [--photons 500000] [--spp 256] [--size 800] [--no-cpu | --no-gpu]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np  # noqa: E402
+import rust_raytracer_b200 as rt  # noqa: E402
+from scenes_util import scene_builder  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--iterations", type=int, default=50)
+ap.add_argument("--photons", type=int, default=500000)
+ap.add_argument("--spp", type=int, default=256)
+ap.add_argument("--size", type=int, default=800)
+ap.add_argument("--no-cpu", action="store_true")
+ap.add_argument("--no-gpu", action="store_true")
+ap.add_argument("--repeat", type=int, default=2)
+a = ap.parse_args()
+
+sb = scene_builder("cornell_ref")
+p = rt.copy_params(sb.params, width=a.size, height=a.size, spp_count=a.spp, seed=1)
+out = {"what": "SPPM (photon_mapper.rs): cornell_ref %dx%d, %d iterations x %d photons, %d spp final pass" % (a.size, a.size, a.iterations, a.photons, a.spp)}
+if not a.no_gpu:
+    ctx = rt.Context(0)
+    scene = rt.Scene(ctx, sb)
+    best = None
+    for _ in range(a.repeat):  # the first call also pays the allocations' first touch
+        t0 = time.perf_counter()
+        acc, st = scene.render_sppm(sb.camera, p, iterations=a.iterations, photons_per_iter=a.photons)
+        wall = time.perf_counter() - t0
+        if best is None or st.ms_total < best[0].ms_total:
+            best = (st, wall)
+    st, wall = best
+    img = acc[..., :3] / a.spp
+    n_emit = a.iterations * a.photons
+    n_eye = a.iterations * a.size * a.size
+    n_final = a.spp * a.size * a.size
+    out["gpu"] = {
+        "ms_total": st.ms_total, "ms_photons": st.ms_photons, "ms_grid": st.ms_grid, "ms_eye": st.ms_eye, "ms_final": st.ms_final, "wall_s": wall,
+        "global_photons_stored": int(st.global_photons), "caustic_photons_stored": int(st.caustic_photons),
+        "photon_rays": int(st.photon_rays), "eye_rays": int(st.eye_rays),
+        "Mphotons_emitted_per_s": n_emit / max(st.ms_photons, 1e-9) / 1e3,
+        "Mphoton_rays_per_s": st.photon_rays / max(st.ms_photons, 1e-9) / 1e3,
+        "Meye_updates_per_s": n_eye / max(st.ms_eye, 1e-9) / 1e3,
+        "Mfinal_paths_per_s": n_final / max(st.ms_final, 1e-9) / 1e3,
+        "image_mean": [float(x) for x in np.nan_to_num(img, nan=0.0, posinf=0.0).reshape(-1, 3).mean(axis=0)],
+    }
+if not a.no_cpu:
+    from oracle_ffi import OracleScene  # the checker, timed beside the product (bench leg only)
+    threads = os.cpu_count() or 8
+    osc = OracleScene(sb)
+
+    def cpu(size, spp):
+        t0 = time.perf_counter()
+        osc.sppm_render(sb.camera, rt.copy_params(p, width=size, height=size, spp_count=spp), iterations=1, photons_per_iter=a.photons, n_threads=threads)
+        return time.perf_counter() - t0
+    t100, t200, t200s = cpu(100, 1), cpu(200, 1), cpu(200, 5)
+    per_spp_px = max(t200s - t200, 0.0) / 4 / 40000            # s per final-pass sample
+    per_px = max(t200 - t100 - 30000 * per_spp_px, 0.0) / 30000  # s per pixel and iteration (eye pass + k-nearest)
+    per_iter = max(t100 - 10000 * (per_px + per_spp_px), 0.0)  # s per iteration (photon pass + kd-tree build)
+    npx = a.size * a.size
+    est = a.iterations * (per_iter + npx * per_px) + a.spp * npx * per_spp_px
+    out["cpu_port"] = {"threads": threads, "sample": "1 iteration x %d photons at 100x100 (%.1f s), 200x200 (%.1f s), 200x200 with 5 spp (%.1f s)" % (a.photons, t100, t200, t200s),
+                       "s_per_iteration_fixed": per_iter, "us_per_pixel_iteration": per_px * 1e6, "us_per_final_sample": per_spp_px * 1e6,
+                       "estimated_full_s": est}
+    if "gpu" in out:
+        out["cpu_port"]["speedup_vs_gpu_total"] = est / (out["gpu"]["ms_total"] * 1e-3)
+print(json.dumps(out))
