@@ -285,7 +285,7 @@ def main():
             "traffic_note": "ncu dram bytes per ray of one launch (%.1f B against %d algorithmic: the ray stream is read whole, the rest is local-memory stack traffic) x rays of the average launch" % (EXTEND_DRAM_BYTES_PER_RAY_NCU, EXTEND_BYTES_PER_RAY),
             "bytes_per_ray": EXTEND_BYTES_PER_RAY, "rays_per_launch": rays_per_launch, "launches": n_ext_launches,
             "avg_launch_ms": ext_ms / n_ext_launches, "kernel_share_of_step": ext_ms / max(stats["ms_total"], 1e-9),
-            "note": "BVH traversal is instruction-issue bound under divergence, not HBM bound (scene is L2-resident): see issue, fp32 and DESIGN.md",
+            "note": "BVH traversal is instruction-issue bound under divergence, not HBM bound (scene is L2-resident): see issue, fp32 and DESIGN.md; the duration is the union of the extend launches' event intervals over the two concurrent pipelines (time during which an extend launch was in flight)",
             "issue": EXTEND_NCU,
             "pipeline_bytes_per_segment": SEGMENT_BYTES_PIPELINE,
             "pipeline_hbm_frac": SEGMENT_BYTES_PIPELINE * (ext + shd) / total_s / 1e9 / peaks["hbm_gbs"],
@@ -305,9 +305,11 @@ def main():
             "config": {"workload": "book-2 final scene 800x800 (BASELINE.json configs[3]): 1409 primitives incl. 400 boxes, 1000 instanced spheres, moving sphere, 2 constant media, Perlin + earthmap textures",
                        "spp_per_step_per_gpu": spp, "full_job_spp": FULL_JOB_SPP, "max_depth": 50, "integrator": "path", "pipeline": args.pipeline,
                        "sharding": "spp ranges per rank + NCCL sum-reduce of the accumulation buffer per step",
+                       "concurrent_pipelines": int(os.environ.get("B200RT_WF_PIPES", "2")),
                        "l2": "256 MB write between timed steps; the wavefront queues (2^26 positions x 144 B of ray/state/hit streams = 9.7 GB) exceed L2"},
             "mrays_per_s": mrays, "rays_per_path": (ext + shd) / paths,
             "stage_ms_per_step": {k: stats[k] / args.steps for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total")},
+            "stage_ms_note": "capture_image runs 2 concurrent wavefront pipelines (half of the samples each, own stream): a stage time is the length of the union of that stage's CUDA-event intervals over the pipelines, queueing behind the other pipeline's kernels included, so the stages overlap and add up to more than ms_total",
             "wavefront_iterations_per_step": stats["wavefront_iterations"] / args.steps,
             "roofline": roofline,
             "fp32": {"peak_tflops_measured": fp32_tflops, "effective_sm_mhz": eff_mhz, "how": "k_fma_peak: 8 independent FMA chains/thread, 8 blocks x 256 threads per SM"},

@@ -14,13 +14,15 @@ struct b200rt_ctx {
   cudaStream_t stream = nullptr;
   cudaDeviceProp prop;
   std::string err;
-  // wavefront pool (allocated lazily, reused across renders)
-  WfBuffers wf{};
-  void* wf_block = nullptr;
-  void* wf_shadow_block = nullptr;
+  // wavefront pools, one per concurrent pipeline (allocated lazily, reused across renders)
+  WfBuffers wf[WF_MAX_PIPES] = {};
+  void* wf_block[WF_MAX_PIPES] = {};
+  void* wf_shadow_block[WF_MAX_PIPES] = {};
   size_t wf_bytes = 0;
+  cudaStream_t pipe_stream[WF_MAX_PIPES] = {};  // [0] unused: pipeline 0 runs on `stream`
+  cudaEvent_t fork_ev = nullptr;
   MegaCounters* mega_cnt = nullptr;
-  WfCounters* host_cnt = nullptr;  // pinned
+  WfCounters* host_cnt = nullptr;  // pinned, WF_MAX_PIPES entries
   cudaEvent_t ev[2] = {nullptr, nullptr};
   // World::new staging: one grow-only pinned buffer and one recycled device block per context, so that rebuilding
   // a scene (the e2e path of bench.py) pays no cudaMallocHost / cudaMalloc / cudaFree (each of which can stall
@@ -29,7 +31,7 @@ struct b200rt_ctx {
   size_t stage_bytes = 0;
   void* spare_block = nullptr;
   size_t spare_bytes = 0;
-  cudaEvent_t sev[64] = {};  // stage events: up to 8 iterations in flight x (generate, extend, shade, shadow) x (begin, end)
+  cudaEvent_t sev[128 * WF_MAX_PIPES] = {};  // stage events per pipeline: 2 alternating sets x up to 8 iterations in flight x 8 (generate, extend, shade, shadow boundaries)
 };
 
 struct b200rt_scene {
@@ -90,13 +92,14 @@ int b200rt_ctx_create(int device, b200rt_ctx** out) {
   if (!c) return B200RT_ERR_NOMEM;
   c->device = device;
   if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&c->prop, device)) != cudaSuccess ||
-      (e = cudaMalloc(&c->mega_cnt, sizeof(MegaCounters))) != cudaSuccess || (e = cudaMallocHost(&c->host_cnt, sizeof(WfCounters))) != cudaSuccess ||
-      (e = cudaEventCreate(&c->ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev[1])) != cudaSuccess) {
+      (e = cudaMalloc(&c->mega_cnt, sizeof(MegaCounters))) != cudaSuccess || (e = cudaMallocHost(&c->host_cnt, sizeof(WfCounters) * WF_MAX_PIPES)) != cudaSuccess ||
+      (e = cudaEventCreate(&c->ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->ev[1])) != cudaSuccess ||
+      (e = cudaEventCreate(&c->fork_ev)) != cudaSuccess) {
     g_global_err = std::string("ctx_create: ") + cudaGetErrorString(e);
     delete c;
     return B200RT_ERR_CUDA;
   }
-  for (int i = 0; i < 64 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->sev[i]);
+  for (int i = 0; i < 128 * WF_MAX_PIPES && e == cudaSuccess; ++i) e = cudaEventCreate(&c->sev[i]);
   if (e != cudaSuccess) {
     g_global_err = std::string("ctx_create: ") + cudaGetErrorString(e);
     delete c;
@@ -109,15 +112,19 @@ int b200rt_ctx_create(int device, b200rt_ctx** out) {
 int b200rt_ctx_destroy(b200rt_ctx* c) {
   if (!c) return B200RT_OK;
   cudaSetDevice(c->device);
-  if (c->wf_block) cudaFree(c->wf_block);
-  if (c->wf_shadow_block) cudaFree(c->wf_shadow_block);
+  for (int k = 0; k < WF_MAX_PIPES; ++k) {
+    if (c->wf_block[k]) cudaFree(c->wf_block[k]);
+    if (c->wf_shadow_block[k]) cudaFree(c->wf_shadow_block[k]);
+    if (c->pipe_stream[k]) cudaStreamDestroy(c->pipe_stream[k]);
+  }
+  if (c->fork_ev) cudaEventDestroy(c->fork_ev);
   if (c->spare_block) cudaFree(c->spare_block);
   if (c->stage_host) cudaFreeHost(c->stage_host);
   if (c->mega_cnt) cudaFree(c->mega_cnt);
   if (c->host_cnt) cudaFreeHost(c->host_cnt);
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
-  for (int i = 0; i < 64; ++i) if (c->sev[i]) cudaEventDestroy(c->sev[i]);
+  for (int i = 0; i < 128 * WF_MAX_PIPES; ++i) if (c->sev[i]) cudaEventDestroy(c->sev[i]);
   delete c;
   return B200RT_OK;
 }

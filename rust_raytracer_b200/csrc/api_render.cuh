@@ -1,36 +1,39 @@
 // api_render.cuh — Camera::capture_image (camera.rs:66-128) on the device: the host-side control loop of the
 // wavefront pipeline, the megakernel launch, tonemap and the FP32 peak probe.  Included by api.cu.
 #pragma once
+#include <algorithm>
+#include <utility>
+#include <thread>
 
-static int wf_ensure_pool(b200rt_ctx* ctx, unsigned int pool, bool shadow) {
+static int wf_ensure_pool(b200rt_ctx* ctx, int pipe, unsigned int pool, bool shadow) {
   const size_t P = pool;
-  if (!(ctx->wf_block && ctx->wf.pool == pool)) {
-    if (ctx->wf_block) { cudaFree(ctx->wf_block); ctx->wf_block = nullptr; }
-    if (ctx->wf_shadow_block) { cudaFree(ctx->wf_shadow_block); ctx->wf_shadow_block = nullptr; }
+  if (!(ctx->wf_block[pipe] && ctx->wf[pipe].pool == pool)) {
+    if (ctx->wf_block[pipe]) { cudaFree(ctx->wf_block[pipe]); ctx->wf_block[pipe] = nullptr; }
+    if (ctx->wf_shadow_block[pipe]) { cudaFree(ctx->wf_shadow_block[pipe]); ctx->wf_shadow_block[pipe] = nullptr; }
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
     size_t o_ray[2], o_st[2];
     for (int k = 0; k < 2; ++k) { o_ray[k] = take(P * 32); o_st[k] = take(P * 32); }  // the two ray / state sets
     size_t o_hit = take(P * 16);
     size_t o_bc = take(4 * WF_MAX_BINS), o_bo = take(4 * (WF_MAX_BINS + 1)), o_cnt = take(sizeof(WfCounters));
-    CU_CHECK(ctx, cudaMalloc(&ctx->wf_block, off));
-    char* b = (char*)ctx->wf_block;
-    ctx->wf_bytes = off;
-    ctx->wf.ray = (float4*)(b + o_ray[0]); ctx->wf.ray_n = (float4*)(b + o_ray[1]);
-    ctx->wf.st = (float4*)(b + o_st[0]); ctx->wf.st_n = (float4*)(b + o_st[1]);
-    ctx->wf.hit = (uint4*)(b + o_hit);
-    ctx->wf.bin_count = (unsigned int*)(b + o_bc); ctx->wf.bin_off = (unsigned int*)(b + o_bo);
-    ctx->wf.cnt = (WfCounters*)(b + o_cnt);
-    ctx->wf.sh_o = ctx->wf.sh_d = ctx->wf.sh_c = nullptr; ctx->wf.sh_seed = nullptr;
-    ctx->wf.pool = pool;
+    CU_CHECK(ctx, cudaMalloc(&ctx->wf_block[pipe], off));
+    char* b = (char*)ctx->wf_block[pipe];
+    ctx->wf_bytes = off;  // per pipeline
+    ctx->wf[pipe].ray = (float4*)(b + o_ray[0]); ctx->wf[pipe].ray_n = (float4*)(b + o_ray[1]);
+    ctx->wf[pipe].st = (float4*)(b + o_st[0]); ctx->wf[pipe].st_n = (float4*)(b + o_st[1]);
+    ctx->wf[pipe].hit = (uint4*)(b + o_hit);
+    ctx->wf[pipe].bin_count = (unsigned int*)(b + o_bc); ctx->wf[pipe].bin_off = (unsigned int*)(b + o_bo);
+    ctx->wf[pipe].cnt = (WfCounters*)(b + o_cnt);
+    ctx->wf[pipe].sh_o = ctx->wf[pipe].sh_d = ctx->wf[pipe].sh_c = nullptr; ctx->wf[pipe].sh_seed = nullptr;
+    ctx->wf[pipe].pool = pool;
   }
-  if (shadow && !ctx->wf_shadow_block) {  // shadow requests (52 B per queue position): only the NEE integrator produces them
+  if (shadow && !ctx->wf_shadow_block[pipe]) {  // shadow requests (52 B per queue position): only the NEE integrator produces them
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
     size_t o_sho = take(P * 16), o_shd = take(P * 16), o_shc = take(P * 16), o_shs = take(P * 4);
-    CU_CHECK(ctx, cudaMalloc(&ctx->wf_shadow_block, off));
-    char* b = (char*)ctx->wf_shadow_block;
-    ctx->wf.sh_o = (float4*)(b + o_sho); ctx->wf.sh_d = (float4*)(b + o_shd); ctx->wf.sh_c = (float4*)(b + o_shc); ctx->wf.sh_seed = (unsigned int*)(b + o_shs);
+    CU_CHECK(ctx, cudaMalloc(&ctx->wf_shadow_block[pipe], off));
+    char* b = (char*)ctx->wf_shadow_block[pipe];
+    ctx->wf[pipe].sh_o = (float4*)(b + o_sho); ctx->wf[pipe].sh_d = (float4*)(b + o_shd); ctx->wf[pipe].sh_c = (float4*)(b + o_shc); ctx->wf[pipe].sh_seed = (unsigned int*)(b + o_shs);
   }
   return B200RT_OK;
 }
@@ -63,28 +66,79 @@ static int env_int(const char* name, int dflt, int lo, int hi) {
 
 // Host control loop of the wavefront pipeline.  Iterations are enqueued in batches (no host round trip inside a
 // batch: the control kernels turn the counters over on the device); the counters are polled once per batch.
-static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap& M, float* accum, b200rt_stats* st) {
+//
+// The sample range is split over `n_pipes` independent pipelines (own pool, counters, bins and CUDA stream; the
+// paths are the same ones: the Philox counter carries the global sample index) that add into the same accumulation
+// buffer.  An iteration is a chain of five dependent launches whose persistent extend kernel ends with a tail of a
+// few long rays, and the last ~40 iterations of a call hold few rays each: with two chains in flight the SMs one
+// chain leaves idle run the other's blocks (book-2: +3.7 % with 2 pipelines; profiles/r1_experiments.md).
+struct WfPipeState {
+  WfBuffers B;
+  RenderConst P;
+  PathMap M;
+  cudaStream_t q;
+  cudaEvent_t* sev;
+  WfCounters* host;
+  bool done, in_flight;
+  int set;  // which of the two event sets the batch in flight records into
+};
+
+static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMap& M0, float* accum, b200rt_stats* st) {
   b200rt_ctx* ctx = s->ctx;
-  cudaStream_t q = ctx->stream;
-  // queue positions in flight: 144 B each (9.7 GB at 2^26 — HBM is plentiful, and a larger pool means fewer, fuller
-  // launches: 2^21 -> 2^24 -> 2^26 is +17 % -> +4 % on book-2, profiles/r1_experiments.md)
-  const unsigned long long cap = 1ull << env_int("B200RT_WF_POOL_LOG2", 26, 12, 28);
-  unsigned long long want = (M.total + 31ull) & ~31ull;
-  unsigned int pool = (unsigned int)(want < cap ? want : cap);
-  int rc = wf_ensure_pool(ctx, pool, P.integrator == B200RT_INTEGRATOR_NEE);
-  if (rc) return rc;
-  WfBuffers B = ctx->wf;
+  // queue positions in flight: 144 B each (9.7 GB at 2^26 over all pipelines — HBM is plentiful, and a larger pool means
+  // fewer, fuller launches: 2^21 -> 2^24 -> 2^26 is +17 % -> +4 % on book-2, profiles/r1_experiments.md)
+  const int pool_log2 = env_int("B200RT_WF_POOL_LOG2", 26, 12, 28);
+  // pipelines: 2 by default when each still gets 2^24 paths (same box, 1 -> 2 pipelines: book-2 800x800x128 spp +3.2 %,
+  // 318k-triangle mesh +5.1 %, Cornell NEE +2.2 %, scene_500 -1.2 %, Cornell MixturePDF at 23 M paths -3.3 %: deep
+  // traversals with long launch tails gain, short renders lose to the halved launches; profiles/r1_experiments.md)
+  int n_pipes = env_int("B200RT_WF_PIPES", 2, 1, WF_MAX_PIPES);
+  const unsigned long long min_paths = 1ull << env_int("B200RT_WF_PIPE_MIN_LOG2", 24, 0, 40);
+  while (n_pipes > 1 && (P0.spp_count < n_pipes || M0.total / (unsigned long long)n_pipes < min_paths)) --n_pipes;
+  const unsigned long long cap = (1ull << pool_log2) / (unsigned long long)n_pipes;
+  unsigned int n_bins, bin_mul;
   {  // bin = 1 + umulhi(prim, bin_mul) maps [0, n_prims) onto bins 1 .. n_bins - 1 (one primitive per bin when they fit)
     // 1024 or 2048 bins (shade keeps the offsets in shared memory up to WF_SMEM_BINS; more only pays through the
     // environment override: measured 1024 / 4096 / 16384 on the 318k-triangle mesh: 1862 / 1868 / 1848 Mpaths/s)
     unsigned int nb = s->n_prims + 1u > 1024u ? 2048u : 1024u;
     const int forced = env_int("B200RT_WF_NBINS", 0, 0, WF_MAX_BINS);
     if (forced > 0) nb = (unsigned int)((forced + 1023) & ~1023);
-    B.n_bins = nb;
+    n_bins = nb;
     const unsigned long long m = (((unsigned long long)(nb - 1)) << 32) / (unsigned long long)(s->n_prims > 0 ? s->n_prims : 1);
-    B.bin_mul = m > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)m;
+    bin_mul = m > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)m;
   }
-  CU_CHECK(ctx, cudaMemsetAsync(B.cnt, 0, sizeof(WfCounters), q));
+  const bool nee = P0.integrator == B200RT_INTEGRATOR_NEE;
+  WfPipeState pipes[WF_MAX_PIPES];
+  for (int k = 0; k < n_pipes; ++k) {
+    WfPipeState& W = pipes[k];
+    W.P = P0;
+    const int base = P0.spp_count / n_pipes, rem = P0.spp_count % n_pipes;  // contiguous sample ranges, remainder to the first pipelines
+    W.P.spp_count = base + (k < rem ? 1 : 0);
+    W.P.spp_begin = P0.spp_begin + k * base + (k < rem ? k : rem);
+    W.M = make_path_map(P0.width, P0.height, W.P.spp_count);
+    const unsigned long long want = (W.M.total + 31ull) & ~31ull;
+    const unsigned int pool = (unsigned int)(want < cap ? want : cap);
+    const int rc_pool = wf_ensure_pool(ctx, k, pool, nee);
+    if (rc_pool) return rc_pool;
+    W.B = ctx->wf[k];
+    W.B.n_bins = n_bins; W.B.bin_mul = bin_mul;
+    if (k == 0) W.q = ctx->stream;
+    else {
+      if (!ctx->pipe_stream[k]) CU_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->pipe_stream[k], cudaStreamNonBlocking));
+      W.q = ctx->pipe_stream[k];
+    }
+    W.sev = ctx->sev + 128 * k;
+    W.set = 0;
+    W.host = ctx->host_cnt + k;
+    W.done = W.M.total == 0;
+    W.in_flight = false;
+    std::memset(W.host, 0, sizeof(WfCounters));
+  }
+  // the other pipelines start after whatever the caller queued on the context stream (the zeroed accumulation buffer);
+  // the same event is the time origin of the stage intervals
+  CU_CHECK(ctx, cudaEventRecord(ctx->fork_ev, ctx->stream));
+  for (int k = 1; k < n_pipes; ++k) CU_CHECK(ctx, cudaStreamWaitEvent(pipes[k].q, ctx->fork_ev, 0));
+  int rc = B200RT_OK;
+  for (int k = 0; k < n_pipes; ++k) CU_CHECK(ctx, cudaMemsetAsync(pipes[k].B.cnt, 0, sizeof(WfCounters), pipes[k].q));
   const int sms = ctx->prop.multiProcessorCount;
   {  // traversal lives in L1 (nodes, primitive records, the local-memory stack): ask for the smallest shared-memory carve-out
     const int carve = env_int("B200RT_CARVEOUT", 0, -1, 100);
@@ -96,60 +150,128 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P, const PathMap
   int occ_ext = 1, occ_shadow = 1, occ_shade = 1;
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend, 128, 0));
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow, 128, 0));
-  CU_CHECK(ctx, P.integrator == B200RT_INTEGRATOR_PATH ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_PATH>, 128, 0)
-                : P.integrator == B200RT_INTEGRATOR_MIXTURE ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_MIXTURE>, 128, 0)
-                                                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_NEE>, 128, 0));
+  CU_CHECK(ctx, P0.integrator == B200RT_INTEGRATOR_PATH ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_PATH>, 128, 0)
+                : P0.integrator == B200RT_INTEGRATOR_MIXTURE ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_MIXTURE>, 128, 0)
+                                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_NEE>, 128, 0));
   const int grid_ext = sms * (occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
   const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", occ_shade > 5 ? 5 : (occ_shade > 0 ? occ_shade : 1), 1, 64);
   // (one resident wave of shade blocks: a larger grid widens the window of queue positions in flight, which interleaves
   //  the bins in the compacted output and costs the next extend pass ~5 %; measured in profiles/r1_experiments.md)
   const int batch = env_int("B200RT_WF_BATCH", 4, 1, 8);
+  const int light_scatters = (P0.flags & B200RT_FLAG_LIGHT_SCATTERS) ? 1 : 0;
   uint64_t launches = 0;
   uint32_t iters = 0;
-  float ms_stage[4] = {0.f, 0.f, 0.f, 0.f};
-  const bool nee = P.integrator == B200RT_INTEGRATOR_NEE;
-  for (;;) {
+  std::vector<std::pair<float, float>> intervals[4];  // per stage, ms since fork_ev, over all pipelines
+  // one batch of iterations of one pipeline + the read-back of its counters
+  auto enqueue_batch = [&](WfPipeState& W) -> int {
+    cudaStream_t q = W.q;
+    WfBuffers& B = W.B;
     for (int b = 0; b < batch; ++b) {
-      cudaEvent_t* ev = ctx->sev + 8 * b;
+      cudaEvent_t* ev = W.sev + 64 * W.set + 8 * b;
       cudaEventRecord(ev[0], q);
       // the set shade just compacted the survivors into becomes the current one; generate appends behind them
       std::swap(B.ray, B.ray_n);
       std::swap(B.st, B.st_n);
-      k_wf_generate<<<grid_gen, 256, 0, q>>>(B, P, M);
-      k_wf_control<<<1, 1024, 0, q>>>(B, M);
+      k_wf_generate<<<grid_gen, 256, 0, q>>>(B, W.P, W.M);
+      k_wf_control<<<1, 1024, 0, q>>>(B, W.M);
       cudaEventRecord(ev[1], q);
-      k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, P.t_min, (P.flags & B200RT_FLAG_LIGHT_SCATTERS) ? 1 : 0);
+      k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
       cudaEventRecord(ev[2], q);
       k_wf_control_shade<<<1, 1024, 0, q>>>(B);
-      if (P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
-      else if (P.integrator == B200RT_INTEGRATOR_MIXTURE) k_wf_shade<B200RT_INTEGRATOR_MIXTURE><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
-      else k_wf_shade<B200RT_INTEGRATOR_NEE><<<grid_shade, 128, 0, q>>>(s->dev, B, P, accum);
+      if (W.P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
+      else if (W.P.integrator == B200RT_INTEGRATOR_MIXTURE) k_wf_shade<B200RT_INTEGRATOR_MIXTURE><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
+      else k_wf_shade<B200RT_INTEGRATOR_NEE><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
       cudaEventRecord(ev[3], q);
       launches += 5;
       if (nee) {
         k_wf_control_shadow<<<1, 1, 0, q>>>(B);
-        k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, P.t_min, accum);
+        k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, W.P.t_min, accum);
         cudaEventRecord(ev[4], q);
         launches += 2;
       }
-      iters++;
+      iters++;  // pipeline iterations = extend launches
     }
     CU_CHECK(ctx, cudaGetLastError());
-    CU_CHECK(ctx, cudaMemcpyAsync(ctx->host_cnt, B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, q));
-    CU_CHECK(ctx, cudaStreamSynchronize(q));
+    CU_CHECK(ctx, cudaMemcpyAsync(W.host, B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, q));
+    W.in_flight = true;
+    return B200RT_OK;
+  };
+  // A finished batch: is the pipeline done (counters)?  If not, the next batch goes out FIRST (into the other event
+  // set) and the stage intervals of the finished one are read from its event timestamps while the device is busy.
+  auto collect = [&](WfPipeState& W, int set) {
     for (int b = 0; b < batch; ++b) {
-      cudaEvent_t* ev = ctx->sev + 8 * b;
-      for (int k = 0; k < (nee ? 4 : 3); ++k) {
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, ev[k], ev[k + 1]) == cudaSuccess) ms_stage[k] += ms;
+      cudaEvent_t* ev = W.sev + 64 * set + 8 * b;
+      float t = 0.f;
+      if (cudaEventElapsedTime(&t, ctx->fork_ev, ev[0]) != cudaSuccess) continue;
+      for (int j = 0; j < (nee ? 4 : 3); ++j) {
+        float d = 0.f;
+        if (cudaEventElapsedTime(&d, ev[j], ev[j + 1]) != cudaSuccess) break;
+        intervals[j].emplace_back(t, t + d);
+        t += d;
       }
     }
-    if (ctx->host_cnt->n_ext_next == 0 && ctx->host_cnt->next_path >= M.total) break;
-    if (iters > 100000000u) { ctx->err = "wavefront loop did not terminate"; return B200RT_ERR_CUDA; }
+  };
+  auto harvest = [&](WfPipeState& W) -> int {
+    const int set = W.set;
+    W.in_flight = false;
+    if (W.host->n_ext_next == 0 && W.host->next_path >= W.M.total) W.done = true;
+    else {
+      W.set ^= 1;
+      const int rc_e = enqueue_batch(W);
+      if (rc_e) return rc_e;
+    }
+    collect(W, set);
+    return B200RT_OK;
+  };
+  // Every pipeline is refilled as soon as ITS batch has drained (no lockstep: a pipeline never waits for another one's
+  // batch); with one pipeline left the host blocks on its stream instead of polling.
+  for (unsigned long long guard = 0;; ++guard) {
+    int active = 0, last = -1;
+    for (int k = 0; k < n_pipes; ++k) if (!pipes[k].done) { ++active; last = k; }
+    if (active == 0) break;
+    if (active == 1) {
+      WfPipeState& W = pipes[last];
+      if (!W.in_flight) { rc = enqueue_batch(W); if (rc) return rc; }
+      CU_CHECK(ctx, cudaStreamSynchronize(W.q));
+      rc = harvest(W);
+      if (rc) return rc;
+      continue;
+    }
+    bool progressed = false;
+    for (int k = 0; k < n_pipes; ++k) {
+      WfPipeState& W = pipes[k];
+      if (W.done) continue;
+      if (W.in_flight) {
+        const cudaError_t e = cudaStreamQuery(W.q);
+        if (e == cudaErrorNotReady) continue;
+        if (e != cudaSuccess) { ctx->err = std::string("wavefront: ") + cudaGetErrorString(e); return B200RT_ERR_CUDA; }
+        rc = harvest(W);
+      } else rc = enqueue_batch(W);
+      if (rc) return rc;
+      progressed = true;
+    }
+    if (!progressed) std::this_thread::yield();
+    if (guard > (1ull << 40)) { ctx->err = "wavefront loop did not terminate"; return B200RT_ERR_CUDA; }
   }
+  // stage time = length of the UNION of that stage's intervals over the pipelines (the time during which at least
+  // one pipeline was in the stage)
+  float ms_stage[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int j = 0; j < 4; ++j) {
+    std::sort(intervals[j].begin(), intervals[j].end());
+    float end = -1e30f;
+    for (const auto& x : intervals[j]) {
+      if (x.second <= end) continue;
+      ms_stage[j] += x.second - (x.first > end ? x.first : end);
+      end = x.second;
+    }
+  }
+  cudaGetLastError();
   if (st) {
+    // with more than one pipeline the stages overlap each other (extend of one under shade of the other): the stage
+    // times are union lengths per stage and may add up to more than ms_total
     st->ms_generate = ms_stage[0]; st->ms_extend = ms_stage[1]; st->ms_shade = ms_stage[2]; st->ms_shadow = ms_stage[3];
-    st->extend_rays = ctx->host_cnt->extend_rays - ctx->host_cnt->dead_rays; st->shadow_rays = ctx->host_cnt->shadow_rays;
+    st->extend_rays = 0; st->shadow_rays = 0;
+    for (int k = 0; k < n_pipes; ++k) { st->extend_rays += pipes[k].host->extend_rays - pipes[k].host->dead_rays; st->shadow_rays += pipes[k].host->shadow_rays; }
     st->kernel_launches = launches; st->wavefront_iterations = iters;
   }
   return B200RT_OK;
@@ -197,6 +319,7 @@ int b200rt_render_device(b200rt_scene* s, const b200rt_camera* cam, const b200rt
   CU_CHECK(ctx, cudaEventSynchronize(ctx->ev[1]));
   CU_CHECK(ctx, cudaEventElapsedTime(&local.ms_total, ctx->ev[0], ctx->ev[1]));
   local.ms_other = local.ms_total - local.ms_generate - local.ms_extend - local.ms_shade - local.ms_shadow;
+  if (local.ms_other < 0.f) local.ms_other = 0.f;  // concurrent pipelines: the stages overlap
   if (params->pipeline == B200RT_PIPELINE_MEGAKERNEL) { local.ms_extend = local.ms_total; local.ms_other = 0.f; }
   if (stats) *stats = local;
   return B200RT_OK;

@@ -37,6 +37,7 @@
 #define WF_MAX_BINS 16384    // capacity of the bin tables; the number of bins in use is WfBuffers::n_bins
 #define WF_SMEM_BINS 2048    // shade keeps the offsets in shared memory up to this many bins
 #define WF_NO_BIN 0xffffffffu
+#define WF_MAX_PIPES 4       // concurrent wavefront pipelines per context (api_render.cuh)
 
 struct WfCounters {
   unsigned long long next_path;     // next path id to generate

@@ -84,3 +84,36 @@ def test_render_multi_two_devices(ctx, path):
     np.testing.assert_allclose(got, full, rtol=1e-4, atol=1e-4)
     assert np.all(got[..., 3] == 9)
     print("render_multi[%s]: render %.2f ms, reduce %.3f ms, wall %.1f ms" % (path, ms.ms_render_max, ms.ms_reduce, ms.ms_wall))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("integrator", ["path", "nee"])
+def test_concurrent_pipelines_render_the_same_paths(ctx, integrator):
+    """render_wavefront splits the sample range over concurrent pipelines (own pool / counters / stream, one accumulation
+    buffer): the paths are the same ones (Philox is keyed on the global sample index), so the ray counts are identical
+    and the image equal up to the order of the per-pixel float adds."""
+    sb = scene_builder("cornell_book3")
+    scene = rt.Scene(ctx, sb)
+    kw = dict(integrator=F.INTEGRATOR_NEE) if integrator == "nee" else {}
+    p = rt.copy_params(sb.params, width=64, height=48, spp_count=7, spp_begin=2, **kw)
+    out = {}
+    old = {k: os.environ.get(k) for k in ("B200RT_WF_PIPES", "B200RT_WF_PIPE_MIN_LOG2")}
+    try:
+        os.environ["B200RT_WF_PIPE_MIN_LOG2"] = "0"
+        for n in (1, 2, 3, 4):
+            os.environ["B200RT_WF_PIPES"] = str(n)
+            out[n] = scene.render(sb.camera, p)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    a1, s1 = out[1]
+    assert s1.paths == 64 * 48 * 7
+    for n in (2, 3, 4):
+        a, s = out[n]
+        assert (s.paths, s.extend_rays, s.shadow_rays) == (s1.paths, s1.extend_rays, s1.shadow_rays), n
+        assert s.wavefront_iterations > s1.wavefront_iterations  # iterations are counted per pipeline
+        np.testing.assert_allclose(a, a1, rtol=1e-4, atol=1e-4)
+        assert np.all(a[..., 3] == 7)
