@@ -153,7 +153,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   CU_CHECK(ctx, P0.integrator == B200RT_INTEGRATOR_PATH ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_PATH>, 128, 0)
                 : P0.integrator == B200RT_INTEGRATOR_MIXTURE ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_MIXTURE>, 128, 0)
                                                              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_NEE>, 128, 0));
-  const int grid_ext = sms * (occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
+  const int grid_ext = sms * env_int("B200RT_WF_EXT_GRID", occ_ext > 0 ? occ_ext : 1, 1, occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
   const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", occ_shade > 5 ? 5 : (occ_shade > 0 ? occ_shade : 1), 1, 64);
   // (one resident wave of shade blocks: a larger grid widens the window of queue positions in flight, which interleaves
   //  the bins in the compacted output and costs the next extend pass ~5 %; measured in profiles/r1_experiments.md)

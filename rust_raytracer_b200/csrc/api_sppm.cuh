@@ -7,14 +7,15 @@
 namespace {
 
 struct SppmBuffers {
-  float4 *pg = nullptr, *pc = nullptr;
-  uint32_t *cell_count = nullptr, *start_g = nullptr, *start_c = nullptr, *cursor = nullptr, *index_g = nullptr, *index_c = nullptr;
+  float4 *pg[2] = {nullptr, nullptr}, *pc[2] = {nullptr, nullptr};  // photons in emission order, double-buffered over the iterations
+  float4 *sg = nullptr, *sc = nullptr;  // photons in cell order
+  uint32_t *tile_sum = nullptr, *cell_count = nullptr, *start_g = nullptr, *start_c = nullptr, *cursor = nullptr, *index_g = nullptr, *index_c = nullptr;
   float4 *px_g = nullptr, *px_c = nullptr;
   uint2* px_n = nullptr;
   SppmCounters* cnt = nullptr;
   float* accum = nullptr;
   void release() {
-    void* all[] = {pg, pc, cell_count, start_g, start_c, cursor, index_g, index_c, px_g, px_c, px_n, cnt, accum};
+    void* all[] = {pg[0], pg[1], pc[0], pc[1], sg, sc, tile_sum, cell_count, start_g, start_c, cursor, index_g, index_c, px_g, px_c, px_n, cnt, accum};
     for (void* p : all) if (p) cudaFree(p);
   }
 };
@@ -35,15 +36,19 @@ SppmGrid sppm_make_grid(const float4* photons, const uint32_t* start, const uint
   return G;
 }
 
-int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, const SppmGrid& G, uint32_t* start, uint32_t* index) {
+int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, SppmGrid& G, uint32_t* start, uint32_t* index, float4* sorted) {
   cudaStream_t q = ctx->stream;
   const uint32_t n_cells = (uint32_t)G.res * G.res * G.res;
   CU_CHECK(ctx, cudaMemsetAsync(B.cell_count, 0, sizeof(uint32_t) * n_cells, q));
   const int blocks = ctx->prop.multiProcessorCount * 4;
   if (G.n) k_sppm_grid_count<<<blocks, 256, 0, q>>>(G.photons, G.n, G.lo, G.inv_cell, G.res, B.cell_count);
-  k_sppm_grid_scan<<<1, 1024, 0, q>>>(B.cell_count, n_cells, start, B.cursor);
-  if (G.n) k_sppm_grid_fill<<<blocks, 256, 0, q>>>(G.photons, G.n, G.lo, G.inv_cell, G.res, B.cursor, index);
+  const uint32_t n_tiles = (n_cells + SPPM_SCAN_TILE - 1) / SPPM_SCAN_TILE;  // <= 512 at 128^3 cells
+  k_sppm_scan_tile_sums<<<n_tiles, 1024, 0, q>>>(B.cell_count, n_cells, B.tile_sum);
+  k_sppm_scan_tile_offsets<<<1, 1024, 0, q>>>(B.tile_sum, n_tiles, start, n_cells);
+  k_sppm_scan_cells<<<n_tiles, 1024, 0, q>>>(B.cell_count, n_cells, B.tile_sum, start, B.cursor);
+  if (G.n) k_sppm_grid_fill<<<blocks, 256, 0, q>>>(G.photons, G.n, G.lo, G.inv_cell, G.res, B.cursor, index, sorted);
   CU_CHECK(ctx, cudaGetLastError());
+  G.photons = sorted;  // the eye pass reads the cell-ordered copy
   return B200RT_OK;
 }
 
@@ -69,12 +74,14 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   SppmBuffers B;
   cudaError_t e = cudaSuccess;
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
-  alloc((void**)&B.pg, (size_t)cap * 64); alloc((void**)&B.pc, (size_t)cap * 64);
-  alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
+  for (int k = 0; k < 2; ++k) { alloc((void**)&B.pg[k], (size_t)cap * 64); alloc((void**)&B.pc[k], (size_t)cap * 64); }
+  alloc((void**)&B.sg, (size_t)cap * 64); alloc((void**)&B.sc, (size_t)cap * 64);
+  alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
   alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
   alloc((void**)&B.index_g, 4 * (size_t)cap); alloc((void**)&B.index_c, 4 * (size_t)cap);
   alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
-  alloc((void**)&B.cnt, sizeof(SppmCounters)); alloc((void**)&B.accum, 16 * (size_t)n_pix);
+  alloc((void**)&B.accum, 16 * (size_t)n_pix);
+  alloc((void**)&B.cnt, 3 * sizeof(SppmCounters));  // [0], [1]: the photon pass of even / odd iterations; [2]: eye + final pass
   if (e != cudaSuccess) { B.release(); ctx->err = std::string("sppm: ") + cudaGetErrorString(e); return B200RT_ERR_NOMEM; }
   auto fail = [&](int code) { B.release(); return code; };
 #define SPPM_CHECK(call)                                                                          \
@@ -98,49 +105,93 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   const SppmPixels px{B.px_g, B.px_c, B.px_n};
   const int sms = ctx->prop.multiProcessorCount;
   float ms = 0.f;
+  // Two streams: the photon pass of iteration i+1 (stream qp, the other photon buffer) runs under the grid build and
+  // the eye pass of iteration i (context stream).  Both kernels follow one photon / one pixel per thread through
+  // data-dependent loops and leave most issue slots empty on their own (28 % / 14 % issue-active), so they overlap
+  // almost for free.  Photon maps do not depend on the pixel statistics, only the eye pass does (photon_mapper.rs:154-160).
+  // blocks per SM (150 / 128 registers per thread let 3 / 4 blocks of 128 threads reside).  Measured at the reference
+  // configuration, serial 339 ms; overlapped with a photon grid of 1 / 2 / 3 / 4 blocks per SM: 303 / 276 / 264 / 253 ms
+  const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8), eye_grid = env_int("B200RT_SPPM_EYE_GRID", 4, 1, 8);
+  cudaStream_t qp = nullptr;
+  cudaEvent_t ev_ph[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}, ev_eye[2] = {nullptr, nullptr}, ev_grid = nullptr;  // timing only
+  SppmCounters* hcnt = nullptr;  // pinned: [0], [1] photon counters, [2] eye counters
+  auto fail2 = [&](int code) {
+    if (qp) { cudaStreamSynchronize(qp); cudaStreamDestroy(qp); }
+    cudaStreamSynchronize(q);
+    for (int a = 0; a < 2; ++a) { for (int b = 0; b < 2; ++b) if (ev_ph[a][b]) cudaEventDestroy(ev_ph[a][b]); if (ev_eye[a]) cudaEventDestroy(ev_eye[a]); }
+    if (ev_grid) cudaEventDestroy(ev_grid);
+    if (hcnt) cudaFreeHost(hcnt);
+    return fail(code);
+  };
+#undef SPPM_CHECK
+#define SPPM_CHECK(call)                                                                          \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess) { ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail2(B200RT_ERR_CUDA); } \
+  } while (0)
+  SPPM_CHECK(cudaStreamCreateWithFlags(&qp, cudaStreamNonBlocking));
+  for (int a = 0; a < 2; ++a) { for (int b = 0; b < 2; ++b) SPPM_CHECK(cudaEventCreate(&ev_ph[a][b])); SPPM_CHECK(cudaEventCreate(&ev_eye[a])); }
+  SPPM_CHECK(cudaEventCreate(&ev_grid));
+  SPPM_CHECK(cudaMallocHost(&hcnt, 3 * sizeof(SppmCounters)));
+  std::memset(hcnt, 0, 3 * sizeof(SppmCounters));
+  SPPM_CHECK(cudaMemsetAsync(B.cnt + 2, 0, sizeof(SppmCounters), q));
   SPPM_CHECK(cudaEventRecord(ctx->ev[0], q));
+  SPPM_CHECK(cudaStreamWaitEvent(qp, ctx->ev[0], 0));
+  auto launch_photons = [&](int it) -> cudaError_t {  // on qp, into buffer it & 1
+    const int k = it & 1;
+    SppmCounters h0;
+    std::memset(&h0, 0, sizeof(h0));
+    for (int a = 0; a < 3; ++a) { h0.lo[a] = 0xffffffffu; h0.hi[a] = 0u; }
+    hcnt[k] = h0;
+    cudaError_t e = cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp);
+    if (e == cudaSuccess) e = cudaEventRecord(ev_ph[k][0], qp);
+    if (e != cudaSuccess) return e;
+    k_sppm_photons<<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k);
+    e = cudaEventRecord(ev_ph[k][1], qp);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp);
+    return e;
+  };
+  SPPM_CHECK(launch_photons(0));
   for (int it = 0; it < sp.iterations; ++it) {
-    SppmCounters h;
-    std::memset(&h, 0, sizeof(h));
-    for (int a = 0; a < 3; ++a) { h.lo[a] = 0xffffffffu; h.hi[a] = 0u; }
-    SPPM_CHECK(cudaMemcpyAsync(B.cnt, &h, sizeof(h), cudaMemcpyHostToDevice, q));
-    SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
-    k_sppm_photons<<<sms * 4, 128, 0, q>>>(s->dev, sp, P.key, it, B.pg, B.pc, cap, B.cnt);
-    SPPM_CHECK(cudaEventRecord(ctx->sev[1], q));
-    SPPM_CHECK(cudaMemcpyAsync(&h, B.cnt, sizeof(h), cudaMemcpyDeviceToHost, q));
-    SPPM_CHECK(cudaStreamSynchronize(q));
-    if (h.overflow) { ctx->err = "sppm: photon buffer overflow (more than 16 stored photons per emitted photon)"; return fail(B200RT_ERR_NOMEM); }
+    const int k = it & 1;
+    SPPM_CHECK(cudaStreamSynchronize(qp));  // photon map of this iteration is complete, its counters are on the host
+    const SppmCounters h = hcnt[k];
+    if (cudaEventElapsedTime(&ms, ev_ph[k][0], ev_ph[k][1]) == cudaSuccess) local.ms_photons += ms;
+    if (h.overflow) { ctx->err = "sppm: photon buffer overflow (more than 16 stored photons per emitted photon)"; return fail2(B200RT_ERR_NOMEM); }
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
     if (h.n_global) for (int a = 0; a < 3; ++a) { lo[a] = sppm_unord(h.lo[a]); hi[a] = sppm_unord(h.hi[a]); }
-    const SppmGrid Gg = sppm_make_grid(B.pg, B.start_g, B.index_g, h.n_global, lo, hi);
-    const SppmGrid Gc = sppm_make_grid(B.pc, B.start_c, B.index_c, h.n_caustic, lo, hi);
-    if ((rc = sppm_build_grid(ctx, B, Gg, B.start_g, B.index_g)) != 0) return fail(rc);
-    if ((rc = sppm_build_grid(ctx, B, Gc, B.start_c, B.index_c)) != 0) return fail(rc);
-    SPPM_CHECK(cudaEventRecord(ctx->sev[2], q));
-    k_sppm_eye<<<sms * 4, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt);
-    SPPM_CHECK(cudaEventRecord(ctx->sev[3], q));
-    SPPM_CHECK(cudaMemcpyAsync(&h, B.cnt, sizeof(h), cudaMemcpyDeviceToHost, q));
+    SppmGrid Gg = sppm_make_grid(B.pg[k], B.start_g, B.index_g, h.n_global, lo, hi);
+    SppmGrid Gc = sppm_make_grid(B.pc[k], B.start_c, B.index_c, h.n_caustic, lo, hi);
+    SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
+    if ((rc = sppm_build_grid(ctx, B, Gg, B.start_g, B.index_g, B.sg)) != 0) return fail2(rc);
+    if ((rc = sppm_build_grid(ctx, B, Gc, B.start_c, B.index_c, B.sc)) != 0) return fail2(rc);
+    SPPM_CHECK(cudaEventRecord(ev_grid, q));
+    if (it + 1 < sp.iterations) {
+      // the next photon pass writes the buffer iteration it - 1 used: its grid build read it and has finished (the host
+      // synchronised the context stream at the end of that iteration)
+      SPPM_CHECK(launch_photons(it + 1));
+    }
+    k_sppm_eye<<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2);
+    SPPM_CHECK(cudaEventRecord(ev_eye[k], q));
+    // the grid tables (cell_count, cursor, start, index, sg, sc) are single-buffered and the stage events are reused:
+    // the host lets the eye pass finish before it builds the next grid — the next photon pass is already running
     SPPM_CHECK(cudaStreamSynchronize(q));
+    if (cudaEventElapsedTime(&ms, ctx->sev[0], ev_grid) == cudaSuccess) local.ms_grid += ms;
+    if (cudaEventElapsedTime(&ms, ev_grid, ev_eye[k]) == cudaSuccess) local.ms_eye += ms;
     local.global_photons += h.n_global; local.caustic_photons += h.n_caustic;
-    local.photon_rays += h.photon_rays; local.eye_rays += h.eye_rays;
-    if (cudaEventElapsedTime(&ms, ctx->sev[0], ctx->sev[1]) == cudaSuccess) local.ms_photons += ms;
-    if (cudaEventElapsedTime(&ms, ctx->sev[1], ctx->sev[2]) == cudaSuccess) local.ms_grid += ms;
-    if (cudaEventElapsedTime(&ms, ctx->sev[2], ctx->sev[3]) == cudaSuccess) local.ms_eye += ms;
+    local.photon_rays += h.photon_rays;
   }
   // final pass: capture_image over the SPPM integrator (photon_mapper.rs:327-365)
   const PathMap M = make_path_map(params->width, params->height, params->spp_count);
   const float n_emitted = (float)((double)sp.iterations * (double)sp.photons_per_iter);  // photon_mapper.rs:229-230
-  SppmCounters h;
-  std::memset(&h, 0, sizeof(h));
-  SPPM_CHECK(cudaMemcpyAsync(B.cnt, &h, sizeof(h), cudaMemcpyHostToDevice, q));
   SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
   if (M.total > 0) {
-    k_sppm_final<<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt);
+    k_sppm_final<<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + 2);
     k_add_count<<<(n_pix + 255) / 256, 256, 0, q>>>(B.accum, (int)n_pix, (float)params->spp_count);
   }
   SPPM_CHECK(cudaEventRecord(ctx->sev[1], q));
   SPPM_CHECK(cudaEventRecord(ctx->ev[1], q));
-  SPPM_CHECK(cudaMemcpyAsync(&h, B.cnt, sizeof(h), cudaMemcpyDeviceToHost, q));
+  SPPM_CHECK(cudaMemcpyAsync(hcnt + 2, B.cnt + 2, sizeof(SppmCounters), cudaMemcpyDeviceToHost, q));
   SPPM_CHECK(cudaMemcpyAsync(accum_host, B.accum, 16 * (size_t)n_pix, cudaMemcpyDeviceToHost, q));
   std::vector<float4> hg, hc;
   std::vector<uint2> hn;
@@ -158,11 +209,11 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
       o[0] = hg[i].x; o[1] = hg[i].y; o[2] = hg[i].z; o[3] = hg[i].w; o[4] = (float)hn[i].x;
       o[5] = hc[i].x; o[6] = hc[i].y; o[7] = hc[i].z; o[8] = hc[i].w; o[9] = (float)hn[i].y;
     }
-  local.eye_rays += h.eye_rays;
+  local.eye_rays = hcnt[2].eye_rays;  // eye passes + final pass
   if (cudaEventElapsedTime(&ms, ctx->sev[0], ctx->sev[1]) == cudaSuccess) local.ms_final = ms;
   if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) local.ms_total = ms;
 #undef SPPM_CHECK
-  B.release();
+  fail2(B200RT_OK);  // releases the stream, the events, the pinned counters and the device buffers
   if (stats) *stats = local;
   return B200RT_OK;
 }
