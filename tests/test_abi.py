@@ -82,3 +82,23 @@ def test_cli_fails_loudly_without_a_device(built, tmp_path):
     assert r.returncode == 1 and "no CPU fallback" in r.stderr and not (tmp_path / "o.png").exists()
     r = subprocess.run([CLI, "--scene", "no_such_scene"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 1 and "scene" in r.stderr
+
+
+def test_rust_sys_crate_declares_the_same_symbols():
+    """rust/b200rt-sys (shipped as source: no Rust toolchain here) must declare exactly the entry points of include/b200rt.h,
+    and its repr(C) structs must have the sizes of the ctypes mirrors (same field lists)."""
+    import re
+    src = open(os.path.join(ROOT, "rust", "b200rt-sys", "src", "lib.rs")).read()
+    declared = set(re.findall(r"pub fn (b200rt_\w+)\(", src))
+    assert declared == set(F.PROTOTYPES.keys()), declared ^ set(F.PROTOTYPES.keys())
+    size_of = {"u8": 1, "i32": 4, "u32": 4, "f32": 4, "u64": 8, "i64": 8, "f64": 8}
+    for rust_name, ct in (("b200rt_camera", F.Camera), ("b200rt_params", F.Params), ("b200rt_stats", F.Stats), ("b200rt_hit", F.Hit),
+                          ("b200rt_multi_stats", F.MultiStats), ("b200rt_sppm_params", F.SppmParams), ("b200rt_sppm_stats", F.SppmStats)):
+        text = re.search(r"pub struct %s \{(.*?)\}" % rust_name, src, re.S).group(1)
+        fields = re.findall(r"pub (\w+): (\[?\w+(?:; \d+\])?)", text)
+        assert [f for f, _ in fields] == [f[0] for f in ct._fields_], rust_name
+        total = 0
+        for _, ty in fields:
+            m = re.match(r"\[(\w+); (\d+)\]", ty)
+            total += size_of[m.group(1)] * int(m.group(2)) if m else size_of[ty]
+        assert total == C.sizeof(ct), (rust_name, total, C.sizeof(ct))  # no padding in any of them: naturally aligned field order
