@@ -235,7 +235,7 @@ typedef struct b200rt_builder b200rt_builder;
 int b200rt_abi_version(void);
 int b200rt_device_count(int* count);
 int b200rt_ctx_create(int device, b200rt_ctx** out);
-int b200rt_ctx_destroy(b200rt_ctx* ctx);
+int b200rt_ctx_destroy(b200rt_ctx* ctx); /* destroy the context's scenes first: a scene keeps a pointer to its context */
 /* Run all work of this context on an existing cudaStream_t (NULL = default stream). */
 int b200rt_ctx_set_stream(b200rt_ctx* ctx, void* cuda_stream);
 const char* b200rt_last_error(const b200rt_ctx* ctx);

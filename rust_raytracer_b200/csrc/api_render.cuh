@@ -173,11 +173,11 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
       std::swap(B.ray, B.ray_n);
       std::swap(B.st, B.st_n);
       k_wf_generate<<<grid_gen, 256, 0, q>>>(B, W.P, W.M);
-      k_wf_control<<<1, 1024, 0, q>>>(B, W.M);
+      k_wf_control<<<1, WF_CTRL_THREADS, 0, q>>>(B, W.M);
       cudaEventRecord(ev[1], q);
       k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
       cudaEventRecord(ev[2], q);
-      k_wf_control_shade<<<1, 1024, 0, q>>>(B);
+      k_wf_control_shade<<<1, WF_CTRL_THREADS, 0, q>>>(B);
       if (W.P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
       else if (W.P.integrator == B200RT_INTEGRATOR_MIXTURE) k_wf_shade<B200RT_INTEGRATOR_MIXTURE><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
       else k_wf_shade<B200RT_INTEGRATOR_NEE><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);

@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P,
 }
 
 // One block turns the counters over between generate and extend (no host round trip inside an iteration).
-__global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, 1024>>>
+__global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, WF_CTRL_THREADS>>>
   for (unsigned int k = threadIdx.x; k < B.n_bins; k += blockDim.x) B.bin_count[k] = 0;
   if (threadIdx.x != 0) return;
   WfCounters* c = B.cnt;
@@ -120,18 +120,23 @@ __global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, 1024>>>
   c->extend_rays += c->n_ext;
 }
 // after extend: bin sizes -> offsets in the next set; their total is the number of records shade will write.
-// One block of 1024 threads: every thread owns n_bins / 1024 consecutive bins, the per-thread sums are scanned
-// in shared memory (Hillis-Steele).
-__global__ void k_wf_control_shade(WfBuffers B) {  // <<<1, 1024>>>
-  __shared__ unsigned int sc[2][1024];
+// One block of WF_CTRL_THREADS threads: every thread owns n_bins / WF_CTRL_THREADS consecutive bins, the per-thread sums
+// are scanned in shared memory (Hillis-Steele).  256 threads: with two pipelines in flight this kernel is launched
+// while the other pipeline's persistent extend blocks fill the SMs and a 1024-thread block needs a whole SM to drain
+// first (measured: 128 / 256 / 1024 threads make no difference on book-2, 1475.5 / 1475.8 / 1475.4 Mpaths/s).
+#ifndef WF_CTRL_THREADS
+#define WF_CTRL_THREADS 256  // power of two, divides 1024 (n_bins is a multiple of 1024)
+#endif
+__global__ void __launch_bounds__(WF_CTRL_THREADS) k_wf_control_shade(WfBuffers B) {  // <<<1, WF_CTRL_THREADS>>>
+  __shared__ unsigned int sc[2][WF_CTRL_THREADS];
   const int t = threadIdx.x;
-  const unsigned int per = B.n_bins >> 10, first = (unsigned int)t * per;
+  const unsigned int per = B.n_bins / WF_CTRL_THREADS, first = (unsigned int)t * per;
   unsigned int mine = 0;
   for (unsigned int k = 0; k < per; ++k) mine += B.bin_count[first + k];
   sc[0][t] = mine;
   __syncthreads();
   int cur = 0;
-  for (int d = 1; d < 1024; d <<= 1) {
+  for (int d = 1; d < WF_CTRL_THREADS; d <<= 1) {
     sc[cur ^ 1][t] = sc[cur][t] + (t >= d ? sc[cur][t - d] : 0u);
     cur ^= 1;
     __syncthreads();
@@ -139,7 +144,7 @@ __global__ void k_wf_control_shade(WfBuffers B) {  // <<<1, 1024>>>
   const unsigned int incl = sc[cur][t];
   unsigned int run = incl - mine;
   for (unsigned int k = 0; k < per; ++k) { B.bin_off[first + k] = run; run += B.bin_count[first + k]; }
-  if (t == 1023) { B.bin_off[B.n_bins] = incl; B.cnt->n_ext_next = incl; }
+  if (t == WF_CTRL_THREADS - 1) { B.bin_off[B.n_bins] = incl; B.cnt->n_ext_next = incl; }
 }
 __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->n_shadow; }
 

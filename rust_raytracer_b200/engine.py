@@ -1,5 +1,6 @@
 """Context / Scene / render wrappers over the C ABI (numpy in, numpy out; optional raw device pointers)."""
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -16,6 +17,7 @@ class Context:
         if rc:
             raise B200RTError(rc, F.lib().b200rt_global_error().decode())
         self.device = device
+        self._scenes = weakref.WeakSet()  # a scene must be destroyed before its context (it keeps a pointer to it)
 
     def _ok(self, rc):
         if rc:
@@ -23,6 +25,8 @@ class Context:
 
     def close(self):
         if self._h:
+            for sc in list(self._scenes):  # also at interpreter exit, where objects die in no particular order
+                sc.close()
             F.lib().b200rt_ctx_destroy(self._h)
             self._h = None
 
@@ -66,6 +70,7 @@ class Scene:
         desc = builder_or_desc.desc() if hasattr(builder_or_desc, "desc") else builder_or_desc
         self._h = C.c_void_p()
         ctx._ok(F.lib().b200rt_scene_create(ctx._h, C.byref(desc), C.byref(self._h)))
+        ctx._scenes.add(self)
 
     def close(self):
         if self._h:
