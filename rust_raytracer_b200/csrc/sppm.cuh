@@ -17,6 +17,9 @@
 
 #define SPPM_MAX_K 128      // heap capacity of the k-nearest estimate (100 / 50 upstream)
 #define SPPM_MAX_BOUNCES 4096
+#ifndef SPPM_REFILL_LANES
+#define SPPM_REFILL_LANES 8  // idle lanes of a photon warp that trigger a work fetch
+#endif
 
 struct SppmConst {
   int iterations, photons_per_iter, k_global, k_caustic;
@@ -38,7 +41,7 @@ struct SppmPixels {
   uint2* n;     // photons (global, caustic)
 };
 struct SppmCounters {
-  unsigned int n_global, n_caustic, overflow, pad;
+  unsigned int n_global, n_caustic, overflow, cursor;  // cursor: next photon id of the pass (per-lane work fetch)
   unsigned long long photon_rays, eye_rays;
   unsigned int lo[3], hi[3];  // ordered-uint bounds of the stored photon positions
 };
@@ -143,17 +146,38 @@ DEV void sppm_store(float4* photons, unsigned int* counter, unsigned int cap, un
 __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, uint2 key, int iter, float4* pg, float4* pc, unsigned int cap, SppmCounters* cnt) {
   unsigned long long n_rays = 0;
   unsigned int lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
-  const unsigned int n_warps_total = (gridDim.x * blockDim.x) >> 5;
-  const unsigned int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  for (unsigned int base = warp * 32u; base < (unsigned int)sp.photons_per_iter; base += n_warps_total * 32u) {
-    const unsigned int id = base + lane;
-    bool alive = id < (unsigned int)sp.photons_per_iter;
-    Ray ray;
-    float3 power = f3(0, 0, 0);
-    if (alive) sppm_emit(S, sp, philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x50u), key), philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x51u), key), ray, power);
-    bool has_specular = false, has_diffuse = false;
-    for (int bounce = 1; bounce <= SPPM_MAX_BOUNCES; ++bounce) {  // whole warps stay in the loop for the aggregated appends
-      if (!__any_sync(0xffffffffu, alive)) break;
+  // Per-lane work fetch: a photon walk lasts 1 to dozens of bounces (2.9 on average in the Cornell box), so a warp that
+  // waits for its longest photon runs at 5.6 of 32 lanes (ncu, profiles/r1_sppm_full_summary.txt).  Lanes whose photon
+  // has died take the next photon ids from a global cursor (one warp-aggregated atomic) as soon as SPPM_REFILL_LANES of
+  // them are idle.  Every draw is keyed (photon id, iteration, bounce), so which lane walks which photon changes nothing
+  // but the order of the records in the map.  (The path tracer's extend kernel does NOT do this: there the queue order
+  // is what keeps a warp coherent; here there is no order to lose.)
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned int n_photons = (unsigned int)sp.photons_per_iter;
+  unsigned int id = 0;
+  int bounce = 0;
+  bool alive = false, exhausted = false, has_specular = false, has_diffuse = false;
+  Ray ray;
+  float3 power = f3(0, 0, 0);
+  ray.o = ray.d = f3(0, 0, 0); ray.time = 0.f; ray.tmax = 0.f; ray.mseed = 0u;
+  for (;;) {
+    const unsigned idle = __ballot_sync(0xffffffffu, !alive);
+    if (!exhausted && (__popc(idle) >= SPPM_REFILL_LANES || idle == 0xffffffffu)) {
+      const int leader = __ffs((int)idle) - 1;
+      unsigned int base = 0;
+      if ((int)lane == leader) base = atomicAdd(&cnt->cursor, (unsigned int)__popc(idle));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (!alive) {
+        id = base + __popc(idle & ((1u << lane) - 1u));
+        if (id < n_photons) {
+          sppm_emit(S, sp, philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x50u), key), philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x51u), key), ray, power);
+          alive = true; bounce = 1; has_specular = false; has_diffuse = false;
+        }
+      }
+      exhausted = base + (unsigned int)__popc(idle) >= n_photons;  // warp-uniform
+    }
+    if (!__any_sync(0xffffffffu, alive)) break;  // only reached with the cursor exhausted
+    {
       bool st_g = false, st_c = false;
       float3 hp = f3(0, 0, 0), hn = f3(0, 0, 0), hd = f3(0, 0, 0), hpow = f3(0, 0, 0);
       if (alive) {
@@ -181,10 +205,12 @@ __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, 
             has_diffuse = true;
           } else if (inter == SPPM_ABSORB) alive = false;
           else has_specular = true;
+          if (alive && bounce >= SPPM_MAX_BOUNCES) alive = false;  // upstream loops until absorbed or lost; the cap only guards the kernel
           if (alive) {
             ray.o = h.p; ray.d = dir; ray.tmax = __int_as_float(0x7f800000);
             ray.mseed = philox4x32(make_uint4(id, (uint32_t)iter, (uint32_t)bounce, 0x51u), key).x;
             power = new_power;
+            ++bounce;
           }
         }
       }
