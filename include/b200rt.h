@@ -251,6 +251,12 @@ int b200rt_scene_destroy(b200rt_scene* scene);
 /* Bytes uploaded host->device by scene_create, BVH node count, device prim count. */
 int b200rt_scene_info(const b200rt_scene* scene, uint64_t* h2d_bytes, uint32_t* bvh_nodes, uint32_t* device_prims);
 
+/* Host only (no CUDA): the wide BVH b200rt_scene_create would build for `desc` in place of BVHNode::new (bvh.rs:60-83) —
+ * node count, depth in BVH4 levels, and the traversal-stack entries the deepest path can need (3 per level) against the
+ * per-thread capacity.  scene_create rebuilds an over-deep tree under a depth budget, so needed <= capacity always. */
+int b200rt_scene_compile_stats(const b200rt_scene_desc* desc, uint32_t* bvh_nodes, uint32_t* bvh4_depth,
+                               uint32_t* stack_needed, uint32_t* stack_capacity);
+
 /* ---- World::hit as a batch operator (world.rs:27-29) -------------------- */
 /* o_time: n x (ox,oy,oz,time); d_tmax: n x (dx,dy,dz,t_max); medium_seed: n x u32 or NULL (the draw
  * ConstantMedium::hit takes inside `hit`, medium.rs:37-38, derived as u01(hash(seed, prim))).
@@ -335,6 +341,25 @@ int b200rt_write_png(const char* path, const uint8_t* rgb8, int32_t width, int32
 int b200rt_camera_make(const double look_from[3], const double look_at[3], const double vup[3], double vfov_deg,
                        double aspect, double aperture, double focus_dist, double time0, double time1,
                        b200rt_camera* out);
+
+/* ---- function-level parity operator (tests) ---- */
+/* Evaluates single functions of the hot path on the device at caller-supplied inputs, through the same device functions
+ * the kernels call, so that they can be compared with the reference's point for point:
+ *   TEXTURE  Texture::get_color (material.rs:52-84)       in 8 floats: texture id (i32 bits), p.xyz, u, v, -, -
+ *                                                         out 4: rgb, -
+ *   SCATTER  Material::scatter + emitted (material.rs:86-212) with the bounce's three uniforms injected
+ *                                                         in 20: material id (bits), front_face (bits), p.xyz, n.xyz (unit,
+ *                                                         facing the ray), u, v, incoming d.xyz, u1, u2, u3, time, -, -, -
+ *                                                         out 16: continues, dir.xyz | attenuation rgb, - | emitted rgb, - |
+ *                                                         the on-sphere sample made of (u1, u2) xyz, -
+ *   CAMERA   Camera::get_ray + jitter (camera.rs:57-64, 97-99)  in 2 u32: pixel, sample
+ *                                                         out 16: o.xyz, time | d.xyz, - | jitter x, y, lens disk x, y | time draw
+ *   SAMPLERS the sampling transforms standing in for vec3.rs:111-162   in 8: u1, u2, n.xyz, -, -, -
+ *                                                         out 12: on-sphere xyz, - | cosine hemisphere about n xyz, - | disk xy
+ * Host pointers; cam / params supply the camera, image size, seed and flags. */
+enum b200rt_eval_kind { B200RT_EVAL_TEXTURE = 0, B200RT_EVAL_SCATTER = 1, B200RT_EVAL_CAMERA = 2, B200RT_EVAL_SAMPLERS = 3 };
+int b200rt_debug_eval(b200rt_scene* scene, const b200rt_camera* cam, const b200rt_params* params, int32_t kind, uint64_t n,
+                      const float* in_host, float* out_host);
 
 /* FP32 FMA-issue microbenchmark (roofline denominator). Returns TFLOP/s (FMA = 2). */
 int b200rt_measure_fp32_peak(b200rt_ctx* ctx, double* tflops, double* sm_mhz_effective);

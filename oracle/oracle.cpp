@@ -20,16 +20,19 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cctype>
 #include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <deque>
 #include <limits>
 #include <memory>
 #include <mutex>
 #include <stdexcept>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 
 #include "../include/b200rt.h"
@@ -171,6 +174,20 @@ static inline double medium_xi(uint32_t seed, uint32_t prim) {
   return ((double)(h >> 9) + 0.5) * (1.0 / 8388608.0);
 }
 
+// Injected draws: stands in for thread_rng() where a test supplies the random values
+// themselves, so that Material::scatter and Camera::get_ray can be compared with the device sample for sample.  The
+// device replaces the rejection loops below by non-rejection transforms of its Philox uniforms (distribution-equal);
+// the test reads the transformed sample back from the device and injects THAT here.
+struct Injected {
+  Vec3 sphere;  // what random_in_unit_sphere() returns
+  Vec3 disk;    // what random_in_unit_disk() returns
+  double xi;    // what rng.gen::<f64>() / gen_range(0..1) returns
+  double next() { return xi; }
+  double range(double lo, double hi) { return lo + (hi - lo) * xi; }
+};
+static inline Vec3 random_in_unit_sphere(Injected& rng) { return rng.sphere; }
+static inline Vec3 random_in_unit_disk(Injected& rng) { return rng.disk; }
+
 // vec3.rs:111-129 — Marsaglia: returns a point ON the unit sphere.
 static Vec3 random_in_unit_sphere(Stream& rng) {
   double u, v, r2;
@@ -182,7 +199,6 @@ static Vec3 random_in_unit_sphere(Stream& rng) {
   }
   return Vec3(2. * u * std::sqrt(1. - r2), 2. * v * std::sqrt(1. - r2), 1. - 2. * r2);
 }
-static Vec3 random_unit_vector(Stream& rng) { return random_in_unit_sphere(rng).unit(); }  // vec3.rs:140-142
 static Vec3 random_in_unit_disk(Stream& rng) {                                             // vec3.rs:153-162
   for (;;) {
     Vec3 p(rng.range(-1., 1.), rng.range(-1., 1.), 0.);
@@ -190,6 +206,7 @@ static Vec3 random_in_unit_disk(Stream& rng) {                                  
     return p;
   }
 }
+template <class R> static Vec3 random_unit_vector(R& rng) { return random_in_unit_sphere(rng).unit(); }  // vec3.rs:140-142
 
 // ---------------------------------------------------------------- ray.rs:3-15 (+ time, + medium seed)
 struct Ray {
@@ -455,6 +472,7 @@ struct Triangle : Hitable {
   Vec3 pa, pb, pc, na, nb, nc;
   const Material* material;
   int prim;
+  double pad = 0.1;  // mesh.rs:33-42; tests may shrink it (the padding never changes hit results, only how much the BVH prunes)
   bool hit(const Ray& ray, double t_min, double t_max, HitRecord& rec) const override {  // mesh.rs:56-137
     Vec3 edge0 = pb - pa, edge1 = pc - pa;
     Vec3 s0 = cross(ray.dir, edge1);
@@ -475,8 +493,8 @@ struct Triangle : Hitable {
     return true;
   }
   bool bounding_box(AABB& out) const override {  // mesh.rs:33-42 (padded by 0.1 on every axis)
-    out.maximum = Vec3(std::fmax(std::fmax(pa.x, pb.x), pc.x) + 0.1, std::fmax(std::fmax(pa.y, pb.y), pc.y) + 0.1, std::fmax(std::fmax(pa.z, pb.z), pc.z) + 0.1);
-    out.minimum = Vec3(std::fmin(std::fmin(pa.x, pb.x), pc.x) - 0.1, std::fmin(std::fmin(pa.y, pb.y), pc.y) - 0.1, std::fmin(std::fmin(pa.z, pb.z), pc.z) - 0.1);
+    out.maximum = Vec3(std::fmax(std::fmax(pa.x, pb.x), pc.x) + pad, std::fmax(std::fmax(pa.y, pb.y), pc.y) + pad, std::fmax(std::fmax(pa.z, pb.z), pc.z) + pad);
+    out.minimum = Vec3(std::fmin(std::fmin(pa.x, pb.x), pc.x) - pad, std::fmin(std::fmin(pa.y, pb.y), pc.y) - pad, std::fmin(std::fmin(pa.z, pb.z), pc.z) - pad);
     return true;
   }
 };
@@ -604,7 +622,7 @@ struct Material {
   int type = 0;
   const Texture* tex = nullptr;
   double param = 0;
-  static Vec3 scattered_direction(Vec3 n, Stream& rng) {  // material.rs:92-98
+  template <class R> static Vec3 scattered_direction(Vec3 n, R& rng) {  // material.rs:92-98
     Vec3 d = n + random_unit_vector(rng);
     if (d.is_near_zero()) d = n;
     return d;
@@ -619,7 +637,7 @@ struct Material {
     return type == B200RT_MAT_DIFFUSE_LIGHT ? tex->get_color(rec) : Vec3::zero();
   }
   bool is_diffuse() const { return type == B200RT_MAT_LAMBERTIAN || type == B200RT_MAT_ISOTROPIC; }
-  ScatterResult scatter(const Ray& r, const HitRecord& rec, Stream& rng) const {
+  template <class R> ScatterResult scatter(const Ray& r, const HitRecord& rec, R& rng) const {
     ScatterResult s;
     switch (type) {
       case B200RT_MAT_LAMBERTIAN:  // material.rs:109-112
@@ -667,7 +685,7 @@ struct Material {
 struct Camera {
   Vec3 origin, llc, horizontal, vertical, u, v, w;
   double lens_radius, time0, time1;
-  Ray get_ray(double s, double t, Stream& rng) const {  // camera.rs:57-64
+  template <class R> Ray get_ray(double s, double t, R& rng) const {  // camera.rs:57-64
     Vec3 rd = lens_radius * random_in_unit_disk(rng);
     Vec3 offset = u * rd.x + v * rd.y;
     double time = time0;
@@ -722,8 +740,8 @@ struct Light {  // book-3 HittablePDF target; absent upstream (nearest analogue 
 };
 
 struct Scene {
-  std::vector<Material> materials;
-  std::vector<Texture> textures;
+  std::deque<Material> materials;  // deques: the object graph holds pointers into them while they grow
+  std::deque<Texture> textures;
   std::vector<uint8_t> image_data;
   std::vector<b200rt_image> images;
   b200rt_perlin perlin;
@@ -1119,6 +1137,8 @@ static Camera make_camera(const b200rt_camera& c) {
   return cam;
 }
 
+#include "oracle_scenes.inc"
+
 }  // namespace oracle
 
 // ======================================================================= C entry points (ctypes)
@@ -1144,6 +1164,51 @@ void* oracle_scene_create(const b200rt_scene_desc* desc, uint64_t bvh_seed) {
   catch (const std::exception& e) { g_err = e.what(); return nullptr; }
 }
 void oracle_scene_destroy(void* s) { delete (Scene*)s; }
+
+// The oracle's own construction of the canonical workloads and of the JSON scene files (oracle_scenes.inc): the object
+// graph is built directly, reference style, without ever seeing the product's tables.  tri_pad <= 0 keeps mesh.rs:33-42's 0.1.
+void* oracle_scene_make(const char* name, uint64_t seed, uint64_t bvh_seed, const char* aux_path, const uint8_t* earth, int32_t ew, int32_t eh, double aspect, double tri_pad,
+                        b200rt_camera* cam_out, b200rt_params* params_out) {
+  try {
+    SceneMaker mk(bvh_seed);
+    if (tri_pad > 0) mk.tri_pad = tri_pad;
+    b200rt_camera cam;
+    b200rt_params par;
+    const std::string n(name ? name : "");
+    Scene* sc = nullptr;
+    if (n == "book1") sc = make_book1(mk, seed, aspect, &cam, &par);
+    else if (n == "cornell_ref") sc = make_cornell_ref(mk, aux_path ? aux_path : "data/mesh/cube.obj", aspect, &cam, &par);
+    else if (n == "cornell_book3") sc = make_cornell_book3(mk, aspect, &cam, &par);
+    else if (n == "book2") sc = make_book2(mk, seed, earth, ew, eh, aspect, &cam, &par);
+    else if (n == "mesh") sc = make_mesh_scene(mk, aux_path ? aux_path : "data/mesh/bun315.obj", 3, aspect, &cam, &par);
+    else if (n == "mesh_small") sc = make_mesh_scene(mk, aux_path ? aux_path : "data/mesh/bun315.obj", 0, aspect, &cam, &par);
+    else throw std::runtime_error("unknown scene '" + n + "'");
+    if (cam_out) *cam_out = cam;
+    if (params_out) *params_out = par;
+    return sc;
+  } catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
+void* oracle_scene_load_json(const char* text, uint64_t len, uint64_t bvh_seed, b200rt_camera* cam_out) {
+  try {
+    SceneMaker mk(bvh_seed);
+    return make_json_scene(mk, text, (size_t)len, cam_out);
+  } catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
+uint64_t oracle_scene_prim_count(void* s) { return (uint64_t)((Scene*)s)->n_prims; }
+int oracle_scene_material_count(void* s) { return (int)((Scene*)s)->materials.size(); }
+// (type, param, texture type) of material i — lets a test pick matching materials on both sides without sharing tables
+int oracle_scene_material_info(void* s, int i, int32_t* type, double* param, int32_t* tex_type) {
+  const Scene& sc = *(Scene*)s;
+  if (i < 0 || (size_t)i >= sc.materials.size()) return 1;
+  *type = sc.materials[i].type; *param = sc.materials[i].param; *tex_type = sc.materials[i].tex->type;
+  return 0;
+}
+int oracle_scene_texture_of_material(void* s, int i) {
+  const Scene& sc = *(Scene*)s;
+  if (i < 0 || (size_t)i >= sc.materials.size()) return -1;
+  for (size_t t = 0; t < sc.textures.size(); ++t) if (&sc.textures[t] == sc.materials[i].tex) return (int)t;
+  return -1;
+}
 
 // World::hit (world.rs:27-29) over a batch.  o_time: n x (ox,oy,oz,time), d_tmax: n x (dx,dy,dz,t_max).
 int oracle_hit_batch(void* scene, const float* o_time, const float* d_tmax, const uint32_t* mseed, uint64_t n, double t_min, oracle_hit* out) {
@@ -1355,6 +1420,49 @@ int oracle_texture_eval(void* scene, int tex, uint64_t n, const double* p_uv /* 
     rec.p = Vec3(p_uv[5 * i], p_uv[5 * i + 1], p_uv[5 * i + 2]); rec.u = p_uv[5 * i + 3]; rec.v = p_uv[5 * i + 4];
     Vec3 c = sc.textures[tex].get_color(rec);
     rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+  }
+  return 0;
+}
+
+// Material::scatter + emitted at injected draws.  in: n x 20 doubles (material id, front_face, p.xyz, normal.xyz (unit,
+// facing the ray), u, v, incoming d.xyz, sphere sample xyz, xi, time); out: n x 12 doubles (has_ray, dir.xyz,
+// attenuation rgb, emitted rgb, interaction, -).
+int oracle_scatter_eval(void* scene, uint64_t n, const double* in, double* out) {
+  const Scene& sc = *(Scene*)scene;
+  for (uint64_t i = 0; i < n; ++i) {
+    const double* a = in + 20 * i;
+    const int mi = (int)a[0];
+    if (mi < 0 || (size_t)mi >= sc.materials.size()) return 1;
+    const Material& m = sc.materials[mi];
+    HitRecord rec;
+    rec.front_face = a[1] != 0.; rec.p = Vec3(a[2], a[3], a[4]); rec.normal = Vec3(a[5], a[6], a[7]); rec.u = a[8]; rec.v = a[9];
+    rec.t = 1.; rec.mat = &m;
+    const Vec3 d(a[10], a[11], a[12]);
+    Ray r(rec.p - d, d, a[17]);
+    Injected inj;
+    inj.sphere = Vec3(a[13], a[14], a[15]); inj.disk = Vec3::zero(); inj.xi = a[16];
+    const ScatterResult s = m.scatter(r, rec, inj);
+    const Vec3 le = m.emitted(rec);
+    double* o = out + 12 * i;
+    o[0] = s.has_ray ? 1. : 0.; o[1] = s.ray.dir.x; o[2] = s.ray.dir.y; o[3] = s.ray.dir.z;
+    o[4] = s.attenuation.x; o[5] = s.attenuation.y; o[6] = s.attenuation.z;
+    o[7] = le.x; o[8] = le.y; o[9] = le.z; o[10] = (double)s.inter; o[11] = 0.;
+  }
+  return 0;
+}
+
+// Camera::get_ray with the jitter of camera.rs:97-99 at injected draws.  in: n x 7 doubles (x, y, jitter x, jitter y,
+// lens disk x, lens disk y, time draw); out: n x 7 doubles (origin, direction, time).
+int oracle_camera_eval(const b200rt_camera* cam_in, int width, int height, uint64_t n, const double* in, double* out) {
+  const Camera cam = make_camera(*cam_in);
+  for (uint64_t i = 0; i < n; ++i) {
+    const double* a = in + 7 * i;
+    const double u = (a[0] + a[2]) / (double)(width - 1), v = (a[1] + a[3]) / (double)(height - 1);
+    Injected inj;
+    inj.sphere = Vec3::zero(); inj.disk = Vec3(a[4], a[5], 0.); inj.xi = a[6];
+    const Ray r = cam.get_ray(u, 1.0 - v, inj);
+    double* o = out + 7 * i;
+    o[0] = r.orig.x; o[1] = r.orig.y; o[2] = r.orig.z; o[3] = r.dir.x; o[4] = r.dir.y; o[5] = r.dir.z; o[6] = r.time;
   }
   return 0;
 }

@@ -119,6 +119,8 @@ mod manual {
         pub fn b200rt_scene_create(ctx: *mut b200rt_ctx, desc: *const b200rt_scene_desc, out: *mut *mut b200rt_scene) -> c_int;
         pub fn b200rt_scene_destroy(scene: *mut b200rt_scene) -> c_int;
         pub fn b200rt_scene_info(scene: *const b200rt_scene, h2d_bytes: *mut u64, bvh_nodes: *mut u32, device_prims: *mut u32) -> c_int;
+    pub fn b200rt_scene_compile_stats(desc: *const b200rt_scene_desc, bvh_nodes: *mut u32, bvh4_depth: *mut u32, stack_needed: *mut u32, stack_capacity: *mut u32) -> c_int;
+    pub fn b200rt_debug_eval(scene: *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, kind: i32, n: u64, in_host: *const f32, out_host: *mut f32) -> c_int;
         // ---- World::hit over a batch (world.rs:27-29)
         pub fn b200rt_intersect_batch(scene: *mut b200rt_scene, o_time: *const f32, d_tmax: *const f32, medium_seed: *const u32, n: u64, t_min: f32, out: *mut b200rt_hit) -> c_int;
         pub fn b200rt_intersect_batch_device(scene: *mut b200rt_scene, o_time: *const f32, d_tmax: *const f32, medium_seed: *const u32, n: u64, t_min: f32, out: *mut b200rt_hit) -> c_int;

@@ -19,6 +19,7 @@ PIPELINE_WAVEFRONT, PIPELINE_MEGAKERNEL = range(2)
 BACKGROUND_CONSTANT, BACKGROUND_SKY = range(2)
 SCENE_FLAT_LIST = 1
 FLAG_LIGHT_SCATTERS = 1
+EVAL_TEXTURE, EVAL_SCATTER, EVAL_CAMERA, EVAL_SAMPLERS = range(4)
 
 
 class Prim(C.Structure):
@@ -112,6 +113,8 @@ PROTOTYPES = {
     "b200rt_scene_create": (C.c_int, [VP, C.POINTER(SceneDesc), C.POINTER(VP)]),
     "b200rt_scene_destroy": (C.c_int, [VP]),
     "b200rt_scene_info": (C.c_int, [VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "b200rt_scene_compile_stats": (C.c_int, [C.POINTER(SceneDesc), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "b200rt_debug_eval": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), C.c_int32, C.c_uint64, VP, VP]),
     "b200rt_intersect_batch": (C.c_int, [VP, VP, VP, VP, C.c_uint64, C.c_float, VP]),
     "b200rt_intersect_batch_device": (C.c_int, [VP, VP, VP, VP, C.c_uint64, C.c_float, VP]),
     "b200rt_render_device": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, C.POINTER(Stats)]),

@@ -208,7 +208,7 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
   sc->dev.prim_obj = (const float4*)(base + parts[12].off);
   sc->dev.instances_d = (const double*)(base + parts[13].off);
   sc->dev.inst_eps = (const float*)(base + parts[14].off);
-  sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_bvh_prims = (int)cs.n_bvh_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0;
+  sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_bvh_prims = (int)cs.n_bvh_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0; sc->dev.has_objf = cs.has_objf ? 1 : 0;
   sc->h2d_bytes = total; sc->n_nodes = cs.n_nodes; sc->n_prims = cs.n_prims;
   *out = sc;
   return B200RT_OK;
@@ -277,3 +277,4 @@ int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_
 #include "api_render.cuh"
 #include "api_sppm.cuh"
 #include "api_multi.cuh"
+#include "api_debug.cuh"

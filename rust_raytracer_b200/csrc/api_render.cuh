@@ -83,6 +83,36 @@ struct WfPipeState {
   int set;  // which of the two event sets the batch in flight records into
 };
 
+#ifdef B200RT_COUNTERS
+// Debug builds only (tools/dbg/dump_rays.py): after the extend launch of one iteration, write every `stride`-th batch of
+// 32 consecutive queue positions (ray, hit, per-ray node / leaf counts), the bin offsets and the root node to a file.
+static void dbg_dump_iteration(b200rt_scene* s, const WfBuffers& B, cudaStream_t q, const unsigned int* steps_dev, const char* path, int stride) {
+  cudaStreamSynchronize(q);
+  WfCounters c;
+  cudaMemcpy(&c, B.cnt, sizeof(c), cudaMemcpyDeviceToHost);
+  const unsigned int n_warps = c.n_ext / 32u, nw = n_warps / (unsigned)stride;
+  std::vector<float> rays((size_t)nw * 32 * 8), root(32);
+  std::vector<unsigned int> hits((size_t)nw * 32 * 4), steps((size_t)nw * 32), off(B.n_bins + 1);
+  if (nw) {
+    cudaMemcpy2D(rays.data(), 1024, B.ray, (size_t)stride * 1024, 1024, nw, cudaMemcpyDeviceToHost);
+    cudaMemcpy2D(hits.data(), 512, B.hit, (size_t)stride * 512, 512, nw, cudaMemcpyDeviceToHost);
+    cudaMemcpy2D(steps.data(), 128, steps_dev, (size_t)stride * 128, 128, nw, cudaMemcpyDeviceToHost);
+  }
+  cudaMemcpy(off.data(), B.bin_off, 4 * (B.n_bins + 1), cudaMemcpyDeviceToHost);  // offsets of the set extend just read (scanned last iteration)
+  cudaMemcpy(root.data(), s->dev.nodes, 128, cudaMemcpyDeviceToHost);
+  FILE* f = std::fopen(path, "wb");
+  if (!f) return;
+  const unsigned int hdr[8] = {c.n_ext, (unsigned)stride, nw, B.n_bins, B.bin_mul, (unsigned)s->dev.n_prims, (unsigned)s->dev.n_bvh_prims, 0u};
+  std::fwrite(hdr, 4, 8, f);
+  std::fwrite(off.data(), 4, off.size(), f);
+  std::fwrite(root.data(), 4, 32, f);
+  std::fwrite(rays.data(), 4, rays.size(), f);
+  std::fwrite(hits.data(), 4, hits.size(), f);
+  std::fwrite(steps.data(), 4, steps.size(), f);
+  std::fclose(f);
+}
+#endif
+
 static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMap& M0, float* accum, b200rt_stats* st) {
   b200rt_ctx* ctx = s->ctx;
   // queue positions in flight: 144 B each (9.7 GB at 2^26 over all pipelines — HBM is plentiful, and a larger pool means
@@ -94,6 +124,12 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   int n_pipes = env_int("B200RT_WF_PIPES", 2, 1, WF_MAX_PIPES);
   const unsigned long long min_paths = 1ull << env_int("B200RT_WF_PIPE_MIN_LOG2", 24, 0, 40);
   while (n_pipes > 1 && (P0.spp_count < n_pipes || M0.total / (unsigned long long)n_pipes < min_paths)) --n_pipes;
+#ifdef B200RT_COUNTERS
+  const char* dump_path = std::getenv("B200RT_DBG_DUMP");
+  const int dump_iter = env_int("B200RT_DBG_DUMP_ITER", 12, 0, 1 << 20), dump_stride = env_int("B200RT_DBG_DUMP_STRIDE", 128, 1, 1 << 20);
+  unsigned int* dump_steps = nullptr;
+  if (dump_path && *dump_path) n_pipes = 1;
+#endif
   const unsigned long long cap = (1ull << pool_log2) / (unsigned long long)n_pipes;
   unsigned int n_bins, bin_mul;
   {  // bin = 1 + umulhi(prim, bin_mul) maps [0, n_prims) onto bins 1 .. n_bins - 1 (one primitive per bin when they fit)
@@ -139,17 +175,26 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   for (int k = 1; k < n_pipes; ++k) CU_CHECK(ctx, cudaStreamWaitEvent(pipes[k].q, ctx->fork_ev, 0));
   int rc = B200RT_OK;
   for (int k = 0; k < n_pipes; ++k) CU_CHECK(ctx, cudaMemsetAsync(pipes[k].B.cnt, 0, sizeof(WfCounters), pipes[k].q));
+#ifdef B200RT_COUNTERS
+  if (dump_path && *dump_path) {
+    CU_CHECK(ctx, cudaMalloc(&dump_steps, 4 * (size_t)pipes[0].B.pool));
+    CU_CHECK(ctx, cudaMemcpyToSymbol(g_dbg_steps, &dump_steps, sizeof(dump_steps)));
+  }
+#endif
   const int sms = ctx->prop.multiProcessorCount;
   {  // traversal lives in L1 (nodes, primitive records, the local-memory stack): ask for the smallest shared-memory carve-out
     const int carve = env_int("B200RT_CARVEOUT", 0, -1, 100);
     if (carve >= 0) {
-      cudaFuncSetAttribute(k_wf_extend, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-      cudaFuncSetAttribute(k_wf_shadow, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+      cudaFuncSetAttribute(k_wf_extend<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+      cudaFuncSetAttribute(k_wf_extend<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+      cudaFuncSetAttribute(k_wf_shadow<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+      cudaFuncSetAttribute(k_wf_shadow<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
     }
   }
   int occ_ext = 1, occ_shadow = 1, occ_shade = 1;
-  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend, 128, 0));
-  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow, 128, 0));
+  const bool objf = s->dev.has_objf != 0;  // any primitive filtered in object space (rotated Cube / rectangle, ellipsoid)?
+  CU_CHECK(ctx, objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<false>, 128, 0));
+  CU_CHECK(ctx, objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow<false>, 128, 0));
   CU_CHECK(ctx, P0.integrator == B200RT_INTEGRATOR_PATH ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_PATH>, 128, 0)
                 : P0.integrator == B200RT_INTEGRATOR_MIXTURE ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_MIXTURE>, 128, 0)
                                                              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_NEE>, 128, 0));
@@ -175,7 +220,11 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
       k_wf_generate<<<grid_gen, 256, 0, q>>>(B, W.P, W.M);
       k_wf_control<<<1, WF_CTRL_THREADS, 0, q>>>(B, W.M);
       cudaEventRecord(ev[1], q);
-      k_wf_extend<<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
+      if (objf) k_wf_extend<true><<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
+      else k_wf_extend<false><<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
+#ifdef B200RT_COUNTERS
+      if (dump_steps && (int)iters == dump_iter) dbg_dump_iteration(s, B, q, dump_steps, dump_path, dump_stride);
+#endif
       cudaEventRecord(ev[2], q);
       k_wf_control_shade<<<1, WF_CTRL_THREADS, 0, q>>>(B);
       if (W.P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
@@ -185,7 +234,8 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
       launches += 5;
       if (nee) {
         k_wf_control_shadow<<<1, 1, 0, q>>>(B);
-        k_wf_shadow<<<grid_shadow, 128, 0, q>>>(s->dev, B, W.P.t_min, accum);
+        if (objf) k_wf_shadow<true><<<grid_shadow, 128, 0, q>>>(s->dev, B, W.P.t_min, accum);
+        else k_wf_shadow<false><<<grid_shadow, 128, 0, q>>>(s->dev, B, W.P.t_min, accum);
         cudaEventRecord(ev[4], q);
         launches += 2;
       }
@@ -266,6 +316,9 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
     }
   }
   cudaGetLastError();
+#ifdef B200RT_COUNTERS
+  if (dump_steps) { unsigned int* z = nullptr; cudaMemcpyToSymbol(g_dbg_steps, &z, sizeof(z)); cudaFree(dump_steps); }
+#endif
   if (st) {
     // with more than one pipeline the stages overlap each other (extend of one under shade of the other): the stage
     // times are union lengths per stage and may add up to more than ms_total

@@ -147,7 +147,8 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     cudaError_t e = cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp);
     if (e == cudaSuccess) e = cudaEventRecord(ev_ph[k][0], qp);
     if (e != cudaSuccess) return e;
-    k_sppm_photons<<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k);
+    if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k);
+    else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k);
     e = cudaEventRecord(ev_ph[k][1], qp);
     if (e == cudaSuccess) e = cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp);
     return e;
@@ -175,7 +176,8 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
       SPPM_CHECK(cudaStreamWaitEvent(qp, ev_grid, 0));
       SPPM_CHECK(launch_photons(it + 1));
     }
-    k_sppm_eye<<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2);
+    if (s->dev.has_objf) k_sppm_eye<true><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2);
+    else k_sppm_eye<false><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2);
     SPPM_CHECK(cudaEventRecord(ev_eye[k], q));
     // the grid tables (cell_count, cursor, start, index, sg, sc) are single-buffered and the stage events are reused:
     // the host lets the eye pass finish before it builds the next grid — the next photon pass is already running
@@ -192,7 +194,8 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   const float n_emitted = (float)((double)sp.iterations * (double)sp.photons_per_iter);  // photon_mapper.rs:229-230
   SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
   if (M.total > 0) {
-    k_sppm_final<<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + 2);
+    if (s->dev.has_objf) k_sppm_final<true><<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + 2);
+    else k_sppm_final<false><<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + 2);
     k_add_count<<<(n_pix + 255) / 256, 256, 0, q>>>(B.accum, (int)n_pix, (float)params->spp_count);
   }
   SPPM_CHECK(cudaEventRecord(ctx->sev[1], q));

@@ -29,9 +29,9 @@ int push_prim(b200rt_builder* b, const b200rt_prim& p) {
   return (int)b->prims.size() - 1;
 }
 
-// Flat-shaded triangle pair / box used when a Transform with rotation wraps an axis-aligned shape:
-// rotated rectangles are no longer axis-aligned, so they are emitted as triangles carrying the face normal
-// (Triangle::hit blends identical vertex normals back into that normal, mesh.rs:104).
+// Every shape keeps its own type under any Transform (transform.rs:17-165): a rotated Cube stays ONE box primitive with
+// an instance matrix (the device filters and decides it in object space), so rectangle uv (rectangle.rs:32,70,107) and
+// the six-rect tie rule of cube.rs:63-66 survive the rotation.
 int add_triangle(b200rt_builder* b, D3 pa, D3 pb, D3 pc, D3 na, D3 nb, D3 nc, int32_t material) {
   b200rt_prim p;
   std::memset(&p, 0, sizeof(p));
@@ -44,15 +44,6 @@ int add_triangle(b200rt_builder* b, D3 pa, D3 pb, D3 pc, D3 na, D3 nb, D3 nc, in
   if (id >= 0) b->tri_normals.insert(b->tri_normals.end(), n, n + 9);
   return id;
 }
-
-int add_quad_as_triangles(b200rt_builder* b, D3 q, D3 eu, D3 ev, D3 n, int32_t material) {
-  int id = add_triangle(b, q, q + eu, q + eu + ev, n, n, n, material);
-  if (id < 0) return id;
-  int id2 = add_triangle(b, q, q + eu + ev, q + ev, n, n, n, material);
-  return id2 < 0 ? id2 : id;
-}
-
-bool top_is_axis_preserving(const b200rt_builder* b) { return b->xf_stack.empty() || b->xf_stack.back().is_positive_diagonal(); }
 
 }  // namespace
 
@@ -101,7 +92,8 @@ int b200rt_builder_seed_perlin(b200rt_builder* b, uint64_t seed) {
   if (!b) return B200RT_ERR_INVALID;
   Pcg32 rng(seed, 7);
   for (int i = 0; i < 256; ++i) {
-    D3 v = unit(D3(rng.range(-1, 1), rng.range(-1, 1), rng.range(-1, 1)));
+    const double x = rng.range(-1, 1), y = rng.range(-1, 1), z = rng.range(-1, 1);  // sequenced: x, y, z (argument evaluation order is unspecified)
+    D3 v = unit(D3(x, y, z));
     b->perlin.ranvec[i][0] = (float)v.x; b->perlin.ranvec[i][1] = (float)v.y; b->perlin.ranvec[i][2] = (float)v.z; b->perlin.ranvec[i][3] = 0;
   }
   int32_t* perms[3] = {b->perlin.perm_x, b->perlin.perm_y, b->perlin.perm_z};
@@ -165,8 +157,6 @@ int b200rt_builder_pop_transform(b200rt_builder* b) {
 
 int b200rt_builder_sphere(b200rt_builder* b, const double c[3], double radius, int32_t material) {
   if (!b || !c) return -B200RT_ERR_INVALID;
-  if (!b->xf_stack.empty() && b->xf_stack.back().similarity_scale() == 0)
-    return fail(b, B200RT_ERR_UNSUPPORTED, "Sphere under a non-similarity Transform (ellipsoid) is not supported");
   b200rt_prim p;
   std::memset(&p, 0, sizeof(p));
   p.type = B200RT_PRIM_SPHERE; p.material = material; p.instance = current_instance(b); p.aux = -1;
@@ -176,8 +166,6 @@ int b200rt_builder_sphere(b200rt_builder* b, const double c[3], double radius, i
 int b200rt_builder_moving_sphere(b200rt_builder* b, const double c0[3], const double c1[3], double time0, double time1, double radius, int32_t material) {
   if (!b || !c0 || !c1) return -B200RT_ERR_INVALID;
   if (!(time1 > time0)) return fail(b, B200RT_ERR_INVALID, "moving sphere needs time1 > time0");
-  if (!b->xf_stack.empty() && b->xf_stack.back().similarity_scale() == 0)
-    return fail(b, B200RT_ERR_UNSUPPORTED, "MovingSphere under a non-similarity Transform is not supported");
   b200rt_prim p;
   std::memset(&p, 0, sizeof(p));
   p.type = B200RT_PRIM_MOVING_SPHERE; p.material = material; p.instance = current_instance(b); p.aux = -1;
@@ -186,12 +174,6 @@ int b200rt_builder_moving_sphere(b200rt_builder* b, const double c0[3], const do
 }
 int b200rt_builder_rect(b200rt_builder* b, int32_t axis, double a0, double b0, double a1, double b1, double k, int32_t material) {
   if (!b || axis < 0 || axis > 2) return -B200RT_ERR_INVALID;
-  if (!top_is_axis_preserving(b)) {
-    const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
-    double q[3], eu[3] = {0, 0, 0}, ev[3] = {0, 0, 0}, n[3] = {0, 0, 0};
-    q[ia] = a0; q[ib] = b0; q[axis] = k; eu[ia] = a1 - a0; ev[ib] = b1 - b0; n[axis] = 1;
-    return add_quad_as_triangles(b, D3(q), D3(eu), D3(ev), D3(n), material);
-  }
   b200rt_prim p;
   std::memset(&p, 0, sizeof(p));
   p.type = axis == 2 ? B200RT_PRIM_XY_RECT : (axis == 1 ? B200RT_PRIM_XZ_RECT : B200RT_PRIM_YZ_RECT);
@@ -201,20 +183,6 @@ int b200rt_builder_rect(b200rt_builder* b, int32_t axis, double a0, double b0, d
 }
 int b200rt_builder_cube(b200rt_builder* b, const double mn[3], const double mx[3], int32_t material) {
   if (!b || !mn || !mx) return -B200RT_ERR_INVALID;
-  if (!top_is_axis_preserving(b)) {  // the six sides of cube.rs:17-54 as flat-shaded triangle pairs
-    int first = -1;
-    for (int axis = 0; axis < 3; ++axis)
-      for (int side = 0; side < 2; ++side) {
-        const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
-        double q[3], eu[3] = {0, 0, 0}, ev[3] = {0, 0, 0}, n[3] = {0, 0, 0};
-        q[ia] = mn[ia]; q[ib] = mn[ib]; q[axis] = side ? mx[axis] : mn[axis];
-        eu[ia] = mx[ia] - mn[ia]; ev[ib] = mx[ib] - mn[ib]; n[axis] = 1;
-        int id = add_quad_as_triangles(b, D3(q), D3(eu), D3(ev), D3(n), material);
-        if (id < 0) return id;
-        if (first < 0) first = id;
-      }
-    return first;
-  }
   b200rt_prim p;
   std::memset(&p, 0, sizeof(p));
   p.type = B200RT_PRIM_BOX; p.material = material; p.instance = current_instance(b); p.aux = -1;
@@ -227,8 +195,6 @@ int b200rt_builder_triangle(b200rt_builder* b, const double pa[3], const double 
 }
 int b200rt_builder_medium_sphere(b200rt_builder* b, const double c[3], double radius, double density, int32_t phase) {
   if (!b || !c || !(density > 0)) return fail(b, B200RT_ERR_INVALID, "medium_sphere: bad arguments");
-  if (!b->xf_stack.empty() && b->xf_stack.back().similarity_scale() == 0)
-    return fail(b, B200RT_ERR_UNSUPPORTED, "ConstantMedium sphere under a non-similarity Transform is not supported");
   b200rt_prim p;
   std::memset(&p, 0, sizeof(p));
   p.type = B200RT_PRIM_MEDIUM_SPHERE; p.material = phase; p.instance = current_instance(b); p.aux = -1;
@@ -237,7 +203,6 @@ int b200rt_builder_medium_sphere(b200rt_builder* b, const double c[3], double ra
 }
 int b200rt_builder_medium_cube(b200rt_builder* b, const double mn[3], const double mx[3], double density, int32_t phase) {
   if (!b || !mn || !mx || !(density > 0)) return fail(b, B200RT_ERR_INVALID, "medium_cube: bad arguments");
-  if (!top_is_axis_preserving(b)) return fail(b, B200RT_ERR_UNSUPPORTED, "ConstantMedium box under a rotating Transform is not supported");
   b200rt_prim p;
   std::memset(&p, 0, sizeof(p));
   p.type = B200RT_PRIM_MEDIUM_BOX; p.material = phase; p.instance = current_instance(b); p.aux = -1;

@@ -27,6 +27,9 @@
 #define B200RT_MAX_LEAF 4
 #endif
 #define B200RT_STACK 64
+// prim_meta.x = type | flags | material << 8
+#define B200RT_PRIM_TYPE_MASK 0x7f
+#define B200RT_PRIM_OBJF 0x80  // instanced primitive whose f32 filter runs in OBJECT space (prim_data holds the object-space record)
 
 #ifdef __CUDACC__
 #include <cuda_runtime.h>
@@ -56,4 +59,5 @@ struct DevScene {
   int n_nodes;
   int n_lights;
   int flat;  // B200RT_SCENE_FLAT_LIST: linear scan, no BVH
+  int has_objf;  // some primitive carries B200RT_PRIM_OBJF: the hot kernels are launched in their OBJF = true instantiation
 };

@@ -8,9 +8,12 @@
 // Debug build (-DB200RT_COUNTERS, tools/dbg): per-ray work statistics of the traversal.
 #ifdef B200RT_COUNTERS
 __device__ unsigned long long g_dbg[64];
+__device__ unsigned int* g_dbg_steps;  // per queue position: HitRaw::dbg (tools/dbg/dump_rays.py)
 #define DBG_INC(i) atomicAdd(&g_dbg[(i)], 1ull)
+#define DBG_RAY(x) x
 #else
 #define DBG_INC(i)
+#define DBG_RAY(x)
 #endif
 // counter slots: 0 rays, 1 inner nodes visited, 2 leaves visited, 3 stack pushes, 4 pops culled, 5 to_object,
 // 10+type filter calls, 20+type exact calls, 30+type exact accepted
@@ -27,6 +30,9 @@ struct HitRaw {
   double t;
   int prim;  // device (leaf-order) primitive index, -1 = miss
   int aux;   // Cube side
+#ifdef B200RT_COUNTERS
+  unsigned int dbg;  // this ray's traversal: inner nodes | leaves << 10 | f32 filter calls << 16 | f64 decisions << 24
+#endif
 };
 
 struct HitInfo {  // HitRecord (hit.rs:7-14)
@@ -80,17 +86,23 @@ DEV RayD to_object(const DevScene& S, int inst, const RayD& w) {
 // different parts of this function), so every heavy f64 sequence exists exactly ONCE: one quadratic-root site
 // serves Sphere, MovingSphere and the sphere ConstantMedium boundary; one rectangle site serves the three
 // rectangles, the Cube faces and the box ConstantMedium boundary; the medium tail (medium.rs:33-52) is shared.
-DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, float t_min, float& t_best32, HitRaw& h) {
-  const int4 meta = __ldg(&S.prim_meta[k]);
-  const int type = meta.x & 0xff;
+//
+// `objf`: Transform::hit in full generality (transform.rs:151-165: any rotation, scale: Vec3, any child).  An instanced
+// primitive whose shape does not survive the transform (a rotated Cube / rectangle / box medium, a sphere under a
+// non-uniform scale) keeps its OBJECT-space record and is filtered on the object-space ray: the caller (test_prim) has
+// then replaced `rf` by that ray and `eps` by its rounding error; the f64 decision runs in object space for every
+// instanced primitive anyway.
+DEV void test_prim_body(const DevScene& S, const Ray& ray, const RayF& rf, const float eps, const int4 meta, int k, float t_min, float& t_best32, HitRaw& h) {
+  const float4* __restrict__ prim_data = S.prim_data;
+  const int type = meta.x & B200RT_PRIM_TYPE_MASK;
   const bool inst = meta.z >= 0;
-  const float eps = inst ? __ldg(&S.inst_eps[meta.z]) : 0.f;
-  const float4 A = __ldg(&S.prim_data[3 * k]);
-  const float4 WB = __ldg(&S.prim_data[3 * k + 1]);
+  const float4 A = __ldg(&prim_data[3 * k]);
+  const float4 WB = __ldg(&prim_data[3 * k + 1]);
   const bool is_medium = type == B200RT_PRIM_MEDIUM_SPHERE || type == B200RT_PRIM_MEDIUM_BOX;
   const bool is_rect = type == B200RT_PRIM_XY_RECT || type == B200RT_PRIM_XZ_RECT || type == B200RT_PRIM_YZ_RECT;
   const int rect_axis = type == B200RT_PRIM_XY_RECT ? 2 : (type == B200RT_PRIM_XZ_RECT ? 1 : 0);
   DBG_INC(10 + type);
+  DBG_RAY(h.dbg += 1u << 16);
   uint32_t cand = 0x3fu;  // Cube faces to confirm: bits 0..5 near the slab entry, bits 8..13 near the exit
   int verdict = FILTER_MAYBE;
   float t_medium = 0.f;
@@ -107,7 +119,7 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
     if (rect_reject(rf, rect_axis, A.x, A.y, A.z, A.w, WB.x, t_min, t_best32, eps)) return;
     cand = 1u << (2 * (2 - rect_axis));  // the rectangle is the "min" side of a degenerate box on its axis
   } else if (type == B200RT_PRIM_TRIANGLE) {
-    const float4 C = __ldg(&S.prim_data[3 * k + 2]);
+    const float4 C = __ldg(&prim_data[3 * k + 2]);
     if (tri_reject(rf, f3(A), f3(WB), f3(C), t_min, t_best32, eps)) return;
   }  // moving spheres go straight to the exact test
   if (verdict == FILTER_MEDIUM_HIT) {  // certain interior scatter, certainly the closest hit so far: t in f32
@@ -118,9 +130,10 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
   }
   // ---- f64 decision
   RayD rd = make_rayd(ray);
-  const float4* rec = S.prim_data + 3 * (size_t)k;
+  const float4* rec = prim_data + 3 * (size_t)k;
   if (inst) { rd = to_object(S, meta.z, rd); rec = S.prim_obj + 3 * (size_t)k; DBG_INC(5); }
   DBG_INC(20 + type);
+  DBG_RAY(h.dbg += 1u << 24);
   const float4 EA = inst ? __ldg(rec) : A;
   const float4 EB = inst ? __ldg(rec + 1) : WB;
   const double tmin_d = (double)t_min, tmax_d = h.t;
@@ -199,6 +212,48 @@ DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, flo
   t_best32 = __double2float_ru(t);
 }
 
+// The object-space arm, out of line: a second copy of the leaf test that only scenes with such primitives ever fetch
+// (inlined, it cost book-2 — which has none — 9 %: +8 % instructions and +50 % spill traffic in k_wf_extend at 64
+// registers).  Everything goes in and out BY VALUE, so the caller keeps its hit record and ray constants in registers
+// and only pays a predicate on its hot path.  The ray is taken to object space in f64 and rounded once, so the filters
+// see an origin that is off by <= 1 ulp per component — the same error class as a baked coordinate, handed to them as `eps`.
+struct ObjfHit { double t; int aux; int hit; };
+__device__ __noinline__ ObjfHit test_prim_objf(const float4* __restrict__ prim_data, const float4* __restrict__ prim_obj, const double* __restrict__ instances_d,
+                                               float ox, float oy, float oz, float dx, float dy, float dz, float time, uint32_t mseed, int4 meta, int k, float t_min,
+                                               float t_best32, double t_best) {
+  DevScene S{};  // the leaf test reads nothing else of the scene
+  S.prim_data = prim_data; S.prim_obj = prim_obj; S.instances_d = instances_d;
+  Ray ray;
+  ray.o = f3(ox, oy, oz); ray.d = f3(dx, dy, dz); ray.time = time; ray.tmax = t_best32; ray.mseed = mseed;
+  const RayD rd = to_object(S, meta.z, make_rayd(ray));
+  RayF rf;
+  rf.o = to_f3(rd.o); rf.d = to_f3(rd.d); rf.time = time;
+  rf.inv = f3(safe_rcp(rf.d.x), safe_rcp(rf.d.y), safe_rcp(rf.d.z));
+  rf.a = dot(rf.d, rf.d);
+  const float eps = 1.2e-7f * fmaxf(fabsf(rf.o.x), fmaxf(fabsf(rf.o.y), fabsf(rf.o.z))) + 1e-30f;
+  HitRaw h;
+  h.t = t_best; h.prim = -1; h.aux = 0;
+  DBG_RAY(h.dbg = 0);
+  test_prim_body(S, ray, rf, eps, meta, k, t_min, t_best32, h);
+  ObjfHit r;
+  r.t = h.t; r.aux = h.aux; r.hit = h.prim >= 0;
+  return r;
+}
+
+// One leaf primitive.  OBJF = false: the scene holds no object-space-filtered primitive (DevScene::has_objf, decided by the
+// host per launch), and the kernel carries neither the branch nor the register constraints of the call (the hot kernels
+// are instantiated both ways: even the never-taken call cost book-2's extend 5.7 %).
+template <bool OBJF>
+DEV void test_prim(const DevScene& S, const Ray& ray, const RayF& rf, int k, float t_min, float& t_best32, HitRaw& h) {
+  const int4 meta = __ldg(&S.prim_meta[k]);
+  if (OBJF && (meta.x & B200RT_PRIM_OBJF)) {
+    const ObjfHit r = test_prim_objf(S.prim_data, S.prim_obj, S.instances_d, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, ray.time, ray.mseed, meta, k, t_min, t_best32, h.t);
+    if (r.hit) { h.t = r.t; h.prim = k; h.aux = r.aux; t_best32 = __double2float_ru(r.t); }
+    return;
+  }
+  test_prim_body(S, ray, rf, meta.z >= 0 ? __ldg(&S.inst_eps[meta.z]) : 0.f, meta, k, t_min, t_best32, h);
+}
+
 #define B200RT_TRAV_DONE 0xFFFFFFFFu  // leaf bit set with an impossible count: never a real child reference
 
 // Traversal stack.  north_star asks for a shared-memory short stack; it is implemented (the first B200RT_SSTACK
@@ -265,7 +320,18 @@ DEV RayT make_rayt(const DevScene& S, const RayF& rf) {
   asm("mov.b64 %0, %1;" : "=l"(t.nodes) : "l"(S.nodes));
   t.inv = rf.inv;
   t.oi = rf.o * rf.inv;
-  t.slack = 4.7683716e-7f * fmaxf(fabsf(t.oi.x), fmaxf(fabsf(t.oi.y), fabsf(t.oi.z)));  // 2 * 2^-22
+  // 2 * 2^-22 * max |o/d| over the axes whose reciprocal is a rounded one (a clamped axis is exact, see safe_rcp: without
+  // this an axis-parallel ray would carry a slack of ~1e26 and lose the slab culling of the other two axes altogether)
+#ifndef B200RT_SLACK_PER_AXIS
+#define B200RT_SLACK_PER_AXIS 1
+#endif
+#if B200RT_SLACK_PER_AXIS
+  const float sx = fabsf(rf.d.x) > B200RT_RCP_CLAMP ? fabsf(t.oi.x) : 0.f, sy = fabsf(rf.d.y) > B200RT_RCP_CLAMP ? fabsf(t.oi.y) : 0.f,
+              sz = fabsf(rf.d.z) > B200RT_RCP_CLAMP ? fabsf(t.oi.z) : 0.f;
+  t.slack = 4.7683716e-7f * fmaxf(sx, fmaxf(sy, sz));
+#else
+  t.slack = 4.7683716e-7f * fmaxf(fabsf(t.oi.x), fmaxf(fabsf(t.oi.y), fabsf(t.oi.z)));
+#endif
   return t;
 }
 
@@ -341,9 +407,18 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32
 // ones the host kept out of it, or ALL of them for the flat-list arm (hit.rs:56-67, n_bvh_prims = 0) — are fed
 // through the same leaf code as pseudo-leaves of up to 16 after the traversal, when t_best already culls most of
 // their work: test_prim is instantiated once per kernel.
-template <bool ANY>
-DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
+//
+// `lanes` != 0: the caller computed, with the warp CONVERGED (a __ballot_sync over the full mask), exactly which
+// lanes call trace() together.  Those lanes then wait for each other at the end of the BVH so that the out-of-BVH
+// tail (book-2's fog: an f64 medium test for half of the rays) runs once per warp with all of them converged
+// instead of once per group of lanes that happen to leave the BVH together.  Every lane of `lanes` executes the
+// same number of __all_sync votes: one per trip of the outer loop until the vote passes, and the vote passes for
+// all of them in the same trip.  Callers that sit in divergent code (megakernel path loop, SPPM bounce loops) pass
+// 0: no vote, no waiting (__activemask() is not a safe substitute there: it may name lanes that never arrive).
+template <bool ANY, bool OBJF = true>
+DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h, const unsigned lanes = 0u) {
   h.t = (double)ray.tmax; h.prim = -1; h.aux = 0;
+  DBG_RAY(h.dbg = 0);
   float t_best32 = ray.tmax;
   const RayF rf = make_rayf(ray);
   const RayT rt = make_rayt(S, rf);
@@ -355,18 +430,15 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
 #endif
   int sp = 0;
   int tail = S.n_bvh_prims;                          // next primitive outside the BVH
-  // The tail is expensive (book-2's fog: an f64 medium test for half of the rays): run it once per warp, with
-  // all lanes converged, instead of once per group of lanes that happen to leave the BVH together.
-  const unsigned lanes = __activemask();
-  const bool wait_tail = !ANY && !S.flat && S.n_bvh_prims < S.n_prims;
+  const bool wait_tail = !ANY && lanes != 0u && !S.flat && S.n_bvh_prims < S.n_prims;  // warp-uniform
   uint32_t cur = S.flat ? B200RT_TRAV_DONE : 0u;  // root node
   for (;;) {
 #if B200RT_TRAV_WW
-    while (!(cur & B200RT_LEAF_BIT)) cur = node_step(S, rf, rt, cur, t_min, t_best32, stack, sp);
+    while (!(cur & B200RT_LEAF_BIT)) { cur = node_step(S, rf, rt, cur, t_min, t_best32, stack, sp); DBG_RAY(h.dbg += 1u); }
 #else
     if (!(cur & B200RT_LEAF_BIT)) { cur = node_step(S, rf, rt, cur, t_min, t_best32, stack, sp); continue; }
 #endif
-    if (wait_tail) {  // warp-uniform: the lanes that finished the BVH wait here until the whole warp has
+    if (wait_tail) {  // the lanes that finished the BVH wait here until every lane of `lanes` has
       const bool all_done = __all_sync(lanes, cur == B200RT_TRAV_DONE);
       if (cur == B200RT_TRAV_DONE && !all_done) continue;
     }
@@ -378,7 +450,8 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h) {
     }
     const int first = (int)(cur & 0x07FFFFFFu), count = (int)((cur >> 27) & 15u) + 1;
     DBG_INC(2);
-    for (int k = first; k < first + count; ++k) test_prim(S, ray, rf, k, t_min, t_best32, h);
+    DBG_RAY(h.dbg += 1u << 10);
+    for (int k = first; k < first + count; ++k) test_prim<OBJF>(S, ray, rf, k, t_min, t_best32, h);
     if (ANY && h.prim >= 0) return;
     cur = pop_next(stack, sp, t_best32);
   }
@@ -396,7 +469,7 @@ DEV void sphere_uv(d3 n, float& u, float& v) {  // sphere.rs:16-20
 DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo& out, const bool WANT_UV) {
   const int k = h.prim;
   const int4 meta = __ldg(&S.prim_meta[k]);
-  const int type = meta.x & 0xff;
+  const int type = meta.x & B200RT_PRIM_TYPE_MASK;
   const bool inst = meta.z >= 0;
   out.type = type; out.material = meta.x >> 8; out.prim_orig = meta.y; out.t = (float)h.t;
   out.u = 0.f; out.v = 0.f;
@@ -407,10 +480,13 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
   const float4 A = __ldg(rec);
   d3 on;  // outward normal in the primitive's own space
   switch (type) {
-    case B200RT_PRIM_SPHERE: on = p - D3(A); break;  // (p - c) / r: the positive scale drops out below
+    // (p - c) / r: |r| drops out below, its SIGN does not (sphere.rs:44 — a negative radius turns the normal inwards,
+    // the hollow-glass-sphere idiom)
+    case B200RT_PRIM_SPHERE: on = p - D3(A); if (A.w < 0.f) on = -on; break;
     case B200RT_PRIM_MOVING_SPHERE: {
       const float4 B = __ldg(rec + 1), C = __ldg(rec + 2);
       on = p - moving_center(D3(A), D3(B), (double)C.x, (double)C.y, rd.time);
+      if (A.w < 0.f) on = -on;
       break;
     }
     case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
@@ -445,7 +521,7 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
   // `on` is the outward normal up to a positive scale.  The cancellation-prone parts (p, p - c, the sign tests of
   // hit.rs:25 / transform.rs:160) stay in f64; Vec3::unit (hit.rs:33) is taken in f32 after the final rounding
   // (2e-7 relative against the 1e-5 tolerance; three f64 divisions and a square root less per hit).
-  if (WANT_UV && (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE)) sphere_uv(on * (1.0 / (double)A.w), out.u, out.v);
+  if (WANT_UV && (type == B200RT_PRIM_SPHERE || type == B200RT_PRIM_MOVING_SPHERE)) sphere_uv(on * (1.0 / fabs((double)A.w)), out.u, out.v);
   const bool front = ddot(rd.d, on) < 0.;  // hit.rs:25
   const d3 n = front ? on : -on;            // hit.rs:26-33
   if (!inst) {

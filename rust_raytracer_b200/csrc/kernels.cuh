@@ -36,12 +36,19 @@ DEV void accum_add(float* accum, uint32_t pixel, float3 c) {
 // ---- World::hit over a batch (world.rs:27-29) ------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_intersect_batch(DevScene S, const float4* __restrict__ o_time, const float4* __restrict__ d_tmax,
                                                          const uint32_t* __restrict__ mseed, unsigned long long n, float t_min, b200rt_hit* __restrict__ out) {
-  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+  // whole warps walk the batch together (the loop bound is warp-uniform), so the set of lanes that trace is known from a
+  // converged ballot and trace() can let them wait for each other before the out-of-BVH tail (the same code path as extend)
+  const unsigned lane = threadIdx.x & 31u;
+  for (unsigned long long base = blockIdx.x * (unsigned long long)blockDim.x + (threadIdx.x - lane); base < n; base += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long i = base + lane;
+    const bool active = i < n;
+    const unsigned tracing = __ballot_sync(0xffffffffu, active);
+    if (!active) continue;
     const float4 o = o_time[i], d = d_tmax[i];
     Ray r;
     r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = d.w; r.mseed = mseed ? mseed[i] : 0u;
     HitRaw h;
-    trace<false>(S, r, t_min, h);
+    trace<false>(S, r, t_min, h, tracing);
     b200rt_hit res;
     if (h.prim < 0) { res.t = __int_as_float(0x7f800000); res.prim = -1; res.nx = res.ny = res.nz = 0.f; res.front_face = 0; res.u = res.v = 0.f; }
     else {

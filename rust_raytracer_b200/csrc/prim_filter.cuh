@@ -18,7 +18,11 @@ struct RayF {
 DEV float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 DEV float rsqrt_fast(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 DEV float sqrt_fast(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-DEV float safe_rcp(float d) { return rcp_fast(fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
+// 1/d for the slab tests.  A (near-)zero component gets +-2^100: a power of two, so plane * inv and o * inv are exact and
+// fmaf(plane, inv, -o * inv) has the exact sign of plane - o: on that axis the slab test degenerates to the exact
+// inside / outside test of the origin and needs no rounding slack (make_rayt).
+#define B200RT_RCP_CLAMP 1e-30f
+DEV float safe_rcp(float d) { return fabsf(d) > B200RT_RCP_CLAMP ? rcp_fast(d) : copysignf(0x1p100f, d); }
 
 // Filter verdicts
 #define FILTER_MAYBE 0        // the exact test decides
@@ -63,7 +67,7 @@ DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float 
   float cc = oc2 - r2;
   float disc = hb * hb - r.a * cc;
   float E = 2e-6f * r.a * (oc2 + r2);
-  if (eps > 0.f) E += r.a * eps * (8.2f * sqrt_fast(oc2) + 4.0f * radius);
+  if (eps > 0.f) E += r.a * eps * (8.2f * sqrt_fast(oc2) + 4.0f * fabsf(radius));
   if (disc < -E) return true;
   if (disc > 4.0f * E) {
     const float rs = rsqrt_fast(disc), s = disc * rs, inva = rcp_fast(r.a);  // s, inva: <= 3 ulp

@@ -51,7 +51,11 @@ struct BinBuilder {
     centroid.resize(pb.size());
     for (size_t i = 0; i < pb.size(); ++i) centroid[i] = D3(0.5 * ((double)pb[i].lo[0] + pb[i].hi[0]), 0.5 * ((double)pb[i].lo[1] + pb[i].hi[1]), 0.5 * ((double)pb[i].lo[2] + pb[i].hi[2]));
   }
-  int build(int first, int count) {
+  // depth_left: binary levels this subtree may still use.  While the budget is roomy the split is binned SAH; once
+  // count > 2^(depth_left - 1) only an even split still fits, so the range is halved at the median of its widest
+  // centroid axis (a chain of geometrically growing primitives, or a deep mesh, would otherwise give a tree whose
+  // BVH4 collapse needs more traversal-stack entries than B200RT_STACK).
+  int build(int first, int count, int depth_left = 1 << 20) {
     int id = (int)nodes.size();
     nodes.emplace_back();
     Box box, cbox;
@@ -83,8 +87,14 @@ struct BinBuilder {
     }
     float leaf_cost = box.area() * count;
     if (count <= B200RT_MAX_LEAF && (best_axis < 0 || best_cost >= leaf_cost)) { nodes[id].first = first; nodes[id].count = count; return id; }
+    const bool force_median = depth_left < 31 && (long long)count > (1ll << std::max(0, depth_left - 1));
     int mid;
-    if (best_axis < 0) {  // all centroids coincide: split the range in the middle
+    if (force_median) {
+      int axis = 0;
+      for (int a = 1; a < 3; ++a) if (cbox.hi[a] - cbox.lo[a] > cbox.hi[axis] - cbox.lo[axis]) axis = a;
+      mid = first + count / 2;
+      std::nth_element(order.begin() + first, order.begin() + mid, order.begin() + first + count, [&](int a, int b) { return centroid[a][axis] < centroid[b][axis]; });
+    } else if (best_axis < 0) {  // all centroids coincide: split the range in the middle
       mid = first + count / 2;
     } else {
       float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
@@ -96,8 +106,8 @@ struct BinBuilder {
       mid = (int)(it - order.begin());
       if (mid == first || mid == first + count) mid = first + count / 2;
     }
-    int l = build(first, mid - first);
-    int r = build(mid, first + count - mid);
+    int l = build(first, mid - first, depth_left - 1);
+    int r = build(mid, first + count - mid, depth_left - 1);
     nodes[id].left = l; nodes[id].right = r;
     return id;
   }
@@ -107,9 +117,11 @@ void put4(std::vector<float>& v, size_t at, float a, float b, float c, float d) 
 float ibits(int32_t i) { float f; std::memcpy(&f, &i, 4); return f; }
 float ubits(uint32_t i) { float f; std::memcpy(&f, &i, 4); return f; }
 
-// Collapse the binary tree into BVH4 nodes (128 B each); returns the node index.
-int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out) {
+// Collapse the binary tree into BVH4 nodes (128 B each); returns the node index.  depth_out: levels of BVH4 nodes below
+// and including this one (the traversal pushes at most 3 entries per level: node_step in intersect.cuh).
+int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out, int& depth_out) {
   int my = (int)(out.size() / 32);
+  int deepest = 0;
   out.resize(out.size() + 32, 0.f);
   int kids[4]; int nk = 0;
   const BinNode& root = bb.nodes[bin_id];
@@ -135,8 +147,9 @@ int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out) {
     const BinNode& c = bb.nodes[kids[i]];
     for (int a = 0; a < 3; ++a) { lo[a][i] = c.box.lo[a]; hi[a][i] = c.box.hi[a]; }
     if (c.left < 0) refs[i] = (int32_t)(B200RT_LEAF_BIT | ((uint32_t)(c.count - 1) << 27) | (uint32_t)c.first);
-    else refs[i] = collapse(bb, kids[i], out);
+    else { int dk = 0; refs[i] = collapse(bb, kids[i], out, dk); deepest = std::max(deepest, dk); }
   }
+  depth_out = deepest + 1;
   size_t at = (size_t)my * 32;
   // rows: lo.x hi.x lo.y hi.y lo.z hi.z refs (pad) — the near plane of an axis is row 2a + sign(d_a), the far one its xor 1
   for (int a = 0; a < 3; ++a) { put4(out, at + 8 * a, lo[a][0], lo[a][1], lo[a][2], lo[a][3]); put4(out, at + 8 * a + 4, hi[a][0], hi[a][1], hi[a][2], hi[a][3]); }
@@ -184,8 +197,17 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     }
   }
   // ---- bake primitives to world space
+  // Transform::new(rotate, scale: Vec3, translate, obj) (transform.rs:17-148) is accepted in full generality.  Where the
+  // shape survives the transform (a sphere under a similarity; an axis rectangle / Cube under a positive diagonal; any
+  // triangle) the f32 filter record is baked to world space; otherwise (B200RT_PRIM_OBJF: rotated Cube / rectangle / box
+  // medium, sphere under a non-uniform scale) the record stays in object space, the device filters on the object-space
+  // ray, and only the bounding box is transformed (the eight corners of the object-space box, transform.rs:110-136).
   std::vector<float> data((size_t)n * 12, 0.f), objdata((size_t)n * 12, 0.f);
   std::vector<Box> boxes(n);
+  std::vector<uint8_t> objf(n, 0);
+  auto grow_transformed = [](Box& bx, const Affine& A, const double lo[3], const double hi[3]) {
+    for (int c = 0; c < 8; ++c) bx.grow(A.point(D3((c & 1) ? hi[0] : lo[0], (c & 2) ? hi[1] : lo[1], (c & 4) ? hi[2] : lo[2])));
+  };
   for (uint32_t i = 0; i < n; ++i) {
     const b200rt_prim& p = d->prims[i];
     if (p.material < 0 || (uint32_t)p.material >= d->n_materials) { err = "material index out of range"; return B200RT_ERR_INVALID; }
@@ -193,37 +215,50 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     const bool inst = p.instance >= 0;
     const Affine A = inst ? M[p.instance] : Affine::identity();
     float* o = &data[(size_t)i * 12];
+    float* q = &objdata[(size_t)i * 12];  // object-space record in the same intermediate layout (the f64 decision runs on it)
     Box& bx = boxes[i];
     switch (p.type) {
       case B200RT_PRIM_SPHERE: case B200RT_PRIM_MEDIUM_SPHERE: case B200RT_PRIM_MOVING_SPHERE: {
-        double s = inst ? A.similarity_scale() : 1.0;
-        if (s == 0) { err = "sphere under a non-similarity transform"; return B200RT_ERR_UNSUPPORTED; }
+        // sphere.rs:24-61 accepts a negative radius (the outward normal (p - c) / r turns inwards); zero divides by zero
+        if (!(p.p[3] != 0.f) || !std::isfinite(p.p[3])) { err = "sphere radius must be non-zero"; return B200RT_ERR_INVALID; }
+        if (p.type == B200RT_PRIM_MOVING_SPHERE && !(p.p[8] > p.p[7])) { err = "moving sphere needs time1 > time0"; return B200RT_ERR_INVALID; }
+        if (p.type == B200RT_PRIM_MEDIUM_SPHERE && !(p.p[4] > 0)) { err = "medium density must be positive"; return B200RT_ERR_INVALID; }
+        for (int k = 0; k < 9; ++k) q[k] = p.p[k];
+        if (p.type == B200RT_PRIM_MEDIUM_SPHERE) { for (int k = 4; k < 9; ++k) q[k] = 0.f; q[4] = (float)(-1.0 / (double)p.p[4]); }
+        const double s = inst ? A.similarity_scale() : 1.0;
+        if (s == 0) {  // ellipsoid in world space: object-space filter
+          objf[i] = 1;
+          const double ra = std::fabs((double)p.p[3]) * (1 + 1e-6);
+          double lo[3], hi[3];
+          for (int a = 0; a < 3; ++a) { lo[a] = p.p[a] - ra; hi[a] = p.p[a] + ra; }
+          if (p.type == B200RT_PRIM_MOVING_SPHERE) for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p.p[4 + a] - ra); hi[a] = std::max(hi[a], p.p[4 + a] + ra); }
+          grow_transformed(bx, A, lo, hi);
+          break;
+        }
         D3 c = A.point(D3(p.p));
         double r = s * p.p[3];
-        if (!(r > 0)) { err = "sphere radius must be positive"; return B200RT_ERR_INVALID; }
         o[0] = (float)c.x; o[1] = (float)c.y; o[2] = (float)c.z; o[3] = (float)r;
-        double rr = (double)o[3] * (1 + 1e-6);
+        double rr = std::fabs((double)o[3]) * (1 + 1e-6);
         bx.grow(D3(o[0] - rr, o[1] - rr, o[2] - rr)); bx.grow(D3(o[0] + rr, o[1] + rr, o[2] + rr));
         if (p.type == B200RT_PRIM_MOVING_SPHERE) {
           D3 c1 = A.point(D3(p.p + 4));
           float c1f[3] = {(float)c1.x, (float)c1.y, (float)c1.z};
-          if (!(p.p[8] > p.p[7])) { err = "moving sphere needs time1 > time0"; return B200RT_ERR_INVALID; }
           o[4] = c1f[0]; o[5] = c1f[1]; o[6] = c1f[2]; o[7] = p.p[7]; o[8] = p.p[8];
           bx.grow(D3(c1f[0] - rr, c1f[1] - rr, c1f[2] - rr)); bx.grow(D3(c1f[0] + rr, c1f[1] + rr, c1f[2] + rr));
         } else if (p.type == B200RT_PRIM_MEDIUM_SPHERE) {
-          if (!(p.p[4] > 0)) { err = "medium density must be positive"; return B200RT_ERR_INVALID; }
-          o[4] = (float)(-1.0 / ((double)p.p[4]));
           // a distance of d object units is s*d world units: density scales by 1/s
-          if (inst) o[4] = (float)(-s / (double)p.p[4]);
+          o[4] = (float)(-s / (double)p.p[4]);
         }
         break;
       }
       case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: {
-        if (inst && !A.is_positive_diagonal()) { err = "axis rectangle under a rotating transform (the builder emits triangles)"; return B200RT_ERR_UNSUPPORTED; }
         const int axis = p.type == B200RT_PRIM_XY_RECT ? 2 : (p.type == B200RT_PRIM_XZ_RECT ? 1 : 0);
         const int ia = axis == 0 ? 1 : 0, ib = axis == 2 ? 1 : 2;
+        if (!(p.p[2] > p.p[0]) || !(p.p[3] > p.p[1])) { err = "degenerate rectangle"; return B200RT_ERR_INVALID; }
+        for (int k = 0; k < 5; ++k) q[k] = p.p[k];
         double lo[3], hi[3];
         lo[ia] = p.p[0]; lo[ib] = p.p[1]; hi[ia] = p.p[2]; hi[ib] = p.p[3]; lo[axis] = hi[axis] = p.p[4];
+        if (inst && !A.is_positive_diagonal()) { objf[i] = 1; grow_transformed(bx, A, lo, hi); break; }
         D3 l = A.point(D3(lo)), h = A.point(D3(hi));
         o[0] = (float)l[ia]; o[1] = (float)l[ib]; o[2] = (float)h[ia]; o[3] = (float)h[ib]; o[4] = (float)l[axis];
         if (!(o[2] > o[0]) || !(o[3] > o[1])) { err = "degenerate rectangle"; return B200RT_ERR_INVALID; }
@@ -233,15 +268,21 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
         break;
       }
       case B200RT_PRIM_BOX: case B200RT_PRIM_MEDIUM_BOX: {
-        if (inst && !A.is_positive_diagonal()) { err = "box under a rotating transform (the builder emits triangles)"; return B200RT_ERR_UNSUPPORTED; }
+        if (!(p.p[3] > p.p[0]) || !(p.p[4] > p.p[1]) || !(p.p[5] > p.p[2])) { err = "degenerate box"; return B200RT_ERR_INVALID; }
+        if (p.type == B200RT_PRIM_MEDIUM_BOX && !(p.p[6] > 0)) { err = "medium density must be positive"; return B200RT_ERR_INVALID; }
+        q[0] = p.p[0]; q[1] = p.p[1]; q[2] = p.p[2]; q[4] = p.p[3]; q[5] = p.p[4]; q[6] = p.p[5];
+        if (p.type == B200RT_PRIM_MEDIUM_BOX) q[7] = (float)(-1.0 / (double)p.p[6]);
+        const bool uniform = A.m[0] == A.m[5] && A.m[5] == A.m[10];
+        if (inst && (!A.is_positive_diagonal() || (p.type == B200RT_PRIM_MEDIUM_BOX && !uniform))) {
+          objf[i] = 1;
+          const double lo[3] = {p.p[0], p.p[1], p.p[2]}, hi[3] = {p.p[3], p.p[4], p.p[5]};
+          grow_transformed(bx, A, lo, hi);
+          break;
+        }
         D3 l = A.point(D3(p.p)), h = A.point(D3(p.p + 3));
         o[0] = (float)l.x; o[1] = (float)l.y; o[2] = (float)l.z; o[4] = (float)h.x; o[5] = (float)h.y; o[6] = (float)h.z;
         if (!(o[4] > o[0]) || !(o[5] > o[1]) || !(o[6] > o[2])) { err = "degenerate box"; return B200RT_ERR_INVALID; }
-        if (p.type == B200RT_PRIM_MEDIUM_BOX) {
-          if (!(p.p[6] > 0)) { err = "medium density must be positive"; return B200RT_ERR_INVALID; }
-          if (inst && !(A.m[0] == A.m[5] && A.m[5] == A.m[10])) { err = "medium box under a non-uniform scale"; return B200RT_ERR_UNSUPPORTED; }
-          o[7] = (float)(-(inst ? A.m[0] : 1.0) / (double)p.p[6]);
-        }
+        if (p.type == B200RT_PRIM_MEDIUM_BOX) o[7] = (float)(-(inst ? A.m[0] : 1.0) / (double)p.p[6]);
         bx.grow(D3(o[0], o[1], o[2])); bx.grow(D3(o[4], o[5], o[6]));
         break;
       }
@@ -251,25 +292,15 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
           D3 w = A.point(D3(p.p + 3 * v));
           o[4 * v] = (float)w.x; o[4 * v + 1] = (float)w.y; o[4 * v + 2] = (float)w.z;
           bx.grow(D3(o[4 * v], o[4 * v + 1], o[4 * v + 2]));
+          for (int c = 0; c < 3; ++c) q[4 * v + c] = p.p[3 * v + c];
         }
         break;
       }
       default: err = "unknown primitive type"; return B200RT_ERR_INVALID;
     }
+    if (objf[i]) { std::memcpy(o, q, 12 * sizeof(float)); cs.has_objf = true; }  // the filter record of an OBJF primitive is its object-space record
     for (int a = 0; a < 3; ++a) if (!std::isfinite(bx.lo[a]) || !std::isfinite(bx.hi[a])) { err = "non-finite primitive"; return B200RT_ERR_INVALID; }
-    if (inst) {
-      // object-space record in the same intermediate layout (the exact test runs there, on the original values)
-      float* q = &objdata[(size_t)i * 12];
-      switch (p.type) {
-        case B200RT_PRIM_SPHERE: case B200RT_PRIM_MOVING_SPHERE: for (int k = 0; k < 9; ++k) q[k] = p.p[k]; break;
-        case B200RT_PRIM_MEDIUM_SPHERE: for (int k = 0; k < 4; ++k) q[k] = p.p[k]; q[4] = (float)(-1.0 / (double)p.p[4]); break;
-        case B200RT_PRIM_XY_RECT: case B200RT_PRIM_XZ_RECT: case B200RT_PRIM_YZ_RECT: for (int k = 0; k < 5; ++k) q[k] = p.p[k]; break;
-        case B200RT_PRIM_BOX: case B200RT_PRIM_MEDIUM_BOX:
-          q[0] = p.p[0]; q[1] = p.p[1]; q[2] = p.p[2]; q[4] = p.p[3]; q[5] = p.p[4]; q[6] = p.p[5];
-          if (p.type == B200RT_PRIM_MEDIUM_BOX) q[7] = (float)(-1.0 / (double)p.p[6]);
-          break;
-        case B200RT_PRIM_TRIANGLE: for (int v = 0; v < 3; ++v) for (int c = 0; c < 3; ++c) q[4 * v + c] = p.p[3 * v + c]; break;
-      }
+    if (inst && !objf[i]) {
       float m = 0;
       for (int a = 0; a < 3; ++a) m = std::max(m, std::max(std::fabs(bx.lo[a]), std::fabs(bx.hi[a])));
       cs.inst_eps[p.instance] = std::max(cs.inst_eps[p.instance], 1.3e-7f * m);  // ~2u |coord|: rounding of M*x to f32 (+ f64 slop)
@@ -298,12 +329,28 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     if (in_idx.empty() || out_idx.size() > 8) { in_idx.resize(n); std::iota(in_idx.begin(), in_idx.end(), 0); out_idx.clear(); }
     std::vector<Box> inboxes(in_idx.size());
     for (size_t k = 0; k < in_idx.size(); ++k) inboxes[k] = boxes[in_idx[k]];
-    BinBuilder bb(inboxes);
-    bb.nodes.reserve(2 * in_idx.size());
-    int root = bb.build(0, (int)in_idx.size());
-    cs.nodes.reserve(in_idx.size() * 16);
-    collapse(bb, root, cs.nodes);
-    for (size_t k = 0; k < in_idx.size(); ++k) order[k] = in_idx[bb.order[k]];
+    // The device traversal keeps a per-thread stack of B200RT_STACK entries and pushes at most 3 per BVH4 level: the tree
+    // is accepted when 3 * depth <= B200RT_STACK, else rebuilt under a tighter binary depth budget (the last budget,
+    // ceil(log2 n) + 1, is a median-split tree whose collapse is about half that deep).
+    int min_budget = 2;
+    while ((1ll << (min_budget - 1)) < (long long)in_idx.size()) ++min_budget;
+    const int budgets[5] = {1 << 20, 48, 36, 28, min_budget};
+    std::vector<int> bb_order;
+    for (int attempt = 0; attempt < 5; ++attempt) {
+      if (attempt > 0 && budgets[attempt] < min_budget) continue;
+      BinBuilder bb(inboxes);
+      bb.nodes.reserve(2 * in_idx.size());
+      int root = bb.build(0, (int)in_idx.size(), budgets[attempt]);
+      cs.nodes.clear();
+      cs.nodes.reserve(in_idx.size() * 16);
+      int depth4 = 0;
+      collapse(bb, root, cs.nodes, depth4);
+      cs.bvh4_depth = (uint32_t)depth4;
+      bb_order.swap(bb.order);
+      if (3 * depth4 <= B200RT_STACK) break;
+    }
+    if (3 * (int)cs.bvh4_depth > B200RT_STACK) { err = "BVH deeper than the traversal stack allows"; return B200RT_ERR_UNSUPPORTED; }
+    for (size_t k = 0; k < in_idx.size(); ++k) order[k] = in_idx[bb_order[k]];
     for (size_t k = 0; k < out_idx.size(); ++k) order[in_idx.size() + k] = out_idx[k];
     cs.n_bvh_prims = (uint32_t)in_idx.size();
   } else {
@@ -339,7 +386,7 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     const b200rt_prim& p = d->prims[i];
     pack(cs.prim_data, k, p.type, &data[(size_t)i * 12]);
     if (p.instance >= 0) pack(cs.prim_obj, k, p.type, &objdata[(size_t)i * 12]);
-    cs.prim_meta[(size_t)k * 4 + 0] = p.type | (p.material << 8);
+    cs.prim_meta[(size_t)k * 4 + 0] = p.type | (objf[i] ? B200RT_PRIM_OBJF : 0) | (p.material << 8);
     cs.prim_meta[(size_t)k * 4 + 1] = i;
     cs.prim_meta[(size_t)k * 4 + 2] = p.instance;
     cs.prim_meta[(size_t)k * 4 + 3] = p.aux;
@@ -390,3 +437,16 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
 }
 
 }  // namespace b200rt
+
+// Host-only introspection of World::new's BVH (no CUDA needed): what b200rt_scene_create would build for `desc`.
+extern "C" int b200rt_scene_compile_stats(const b200rt_scene_desc* desc, uint32_t* bvh_nodes, uint32_t* bvh4_depth, uint32_t* stack_needed, uint32_t* stack_capacity) {
+  b200rt::CompiledScene cs;
+  std::string err;
+  const int rc = b200rt::compile_scene(desc, cs, err);
+  if (rc) return rc;
+  if (bvh_nodes) *bvh_nodes = cs.n_nodes;
+  if (bvh4_depth) *bvh4_depth = cs.bvh4_depth;
+  if (stack_needed) *stack_needed = 3 * cs.bvh4_depth;
+  if (stack_capacity) *stack_capacity = B200RT_STACK;
+  return B200RT_OK;
+}

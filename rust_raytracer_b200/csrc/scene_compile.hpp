@@ -25,7 +25,9 @@ struct CompiledScene {
   std::vector<int32_t> perlin_perm;  // 3 x 256
   std::vector<float> lights;       // 12 floats per light
   uint32_t n_prims = 0, n_bvh_prims = 0, n_nodes = 0, n_lights = 0;
+  uint32_t bvh4_depth = 0;  // levels of BVH4 nodes; the traversal stack needs at most 3 entries per level
   bool flat = false;
+  bool has_objf = false;  // some primitive is filtered in object space (B200RT_PRIM_OBJF)
 };
 
 // Validates, bakes and builds; returns a B200RT_* status and fills err.

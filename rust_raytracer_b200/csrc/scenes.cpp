@@ -33,13 +33,16 @@ void book1(SceneBuilder& sb, uint64_t seed, double aspect, b200rt_camera* cam, b
   world.push_back(make_shared<Sphere>(Vec3(0, -1000, 0), 1000, ground));
   for (int a = -11; a < 11; ++a)
     for (int b = -11; b < 11; ++b) {
-      double choose = rng.next();
-      Vec3 c(a + 0.9 * rng.next(), 0.2, b + 0.9 * rng.next());
+      // every draw is sequenced explicitly (the evaluation order of function arguments is unspecified in C++): the fixture
+      // must be the same whatever the compiler, and the oracle's own generator (oracle/oracle_scenes.inc) draws in this order
+      const double choose = rng.next();
+      const double cx = a + 0.9 * rng.next(), cz = b + 0.9 * rng.next();
+      Vec3 c(cx, 0.2, cz);
       double dx = c.x - 4, dy = c.y - 0.2, dz = c.z;
       if (std::sqrt(dx * dx + dy * dy + dz * dz) <= 0.9) continue;
       MaterialPtr m;
-      if (choose < 0.8) m = make_shared<Lambertian>(ConstantTexture(Vec3(rng.next() * rng.next(), rng.next() * rng.next(), rng.next() * rng.next())));
-      else if (choose < 0.95) { Vec3 al(rng.range(0.5, 1), rng.range(0.5, 1), rng.range(0.5, 1)); m = make_shared<Metal>(ConstantTexture(al), rng.range(0, 0.5)); }
+      if (choose < 0.8) { const double r0 = rng.next() * rng.next(), g0 = rng.next() * rng.next(), b0 = rng.next() * rng.next(); m = make_shared<Lambertian>(ConstantTexture(Vec3(r0, g0, b0))); }
+      else if (choose < 0.95) { const double r0 = rng.range(0.5, 1), g0 = rng.range(0.5, 1), b0 = rng.range(0.5, 1); const double fuzz = rng.range(0, 0.5); m = make_shared<Metal>(ConstantTexture(Vec3(r0, g0, b0)), fuzz); }
       else m = make_shared<Dielectric>(1.5, ConstantTexture(Vec3::ones()));
       world.push_back(make_shared<Sphere>(c, 0.2, m));
     }
@@ -51,8 +54,8 @@ void book1(SceneBuilder& sb, uint64_t seed, double aspect, b200rt_camera* cam, b
   default_params(params, 400, 225, 100, B200RT_INTEGRATOR_PATH, B200RT_BACKGROUND_SKY, 0.5, 0.7, 1.0);
 }
 
-// The five walls of scene.rs:33-66 and the light of scene.rs:26-32 (as a DiffuseLight rectangle).
-HitablePtr cornell_walls(HitableList& list, MaterialPtr white, double emit) {
+// The five walls of scene.rs:33-66.
+void cornell_walls(HitableList& list, MaterialPtr white) {
   MaterialPtr red = make_shared<Lambertian>(ConstantTexture(Vec3(0.75, 0.25, 0.25)));
   MaterialPtr blue = make_shared<Lambertian>(ConstantTexture(Vec3(0.25, 0.25, 0.75)));
   list.push_back(make_shared<YZRectangle>(make_pair(0.0, 0.0), make_pair(555.0, 555.0), 555., red));
@@ -60,10 +63,10 @@ HitablePtr cornell_walls(HitableList& list, MaterialPtr white, double emit) {
   list.push_back(make_shared<XZRectangle>(make_pair(0., 0.), make_pair(555., 555.), 0., white));
   list.push_back(make_shared<XZRectangle>(make_pair(0., 0.), make_pair(555., 555.), 555., white));
   list.push_back(make_shared<XYRectangle>(make_pair(0., 0.), make_pair(555., 555.), 555., white));
-  // XZRectLight::new((213,227),(343,332),554, flux, scale) (light.rs:134-146): an XZRectangle with a DiffuseLight
-  HitablePtr light = make_shared<XZRectangle>(make_pair(213., 227.), make_pair(343., 332.), 554., make_shared<DiffuseLight>(ConstantTexture(Vec3(emit, emit, emit))));
-  list.push_back(light);
-  return light;
+}
+// XZRectLight::new((213,227),(343,332),554, flux, scale) (light.rs:134-146, scene.rs:26-32): an XZRectangle with a DiffuseLight
+HitablePtr cornell_light(double emit) {
+  return make_shared<XZRectangle>(make_pair(213., 227.), make_pair(343., 332.), 554., make_shared<DiffuseLight>(ConstantTexture(Vec3(emit, emit, emit))));
 }
 
 // The reference's own scene (scene.rs:16-112): glass + mirror spheres, Transform(Mesh(cube.obj)), Cube.
@@ -72,9 +75,11 @@ HitablePtr cornell_walls(HitableList& list, MaterialPtr white, double emit) {
 void cornell_ref(SceneBuilder& sb, const char* obj_path, double aspect, b200rt_camera* cam, b200rt_params* params) {
   MaterialPtr white = make_shared<Lambertian>(ConstantTexture(Vec3(0.75, 0.75, 0.75)));
   HitableList list;
-  HitablePtr light = cornell_walls(list, white, 15.0);
-  list.push_back(make_shared<Sphere>(Vec3(140., 100., 240.), 100., make_shared<Dielectric>(1.5, ConstantTexture(Vec3(0.999, 0.999, 0.999)))));
-  list.push_back(make_shared<Sphere>(Vec3(400., 100., 360.), 100., make_shared<Metal>(ConstantTexture(Vec3(0.999, 0.999, 0.999)), 0.)));
+  cornell_walls(list, white);                                                                                                                     // scene.rs:33-66
+  list.push_back(make_shared<Sphere>(Vec3(140., 100., 240.), 100., make_shared<Dielectric>(1.5, ConstantTexture(Vec3(0.999, 0.999, 0.999)))));  // scene.rs:67-74
+  list.push_back(make_shared<Sphere>(Vec3(400., 100., 360.), 100., make_shared<Metal>(ConstantTexture(Vec3(0.999, 0.999, 0.999)), 0.)));        // scene.rs:75-82
+  HitablePtr light = cornell_light(15.0);                                                                                                         // scene.rs:83
+  list.push_back(light);
   list.push_back(make_shared<Transform>(Vec3::zero(), Vec3::ones() * 50., Vec3(100., 50., 100.), Mesh::load_obj(obj_path ? obj_path : "data/mesh/cube.obj", white)));
   list.push_back(make_shared<Cube>(Vec3(300., 0., 100.), Vec3(380., 100., 180.), white));
   World w(list, Camera(make_pair(Vec3(278., 278., -800.), Vec3(278., 278., 278.)), Vec3(0., 1., 0.), 50., aspect > 0 ? aspect : 1.0, 0.0, 10.0), {light}, sb);
@@ -86,7 +91,9 @@ void cornell_ref(SceneBuilder& sb, const char* obj_path, double aspect, b200rt_c
 void cornell_book3(SceneBuilder& sb, double aspect, b200rt_camera* cam, b200rt_params* params) {
   MaterialPtr white = make_shared<Lambertian>(ConstantTexture(Vec3(0.73, 0.73, 0.73)));
   HitableList list;
-  HitablePtr light = cornell_walls(list, white, 15.0);
+  cornell_walls(list, white);
+  HitablePtr light = cornell_light(15.0);
+  list.push_back(light);
   list.push_back(make_shared<Transform>(Vec3(0, 15, 0), Vec3::ones(), Vec3(265, 0, 295), make_shared<Cube>(Vec3(0, 0, 0), Vec3(165, 330, 165), white)));
   list.push_back(make_shared<Transform>(Vec3(0, -18, 0), Vec3::ones(), Vec3(130, 0, 65), make_shared<Cube>(Vec3(0, 0, 0), Vec3(165, 165, 165), white)));
   World w(list, Camera(make_pair(Vec3(278., 278., -800.), Vec3(278., 278., 0.)), Vec3(0., 1., 0.), 40., aspect > 0 ? aspect : 1.0, 0.0, 10.0), {light}, sb);
@@ -124,7 +131,7 @@ void book2(SceneBuilder& sb, uint64_t seed, const uint8_t* earth, int ew, int eh
   list.push_back(make_shared<Sphere>(Vec3(220, 280, 300), 80, make_shared<Lambertian>(NoiseTexture(0.1))));
   HitableList boxes2;
   MaterialPtr white = make_shared<Lambertian>(ConstantTexture(Vec3(.73, .73, .73)));
-  for (int j = 0; j < 1000; ++j) boxes2.push_back(make_shared<Sphere>(Vec3(rng.range(0, 165), rng.range(0, 165), rng.range(0, 165)), 10, white));
+  for (int j = 0; j < 1000; ++j) { const double x = rng.range(0, 165), y = rng.range(0, 165), z = rng.range(0, 165); boxes2.push_back(make_shared<Sphere>(Vec3(x, y, z), 10, white)); }
   list.push_back(make_shared<Transform>(Vec3(0, 15, 0), Vec3::ones(), Vec3(-100, 270, 395), make_shared<BVHNode>(boxes2)));
   World w(list, Camera(make_pair(Vec3(478, 278, -600), Vec3(278, 278, 0)), Vec3(0, 1, 0), 40.0, aspect > 0 ? aspect : 1.0, 0.0, 10.0, 0.0, 1.0), {light}, sb);
   *cam = w.cam.cam;
@@ -136,7 +143,9 @@ void book2(SceneBuilder& sb, uint64_t seed, const uint8_t* earth, int ew, int eh
 void mesh_scene(SceneBuilder& sb, const char* obj_path, int subdivide, double aspect, b200rt_camera* cam, b200rt_params* params) {
   MaterialPtr white = make_shared<Lambertian>(ConstantTexture(Vec3(0.75, 0.75, 0.75)));
   HitableList list;
-  HitablePtr light = cornell_walls(list, white, 15.0);
+  cornell_walls(list, white);
+  HitablePtr light = cornell_light(15.0);
+  list.push_back(light);
   list.push_back(make_shared<Sphere>(Vec3(430., 80., 150.), 80., make_shared<Metal>(ConstantTexture(Vec3(0.999, 0.999, 0.999)), 0.)));
   // bun315 spans roughly [-0.095,0.061] x [0.033,0.187] x [-0.062,0.059]: scale 2200 -> ~340 units tall
   list.push_back(make_shared<Transform>(Vec3(0, 180, 0), Vec3::ones() * 2200., Vec3(240., -72., 300.), Mesh::load_obj(obj_path ? obj_path : "data/mesh/bun315.obj", white, true, subdivide)));

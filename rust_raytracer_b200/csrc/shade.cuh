@@ -53,8 +53,10 @@ DEV float3 texture_color(const DevScene& S, int tex, const HitInfo& h) {
   }
   if (type == B200RT_TEX_IMAGE) {  // material.rs:70-84 (index clamped; upstream would panic at u == 1)
     const int4 im = __ldg(&S.images[__float_as_int(hd.y)]);
-    float u = fminf(fmaxf(h.u, 0.f), 1.f), v = 1.f - fminf(fmaxf(h.v, 0.f), 1.f);
-    int x = min((int)floorf(im.y * u), im.y - 1), y = min((int)floorf(im.z * v), im.z - 1);
+    // the texel index in f64 from the f32 (u, v): w * u is exact there, so the floor agrees with the f64 reference at every
+    // texel boundary (two DMULs per image-textured hit)
+    const double u = (double)fminf(fmaxf(h.u, 0.f), 1.f), v = 1.0 - (double)fminf(fmaxf(h.v, 0.f), 1.f);
+    int x = min((int)floor((double)im.y * u), im.y - 1), y = min((int)floor((double)im.z * v), im.z - 1);
     const uint8_t* px = S.image_data + im.x + 3 * ((size_t)y * im.y + x);
     return f3(px[0] * (1.f / 255.f), px[1] * (1.f / 255.f), px[2] * (1.f / 255.f));
   }
@@ -173,23 +175,17 @@ DEV float3 refract3(float3 uv, float3 n, float eta) {                        // 
   return perp + par;
 }
 
-// Processes the hit `h` of `ray`: adds emission, samples the next direction.  Returns true when the path
-// continues (ray is replaced).  depth bookkeeping (photon_mapper.rs:334-339) is done by the caller.
+// Material::scatter / emitted for a finished HitRecord `h` with the three uniforms of this bounce supplied by the caller
+// (u1, u2 -> direction sample, u3 -> choice draw): adds emission, samples the next direction.  Returns true when the
+// path continues (ray is replaced).  Split from shade_hit so that the function-level parity operator
+// (b200rt_debug_eval) runs exactly the code the shade kernel runs, on injected inputs.
 // INTEG >= 0 fixes the integrator at compile time (the wavefront shade kernel is instantiated per integrator, so
 // the PATH build carries no light-sampling code: fewer registers, a third of the instructions); -1 reads P.integrator.
 template <int INTEG = -1>
-DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitRaw& hr, PathState& ps, ShadowReq& sreq) {
+DEV bool shade_surface(const DevScene& S, const RenderConst& P, Ray& ray, const HitInfo& h, const float4 mat, const float u1, const float u2, const float u3,
+                       const uint32_t next_seed, PathState& ps, ShadowReq& sreq) {
   const int integrator = INTEG >= 0 ? INTEG : P.integrator;
-  sreq.valid = false;
-  const int4 meta = __ldg(&S.prim_meta[hr.prim]);
-  const float4 mat = __ldg(&S.materials[meta.x >> 8]);
   const int mtype = __float_as_int(mat.x), tex = __float_as_int(mat.y);
-  HitInfo h;
-  finish_hit(S, ray, hr, h, texture_needs_uv(S, tex));
-  ps.bounce++;
-  const uint4 rnd = philox4x32(make_uint4(ps.pixel, ps.sample, (uint32_t)ps.bounce, 0u), P.key);
-  const float u1 = u01(rnd.x), u2 = u01(rnd.y), u3 = u01(rnd.z);
-  const uint32_t next_seed = rnd.w;
   const float3 color = texture_color(S, tex, h);
 
   if (mtype == B200RT_MAT_DIFFUSE_LIGHT) {  // emitted = emit.get_color(rec), both faces (material.rs:209-211)
@@ -297,4 +293,18 @@ DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitR
   ps.throughput = ps.throughput * color;
   ray.o = h.p; ray.d = dir; ray.mseed = next_seed;
   return true;
+}
+
+// Processes the hit `hr` of `ray`: HitRecord::new, the Philox draws of this bounce, then shade_surface.
+// depth bookkeeping (photon_mapper.rs:334-339) is done by the caller.
+template <int INTEG = -1>
+DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitRaw& hr, PathState& ps, ShadowReq& sreq) {
+  sreq.valid = false;
+  const int4 meta = __ldg(&S.prim_meta[hr.prim]);
+  const float4 mat = __ldg(&S.materials[meta.x >> 8]);
+  HitInfo h;
+  finish_hit(S, ray, hr, h, texture_needs_uv(S, __float_as_int(mat.y)));
+  ps.bounce++;
+  const uint4 rnd = philox4x32(make_uint4(ps.pixel, ps.sample, (uint32_t)ps.bounce, 0u), P.key);
+  return shade_surface<INTEG>(S, P, ray, h, mat, u01(rnd.x), u01(rnd.y), u01(rnd.z), rnd.w, ps, sreq);
 }

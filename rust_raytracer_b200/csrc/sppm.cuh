@@ -143,6 +143,7 @@ DEV void sppm_store(float4* photons, unsigned int* counter, unsigned int cap, un
 }
 
 // SPPMIntegrator::generate_photon_map (photon_mapper.rs:238-281)
+template <bool OBJF>
 __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, uint2 key, int iter, float4* pg, float4* pc, unsigned int cap, SppmCounters* cnt) {
   unsigned long long n_rays = 0;
   unsigned int lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
@@ -182,7 +183,7 @@ __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, 
       float3 hp = f3(0, 0, 0), hn = f3(0, 0, 0), hd = f3(0, 0, 0), hpow = f3(0, 0, 0);
       if (alive) {
         HitRaw hr;
-        trace<false>(S, ray, 0.0001f, hr);  // photon_mapper.rs:246
+        trace<false, OBJF>(S, ray, 0.0001f, hr);  // photon_mapper.rs:246
         n_rays++;
         if (hr.prim < 0) alive = false;
         else {
@@ -408,6 +409,7 @@ DEV void sppm_update(const SppmGrid& G, float3 p, float3 bsdf, int k_init, doubl
 }
 
 // SPPMIntegrator::update_sppm (photon_mapper.rs:282-305): one jittered eye ray per pixel and iteration
+template <bool OBJF>
 __global__ void __launch_bounds__(128) k_sppm_eye(DevScene S, RenderConst P, SppmConst sp, int iter, SppmGrid Gg, SppmGrid Gc, SppmPixels px, SppmCounters* cnt) {
   const uint32_t n_pix = (uint32_t)(P.width * P.height);
   unsigned long long n_rays = 0;
@@ -415,7 +417,7 @@ __global__ void __launch_bounds__(128) k_sppm_eye(DevScene S, RenderConst P, Spp
     Ray ray = camera_ray(P, pixel, (uint32_t)iter);
     for (int bounce = 1; bounce <= SPPM_MAX_BOUNCES; ++bounce) {
       HitRaw hr;
-      trace<false>(S, ray, 0.001f, hr);  // photon_mapper.rs:290
+      trace<false, OBJF>(S, ray, 0.001f, hr);  // photon_mapper.rs:290
       n_rays++;
       if (hr.prim < 0) break;
       const int4 meta = __ldg(&S.prim_meta[hr.prim]);
@@ -447,6 +449,7 @@ DEV float3 sppm_adjust(float4 st, float n_emitted) {  // adjust_flux (photon_map
   const float d = PI_F * st.w * n_emitted;
   return f3(st.x / d, st.y / d, st.z / d);
 }
+template <bool OBJF>
 __global__ void __launch_bounds__(128) k_sppm_final(DevScene S, RenderConst P, PathMap M, SppmPixels px, float n_emitted, float* __restrict__ accum, SppmCounters* cnt) {
   unsigned long long n_rays = 0;
   for (unsigned long long id = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; id < M.total; id += (unsigned long long)gridDim.x * blockDim.x) {
@@ -457,7 +460,7 @@ __global__ void __launch_bounds__(128) k_sppm_final(DevScene S, RenderConst P, P
     int depth = P.max_depth;
     for (int bounce = 1;; ++bounce) {
       HitRaw hr;
-      trace<false>(S, ray, P.t_min, hr);
+      trace<false, OBJF>(S, ray, P.t_min, hr);
       n_rays++;
       if (hr.prim < 0 || depth <= 0) break;
       depth--;

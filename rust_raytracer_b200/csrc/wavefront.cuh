@@ -67,8 +67,10 @@ struct WfBuffers {
 };
 
 // Append one element per participating lane with a single atomic per warp (warp-aggregated compaction).
+// Must be called with the whole warp converged (every call site sits at the top level of a loop that whole warps
+// walk together): the vote names all 32 lanes instead of guessing them with __activemask().
 DEV unsigned int warp_append(unsigned int* counter, bool pred) {
-  const unsigned mask = __ballot_sync(__activemask(), pred);
+  const unsigned mask = __ballot_sync(0xffffffffu, pred);
   if (!pred) return 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
   const int leader = __ffs(mask) - 1;
@@ -165,6 +167,7 @@ __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->
 DEV unsigned int wf_pack_prim(int prim, int aux) { return (unsigned int)(prim + 2) | ((unsigned int)aux << 28); }
 DEV int wf_unpack_prim(unsigned int w) { return (int)(w & 0x0FFFFFFFu) - 2; }
 DEV int wf_unpack_aux(unsigned int w) { return (int)(w >> 28); }
+template <bool OBJF>
 __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevScene S, WfBuffers B, float t_min, int light_scatters) {
   const unsigned int n = B.cnt->n_ext;
   const unsigned lane = threadIdx.x & 31;
@@ -189,19 +192,23 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     unsigned int bin = WF_NO_BIN;  // "does not go on"
     HitRaw h;
     h.t = 0.; h.prim = WF_PRIM_DEAD; h.aux = 0;
+    DBG_RAY(h.dbg = 0);
     bool dead = false;
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f), d = o;
     if (active) {
-      const float4 o = WF_LD(ray + 0), d = WF_LD(ray + 1);
+      o = WF_LD(ray + 0); d = WF_LD(ray + 1);
       dead = d.x == 0.f && d.y == 0.f && d.z == 0.f;
-      if (!dead) {
-        Ray r;
-        r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = __int_as_float(0x7f800000); r.mseed = __float_as_uint(d.w);
-        trace<false>(S, r, t_min, h);
-        if (h.prim >= 0) {  // will the path go on?  Every material scatters except DiffuseLight (material.rs:201-212 behind a flag)
-          const int4 meta = __ldg(&S.prim_meta[h.prim]);
-          const int mtype = __float_as_int(__ldg(&S.materials[meta.x >> 8]).x);
-          if (mtype != B200RT_MAT_DIFFUSE_LIGHT || light_scatters) bin = 1u + __umulhi((unsigned int)h.prim, B.bin_mul);
-        }
+    }
+    // the lanes that traverse, taken with the warp converged: trace() lets exactly these wait for each other
+    const unsigned tracing = __ballot_sync(0xffffffffu, active && !dead);
+    if (active && !dead) {
+      Ray r;
+      r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = __int_as_float(0x7f800000); r.mseed = __float_as_uint(d.w);
+      trace<false, OBJF>(S, r, t_min, h, tracing);
+      if (h.prim >= 0) {  // will the path go on?  Every material scatters except DiffuseLight (material.rs:201-212 behind a flag)
+        const int4 meta = __ldg(&S.prim_meta[h.prim]);
+        const int mtype = __float_as_int(__ldg(&S.materials[meta.x >> 8]).x);
+        if (mtype != B200RT_MAT_DIFFUSE_LIGHT || light_scatters) bin = 1u + __umulhi((unsigned int)h.prim, B.bin_mul);
       }
     }
     // rank inside the bin: the leader lane of every bin present in the warp issues its atomic in the same
@@ -214,6 +221,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     rank = __shfl_sync(0xffffffffu, rank, leader) + __popc(peers & ((1u << lane) - 1u));
     const unsigned n_dead = __popc(__ballot_sync(0xffffffffu, dead));
     if (n_dead && lane == 0) atomicAdd(&B.cnt->dead_rays, n_dead);
+    DBG_RAY(if (active && g_dbg_steps) g_dbg_steps[i] = dead ? 0xffffffffu : h.dbg);
     if (active) {
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
       WF_ST(B.hit + i, make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), wf_pack_prim(h.prim, h.aux), goes_on ? rank : WF_NO_RANK));
@@ -327,6 +335,7 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
 }
 
 // shadow: any-hit traversal of the light-sample rays; unoccluded samples add their contribution
+template <bool OBJF>
 __global__ void __launch_bounds__(128) k_wf_shadow(DevScene S, WfBuffers B, float t_min, float* __restrict__ accum) {
   const unsigned int n = B.cnt->n_shadow;
   const unsigned lane = threadIdx.x & 31;
@@ -341,7 +350,7 @@ __global__ void __launch_bounds__(128) k_wf_shadow(DevScene S, WfBuffers B, floa
       Ray r;
       r.o = f3(o); r.time = o.w; r.d = f3(d); r.tmax = d.w; r.mseed = B.sh_seed[i];
       HitRaw h;
-      trace<true>(S, r, t_min, h);
+      trace<true, OBJF>(S, r, t_min, h);
       if (h.prim < 0) accum_add(accum, __float_as_uint(c.w), f3(c));
     }
   }

@@ -105,6 +105,15 @@ class Scene:
         self.ctx._ok(F.lib().b200rt_intersect_batch(self._h, o.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p), seed_ptr, n, t_min, out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def debug_eval(self, kind, camera, params, rows):
+        """b200rt_debug_eval: single functions of the hot path on the device at caller-supplied inputs (F.EVAL_*).
+        rows: float32 (n, 8 | 20 | 2 | 8); returns float32 (n, 4 | 16 | 16 | 12)."""
+        in_w, out_w = {F.EVAL_TEXTURE: (8, 4), F.EVAL_SCATTER: (20, 16), F.EVAL_CAMERA: (2, 16), F.EVAL_SAMPLERS: (8, 12)}[kind]
+        a = np.ascontiguousarray(rows, dtype=np.float32).reshape(-1, in_w)
+        out = np.zeros((a.shape[0], out_w), np.float32)
+        self.ctx._ok(F.lib().b200rt_debug_eval(self._h, C.byref(camera), C.byref(params), kind, a.shape[0], a.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+        return out
+
     def render(self, camera, params):
         """capture_image into a fresh host buffer: returns (accum[h,w,4] float32 sums + count, Stats)."""
         accum = np.zeros((params.height, params.width, 4), np.float32)
@@ -128,6 +137,16 @@ class Scene:
         st = F.Stats()
         self.ctx._ok(F.lib().b200rt_render_device(self._h, C.byref(camera), C.byref(params), C.c_void_p(accum_ptr), C.byref(st)))
         return st
+
+
+def compile_stats(builder_or_desc):
+    """Host only: the wide BVH scene_create would build — {"bvh_nodes", "bvh4_depth", "stack_needed", "stack_capacity"}."""
+    desc = builder_or_desc.desc() if hasattr(builder_or_desc, "desc") else builder_or_desc
+    v = [C.c_uint32() for _ in range(4)]
+    rc = F.lib().b200rt_scene_compile_stats(C.byref(desc), *[C.byref(x) for x in v])
+    if rc:
+        raise B200RTError(rc, "scene_compile_stats")
+    return dict(zip(("bvh_nodes", "bvh4_depth", "stack_needed", "stack_capacity"), [x.value for x in v]))
 
 
 def render_multi(scenes, camera, params):

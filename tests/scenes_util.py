@@ -9,10 +9,33 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DATA = os.path.join(ROOT, "data")
 
 
+_EARTH = None
+
+
 def earth_rgb():
-    """Decoded texture/earthmap.jpg (decode once on the host; the same RGB8 array feeds oracle and GPU)."""
-    npy = os.path.join(ROOT, "tests", "golden", "earthmap_256x128.npy")
-    return np.load(npy)
+    """Decoded data/earthmap.jpg, 1024x512 — the texture bench.py renders with (decode once on the host: the same RGB8
+    array feeds oracle and GPU, so the decoder choice cancels out); the 256x128 fixture only if PIL is missing."""
+    global _EARTH
+    if _EARTH is None:
+        try:
+            from PIL import Image
+            _EARTH = np.ascontiguousarray(np.asarray(Image.open(os.path.join(DATA, "earthmap.jpg")).convert("RGB"), dtype=np.uint8))
+        except Exception:
+            _EARTH = np.load(os.path.join(ROOT, "tests", "golden", "earthmap_256x128.npy"))
+    return _EARTH
+
+
+AUX = {"cornell_ref": os.path.join(DATA, "mesh", "cube.obj"), "mesh": os.path.join(DATA, "mesh", "bun315.obj"),
+       "mesh_small": os.path.join(DATA, "mesh", "bun315.obj")}
+
+
+def oracle_scene(name, seed=1, tri_pad=0.0):
+    """The oracle's OWN construction of a canonical scene / JSON file (oracle/oracle_scenes.inc): built inside liboracle.so as
+    the reference's object graph, never from the product's tables."""
+    from oracle_ffi import OracleScene
+    if name.startswith("json:"):
+        return OracleScene.load_json(open(os.path.join(DATA, name[5:] + ".json")).read())
+    return OracleScene.make(name, seed=seed, aux_path=AUX.get(name), earth=earth_rgb() if name == "book2" else None, tri_pad=tri_pad)
 
 
 def scene_builder(name, seed=1):
@@ -21,8 +44,7 @@ def scene_builder(name, seed=1):
         sb = rt.SceneBuilder().load_json(open(path).read())
         sb.params = rt.make_params(192, 108, 8)
         return sb
-    aux = {"cornell_ref": os.path.join(DATA, "mesh", "cube.obj"), "mesh": os.path.join(DATA, "mesh", "bun315.obj"),
-           "mesh_small": os.path.join(DATA, "mesh", "bun315.obj")}.get(name)
+    aux = AUX.get(name)
     earth = earth_rgb() if name == "book2" else None
     return rt.SceneBuilder().make_scene(name, seed=seed, aux_path=aux, earth=earth)
 

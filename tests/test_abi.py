@@ -52,7 +52,8 @@ def test_package_does_not_touch_the_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")) and f != "build.py":
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
-                assert "liboracle" not in text and "oracle_ffi" not in text and "oracle/" not in text.replace("the oracle/", ""), os.path.join(dirpath, f)
+                code = text.replace("the oracle/", "").replace("(oracle/oracle_scenes.inc)", "")  # comments may NAME the checker
+                assert "liboracle" not in code and "oracle_ffi" not in code and "oracle_py" not in code and "oracle/" not in code, os.path.join(dirpath, f)
 
 
 def test_write_png_round_trip(built, tmp_path):

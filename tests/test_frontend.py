@@ -1,4 +1,5 @@
 """Host logic: the mirror of the reference's construction API flattens into the tables of include/b200rt.h."""
+import ctypes as C
 import json
 import os
 
@@ -123,25 +124,68 @@ def test_json_errors():
 
 
 def test_transform_composition_and_rotated_shapes():
-    """M = T*S*Rx*Ry*Rz (transform.rs:28-106); a rotated Cube is emitted as 12 flat triangles, a rotated sphere stays a sphere."""
+    """M = T*S*Rx*Ry*Rz (transform.rs:28-106).  Every shape keeps its own type under any Transform (transform.rs:17-165 takes
+    any rotation, scale: Vec3 and any child): a rotated Cube stays ONE box primitive with an instance matrix (rectangle uv and
+    the six-rect tie rule of cube.rs:63-66 survive), and a sphere under a non-uniform scale is accepted (object-space test)."""
     white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
     items = rt.HitableList([
         rt.Transform((10, 20, 30), (2, 2, 2), (1, 2, 3), rt.Sphere((0, 0, 0), 1, white)),
         rt.Transform((0, 15, 0), (1, 1, 1), (265, 0, 295), rt.Cube((0, 0, 0), (165, 330, 165), white)),
         rt.Transform((0, 0, 0), (2, 3, 4), (0, 0, 0), rt.Cube((0, 0, 0), (1, 1, 1), white)),
+        rt.Transform((30, 0, 0), (1, 1, 1), (0, 0, 0), rt.XZRectangle((0, 0), (1, 1), 0.5, white)),
+        rt.Transform((0, 0, 0), (1, 2, 1), (0, 0, 0), rt.Sphere((0, 0, 0), 1, white)),  # an ellipsoid in world space
+        rt.Transform((0, 0, 45), (1, 1, 1), (5, 0, 0), rt.ConstantMedium(0.5, rt.Cube((0, 0, 0), (1, 1, 1), white), rt.Isotropic(rt.ConstantTexture((1, 1, 1))))),
+        rt.Sphere((0, 0, 0), -0.9, white),  # negative radius: the hollow-sphere idiom (sphere.rs:44 divides by r)
     ])
     d = rt.World(items, rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1)).builder.desc()
     types = [d.prims[i].type for i in range(d.n_prims)]
-    assert types == [F.PRIM_SPHERE] + [F.PRIM_TRIANGLE] * 12 + [F.PRIM_BOX]
+    assert types == [F.PRIM_SPHERE, F.PRIM_BOX, F.PRIM_BOX, F.PRIM_XZ_RECT, F.PRIM_SPHERE, F.PRIM_MEDIUM_BOX, F.PRIM_SPHERE]
+    assert [d.prims[i].instance for i in range(d.n_prims)] == [0, 1, 2, 3, 4, 5, -1]
     rx, ry, rz = np.radians([10, 20, 30])
     Rx = np.array([[1, 0, 0], [0, np.cos(rx), -np.sin(rx)], [0, np.sin(rx), np.cos(rx)]])
     Ry = np.array([[np.cos(ry), 0, np.sin(ry)], [0, 1, 0], [-np.sin(ry), 0, np.cos(ry)]])
     Rz = np.array([[np.cos(rz), -np.sin(rz), 0], [np.sin(rz), np.cos(rz), 0], [0, 0, 1]])
     want = np.hstack([2 * Rx @ Ry @ Rz, [[1], [2], [3]]])
     np.testing.assert_allclose(np.array(d.instances[0].m[:]).reshape(3, 4), want, atol=1e-15)
-    with pytest.raises(rt.B200RTError) as e:  # ellipsoid
-        rt.World(rt.HitableList([rt.Transform((0, 0, 0), (1, 2, 1), (0, 0, 0), rt.Sphere((0, 0, 0), 1, white))]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
-    assert e.value.status == F.ERR_UNSUPPORTED
+    st = rt.compile_stats(d)  # World::new's host half accepts all of it (no CUDA needed)
+    assert st["bvh_nodes"] >= 1 and st["stack_needed"] <= st["stack_capacity"]
+    sb = rt.SceneBuilder()
+    m = sb._id(F.lib().b200rt_builder_material(sb.handle, F.MAT_LAMBERTIAN, sb._id(F.lib().b200rt_builder_texture_constant(sb.handle, 1, 1, 1)), 0))
+    sb._id(F.lib().b200rt_builder_sphere(sb.handle, F.d3((0, 0, 0)), 0.0, m))
+    with pytest.raises(rt.B200RTError) as e:  # radius 0 divides by zero upstream
+        rt.compile_stats(sb)
+    assert e.value.status == F.ERR_INVALID
+
+
+def test_bvh_depth_is_bounded_by_the_traversal_stack():
+    """The device keeps a per-thread traversal stack and pushes up to 3 entries per BVH4 level.  A chain of spheres of
+    geometrically growing size along a line makes a plain SAH build peel one primitive per level (binary depth ~n): World::new
+    must come back with a tree whose deepest path fits the stack (rebuilt under a depth budget), never with a silent overflow."""
+    white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
+    for n, ratio in ((200, 1.6), (400, 1.2), (3000, 1.01)):
+        items, x, r = [], 0.0, 1e-3
+        for _ in range(n):
+            items.append(rt.Sphere((x + r, 0, 0), r, white))
+            x += 2 * r
+            r *= ratio
+            if r > 1e30:
+                break
+        st = rt.compile_stats(rt.World(rt.HitableList(items), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1)).builder)
+        assert st["stack_needed"] == 3 * st["bvh4_depth"] and st["stack_needed"] <= st["stack_capacity"], (n, st)
+    st = rt.compile_stats(scene_builder("book2"))
+    assert st["bvh4_depth"] <= 10  # the budget never touches an ordinary scene
+
+
+def test_scene_500_yaml_builds_the_same_tables_as_its_json_twin():
+    """README.md:86-89: data/scene_500.yaml (894 KB, 1,005 spheres, 999 BVHNodes) carries the same objects as scene_500.json."""
+    a = rt.SceneBuilder().load_json(open(os.path.join(DATA, "scene_500.json")).read())
+    b = rt.SceneBuilder().load_yaml(open(os.path.join(DATA, "scene_500.yaml")).read())
+    da, db = a.desc(), b.desc()
+    assert da.n_prims == db.n_prims == 1005 and da.n_materials == db.n_materials and da.n_textures == db.n_textures and da.flags == db.flags
+    assert bytes(C.string_at(da.prims, 64 * da.n_prims)) == bytes(C.string_at(db.prims, 64 * db.n_prims))
+    assert bytes(C.string_at(da.materials, 16 * da.n_materials)) == bytes(C.string_at(db.materials, 16 * db.n_materials))
+    assert bytes(C.string_at(da.textures, 48 * da.n_textures)) == bytes(C.string_at(db.textures, 48 * db.n_textures))
+    assert bytes(a.camera) == bytes(b.camera)
 
 
 def test_camera_new_matches_reference_formula():
