@@ -22,21 +22,18 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WIDTH, HEIGHT = 800, 800
-SPP_PER_STEP = 512          # per GPU and step = one capture_image call; the full job is 10,000 spp.  A call drains its pool once at the
-                            # end, so throughput rises with its size: 128 / 256 / 512 / 1250 spp per call = 1477 / 1515 / 1529 / 1535 Mpaths/s
-FULL_JOB_SPP = 10000
+FULL_JOB_SPP = 10000        # BASELINE.json: "book-2 final scene 800x800, 10k spp at 1/2/4/8 B200" — the default step IS that job,
+                            # split over the ranks by sample index (strong scaling: the total work is fixed as N grows)
+SPP_PER_STEP = 512          # --scaling weak: per GPU and step (one capture_image call).  A call drains its pool once at the end, so
+                            # throughput rises with its size: 128 / 256 / 512 / 1250 spp per call = 1477 / 1515 / 1529 / 1535 Mpaths/s
 METRIC = "Mpaths/s (device-timed) on book-2 final scene"
 UNIT = "Mpaths/s"
 # extend kernel, per ray: the 32-byte ray stream read (o, time | d, medium seed) + the 16-byte hit written (t as f64, prim, rank)
 EXTEND_BYTES_PER_RAY = 48
 SEGMENT_BYTES_PIPELINE = 128  # ray 32 + hit 16 + state 16, written once and read once
-# ncu --set full, k_wf_extend, launch of 18,292,061 rays: dram__bytes_read.sum 0.5996 GB + dram__bytes_write.sum 0.3108 GB
-# (profiles/r1_final2_extend_shade_full.txt) -> DRAM bytes per ray; issue/lane figures from the same capture
-EXTEND_DRAM_BYTES_PER_RAY_NCU = (0.599593e9 + 310.840576e6) / 18292061
-EXTEND_NCU = {"issue_active_pct": 76.4, "alu_pipe_pct": 48.6, "fma_pipe_pct": 27.3, "fp64_pipe_pct": 6.3, "lanes_per_instruction": 14.4,
-              "warp_instructions_per_32_rays": 3144, "l1_hit_pct": 86.3, "l2_hit_pct": 73.6, "dram_pct_of_peak": 5.4,
-              "shade_issue_active_pct": 50.8, "shade_dram_pct_of_peak": 36.0, "shade_dram_bytes_per_ray": 125.2,
-              "source": "profiles/r1_final2_extend_shade_full.txt"}
+PATH_BYTES = 32               # one float4 framebuffer read-modify-write per path
+# ncu --set full of the dominant kernel (constants of one committed capture; bench.py measures everything else live)
+NCU = json.load(open(os.path.join(ROOT, "profiles", "ncu_constants.json")))
 
 
 def earth_image():
@@ -106,16 +103,96 @@ def measured_peaks():
 
 
 def cpu_baseline_run(spp, threads, seed=1):
-    """The oracle (C++ f64 restatement of the reference) on the host cores: returns (Mpaths/s, Mrays/s, seconds)."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import rust_raytracer_b200 as rt
-    from oracle_ffi import OracleScene
-    sb, params = build_scene_builder()
-    orc = OracleScene(sb)
-    p = rt.copy_params(params, spp_count=spp, seed=seed)
-    _, ext, shd, sec = orc.render(sb.camera, p, n_jobs=max(64, 4 * threads), n_threads=threads)
+    """The oracle (C++ f64 restatement of the reference) on the host cores: returns (Mpaths/s, Mrays/s, seconds).
+    The scene is the oracle's OWN construction of the book-2 fixture (oracle/oracle_scenes.inc: the reference's object graph
+    with nested BVHNode::new, Transform over the sphere BVH, ConstantMedium over its boundary); nothing of the product is
+    imported or mapped on this path (oracle/oracle_py.py is standalone)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py
+    orc = oracle_py.OracleScene.make("book2", seed=1, earth=earth_image())
+    p = oracle_py.copy_params(orc.params, width=WIDTH, height=HEIGHT, spp_count=spp, seed=seed)
+    _, ext, shd, sec = orc.render(orc.camera, p, n_jobs=max(64, 4 * threads), n_threads=threads)
     paths = WIDTH * HEIGHT * spp
     return paths / sec / 1e6, (ext + shd) / sec / 1e6, sec
+
+
+def algorithmic_flops():
+    """flops_alg = sum(counts x C), the counts measured on this box by the -DB200RT_COUNTERS twin of the
+    library on the benchmark scene (tools/opcount.py, a child process; never on the timed path)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import opcount
+    return opcount.algorithmic_flops("book2", WIDTH, HEIGHT, "path")
+
+
+def run_sppm(args):
+    """--workload sppm: what the reference's main() renders (main.rs:33-53): scene.rs:16-112 at 800x800, SPPMIntegrator::new =
+    50 iterations x 500,000 photons (photon_mapper.rs:148-149), then capture_image at 256 spp over SPPMIntegrator::sample_ray.
+    One step = one such frame through b200rt_render_sppm (host buffers in and out: the timed region is the public call).
+    cpu_baseline: the oracle restatement on bounded samples (one iteration at two small image sizes + a few final-pass samples)
+    scaled to the full job, which is exact for this algorithm (every iteration, pixel and sample costs the same on average);
+    its k-nearest is an exhaustive scan standing in for kd-tree 0.4.1, so only its photon pass and final pass are like for like."""
+    import time as _t
+    import numpy as np
+    import rust_raytracer_b200 as rt
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from scenes_util import scene_builder, oracle_scene
+    W = H = 800
+    ITER, PHOTONS, SPP = 50, 500000, 256
+    sb = scene_builder("cornell_ref")
+    ctx = rt.Context(0)
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=W, height=H, spp_count=SPP, seed=1)
+    for _ in range(max(args.warmup, 1)):
+        scene.render_sppm(sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS)
+    sampler = ClockSampler(0)
+    sampler.start()
+    ms, wall, last = [], [], None
+    for i in range(args.steps):
+        t0 = _t.perf_counter()
+        acc, st = scene.render_sppm(sb.camera, rt.copy_params(p, seed=2 + i), iterations=ITER, photons_per_iter=PHOTONS)
+        wall.append(_t.perf_counter() - t0)
+        ms.append(st.ms_total)
+        last = st
+    _t.sleep(0.3)
+    sampler.stop()
+    st = last
+    cpu = None
+    if not args.no_cpu_baseline:
+        threads = os.cpu_count() or 8
+        orc = oracle_scene("cornell_ref")
+        small = max(20000, PHOTONS // 25)  # photons of the bounded sample (the per-photon cost is constant)
+
+        def cpu_run(size, spp):
+            t0 = _t.perf_counter()
+            orc.sppm_render(sb.camera, rt.copy_params(p, width=size, height=size, spp_count=spp), iterations=1, photons_per_iter=small, n_threads=threads)
+            return _t.perf_counter() - t0
+        t_a, t_b, t_c = cpu_run(8, 1), cpu_run(48, 1), cpu_run(48, 9)
+        per_sample = max(t_c - t_b, 0.0) / 8 / (48 * 48)
+        per_px = max(t_b - t_a - (48 * 48 - 64) * per_sample, 0.0) / (48 * 48 - 64)   # eye pass + exhaustive k-nearest over `small` photons
+        per_photon = max(t_a - 64 * (per_px + per_sample), 0.0) / small
+        est_like_for_like = ITER * PHOTONS * per_photon + SPP * W * H * per_sample
+        cpu = {"value": est_like_for_like * 1e3, "unit": "ms per frame (photon passes + final pass only)", "cores": threads, "kind": "port",
+               "sample": "1 iteration x %d photons at 8x8 (%.1f s), 48x48 (%.1f s), 48x48 with 9 spp (%.1f s), scaled to 50 x 500,000 photons and 800x800x256 samples" % (small, t_a, t_b, t_c),
+               "us_per_photon": per_photon * 1e6, "us_per_final_sample": per_sample * 1e6,
+               "note": "the oracle's eye pass replaces kd-tree 0.4.1 by an exhaustive scan (a checker, not a baseline) and is left out of this figure; the GPU time beside it is ms_photons + ms_final"}
+    n_emit, n_eye, n_final = ITER * PHOTONS, ITER * W * H, SPP * W * H
+    out = {"metric": "SPPM frame of the reference's main() (cornell_ref 800x800, 50 x 500,000 photons, 256 spp)", "value": float(np.mean(ms)), "unit": "ms per frame",
+           "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": float(np.mean(ms)), "higher_is_better": False, "scaling": "n/a (one device)", "vs_baseline": None,
+           "dtype": "f32 (f64 hit confirmation)", "data": "synthetic",
+           "config": {"workload": "SPPMIntegrator::new + capture_image (photon_mapper.rs:139-236, 327-365; main.rs:33-53)", "iterations": ITER, "photons_per_iteration": PHOTONS, "spp": SPP},
+           "stage_ms": {"photons": st.ms_photons, "grid": st.ms_grid, "eye": st.ms_eye, "final": st.ms_final, "total": st.ms_total,
+                        "note": "the photon pass of iteration i+1 runs on a second stream under the grid build and eye pass of iteration i: the stage times overlap"},
+           "rates": {"Mphotons_emitted_per_s": n_emit / st.ms_photons / 1e3, "Mphoton_rays_per_s": st.photon_rays / st.ms_photons / 1e3,
+                     "Meye_updates_per_s": n_eye / st.ms_eye / 1e3, "Mfinal_paths_per_s": n_final / st.ms_final / 1e3},
+           "photons_stored": {"global": int(st.global_photons), "caustic": int(st.caustic_photons)},
+           "roofline": {"bound": "hbm", "kernel": "k_sppm_eye (radius gather)", "achieved": None, "peak": measured_peaks()[0]["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None,
+                        "note": "not HBM-bound: the eye pass walks photon cells per pixel (latency / divergence bound, profiles/r1_sppm_full_summary.txt); no roofline fraction is claimed for SPPM"},
+           "cpu_baseline": cpu,
+           "e2e": {"value": float(np.mean(wall)) * 1e3, "unit": "ms per frame", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": W * H * 16,
+                   "what": "host clock around b200rt_render_sppm (image returned to a host buffer)"},
+           "gpu_launches": None, "clocks": sampler.summary(), "device": ctx.device_info()}
+    print(json.dumps(out))
+    return 0
 
 
 def run_reference(args):
@@ -156,11 +233,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200rt")
     ap.add_argument("--pipeline", default="wavefront", choices=["wavefront", "megakernel"])
-    ap.add_argument("--spp", type=int, default=SPP_PER_STEP)
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default): a step is the full 10,000-spp job split over the ranks; weak: --spp samples per GPU per step")
+    ap.add_argument("--spp", type=int, default=0, help="strong: total spp of the job (default 10000); weak: spp per GPU per step (default 512)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="path", choices=["path", "sppm"], help="path: the BASELINE.json metric (default); sppm: the reference's own main()")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "sppm":
+        return run_sppm(args)
     args.warmup = max(args.warmup, 3)
 
     import numpy as np
@@ -180,7 +262,14 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version / debug lines must not precede the JSON line on stdout
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
-    spp = args.spp
+    strong = args.scaling == "strong"
+    job_spp = args.spp or (FULL_JOB_SPP if strong else SPP_PER_STEP)
+    if strong:  # contiguous sample ranges of the fixed job, remainder to the first ranks
+        spp = job_spp // world + (1 if rank < job_spp % world else 0)
+        rank_first = rank * (job_spp // world) + min(rank, job_spp % world)
+        step_spp = job_spp
+    else:
+        spp, rank_first, step_spp = job_spp, rank * job_spp, job_spp * world
 
     ctx = rt.Context(local_rank)
     stream = torch.cuda.current_stream()
@@ -200,15 +289,16 @@ def main():
 
     def one_step(step_index, stats_acc):
         # global sample range of this rank for this step: disjoint across ranks and steps
-        begin = (step_index * world + rank) * spp
+        begin = step_index * step_spp + rank_first
         p = rt.copy_params(params, spp_begin=begin)
         accum.zero_()
         st = scene.render_device(sb.camera, p, accum.data_ptr())
         reduce_accum(accum, dst=0)
         for k in ("paths", "extend_rays", "shadow_rays", "kernel_launches", "wavefront_iterations"):
             stats_acc[k] = stats_acc.get(k, 0) + getattr(st, k)
-        for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total"):
+        for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total", "ms_generate_sum", "ms_extend_sum", "ms_shade_sum", "ms_shadow_sum"):
             stats_acc[k] = stats_acc.get(k, 0.0) + getattr(st, k)
+        stats_acc["pipelines"] = st.pipelines
 
     warm = {}
     for i in range(args.warmup):
@@ -246,7 +336,7 @@ def main():
 
     # ---- end to end through the public API with HOST buffers: scene tables H2D + render + reduce + image D2H
     host_img = torch.empty((HEIGHT, WIDTH, 4), dtype=torch.float32).pin_memory()
-    e2e_steps = max(3, min(args.steps, 5))
+    e2e_steps = 3
     e2e_marks = []
     sync_all()
     t0 = time.perf_counter()
@@ -255,7 +345,7 @@ def main():
             sync_all()
             t0 = time.perf_counter()
         sc2 = rt.Scene(ctx, sb)  # World::new: validate, bake, build the BVH, upload (H2D)
-        begin = ((args.warmup + args.steps + i) * world + rank) * spp
+        begin = (args.warmup + args.steps + 1 + i) * step_spp + rank_first
         accum.zero_()
         sc2.render_device(sb.camera, rt.copy_params(params, spp_begin=begin), accum.data_ptr())
         reduce_accum(accum, dst=0)
@@ -269,27 +359,65 @@ def main():
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_value = WIDTH * HEIGHT * spp * world * e2e_steps / float(e2e_t.item()) / 1e6
+    e2e_value = WIDTH * HEIGHT * step_spp * e2e_steps / float(e2e_t.item()) / 1e6
+
+    # ---- one step with ONE pipeline (rank 0): clean per-kernel durations (with two concurrent pipelines the stage intervals overlap)
+    single = None
+    if rank == 0 and args.pipeline == "wavefront":
+        os.environ["B200RT_WF_PIPES"] = "1"
+        try:
+            single = {}
+            torch.cuda.synchronize()
+            p1 = rt.copy_params(params, spp_begin=(args.warmup + args.steps + e2e_steps + 2) * step_spp, spp_count=min(spp, 512))
+            accum.zero_()
+            st1 = scene.render_device(sb.camera, p1, accum.data_ptr())
+            for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total"):
+                single[k] = getattr(st1, k)
+            single.update(spp=min(spp, 512), iterations=st1.wavefront_iterations, extend_rays=int(st1.extend_rays), paths=int(st1.paths))
+        finally:
+            os.environ.pop("B200RT_WF_PIPES", None)
 
     if rank == 0:
         peaks, peak_kind = measured_peaks()
-        n_ext_launches = max(1, stats["wavefront_iterations"]) if args.pipeline == "wavefront" else args.steps
-        ext_ms = stats["ms_extend"]
-        rays_per_launch = stats["extend_rays"] / n_ext_launches
-        achieved = EXTEND_BYTES_PER_RAY * stats["extend_rays"] / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None
         fp32_tflops, eff_mhz = ctx.measure_fp32_peak()
+        flops_per_path, flop_detail = algorithmic_flops() if args.pipeline == "wavefront" else (None, "megakernel")
+        n_iter = max(1, stats["wavefront_iterations"])
+        rays_per_path = (ext + shd) / paths
+        # the dominant kernel, k_wf_extend, from the single-pipeline step: its launches do not overlap anything there
+        if single and single["iterations"] > 0 and single["ms_extend"] > 0:
+            ext_launch_ms = single["ms_extend"] / single["iterations"]
+            ext_rays_launch = single["extend_rays"] / single["iterations"]
+            ext_share = single["ms_extend"] / single["ms_total"]
+            paths_launch = single["paths"] / single["iterations"]
+        else:
+            ext_launch_ms = ext_rays_launch = ext_share = paths_launch = None
+        ext_flops_path = (flop_detail["flop_per_path"]["box_tests"] + flop_detail["flop_per_path"]["primitive_tests"]) if flops_per_path else None
+        ext_tflops = ext_flops_path * paths_launch / (ext_launch_ms * 1e-3) / 1e12 if (ext_flops_path and ext_launch_ms) else None
+        ext_gbs = EXTEND_BYTES_PER_RAY * ext_rays_launch / (ext_launch_ms * 1e-3) / 1e9 if ext_launch_ms else None
+        lanes = NCU["extend"]["lanes_per_instruction"]
+        pipeline_bytes = SEGMENT_BYTES_PIPELINE * ext + 96 * shd + PATH_BYTES * paths
         roofline = {
-            "bound": "hbm", "kernel": "k_wf_extend" if args.pipeline == "wavefront" else "k_megakernel",
-            "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (achieved / peaks["hbm_gbs"]) if achieved else None,
-            "peak_source": "MEASURED_PEAKS.json (%s)" % peak_kind,
-            "traffic": EXTEND_DRAM_BYTES_PER_RAY_NCU * rays_per_launch if args.pipeline == "wavefront" else None,
-            "traffic_note": "ncu dram bytes per ray of one launch (%.1f B against %d algorithmic: the ray stream is read whole, the rest is local-memory stack traffic) x rays of the average launch" % (EXTEND_DRAM_BYTES_PER_RAY_NCU, EXTEND_BYTES_PER_RAY),
-            "bytes_per_ray": EXTEND_BYTES_PER_RAY, "rays_per_launch": rays_per_launch, "launches": n_ext_launches,
-            "avg_launch_ms": ext_ms / n_ext_launches, "kernel_share_of_step": ext_ms / max(stats["ms_total"], 1e-9),
-            "note": "BVH traversal is instruction-issue bound under divergence, not HBM bound (scene is L2-resident): see issue, fp32 and DESIGN.md; the duration is the union of the extend launches' event intervals over the two concurrent pipelines (time during which an extend launch was in flight)",
-            "issue": EXTEND_NCU,
-            "pipeline_bytes_per_segment": SEGMENT_BYTES_PIPELINE,
-            "pipeline_hbm_frac": SEGMENT_BYTES_PIPELINE * (ext + shd) / total_s / 1e9 / peaks["hbm_gbs"],
+            "bound": "fp32_issue", "kernel": "k_wf_extend" if args.pipeline == "wavefront" else "k_megakernel",
+            "achieved": ext_tflops, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": (ext_tflops / fp32_tflops) if ext_tflops else None,
+            "fp32_frac": (ext_tflops / fp32_tflops) if ext_tflops else None,
+            "peak_source": "measured live: k_fma_peak (8 independent FMA chains per thread, 8 x 256 threads per SM), %.0f MHz effective" % eff_mhz,
+            "what": "SURVEY.md section 8(d): algorithmic flops of the launch = (25 flop x ray-box slab tests + per-type constants x primitive tests), the operation counts measured on this box by the -DB200RT_COUNTERS twin of the library on the same scene, x paths per launch / the kernel's average launch duration in a single-pipeline step (CUDA events)",
+            "flops_per_path_kernel": ext_flops_path, "paths_per_launch": paths_launch, "rays_per_launch": ext_rays_launch, "avg_launch_ms": ext_launch_ms,
+            "kernel_share_of_step": ext_share,
+            "issue": {"issue_active_pct": NCU["extend"]["issue_active_pct"], "fma_pipe_pct": NCU["extend"]["fma_pipe_pct"], "lanes_per_instruction": lanes,
+                      "lane_weighted_fma_pipe_pct": NCU["extend"]["fma_pipe_pct"] * lanes / 32.0, "alu_pipe_pct": NCU["extend"]["alu_pipe_pct"],
+                      "fp64_pipe_pct": NCU["extend"]["fp64_pipe_pct"], "l1_hit_pct": NCU["extend"]["l1_hit_pct"], "l2_hit_pct": NCU["extend"]["l2_hit_pct"],
+                      "source": NCU["source"]},
+            "traffic": NCU["extend"]["dram_bytes_per_ray"] * ext_rays_launch if ext_rays_launch else None,
+            "traffic_note": "ncu dram__bytes_read + dram__bytes_write per ray of one launch (%.1f B against %d algorithmic) x rays of the average launch" % (NCU["extend"]["dram_bytes_per_ray"], EXTEND_BYTES_PER_RAY),
+            "hbm": {"achieved": ext_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (ext_gbs / peaks["hbm_gbs"]) if ext_gbs else None, "bytes_per_ray": EXTEND_BYTES_PER_RAY,
+                    "peak_source": "MEASURED_PEAKS.json (%s)" % peak_kind, "note": "secondary roof: the scene is L2-resident, extend streams 32 B in and 16 B out per ray"},
+            "pipeline": {"fp32_frac": (flops_per_path * paths / total_s / 1e12 / fp32_tflops) if flops_per_path else None,
+                         "tflops_algorithmic": (flops_per_path * paths / total_s / 1e12) if flops_per_path else None,
+                         "flops_per_path": flops_per_path,
+                         "hbm_frac": pipeline_bytes / total_s / 1e9 / peaks["hbm_gbs"], "hbm_gbs": pipeline_bytes / total_s / 1e9,
+                         "bytes": "128 B per extend ray + 96 B per shadow ray + 32 B per path (SURVEY.md section 8(d))"},
+            "operation_counts": flop_detail,
         }
         cpu = None
         if not args.no_cpu_baseline and world == 1:
@@ -298,20 +426,24 @@ def main():
             cspp = max(1, min(32, int(12.0 / max(sec, 1e-3))))
             mp, mr, sec = cpu_baseline_run(cspp, threads)
             cpu = {"value": mp, "unit": UNIT, "cores": threads, "kind": "port", "mrays_per_s": mr,
-                   "sample": "800x800 x %d spp (%.1f s), oracle/ C++ f64 restatement, %d threads" % (cspp, sec, threads)}
+                   "sample": "800x800 x %d spp (%.1f s), oracle/ C++ f64 restatement on its own object graph (oracle/oracle_scenes.inc), %d threads" % (cspp, sec, threads)}
+        n_pipes = int(stats.get("pipelines", 1))
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_s * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": total_s * 1e3 / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f32 (f64 hit confirmation)", "data": "synthetic",
             "config": {"workload": "book-2 final scene 800x800 (BASELINE.json configs[3]): 1409 primitives incl. 400 boxes, 1000 instanced spheres, moving sphere, 2 constant media, Perlin + earthmap textures",
-                       "spp_per_step_per_gpu": spp, "full_job_spp": FULL_JOB_SPP, "max_depth": 50, "integrator": "path", "pipeline": args.pipeline,
+                       "step": ("the full %d-spp job, split over the %d rank(s) by sample index (%d spp on this rank)" % (job_spp, world, spp)) if strong else ("%d spp per GPU" % spp),
+                       "spp_per_step_total": step_spp, "spp_per_step_per_gpu": spp, "full_job_spp": FULL_JOB_SPP, "max_depth": 50, "integrator": "path", "pipeline": args.pipeline,
                        "sharding": "spp ranges per rank + NCCL sum-reduce of the accumulation buffer per step",
-                       "concurrent_pipelines": int(os.environ.get("B200RT_WF_PIPES", "2")),
+                       "concurrent_pipelines": n_pipes,
                        "l2": "256 MB write between timed steps; the wavefront queues (2^26 positions x 144 B of ray/state/hit streams = 9.7 GB) exceed L2"},
-            "mrays_per_s": mrays, "rays_per_path": (ext + shd) / paths,
+            "mrays_per_s": mrays, "rays_per_path": rays_per_path,
             "stage_ms_per_step": {k: stats[k] / args.steps for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total")},
-            "stage_ms_note": "capture_image runs 2 concurrent wavefront pipelines (half of the samples each, own stream): a stage time is the length of the union of that stage's CUDA-event intervals over the pipelines, queueing behind the other pipeline's kernels included, so the stages overlap and add up to more than ms_total",
-            "wavefront_iterations_per_step": stats["wavefront_iterations"] / args.steps,
+            "stage_ms_sum_per_step": {k: stats[k + "_sum"] / args.steps for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow")},
+            "stage_ms_single_pipeline": single,
+            "stage_ms_note": "capture_image runs %d concurrent wavefront pipeline(s) (own stream each). stage_ms_per_step: length of the UNION of a stage's CUDA-event intervals over the pipelines (they overlap: the sum exceeds ms_total). stage_ms_sum_per_step: every launch's own event-pair duration added up (a launch queued behind the other pipeline's blocks counts its wait). stage_ms_single_pipeline: one extra, untimed step with ONE pipeline, where stages neither overlap nor queue: the per-kernel durations the roofline uses" % n_pipes,
+            "wavefront_iterations_per_step": n_iter / args.steps,
             "roofline": roofline,
             "fp32": {"peak_tflops_measured": fp32_tflops, "effective_sm_mhz": eff_mhz, "how": "k_fma_peak: 8 independent FMA chains/thread, 8 blocks x 256 threads per SM"},
             "cpu_baseline": cpu,

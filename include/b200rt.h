@@ -215,7 +215,15 @@ typedef struct b200rt_stats {
   float ms_shadow;
   float ms_other;
   uint32_t wavefront_iterations;
-  uint32_t pad;
+  uint32_t pipelines; /* concurrent wavefront pipelines this call ran (1 or 2) */
+  /* With 2 pipelines the stage times above are the length of the UNION of that stage's CUDA-event intervals over the
+   * pipelines (time during which at least one pipeline was in the stage; they overlap and add up to more than ms_total).
+   * The *_sum fields add up every launch's own event-pair duration instead (queueing behind the other pipeline's blocks
+   * included): generate + control | extend | control + shade | shadow. */
+  float ms_generate_sum;
+  float ms_extend_sum;
+  float ms_shade_sum;
+  float ms_shadow_sum;
 } b200rt_stats;
 
 /* Result of `World::hit` (world.rs:27-29, hit.rs:7-39) for one ray. prim = index into desc.prims or -1. */

@@ -1367,7 +1367,8 @@ void oracle_tonemap(const double* mean_rgb, uint64_t n_pixels, uint8_t* out) {
 //     8 cross, 9 neg, 10 squared_length -> out[0], 11 length -> out[0], 12 unit (returns 1 on the zero vector "panic"),
 //     13 reflect(a, b), 14 refract(a, b, eta = out[0] on entry)
 int oracle_vec3_op(int op, const double* a, const double* b, double* out) {
-  Vec3 A(a[0], a[1], a[2]), B = b ? Vec3(b[0], b[1], b[2]) : Vec3();
+  const bool b_is_vector = op == 0 || op == 2 || op == 4 || op == 7 || op == 8 || op == 13 || op == 14;  // the scalar ops read b[0] only
+  Vec3 A(a[0], a[1], a[2]), B = (b && b_is_vector) ? Vec3(b[0], b[1], b[2]) : Vec3();
   Vec3 r;
   try {
     switch (op) {

@@ -12,7 +12,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
-ORACLE_PATH = os.path.join(HERE, "liboracle.so")
+ORACLE_PATH = os.environ.get("ORACLE_LIB") or os.path.join(HERE, "liboracle.so")  # ORACLE_LIB: an instrumented build (make -C oracle asan)
 
 
 class Camera(C.Structure):  # b200rt_camera

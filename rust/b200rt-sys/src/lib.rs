@@ -78,7 +78,8 @@ mod manual {
     pub struct b200rt_stats {
         pub paths: u64, pub extend_rays: u64, pub shadow_rays: u64, pub kernel_launches: u64,
         pub ms_total: f32, pub ms_generate: f32, pub ms_extend: f32, pub ms_shade: f32, pub ms_shadow: f32, pub ms_other: f32,
-        pub wavefront_iterations: u32, pub pad: u32,
+        pub wavefront_iterations: u32, pub pipelines: u32,
+        pub ms_generate_sum: f32, pub ms_extend_sum: f32, pub ms_shade_sum: f32, pub ms_shadow_sum: f32,
     }
 
     /// `HitRecord` (hit.rs:7-39) of one ray; prim = index into the scene's primitive list or -1.

@@ -71,7 +71,8 @@ class Params(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("extend_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("ms_total", C.c_float), ("ms_generate", C.c_float), ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_shadow", C.c_float),
-                ("ms_other", C.c_float), ("wavefront_iterations", C.c_uint32), ("pad", C.c_uint32)]
+                ("ms_other", C.c_float), ("wavefront_iterations", C.c_uint32), ("pipelines", C.c_uint32),
+                ("ms_generate_sum", C.c_float), ("ms_extend_sum", C.c_float), ("ms_shade_sum", C.c_float), ("ms_shadow_sum", C.c_float)]
 
 
 class SppmParams(C.Structure):

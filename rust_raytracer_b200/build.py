@@ -20,6 +20,7 @@ NVCC_FLAGS = [
     "-shared", "-Xcompiler", "-fPIC,-O3,-Wall", "-Xptxas", "-v", "--use_fast_math=false",
 ]
 SOURCES = ["api.cu", "builder.cpp", "loaders.cpp", "scenes.cpp", "scene_compile.cpp", "png_out.cpp"]
+COUNTERS_LIB = os.path.join(HERE, "libb200rt_counters.so")  # the same sources with -DB200RT_COUNTERS: per-operation counts (bench.py's algorithmic flops, tools/dbg)
 CLI = os.path.join(HERE, "b200rt_render")  # the reference's `main` over the C ABI (csrc/cli_main.cpp)
 
 
@@ -54,6 +55,22 @@ def build_library(force=False, verbose=False):
         raise RuntimeError("nvcc failed (see %s)" % log)
     build_cli()
     return LIB
+
+
+def build_counters(force=False):
+    """The instrumented twin of the library (-DB200RT_COUNTERS): counts node visits, primitive tests, scatter calls ... so that
+    bench.py can report SURVEY.md section 8(d)'s algorithmic flops of the workload it times.  Never on the timed path."""
+    header = os.path.join(ROOT, "include", "b200rt.h")
+    if not force and not _newer(COUNTERS_LIB, _deps(CSRC, [header])):
+        return COUNTERS_LIB
+    nvcc = os.environ.get("NVCC", "nvcc")
+    flags = [f for f in NVCC_FLAGS if f not in ("--use_fast_math=false", "-v", "-Xptxas")] + ["-DB200RT_COUNTERS"]
+    cmd = [nvcc] + flags + ["-o", COUNTERS_LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout)
+        raise RuntimeError("nvcc failed for the counters build")
+    return COUNTERS_LIB
 
 
 def build_cli():
@@ -98,6 +115,7 @@ def build_oracle(force=False):
 
 if __name__ == "__main__":
     build_library(force="--force" in sys.argv, verbose=True)
+    build_counters(force="--force" in sys.argv)
     build_oracle(force="--force" in sys.argv)
     print(LIB)
     print(ORACLE_LIB)

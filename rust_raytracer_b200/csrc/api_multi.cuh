@@ -88,11 +88,17 @@ extern "C" int b200rt_render_multi(int32_t n_dev, b200rt_scene* const* scenes, c
   if (n_dev < 1 || n_dev > B200RT_MULTI_MAX_DEV || !scenes || !cam || !params || !accum_host) return B200RT_ERR_INVALID;
   for (int g = 0; g < n_dev; ++g) if (!scenes[g]) return B200RT_ERR_INVALID;
   b200rt_ctx* root = scenes[0]->ctx;
+  // One context per scene, normally one device per context.  Several contexts on ONE device are allowed as well (each has
+  // its own streams and queue pools; the "peer" buffers are then plain local memory): that is how a one-GPU box exercises this
+  // entry point, sample ranges, host threads and k_reduce_peers included.  NCCL cannot rank one device twice.
   std::vector<int> devs(n_dev);
+  bool shared_device = false;
   for (int g = 0; g < n_dev; ++g) {
     devs[g] = scenes[g]->ctx->device;
-    for (int k = 0; k < g; ++k)
-      if (devs[k] == devs[g]) { root->err = "render_multi: every scene must live on its own device"; return B200RT_ERR_INVALID; }
+    for (int k = 0; k < g; ++k) {
+      if (scenes[k]->ctx == scenes[g]->ctx) { root->err = "render_multi: every scene needs its own context"; return B200RT_ERR_INVALID; }
+      if (devs[k] == devs[g]) shared_device = true;
+    }
   }
   int rc = validate_params(root, params);
   if (rc) return rc;
@@ -142,10 +148,11 @@ extern "C" int b200rt_render_multi(int32_t n_dev, b200rt_scene* const* scenes, c
     bool can_peer = true;
     for (int g = 1; g < n_dev; ++g) {
       int can = 0;
-      if (cudaDeviceCanAccessPeer(&can, devs[0], devs[g]) != cudaSuccess || !can) can_peer = false;
+      if (devs[g] != devs[0] && (cudaDeviceCanAccessPeer(&can, devs[0], devs[g]) != cudaSuccess || !can)) can_peer = false;
     }
     cudaGetLastError();
     const bool use_nccl = want_nccl || (!can_peer && !want_peer);
+    if (use_nccl && shared_device) { root->err = "render_multi: NCCL cannot reduce between contexts that share a device (use the peer path)"; release(); return B200RT_ERR_INVALID; }
     NcclApi none;
     NcclApi& N = use_nccl ? nccl_api() : none;
     if (use_nccl && !N.ok) {
@@ -178,13 +185,14 @@ extern "C" int b200rt_render_multi(int32_t n_dev, b200rt_scene* const* scenes, c
       src.n = n_dev - 1;
       cudaSetDevice(devs[0]);
       for (int g = 1; g < n_dev; ++g) {
+        src.p[g - 1] = (const float4*)accum[g];
+        if (devs[g] == devs[0]) continue;  // same device: local memory
         int can = 0;
         cudaDeviceCanAccessPeer(&can, devs[0], devs[g]);
         if (!can) { root->err = "render_multi: B200RT_MULTI_REDUCE=peer but no peer access from device " + std::to_string(devs[0]) + " to " + std::to_string(devs[g]); release(); return B200RT_ERR_CUDA; }
         const cudaError_t e = cudaDeviceEnablePeerAccess(devs[g], 0);
         if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { root->err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e); release(); return B200RT_ERR_CUDA; }
         cudaGetLastError();  // clears "already enabled"
-        src.p[g - 1] = (const float4*)accum[g];
       }
       cudaEventRecord(root->ev[0], root->stream);
       k_reduce_peers<<<root->prop.multiProcessorCount * 4, 256, 0, root->stream>>>((float4*)accum[0], src, n4);

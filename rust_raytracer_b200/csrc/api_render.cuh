@@ -207,6 +207,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   uint64_t launches = 0;
   uint32_t iters = 0;
   std::vector<std::pair<float, float>> intervals[4];  // per stage, ms since fork_ev, over all pipelines
+  double ms_sum[4] = {0., 0., 0., 0.};                // per stage, every launch's own event-pair duration added up
   // one batch of iterations of one pipeline + the read-back of its counters
   auto enqueue_batch = [&](WfPipeState& W) -> int {
     cudaStream_t q = W.q;
@@ -257,6 +258,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
         float d = 0.f;
         if (cudaEventElapsedTime(&d, ev[j], ev[j + 1]) != cudaSuccess) break;
         intervals[j].emplace_back(t, t + d);
+        ms_sum[j] += d;
         t += d;
       }
     }
@@ -326,6 +328,8 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
     st->extend_rays = 0; st->shadow_rays = 0;
     for (int k = 0; k < n_pipes; ++k) { st->extend_rays += pipes[k].host->extend_rays - pipes[k].host->dead_rays; st->shadow_rays += pipes[k].host->shadow_rays; }
     st->kernel_launches = launches; st->wavefront_iterations = iters;
+    st->pipelines = (uint32_t)n_pipes;
+    st->ms_generate_sum = (float)ms_sum[0]; st->ms_extend_sum = (float)ms_sum[1]; st->ms_shade_sum = (float)ms_sum[2]; st->ms_shadow_sum = (float)ms_sum[3];
   }
   return B200RT_OK;
 }

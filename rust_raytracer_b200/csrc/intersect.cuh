@@ -15,8 +15,11 @@ __device__ unsigned int* g_dbg_steps;  // per queue position: HitRaw::dbg (tools
 #define DBG_INC(i)
 #define DBG_RAY(x)
 #endif
-// counter slots: 0 rays, 1 inner nodes visited, 2 leaves visited, 3 stack pushes, 4 pops culled, 5 to_object,
-// 10+type filter calls, 20+type exact calls, 30+type exact accepted
+// counter slots: 0 rays, 1 inner nodes visited, 2 leaves visited, 4 pops culled, 5 to_object, 6 child boxes slab-tested
+// (non-empty slots of the visited nodes), 7 HitRecord::new, 8 sphere uv, 9 primary rays generated,
+// 10+type primitive tests (f32 filter calls), 20+type f64 decisions, 30+type accepted,
+// 40+material type scatter calls, 48+texture type get_color calls, 56 light samples
+// (bench.py turns these into SURVEY.md section 8(d)'s algorithmic flops)
 
 struct Ray {
   float3 o;
@@ -339,6 +342,10 @@ DEV RayT make_rayt(const DevScene& S, const RayF& rf) {
 // hits and returns the nearest child reference (or the next stack entry when no child is hit).
 DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32_t cur, float t_min, float t_best32, TStack& stack, int& sp) {
   DBG_INC(1);
+#ifdef B200RT_COUNTERS
+  { const int4 rfc = __ldg(reinterpret_cast<const int4*>(rt.nodes + (cur << 3)) + 6);
+    atomicAdd(&g_dbg[6], (unsigned long long)((rfc.x != B200RT_CHILD_EMPTY) + (rfc.y != B200RT_CHILD_EMPTY) + (rfc.z != B200RT_CHILD_EMPTY) + (rfc.w != B200RT_CHILD_EMPTY))); }
+#endif
   float tn[4];
 #if B200RT_NODE_FAST
   // 32-bit row indices off a base pointer the compiler cannot see through: the near row of an axis is
@@ -458,6 +465,7 @@ DEV void trace(const DevScene& S, const Ray& ray, float t_min, HitRaw& h, const 
 }
 
 DEV void sphere_uv(d3 n, float& u, float& v) {  // sphere.rs:16-20
+  DBG_INC(8);
   double theta = acos(-n.y), phi = atan2(-n.z, n.x) + PI_D;
   u = (float)(phi * (1.0 / PI_D) * 0.5);
   v = (float)(theta * (1.0 / PI_D));
@@ -471,6 +479,7 @@ DEV void finish_hit(const DevScene& S, const Ray& ray, const HitRaw& h, HitInfo&
   const int4 meta = __ldg(&S.prim_meta[k]);
   const int type = meta.x & B200RT_PRIM_TYPE_MASK;
   const bool inst = meta.z >= 0;
+  DBG_INC(7);
   out.type = type; out.material = meta.x >> 8; out.prim_orig = meta.y; out.t = (float)h.t;
   out.u = 0.f; out.v = 0.f;
   RayD rd = make_rayd(ray);

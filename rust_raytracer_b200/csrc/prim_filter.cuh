@@ -40,6 +40,7 @@ DEV float safe_rcp(float d) { return fabsf(d) > B200RT_RCP_CLAMP ? rcp_fast(d) :
 DEV int medium_far_reject(const RayF& r, float t_in, float e_in, float t_out, float e_out, float neg_inv_density, float xi, float t_min, float t_best, float* t_hit) {
   const float lo = fmaxf(fmaxf(t_in - e_in, t_min), 0.f);
   const float hi = fminf(t_out + e_out, t_best);
+  if (!(r.a <= 3.0e38f)) return FILTER_MAYBE;  // |d|^2 overflowed: no f32 verdict
   const float len = sqrt_fast(r.a);  // <= 2 ulp, inside the 2e-6 margins below
   float upper = fmaxf(hi - lo, 0.f) + 2e-7f * (fabsf(hi) + fabsf(lo));
   upper = upper * len * (1.0f + 2e-6f);
@@ -68,6 +69,10 @@ DEV int sphere_reject(const RayF& r, float3 c, float radius, float t_min, float 
   float disc = hb * hb - r.a * cc;
   float E = 2e-6f * r.a * (oc2 + r2);
   if (eps > 0.f) E += r.a * eps * (8.2f * sqrt_fast(oc2) + 4.0f * fabsf(radius));
+  // An overflowed intermediate (coordinates around 1e10 and beyond: a * c and half_b^2 pass 3.4e38) must not decide anything:
+  // with the product a * c at +inf and half_b * half_b exact inside the FMA, disc comes out -inf for a ray that hits.
+  // The f64 stage has the range.
+  if (!(fabsf(disc) <= 3.0e38f) || !(E <= 3.0e38f)) return false;
   if (disc < -E) return true;
   if (disc > 4.0f * E) {
     const float rs = rsqrt_fast(disc), s = disc * rs, inva = rcp_fast(r.a);  // s, inva: <= 3 ulp

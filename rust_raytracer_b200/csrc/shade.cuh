@@ -46,6 +46,7 @@ DEV bool texture_needs_uv(const DevScene& S, int tex) { return __float_as_int(__
 DEV float3 texture_color(const DevScene& S, int tex, const HitInfo& h) {
   const float4 hd = __ldg(&S.textures[3 * tex]);
   const int type = __float_as_int(hd.x);
+  DBG_INC(48 + type);
   if (type == B200RT_TEX_CONSTANT) return f3(__ldg(&S.textures[3 * tex + 1]));
   if (type == B200RT_TEX_CHECKER) {  // material.rs:58-68
     float sines = sinf(10.f * h.p.x) * sinf(10.f * h.p.y) * sinf(10.f * h.p.z);
@@ -94,6 +95,7 @@ DEV float light_pdf_all(const DevScene& S, float3 o, float3 d, float t_min) {
   return s / (float)S.n_lights;
 }
 DEV float3 light_sample_dir(const DevScene& S, int li, float3 o, float u1, float u2) {
+  DBG_INC(56);
   const float4 L0 = __ldg(&S.lights[3 * li]), L1 = __ldg(&S.lights[3 * li + 1]);
   if (__float_as_int(L0.x) == 1) {
     const float4 L2 = __ldg(&S.lights[3 * li + 2]);
@@ -120,6 +122,7 @@ DEV int light_index_of_prim(const DevScene& S, int prim_orig) {
 // ---- camera (camera.rs:57-64, 97-99) ---------------------------------------------------------------------
 DEV float3 ld3(const float* p) { return f3(p[0], p[1], p[2]); }
 DEV Ray camera_ray(const RenderConst& P, uint32_t pixel, uint32_t sample) {
+  DBG_INC(9);
   const uint4 r0 = philox4x32(make_uint4(pixel, sample, 0u, 0u), P.key);
   const uint4 r1 = philox4x32(make_uint4(pixel, sample, 0u, 1u), P.key);
   const int x = pixel % P.width, y = pixel / P.width;
@@ -187,6 +190,7 @@ DEV bool shade_surface(const DevScene& S, const RenderConst& P, Ray& ray, const 
   const int integrator = INTEG >= 0 ? INTEG : P.integrator;
   const int mtype = __float_as_int(mat.x), tex = __float_as_int(mat.y);
   const float3 color = texture_color(S, tex, h);
+  DBG_INC(40 + mtype);
 
   if (mtype == B200RT_MAT_DIFFUSE_LIGHT) {  // emitted = emit.get_color(rec), both faces (material.rs:209-211)
     float w = 1.f;

@@ -42,13 +42,13 @@
 struct WfCounters {
   unsigned long long next_path;     // next path id to generate
   unsigned long long extend_rays, shadow_rays, paths_done;
+  unsigned long long dead_rays;     // dead records met by extend (not rays: subtracted from the statistics)
   unsigned int n_ext;               // rays in the current set (extend + shade work list)
   unsigned int n_ext_next;          // survivors appended to the next set by shade
   unsigned int n_shadow;            // shadow requests this iteration
   unsigned int ext_cursor;          // work-fetch cursor of the persistent extend kernel
   unsigned int shadow_cursor;
-  unsigned int dead_rays;           // dead records met by extend (not rays: subtracted from the statistics)
-  unsigned int pad[2];
+  unsigned int pad;
 };
 
 struct WfBuffers {
@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
     if (goes_on && (int)lane == leader) rank = atomicAdd(&B.bin_count[bin], (unsigned)__popc(peers));
     rank = __shfl_sync(0xffffffffu, rank, leader) + __popc(peers & ((1u << lane) - 1u));
     const unsigned n_dead = __popc(__ballot_sync(0xffffffffu, dead));
-    if (n_dead && lane == 0) atomicAdd(&B.cnt->dead_rays, n_dead);
+    if (n_dead && lane == 0) atomicAdd(&B.cnt->dead_rays, (unsigned long long)n_dead);
     DBG_RAY(if (active && g_dbg_steps) g_dbg_steps[i] = dead ? 0xffffffffu : h.dbg);
     if (active) {
       const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);

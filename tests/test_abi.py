@@ -32,7 +32,7 @@ def test_struct_sizes_match_the_header(built):
     assert C.sizeof(F.Prim) == 64 and C.sizeof(F.Material) == 16 and C.sizeof(F.Texture) == 48
     assert C.sizeof(F.Image) == 16 and C.sizeof(F.Instance) == 96 and C.sizeof(F.Hit) == 32
     assert C.sizeof(F.Perlin) == 256 * 16 + 3 * 256 * 4
-    assert C.sizeof(F.Camera) == 24 * 4 and C.sizeof(F.Params) == 64 and C.sizeof(F.Stats) == 64
+    assert C.sizeof(F.Camera) == 24 * 4 and C.sizeof(F.Params) == 64 and C.sizeof(F.Stats) == 80
 
 
 def test_no_cpu_fallback(built):

@@ -50,10 +50,47 @@ def test_render_multi_argument_errors(ctx):
     scene = rt.Scene(ctx, sb)
     p = rt.copy_params(sb.params, width=16, height=16, spp_count=2)
     with pytest.raises(rt.B200RTError) as e:
-        rt.render_multi([scene, scene], sb.camera, p)  # two shards on one device
-    assert e.value.status == F.ERR_INVALID and "own device" in str(e.value)
+        rt.render_multi([scene, scene], sb.camera, p)  # two shards on one context (a context is not thread-safe)
+    assert e.value.status == F.ERR_INVALID and "own context" in str(e.value)
     with pytest.raises(rt.B200RTError):
         rt.render_multi([scene], sb.camera, rt.copy_params(p, width=0))
+    ctx_b = rt.Context(0)
+    old = os.environ.get("B200RT_MULTI_REDUCE")
+    os.environ["B200RT_MULTI_REDUCE"] = "nccl"
+    try:
+        with pytest.raises(rt.B200RTError) as e:  # NCCL cannot rank one device twice
+            rt.render_multi([scene, rt.Scene(ctx_b, sb)], sb.camera, p)
+        assert "share a device" in str(e.value)
+    finally:
+        os.environ.pop("B200RT_MULTI_REDUCE") if old is None else os.environ.__setitem__("B200RT_MULTI_REDUCE", old)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_ctx", [2, 3])
+def test_render_multi_on_one_device_through_the_peer_reduce(ctx, n_ctx):
+    """The whole multi-device entry point on ONE GPU (the driver's box): n contexts on device 0, one host thread each, disjoint
+    contiguous sample ranges, then k_reduce_peers sums the per-context buffers (plain local memory here, NVLink peers on a
+    multi-GPU box) — against the same sample ranges rendered one by one and added on the host."""
+    sb = scene_builder("book2")
+    ctxs = [ctx] + [rt.Context(0) for _ in range(n_ctx - 1)]
+    scenes = [rt.Scene(c, sb) for c in ctxs]
+    p = rt.copy_params(sb.params, width=96, height=80, spp_count=11, spp_begin=4)  # 11 = 6 + 5 or 4 + 4 + 3
+    from rust_raytracer_b200.sharding import spp_range
+    want = np.zeros((80, 96, 4), np.float32)
+    rays = 0
+    for r in range(n_ctx):
+        b, c = spp_range(r, n_ctx, 11, 4)
+        img, st = scenes[0].render(sb.camera, rt.copy_params(p, spp_begin=b, spp_count=c))
+        want += img
+        rays += st.extend_rays
+    got, st, ms = rt.render_multi(scenes, sb.camera, p)
+    assert ms.n_dev == n_ctx and ms.reduce_path == F.REDUCE_PEER and ms.paths == 96 * 80 * 11 and ms.extend_rays == rays
+    assert [s.paths for s in st] == [96 * 80 * spp_range(r, n_ctx, 11, 4)[1] for r in range(n_ctx)]
+    np.testing.assert_allclose(got, want, rtol=1e-4, atol=1e-4)
+    assert np.all(got[..., 3] == 11)
+    full, _ = scenes[0].render(sb.camera, p)
+    np.testing.assert_allclose(got, full, rtol=1e-4, atol=1e-4)
+    print("render_multi, %d contexts on one device: render %.2f ms, peer reduce %.3f ms" % (n_ctx, ms.ms_render_max, ms.ms_reduce))
 
 
 @pytest.mark.gpu

@@ -8,8 +8,7 @@ import pytest
 
 import rust_raytracer_b200 as rt
 from rust_raytracer_b200 import _ffi as F
-from oracle_ffi import OracleScene
-from scenes_util import scene_builder
+from scenes_util import scene_builder, oracle_scene
 
 W, H, SPP = 40, 40, 4
 ITER, PHOTONS = 6, 20000
@@ -17,7 +16,8 @@ ITER, PHOTONS = 6, 20000
 
 def _oracle(sb, seed, **kw):
     p = rt.copy_params(sb.params, width=W, height=H, spp_count=SPP, seed=seed)
-    return OracleScene(sb).sppm_render(sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS, **kw)
+    return oracle_scene("cornell_ref").sppm_render(sb.camera, p,  # the oracle's own scene.rs:16-112 graph
+                                                    iterations=ITER, photons_per_iter=PHOTONS, **kw)
 
 
 def test_oracle_sppm_known_answers(built):

@@ -20,7 +20,7 @@ for a in args:
             env[k] = v
         elif p and p != "main":
             env["B200RT_LIB"] = os.path.join(ROOT, p)
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", steps, "--warmup", "3", "--no-cpu-baseline"], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", steps, "--warmup", "3", "--no-cpu-baseline", "--scaling", "weak"], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
     try:
         d = json.loads(r.stdout.strip().splitlines()[-1])
         st = d["stage_ms_per_step"]
