@@ -1,23 +1,33 @@
 // device_scene.h — layout of the GPU-resident scene (shared by the host scene compiler and the kernels).
 //
-// HBM layout (all arrays 128-byte aligned, read-only during a render, L2-resident for C1..C4):
-//   nodes      : BVH4 nodes, 128 B each (two 64-byte halves = 8 x float4):
-//                  [0..2] child lo.x/lo.y/lo.z x4   [3..5] child hi.x/hi.y/hi.z x4
-//                  [6]    child refs x4 (int bits)  [7]    unused
+// HBM layout (all arrays 256-byte aligned inside one allocation, read-only during a render, L2-resident for C1..C5):
+//   nodes      : BVH4 nodes, 128 B each = 8 rows of float4 (one component per child slot 0..3):
+//                  row 0 lo.x | row 1 hi.x | row 2 lo.y | row 3 hi.y | row 4 lo.z | row 5 hi.z | row 6 child refs (int bits) | row 7 unused
+//                (interleaved so that the NEAR plane of axis a is row 2a + sign bit of d_a and the far plane its xor 1:
+//                 scene_compile.cpp collapse() writes it, intersect.cuh node_step() reads it)
 //                child ref: >= 0 inner node index; bit31 set: leaf, bits 27..30 = count-1, bits 0..26 = first prim;
-//                B200RT_CHILD_EMPTY for an unused slot.
-//   prim_data  : 3 x float4 per primitive in BVH leaf order, WORLD space (instances baked):
-//                  sphere  A=(c, r)                         moving  A=(c0, r) B=(c1-c0, 1/(t1-t0)) C.x = t0
-//                  rect    A=(a0, b0, a1, b1) B.x = k       box     A=(min,_) B=(max,_)
-//                  tri     A=(v0,_) B=(v1,_) C=(v2,_)
-//                  medium sphere A=(c, r) B.x = -1/density  medium box A=(min,_) B=(max, -1/density)
-//   prim_meta  : int4 per primitive: x = type | material << 8, y = original desc index, z = instance (-1), w = aux
+//                B200RT_CHILD_EMPTY for an unused slot, whose box is inverted and infinite (lo = +inf, hi = -inf: never hit).
+//   prim_data  : 3 x float4 per primitive in BVH leaf order: the record the f32 FILTER reads.  WORLD space (instance baked in
+//                f64, rounded once), except for B200RT_PRIM_OBJF primitives, whose record stays in OBJECT space:
+//                  sphere         A = (c, r)   (r < 0 allowed: sphere.rs:44)
+//                  moving sphere  A = (c0, r)  B = (c1, -)  [absolute second centre]  C = (time0, time1, -, -)
+//                  rect           A = (a0, b0, a1, b1)  B.x = k
+//                  box            A = (min, -)  B = (max, -)
+//                  triangle       A = (v0, -)  B = (v1, -)  C = (v2, -)
+//                  medium sphere  A = (c, r)  B.x = -1/density      medium box  A = (min, -)  B = (max, -1/density)
+//                (densities of baked media are per WORLD unit: -s/density under a similarity of scale s)
+//   prim_obj   : same layout, OBJECT space (the original f32 values): what the f64 decision of an instanced primitive reads
+//                behind M^-1, exactly like Transform::hit; only filled for instanced primitives
+//   prim_meta  : int4 per primitive: x = type | B200RT_PRIM_OBJF | material << 8, y = original desc index, z = instance (-1), w = aux
 //   tri_normals: 3 x float4 per entry (object-space vertex normals), indexed by prim_meta.w
-//   instances  : 6 x float4 per instance: rows of the linear part of M (3), rows of the linear part of M^-1 (3)
+//   instances  : 6 x float4 per instance: rows of the linear part of M (3), rows of the linear part of M^-1 (3)  [f32, informational]
+//   instances_d: 24 doubles per instance: M (3x4 row-major), M^-1 (3x4): what to_object() and finish_hit() use
+//   inst_eps   : per instance, absolute f32 rounding error of its baked world-space coordinates (filter margin)
 //   materials  : float4 (type bits, texture bits, param, 0)
 //   textures   : 3 x float4: (type bits, image bits, scale, 0), c0, c1
 //   images     : int4 (offset, w, h, 0) + RGB8 bytes
-//   lights     : 2 x float4 per light: (kind bits, device prim bits, axis bits, 0), (a0,b0,a1,b1 | c,r), second.x.. see kernels
+//   lights     : 3 x float4 per light: (kind bits [0 sphere, 1 rect], original prim bits, axis bits, material bits),
+//                (a0, b0, a1, b1) or (c, r), (k, area, 0, 0)
 #pragma once
 #include <stdint.h>
 
