@@ -283,6 +283,20 @@ int b200rt_render_device(b200rt_scene* scene, const b200rt_camera* cam, const b2
                          b200rt_stats* stats);
 int b200rt_render(b200rt_scene* scene, const b200rt_camera* cam, const b200rt_params* params, float* accum_host,
                   b200rt_stats* stats);
+/* ---- capture_image without any device allocation ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contract as b200rt_render_device
+ * (wavefront pipeline, any integrator; accum_dev is the caller's device buffer), but the wavefront queues live in ONE
+ * file-scope static __device__ array of B200RT_STATIC_POOL_BYTES that every GPU which loads the library holds until exit;
+ * the call makes no cudaMalloc / cudaFree.  Limit: width * height * spp_count <= B200RT_STATIC_MAX_PATHS per call, larger
+ * requests fail with B200RT_ERR_INVALID and a message.  All calls share the array (it keeps the last call's contents; what
+ * must start at zero is cleared per call): calls that overlap on one GPU race on it — serialise them. */
+#define B200RT_STATIC_POOL_POSITIONS 65536u        /* paths in flight */
+#define B200RT_STATIC_POOL_BYTES (13u << 20)       /* 13 MiB of device memory per GPU */
+#define B200RT_STATIC_MAX_PATHS (1ull << 24)       /* per call */
+int b200rt_render_device_static(b200rt_scene* scene, const b200rt_camera* cam, const b200rt_params* params, float* accum_dev,
+                                b200rt_stats* stats);
+
 /* ---- capture_image over several GPUs of one node ---- */
 #define B200RT_REDUCE_NONE 0 /* one device: nothing to sum */
 #define B200RT_REDUCE_NCCL 1 /* ncclReduce over NVLink (libnccl.so.2 loaded at run time) */

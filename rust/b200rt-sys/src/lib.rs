@@ -127,6 +127,7 @@ mod manual {
         pub fn b200rt_intersect_batch_device(scene: *mut b200rt_scene, o_time: *const f32, d_tmax: *const f32, medium_seed: *const u32, n: u64, t_min: f32, out: *mut b200rt_hit) -> c_int;
         // ---- Camera::capture_image (camera.rs:66-128)
         pub fn b200rt_render_device(scene: *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, accum_dev: *mut f32, stats: *mut b200rt_stats) -> c_int;
+    pub fn b200rt_render_device_static(scene: *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, accum_dev: *mut f32, stats: *mut b200rt_stats) -> c_int;
         pub fn b200rt_render(scene: *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, accum_host: *mut f32, stats: *mut b200rt_stats) -> c_int;
         pub fn b200rt_render_multi(n_dev: i32, scenes: *const *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, accum_host: *mut f32,
                                    stats_per_device: *mut b200rt_stats, multi: *mut b200rt_multi_stats) -> c_int;

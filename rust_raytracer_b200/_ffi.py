@@ -119,6 +119,7 @@ PROTOTYPES = {
     "b200rt_intersect_batch": (C.c_int, [VP, VP, VP, VP, C.c_uint64, C.c_float, VP]),
     "b200rt_intersect_batch_device": (C.c_int, [VP, VP, VP, VP, C.c_uint64, C.c_float, VP]),
     "b200rt_render_device": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, C.POINTER(Stats)]),
+    "b200rt_render_device_static": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, C.POINTER(Stats)]),
     "b200rt_render": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, C.POINTER(Stats)]),
     "b200rt_tonemap_rgb8": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),
     "b200rt_tonemap_rgb8_device": (C.c_int, [VP, VP, C.c_int32, C.c_int32, VP]),

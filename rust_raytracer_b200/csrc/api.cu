@@ -31,6 +31,7 @@ struct b200rt_ctx {
   size_t stage_bytes = 0;
   void* spare_block = nullptr;
   size_t spare_bytes = 0;
+  const WfBuffers* static_wf = nullptr;  // set for the duration of b200rt_render_device_static: render_wavefront takes its queues from there
   cudaEvent_t sev[128 * WF_MAX_PIPES] = {};  // stage events per pipeline: 2 alternating sets x up to 8 iterations in flight x 8 (generate, extend, shade, shadow boundaries)
 };
 
@@ -278,3 +279,4 @@ int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_
 #include "api_sppm.cuh"
 #include "api_multi.cuh"
 #include "api_debug.cuh"
+#include "api_static.cuh"

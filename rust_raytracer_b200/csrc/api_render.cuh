@@ -130,7 +130,8 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   unsigned int* dump_steps = nullptr;
   if (dump_path && *dump_path) n_pipes = 1;
 #endif
-  const unsigned long long cap = (1ull << pool_log2) / (unsigned long long)n_pipes;
+  if (ctx->static_wf) n_pipes = 1;  // b200rt_render_device_static: one pipeline over the library's static queue block
+  const unsigned long long cap = ctx->static_wf ? (unsigned long long)ctx->static_wf->pool : (1ull << pool_log2) / (unsigned long long)n_pipes;
   unsigned int n_bins, bin_mul;
   {  // bin = 1 + umulhi(prim, bin_mul) maps [0, n_prims) onto bins 1 .. n_bins - 1 (one primitive per bin when they fit)
     // 1024 or 2048 bins (shade keeps the offsets in shared memory up to WF_SMEM_BINS; more only pays through the
@@ -153,9 +154,12 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
     W.M = make_path_map(P0.width, P0.height, W.P.spp_count);
     const unsigned long long want = (W.M.total + 31ull) & ~31ull;
     const unsigned int pool = (unsigned int)(want < cap ? want : cap);
-    const int rc_pool = wf_ensure_pool(ctx, k, pool, nee);
-    if (rc_pool) return rc_pool;
-    W.B = ctx->wf[k];
+    if (ctx->static_wf) { W.B = *ctx->static_wf; W.B.pool = pool; }
+    else {
+      const int rc_pool = wf_ensure_pool(ctx, k, pool, nee);
+      if (rc_pool) return rc_pool;
+      W.B = ctx->wf[k];
+    }
     W.B.n_bins = n_bins; W.B.bin_mul = bin_mul;
     if (k == 0) W.q = ctx->stream;
     else {

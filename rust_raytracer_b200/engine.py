@@ -133,6 +133,12 @@ class Scene:
                                                 px.ctypes.data_as(C.c_void_p) if want_pixel_stats else None, C.byref(st)))
         return (accum, px, st) if want_pixel_stats else (accum, st)
 
+    def render_device_static(self, camera, params, accum_ptr):
+        """b200rt_render_device_static: the same render with the queues in the library's static device array (no cudaMalloc)."""
+        st = F.Stats()
+        self.ctx._ok(F.lib().b200rt_render_device_static(self._h, C.byref(camera), C.byref(params), C.c_void_p(accum_ptr), C.byref(st)))
+        return st
+
     def render_device(self, camera, params, accum_ptr):
         st = F.Stats()
         self.ctx._ok(F.lib().b200rt_render_device(self._h, C.byref(camera), C.byref(params), C.c_void_p(accum_ptr), C.byref(st)))
