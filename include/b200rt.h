@@ -352,6 +352,18 @@ int b200rt_render_sppm(b200rt_scene* scene, const b200rt_camera* cam, const b200
                        const b200rt_sppm_params* sppm, float* accum_host, float* pixel_stats_host,
                        b200rt_sppm_stats* stats);
 
+/* The same integrator over n_dev GPUs of one node ("SPPM would need a photon all-gather per iteration";
+ * the reference runs photon_mapper.rs:158-233 on one thread pool).  scenes[g]: the same scene on n_dev contexts (normally one
+ * device each; several contexts on one device are accepted).  Per iteration the photons are sharded by id, each device's grid
+ * build reads all shards in place over NVLink peer mappings (the all-gather is fused into the counting sort), and the pixels'
+ * SPPM statistics are sharded by pixel index; the final pass is sharded by sample index and summed on scenes[0]'s device.
+ * The stored photon counts and the ray counts equal the one-device call's exactly (every draw is keyed by the global photon /
+ * pixel id); the image up to float summation order.  Needs peer access between the devices (no NCCL, no host staging).
+ * stats->ms_total is the host clock around the whole call; the per-stage fields are not filled. */
+int b200rt_render_sppm_multi(int32_t n_dev, b200rt_scene* const* scenes, const b200rt_camera* cam,
+                             const b200rt_params* params, const b200rt_sppm_params* sppm, float* accum_host,
+                             float* pixel_stats_host, b200rt_sppm_stats* stats);
+
 /* From<Vec3> for Rgb<u8> (vec3.rs:223-231): floor(clamp(sqrt(sum/count),0,1)*255). Device kernel; host buffers. */
 int b200rt_tonemap_rgb8(b200rt_ctx* ctx, const float* accum_host, int32_t width, int32_t height, uint8_t* rgb_out);
 int b200rt_tonemap_rgb8_device(b200rt_ctx* ctx, const float* accum_dev, int32_t width, int32_t height, uint8_t* rgb_dev);

@@ -134,6 +134,8 @@ mod manual {
         // ---- SPPMIntegrator (integrator/photon_mapper.rs)
         pub fn b200rt_render_sppm(scene: *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, sppm: *const b200rt_sppm_params,
                                   accum_host: *mut f32, pixel_stats_host: *mut f32, stats: *mut b200rt_sppm_stats) -> c_int;
+    pub fn b200rt_render_sppm_multi(n_dev: i32, scenes: *const *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, sppm: *const b200rt_sppm_params,
+                                  accum_host: *mut f32, pixel_stats_host: *mut f32, stats: *mut b200rt_sppm_stats) -> c_int;
         // ---- From<Vec3> for Rgb<u8> (vec3.rs:223-231), RgbImage::save (main.rs:54), Camera::new (camera.rs:24-55)
         pub fn b200rt_tonemap_rgb8(ctx: *mut b200rt_ctx, accum_host: *const f32, width: i32, height: i32, rgb_out: *mut u8) -> c_int;
         pub fn b200rt_tonemap_rgb8_device(ctx: *mut b200rt_ctx, accum_dev: *const f32, width: i32, height: i32, rgb_dev: *mut u8) -> c_int;

@@ -126,6 +126,7 @@ PROTOTYPES = {
     "b200rt_write_png": (C.c_int, [C.c_char_p, VP, C.c_int32, C.c_int32]),
     "b200rt_render_multi": (C.c_int, [C.c_int32, C.POINTER(VP), C.POINTER(Camera), C.POINTER(Params), VP, C.POINTER(Stats), C.POINTER(MultiStats)]),
     "b200rt_render_sppm": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), VP, VP, VP, VP]),
+    "b200rt_render_sppm_multi": (C.c_int, [C.c_int32, C.POINTER(VP), C.POINTER(Camera), C.POINTER(Params), VP, VP, VP, VP]),
     "b200rt_camera_make": (C.c_int, [D3, D3, D3, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(Camera)]),
     "b200rt_measure_fp32_peak": (C.c_int, [VP, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "b200rt_builder_create": (C.c_int, [C.POINTER(VP)]),

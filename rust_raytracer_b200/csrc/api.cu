@@ -278,5 +278,6 @@ int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_
 #include "api_render.cuh"
 #include "api_sppm.cuh"
 #include "api_multi.cuh"
+#include "api_sppm_multi.cuh"
 #include "api_debug.cuh"
 #include "api_static.cuh"

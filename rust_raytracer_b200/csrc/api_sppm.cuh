@@ -36,17 +36,25 @@ SppmGrid sppm_make_grid(const float4* photons, const uint32_t* start, const uint
   return G;
 }
 
-int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, SppmGrid& G, uint32_t* start, uint32_t* index, float4* sorted) {
+SppmSegs sppm_one_seg(const float4* photons, uint32_t n) {
+  SppmSegs S;
+  std::memset(&S, 0, sizeof(S));
+  S.p[0] = photons; S.start[0] = 0; S.start[1] = n; S.n = 1;
+  return S;
+}
+
+// `segs`: where the G.n photons of the map live (one local buffer, or the shards of several devices)
+int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, SppmGrid& G, const SppmSegs& segs, uint32_t* start, uint32_t* index, float4* sorted) {
   cudaStream_t q = ctx->stream;
   const uint32_t n_cells = (uint32_t)G.res * G.res * G.res;
   CU_CHECK(ctx, cudaMemsetAsync(B.cell_count, 0, sizeof(uint32_t) * n_cells, q));
   const int blocks = ctx->prop.multiProcessorCount * 4;
-  if (G.n) k_sppm_grid_count<<<blocks, 256, 0, q>>>(G.photons, G.n, G.lo, G.inv_cell, G.res, B.cell_count);
+  if (G.n) k_sppm_grid_count<<<blocks, 256, 0, q>>>(segs, G.n, G.lo, G.inv_cell, G.res, B.cell_count);
   const uint32_t n_tiles = (n_cells + SPPM_SCAN_TILE - 1) / SPPM_SCAN_TILE;  // <= 512 at 128^3 cells
   k_sppm_scan_tile_sums<<<n_tiles, 1024, 0, q>>>(B.cell_count, n_cells, B.tile_sum);
   k_sppm_scan_tile_offsets<<<1, 1024, 0, q>>>(B.tile_sum, n_tiles, start, n_cells);
   k_sppm_scan_cells<<<n_tiles, 1024, 0, q>>>(B.cell_count, n_cells, B.tile_sum, start, B.cursor);
-  if (G.n) k_sppm_grid_fill<<<blocks, 256, 0, q>>>(G.photons, G.n, G.lo, G.inv_cell, G.res, B.cursor, index, sorted);
+  if (G.n) k_sppm_grid_fill<<<blocks, 256, 0, q>>>(segs, G.n, G.lo, G.inv_cell, G.res, B.cursor, index, sorted);
   CU_CHECK(ctx, cudaGetLastError());
   G.photons = sorted;  // the eye pass reads the cell-ordered copy
   return B200RT_OK;
@@ -147,8 +155,8 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     cudaError_t e = cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp);
     if (e == cudaSuccess) e = cudaEventRecord(ev_ph[k][0], qp);
     if (e != cudaSuccess) return e;
-    if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k);
-    else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k);
+    if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter);
+    else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter);
     e = cudaEventRecord(ev_ph[k][1], qp);
     if (e == cudaSuccess) e = cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp);
     return e;
@@ -165,8 +173,8 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     SppmGrid Gg = sppm_make_grid(B.pg[k], B.start_g, B.index_g, h.n_global, lo, hi);
     SppmGrid Gc = sppm_make_grid(B.pc[k], B.start_c, B.index_c, h.n_caustic, lo, hi);
     SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
-    if ((rc = sppm_build_grid(ctx, B, Gg, B.start_g, B.index_g, B.sg)) != 0) return fail2(rc);
-    if ((rc = sppm_build_grid(ctx, B, Gc, B.start_c, B.index_c, B.sc)) != 0) return fail2(rc);
+    if ((rc = sppm_build_grid(ctx, B, Gg, sppm_one_seg(B.pg[k], h.n_global), B.start_g, B.index_g, B.sg)) != 0) return fail2(rc);
+    if ((rc = sppm_build_grid(ctx, B, Gc, sppm_one_seg(B.pc[k], h.n_caustic), B.start_c, B.index_c, B.sc)) != 0) return fail2(rc);
     SPPM_CHECK(cudaEventRecord(ev_grid, q));
     if (it + 1 < sp.iterations) {
       // the next photon pass writes the buffer iteration it - 1 used: its grid build read it and has finished (the host
@@ -176,8 +184,8 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
       SPPM_CHECK(cudaStreamWaitEvent(qp, ev_grid, 0));
       SPPM_CHECK(launch_photons(it + 1));
     }
-    if (s->dev.has_objf) k_sppm_eye<true><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2);
-    else k_sppm_eye<false><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2);
+    if (s->dev.has_objf) k_sppm_eye<true><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2, 0u, n_pix);
+    else k_sppm_eye<false><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2, 0u, n_pix);
     SPPM_CHECK(cudaEventRecord(ev_eye[k], q));
     // the grid tables (cell_count, cursor, start, index, sg, sc) are single-buffered and the stage events are reused:
     // the host lets the eye pass finish before it builds the next grid — the next photon pass is already running

@@ -35,6 +35,20 @@ struct SppmGrid {  // one photon map
   float3 lo;
   float inv_cell, cell;
 };
+// A photon map as the concatenation of up to 16 segments: the emission-ordered buffers of the devices that traced the
+// photons (one segment on one device).  The grid build reads them in place — over NVLink peer mappings when they live on
+// other GPUs — and writes the cell-ordered copy locally: the all-gather of the map is fused into the counting sort.
+#define SPPM_MAX_SEGS 16
+struct SppmSegs {
+  const float4* p[SPPM_MAX_SEGS];
+  uint32_t start[SPPM_MAX_SEGS + 1];  // photon i lives in segment s with start[s] <= i < start[s + 1]
+  int n;
+};
+DEV const float4* sppm_seg_photon(const SppmSegs& S, uint32_t i) {
+  int s = 0;
+  while (s + 1 < S.n && i >= S.start[s + 1]) ++s;
+  return S.p[s] + 4 * (size_t)(i - S.start[s]);
+}
 struct SppmPixels {
   float4* g;    // global: flux rgb, radius2
   float4* c;    // caustic
@@ -144,7 +158,9 @@ DEV void sppm_store(float4* photons, unsigned int* counter, unsigned int cap, un
 
 // SPPMIntegrator::generate_photon_map (photon_mapper.rs:238-281)
 template <bool OBJF>
-__global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, uint2 key, int iter, float4* pg, float4* pc, unsigned int cap, SppmCounters* cnt) {
+// [id_first, id_first + id_count): the photon ids this launch emits (a shard of the iteration's photons on one of several GPUs)
+__global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, uint2 key, int iter, float4* pg, float4* pc, unsigned int cap, SppmCounters* cnt,
+                                                      unsigned int id_first, unsigned int id_count) {
   unsigned long long n_rays = 0;
   unsigned int lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
   // Per-lane work fetch: a photon walk lasts 1 to dozens of bounces (2.9 on average in the Cornell box), so a warp that
@@ -154,7 +170,7 @@ __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, 
   // but the order of the records in the map.  (The path tracer's extend kernel does NOT do this: there the queue order
   // is what keeps a warp coherent; here there is no order to lose.)
   const unsigned lane = threadIdx.x & 31;
-  const unsigned int n_photons = (unsigned int)sp.photons_per_iter;
+  const unsigned int n_photons = id_count;  // the cursor counts inside the shard
   unsigned int id = 0;
   int bounce = 0;
   bool alive = false, exhausted = false, has_specular = false, has_diffuse = false;
@@ -170,7 +186,9 @@ __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, 
       base = __shfl_sync(0xffffffffu, base, leader);
       if (!alive) {
         id = base + __popc(idle & ((1u << lane) - 1u));
-        if (id < n_photons) {
+        const bool have = id < n_photons;
+        id += id_first;  // the global photon id keys every draw
+        if (have) {
           sppm_emit(S, sp, philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x50u), key), philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x51u), key), ray, power);
           alive = true; bounce = 1; has_specular = false; has_diffuse = false;
         }
@@ -238,9 +256,9 @@ DEV int3 sppm_cell_of(float3 p, float3 lo, float inv_cell, int res) {
 }
 DEV uint32_t sppm_cell_id(int3 c, int res) { return (uint32_t)((c.z * res + c.y) * res + c.x); }
 
-__global__ void k_sppm_grid_count(const float4* photons, uint32_t n, float3 lo, float inv_cell, int res, uint32_t* cell_count) {
+__global__ void k_sppm_grid_count(SppmSegs photons, uint32_t n, float3 lo, float inv_cell, int res, uint32_t* cell_count) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    atomicAdd(&cell_count[sppm_cell_id(sppm_cell_of(f3(photons[4 * (size_t)i]), lo, inv_cell, res), res)], 1u);
+    atomicAdd(&cell_count[sppm_cell_id(sppm_cell_of(f3(*sppm_seg_photon(photons, i)), lo, inv_cell, res), res)], 1u);
 }
 // Exclusive scan of n_cells counts into cell_start (n_cells + 1 entries); cursor = copy of the starts.  Three small
 // launches over 4096-cell tiles (tile sums -> scan of the <= 512 tile sums -> scan inside every tile); the first
@@ -300,10 +318,10 @@ __global__ void __launch_bounds__(1024) k_sppm_scan_cells(const uint32_t* __rest
 // The photon records themselves are moved into cell order (`sorted`), so that a gather over a cell reads one contiguous
 // run of 64-byte records instead of chasing indices through the emission-ordered array; index[] becomes the identity
 // over the sorted array (the consumers keep their cell_start -> index -> photon walk).
-__global__ void k_sppm_grid_fill(const float4* __restrict__ photons, uint32_t n, float3 lo, float inv_cell, int res, uint32_t* cursor, uint32_t* index,
+__global__ void k_sppm_grid_fill(SppmSegs photons, uint32_t n, float3 lo, float inv_cell, int res, uint32_t* cursor, uint32_t* index,
                                  float4* __restrict__ sorted) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const float4* src = photons + 4 * (size_t)i;
+    const float4* src = sppm_seg_photon(photons, i);
     const float4 a = src[0], b = src[1], c = src[2], d = src[3];
     const uint32_t pos = atomicAdd(&cursor[sppm_cell_id(sppm_cell_of(f3(a), lo, inv_cell, res), res)], 1u);
     float4* dst = sorted + 4 * (size_t)pos;
@@ -410,10 +428,12 @@ DEV void sppm_update(const SppmGrid& G, float3 p, float3 bsdf, int k_init, doubl
 
 // SPPMIntegrator::update_sppm (photon_mapper.rs:282-305): one jittered eye ray per pixel and iteration
 template <bool OBJF>
-__global__ void __launch_bounds__(128) k_sppm_eye(DevScene S, RenderConst P, SppmConst sp, int iter, SppmGrid Gg, SppmGrid Gc, SppmPixels px, SppmCounters* cnt) {
-  const uint32_t n_pix = (uint32_t)(P.width * P.height);
+// [pix_first, pix_first + pix_count): the pixels whose statistics this device owns
+__global__ void __launch_bounds__(128) k_sppm_eye(DevScene S, RenderConst P, SppmConst sp, int iter, SppmGrid Gg, SppmGrid Gc, SppmPixels px, SppmCounters* cnt,
+                                                  uint32_t pix_first, uint32_t pix_count) {
+  const uint32_t n_pix = pix_first + pix_count;
   unsigned long long n_rays = 0;
-  for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < n_pix; pixel += gridDim.x * blockDim.x) {
+  for (uint32_t pixel = pix_first + blockIdx.x * blockDim.x + threadIdx.x; pixel < n_pix; pixel += gridDim.x * blockDim.x) {
     Ray ray = camera_ray(P, pixel, (uint32_t)iter);
     for (int bounce = 1; bounce <= SPPM_MAX_BOUNCES; ++bounce) {
       HitRaw hr;

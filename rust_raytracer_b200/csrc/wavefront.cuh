@@ -230,6 +230,20 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
   }
 }
 
+// ---- bulk asynchronous copies (TMA, 1-D): global -> shared memory behind an mbarrier
+#ifndef B200RT_SHADE_BULK  // > 0: stages of the shade kernel's input tiles kept in flight by cp.async.bulk (0: plain loads + L2 prefetch)
+#define B200RT_SHADE_BULK 0
+#endif
+DEV uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+DEV void mbar_init(uint32_t bar, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
+DEV void mbar_expect_tx(uint32_t bar, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory"); }
+DEV void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, unsigned long long policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
+}
+DEV void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile("{\n.reg .pred P1;\nLAB_WAIT:\nmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n@P1 bra DONE;\nbra LAB_WAIT;\nDONE:\n}" ::"r"(bar), "r"(parity) : "memory");
+}
+
 // shade: walks the current queue in order (streaming reads of whole records) and stores every surviving path at
 // its place in the next set.
 #ifndef B200RT_SHADE_MINBLOCKS_PATH  // the PATH instantiation fits 96 registers without spilling (5 blocks/SM) ...
@@ -265,11 +279,52 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
 #ifndef B200RT_SHADE_PREFETCH  // measured: with streaming reads the explicit prefetch only costs registers (18.3 ms vs 17.2 ms at 96 regs)
 #define B200RT_SHADE_PREFETCH 0
 #endif
+#if B200RT_SHADE_BULK
+  // Input tiles of 128 queue positions (ray 4 KB | state 4 KB | hit 2 KB) are copied to shared memory by the TMA unit,
+  // B200RT_SHADE_BULK tiles ahead of the one being shaded: the loads occupy no registers and no warp waits on DRAM.
+  __shared__ __align__(128) unsigned char s_tile[B200RT_SHADE_BULK][10240];
+  __shared__ __align__(8) unsigned long long s_bar[B200RT_SHADE_BULK];
+  const unsigned int n_tiles = (n_ext + 127u) >> 7;
+  unsigned long long l2_evict_first;
+  asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(l2_evict_first));
+  auto issue_tile = [&](unsigned int tile, int st) {  // one thread
+    const unsigned int first = tile << 7, cnt = min(128u, n_ext - first);
+    const uint32_t bar = smem_u32(&s_bar[st]), dst = smem_u32(&s_tile[st][0]);
+    mbar_expect_tx(bar, cnt * 80u);
+    bulk_g2s(dst, B.ray + 2 * (size_t)first, cnt * 32u, bar, l2_evict_first);
+    bulk_g2s(dst + 4096u, B.st + 2 * (size_t)first, cnt * 32u, bar, l2_evict_first);
+    bulk_g2s(dst + 8192u, B.hit + first, cnt * 16u, bar, l2_evict_first);
+  };
+  if (threadIdx.x == 0) {
+    for (int st = 0; st < B200RT_SHADE_BULK; ++st) mbar_init(smem_u32(&s_bar[st]), 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (int st = 0; st < B200RT_SHADE_BULK; ++st) { const unsigned int tile = blockIdx.x + st * gridDim.x; if (tile < n_tiles) issue_tile(tile, st); }
+  unsigned int it = 0;
+  (void)n_work; (void)stride; (void)g0;
+  for (unsigned int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {  // block-uniform trip count (the barrier below)
+    const unsigned int gi = (tile << 7) + threadIdx.x;
+    {
+      const int st = (int)(it % B200RT_SHADE_BULK);
+      mbar_wait(smem_u32(&s_bar[st]), (it / B200RT_SHADE_BULK) & 1u);
+      if (gi < n_ext) {
+        const float4* r = reinterpret_cast<const float4*>(&s_tile[st][0]) + 2 * threadIdx.x;
+        const float4* t = reinterpret_cast<const float4*>(&s_tile[st][4096]) + 2 * threadIdx.x;
+        n_o = r[0]; n_d = r[1]; n_sa = t[0]; n_sb = t[1]; n_hh = reinterpret_cast<const uint4*>(&s_tile[st][8192])[threadIdx.x];
+      }
+      __syncthreads();  // every thread holds its record: the stage can be refilled
+      const unsigned int next = tile + B200RT_SHADE_BULK * gridDim.x;
+      if (threadIdx.x == 0 && next < n_tiles) issue_tile(next, st);
+    }
+#else
 #if B200RT_SHADE_PREFETCH
   if (g0 < n_ext) load_rec(g0);
 #endif
   for (unsigned int gi = g0; gi < n_work; gi += stride) {
-#if !B200RT_SHADE_PREFETCH
+#endif
+#if !B200RT_SHADE_PREFETCH && !B200RT_SHADE_BULK
 #if B200RT_SHADE_L2PF
     if (gi + B200RT_SHADE_L2PF * stride < n_ext) {  // pull a later iteration's records into L2: costs no registers
       const unsigned int nx = gi + B200RT_SHADE_L2PF * stride;

@@ -145,6 +145,21 @@ class Scene:
         return st
 
 
+def render_sppm_multi(scenes, camera, params, iterations=50, photons_per_iter=500000, k_global=100, k_caustic=50, alpha=0.7, light_scale=1e6,
+                      want_pixel_stats=False):
+    """b200rt_render_sppm_multi: the SPPM integrator over the devices of `scenes` (photons sharded by id, the map all-gathered
+    inside the grid build over peer memory, pixel statistics sharded by pixel).  Returns like Scene.render_sppm."""
+    n = len(scenes)
+    handles = (C.c_void_p * n)(*[s._h for s in scenes])
+    accum = np.zeros((params.height, params.width, 4), np.float32)
+    px = np.zeros((params.height, params.width, 10), np.float32) if want_pixel_stats else None
+    sp = F.SppmParams(iterations, photons_per_iter, k_global, k_caustic, alpha, light_scale)
+    st = F.SppmStats()
+    scenes[0].ctx._ok(F.lib().b200rt_render_sppm_multi(n, handles, C.byref(camera), C.byref(params), C.byref(sp), accum.ctypes.data_as(C.c_void_p),
+                                                       px.ctypes.data_as(C.c_void_p) if want_pixel_stats else None, C.byref(st)))
+    return (accum, px, st) if want_pixel_stats else (accum, st)
+
+
 def compile_stats(builder_or_desc):
     """Host only: the wide BVH scene_create would build — {"bvh_nodes", "bvh4_depth", "stack_needed", "stack_capacity"}."""
     desc = builder_or_desc.desc() if hasattr(builder_or_desc, "desc") else builder_or_desc

@@ -104,3 +104,61 @@ def test_sppm_argument_errors(ctx):
         args.update(kw)
         with pytest.raises(rt.B200RTError):
             scene2.render_sppm(sb2.camera, rt.copy_params(sb2.params, width=16, height=16, spp_count=1), **args)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_ctx", [2, 3])
+def test_sppm_multi_on_one_device_equals_render_sppm(ctx, n_ctx):
+    """b200rt_render_sppm_multi with n contexts on ONE GPU (the driver's box): photons sharded by id, the photon maps gathered
+    inside the grid build (plain local memory here, NVLink peer mappings on a multi-GPU box), pixel statistics sharded by pixel,
+    final pass by sample index + k_reduce_peers.  Every draw is keyed by the global photon / pixel id, so the stored photon
+    counts and the ray counts equal the one-device call's EXACTLY; statistics and image agree up to float summation order
+    (the order of the photons inside a cell differs) and k-th-neighbour ties."""
+    sb = scene_builder("cornell_ref")
+    p = rt.copy_params(sb.params, width=W, height=H, spp_count=SPP + 1, seed=5)  # 5 samples over 2 or 3 shards: uneven split
+    one = rt.Scene(ctx, sb)
+    acc1, px1, st1 = one.render_sppm(sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS + 1, want_pixel_stats=True)
+    scenes = [one] + [rt.Scene(rt.Context(0), sb) for _ in range(n_ctx - 1)]
+    accm, pxm, stm = rt.render_sppm_multi(scenes, sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS + 1, want_pixel_stats=True)
+    assert (stm.global_photons, stm.caustic_photons, stm.photon_rays, stm.eye_rays) == (st1.global_photons, st1.caustic_photons, st1.photon_rays, st1.eye_rays)
+    assert np.all(accm[..., 3] == SPP + 1)
+    assert np.array_equal(pxm[..., 4], px1[..., 4]) and np.array_equal(pxm[..., 9], px1[..., 9])  # photon counts per pixel: integers, order-independent
+    for k in (3, 8):  # radius2: a product of exactly representable ratios applied in the same order
+        np.testing.assert_allclose(pxm[..., k], px1[..., k], rtol=1e-5, atol=0)
+    for k0 in (0, 5):  # flux: sums over the photons in range, in cell order
+        np.testing.assert_allclose(pxm[..., k0:k0 + 3], px1[..., k0:k0 + 3], rtol=2e-3, atol=1e-3 * float(np.abs(px1[..., k0:k0 + 3]).max()))
+    a, b = np.nan_to_num(accm[..., :3], nan=0.0, posinf=0.0), np.nan_to_num(acc1[..., :3], nan=0.0, posinf=0.0)
+    assert abs(a.mean() - b.mean()) < 1e-3 * b.mean()
+    assert np.mean(np.abs(a - b) <= 2e-3 * np.abs(b) + 1e-3 * b.mean()) > 0.999
+    print("sppm multi x%d on one device: %.1f ms wall (one context: %.1f ms device)" % (n_ctx, stm.ms_total, st1.ms_total))
+
+
+@pytest.mark.gpu
+def test_sppm_multi_two_devices(ctx):
+    import ctypes as C
+    n = C.c_int(0)
+    F.lib().b200rt_device_count(C.byref(n))
+    if n.value < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    sb = scene_builder("cornell_ref")
+    p = rt.copy_params(sb.params, width=W, height=H, spp_count=SPP, seed=5)
+    s0, s1 = rt.Scene(ctx, sb), rt.Scene(rt.Context(1), sb)
+    acc1, st1 = s0.render_sppm(sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS)
+    accm, stm = rt.render_sppm_multi([s0, s1], sb.camera, p, iterations=ITER, photons_per_iter=PHOTONS)
+    assert (stm.global_photons, stm.caustic_photons, stm.photon_rays, stm.eye_rays) == (st1.global_photons, st1.caustic_photons, st1.photon_rays, st1.eye_rays)
+    a, b = np.nan_to_num(accm[..., :3], nan=0.0, posinf=0.0), np.nan_to_num(acc1[..., :3], nan=0.0, posinf=0.0)
+    assert abs(a.mean() - b.mean()) < 1e-3 * b.mean()
+
+
+@pytest.mark.gpu
+def test_sppm_multi_argument_errors(ctx):
+    sb = scene_builder("cornell_ref")
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=16, height=16, spp_count=1)
+    with pytest.raises(rt.B200RTError) as e:
+        rt.render_sppm_multi([scene, scene], sb.camera, p, iterations=1, photons_per_iter=100)
+    assert e.value.status == F.ERR_INVALID and "own context" in str(e.value)
+    with pytest.raises(rt.B200RTError):
+        rt.render_sppm_multi([scene], sb.camera, p, iterations=0, photons_per_iter=100)
+    acc, st = rt.render_sppm_multi([scene], sb.camera, p, iterations=2, photons_per_iter=3000)  # one device: no peers at all
+    assert st.global_photons > 1000 and np.all(acc[..., 3] == 1)

@@ -2,7 +2,8 @@
 b200rt_render_multi call (sample ranges per device + one peer-memory / NCCL reduce), then tonemap + PNG.  Prints one JSON
 line with the device time (slowest GPU's CUDA-event render time + the reduce), the host wall time of the call, and a
 consistency check against an independent one-GPU render (different samples): per-channel image means.
-usage: python tools/full_job.py [--spp 10000] [--gpus N] [--check-spp 1024] [--out gpurun_out/book2_full.png]"""
+--scene mesh runs BASELINE configs[4] the same way: the 317,952-triangle mesh in the Cornell box, 1920x1080, 4096 spp, MixturePDF.
+usage: python tools/full_job.py [--scene book2|mesh] [--spp N] [--gpus N] [--check-spp 1024] [--out gpurun_out/book2_full.png]"""
 import argparse
 import ctypes as C
 import json
@@ -19,7 +20,8 @@ from rust_raytracer_b200 import _ffi as F  # noqa: E402
 from scenes_util import scene_builder  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--spp", type=int, default=10000)
+ap.add_argument("--scene", default="book2", choices=["book2", "mesh"])
+ap.add_argument("--spp", type=int, default=0)
 ap.add_argument("--gpus", type=int, default=0)
 ap.add_argument("--check-spp", type=int, default=1024)
 ap.add_argument("--out", default="")
@@ -27,8 +29,9 @@ a = ap.parse_args()
 n = C.c_int(0)
 F.lib().b200rt_device_count(C.byref(n))
 gpus = a.gpus or n.value
-sb = scene_builder("book2")
-W = H = 800
+sb = scene_builder(a.scene)
+W, H = (800, 800) if a.scene == "book2" else (1920, 1080)
+a.spp = a.spp or (10000 if a.scene == "book2" else 4096)
 ctxs = [rt.Context(g) for g in range(gpus)]
 scenes = [rt.Scene(c, sb) for c in ctxs]
 p = rt.copy_params(sb.params, width=W, height=H, spp_count=a.spp, seed=1)
@@ -38,7 +41,8 @@ acc, st, ms = rt.render_multi(scenes, sb.camera, p)
 wall = time.perf_counter() - t0
 paths = W * H * a.spp
 dev_ms = ms.ms_render_max + ms.ms_reduce
-out = {"job": "book-2 final scene %dx%d, %d spp, depth 50, %d x B200, one b200rt_render_multi call" % (W, H, a.spp, gpus),
+what = "book-2 final scene" if a.scene == "book2" else "317,952-triangle mesh in the Cornell box (MixturePDF)"
+out = {"job": "%s %dx%d, %d spp, depth 50, %d x B200, one b200rt_render_multi call" % (what, W, H, a.spp, gpus),
        "paths": paths, "rays": int(ms.extend_rays + ms.shadow_rays),
        "device_ms": dev_ms, "ms_render_max": ms.ms_render_max, "ms_render_per_gpu": [round(s.ms_total, 1) for s in st], "ms_reduce": ms.ms_reduce,
        "reduce_path": {0: "none", 1: "nccl", 2: "peer"}[ms.reduce_path], "wall_ms": wall * 1e3,
@@ -55,7 +59,7 @@ if a.check_spp > 0:
                     "rel_diff_of_means": [float(abs(x - y) / y) for x, y in zip(out["image_mean"], m1)],
                     "one_gpu_Mpaths_per_s": W * H * a.check_spp / st1.ms_total / 1e3}
     # 16x16 tile means: the 10k-spp job against the check render (whose noise dominates)
-    t = lambda im: im.reshape(H // 16, 16, W // 16, 16, 3).mean(axis=(1, 3))  # noqa: E731
+    t = lambda im: im[:H // 16 * 16].reshape(H // 16, 16, W // 16, 16, 3).mean(axis=(1, 3))  # noqa: E731
     out["check"]["tile_rms_rel"] = float(np.sqrt(np.mean((t(img) - t(img1)) ** 2)) / np.mean(t(img1)))
 if a.out:
     rgb = ctxs[0].tonemap(acc)
