@@ -160,19 +160,20 @@ def run_sppm(args):
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 8
         orc = oracle_scene("cornell_ref")
-        small = max(20000, PHOTONS // 25)  # photons of the bounded sample (the per-photon cost is constant)
+        # bounded sample: ONE iteration with the full 500,000 photons on an 8x8 image (the photon pass; the 64 eye look-ups of the
+        # exhaustive-scan checker are ~0.05 s inside it), then the same with 8192 more final-pass samples per pixel
 
         def cpu_run(size, spp):
             t0 = _t.perf_counter()
-            orc.sppm_render(sb.camera, rt.copy_params(p, width=size, height=size, spp_count=spp), iterations=1, photons_per_iter=small, n_threads=threads)
+            orc.sppm_render(sb.camera, rt.copy_params(p, width=size, height=size, spp_count=spp), iterations=1, photons_per_iter=PHOTONS, n_threads=threads)
             return _t.perf_counter() - t0
-        t_a, t_b, t_c = cpu_run(8, 1), cpu_run(48, 1), cpu_run(48, 9)
-        per_sample = max(t_c - t_b, 0.0) / 8 / (48 * 48)
-        per_px = max(t_b - t_a - (48 * 48 - 64) * per_sample, 0.0) / (48 * 48 - 64)   # eye pass + exhaustive k-nearest over `small` photons
-        per_photon = max(t_a - 64 * (per_px + per_sample), 0.0) / small
+        cpu_run(8, 1)  # warm-up (page-in, thread pool)
+        t_a, t_c = cpu_run(8, 1), cpu_run(8, 8193)
+        per_photon = t_a / PHOTONS
+        per_sample = max(t_c - t_a, 0.0) / (8192 * 64)
         est_like_for_like = ITER * PHOTONS * per_photon + SPP * W * H * per_sample
         cpu = {"value": est_like_for_like * 1e3, "unit": "ms per frame (photon passes + final pass only)", "cores": threads, "kind": "port",
-               "sample": "1 iteration x %d photons at 8x8 (%.1f s), 48x48 (%.1f s), 48x48 with 9 spp (%.1f s), scaled to 50 x 500,000 photons and 800x800x256 samples" % (small, t_a, t_b, t_c),
+               "sample": "1 iteration x %d photons at 8x8 with 1 spp (%.2f s) and with 8193 spp (%.2f s), scaled to 50 x 500,000 photons and 800x800x256 samples" % (PHOTONS, t_a, t_c),
                "us_per_photon": per_photon * 1e6, "us_per_final_sample": per_sample * 1e6,
                "note": "the oracle's eye pass replaces kd-tree 0.4.1 by an exhaustive scan (a checker, not a baseline) and is left out of this figure; the GPU time beside it is ms_photons + ms_final"}
     n_emit, n_eye, n_final = ITER * PHOTONS, ITER * W * H, SPP * W * H

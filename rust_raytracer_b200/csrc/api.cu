@@ -242,6 +242,7 @@ int b200rt_intersect_batch_device(b200rt_scene* s, const float* o_time, const fl
   if (n == 0) return B200RT_OK;  // empty batch
   b200rt_ctx* ctx = s->ctx;
   CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  cudaGetLastError();  // stale non-sticky errors of earlier, unrelated calls are not this launch's
   const int threads = 128;
   unsigned long long want = (n + threads - 1) / threads;
   unsigned long long cap = (unsigned long long)ctx->prop.multiProcessorCount * 64ull;

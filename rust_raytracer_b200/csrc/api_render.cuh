@@ -113,6 +113,18 @@ static void dbg_dump_iteration(b200rt_scene* s, const WfBuffers& B, cudaStream_t
 }
 #endif
 
+// bin = 1 + umulhi(prim, bin_mul) maps [0, n_prims) onto bins 1 .. n_bins - 1 (one primitive per bin when they fit)
+// 1024 or 2048 bins (shade keeps the offsets in shared memory up to WF_SMEM_BINS; more only pays through the
+// environment override: measured 1024 / 4096 / 16384 on the 318k-triangle mesh: 1862 / 1868 / 1848 Mpaths/s)
+static void wf_bin_layout(uint32_t n_prims, unsigned int& n_bins, unsigned int& bin_mul) {
+  unsigned int nb = n_prims + 1u > 1024u ? 2048u : 1024u;
+  const int forced = env_int("B200RT_WF_NBINS", 0, 0, WF_MAX_BINS);
+  if (forced > 0) nb = (unsigned int)((forced + 1023) & ~1023);
+  n_bins = nb;
+  const unsigned long long m = (((unsigned long long)(nb - 1)) << 32) / (unsigned long long)(n_prims > 0 ? n_prims : 1);
+  bin_mul = m > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)m;
+}
+
 static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMap& M0, float* accum, b200rt_stats* st) {
   b200rt_ctx* ctx = s->ctx;
   // queue positions in flight: 144 B each (9.7 GB at 2^26 over all pipelines — HBM is plentiful, and a larger pool means
@@ -133,16 +145,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   if (ctx->static_wf) n_pipes = 1;  // b200rt_render_device_static: one pipeline over the library's static queue block
   const unsigned long long cap = ctx->static_wf ? (unsigned long long)ctx->static_wf->pool : (1ull << pool_log2) / (unsigned long long)n_pipes;
   unsigned int n_bins, bin_mul;
-  {  // bin = 1 + umulhi(prim, bin_mul) maps [0, n_prims) onto bins 1 .. n_bins - 1 (one primitive per bin when they fit)
-    // 1024 or 2048 bins (shade keeps the offsets in shared memory up to WF_SMEM_BINS; more only pays through the
-    // environment override: measured 1024 / 4096 / 16384 on the 318k-triangle mesh: 1862 / 1868 / 1848 Mpaths/s)
-    unsigned int nb = s->n_prims + 1u > 1024u ? 2048u : 1024u;
-    const int forced = env_int("B200RT_WF_NBINS", 0, 0, WF_MAX_BINS);
-    if (forced > 0) nb = (unsigned int)((forced + 1023) & ~1023);
-    n_bins = nb;
-    const unsigned long long m = (((unsigned long long)(nb - 1)) << 32) / (unsigned long long)(s->n_prims > 0 ? s->n_prims : 1);
-    bin_mul = m > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)m;
-  }
+  wf_bin_layout(s->n_prims, n_bins, bin_mul);
   const bool nee = P0.integrator == B200RT_INTEGRATOR_NEE;
   WfPipeState pipes[WF_MAX_PIPES];
   for (int k = 0; k < n_pipes; ++k) {
@@ -362,6 +365,7 @@ int b200rt_render_device(b200rt_scene* s, const b200rt_camera* cam, const b200rt
   int rc = validate_params(ctx, params);
   if (rc) return rc;
   CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  cudaGetLastError();  // stale non-sticky errors of earlier, unrelated calls are not this call's
   b200rt_stats local;
   std::memset(&local, 0, sizeof(local));
   const RenderConst P = make_render_const(cam, params);

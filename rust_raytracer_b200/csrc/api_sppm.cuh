@@ -8,14 +8,28 @@ namespace {
 
 struct SppmBuffers {
   float4 *pg[2] = {nullptr, nullptr}, *pc[2] = {nullptr, nullptr};  // photons in emission order, double-buffered over the iterations
-  float4 *sg = nullptr, *sc = nullptr;  // photons in cell order
-  uint32_t *tile_sum = nullptr, *cell_count = nullptr, *start_g = nullptr, *start_c = nullptr, *cursor = nullptr, *index_g = nullptr, *index_c = nullptr;
+  float4 *sg = nullptr, *sc = nullptr;  // photons in cell order: `sorted_cap` positions, then 2 x `sorted_cap` attribute rows
+  size_t sorted_cap = 0;
+  uint32_t *tile_sum = nullptr, *cell_count = nullptr, *start_g = nullptr, *start_c = nullptr, *cursor = nullptr;
   float4 *px_g = nullptr, *px_c = nullptr;
   uint2* px_n = nullptr;
+  float4 *vp = nullptr, *vb = nullptr;       // eye pass: visible point and bsdf per pixel
+  uint32_t *knn_list = nullptr, *knn_n = nullptr;  // eye pass: (pixel, map) pairs for the k-nearest kernel
   SppmCounters* cnt = nullptr;
   float* accum = nullptr;
+  cudaError_t alloc_maps(size_t cap, size_t n_pix) {  // the cell-ordered maps and the eye-pass scratch (both entry points)
+    sorted_cap = cap;
+    cudaError_t e = cudaMalloc((void**)&sg, cap * 48);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&sc, cap * 48);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&vp, 16 * n_pix);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&vb, 16 * n_pix);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&knn_list, 4 * 2 * n_pix);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&knn_n, 256);
+    return e;
+  }
+  SppmEye eye() const { return SppmEye{vp, vb, knn_list, knn_n}; }
   void release() {
-    void* all[] = {pg[0], pg[1], pc[0], pc[1], sg, sc, tile_sum, cell_count, start_g, start_c, cursor, index_g, index_c, px_g, px_c, px_n, cnt, accum};
+    void* all[] = {pg[0], pg[1], pc[0], pc[1], sg, sc, tile_sum, cell_count, start_g, start_c, cursor, px_g, px_c, px_n, vp, vb, knn_list, knn_n, cnt, accum};
     for (void* p : all) if (p) cudaFree(p);
   }
 };
@@ -23,9 +37,9 @@ struct SppmBuffers {
 const int SPPM_MAX_RES = 128;
 
 // grid resolution and placement for a map of n photons inside the photon bounding box [lo, hi]
-SppmGrid sppm_make_grid(const float4* photons, const uint32_t* start, const uint32_t* index, uint32_t n, const float lo[3], const float hi[3]) {
+SppmGrid sppm_make_grid(const uint32_t* start, uint32_t n, const float lo[3], const float hi[3]) {
   SppmGrid G;
-  G.photons = photons; G.cell_start = start; G.index = index; G.n = n;
+  G.pos = nullptr; G.attr = nullptr; G.cell_start = start; G.n = n;  // pos / attr: set by sppm_build_grid
   int res = (int)std::cbrt((double)n / 2.0) + 1;
   G.res = res < 1 ? 1 : (res > SPPM_MAX_RES ? SPPM_MAX_RES : res);
   float ext = std::fmax(hi[0] - lo[0], std::fmax(hi[1] - lo[1], hi[2] - lo[2]));
@@ -44,7 +58,7 @@ SppmSegs sppm_one_seg(const float4* photons, uint32_t n) {
 }
 
 // `segs`: where the G.n photons of the map live (one local buffer, or the shards of several devices)
-int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, SppmGrid& G, const SppmSegs& segs, uint32_t* start, uint32_t* index, float4* sorted) {
+int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, SppmGrid& G, const SppmSegs& segs, uint32_t* start, float4* sorted) {
   cudaStream_t q = ctx->stream;
   const uint32_t n_cells = (uint32_t)G.res * G.res * G.res;
   CU_CHECK(ctx, cudaMemsetAsync(B.cell_count, 0, sizeof(uint32_t) * n_cells, q));
@@ -54,9 +68,130 @@ int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, SppmGrid& G, const SppmSegs
   k_sppm_scan_tile_sums<<<n_tiles, 1024, 0, q>>>(B.cell_count, n_cells, B.tile_sum);
   k_sppm_scan_tile_offsets<<<1, 1024, 0, q>>>(B.tile_sum, n_tiles, start, n_cells);
   k_sppm_scan_cells<<<n_tiles, 1024, 0, q>>>(B.cell_count, n_cells, B.tile_sum, start, B.cursor);
-  if (G.n) k_sppm_grid_fill<<<blocks, 256, 0, q>>>(segs, G.n, G.lo, G.inv_cell, G.res, B.cursor, index, sorted);
+  float4* attr = sorted + B.sorted_cap;
+  if (G.n) k_sppm_grid_fill<<<blocks, 256, 0, q>>>(segs, G.n, G.lo, G.inv_cell, G.res, B.cursor, sorted, attr);
   CU_CHECK(ctx, cudaGetLastError());
-  G.photons = sorted;  // the eye pass reads the cell-ordered copy
+  G.pos = sorted; G.attr = attr;  // the eye pass reads the cell-ordered copy
+  return B200RT_OK;
+}
+
+// SPPMIntegrator::update_sppm for the pixels [pix_first, pix_first + pix_count) on the context stream: the eye rays to their
+// visible points, the radius gather for the pixels that have statistics, the k-nearest start for those that do not
+int sppm_eye_pass(b200rt_ctx* ctx, const b200rt_scene* s, const RenderConst& Peye, const SppmConst& sp, int it, const SppmGrid& Gg, const SppmGrid& Gc,
+                  const SppmPixels& px, SppmBuffers& B, uint32_t pix_first, uint32_t pix_count) {
+  cudaStream_t q = ctx->stream;
+  const int sms = ctx->prop.multiProcessorCount;
+  const SppmEye E = B.eye();
+  if (pix_count == 0) return B200RT_OK;
+  CU_CHECK(ctx, cudaMemsetAsync(B.knn_n, 0, 4, q));
+  const int trace_blocks = (int)std::min<uint32_t>((pix_count + 127u) / 128u, (uint32_t)sms * 8u);
+  if (s->dev.has_objf) k_sppm_eye_trace<true><<<trace_blocks, 128, 0, q>>>(s->dev, Peye, it, px, E, B.cnt + 2, pix_first, pix_count);
+  else k_sppm_eye_trace<false><<<trace_blocks, 128, 0, q>>>(s->dev, Peye, it, px, E, B.cnt + 2, pix_first, pix_count);
+  const uint32_t gather_threads = pix_count * SPPM_GATHER_LANES;
+  const int gather_blocks = (int)std::min<uint32_t>((gather_threads + 255u) / 256u, (uint32_t)sms * 32u);
+  k_sppm_gather<<<gather_blocks, 256, 0, q>>>(Gg, Gc, px, E, sp.alpha, pix_first, pix_count);
+  // every pixel needs its k-nearest start once (the first iteration it sees a diffuse surface): a full grid then, stragglers later
+  const int knn_blocks = it == 0 ? sms * 16 : sms * 2;
+  k_sppm_knn<<<knn_blocks, 128, 0, q>>>(Gg, Gc, px, E, sp.k_global, sp.k_caustic);
+  CU_CHECK(ctx, cudaGetLastError());
+  return B200RT_OK;
+}
+
+// ---- the photon pass through the wavefront queues (kernels: sppm.cuh) ---------------------------------------------
+struct SppmPhotonWf {
+  void* block = nullptr;
+  WfBuffers B{};
+  PathMap M{};
+  WfCounters* host = nullptr;  // pinned: the queue counters after the last launched wavefront iteration
+  unsigned int* n_log = nullptr;  // device: rays in the queue per wavefront iteration
+  unsigned int* n_log_host = nullptr;  // pinned
+  int launched = 0;   // wavefront iterations queued for the current pass
+  int plan = 40;      // wavefront iterations to queue before looking at the counters (adapted from the last pass)
+  int grid_ext = 0, grid_shade = 0, sms = 0;
+  bool objf = false;
+  static const int MAX_ITERS = 4096;
+  void release() {
+    if (block) cudaFree(block);
+    if (n_log) cudaFree(n_log);
+    if (host) cudaFreeHost(host);
+    if (n_log_host) cudaFreeHost(n_log_host);
+    block = nullptr; n_log = nullptr; host = nullptr; n_log_host = nullptr;
+  }
+};
+
+int sppm_photon_wf_alloc(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, unsigned int n_photons) {
+  const size_t P = ((size_t)n_photons + 31u) & ~(size_t)31u;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
+  size_t o_ray[2], o_st[2];
+  for (int k = 0; k < 2; ++k) { o_ray[k] = take(P * 32); o_st[k] = take(P * 32); }
+  const size_t o_hit = take(P * 16), o_bc = take(4 * WF_MAX_BINS), o_bo = take(4 * (WF_MAX_BINS + 1)), o_cnt = take(sizeof(WfCounters));
+  CU_CHECK(ctx, cudaMalloc(&W.block, off));
+  CU_CHECK(ctx, cudaMalloc((void**)&W.n_log, 4 * SppmPhotonWf::MAX_ITERS));
+  CU_CHECK(ctx, cudaMallocHost((void**)&W.host, sizeof(WfCounters)));
+  CU_CHECK(ctx, cudaMallocHost((void**)&W.n_log_host, 4 * SppmPhotonWf::MAX_ITERS));
+  char* b = (char*)W.block;
+  W.B.ray = (float4*)(b + o_ray[0]); W.B.ray_n = (float4*)(b + o_ray[1]); W.B.st = (float4*)(b + o_st[0]); W.B.st_n = (float4*)(b + o_st[1]);
+  W.B.hit = (uint4*)(b + o_hit); W.B.bin_count = (unsigned int*)(b + o_bc); W.B.bin_off = (unsigned int*)(b + o_bo); W.B.cnt = (WfCounters*)(b + o_cnt);
+  W.B.sh_o = W.B.sh_d = W.B.sh_c = nullptr; W.B.sh_seed = nullptr;
+  W.B.pool = (unsigned int)P;
+  wf_bin_layout(s->n_prims, W.B.n_bins, W.B.bin_mul);
+  W.M.tiles_x = 0; W.M.per_sample = n_photons; W.M.total = n_photons;
+  W.sms = ctx->prop.multiProcessorCount;
+  W.objf = s->dev.has_objf != 0;
+  int occ_ext = 1, occ_shade = 1;
+  CU_CHECK(ctx, W.objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<false>, 128, 0));
+  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_sppm_ph_shade, 128, 0));
+  W.grid_ext = W.sms * (occ_ext > 0 ? occ_ext : 1);
+  W.grid_shade = W.sms * (occ_shade > 0 ? occ_shade : 1);
+  W.plan = env_int("B200RT_SPPM_PHOTON_ITERS", 40, 1, SppmPhotonWf::MAX_ITERS);
+  return B200RT_OK;
+}
+
+// `n` more wavefront iterations of the current pass on `qp`, then the read-back of the queue counters
+int sppm_photon_wf_enqueue(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, const SppmConst& sp, uint2 key, int it, float4* pg, float4* pc, unsigned int cap,
+                           SppmCounters* cnt_dev, unsigned int id_first, int n, cudaStream_t qp) {
+  for (int b = 0; b < n && W.launched < SppmPhotonWf::MAX_ITERS; ++b, ++W.launched) {
+    const int j = W.launched;
+    std::swap(W.B.ray, W.B.ray_n);
+    std::swap(W.B.st, W.B.st_n);
+    // launch sizes follow the queue: it shrinks geometrically (a bound, not a promise: the kernels are persistent / grid-stride)
+    const double est = (double)W.M.total * std::pow(0.8, (double)j);
+    const int want = (int)std::min<double>(est / 128.0 + 1.0, 1e9);
+    const int g_ext = std::max(std::min(W.grid_ext, want), W.sms), g_shade = std::max(std::min(W.grid_shade, want), W.sms);
+    if (j == 0) k_sppm_ph_generate<<<W.sms * 8, 256, 0, qp>>>(s->dev, W.B, W.M, sp, key, it, id_first);
+    k_sppm_ph_control<<<1, WF_CTRL_THREADS, 0, qp>>>(W.B, W.M, W.n_log, j);
+    if (W.objf) k_wf_extend<true><<<g_ext, 128, 0, qp>>>(s->dev, W.B, 0.0001f, 1);  // photon_mapper.rs:246
+    else k_wf_extend<false><<<g_ext, 128, 0, qp>>>(s->dev, W.B, 0.0001f, 1);
+    k_wf_control_shade<<<1, WF_CTRL_THREADS, 0, qp>>>(W.B);
+    k_sppm_ph_shade<<<g_shade, 128, 0, qp>>>(s->dev, W.B, key, it, pg, pc, cap, cnt_dev);
+  }
+  CU_CHECK(ctx, cudaGetLastError());
+  CU_CHECK(ctx, cudaMemcpyAsync(W.host, W.B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, qp));
+  CU_CHECK(ctx, cudaMemcpyAsync(W.n_log_host, W.n_log, 4 * (size_t)W.launched, cudaMemcpyDeviceToHost, qp));
+  return B200RT_OK;
+}
+int sppm_photon_wf_begin(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, const SppmConst& sp, uint2 key, int it, float4* pg, float4* pc, unsigned int cap,
+                         SppmCounters* cnt_dev, unsigned int id_first, cudaStream_t qp) {
+  CU_CHECK(ctx, cudaMemsetAsync(W.B.cnt, 0, sizeof(WfCounters), qp));
+  W.launched = 0;
+  return sppm_photon_wf_enqueue(ctx, s, W, sp, key, it, pg, pc, cap, cnt_dev, id_first, W.plan, qp);
+}
+// after cudaStreamSynchronize(qp): has the queue drained?  If not, more iterations (the rare long photon walks), blocking.
+// Returns the rays traced by the pass in *photon_rays.
+int sppm_photon_wf_finish(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, const SppmConst& sp, uint2 key, int it, float4* pg, float4* pc, unsigned int cap,
+                          SppmCounters* cnt_dev, unsigned int id_first, cudaStream_t qp, unsigned long long* photon_rays) {
+  while (W.host->n_ext_next != 0 || W.host->next_path < W.M.total) {
+    if (W.launched >= SppmPhotonWf::MAX_ITERS) { ctx->err = "sppm: a photon walk exceeded the wavefront iteration budget"; return B200RT_ERR_CUDA; }
+    const int rc = sppm_photon_wf_enqueue(ctx, s, W, sp, key, it, pg, pc, cap, cnt_dev, id_first, 8, qp);
+    if (rc) return rc;
+    CU_CHECK(ctx, cudaStreamSynchronize(qp));
+  }
+  // the SPPM iteration counter's photon_rays also needs the counters of the pass; extend counts dead records, not rays
+  *photon_rays = W.host->extend_rays - W.host->dead_rays;
+  int used = 0;
+  while (used < W.launched && W.n_log_host[used] != 0u) ++used;  // iterations that held rays
+  if (!std::getenv("B200RT_SPPM_PHOTON_ITERS")) W.plan = std::min(std::max(used + 4, 8), (int)SppmPhotonWf::MAX_ITERS);
   return B200RT_OK;
 }
 
@@ -75,6 +210,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   }
   if (s->dev.n_lights < 1) { ctx->err = "sppm: the scene has no marked light (World::new takes a light list, world.rs:15-25)"; return B200RT_ERR_INVALID; }
   CU_CHECK(ctx, cudaSetDevice(ctx->device));
+  cudaGetLastError();  // a non-sticky error an earlier, unrelated call left in this thread is not this call's (the launch checks below poll the same state)
   cudaStream_t q = ctx->stream;
   const uint32_t n_pix = (uint32_t)params->width * params->height;
   const unsigned int cap = (unsigned int)sppm->photons_per_iter * 16u;  // stored photons per iteration (~1.5 per emitted photon in a Cornell box)
@@ -83,10 +219,9 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   cudaError_t e = cudaSuccess;
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
   for (int k = 0; k < 2; ++k) { alloc((void**)&B.pg[k], (size_t)cap * 64); alloc((void**)&B.pc[k], (size_t)cap * 64); }
-  alloc((void**)&B.sg, (size_t)cap * 64); alloc((void**)&B.sc, (size_t)cap * 64);
+  if (e == cudaSuccess) e = B.alloc_maps(cap, n_pix);
   alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
   alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
-  alloc((void**)&B.index_g, 4 * (size_t)cap); alloc((void**)&B.index_c, 4 * (size_t)cap);
   alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
   alloc((void**)&B.accum, 16 * (size_t)n_pix);
   alloc((void**)&B.cnt, 3 * sizeof(SppmCounters));  // [0], [1]: the photon pass of even / odd iterations; [2]: eye + final pass
@@ -119,7 +254,10 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   // almost for free.  Photon maps do not depend on the pixel statistics, only the eye pass does (photon_mapper.rs:154-160).
   // blocks per SM (150 / 128 registers per thread let 3 / 4 blocks of 128 threads reside).  Measured at the reference
   // configuration, serial 339 ms; overlapped with a photon grid of 1 / 2 / 3 / 4 blocks per SM: 303 / 276 / 264 / 253 ms
-  const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8), eye_grid = env_int("B200RT_SPPM_EYE_GRID", 4, 1, 8);
+  const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8);
+  // photon pass: through the wavefront queues (default), or the one-thread-per-photon kernel of round 1 (A/B)
+  const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;
+  SppmPhotonWf PW;
   const bool trace = env_int("B200RT_SPPM_TRACE", 0, 0, 1) != 0;
   cudaStream_t qp = nullptr;
   cudaEvent_t ev_ph[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}, ev_eye[2] = {nullptr, nullptr}, ev_grid = nullptr;  // timing only
@@ -130,6 +268,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     for (int a = 0; a < 2; ++a) { for (int b = 0; b < 2; ++b) if (ev_ph[a][b]) cudaEventDestroy(ev_ph[a][b]); if (ev_eye[a]) cudaEventDestroy(ev_eye[a]); }
     if (ev_grid) cudaEventDestroy(ev_grid);
     if (hcnt) cudaFreeHost(hcnt);
+    PW.release();
     return fail(code);
   };
 #undef SPPM_CHECK
@@ -143,6 +282,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   SPPM_CHECK(cudaEventCreate(&ev_grid));
   SPPM_CHECK(cudaMallocHost(&hcnt, 3 * sizeof(SppmCounters)));
   std::memset(hcnt, 0, 3 * sizeof(SppmCounters));
+  if (!photons_mega && (rc = sppm_photon_wf_alloc(ctx, s, PW, (unsigned int)sp.photons_per_iter)) != 0) return fail2(rc);
   SPPM_CHECK(cudaMemsetAsync(B.cnt + 2, 0, sizeof(SppmCounters), q));
   SPPM_CHECK(cudaEventRecord(ctx->ev[0], q));
   SPPM_CHECK(cudaStreamWaitEvent(qp, ctx->ev[0], 0));
@@ -155,7 +295,9 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     cudaError_t e = cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp);
     if (e == cudaSuccess) e = cudaEventRecord(ev_ph[k][0], qp);
     if (e != cudaSuccess) return e;
-    if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter);
+    if (!photons_mega) {
+      if (sppm_photon_wf_begin(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, qp)) return cudaErrorUnknown;
+    } else if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter);
     else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter);
     e = cudaEventRecord(ev_ph[k][1], qp);
     if (e == cudaSuccess) e = cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp);
@@ -165,16 +307,26 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   for (int it = 0; it < sp.iterations; ++it) {
     const int k = it & 1;
     SPPM_CHECK(cudaStreamSynchronize(qp));  // photon map of this iteration is complete, its counters are on the host
+    if (!photons_mega) {  // ... unless a photon walk outlasted the queued wavefront iterations (then: more of them, and the counters again)
+      const int launched = PW.launched;
+      unsigned long long rays = 0;
+      if ((rc = sppm_photon_wf_finish(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, qp, &rays)) != 0) return fail2(rc);
+      if (PW.launched != launched) {
+        SPPM_CHECK(cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp));
+        SPPM_CHECK(cudaStreamSynchronize(qp));
+      }
+      hcnt[k].photon_rays = rays;
+    }
     const SppmCounters h = hcnt[k];
     if (cudaEventElapsedTime(&ms, ev_ph[k][0], ev_ph[k][1]) == cudaSuccess) local.ms_photons += ms;
     if (h.overflow) { ctx->err = "sppm: photon buffer overflow (more than 16 stored photons per emitted photon)"; return fail2(B200RT_ERR_NOMEM); }
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
     if (h.n_global) for (int a = 0; a < 3; ++a) { lo[a] = sppm_unord(h.lo[a]); hi[a] = sppm_unord(h.hi[a]); }
-    SppmGrid Gg = sppm_make_grid(B.pg[k], B.start_g, B.index_g, h.n_global, lo, hi);
-    SppmGrid Gc = sppm_make_grid(B.pc[k], B.start_c, B.index_c, h.n_caustic, lo, hi);
+    SppmGrid Gg = sppm_make_grid(B.start_g, h.n_global, lo, hi);
+    SppmGrid Gc = sppm_make_grid(B.start_c, h.n_caustic, lo, hi);
     SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
-    if ((rc = sppm_build_grid(ctx, B, Gg, sppm_one_seg(B.pg[k], h.n_global), B.start_g, B.index_g, B.sg)) != 0) return fail2(rc);
-    if ((rc = sppm_build_grid(ctx, B, Gc, sppm_one_seg(B.pc[k], h.n_caustic), B.start_c, B.index_c, B.sc)) != 0) return fail2(rc);
+    if ((rc = sppm_build_grid(ctx, B, Gg, sppm_one_seg(B.pg[k], h.n_global), B.start_g, B.sg)) != 0) return fail2(rc);
+    if ((rc = sppm_build_grid(ctx, B, Gc, sppm_one_seg(B.pc[k], h.n_caustic), B.start_c, B.sc)) != 0) return fail2(rc);
     SPPM_CHECK(cudaEventRecord(ev_grid, q));
     if (it + 1 < sp.iterations) {
       // the next photon pass writes the buffer iteration it - 1 used: its grid build read it and has finished (the host
@@ -184,8 +336,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
       SPPM_CHECK(cudaStreamWaitEvent(qp, ev_grid, 0));
       SPPM_CHECK(launch_photons(it + 1));
     }
-    if (s->dev.has_objf) k_sppm_eye<true><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2, 0u, n_pix);
-    else k_sppm_eye<false><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2, 0u, n_pix);
+    if ((rc = sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, 0u, n_pix)) != 0) return fail2(rc);
     SPPM_CHECK(cudaEventRecord(ev_eye[k], q));
     // the grid tables (cell_count, cursor, start, index, sg, sc) are single-buffered and the stage events are reused:
     // the host lets the eye pass finish before it builds the next grid — the next photon pass is already running

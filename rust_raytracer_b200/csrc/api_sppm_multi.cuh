@@ -85,6 +85,7 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   };
   // ---- set-up: peer mappings, buffers
   bool good = ok(cudaSetDevice(ctx->device), "cudaSetDevice");
+  cudaGetLastError();  // as in b200rt_render_sppm: stale non-sticky errors are not this call's
   for (int h = 0; good && h < G; ++h) {
     const int peer = scenes[h]->ctx->device;
     if (peer == ctx->device) continue;
@@ -99,10 +100,9 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     cudaError_t e = cudaSuccess;
     auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
     for (int k = 0; k < 2; ++k) { alloc((void**)&B.pg[k], (size_t)cap_shard * 64); alloc((void**)&B.pc[k], (size_t)cap_shard * 64); }
-    alloc((void**)&B.sg, (size_t)cap_total * 64); alloc((void**)&B.sc, (size_t)cap_total * 64);
+    if (e == cudaSuccess) e = B.alloc_maps(cap_total, n_pix);
     alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
     alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
-    alloc((void**)&B.index_g, 4 * (size_t)cap_total); alloc((void**)&B.index_c, 4 * (size_t)cap_total);
     alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
     alloc((void**)&B.accum, 16 * (size_t)n_pix);
     alloc((void**)&B.cnt, 3 * sizeof(SppmCounters));
@@ -125,7 +125,10 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   RenderConst Peye = P;
   Peye.key.y ^= 0x5EE05EE0u;  // as in b200rt_render_sppm
   const int sms = ctx->prop.multiProcessorCount;
-  const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8), eye_grid = env_int("B200RT_SPPM_EYE_GRID", 4, 1, 8);
+  const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8);
+  const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;  // as in b200rt_render_sppm
+  SppmPhotonWf PW;
+  if (good && !photons_mega && id_count && sppm_photon_wf_alloc(ctx, s, PW, id_count)) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon queues: " + ctx->err); good = false; }
   auto launch_photons = [&](int it) -> bool {  // on qp, into the buffers of parity it & 1
     const int k = it & 1;
     SppmCounters h0;
@@ -133,7 +136,9 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     for (int a = 0; a < 3; ++a) { h0.lo[a] = 0xffffffffu; h0.hi[a] = 0u; }
     hcnt[k] = h0;
     if (!ok(cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp), "memcpy")) return false;
-    if (id_count) {
+    if (id_count && !photons_mega) {
+      if (sppm_photon_wf_begin(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, qp)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: photon pass: " + ctx->err); return false; }
+    } else if (id_count) {
       if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count);
       else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count);
     }
@@ -145,6 +150,13 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     const int k = it & 1;
     if (good && !sh.failed) {
       good = ok(cudaStreamSynchronize(qp), "photon pass");  // this device's shard of the map is complete, its counters are on the host
+      if (good && id_count && !photons_mega) {  // ... unless a photon walk outlasted the queued wavefront iterations
+        const int launched = PW.launched;
+        unsigned long long rays = 0;
+        if (sppm_photon_wf_finish(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, qp, &rays)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: photon pass: " + ctx->err); good = false; }
+        if (good && PW.launched != launched) good = ok(cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp), "memcpy") && ok(cudaStreamSynchronize(qp), "photon pass");
+        if (good) hcnt[k].photon_rays = rays;
+      }
       if (good && hcnt[k].overflow) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon buffer overflow (more than 16 stored photons per emitted photon)"); good = false; }
       sh.counts[g][k] = hcnt[k];
     }
@@ -164,10 +176,10 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     const uint32_t n_g = seg_g.start[G], n_c = seg_c.start[G];
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
     if (n_g) for (int a = 0; a < 3; ++a) { lo[a] = sppm_unord(lo_u[a]); hi[a] = sppm_unord(hi_u[a]); }
-    SppmGrid Gg = sppm_make_grid(nullptr, B.start_g, B.index_g, n_g, lo, hi);
-    SppmGrid Gc = sppm_make_grid(nullptr, B.start_c, B.index_c, n_c, lo, hi);
+    SppmGrid Gg = sppm_make_grid(B.start_g, n_g, lo, hi);
+    SppmGrid Gc = sppm_make_grid(B.start_c, n_c, lo, hi);
     // counting sort over all shards, peers' read in place over NVLink: the all-gather is this kernel pair's input side
-    if (sppm_build_grid(ctx, B, Gg, seg_g, B.start_g, B.index_g, B.sg) || sppm_build_grid(ctx, B, Gc, seg_c, B.start_c, B.index_c, B.sc)) {
+    if (sppm_build_grid(ctx, B, Gg, seg_g, B.start_g, B.sg) || sppm_build_grid(ctx, B, Gc, seg_c, B.start_c, B.sc)) {
       sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: grid build: " + ctx->err); good = false; continue;
     }
     good = ok(cudaEventRecord(ev_grid, q), "event");
@@ -179,9 +191,7 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     }
     if (good && pix_count) {
       const SppmPixels px = sh.px[g];
-      if (s->dev.has_objf) k_sppm_eye<true><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2, pix_first, pix_count);
-      else k_sppm_eye<false><<<sms * eye_grid, 128, 0, q>>>(s->dev, Peye, sp, it, Gg, Gc, px, B.cnt + 2, pix_first, pix_count);
-      good = ok(cudaGetLastError(), "k_sppm_eye");
+      if (sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, pix_first, pix_count)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: eye pass: " + ctx->err); good = false; }
     }
     // grid tables are single-buffered, and the peers may not overwrite the shards this grid build reads before it is done
     if (good) good = ok(cudaStreamSynchronize(q), "eye pass");
@@ -216,6 +226,7 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   bar.wait();  // C: every accumulation buffer is complete; the root reduces and reads them in b200rt_render_sppm_multi
   bar.wait();  // D: the root is done with the peers' buffers
   if (qp) { cudaStreamSynchronize(qp); cudaStreamDestroy(qp); }
+  PW.release();
   if (ev_grid) cudaEventDestroy(ev_grid);
   if (hcnt) cudaFreeHost(hcnt);
   B.release();

@@ -26,10 +26,10 @@ struct SppmConst {
   double alpha;  // f64: (ALPHA * photons as f64) as usize (photon_mapper.rs:59) truncates, 0.7f * 10 would give 6
   float light_scale;
 };
-struct SppmGrid {  // one photon map
-  const float4* photons;  // 4 x float4 per photon: (pos, 0) (power, 0) (direction, 0) (normal, 0)
+struct SppmGrid {  // one photon map, cell-ordered: what a gather tests (the position) apart from what an accepted photon adds
+  const float4* pos;   // (pos, 0) per photon
+  const float4* attr;  // 2 x float4 per photon: (power, 0) (normal, 0) — the photon's direction is not used by any bsdf here
   const uint32_t* cell_start;  // res^3 + 1
-  const uint32_t* index;       // photon indices sorted by cell
   uint32_t n;
   int res;
   float3 lo;
@@ -53,6 +53,12 @@ struct SppmPixels {
   float4* g;    // global: flux rgb, radius2
   float4* c;    // caustic
   uint2* n;     // photons (global, caustic)
+};
+struct SppmEye {  // what the eye pass hands from its trace kernel to the gather / k-nearest kernels
+  float4* vp;          // per pixel: the visible point (position, 1) or (., 0) when the eye path found no diffuse surface
+  float4* vb;          // per pixel: bsdf at the visible point
+  uint32_t* knn_list;  // (pixel | map << 31) whose statistics are still empty: the k-nearest kernel's work list
+  uint32_t* knn_n;
 };
 struct SppmCounters {
   unsigned int n_global, n_caustic, overflow, cursor;  // cursor: next photon id of the pass (per-lane work fetch)
@@ -249,6 +255,125 @@ __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, 
   if (lane == 0 && n_rays) atomicAdd(&cnt->photon_rays, n_rays);
 }
 
+// ---- the photon pass through the wavefront queues (round 2) --------------------------------------------------------
+// k_sppm_photons above follows one photon per thread through emission, traversal, hit record, texture, scatter and roulette:
+// 150 registers, and its warps spend 5 issue slots waiting for instructions for every one they use (stall no_instruction 5.0
+// per issue, profiles/r1_sppm_photons_refill_full.txt) — divergent lanes walk a code footprint no instruction cache holds.
+// Here the photons ride the path tracer's queues instead: k_sppm_ph_generate emits (AllLights::emit), the SAME k_wf_extend
+// traverses (t_min 0.0001, every hit "goes on" — DiffuseLight scatters photons, material.rs:198-208), and k_sppm_ph_shade
+// streams the queue in order: hit record, scatter_photon with its Russian roulette (material.rs:27-45), photon records
+// appended to the maps, the survivor stored at offset[bin] + rank of the next set (an absorbed photon leaves a dead record).
+// State stream of a photon: (power rgb, flags: 1 = has_specular, 2 = has_diffuse) (photon id, bounce, 0, 0).
+// Every draw is keyed (photon id, iteration, bounce) exactly as in k_sppm_photons: the stored photons are the same set.
+__global__ void __launch_bounds__(256) k_sppm_ph_generate(DevScene S, WfBuffers B, PathMap M, SppmConst sp, uint2 key, int iter, unsigned int id_first) {
+  const unsigned int n_new = wf_new_paths(B.cnt, M, B.pool);
+  const unsigned long long base = B.cnt->next_path;
+  const unsigned int off = B.cnt->n_ext_next;
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_new; i += gridDim.x * blockDim.x) {
+    const uint32_t id = id_first + (uint32_t)(base + i);
+    Ray r;
+    float3 power;
+    sppm_emit(S, sp, philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x50u), key), philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x51u), key), r, power);
+    float4* ray = B.ray + 2 * (size_t)(off + i);
+    float4* st = B.st + 2 * (size_t)(off + i);
+    WF_ST(ray + 0, make_float4(r.o.x, r.o.y, r.o.z, r.time));
+    WF_ST(ray + 1, make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(r.mseed)));
+    WF_ST(st + 0, make_float4(power.x, power.y, power.z, __uint_as_float(0u)));
+    WF_ST(st + 1, make_float4(__uint_as_float(id), __uint_as_float(1u), 0.f, 0.f));
+  }
+}
+// k_wf_control + a log of the queue length per wavefront iteration (the host sizes the next pass's launch count from it)
+__global__ void k_sppm_ph_control(WfBuffers B, PathMap M, unsigned int* n_log, int j) {
+  for (unsigned int k = threadIdx.x; k < B.n_bins; k += blockDim.x) B.bin_count[k] = 0;
+  if (threadIdx.x != 0) return;
+  WfCounters* c = B.cnt;
+  const unsigned int n_new = wf_new_paths(c, M, B.pool);
+  c->next_path += n_new;
+  c->n_ext = c->n_ext_next + n_new;
+  c->n_ext_next = 0;
+  c->ext_cursor = 0;
+  c->extend_rays += c->n_ext;
+  n_log[j] = c->n_ext;
+}
+__global__ void __launch_bounds__(128, 4) k_sppm_ph_shade(DevScene S, WfBuffers B, uint2 key, int iter, float4* pg, float4* pc, unsigned int cap, SppmCounters* cnt) {
+  __shared__ unsigned int s_off[WF_SMEM_BINS + 1];
+  const bool off_in_smem = B.n_bins <= WF_SMEM_BINS;
+  if (off_in_smem) for (unsigned int k = threadIdx.x; k <= B.n_bins; k += blockDim.x) s_off[k] = B.bin_off[k];
+  __syncthreads();
+  const unsigned int n_ext = B.cnt->n_ext;
+  const unsigned int n_work = (n_ext + 31u) & ~31u;  // whole warps stay in the loop (warp-aggregated appends)
+  unsigned int lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
+  for (unsigned int gi = blockIdx.x * blockDim.x + threadIdx.x; gi < n_work; gi += gridDim.x * blockDim.x) {
+    bool st_g = false, st_c = false, alive = false;
+    float3 hp = f3(0, 0, 0), hn = f3(0, 0, 0), hd = f3(0, 0, 0), hpow = f3(0, 0, 0), dir = f3(0, 0, 0), new_power = f3(0, 0, 0);
+    uint32_t id = 0, bounce = 0, flags = 0, next_seed = 0;
+    unsigned int rank = WF_NO_RANK;
+    int hprim = WF_PRIM_DEAD;
+    float time = 0.f;
+    if (gi < n_ext) {
+      const uint4 hh = WF_LD(B.hit + gi);
+      hprim = wf_unpack_prim(hh.z);
+      rank = hh.w;
+      if (hprim >= 0) {
+        const float4 o = WF_LD(B.ray + 2 * (size_t)gi), d = WF_LD(B.ray + 2 * (size_t)gi + 1);
+        const float4 sa = WF_LD(B.st + 2 * (size_t)gi), sb = WF_LD(B.st + 2 * (size_t)gi + 1);
+        Ray ray;
+        ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
+        time = o.w;
+        const float3 power = f3(sa);
+        flags = __float_as_uint(sa.w); id = __float_as_uint(sb.x); bounce = __float_as_uint(sb.y);
+        HitRaw hr;
+        hr.t = __longlong_as_double((long long)(((unsigned long long)hh.y << 32) | hh.x)); hr.prim = hprim; hr.aux = wf_unpack_aux(hh.z);
+        const int4 meta = __ldg(&S.prim_meta[hprim]);
+        const float4 mat = __ldg(&S.materials[meta.x >> 8]);
+        HitInfo h;
+        finish_hit(S, ray, hr, h, texture_needs_uv(S, __float_as_int(mat.y)));
+        const uint4 r = philox4x32(make_uint4(id, (uint32_t)iter, bounce, 0x50u), key);
+        float3 f;
+        int inter = sppm_scatter(S, mat, h, ray, u01(r.x), u01(r.y), u01(r.z), dir, f);
+        new_power = power;
+        if (inter != SPPM_ABSORB) {  // scatter_photon (material.rs:27-45): Russian roulette on max(f)
+          const float hmax = maxcomp(f);
+          if (u01(r.w) > hmax) inter = SPPM_ABSORB;
+          else new_power = power * (f * (1.0f / hmax));
+        }
+        alive = inter != SPPM_ABSORB;
+        if (inter == SPPM_DIFFUSE) {
+          st_g = true; st_c = !(flags & 2u) && (flags & 1u);
+          hp = h.p; hn = h.n; hd = ray.d; hpow = power;
+          flags |= 2u;
+        } else if (inter == SPPM_SPECULAR) flags |= 1u;
+        if (alive && bounce >= SPPM_MAX_BOUNCES) alive = false;  // upstream loops until absorbed or lost; the cap only guards the kernel
+        if (alive && rank != WF_NO_RANK) {  // the next record, at the place extend reserved in the next set
+          next_seed = philox4x32(make_uint4(id, (uint32_t)iter, bounce, 0x51u), key).x;
+          const unsigned int bin = 1u + __umulhi((unsigned int)hprim, B.bin_mul);
+          const size_t dst = 2 * (size_t)((off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank);
+          WF_ST(B.ray_n + dst, make_float4(h.p.x, h.p.y, h.p.z, time));
+          WF_ST(B.ray_n + dst + 1, make_float4(dir.x, dir.y, dir.z, __uint_as_float(next_seed)));
+          WF_ST(B.st_n + dst, make_float4(new_power.x, new_power.y, new_power.z, __uint_as_float(flags)));
+          WF_ST(B.st_n + dst + 1, make_float4(__uint_as_float(id), __uint_as_float(bounce + 1u), 0.f, 0.f));
+        }
+      }
+      if (!alive && rank != WF_NO_RANK && hprim >= 0) {  // predicted to go on, absorbed here: a dead record extend will skip
+        const unsigned int bin = 1u + __umulhi((unsigned int)hprim, B.bin_mul);
+        const size_t dst = 2 * (size_t)((off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank);
+        WF_ST(B.ray_n + dst, make_float4(0.f, 0.f, 0.f, 0.f));
+        WF_ST(B.ray_n + dst + 1, make_float4(0.f, 0.f, 0.f, 0.f));
+      }
+    }
+    sppm_store(pg, &cnt->n_global, cap, &cnt->overflow, st_g, hp, hpow, hd, hn);
+    sppm_store(pc, &cnt->n_caustic, cap, &cnt->overflow, st_c, hp, hpow, hd, hn);
+    if (st_g) {
+      lo[0] = min(lo[0], sppm_ord(hp.x)); lo[1] = min(lo[1], sppm_ord(hp.y)); lo[2] = min(lo[2], sppm_ord(hp.z));
+      hi[0] = max(hi[0], sppm_ord(hp.x)); hi[1] = max(hi[1], sppm_ord(hp.y)); hi[2] = max(hi[2], sppm_ord(hp.z));
+    }
+  }
+  for (int a = 0; a < 3; ++a) {
+    for (int o = 16; o > 0; o >>= 1) { lo[a] = min(lo[a], __shfl_down_sync(0xffffffffu, lo[a], o)); hi[a] = max(hi[a], __shfl_down_sync(0xffffffffu, hi[a], o)); }
+    if ((threadIdx.x & 31) == 0 && lo[a] <= hi[a]) { atomicMin(&cnt->lo[a], lo[a]); atomicMax(&cnt->hi[a], hi[a]); }
+  }
+}
+
 // ---- the photon grid: counting sort by cell ----------------------------------------------------------------------
 DEV int3 sppm_cell_of(float3 p, float3 lo, float inv_cell, int res) {
   return make_int3(min(res - 1, max(0, (int)floorf((p.x - lo.x) * inv_cell))), min(res - 1, max(0, (int)floorf((p.y - lo.y) * inv_cell))),
@@ -315,153 +440,252 @@ __global__ void __launch_bounds__(1024) k_sppm_scan_cells(const uint32_t* __rest
     run += c[k];
   }
 }
-// The photon records themselves are moved into cell order (`sorted`), so that a gather over a cell reads one contiguous
-// run of 64-byte records instead of chasing indices through the emission-ordered array; index[] becomes the identity
-// over the sorted array (the consumers keep their cell_start -> index -> photon walk).
-__global__ void k_sppm_grid_fill(SppmSegs photons, uint32_t n, float3 lo, float inv_cell, int res, uint32_t* cursor, uint32_t* index,
-                                 float4* __restrict__ sorted) {
+// The photon records themselves are moved into cell order, split into what a gather tests (16-byte positions: the run of a
+// grid row is one contiguous read) and what an accepted photon adds (power, normal: one 32-byte sector).
+__global__ void k_sppm_grid_fill(SppmSegs photons, uint32_t n, float3 lo, float inv_cell, int res, uint32_t* cursor, float4* __restrict__ pos_out,
+                                 float4* __restrict__ attr_out) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float4* src = sppm_seg_photon(photons, i);
-    const float4 a = src[0], b = src[1], c = src[2], d = src[3];
-    const uint32_t pos = atomicAdd(&cursor[sppm_cell_id(sppm_cell_of(f3(a), lo, inv_cell, res), res)], 1u);
-    float4* dst = sorted + 4 * (size_t)pos;
-    dst[0] = a; dst[1] = b; dst[2] = c; dst[3] = d;
-    index[pos] = pos;
+    const float4 a = src[0], b = src[1], d = src[3];
+    const uint32_t at = atomicAdd(&cursor[sppm_cell_id(sppm_cell_of(f3(a), lo, inv_cell, res), res)], 1u);
+    pos_out[at] = a;
+    attr_out[2 * (size_t)at] = b; attr_out[2 * (size_t)at + 1] = d;
   }
 }
 
 // ---- SPPM::update (photon_mapper.rs:42-64) over the grid ---------------------------------------------------------
+// The eye pass is three kernels (round 2; the first version followed one pixel per thread through the trace AND both map
+// look-ups: 6.9 active lanes per instruction, 14 % issue-active, the k-nearest of the first iteration alone 45 of 232 ms):
+//   k_sppm_eye_trace : one thread per pixel, the eye ray through the specular chain to its first diffuse hit; stores the visible
+//                      point (position, bsdf) and lists the (pixel, map) pairs whose statistics are still empty
+//   k_sppm_gather    : SPPM_GATHER_LANES lanes per pixel share the radius gather — the cells a pixel's sphere overlaps are
+//                      walked as x-runs (the photons of consecutive cells of one grid row are one contiguous run of the
+//                      cell-ordered array), one run per lane at a time
+//   k_sppm_knn       : one warp per listed (pixel, map): exact k-nearest by growing cubes of cells, the squared distances of
+//                      the cube's photons kept in shared memory, the k-th smallest found by bisection on the float bits
+// Squared distance of a photon, one rounding sequence at every site (the k-nearest kernel compares distances computed in
+// different passes bit for bit).
+DEV float sppm_d2(float4 pos, float3 p) {
+  const float dx = __fsub_rn(pos.x, p.x), dy = __fsub_rn(pos.y, p.y), dz = __fsub_rn(pos.z, p.z);
+  return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+}
 // Vec3::elemul(rec.mat.bsdf(photon.direction, rec), photon.power) * (1 - disk_factor) (photon_mapper.rs:72-74, 90-92)
-DEV float3 sppm_photon_flux(const SppmGrid& G, uint32_t i, float3 p, float3 bsdf) {
-  const float4* ph = G.photons + 4 * (size_t)i;
-  const float3 pos = f3(__ldg(ph)), power = f3(__ldg(ph + 1)), nrm = f3(__ldg(ph + 3));
-  const float3 d = pos - p;
+DEV float3 sppm_photon_flux(const SppmGrid& G, uint32_t i, float4 pos4, float3 p, float3 bsdf) {
+  const float4* at = G.attr + 2 * (size_t)i;
+  const float3 power = f3(__ldg(at)), nrm = f3(__ldg(at + 1));
+  const float3 d = f3(pos4) - p;
   const float disk = fabsf(dot(nrm, d * rsqrtf(dot(d, d))));
   return bsdf * power * (1.0f - disk);
 }
-DEV void sppm_heap_push(float* hd, uint32_t* hi, int& n, int k, float d, uint32_t idx) {
-  if (n < k) {  // sift up
-    int c = n++;
-    while (c > 0) {
-      const int par = (c - 1) >> 1;
-      if (hd[par] >= d) break;
-      hd[c] = hd[par]; hi[c] = hi[par]; c = par;
-    }
-    hd[c] = d; hi[c] = idx;
-  } else if (d < hd[0]) {  // replace the farthest, sift down
-    int c = 0;
-    for (;;) {
-      int l = 2 * c + 1, r = l + 1, m = l;
-      if (l >= n) break;
-      if (r < n && hd[r] > hd[l]) m = r;
-      if (hd[m] <= d) break;
-      hd[c] = hd[m]; hi[c] = hi[m]; c = m;
-    }
-    hd[c] = d; hi[c] = idx;
-  }
-}
-DEV void sppm_visit_cell(const SppmGrid& G, int x, int y, int z, float3 p, float* hd, uint32_t* hi, int& n, int k) {
-  const uint32_t c = sppm_cell_id(make_int3(x, y, z), G.res);
-  for (uint32_t j = __ldg(&G.cell_start[c]), e = __ldg(&G.cell_start[c + 1]); j < e; ++j) {
-    const uint32_t i = __ldg(&G.index[j]);
-    const float3 d = f3(__ldg(G.photons + 4 * (size_t)i)) - p;
-    sppm_heap_push(hd, hi, n, k, dot(d, d), i);
-  }
-}
-// PhotonMap::estimate_flux_by_count (photon_mapper.rs:77-96): the k nearest photons, exactly
-DEV void sppm_estimate_by_count(const SppmGrid& G, float3 p, float3 bsdf, int k, float3& flux, float& radius2) {
-  float hd[SPPM_MAX_K];
-  uint32_t hi[SPPM_MAX_K];
-  int n = 0;
-  flux = f3(0, 0, 0); radius2 = 0.f;
-  if (G.n == 0) return;
-  const int3 c0 = sppm_cell_of(p, G.lo, G.inv_cell, G.res);
-  for (int s = 0; s < G.res; ++s) {  // shell s: cells at Chebyshev distance s from c0
-    const int z0 = max(0, c0.z - s), z1 = min(G.res - 1, c0.z + s), y0 = max(0, c0.y - s), y1 = min(G.res - 1, c0.y + s);
-    for (int z = z0; z <= z1; ++z)
-      for (int y = y0; y <= y1; ++y) {
-        if (abs(z - c0.z) == s || abs(y - c0.y) == s) {
-          for (int x = max(0, c0.x - s); x <= min(G.res - 1, c0.x + s); ++x) sppm_visit_cell(G, x, y, z, p, hd, hi, n, k);
-        } else {
-          if (c0.x - s >= 0) sppm_visit_cell(G, c0.x - s, y, z, p, hd, hi, n, k);
-          if (s > 0 && c0.x + s < G.res) sppm_visit_cell(G, c0.x + s, y, z, p, hd, hi, n, k);
-        }
-      }
-    // every photon not visited yet lies at least s cells away along some axis
-    const float reach = (float)s * G.cell;
-    if (n == k && hd[0] <= reach * reach) break;
-  }
-  for (int j = 0; j < n; ++j) { radius2 = fmaxf(radius2, hd[j]); flux = flux + sppm_photon_flux(G, hi[j], p, bsdf); }
-}
-// PhotonMap::estimate_flux_within_radius (photon_mapper.rs:99-114): squared distance < radius^2
-DEV void sppm_estimate_within(const SppmGrid& G, float3 p, float3 bsdf, float radius2, float3& flux, uint32_t& count) {
-  flux = f3(0, 0, 0); count = 0;
-  if (G.n == 0) return;
-  const float r = sqrtf(radius2);
-  const int3 a = sppm_cell_of(p - f3(r, r, r), G.lo, G.inv_cell, G.res), b = sppm_cell_of(p + f3(r, r, r), G.lo, G.inv_cell, G.res);
-  for (int z = a.z; z <= b.z; ++z)
-    for (int y = a.y; y <= b.y; ++y)
-      for (int x = a.x; x <= b.x; ++x) {
-        const uint32_t c = sppm_cell_id(make_int3(x, y, z), G.res);
-        for (uint32_t j = __ldg(&G.cell_start[c]), e = __ldg(&G.cell_start[c + 1]); j < e; ++j) {
-          const uint32_t i = __ldg(&G.index[j]);
-          const float3 d = f3(__ldg(G.photons + 4 * (size_t)i)) - p;
-          if (dot(d, d) < r * r) { ++count; flux = flux + sppm_photon_flux(G, i, p, bsdf); }
-        }
-      }
-}
-DEV void sppm_update(const SppmGrid& G, float3 p, float3 bsdf, int k_init, double alpha, float4& st, uint32_t& photons) {
-  if (photons == 0) {
-    photons = (uint32_t)k_init;
-    float3 flux; float r2;
-    sppm_estimate_by_count(G, p, bsdf, k_init, flux, r2);
-    st = make_float4(flux.x, flux.y, flux.z, r2);
-  } else {
-    float3 flux; uint32_t m;
-    sppm_estimate_within(G, p, bsdf, st.w, flux, m);
-    const uint32_t prev = photons;
-    photons += (uint32_t)(alpha * (double)m);
-    const float frac = (float)((double)photons / (double)(prev + m));
-    st = make_float4((st.x + flux.x) * frac, (st.y + flux.y) * frac, (st.z + flux.z) * frac, st.w * frac);
-  }
-}
 
-// SPPMIntegrator::update_sppm (photon_mapper.rs:282-305): one jittered eye ray per pixel and iteration
-template <bool OBJF>
+// SPPMIntegrator::update_sppm (photon_mapper.rs:282-305), first half: one jittered eye ray per pixel and iteration
 // [pix_first, pix_first + pix_count): the pixels whose statistics this device owns
-__global__ void __launch_bounds__(128) k_sppm_eye(DevScene S, RenderConst P, SppmConst sp, int iter, SppmGrid Gg, SppmGrid Gc, SppmPixels px, SppmCounters* cnt,
-                                                  uint32_t pix_first, uint32_t pix_count) {
-  const uint32_t n_pix = pix_first + pix_count;
+template <bool OBJF>
+__global__ void __launch_bounds__(128) k_sppm_eye_trace(DevScene S, RenderConst P, int iter, SppmPixels px, SppmEye E, SppmCounters* cnt, uint32_t pix_first, uint32_t pix_count) {
   unsigned long long n_rays = 0;
-  for (uint32_t pixel = pix_first + blockIdx.x * blockDim.x + threadIdx.x; pixel < n_pix; pixel += gridDim.x * blockDim.x) {
-    Ray ray = camera_ray(P, pixel, (uint32_t)iter);
-    for (int bounce = 1; bounce <= SPPM_MAX_BOUNCES; ++bounce) {
-      HitRaw hr;
-      trace<false, OBJF>(S, ray, 0.001f, hr);  // photon_mapper.rs:290
-      n_rays++;
-      if (hr.prim < 0) break;
-      const int4 meta = __ldg(&S.prim_meta[hr.prim]);
-      const float4 mat = __ldg(&S.materials[meta.x >> 8]);
-      HitInfo h;
-      finish_hit(S, ray, hr, h, texture_needs_uv(S, __float_as_int(mat.y)));
-      const uint4 r = philox4x32(make_uint4(pixel, (uint32_t)iter, (uint32_t)bounce, 0x60u), P.key);
-      float3 dir, f;
-      const int inter = sppm_scatter(S, mat, h, ray, u01(r.x), u01(r.y), u01(r.z), dir, f);
-      if (inter == SPPM_DIFFUSE) {
-        const float3 bsdf = sppm_bsdf(S, mat, h);
-        float4 c = px.c[pixel], g = px.g[pixel];
-        uint2 n = px.n[pixel];
-        sppm_update(Gc, h.p, bsdf, sp.k_caustic, sp.alpha, c, n.y);  // caustic first, like upstream
-        sppm_update(Gg, h.p, bsdf, sp.k_global, sp.alpha, g, n.x);
-        px.c[pixel] = c; px.g[pixel] = g; px.n[pixel] = n;
-        break;
+  const uint32_t n_work = (pix_count + 31u) & ~31u;  // whole warps walk the loop (warp-aggregated appends)
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_work; i += gridDim.x * blockDim.x) {
+    const bool active = i < pix_count;
+    const uint32_t pixel = pix_first + i;
+    bool found = false;
+    float3 hp = f3(0, 0, 0), hb = f3(0, 0, 0);
+    if (active) {
+      Ray ray = camera_ray(P, pixel, (uint32_t)iter);
+      for (int bounce = 1; bounce <= SPPM_MAX_BOUNCES; ++bounce) {
+        HitRaw hr;
+        trace<false, OBJF>(S, ray, 0.001f, hr);  // photon_mapper.rs:290
+        n_rays++;
+        if (hr.prim < 0) break;
+        const int4 meta = __ldg(&S.prim_meta[hr.prim]);
+        const float4 mat = __ldg(&S.materials[meta.x >> 8]);
+        HitInfo h;
+        finish_hit(S, ray, hr, h, texture_needs_uv(S, __float_as_int(mat.y)));
+        const uint4 r = philox4x32(make_uint4(pixel, (uint32_t)iter, (uint32_t)bounce, 0x60u), P.key);
+        float3 dir, f;
+        const int inter = sppm_scatter(S, mat, h, ray, u01(r.x), u01(r.y), u01(r.z), dir, f);
+        if (inter == SPPM_DIFFUSE) { found = true; hp = h.p; hb = sppm_bsdf(S, mat, h); break; }
+        if (inter == SPPM_ABSORB) break;
+        ray.o = h.p; ray.d = dir; ray.tmax = __int_as_float(0x7f800000); ray.mseed = r.w;
       }
-      if (inter == SPPM_ABSORB) break;
-      ray.o = h.p; ray.d = dir; ray.tmax = __int_as_float(0x7f800000); ray.mseed = r.w;
+      E.vp[pixel] = make_float4(hp.x, hp.y, hp.z, found ? 1.f : 0.f);
+      if (found) E.vb[pixel] = make_float4(hb.x, hb.y, hb.z, 0.f);
     }
+    uint2 n = make_uint2(1u, 1u);
+    if (found) n = px.n[pixel];
+    const unsigned int at_c = warp_append(E.knn_n, found && n.y == 0u);  // caustic first, like upstream
+    if (found && n.y == 0u) E.knn_list[at_c] = pixel | 0x80000000u;
+    const unsigned int at_g = warp_append(E.knn_n, found && n.x == 0u);
+    if (found && n.x == 0u) E.knn_list[at_g] = pixel;
   }
   for (int o = 16; o > 0; o >>= 1) n_rays += __shfl_down_sync(0xffffffffu, n_rays, o);
   if ((threadIdx.x & 31) == 0 && n_rays) atomicAdd(&cnt->eye_rays, n_rays);
+}
+
+// PhotonMap::estimate_flux_within_radius (photon_mapper.rs:99-114: squared distance < radius^2) + SPPM::update (49-64),
+// SPPM_GATHER_LANES lanes per pixel.  Lane l takes the grid rows l, l + LANES, ... of the cell box the sphere overlaps; the
+// photons of one row's cells [a.x, b.x] are the contiguous run cell_start[row + a.x] .. cell_start[row + b.x + 1].
+#ifndef SPPM_GATHER_LANES
+#define SPPM_GATHER_LANES 8
+#endif
+DEV void sppm_gather_map(const SppmGrid& G, bool on, float3 p, float3 bsdf, float radius2, unsigned sub, float3& flux, uint32_t& count) {
+  flux = f3(0, 0, 0); count = 0;
+  const float r = sqrtf(radius2), rr = r * r;
+  const int3 a = sppm_cell_of(p - f3(r, r, r), G.lo, G.inv_cell, G.res), b = sppm_cell_of(p + f3(r, r, r), G.lo, G.inv_cell, G.res);
+  const int ny = b.y - a.y + 1, rows = (on && G.n != 0) ? ny * (b.z - a.z + 1) : 0;  // the shuffles below are reached by every lane
+  for (int row = (int)sub; row < rows; row += SPPM_GATHER_LANES) {
+    const int z = a.z + row / ny, y = a.y + row % ny;
+    const uint32_t base = (uint32_t)((z * G.res + y) * G.res);
+    const uint32_t j1 = __ldg(&G.cell_start[base + (uint32_t)b.x + 1u]);
+    for (uint32_t j = __ldg(&G.cell_start[base + (uint32_t)a.x]); j < j1; ++j) {
+      const float4 pos = __ldg(G.pos + j);
+      if (sppm_d2(pos, p) < rr) { ++count; flux = flux + sppm_photon_flux(G, j, pos, p, bsdf); }
+    }
+  }
+#pragma unroll
+  for (int o = SPPM_GATHER_LANES / 2; o > 0; o >>= 1) {
+    flux.x += __shfl_xor_sync(0xffffffffu, flux.x, o); flux.y += __shfl_xor_sync(0xffffffffu, flux.y, o); flux.z += __shfl_xor_sync(0xffffffffu, flux.z, o);
+    count += __shfl_xor_sync(0xffffffffu, count, o);
+  }
+}
+DEV void sppm_update_gathered(float3 flux, uint32_t m, double alpha, float4& st, uint32_t& photons) {  // photon_mapper.rs:55-63
+  const uint32_t prev = photons;
+  photons += (uint32_t)(alpha * (double)m);
+  const float frac = (float)((double)photons / (double)(prev + m));
+  st = make_float4((st.x + flux.x) * frac, (st.y + flux.y) * frac, (st.z + flux.z) * frac, st.w * frac);
+}
+__global__ void __launch_bounds__(256) k_sppm_gather(SppmGrid Gg, SppmGrid Gc, SppmPixels px, SppmEye E, double alpha, uint32_t pix_first, uint32_t pix_count) {
+  const unsigned sub = threadIdx.x % SPPM_GATHER_LANES;
+  const uint32_t per_pass = gridDim.x * blockDim.x / SPPM_GATHER_LANES;
+  const uint32_t n_work = (pix_count + (32u / SPPM_GATHER_LANES) - 1u) / (32u / SPPM_GATHER_LANES) * (32u / SPPM_GATHER_LANES);  // whole warps (shuffles)
+  for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) / SPPM_GATHER_LANES; i < n_work; i += per_pass) {
+    const uint32_t pixel = pix_first + i;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < pix_count) v = __ldg(&E.vp[pixel]);
+    const bool valid = v.w != 0.f;  // uniform over the pixel's lanes
+    uint2 n = make_uint2(0u, 0u);
+    float3 bsdf = f3(0, 0, 0);
+    if (valid) { n = px.n[pixel]; bsdf = f3(__ldg(&E.vb[pixel])); }
+    const float3 p = f3(v);
+    // a map whose statistics are still empty (n == 0) is the k-nearest kernel's; the shuffles below are reached by all lanes
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f), g = c;
+    if (valid && n.y) c = px.c[pixel];
+    if (valid && n.x) g = px.g[pixel];
+    float3 fc, fg;
+    uint32_t mc, mg;
+    sppm_gather_map(Gc, valid && n.y != 0u, p, bsdf, c.w, sub, fc, mc);
+    sppm_gather_map(Gg, valid && n.x != 0u, p, bsdf, g.w, sub, fg, mg);
+    if (sub == 0 && valid) {
+      if (n.y) { sppm_update_gathered(fc, mc, alpha, c, n.y); px.c[pixel] = c; reinterpret_cast<uint32_t*>(&px.n[pixel])[1] = n.y; }
+      if (n.x) { sppm_update_gathered(fg, mg, alpha, g, n.x); px.g[pixel] = g; reinterpret_cast<uint32_t*>(&px.n[pixel])[0] = n.x; }
+    }
+  }
+}
+
+// PhotonMap::estimate_flux_by_count (photon_mapper.rs:77-96): the k nearest photons, exactly — one warp per (pixel, map).
+// Cube s = the cells within Chebyshev distance s of the point's cell; every photon outside it lies more than s cells away
+// along some axis.  The warp grows s until k photons lie within s cells of the point, keeping the squared distances of the
+// cube's photons in shared memory (a cube that holds more than SPPM_KNN_CAP photons is re-read from the grid instead), finds
+// the k-th smallest by bisection on the float bits, and adds up the flux of the photons up to that distance: what
+// kd_tree.nearests(k) returns, its largest squared distance being the initial radius^2 (photon_mapper.rs:80-95).
+#define SPPM_KNN_CAP 2048
+struct SppmCube { int x0, x1, y0, y1, z0, z1; };
+DEV SppmCube sppm_cube(const SppmGrid& G, int3 c0, int s) {
+  SppmCube q;
+  q.x0 = max(0, c0.x - s); q.x1 = min(G.res - 1, c0.x + s); q.y0 = max(0, c0.y - s); q.y1 = min(G.res - 1, c0.y + s);
+  q.z0 = max(0, c0.z - s); q.z1 = min(G.res - 1, c0.z + s);
+  return q;
+}
+template <class F>
+DEV void sppm_for_each_in_cube(const SppmGrid& G, const SppmCube& q, unsigned lane, F f) {  // rows of the cube over the lanes of the warp
+  const int ny = q.y1 - q.y0 + 1, rows = ny * (q.z1 - q.z0 + 1);
+  for (int row = (int)lane; row < rows; row += 32) {
+    const int z = q.z0 + row / ny, y = q.y0 + row % ny;
+    const uint32_t base = (uint32_t)((z * G.res + y) * G.res);
+    const uint32_t j1 = __ldg(&G.cell_start[base + (uint32_t)q.x1 + 1u]);
+    for (uint32_t j = __ldg(&G.cell_start[base + (uint32_t)q.x0]); j < j1; ++j) f(j, __ldg(G.pos + j));
+  }
+}
+DEV uint32_t sppm_warp_sum(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__global__ void __launch_bounds__(128) k_sppm_knn(SppmGrid Gg, SppmGrid Gc, SppmPixels px, SppmEye E, int k_global, int k_caustic) {
+  __shared__ uint32_t s_keys[4][SPPM_KNN_CAP];
+  const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t n_list = *E.knn_n;
+  uint32_t* keys = s_keys[w];
+  for (uint32_t e = blockIdx.x * 4u + w; e < n_list; e += gridDim.x * 4u) {
+    const uint32_t entry = E.knn_list[e], pixel = entry & 0x7fffffffu;
+    const bool caustic = (entry >> 31) != 0u;
+    const SppmGrid G = caustic ? Gc : Gg;
+    const uint32_t k = (uint32_t)(caustic ? k_caustic : k_global);
+    const float3 p = f3(__ldg(&E.vp[pixel])), bsdf = f3(__ldg(&E.vb[pixel]));
+    float3 flux = f3(0, 0, 0);
+    uint32_t tau = 0u;  // bits of the k-th smallest squared distance (non-negative floats order like their bits)
+    if (G.n != 0) {
+      const int3 c0 = sppm_cell_of(p, G.lo, G.inv_cell, G.res);
+      SppmCube q;
+      uint32_t n_in = 0, hi_key = 0x7f800000u;
+      bool in_smem = false;
+      for (int s = 0;; ++s) {
+        q = sppm_cube(G, c0, s);
+        const bool whole = q.x0 == 0 && q.y0 == 0 && q.z0 == 0 && q.x1 == G.res - 1 && q.y1 == G.res - 1 && q.z1 == G.res - 1;
+        // photons in the cube, from the cell table alone (no photon is touched while the cube holds fewer than k)
+        const int ny = q.y1 - q.y0 + 1, rows = ny * (q.z1 - q.z0 + 1);
+        uint32_t mine = 0;
+        for (int row = (int)lane; row < rows; row += 32) {
+          const uint32_t base = (uint32_t)(((q.z0 + row / ny) * G.res + q.y0 + row % ny) * G.res);
+          mine += __ldg(&G.cell_start[base + (uint32_t)q.x1 + 1u]) - __ldg(&G.cell_start[base + (uint32_t)q.x0]);
+        }
+        uint32_t incl = mine;  // this lane's place in the key buffer: exclusive scan over the lanes
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += o; }
+        n_in = __shfl_sync(0xffffffffu, incl, 31);
+        if (n_in < k && !whole) continue;
+        in_smem = n_in <= SPPM_KNN_CAP;
+        __syncwarp();
+        if (in_smem) {
+          uint32_t at = incl - mine;
+          sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { keys[at++] = __float_as_uint(sppm_d2(pos, p)); });
+        }
+        __syncwarp();
+        if (n_in >= k) {  // are k of them within s cells (the distance no unvisited photon can undercut)?
+          const float reach = (float)s * G.cell;
+          const uint32_t reach_key = __float_as_uint(reach * reach);
+          uint32_t c = 0;
+          if (in_smem) { for (uint32_t i = lane; i < n_in; i += 32) c += keys[i] <= reach_key ? 1u : 0u; }
+          else sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { c += __float_as_uint(sppm_d2(pos, p)) <= reach_key ? 1u : 0u; });
+          c = sppm_warp_sum(c);
+          if (c >= k) { hi_key = reach_key; break; }
+        }
+        if (whole) break;  // the cube is the whole grid: every photon has been seen
+      }
+      // smallest tau with #{d2 <= tau} >= min(k, n_in)
+      const uint32_t want = n_in < k ? n_in : k;
+      uint32_t lo_key = 0u;
+      while (lo_key < hi_key) {
+        const uint32_t mid = lo_key + ((hi_key - lo_key) >> 1);
+        uint32_t c = 0;
+        if (in_smem) { for (uint32_t i = lane; i < n_in; i += 32) c += keys[i] <= mid ? 1u : 0u; }
+        else sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { c += __float_as_uint(sppm_d2(pos, p)) <= mid ? 1u : 0u; });
+        c = sppm_warp_sum(c);
+        if (c >= want) hi_key = mid; else lo_key = mid + 1u;
+      }
+      tau = lo_key;
+      sppm_for_each_in_cube(G, q, lane, [&](uint32_t j, float4 pos) {
+        if (__float_as_uint(sppm_d2(pos, p)) <= tau) flux = flux + sppm_photon_flux(G, j, pos, p, bsdf);
+      });
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { flux.x += __shfl_xor_sync(0xffffffffu, flux.x, o); flux.y += __shfl_xor_sync(0xffffffffu, flux.y, o); flux.z += __shfl_xor_sync(0xffffffffu, flux.z, o); }
+      __syncwarp();
+    }
+    if (lane == 0) {  // SPPM::update, first time (photon_mapper.rs:50-54)
+      const float4 st = make_float4(flux.x, flux.y, flux.z, __uint_as_float(tau));
+      if (caustic) { px.c[pixel] = st; reinterpret_cast<uint32_t*>(&px.n[pixel])[1] = k; }
+      else { px.g[pixel] = st; reinterpret_cast<uint32_t*>(&px.n[pixel])[0] = k; }
+    }
+  }
 }
 
 // impl Integrator for SPPMIntegrator (photon_mapper.rs:327-365) under Camera::capture_image
