@@ -6,8 +6,10 @@
 
 namespace {
 
+#define SPPM_MAX_NB 8  // photon buffers per call: passes in flight + 1
+
 struct SppmBuffers {
-  float4 *pg[2] = {nullptr, nullptr}, *pc[2] = {nullptr, nullptr};  // photons in emission order, double-buffered over the iterations
+  float4 *pg[SPPM_MAX_NB] = {}, *pc[SPPM_MAX_NB] = {};  // photons in emission order, one pair per photon pass in flight (+ the one being sorted)
   float4 *sg = nullptr, *sc = nullptr;  // photons in cell order: `sorted_cap` positions, then 2 x `sorted_cap` attribute rows
   size_t sorted_cap = 0;
   uint32_t *tile_sum = nullptr, *cell_count = nullptr, *start_g = nullptr, *start_c = nullptr, *cursor = nullptr;
@@ -29,7 +31,8 @@ struct SppmBuffers {
   }
   SppmEye eye() const { return SppmEye{vp, vb, knn_list, knn_n}; }
   void release() {
-    void* all[] = {pg[0], pg[1], pc[0], pc[1], sg, sc, tile_sum, cell_count, start_g, start_c, cursor, px_g, px_c, px_n, vp, vb, knn_list, knn_n, cnt, accum};
+    for (int k = 0; k < SPPM_MAX_NB; ++k) { if (pg[k]) cudaFree(pg[k]); if (pc[k]) cudaFree(pc[k]); }
+    void* all[] = {sg, sc, tile_sum, cell_count, start_g, start_c, cursor, px_g, px_c, px_n, vp, vb, knn_list, knn_n, cnt, accum};
     for (void* p : all) if (p) cudaFree(p);
   }
 };
@@ -78,15 +81,15 @@ int sppm_build_grid(b200rt_ctx* ctx, SppmBuffers& B, SppmGrid& G, const SppmSegs
 // SPPMIntegrator::update_sppm for the pixels [pix_first, pix_first + pix_count) on the context stream: the eye rays to their
 // visible points, the radius gather for the pixels that have statistics, the k-nearest start for those that do not
 int sppm_eye_pass(b200rt_ctx* ctx, const b200rt_scene* s, const RenderConst& Peye, const SppmConst& sp, int it, const SppmGrid& Gg, const SppmGrid& Gc,
-                  const SppmPixels& px, SppmBuffers& B, uint32_t pix_first, uint32_t pix_count) {
+                  const SppmPixels& px, SppmBuffers& B, SppmCounters* eye_cnt, uint32_t pix_first, uint32_t pix_count) {
   cudaStream_t q = ctx->stream;
   const int sms = ctx->prop.multiProcessorCount;
   const SppmEye E = B.eye();
   if (pix_count == 0) return B200RT_OK;
   CU_CHECK(ctx, cudaMemsetAsync(B.knn_n, 0, 4, q));
   const int trace_blocks = (int)std::min<uint32_t>((pix_count + 127u) / 128u, (uint32_t)sms * 8u);
-  if (s->dev.has_objf) k_sppm_eye_trace<true><<<trace_blocks, 128, 0, q>>>(s->dev, Peye, it, px, E, B.cnt + 2, pix_first, pix_count);
-  else k_sppm_eye_trace<false><<<trace_blocks, 128, 0, q>>>(s->dev, Peye, it, px, E, B.cnt + 2, pix_first, pix_count);
+  if (s->dev.has_objf) k_sppm_eye_trace<true><<<trace_blocks, 128, 0, q>>>(s->dev, Peye, it, px, E, eye_cnt, pix_first, pix_count);
+  else k_sppm_eye_trace<false><<<trace_blocks, 128, 0, q>>>(s->dev, Peye, it, px, E, eye_cnt, pix_first, pix_count);
   const uint32_t gather_threads = pix_count * SPPM_GATHER_LANES;
   const int gather_blocks = (int)std::min<uint32_t>((gather_threads + 255u) / 256u, (uint32_t)sms * 32u);
   k_sppm_gather<<<gather_blocks, 256, 0, q>>>(Gg, Gc, px, E, sp.alpha, pix_first, pix_count);
@@ -106,7 +109,7 @@ struct SppmPhotonWf {
   unsigned int* n_log = nullptr;  // device: rays in the queue per wavefront iteration
   unsigned int* n_log_host = nullptr;  // pinned
   int launched = 0;   // wavefront iterations queued for the current pass
-  int plan = 40;      // wavefront iterations to queue before looking at the counters (adapted from the last pass)
+  int plan = 12;      // wavefront iterations per pass before the tail kernel (adapted from the last pass's queue lengths)
   int grid_ext = 0, grid_shade = 0, sms = 0;
   bool objf = false;
   static const int MAX_ITERS = 4096;
@@ -144,15 +147,21 @@ int sppm_photon_wf_alloc(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W
   CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_sppm_ph_shade, 128, 0));
   W.grid_ext = W.sms * (occ_ext > 0 ? occ_ext : 1);
   W.grid_shade = W.sms * (occ_shade > 0 ? occ_shade : 1);
-  W.plan = env_int("B200RT_SPPM_PHOTON_ITERS", 40, 1, SppmPhotonWf::MAX_ITERS);
+  W.plan = env_int("B200RT_SPPM_PHOTON_ITERS", 12, 1, SppmPhotonWf::MAX_ITERS);
   return B200RT_OK;
 }
 
-// `n` more wavefront iterations of the current pass on `qp`, then the read-back of the queue counters
-int sppm_photon_wf_enqueue(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, const SppmConst& sp, uint2 key, int it, float4* pg, float4* pc, unsigned int cap,
-                           SppmCounters* cnt_dev, unsigned int id_first, int n, cudaStream_t qp) {
-  for (int b = 0; b < n && W.launched < SppmPhotonWf::MAX_ITERS; ++b, ++W.launched) {
-    const int j = W.launched;
+// One photon pass on `qp`: `W.plan` wavefront iterations carry the bulk of the photons (the queue shrinks by a third per bounce),
+// then ONE launch of the per-thread walk finishes whatever the queue still holds.  The tail is what a photon pass cannot
+// shorten: a photon caught inside the glass sphere by total internal reflection survives every roulette (max f = 1,
+// material.rs:27-45) and bounces hundreds of times, one dependent traversal after the other — as queue iterations that is
+// hundreds of near-empty launches (measured: 500 per pass, 17-30 ms), as one thread's loop a few ms that the NEXT passes'
+// bulk overlaps (the host keeps several passes in flight on their own streams).  No host round trip inside a pass.
+int sppm_photon_wf_begin(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, const SppmConst& sp, uint2 key, int it, float4* pg, float4* pc, unsigned int cap,
+                         SppmCounters* cnt_dev, unsigned int id_first, cudaStream_t qp) {
+  CU_CHECK(ctx, cudaMemsetAsync(W.B.cnt, 0, sizeof(WfCounters), qp));
+  W.launched = 0;
+  for (int j = 0; j < W.plan; ++j, ++W.launched) {
     std::swap(W.B.ray, W.B.ray_n);
     std::swap(W.B.st, W.B.st_n);
     // launch sizes follow the queue: it shrinks geometrically (a bound, not a promise: the kernels are persistent / grid-stride)
@@ -166,33 +175,23 @@ int sppm_photon_wf_enqueue(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf&
     k_wf_control_shade<<<1, WF_CTRL_THREADS, 0, qp>>>(W.B);
     k_sppm_ph_shade<<<g_shade, 128, 0, qp>>>(s->dev, W.B, key, it, pg, pc, cap, cnt_dev);
   }
+  // the survivors of the last shade pass sit in the next set
+  if (W.objf) k_sppm_photons<true><<<W.sms, 128, 0, qp>>>(s->dev, sp, key, it, pg, pc, cap, cnt_dev, 0u, 0u, W.B.ray_n, W.B.st_n, &W.B.cnt->n_ext_next);
+  else k_sppm_photons<false><<<W.sms, 128, 0, qp>>>(s->dev, sp, key, it, pg, pc, cap, cnt_dev, 0u, 0u, W.B.ray_n, W.B.st_n, &W.B.cnt->n_ext_next);
   CU_CHECK(ctx, cudaGetLastError());
   CU_CHECK(ctx, cudaMemcpyAsync(W.host, W.B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, qp));
   CU_CHECK(ctx, cudaMemcpyAsync(W.n_log_host, W.n_log, 4 * (size_t)W.launched, cudaMemcpyDeviceToHost, qp));
   return B200RT_OK;
 }
-int sppm_photon_wf_begin(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, const SppmConst& sp, uint2 key, int it, float4* pg, float4* pc, unsigned int cap,
-                         SppmCounters* cnt_dev, unsigned int id_first, cudaStream_t qp) {
-  CU_CHECK(ctx, cudaMemsetAsync(W.B.cnt, 0, sizeof(WfCounters), qp));
-  W.launched = 0;
-  return sppm_photon_wf_enqueue(ctx, s, W, sp, key, it, pg, pc, cap, cnt_dev, id_first, W.plan, qp);
-}
-// after cudaStreamSynchronize(qp): has the queue drained?  If not, more iterations (the rare long photon walks), blocking.
-// Returns the rays traced by the pass in *photon_rays.
-int sppm_photon_wf_finish(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, const SppmConst& sp, uint2 key, int it, float4* pg, float4* pc, unsigned int cap,
-                          SppmCounters* cnt_dev, unsigned int id_first, cudaStream_t qp, unsigned long long* photon_rays) {
-  while (W.host->n_ext_next != 0 || W.host->next_path < W.M.total) {
-    if (W.launched >= SppmPhotonWf::MAX_ITERS) { ctx->err = "sppm: a photon walk exceeded the wavefront iteration budget"; return B200RT_ERR_CUDA; }
-    const int rc = sppm_photon_wf_enqueue(ctx, s, W, sp, key, it, pg, pc, cap, cnt_dev, id_first, 8, qp);
-    if (rc) return rc;
-    CU_CHECK(ctx, cudaStreamSynchronize(qp));
-  }
-  // the SPPM iteration counter's photon_rays also needs the counters of the pass; extend counts dead records, not rays
-  *photon_rays = W.host->extend_rays - W.host->dead_rays;
+// after cudaStreamSynchronize(qp) and the read-back of *cnt_host: the rays of the pass (queue iterations + tail), and the
+// number of queue iterations the next pass gets — up to where the queue fell below SPPM_TAIL_RAYS
+#define SPPM_TAIL_RAYS 2048u
+void sppm_photon_wf_finish(SppmPhotonWf& W, SppmCounters* cnt_host) {
+  cnt_host->photon_rays += W.host->extend_rays - W.host->dead_rays;  // extend counts dead records as well
+  if (std::getenv("B200RT_SPPM_PHOTON_ITERS")) return;
   int used = 0;
-  while (used < W.launched && W.n_log_host[used] != 0u) ++used;  // iterations that held rays
-  if (!std::getenv("B200RT_SPPM_PHOTON_ITERS")) W.plan = std::min(std::max(used + 4, 8), (int)SppmPhotonWf::MAX_ITERS);
-  return B200RT_OK;
+  while (used < W.launched && W.n_log_host[used] >= SPPM_TAIL_RAYS) ++used;
+  W.plan = std::min(std::max(used == W.launched ? used + 4 : used, 2), 64);
 }
 
 }  // namespace
@@ -218,13 +217,18 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   SppmBuffers B;
   cudaError_t e = cudaSuccess;
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
-  for (int k = 0; k < 2; ++k) { alloc((void**)&B.pg[k], (size_t)cap * 64); alloc((void**)&B.pc[k], (size_t)cap * 64); }
+  // Photon passes in flight: a pass ends in a tail of a few photons that bounce hundreds of times (one dependent traversal after
+  // the other: ms), and no pass depends on the pixel statistics (photon_mapper.rs:154-160) — so several run ahead of the eye pass,
+  // each on its own stream with its own queues and buffers, and the tail of one hides under the bulk of the next.
+  const int inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 3, 1, SPPM_MAX_NB - 1), sppm->iterations);
+  const int NB = inflight + 1;
+  for (int k = 0; k < NB; ++k) { alloc((void**)&B.pg[k], (size_t)cap * 64); alloc((void**)&B.pc[k], (size_t)cap * 64); }
   if (e == cudaSuccess) e = B.alloc_maps(cap, n_pix);
   alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
   alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
   alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
   alloc((void**)&B.accum, 16 * (size_t)n_pix);
-  alloc((void**)&B.cnt, 3 * sizeof(SppmCounters));  // [0], [1]: the photon pass of even / odd iterations; [2]: eye + final pass
+  alloc((void**)&B.cnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters));  // [k < NB]: the photon pass into buffer k; [SPPM_MAX_NB]: eye + final pass
   if (e != cudaSuccess) { B.release(); ctx->err = std::string("sppm: ") + cudaGetErrorString(e); return B200RT_ERR_NOMEM; }
   auto fail = [&](int code) { B.release(); return code; };
 #define SPPM_CHECK(call)                                                                          \
@@ -257,18 +261,20 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8);
   // photon pass: through the wavefront queues (default), or the one-thread-per-photon kernel of round 1 (A/B)
   const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;
-  SppmPhotonWf PW;
+  SppmPhotonWf PW[SPPM_MAX_NB];
   const bool trace = env_int("B200RT_SPPM_TRACE", 0, 0, 1) != 0;
-  cudaStream_t qp = nullptr;
-  cudaEvent_t ev_ph[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}, ev_eye[2] = {nullptr, nullptr}, ev_grid = nullptr;  // timing only
-  SppmCounters* hcnt = nullptr;  // pinned: [0], [1] photon counters, [2] eye counters
+  cudaStream_t qp[SPPM_MAX_NB] = {};
+  cudaEvent_t ev_ph[SPPM_MAX_NB][2] = {}, ev_eye = nullptr, ev_grid = nullptr;  // ev_ph, ev_eye: timing only
+  SppmCounters* hcnt = nullptr;  // pinned: [k < NB] photon counters, [SPPM_MAX_NB] eye counters
+  const int EYE = SPPM_MAX_NB;
   auto fail2 = [&](int code) {
-    if (qp) { cudaStreamSynchronize(qp); cudaStreamDestroy(qp); }
+    for (int k = 0; k < SPPM_MAX_NB; ++k) if (qp[k]) { cudaStreamSynchronize(qp[k]); cudaStreamDestroy(qp[k]); }
     cudaStreamSynchronize(q);
-    for (int a = 0; a < 2; ++a) { for (int b = 0; b < 2; ++b) if (ev_ph[a][b]) cudaEventDestroy(ev_ph[a][b]); if (ev_eye[a]) cudaEventDestroy(ev_eye[a]); }
+    for (int a = 0; a < SPPM_MAX_NB; ++a) for (int b = 0; b < 2; ++b) if (ev_ph[a][b]) cudaEventDestroy(ev_ph[a][b]);
+    if (ev_eye) cudaEventDestroy(ev_eye);
     if (ev_grid) cudaEventDestroy(ev_grid);
     if (hcnt) cudaFreeHost(hcnt);
-    PW.release();
+    for (int k = 0; k < SPPM_MAX_NB; ++k) PW[k].release();
     return fail(code);
   };
 #undef SPPM_CHECK
@@ -277,45 +283,42 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     cudaError_t e_ = (call);                                                                      \
     if (e_ != cudaSuccess) { ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail2(B200RT_ERR_CUDA); } \
   } while (0)
-  SPPM_CHECK(cudaStreamCreateWithFlags(&qp, cudaStreamNonBlocking));
-  for (int a = 0; a < 2; ++a) { for (int b = 0; b < 2; ++b) SPPM_CHECK(cudaEventCreate(&ev_ph[a][b])); SPPM_CHECK(cudaEventCreate(&ev_eye[a])); }
+  for (int k = 0; k < NB; ++k) {
+    SPPM_CHECK(cudaStreamCreateWithFlags(&qp[k], cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) SPPM_CHECK(cudaEventCreate(&ev_ph[k][b]));
+    if (!photons_mega && (rc = sppm_photon_wf_alloc(ctx, s, PW[k], (unsigned int)sp.photons_per_iter)) != 0) return fail2(rc);
+  }
+  SPPM_CHECK(cudaEventCreate(&ev_eye));
   SPPM_CHECK(cudaEventCreate(&ev_grid));
-  SPPM_CHECK(cudaMallocHost(&hcnt, 3 * sizeof(SppmCounters)));
-  std::memset(hcnt, 0, 3 * sizeof(SppmCounters));
-  if (!photons_mega && (rc = sppm_photon_wf_alloc(ctx, s, PW, (unsigned int)sp.photons_per_iter)) != 0) return fail2(rc);
-  SPPM_CHECK(cudaMemsetAsync(B.cnt + 2, 0, sizeof(SppmCounters), q));
+  SPPM_CHECK(cudaMallocHost(&hcnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters)));
+  std::memset(hcnt, 0, (SPPM_MAX_NB + 1) * sizeof(SppmCounters));
+  SPPM_CHECK(cudaMemsetAsync(B.cnt + EYE, 0, sizeof(SppmCounters), q));
   SPPM_CHECK(cudaEventRecord(ctx->ev[0], q));
-  SPPM_CHECK(cudaStreamWaitEvent(qp, ctx->ev[0], 0));
-  auto launch_photons = [&](int it) -> cudaError_t {  // on qp, into buffer it & 1
-    const int k = it & 1;
+  for (int k = 0; k < NB; ++k) SPPM_CHECK(cudaStreamWaitEvent(qp[k], ctx->ev[0], 0));
+  auto launch_photons = [&](int it) -> cudaError_t {  // on stream / into buffer it % NB
+    const int k = it % NB;
     SppmCounters h0;
     std::memset(&h0, 0, sizeof(h0));
     for (int a = 0; a < 3; ++a) { h0.lo[a] = 0xffffffffu; h0.hi[a] = 0u; }
     hcnt[k] = h0;
-    cudaError_t e = cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp);
-    if (e == cudaSuccess) e = cudaEventRecord(ev_ph[k][0], qp);
+    cudaError_t e = cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp[k]);
+    if (e == cudaSuccess) e = cudaEventRecord(ev_ph[k][0], qp[k]);
     if (e != cudaSuccess) return e;
     if (!photons_mega) {
-      if (sppm_photon_wf_begin(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, qp)) return cudaErrorUnknown;
-    } else if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter);
-    else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter);
-    e = cudaEventRecord(ev_ph[k][1], qp);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp);
+      if (sppm_photon_wf_begin(ctx, s, PW[k], sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, qp[k])) return cudaErrorUnknown;
+    } else if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp[k]>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter, nullptr, nullptr, nullptr);
+    else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp[k]>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, (unsigned int)sp.photons_per_iter, nullptr, nullptr, nullptr);
+    e = cudaEventRecord(ev_ph[k][1], qp[k]);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp[k]);
     return e;
   };
-  SPPM_CHECK(launch_photons(0));
+  for (int it = 0; it < inflight && it < sp.iterations; ++it) SPPM_CHECK(launch_photons(it));
   for (int it = 0; it < sp.iterations; ++it) {
-    const int k = it & 1;
-    SPPM_CHECK(cudaStreamSynchronize(qp));  // photon map of this iteration is complete, its counters are on the host
-    if (!photons_mega) {  // ... unless a photon walk outlasted the queued wavefront iterations (then: more of them, and the counters again)
-      const int launched = PW.launched;
-      unsigned long long rays = 0;
-      if ((rc = sppm_photon_wf_finish(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap, B.cnt + k, 0u, qp, &rays)) != 0) return fail2(rc);
-      if (PW.launched != launched) {
-        SPPM_CHECK(cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp));
-        SPPM_CHECK(cudaStreamSynchronize(qp));
-      }
-      hcnt[k].photon_rays = rays;
+    const int k = it % NB;
+    SPPM_CHECK(cudaStreamSynchronize(qp[k]));  // photon map of this iteration is complete, its counters are on the host
+    if (!photons_mega) {
+      sppm_photon_wf_finish(PW[k], hcnt + k);
+      for (int j = 0; j < NB; ++j) PW[j].plan = PW[k].plan;  // every later pass: queue iterations up to where this one's queue ran low
     }
     const SppmCounters h = hcnt[k];
     if (cudaEventElapsedTime(&ms, ev_ph[k][0], ev_ph[k][1]) == cudaSuccess) local.ms_photons += ms;
@@ -328,23 +331,24 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     if ((rc = sppm_build_grid(ctx, B, Gg, sppm_one_seg(B.pg[k], h.n_global), B.start_g, B.sg)) != 0) return fail2(rc);
     if ((rc = sppm_build_grid(ctx, B, Gc, sppm_one_seg(B.pc[k], h.n_caustic), B.start_c, B.sc)) != 0) return fail2(rc);
     SPPM_CHECK(cudaEventRecord(ev_grid, q));
-    if (it + 1 < sp.iterations) {
-      // the next photon pass writes the buffer iteration it - 1 used: its grid build read it and has finished (the host
+    if (it + inflight < sp.iterations) {
+      // pass it + inflight writes the buffer iteration it - 1 used: its grid build read it and has finished (the host
       // synchronised the context stream at the end of that iteration).  It starts after THIS iteration's grid build:
       // launched earlier, its blocks fill every SM while the dozen small grid kernels are still trickling through their
       // stream, and each of those then waits for photon blocks to retire (grid 0.96 ms instead of 0.10 ms per iteration)
-      SPPM_CHECK(cudaStreamWaitEvent(qp, ev_grid, 0));
-      SPPM_CHECK(launch_photons(it + 1));
+      SPPM_CHECK(cudaStreamWaitEvent(qp[(it + inflight) % NB], ev_grid, 0));
+      SPPM_CHECK(launch_photons(it + inflight));
     }
-    if ((rc = sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, 0u, n_pix)) != 0) return fail2(rc);
-    SPPM_CHECK(cudaEventRecord(ev_eye[k], q));
-    // the grid tables (cell_count, cursor, start, index, sg, sc) are single-buffered and the stage events are reused:
-    // the host lets the eye pass finish before it builds the next grid — the next photon pass is already running
+    if ((rc = sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + EYE, 0u, n_pix)) != 0) return fail2(rc);
+    SPPM_CHECK(cudaEventRecord(ev_eye, q));
+    // the grid tables (cell_count, cursor, start, sg, sc) are single-buffered and the stage events are reused:
+    // the host lets the eye pass finish before it builds the next grid — the next photon passes are already running
     SPPM_CHECK(cudaStreamSynchronize(q));
     float ms_g = 0.f, ms_e = 0.f;
     if (cudaEventElapsedTime(&ms_g, ctx->sev[0], ev_grid) == cudaSuccess) local.ms_grid += ms_g;
-    if (cudaEventElapsedTime(&ms_e, ev_grid, ev_eye[k]) == cudaSuccess) local.ms_eye += ms_e;
-    if (trace) std::fprintf(stderr, "sppm it %d: photons %.3f ms (%u global, %u caustic), grid %.3f ms (res %d / %d), eye %.3f ms\n", it, ms, h.n_global, h.n_caustic, ms_g, Gg.res, Gc.res, ms_e);
+    if (cudaEventElapsedTime(&ms_e, ev_grid, ev_eye) == cudaSuccess) local.ms_eye += ms_e;
+    if (trace) std::fprintf(stderr, "sppm it %d: photons %.3f ms (%u global, %u caustic; %d queue iterations), grid %.3f ms (res %d / %d), eye %.3f ms\n", it, ms, h.n_global, h.n_caustic,
+                            photons_mega ? 0 : PW[k].launched, ms_g, Gg.res, Gc.res, ms_e);
     local.global_photons += h.n_global; local.caustic_photons += h.n_caustic;
     local.photon_rays += h.photon_rays;
   }
@@ -353,13 +357,13 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   const float n_emitted = (float)((double)sp.iterations * (double)sp.photons_per_iter);  // photon_mapper.rs:229-230
   SPPM_CHECK(cudaEventRecord(ctx->sev[0], q));
   if (M.total > 0) {
-    if (s->dev.has_objf) k_sppm_final<true><<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + 2);
-    else k_sppm_final<false><<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + 2);
+    if (s->dev.has_objf) k_sppm_final<true><<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + EYE);
+    else k_sppm_final<false><<<sms * 8, 128, 0, q>>>(s->dev, P, M, px, n_emitted, B.accum, B.cnt + EYE);
     k_add_count<<<(n_pix + 255) / 256, 256, 0, q>>>(B.accum, (int)n_pix, (float)params->spp_count);
   }
   SPPM_CHECK(cudaEventRecord(ctx->sev[1], q));
   SPPM_CHECK(cudaEventRecord(ctx->ev[1], q));
-  SPPM_CHECK(cudaMemcpyAsync(hcnt + 2, B.cnt + 2, sizeof(SppmCounters), cudaMemcpyDeviceToHost, q));
+  SPPM_CHECK(cudaMemcpyAsync(hcnt + EYE, B.cnt + EYE, sizeof(SppmCounters), cudaMemcpyDeviceToHost, q));
   SPPM_CHECK(cudaMemcpyAsync(accum_host, B.accum, 16 * (size_t)n_pix, cudaMemcpyDeviceToHost, q));
   std::vector<float4> hg, hc;
   std::vector<uint2> hn;
@@ -377,7 +381,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
       o[0] = hg[i].x; o[1] = hg[i].y; o[2] = hg[i].z; o[3] = hg[i].w; o[4] = (float)hn[i].x;
       o[5] = hc[i].x; o[6] = hc[i].y; o[7] = hc[i].z; o[8] = hc[i].w; o[9] = (float)hn[i].y;
     }
-  local.eye_rays = hcnt[2].eye_rays;  // eye passes + final pass
+  local.eye_rays = hcnt[EYE].eye_rays;  // eye passes + final pass
   if (cudaEventElapsedTime(&ms, ctx->sev[0], ctx->sev[1]) == cudaSuccess) local.ms_final = ms;
   if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) local.ms_total = ms;
 #undef SPPM_CHECK

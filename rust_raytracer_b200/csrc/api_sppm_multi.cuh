@@ -139,8 +139,8 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     if (id_count && !photons_mega) {
       if (sppm_photon_wf_begin(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, qp)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: photon pass: " + ctx->err); return false; }
     } else if (id_count) {
-      if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count);
-      else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count);
+      if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count, nullptr, nullptr, nullptr);
+      else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count, nullptr, nullptr, nullptr);
     }
     return ok(cudaGetLastError(), "k_sppm_photons") && ok(cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp), "memcpy");
   };
@@ -150,13 +150,7 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     const int k = it & 1;
     if (good && !sh.failed) {
       good = ok(cudaStreamSynchronize(qp), "photon pass");  // this device's shard of the map is complete, its counters are on the host
-      if (good && id_count && !photons_mega) {  // ... unless a photon walk outlasted the queued wavefront iterations
-        const int launched = PW.launched;
-        unsigned long long rays = 0;
-        if (sppm_photon_wf_finish(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, qp, &rays)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: photon pass: " + ctx->err); good = false; }
-        if (good && PW.launched != launched) good = ok(cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp), "memcpy") && ok(cudaStreamSynchronize(qp), "photon pass");
-        if (good) hcnt[k].photon_rays = rays;
-      }
+      if (good && id_count && !photons_mega) sppm_photon_wf_finish(PW, hcnt + k);
       if (good && hcnt[k].overflow) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon buffer overflow (more than 16 stored photons per emitted photon)"); good = false; }
       sh.counts[g][k] = hcnt[k];
     }
@@ -191,7 +185,7 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     }
     if (good && pix_count) {
       const SppmPixels px = sh.px[g];
-      if (sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, pix_first, pix_count)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: eye pass: " + ctx->err); good = false; }
+      if (sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + 2, pix_first, pix_count)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: eye pass: " + ctx->err); good = false; }
     }
     // grid tables are single-buffered, and the peers may not overwrite the shards this grid build reads before it is done
     if (good) good = ok(cudaStreamSynchronize(q), "eye pass");

@@ -165,8 +165,11 @@ DEV void sppm_store(float4* photons, unsigned int* counter, unsigned int cap, un
 // SPPMIntegrator::generate_photon_map (photon_mapper.rs:238-281)
 template <bool OBJF>
 // [id_first, id_first + id_count): the photon ids this launch emits (a shard of the iteration's photons on one of several GPUs)
+// q_ray != nullptr: the walks do not start at a light but continue the *q_n records of a wavefront queue (ray stream q_ray, state
+// stream q_st; dead records skipped) — the tail of the wavefront photon pass below: the few photons that outlive its bulk.
 __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, uint2 key, int iter, float4* pg, float4* pc, unsigned int cap, SppmCounters* cnt,
-                                                      unsigned int id_first, unsigned int id_count) {
+                                                      unsigned int id_first, unsigned int id_count, const float4* __restrict__ q_ray, const float4* __restrict__ q_st,
+                                                      const unsigned int* __restrict__ q_n) {
   unsigned long long n_rays = 0;
   unsigned int lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
   // Per-lane work fetch: a photon walk lasts 1 to dozens of bounces (2.9 on average in the Cornell box), so a warp that
@@ -176,7 +179,7 @@ __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, 
   // but the order of the records in the map.  (The path tracer's extend kernel does NOT do this: there the queue order
   // is what keeps a warp coherent; here there is no order to lose.)
   const unsigned lane = threadIdx.x & 31;
-  const unsigned int n_photons = id_count;  // the cursor counts inside the shard
+  const unsigned int n_photons = q_ray ? *q_n : id_count;  // the cursor counts inside the shard (or the queue)
   unsigned int id = 0;
   int bounce = 0;
   bool alive = false, exhausted = false, has_specular = false, has_diffuse = false;
@@ -194,7 +197,18 @@ __global__ void __launch_bounds__(128) k_sppm_photons(DevScene S, SppmConst sp, 
         id = base + __popc(idle & ((1u << lane) - 1u));
         const bool have = id < n_photons;
         id += id_first;  // the global photon id keys every draw
-        if (have) {
+        if (have && q_ray) {  // continue a queued walk
+          const size_t at = 2 * (size_t)(id - id_first);
+          const float4 o = __ldcs(q_ray + at), d = __ldcs(q_ray + at + 1);
+          if (!(d.x == 0.f && d.y == 0.f && d.z == 0.f)) {
+            const float4 sa = __ldcs(q_st + at), sb = __ldcs(q_st + at + 1);
+            ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
+            power = f3(sa);
+            has_specular = (__float_as_uint(sa.w) & 1u) != 0u; has_diffuse = (__float_as_uint(sa.w) & 2u) != 0u;
+            id = __float_as_uint(sb.x); bounce = (int)__float_as_uint(sb.y);
+            alive = true;
+          }
+        } else if (have) {
           sppm_emit(S, sp, philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x50u), key), philox4x32(make_uint4(id, (uint32_t)iter, 0u, 0x51u), key), ray, power);
           alive = true; bounce = 1; has_specular = false; has_diffuse = false;
         }
@@ -522,8 +536,11 @@ __global__ void __launch_bounds__(128) k_sppm_eye_trace(DevScene S, RenderConst 
 }
 
 // PhotonMap::estimate_flux_within_radius (photon_mapper.rs:99-114: squared distance < radius^2) + SPPM::update (49-64),
-// SPPM_GATHER_LANES lanes per pixel.  Lane l takes the grid rows l, l + LANES, ... of the cell box the sphere overlaps; the
-// photons of one row's cells [a.x, b.x] are the contiguous run cell_start[row + a.x] .. cell_start[row + b.x + 1].
+// SPPM_GATHER_LANES lanes per pixel.  The photons of the cells [a.x, b.x] of one grid row are the contiguous run
+// cell_start[row + a.x] .. cell_start[row + b.x + 1] of the cell-ordered array.  The lanes first fetch the bounds of up to
+// SPPM_GATHER_LANES rows at once (one row per lane: the dependent cell_start loads of all rows are in flight together), then
+// walk the rows one after the other with the lanes striding over the row's photons.  (One row per lane, the first version, ran
+// at 9 of 32 lanes: photons sit on surfaces, so 1-3 of a pixel's 9-16 rows hold all of them — ~24 per surface cell here.)
 #ifndef SPPM_GATHER_LANES
 #define SPPM_GATHER_LANES 8
 #endif
@@ -531,14 +548,23 @@ DEV void sppm_gather_map(const SppmGrid& G, bool on, float3 p, float3 bsdf, floa
   flux = f3(0, 0, 0); count = 0;
   const float r = sqrtf(radius2), rr = r * r;
   const int3 a = sppm_cell_of(p - f3(r, r, r), G.lo, G.inv_cell, G.res), b = sppm_cell_of(p + f3(r, r, r), G.lo, G.inv_cell, G.res);
-  const int ny = b.y - a.y + 1, rows = (on && G.n != 0) ? ny * (b.z - a.z + 1) : 0;  // the shuffles below are reached by every lane
-  for (int row = (int)sub; row < rows; row += SPPM_GATHER_LANES) {
-    const int z = a.z + row / ny, y = a.y + row % ny;
-    const uint32_t base = (uint32_t)((z * G.res + y) * G.res);
-    const uint32_t j1 = __ldg(&G.cell_start[base + (uint32_t)b.x + 1u]);
-    for (uint32_t j = __ldg(&G.cell_start[base + (uint32_t)a.x]); j < j1; ++j) {
-      const float4 pos = __ldg(G.pos + j);
-      if (sppm_d2(pos, p) < rr) { ++count; flux = flux + sppm_photon_flux(G, j, pos, p, bsdf); }
+  const int ny = b.y - a.y + 1, rows = (on && G.n != 0) ? ny * (b.z - a.z + 1) : 0;  // uniform over the pixel's lanes; the shuffles below are reached by every lane
+  const unsigned lane = threadIdx.x & 31u, group_base = lane & ~(unsigned)(SPPM_GATHER_LANES - 1);
+  const int max_rows = __reduce_max_sync(0xffffffffu, rows);  // the groups of a warp walk their row batches together
+  for (int r0 = 0; r0 < max_rows; r0 += SPPM_GATHER_LANES) {
+    uint32_t j0 = 0, j1 = 0;
+    const int mine = r0 + (int)sub;
+    if (mine < rows) {
+      const uint32_t base = (uint32_t)(((a.z + mine / ny) * G.res + a.y + mine % ny) * G.res);
+      j0 = __ldg(&G.cell_start[base + (uint32_t)a.x]); j1 = __ldg(&G.cell_start[base + (uint32_t)b.x + 1u]);
+    }
+#pragma unroll
+    for (int k = 0; k < SPPM_GATHER_LANES; ++k) {
+      const uint32_t e = __shfl_sync(0xffffffffu, j1, group_base + k);
+      for (uint32_t j = __shfl_sync(0xffffffffu, j0, group_base + k) + sub; j < e; j += SPPM_GATHER_LANES) {
+        const float4 pos = __ldg(G.pos + j);
+        if (sppm_d2(pos, p) < rr) { ++count; flux = flux + sppm_photon_flux(G, j, pos, p, bsdf); }
+      }
     }
   }
 #pragma unroll
@@ -583,10 +609,15 @@ __global__ void __launch_bounds__(256) k_sppm_gather(SppmGrid Gg, SppmGrid Gc, S
 
 // PhotonMap::estimate_flux_by_count (photon_mapper.rs:77-96): the k nearest photons, exactly — one warp per (pixel, map).
 // Cube s = the cells within Chebyshev distance s of the point's cell; every photon outside it lies more than s cells away
-// along some axis.  The warp grows s until k photons lie within s cells of the point, keeping the squared distances of the
-// cube's photons in shared memory (a cube that holds more than SPPM_KNN_CAP photons is re-read from the grid instead), finds
-// the k-th smallest by bisection on the float bits, and adds up the flux of the photons up to that distance: what
-// kd_tree.nearests(k) returns, its largest squared distance being the initial radius^2 (photon_mapper.rs:80-95).
+// along some axis.  The warp grows s (from the cell table alone) until the cube holds k photons, selects the k-th smallest
+// squared distance among them — an upper bound of the true one — and, if that reaches beyond s cells, jumps to the cube that
+// covers it and selects again: then the k nearest of the cube are the k nearest of the map.  Selection: the cube's squared
+// distances go to shared memory and a quickselect (count against a pivot, compact the side that holds the k-th) narrows them
+// down; a cube with more photons than the buffer holds is first narrowed by value — a 2048-bin histogram of the float bits
+// over the current interval, refined until the bin with the k-th fits.  The flux of the photons up to the k-th distance is
+// what kd_tree.nearests(k) returns, its largest squared distance the initial radius^2 (photon_mapper.rs:80-95).
+// (First version: bisection on the float bits — 31 counting passes per point, over the grid itself for a large cube, and a
+// fill + count per shell: 19.7 ms for the first iteration at the reference configuration.)
 #define SPPM_KNN_CAP 2048
 struct SppmCube { int x0, x1, y0, y1, z0, z1; };
 DEV SppmCube sppm_cube(const SppmGrid& G, int3 c0, int s) {
@@ -610,6 +641,115 @@ DEV uint32_t sppm_warp_sum(uint32_t v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// photons in the cube (all lanes) and this lane's exclusive share of them, from the cell table alone
+DEV uint32_t sppm_cube_count(const SppmGrid& G, const SppmCube& q, unsigned lane, uint32_t& before_me) {
+  const int ny = q.y1 - q.y0 + 1, rows = ny * (q.z1 - q.z0 + 1);
+  uint32_t mine = 0;
+  for (int row = (int)lane; row < rows; row += 32) {
+    const uint32_t base = (uint32_t)(((q.z0 + row / ny) * G.res + q.y0 + row % ny) * G.res);
+    mine += __ldg(&G.cell_start[base + (uint32_t)q.x1 + 1u]) - __ldg(&G.cell_start[base + (uint32_t)q.x0]);
+  }
+  uint32_t incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += o; }
+  before_me = incl - mine;
+  return __shfl_sync(0xffffffffu, incl, 31);
+}
+// the want-th smallest (1-based) of keys[0, n): quickselect in place, then bisection between the extremes of the few left
+DEV uint32_t sppm_select_smem(uint32_t* keys, uint32_t n, uint32_t want, unsigned lane) {
+  while (n > 64u) {
+    const uint32_t a = keys[0], b = keys[n >> 1], c = keys[n - 1u];
+    const uint32_t pivot = max(min(a, b), min(max(a, b), c));  // median of three
+    uint32_t below = 0, equal = 0;
+    for (uint32_t i = lane; i < n; i += 32) { const uint32_t v = keys[i]; below += v < pivot ? 1u : 0u; equal += v == pivot ? 1u : 0u; }
+    below = sppm_warp_sum(below); equal = sppm_warp_sum(equal);
+    if (want > below && want <= below + equal) return pivot;
+    const bool take_low = want <= below;
+    if (!take_low) want -= below + equal;
+    uint32_t out = 0;
+    for (uint32_t i0 = 0; i0 < n; i0 += 32) {  // warp-uniform trip count; writes land at or below the positions already read
+      const uint32_t i = i0 + lane;
+      const uint32_t v = i < n ? keys[i] : 0u;
+      const bool keep = i < n && (take_low ? v < pivot : v > pivot);
+      const unsigned m = __ballot_sync(0xffffffffu, keep);
+      __syncwarp();
+      if (keep) keys[out + __popc(m & ((1u << lane) - 1u))] = v;
+      out += __popc(m);
+    }
+    __syncwarp();
+    n = out;
+  }
+  uint32_t mn = 0xffffffffu, mx = 0u;
+  for (uint32_t i = lane; i < n; i += 32) { mn = min(mn, keys[i]); mx = max(mx, keys[i]); }
+  uint32_t lo = __reduce_min_sync(0xffffffffu, mn), hi = __reduce_max_sync(0xffffffffu, mx);
+  while (lo < hi) {
+    const uint32_t mid = lo + ((hi - lo) >> 1);
+    uint32_t cc = 0;
+    for (uint32_t i = lane; i < n; i += 32) cc += keys[i] <= mid ? 1u : 0u;
+    if (sppm_warp_sum(cc) >= want) hi = mid; else lo = mid + 1u;
+  }
+  return lo;
+}
+// the want-th smallest squared distance (as float bits) of the n_in photons of cube q; `before_me` from sppm_cube_count
+DEV uint32_t sppm_select_cube(const SppmGrid& G, const SppmCube& q, float3 p, uint32_t* keys, uint32_t n_in, uint32_t before_me, uint32_t want, unsigned lane) {
+  __syncwarp();
+  if (n_in <= SPPM_KNN_CAP) {
+    uint32_t at = before_me;
+    sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { keys[at++] = __float_as_uint(sppm_d2(pos, p)); });
+    __syncwarp();
+    return sppm_select_smem(keys, n_in, want, lane);
+  }
+  // too many for the buffer: narrow the interval [lo, hi] of float bits that holds the want-th, 2048 bins at a time
+  uint32_t lo = 0u, hi = 0x7f800000u;
+  for (;;) {
+    const unsigned long long span = (unsigned long long)(hi - lo) + 1ull;
+    for (uint32_t i = lane; i < SPPM_KNN_CAP; i += 32) keys[i] = 0u;
+    __syncwarp();
+    sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) {
+      const uint32_t key = __float_as_uint(sppm_d2(pos, p));
+      if (key >= lo && key <= hi) atomicAdd(&keys[(uint32_t)(((unsigned long long)(key - lo) * SPPM_KNN_CAP) / span)], 1u);
+    });
+    __syncwarp();
+    // the bin that holds the want-th of [lo, hi]: every lane owns 64 consecutive bins
+    uint32_t mine = 0;
+    for (uint32_t i = 0; i < SPPM_KNN_CAP / 32; ++i) mine += keys[lane * (SPPM_KNN_CAP / 32) + i];
+    uint32_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += o; }
+    const unsigned owner_mask = __ballot_sync(0xffffffffu, incl >= want);
+    const int owner = __ffs((int)owner_mask) - 1;  // first lane whose inclusive sum reaches want (exists: want <= photons in [lo, hi])
+    uint32_t bin = 0, before = 0, in_bin = 0;
+    if ((int)lane == owner) {
+      uint32_t run = incl - mine;
+      for (uint32_t i = 0; i < SPPM_KNN_CAP / 32; ++i) {
+        const uint32_t c = keys[lane * (SPPM_KNN_CAP / 32) + i];
+        if (run + c >= want) { bin = lane * (SPPM_KNN_CAP / 32) + i; before = run; in_bin = c; break; }
+        run += c;
+      }
+    }
+    bin = __shfl_sync(0xffffffffu, bin, owner); before = __shfl_sync(0xffffffffu, before, owner); in_bin = __shfl_sync(0xffffffffu, in_bin, owner);
+    // keys of bin b: key - lo in [ceil(b span / 2048), ceil((b + 1) span / 2048) - 1]
+    const uint32_t new_lo = lo + (uint32_t)(((unsigned long long)bin * span + SPPM_KNN_CAP - 1) / SPPM_KNN_CAP);
+    const uint32_t new_hi = lo + (uint32_t)((((unsigned long long)bin + 1ull) * span + SPPM_KNN_CAP - 1) / SPPM_KNN_CAP) - 1u;
+    lo = new_lo; hi = new_hi; want -= before;
+    __syncwarp();
+    if (lo == hi) return lo;
+    if (in_bin <= SPPM_KNN_CAP) {  // collect the bin's keys and finish in shared memory
+      uint32_t n = 0;  // warp-uniform running count: the lanes append through ballots, a cube row at a time would diverge, so use an atomic cursor
+      __shared__ uint32_t s_cursor[4];
+      if (lane == 0) s_cursor[threadIdx.x >> 5] = 0u;
+      __syncwarp();
+      sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) {
+        const uint32_t key = __float_as_uint(sppm_d2(pos, p));
+        if (key >= lo && key <= hi) keys[atomicAdd(&s_cursor[threadIdx.x >> 5], 1u)] = key;
+      });
+      __syncwarp();
+      n = s_cursor[threadIdx.x >> 5];
+      __syncwarp();
+      return sppm_select_smem(keys, n, want, lane);
+    }
+  }
+}
 __global__ void __launch_bounds__(128) k_sppm_knn(SppmGrid Gg, SppmGrid Gc, SppmPixels px, SppmEye E, int k_global, int k_caustic) {
   __shared__ uint32_t s_keys[4][SPPM_KNN_CAP];
   const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -626,53 +766,26 @@ __global__ void __launch_bounds__(128) k_sppm_knn(SppmGrid Gg, SppmGrid Gc, Sppm
     if (G.n != 0) {
       const int3 c0 = sppm_cell_of(p, G.lo, G.inv_cell, G.res);
       SppmCube q;
-      uint32_t n_in = 0, hi_key = 0x7f800000u;
-      bool in_smem = false;
-      for (int s = 0;; ++s) {
+      uint32_t n_in = 0, before_me = 0;
+      int s = 0;
+      bool whole = false;
+      for (;; ++s) {  // the smallest cube with k photons
         q = sppm_cube(G, c0, s);
-        const bool whole = q.x0 == 0 && q.y0 == 0 && q.z0 == 0 && q.x1 == G.res - 1 && q.y1 == G.res - 1 && q.z1 == G.res - 1;
-        // photons in the cube, from the cell table alone (no photon is touched while the cube holds fewer than k)
-        const int ny = q.y1 - q.y0 + 1, rows = ny * (q.z1 - q.z0 + 1);
-        uint32_t mine = 0;
-        for (int row = (int)lane; row < rows; row += 32) {
-          const uint32_t base = (uint32_t)(((q.z0 + row / ny) * G.res + q.y0 + row % ny) * G.res);
-          mine += __ldg(&G.cell_start[base + (uint32_t)q.x1 + 1u]) - __ldg(&G.cell_start[base + (uint32_t)q.x0]);
-        }
-        uint32_t incl = mine;  // this lane's place in the key buffer: exclusive scan over the lanes
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += o; }
-        n_in = __shfl_sync(0xffffffffu, incl, 31);
-        if (n_in < k && !whole) continue;
-        in_smem = n_in <= SPPM_KNN_CAP;
-        __syncwarp();
-        if (in_smem) {
-          uint32_t at = incl - mine;
-          sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { keys[at++] = __float_as_uint(sppm_d2(pos, p)); });
-        }
-        __syncwarp();
-        if (n_in >= k) {  // are k of them within s cells (the distance no unvisited photon can undercut)?
-          const float reach = (float)s * G.cell;
-          const uint32_t reach_key = __float_as_uint(reach * reach);
-          uint32_t c = 0;
-          if (in_smem) { for (uint32_t i = lane; i < n_in; i += 32) c += keys[i] <= reach_key ? 1u : 0u; }
-          else sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { c += __float_as_uint(sppm_d2(pos, p)) <= reach_key ? 1u : 0u; });
-          c = sppm_warp_sum(c);
-          if (c >= k) { hi_key = reach_key; break; }
-        }
-        if (whole) break;  // the cube is the whole grid: every photon has been seen
+        whole = q.x0 == 0 && q.y0 == 0 && q.z0 == 0 && q.x1 == G.res - 1 && q.y1 == G.res - 1 && q.z1 == G.res - 1;
+        n_in = sppm_cube_count(G, q, lane, before_me);
+        if (n_in >= k || whole) break;
       }
-      // smallest tau with #{d2 <= tau} >= min(k, n_in)
-      const uint32_t want = n_in < k ? n_in : k;
-      uint32_t lo_key = 0u;
-      while (lo_key < hi_key) {
-        const uint32_t mid = lo_key + ((hi_key - lo_key) >> 1);
-        uint32_t c = 0;
-        if (in_smem) { for (uint32_t i = lane; i < n_in; i += 32) c += keys[i] <= mid ? 1u : 0u; }
-        else sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { c += __float_as_uint(sppm_d2(pos, p)) <= mid ? 1u : 0u; });
-        c = sppm_warp_sum(c);
-        if (c >= want) hi_key = mid; else lo_key = mid + 1u;
+      for (;;) {
+        tau = sppm_select_cube(G, q, p, keys, n_in, before_me, n_in < k ? n_in : k, lane);
+        const float reach = (float)s * G.cell;
+        if (whole || tau <= __float_as_uint(reach * reach)) break;  // no photon outside the cube is nearer than s cells
+        // the k-th of this cube bounds the true one: the cube that reaches that far holds the k nearest of the map
+        const int s_need = (int)ceilf(sqrtf(__uint_as_float(tau)) * G.inv_cell * 1.0001f);
+        s = max(s + 1, min(s_need, G.res));
+        q = sppm_cube(G, c0, s);
+        whole = q.x0 == 0 && q.y0 == 0 && q.z0 == 0 && q.x1 == G.res - 1 && q.y1 == G.res - 1 && q.z1 == G.res - 1;
+        n_in = sppm_cube_count(G, q, lane, before_me);
       }
-      tau = lo_key;
       sppm_for_each_in_cube(G, q, lane, [&](uint32_t j, float4 pos) {
         if (__float_as_uint(sppm_d2(pos, p)) <= tau) flux = flux + sppm_photon_flux(G, j, pos, p, bsdf);
       });
