@@ -259,8 +259,14 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local_rank)
+    json_out = sys.stdout
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version / debug lines must not precede the JSON line on stdout
+        # NCCL's version / debug lines must not precede the JSON line on stdout (it prints "NCCL version ..." to fd 1 from native
+        # code when the first communicator comes up): fd 1 points at stderr for the whole run, the JSON line goes to the saved fd
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        sys.stdout.flush()
+        json_out = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     strong = args.scaling == "strong"
@@ -456,7 +462,8 @@ def main():
             "device": ctx.device_info(),
             "scene": info,
         }
-        print(json.dumps(out))
+        json_out.write(json.dumps(out) + "\n")
+        json_out.flush()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -243,7 +243,9 @@ typedef struct b200rt_builder b200rt_builder;
 int b200rt_abi_version(void);
 int b200rt_device_count(int* count);
 int b200rt_ctx_create(int device, b200rt_ctx** out);
-int b200rt_ctx_destroy(b200rt_ctx* ctx); /* destroy the context's scenes first: a scene keeps a pointer to its context */
+/* Destroy the context's scenes first.  Scenes that are still alive are orphaned, not left dangling: every entry point then
+ * returns B200RT_ERR_INVALID for them (b200rt_global_error says why) and b200rt_scene_destroy still frees their tables. */
+int b200rt_ctx_destroy(b200rt_ctx* ctx);
 /* Run all work of this context on an existing cudaStream_t (NULL = default stream). */
 int b200rt_ctx_set_stream(b200rt_ctx* ctx, void* cuda_stream);
 const char* b200rt_last_error(const b200rt_ctx* ctx);
@@ -359,7 +361,9 @@ int b200rt_render_sppm(b200rt_scene* scene, const b200rt_camera* cam, const b200
  * SPPM statistics are sharded by pixel index; the final pass is sharded by sample index and summed on scenes[0]'s device.
  * The stored photon counts and the ray counts equal the one-device call's exactly (every draw is keyed by the global photon /
  * pixel id); the image up to float summation order.  Needs peer access between the devices (no NCCL, no host staging).
- * stats->ms_total is the host clock around the whole call; the per-stage fields are not filled. */
+ * Here the stats times are HOST clocks: ms_total around the whole call (buffer set-up and release included), ms_eye over the
+ * SPPM iterations (photon passes, grid builds and eye passes of all devices), ms_final over everything after them (statistics
+ * gather, final pass, reduce, copies out, release); ms_photons and ms_grid are not filled. */
 int b200rt_render_sppm_multi(int32_t n_dev, b200rt_scene* const* scenes, const b200rt_camera* cam,
                              const b200rt_params* params, const b200rt_sppm_params* sppm, float* accum_host,
                              float* pixel_stats_host, b200rt_sppm_stats* stats);

@@ -9,6 +9,29 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(HERE, "libb200rt.so")  # B200RT_LIB: A/B builds of the same library
 
+
+
+def _name_bundled_nccl():
+    """Point the library's dlopen of NCCL (b200rt_render_multi's ncclReduce path) at the copy bundled with this interpreter's
+    torch wheel, when there is one and the host has not chosen (B200RT_NCCL_LIB).  The loader keeps one object per SONAME: a
+    process that maps the SYSTEM libnccl.so.2 first and imports torch later breaks that import if torch was built against a
+    newer NCCL.  Nothing is imported or loaded here; a path is named."""
+    if os.environ.get("B200RT_NCCL_LIB"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["B200RT_NCCL_LIB"] = cand
+                return
+    except Exception:
+        pass
+
+
+_name_bundled_nccl()
+
 OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_IO, ERR_PARSE = range(7)
 
 PRIM_SPHERE, PRIM_MOVING_SPHERE, PRIM_XY_RECT, PRIM_XZ_RECT, PRIM_YZ_RECT, PRIM_BOX, PRIM_TRIANGLE, PRIM_MEDIUM_SPHERE, PRIM_MEDIUM_BOX = range(9)

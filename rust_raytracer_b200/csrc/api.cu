@@ -1,7 +1,9 @@
 // api.cu — the C ABI of include/b200rt.h: context, scene upload, World::hit batch operator, capture_image
 // (wavefront and megakernel pipelines), tonemap.  Every entry point returns a status; nothing throws across the ABI.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -32,11 +34,16 @@ struct b200rt_ctx {
   void* spare_block = nullptr;
   size_t spare_bytes = 0;
   const WfBuffers* static_wf = nullptr;  // set for the duration of b200rt_render_device_static: render_wavefront takes its queues from there
+  // the scenes created on this context and not yet destroyed: b200rt_ctx_destroy orphans them (ctx = nullptr), so that a host
+  // that releases a context before its scenes (a garbage collector does) gets B200RT_ERR_INVALID from them, not a dangling pointer
+  std::mutex scenes_mutex;
+  std::vector<struct b200rt_scene*> scenes;
   cudaEvent_t sev[128 * WF_MAX_PIPES] = {};  // stage events per pipeline: 2 alternating sets x up to 8 iterations in flight x 8 (generate, extend, shade, shadow boundaries)
 };
 
 struct b200rt_scene {
-  b200rt_ctx* ctx = nullptr;
+  b200rt_ctx* ctx = nullptr;  // nullptr once the context has been destroyed (every entry point then returns B200RT_ERR_INVALID)
+  int device = 0;
   DevScene dev{};
   void* block = nullptr;  // one allocation holding every table
   size_t block_bytes = 0;
@@ -45,6 +52,11 @@ struct b200rt_scene {
 };
 
 static thread_local std::string g_global_err;
+// a scene whose context has been destroyed
+#define SCENE_ALIVE(s)                                                                                              \
+  do {                                                                                                               \
+    if (!(s)->ctx) { g_global_err = "the scene's context has been destroyed (b200rt_ctx_destroy before b200rt_scene_destroy)"; return B200RT_ERR_INVALID; } \
+  } while (0)
 
 #define CU_CHECK(ctx, call)                                                                                      \
   do {                                                                                                           \
@@ -113,6 +125,12 @@ int b200rt_ctx_create(int device, b200rt_ctx** out) {
 int b200rt_ctx_destroy(b200rt_ctx* c) {
   if (!c) return B200RT_OK;
   cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  {
+    std::lock_guard<std::mutex> lock(c->scenes_mutex);
+    for (b200rt_scene* s : c->scenes) s->ctx = nullptr;  // orphaned: b200rt_scene_destroy still frees their tables
+    c->scenes.clear();
+  }
   for (int k = 0; k < WF_MAX_PIPES; ++k) {
     if (c->wf_block[k]) cudaFree(c->wf_block[k]);
     if (c->wf_shadow_block[k]) cudaFree(c->wf_shadow_block[k]);
@@ -211,6 +229,11 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
   sc->dev.inst_eps = (const float*)(base + parts[14].off);
   sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_bvh_prims = (int)cs.n_bvh_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0; sc->dev.has_objf = cs.has_objf ? 1 : 0;
   sc->h2d_bytes = total; sc->n_nodes = cs.n_nodes; sc->n_prims = cs.n_prims;
+  sc->device = ctx->device;
+  {
+    std::lock_guard<std::mutex> lock(ctx->scenes_mutex);
+    ctx->scenes.push_back(sc);
+  }
   *out = sc;
   return B200RT_OK;
 }
@@ -218,7 +241,16 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
 int b200rt_scene_destroy(b200rt_scene* s) {
   if (!s) return B200RT_OK;
   b200rt_ctx* ctx = s->ctx;
-  cudaSetDevice(ctx->device);
+  cudaSetDevice(s->device);
+  if (!ctx) {  // its context went first: nothing of it is left to wait for or to recycle into
+    if (s->block) { cudaDeviceSynchronize(); cudaFree(s->block); }
+    delete s;
+    return B200RT_OK;
+  }
+  {
+    std::lock_guard<std::mutex> lock(ctx->scenes_mutex);
+    ctx->scenes.erase(std::remove(ctx->scenes.begin(), ctx->scenes.end(), s), ctx->scenes.end());
+  }
   if (s->block) {
     cudaStreamSynchronize(ctx->stream);  // nothing in flight may still read the tables
     if (!ctx->spare_block) { ctx->spare_block = s->block; ctx->spare_bytes = s->block_bytes; }
@@ -240,6 +272,7 @@ int b200rt_scene_info(const b200rt_scene* s, uint64_t* h2d_bytes, uint32_t* bvh_
 int b200rt_intersect_batch_device(b200rt_scene* s, const float* o_time, const float* d_tmax, const uint32_t* medium_seed, uint64_t n, float t_min, b200rt_hit* out) {
   if (!s || (n && (!o_time || !d_tmax || !out))) return B200RT_ERR_INVALID;
   if (n == 0) return B200RT_OK;  // empty batch
+  SCENE_ALIVE(s);
   b200rt_ctx* ctx = s->ctx;
   CU_CHECK(ctx, cudaSetDevice(ctx->device));
   cudaGetLastError();  // stale non-sticky errors of earlier, unrelated calls are not this launch's
@@ -255,6 +288,7 @@ int b200rt_intersect_batch_device(b200rt_scene* s, const float* o_time, const fl
 int b200rt_intersect_batch(b200rt_scene* s, const float* o_time, const float* d_tmax, const uint32_t* medium_seed, uint64_t n, float t_min, b200rt_hit* out) {
   if (!s || (n && (!o_time || !d_tmax || !out))) return B200RT_ERR_INVALID;
   if (n == 0) return B200RT_OK;
+  SCENE_ALIVE(s);
   b200rt_ctx* ctx = s->ctx;
   CU_CHECK(ctx, cudaSetDevice(ctx->device));
   float *d_o = nullptr, *d_d = nullptr;

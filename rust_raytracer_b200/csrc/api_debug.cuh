@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(128) k_debug_eval(DevScene S, RenderConst P, i
 extern "C" int b200rt_debug_eval(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, int32_t kind, uint64_t n, const float* in_host, float* out_host) {
   if (!s || !cam || !params || kind < B200RT_EVAL_TEXTURE || kind > B200RT_EVAL_SAMPLERS || (n && (!in_host || !out_host))) return B200RT_ERR_INVALID;
   if (n == 0) return B200RT_OK;
+  SCENE_ALIVE(s);
   b200rt_ctx* ctx = s->ctx;
   CU_CHECK(ctx, cudaSetDevice(ctx->device));
   static const int in_w[4] = {8, 20, 2, 8}, out_w[4] = {4, 16, 16, 12};

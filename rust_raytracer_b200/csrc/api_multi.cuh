@@ -45,10 +45,20 @@ std::map<std::vector<int>, std::vector<rt_ncclComm_t>> g_nccl_comms;  // one cli
 NcclApi& nccl_api() {  // call with g_multi_mutex held
   if (g_nccl_tried) return g_nccl;
   g_nccl_tried = true;
+  // Order: the NCCL the host process already has (RTLD_NOLOAD: a torch process keeps its own, bundled one), then the one the
+  // host names (B200RT_NCCL_LIB: the Python wrapper points it at the interpreter's bundled copy), then the system's.  The
+  // order matters beyond taste: the loader keeps ONE object per SONAME, so a process that maps the system libnccl.so.2 first
+  // and imports torch later hands torch that copy — and a torch built against a newer NCCL then fails to import
+  // (libtorch_cuda.so: undefined symbol ncclDevCommCreate; met on a 2-GPU box when the two-device tests ran before a torch import).
+  g_nccl.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+  if (!g_nccl.handle) {
+    const char* named = std::getenv("B200RT_NCCL_LIB");
+    if (named && *named) g_nccl.handle = dlopen(named, RTLD_NOW | RTLD_LOCAL);
+  }
   const char* names[] = {"libnccl.so.2", "libnccl.so"};
   for (const char* n : names) {
-    g_nccl.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
     if (g_nccl.handle) break;
+    g_nccl.handle = dlopen(n, RTLD_NOW | RTLD_LOCAL);
   }
   if (!g_nccl.handle) return g_nccl;
   g_nccl.CommInitAll = (int (*)(rt_ncclComm_t*, int, const int*))dlsym(g_nccl.handle, "ncclCommInitAll");
@@ -86,7 +96,7 @@ void multi_spp_range(int rank, int world, int spp_begin, int spp_total, int& beg
 extern "C" int b200rt_render_multi(int32_t n_dev, b200rt_scene* const* scenes, const b200rt_camera* cam, const b200rt_params* params,
                                    float* accum_host, b200rt_stats* stats_per_device, b200rt_multi_stats* multi) {
   if (n_dev < 1 || n_dev > B200RT_MULTI_MAX_DEV || !scenes || !cam || !params || !accum_host) return B200RT_ERR_INVALID;
-  for (int g = 0; g < n_dev; ++g) if (!scenes[g]) return B200RT_ERR_INVALID;
+  for (int g = 0; g < n_dev; ++g) { if (!scenes[g]) return B200RT_ERR_INVALID; SCENE_ALIVE(scenes[g]); }
   b200rt_ctx* root = scenes[0]->ctx;
   // One context per scene, normally one device per context.  Several contexts on ONE device are allowed as well (each has
   // its own streams and queue pools; the "peer" buffers are then plain local memory): that is how a one-GPU box exercises this

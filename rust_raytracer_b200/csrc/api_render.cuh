@@ -361,6 +361,7 @@ extern "C" {
 
 int b200rt_render_device(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, float* accum_dev, b200rt_stats* stats) {
   if (!s || !cam || !params || !accum_dev) return B200RT_ERR_INVALID;
+  SCENE_ALIVE(s);
   b200rt_ctx* ctx = s->ctx;
   int rc = validate_params(ctx, params);
   if (rc) return rc;
@@ -392,6 +393,7 @@ int b200rt_render_device(b200rt_scene* s, const b200rt_camera* cam, const b200rt
 
 int b200rt_render(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, float* accum_host, b200rt_stats* stats) {
   if (!s || !cam || !params || !accum_host) return B200RT_ERR_INVALID;
+  SCENE_ALIVE(s);
   b200rt_ctx* ctx = s->ctx;
   int rc = validate_params(ctx, params);
   if (rc) return rc;

@@ -199,6 +199,7 @@ void sppm_photon_wf_finish(SppmPhotonWf& W, SppmCounters* cnt_host) {
 extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, const b200rt_sppm_params* sppm,
                                   float* accum_host, float* pixel_stats_host, b200rt_sppm_stats* stats) {
   if (!s || !cam || !params || !sppm || !accum_host) return B200RT_ERR_INVALID;
+  SCENE_ALIVE(s);
   b200rt_ctx* ctx = s->ctx;
   int rc = validate_params(ctx, params);
   if (rc) return rc;

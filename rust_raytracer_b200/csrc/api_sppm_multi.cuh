@@ -41,12 +41,13 @@ struct SppmShared {  // what the device threads publish to each other
   std::string err;
   int err_code = B200RT_OK;
   // per device: photon buffers of both parities, the per-pixel statistics, the accumulation buffer
-  float4* pg[B200RT_MULTI_MAX_DEV][2];
-  float4* pc[B200RT_MULTI_MAX_DEV][2];
+  float4* pg[B200RT_MULTI_MAX_DEV][SPPM_MAX_NB];
+  float4* pc[B200RT_MULTI_MAX_DEV][SPPM_MAX_NB];
   SppmPixels px[B200RT_MULTI_MAX_DEV];
   float* accum[B200RT_MULTI_MAX_DEV];
   // per device and parity: what the photon pass stored
-  SppmCounters counts[B200RT_MULTI_MAX_DEV][2];
+  SppmCounters counts[B200RT_MULTI_MAX_DEV][SPPM_MAX_NB];
+  int inflight = 1;  // photon passes ahead of the eye pass (the same on every device)
   // totals
   std::atomic<unsigned long long> global_photons{0}, caustic_photons{0}, photon_rays{0}, eye_rays{0};
   void fail(int code, const std::string& what) {
@@ -75,7 +76,8 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   const unsigned int cap_shard = (id_count + 1u) * 16u;
   const uint32_t max_cells = (uint32_t)SPPM_MAX_RES * SPPM_MAX_RES * SPPM_MAX_RES;
   SppmBuffers B;
-  cudaStream_t q = ctx->stream, qp = nullptr;
+  cudaStream_t q = ctx->stream, qp[SPPM_MAX_NB] = {};
+  const int inflight = sh.inflight, NB = inflight + 1, EYE = SPPM_MAX_NB;  // as in b200rt_render_sppm: buffer / stream / queues k = pass % NB
   cudaEvent_t ev_grid = nullptr;
   SppmCounters* hcnt = nullptr;
   auto ok = [&](cudaError_t e, const char* what) {
@@ -99,21 +101,22 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   if (good) {
     cudaError_t e = cudaSuccess;
     auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
-    for (int k = 0; k < 2; ++k) { alloc((void**)&B.pg[k], (size_t)cap_shard * 64); alloc((void**)&B.pc[k], (size_t)cap_shard * 64); }
+    for (int k = 0; k < NB; ++k) { alloc((void**)&B.pg[k], (size_t)cap_shard * 64); alloc((void**)&B.pc[k], (size_t)cap_shard * 64); }
     if (e == cudaSuccess) e = B.alloc_maps(cap_total, n_pix);
     alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
     alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
     alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
     alloc((void**)&B.accum, 16 * (size_t)n_pix);
-    alloc((void**)&B.cnt, 3 * sizeof(SppmCounters));
+    alloc((void**)&B.cnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters));
     good = ok(e, "cudaMalloc");
-    if (good) good = ok(cudaStreamCreateWithFlags(&qp, cudaStreamNonBlocking), "cudaStreamCreate") && ok(cudaEventCreateWithFlags(&ev_grid, cudaEventDisableTiming), "cudaEventCreate") &&
-                     ok(cudaMallocHost(&hcnt, 3 * sizeof(SppmCounters)), "cudaMallocHost");
+    for (int k = 0; good && k < NB; ++k) good = ok(cudaStreamCreateWithFlags(&qp[k], cudaStreamNonBlocking), "cudaStreamCreate");
+    if (good) good = ok(cudaEventCreateWithFlags(&ev_grid, cudaEventDisableTiming), "cudaEventCreate") &&
+                     ok(cudaMallocHost(&hcnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters)), "cudaMallocHost");
     if (good) good = ok(cudaMemsetAsync(B.px_g, 0, 16 * (size_t)n_pix, q), "memset") && ok(cudaMemsetAsync(B.px_c, 0, 16 * (size_t)n_pix, q), "memset") &&
                      ok(cudaMemsetAsync(B.px_n, 0, 8 * (size_t)n_pix, q), "memset") && ok(cudaMemsetAsync(B.accum, 0, 16 * (size_t)n_pix, q), "memset") &&
-                     ok(cudaMemsetAsync(B.cnt + 2, 0, sizeof(SppmCounters), q), "memset") && ok(cudaStreamSynchronize(q), "sync");
+                     ok(cudaMemsetAsync(B.cnt + EYE, 0, sizeof(SppmCounters), q), "memset") && ok(cudaStreamSynchronize(q), "sync");
   }
-  for (int k = 0; k < 2; ++k) { sh.pg[g][k] = B.pg[k]; sh.pc[g][k] = B.pc[k]; }
+  for (int k = 0; k < NB; ++k) { sh.pg[g][k] = B.pg[k]; sh.pc[g][k] = B.pc[k]; }
   sh.px[g] = SppmPixels{B.px_g, B.px_c, B.px_n};
   sh.accum[g] = B.accum;
   bar.wait();  // every device has published its buffers (or failed)
@@ -127,30 +130,35 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   const int sms = ctx->prop.multiProcessorCount;
   const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8);
   const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;  // as in b200rt_render_sppm
-  SppmPhotonWf PW;
-  if (good && !photons_mega && id_count && sppm_photon_wf_alloc(ctx, s, PW, id_count)) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon queues: " + ctx->err); good = false; }
-  auto launch_photons = [&](int it) -> bool {  // on qp, into the buffers of parity it & 1
-    const int k = it & 1;
+  SppmPhotonWf PW[SPPM_MAX_NB];
+  for (int k = 0; good && k < NB; ++k)
+    if (!photons_mega && id_count && sppm_photon_wf_alloc(ctx, s, PW[k], id_count)) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon queues: " + ctx->err); good = false; }
+  auto launch_photons = [&](int it) -> bool {  // on stream / into the buffers it % NB
+    const int k = it % NB;
+    cudaStream_t qpk = qp[k];
     SppmCounters h0;
     std::memset(&h0, 0, sizeof(h0));
     for (int a = 0; a < 3; ++a) { h0.lo[a] = 0xffffffffu; h0.hi[a] = 0u; }
     hcnt[k] = h0;
-    if (!ok(cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qp), "memcpy")) return false;
+    if (!ok(cudaMemcpyAsync(B.cnt + k, hcnt + k, sizeof(SppmCounters), cudaMemcpyHostToDevice, qpk), "memcpy")) return false;
     if (id_count && !photons_mega) {
-      if (sppm_photon_wf_begin(ctx, s, PW, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, qp)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: photon pass: " + ctx->err); return false; }
+      if (sppm_photon_wf_begin(ctx, s, PW[k], sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, qpk)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: photon pass: " + ctx->err); return false; }
     } else if (id_count) {
-      if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count, nullptr, nullptr, nullptr);
-      else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qp>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count, nullptr, nullptr, nullptr);
+      if (s->dev.has_objf) k_sppm_photons<true><<<sms * photon_grid, 128, 0, qpk>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count, nullptr, nullptr, nullptr);
+      else k_sppm_photons<false><<<sms * photon_grid, 128, 0, qpk>>>(s->dev, sp, P.key, it, B.pg[k], B.pc[k], cap_shard, B.cnt + k, id_first, id_count, nullptr, nullptr, nullptr);
     }
-    return ok(cudaGetLastError(), "k_sppm_photons") && ok(cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qp), "memcpy");
+    return ok(cudaGetLastError(), "k_sppm_photons") && ok(cudaMemcpyAsync(hcnt + k, B.cnt + k, sizeof(SppmCounters), cudaMemcpyDeviceToHost, qpk), "memcpy");
   };
-  if (good && !sh.failed) good = launch_photons(0);
+  for (int it = 0; it < inflight && it < sp.iterations; ++it) if (good && !sh.failed) good = launch_photons(it);
   // ---- the SPPM iterations
   for (int it = 0; it < sp.iterations; ++it) {
-    const int k = it & 1;
+    const int k = it % NB;
     if (good && !sh.failed) {
-      good = ok(cudaStreamSynchronize(qp), "photon pass");  // this device's shard of the map is complete, its counters are on the host
-      if (good && id_count && !photons_mega) sppm_photon_wf_finish(PW, hcnt + k);
+      good = ok(cudaStreamSynchronize(qp[k]), "photon pass");  // this device's shard of the map is complete, its counters are on the host
+      if (good && id_count && !photons_mega) {
+        sppm_photon_wf_finish(PW[k], hcnt + k);
+        for (int j = 0; j < NB; ++j) PW[j].plan = PW[k].plan;
+      }
       if (good && hcnt[k].overflow) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon buffer overflow (more than 16 stored photons per emitted photon)"); good = false; }
       sh.counts[g][k] = hcnt[k];
     }
@@ -177,15 +185,15 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
       sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: grid build: " + ctx->err); good = false; continue;
     }
     good = ok(cudaEventRecord(ev_grid, q), "event");
-    if (good && it + 1 < sp.iterations) {
-      // the next photon pass writes the buffers of the other parity, which every peer's grid build of iteration it - 1 has
-      // finished reading: each thread synchronised its stream at the end of that iteration, before it arrived at barrier A of
-      // this one.  It starts after the local grid build (see b200rt_render_sppm: photon blocks starve the small grid kernels).
-      good = ok(cudaStreamWaitEvent(qp, ev_grid, 0), "wait") && launch_photons(it + 1);
+    if (good && it + inflight < sp.iterations) {
+      // pass it + inflight writes the buffers (it - 1) % NB, which every peer's grid build of iteration it - 1 has finished
+      // reading: each thread synchronised its stream at the end of that iteration, before it arrived at barrier A of this one.
+      // It starts after the local grid build (see b200rt_render_sppm: photon blocks starve the small grid kernels).
+      good = ok(cudaStreamWaitEvent(qp[(it + inflight) % NB], ev_grid, 0), "wait") && launch_photons(it + inflight);
     }
     if (good && pix_count) {
       const SppmPixels px = sh.px[g];
-      if (sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + 2, pix_first, pix_count)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: eye pass: " + ctx->err); good = false; }
+      if (sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + EYE, pix_first, pix_count)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: eye pass: " + ctx->err); good = false; }
     }
     // grid tables are single-buffered, and the peers may not overwrite the shards this grid build reads before it is done
     if (good) good = ok(cudaStreamSynchronize(q), "eye pass");
@@ -210,17 +218,16 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
     const PathMap M = make_path_map(params->width, params->height, spp_cnt);
     const float n_emitted = (float)((double)sp.iterations * (double)sp.photons_per_iter);  // photon_mapper.rs:229-230
     if (good && M.total > 0) {
-      if (s->dev.has_objf) k_sppm_final<true><<<sms * 8, 128, 0, q>>>(s->dev, Pf, M, sh.px[g], n_emitted, B.accum, B.cnt + 2);
-      else k_sppm_final<false><<<sms * 8, 128, 0, q>>>(s->dev, Pf, M, sh.px[g], n_emitted, B.accum, B.cnt + 2);
+      if (s->dev.has_objf) k_sppm_final<true><<<sms * 8, 128, 0, q>>>(s->dev, Pf, M, sh.px[g], n_emitted, B.accum, B.cnt + EYE);
+      else k_sppm_final<false><<<sms * 8, 128, 0, q>>>(s->dev, Pf, M, sh.px[g], n_emitted, B.accum, B.cnt + EYE);
       good = ok(cudaGetLastError(), "k_sppm_final");
     }
-    if (good) good = ok(cudaMemcpyAsync(hcnt + 2, B.cnt + 2, sizeof(SppmCounters), cudaMemcpyDeviceToHost, q), "memcpy") && ok(cudaStreamSynchronize(q), "final pass");
-    if (good) sh.eye_rays += hcnt[2].eye_rays;
+    if (good) good = ok(cudaMemcpyAsync(hcnt + EYE, B.cnt + EYE, sizeof(SppmCounters), cudaMemcpyDeviceToHost, q), "memcpy") && ok(cudaStreamSynchronize(q), "final pass");
+    if (good) sh.eye_rays += hcnt[EYE].eye_rays;
   }
   bar.wait();  // C: every accumulation buffer is complete; the root reduces and reads them in b200rt_render_sppm_multi
   bar.wait();  // D: the root is done with the peers' buffers
-  if (qp) { cudaStreamSynchronize(qp); cudaStreamDestroy(qp); }
-  PW.release();
+  for (int k = 0; k < SPPM_MAX_NB; ++k) { if (qp[k]) { cudaStreamSynchronize(qp[k]); cudaStreamDestroy(qp[k]); } PW[k].release(); }
   if (ev_grid) cudaEventDestroy(ev_grid);
   if (hcnt) cudaFreeHost(hcnt);
   B.release();
@@ -231,7 +238,7 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
 extern "C" int b200rt_render_sppm_multi(int32_t n_dev, b200rt_scene* const* scenes, const b200rt_camera* cam, const b200rt_params* params,
                                         const b200rt_sppm_params* sppm, float* accum_host, float* pixel_stats_host, b200rt_sppm_stats* stats) {
   if (n_dev < 1 || n_dev > B200RT_MULTI_MAX_DEV || n_dev > SPPM_MAX_SEGS || !scenes || !cam || !params || !sppm || !accum_host) return B200RT_ERR_INVALID;
-  for (int g = 0; g < n_dev; ++g) if (!scenes[g]) return B200RT_ERR_INVALID;
+  for (int g = 0; g < n_dev; ++g) { if (!scenes[g]) return B200RT_ERR_INVALID; SCENE_ALIVE(scenes[g]); }
   b200rt_ctx* root = scenes[0]->ctx;
   for (int g = 0; g < n_dev; ++g)
     for (int k = 0; k < g; ++k)
@@ -248,6 +255,7 @@ extern "C" int b200rt_render_sppm_multi(int32_t n_dev, b200rt_scene* const* scen
   const uint32_t n_pix = (uint32_t)params->width * params->height;
   SppmShared sh;
   sh.n_dev = n_dev;
+  sh.inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 3, 1, SPPM_MAX_NB - 1), sppm->iterations);
   std::memset(sh.pg, 0, sizeof(sh.pg)); std::memset(sh.pc, 0, sizeof(sh.pc)); std::memset(sh.px, 0, sizeof(sh.px)); std::memset(sh.accum, 0, sizeof(sh.accum));
   std::memset(sh.counts, 0, sizeof(sh.counts));
   HostBarrier bar(n_dev + 1);  // the device threads + this one (which does the root's reduce between barriers C and D)
@@ -255,8 +263,10 @@ extern "C" int b200rt_render_sppm_multi(int32_t n_dev, b200rt_scene* const* scen
   std::vector<std::thread> threads;
   for (int g = 0; g < n_dev; ++g) threads.emplace_back(sppm_multi_worker, g, std::ref(sh), std::ref(bar), scenes, cam, params, sppm);
   bar.wait();                                                 // buffers published
+  const auto t1 = std::chrono::steady_clock::now();
   for (int it = 0; it < sppm->iterations; ++it) bar.wait();   // A of every iteration
   bar.wait();                                                 // B
+  const auto t2 = std::chrono::steady_clock::now();
   bar.wait();                                                 // C
   cudaError_t e = cudaSuccess;
   if (!sh.failed) {
@@ -294,7 +304,10 @@ extern "C" int b200rt_render_sppm_multi(int32_t n_dev, b200rt_scene* const* scen
   if (stats) {
     std::memset(stats, 0, sizeof(*stats));
     stats->global_photons = sh.global_photons; stats->caustic_photons = sh.caustic_photons; stats->photon_rays = sh.photon_rays; stats->eye_rays = sh.eye_rays;
-    stats->ms_total = (float)(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() * 1e3);  // host clock around the whole call (buffer set-up included)
+    const auto t3 = std::chrono::steady_clock::now();
+    stats->ms_total = (float)(std::chrono::duration<double>(t3 - t0).count() * 1e3);  // host clock around the whole call (buffer set-up included)
+    stats->ms_eye = (float)(std::chrono::duration<double>(t2 - t1).count() * 1e3);    // host clock of the SPPM iterations (all devices: photon passes, grid builds, eye passes)
+    stats->ms_final = (float)(std::chrono::duration<double>(t3 - t2).count() * 1e3);  // host clock of the statistics gather, the final pass, the reduce, the copies out and the release
   }
   return B200RT_OK;
 }

@@ -52,6 +52,7 @@ int static_pool_address(b200rt_ctx* ctx, unsigned char** out) {
 
 extern "C" int b200rt_render_device_static(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, float* accum_dev, b200rt_stats* stats) {
   if (!s || !cam || !params || !accum_dev) return B200RT_ERR_INVALID;
+  SCENE_ALIVE(s);
   b200rt_ctx* ctx = s->ctx;
   int rc = validate_params(ctx, params);
   if (rc) return rc;

@@ -626,14 +626,29 @@ DEV SppmCube sppm_cube(const SppmGrid& G, int3 c0, int s) {
   q.z0 = max(0, c0.z - s); q.z1 = min(G.res - 1, c0.z + s);
   return q;
 }
+// Every photon of the cube, the whole warp on one grid row at a time: the lanes fetch the bounds of 32 rows together, then
+// stride over the photons of each non-empty row (the x-run of a row is contiguous in the cell-ordered array).  f(j, position,
+// ordinal) with ordinal = the photon's place in this enumeration.  (One row per lane, the first version, ran at 2-5 of 32
+// lanes: photons sit on surfaces, so a few of a cube's rows hold all of them.)  Called with the warp converged.
 template <class F>
-DEV void sppm_for_each_in_cube(const SppmGrid& G, const SppmCube& q, unsigned lane, F f) {  // rows of the cube over the lanes of the warp
+DEV void sppm_for_each_in_cube(const SppmGrid& G, const SppmCube& q, unsigned lane, F f) {
   const int ny = q.y1 - q.y0 + 1, rows = ny * (q.z1 - q.z0 + 1);
-  for (int row = (int)lane; row < rows; row += 32) {
-    const int z = q.z0 + row / ny, y = q.y0 + row % ny;
-    const uint32_t base = (uint32_t)((z * G.res + y) * G.res);
-    const uint32_t j1 = __ldg(&G.cell_start[base + (uint32_t)q.x1 + 1u]);
-    for (uint32_t j = __ldg(&G.cell_start[base + (uint32_t)q.x0]); j < j1; ++j) f(j, __ldg(G.pos + j));
+  uint32_t run = 0;
+  for (int r0 = 0; r0 < rows; r0 += 32) {
+    uint32_t j0 = 0, j1 = 0;
+    const int mine = r0 + (int)lane;
+    if (mine < rows) {
+      const uint32_t base = (uint32_t)(((q.z0 + mine / ny) * G.res + q.y0 + mine % ny) * G.res);
+      j0 = __ldg(&G.cell_start[base + (uint32_t)q.x0]); j1 = __ldg(&G.cell_start[base + (uint32_t)q.x1 + 1u]);
+    }
+    unsigned nonempty = __ballot_sync(0xffffffffu, j1 > j0);
+    while (nonempty) {
+      const int k = __ffs((int)nonempty) - 1;
+      nonempty &= nonempty - 1u;
+      const uint32_t b0 = __shfl_sync(0xffffffffu, j0, k), b1 = __shfl_sync(0xffffffffu, j1, k);
+      for (uint32_t j = b0 + lane; j < b1; j += 32) f(j, __ldg(G.pos + j), run + (j - b0));
+      run += b1 - b0;
+    }
   }
 }
 DEV uint32_t sppm_warp_sum(uint32_t v) {
@@ -655,9 +670,9 @@ DEV uint32_t sppm_cube_count(const SppmGrid& G, const SppmCube& q, unsigned lane
   before_me = incl - mine;
   return __shfl_sync(0xffffffffu, incl, 31);
 }
-// the want-th smallest (1-based) of keys[0, n): quickselect in place, then bisection between the extremes of the few left
+// the want-th smallest (1-based) of keys[0, n), 1 <= want <= n: quickselect in place down to one key per lane, then a rank by shuffles
 DEV uint32_t sppm_select_smem(uint32_t* keys, uint32_t n, uint32_t want, unsigned lane) {
-  while (n > 64u) {
+  while (n > 32u) {
     const uint32_t a = keys[0], b = keys[n >> 1], c = keys[n - 1u];
     const uint32_t pivot = max(min(a, b), min(max(a, b), c));  // median of three
     uint32_t below = 0, equal = 0;
@@ -679,23 +694,22 @@ DEV uint32_t sppm_select_smem(uint32_t* keys, uint32_t n, uint32_t want, unsigne
     __syncwarp();
     n = out;
   }
-  uint32_t mn = 0xffffffffu, mx = 0u;
-  for (uint32_t i = lane; i < n; i += 32) { mn = min(mn, keys[i]); mx = max(mx, keys[i]); }
-  uint32_t lo = __reduce_min_sync(0xffffffffu, mn), hi = __reduce_max_sync(0xffffffffu, mx);
-  while (lo < hi) {
-    const uint32_t mid = lo + ((hi - lo) >> 1);
-    uint32_t cc = 0;
-    for (uint32_t i = lane; i < n; i += 32) cc += keys[i] <= mid ? 1u : 0u;
-    if (sppm_warp_sum(cc) >= want) hi = mid; else lo = mid + 1u;
+  // at most 32 left: every lane ranks its key among them (ties broken by lane), the lane of rank want - 1 holds the answer
+  const uint32_t v = lane < n ? keys[lane] : 0xffffffffu;
+  uint32_t rank = 0;
+#pragma unroll
+  for (int o = 0; o < 32; ++o) {
+    const uint32_t u = __shfl_sync(0xffffffffu, v, o);
+    rank += (u < v || (u == v && (unsigned)o < lane)) ? 1u : 0u;
   }
-  return lo;
+  const unsigned holder = __ballot_sync(0xffffffffu, lane < n && rank == want - 1u);
+  return __shfl_sync(0xffffffffu, v, __ffs((int)holder) - 1);
 }
 // the want-th smallest squared distance (as float bits) of the n_in photons of cube q; `before_me` from sppm_cube_count
 DEV uint32_t sppm_select_cube(const SppmGrid& G, const SppmCube& q, float3 p, uint32_t* keys, uint32_t n_in, uint32_t before_me, uint32_t want, unsigned lane) {
   __syncwarp();
   if (n_in <= SPPM_KNN_CAP) {
-    uint32_t at = before_me;
-    sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) { keys[at++] = __float_as_uint(sppm_d2(pos, p)); });
+    sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos, uint32_t at) { keys[at] = __float_as_uint(sppm_d2(pos, p)); });
     __syncwarp();
     return sppm_select_smem(keys, n_in, want, lane);
   }
@@ -705,7 +719,7 @@ DEV uint32_t sppm_select_cube(const SppmGrid& G, const SppmCube& q, float3 p, ui
     const unsigned long long span = (unsigned long long)(hi - lo) + 1ull;
     for (uint32_t i = lane; i < SPPM_KNN_CAP; i += 32) keys[i] = 0u;
     __syncwarp();
-    sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) {
+    sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos, uint32_t) {
       const uint32_t key = __float_as_uint(sppm_d2(pos, p));
       if (key >= lo && key <= hi) atomicAdd(&keys[(uint32_t)(((unsigned long long)(key - lo) * SPPM_KNN_CAP) / span)], 1u);
     });
@@ -739,7 +753,7 @@ DEV uint32_t sppm_select_cube(const SppmGrid& G, const SppmCube& q, float3 p, ui
       __shared__ uint32_t s_cursor[4];
       if (lane == 0) s_cursor[threadIdx.x >> 5] = 0u;
       __syncwarp();
-      sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos) {
+      sppm_for_each_in_cube(G, q, lane, [&](uint32_t, float4 pos, uint32_t) {
         const uint32_t key = __float_as_uint(sppm_d2(pos, p));
         if (key >= lo && key <= hi) keys[atomicAdd(&s_cursor[threadIdx.x >> 5], 1u)] = key;
       });
@@ -786,7 +800,7 @@ __global__ void __launch_bounds__(128) k_sppm_knn(SppmGrid Gg, SppmGrid Gc, Sppm
         whole = q.x0 == 0 && q.y0 == 0 && q.z0 == 0 && q.x1 == G.res - 1 && q.y1 == G.res - 1 && q.z1 == G.res - 1;
         n_in = sppm_cube_count(G, q, lane, before_me);
       }
-      sppm_for_each_in_cube(G, q, lane, [&](uint32_t j, float4 pos) {
+      sppm_for_each_in_cube(G, q, lane, [&](uint32_t j, float4 pos, uint32_t) {
         if (__float_as_uint(sppm_d2(pos, p)) <= tau) flux = flux + sppm_photon_flux(G, j, pos, p, bsdf);
       });
 #pragma unroll

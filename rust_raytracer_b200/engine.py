@@ -17,7 +17,11 @@ class Context:
         if rc:
             raise B200RTError(rc, F.lib().b200rt_global_error().decode())
         self.device = device
-        self._scenes = weakref.WeakSet()  # a scene must be destroyed before its context (it keeps a pointer to it)
+        # A scene should be destroyed before its context.  The weak set lets close() do that in the ordinary case; it cannot in the
+        # garbage collector's (weak references to unreachable objects are cleared BEFORE their finalizers run, so a context
+        # collected together with its scenes no longer sees them) — there the library's own bookkeeping takes over: it
+        # orphans the scenes of a destroyed context, and b200rt_scene_destroy of an orphan only frees its tables.
+        self._scenes = weakref.WeakSet()
 
     def _ok(self, rc):
         if rc:

@@ -154,3 +154,26 @@ def test_concurrent_pipelines_render_the_same_paths(ctx, integrator):
         assert s.wavefront_iterations > s1.wavefront_iterations  # iterations are counted per pipeline
         np.testing.assert_allclose(a, a1, rtol=1e-4, atol=1e-4)
         assert np.all(a[..., 3] == 7)
+
+
+@pytest.mark.gpu
+def test_context_destroyed_before_its_scene_orphans_the_scene(ctx):
+    """A garbage collector may finalize a context before its scenes (weak references to unreachable objects are cleared before
+    their finalizers run).  The library orphans the scenes of a destroyed context: entry points answer ERR_INVALID instead of
+    following a dangling pointer, b200rt_scene_destroy still frees the tables, and no CUDA error is left behind for the next call."""
+    import ctypes as C
+    sb = scene_builder("cornell_ref")
+    c2 = rt.Context(0)
+    sc = rt.Scene(c2, sb)
+    h_ctx, c2._h = c2._h, None  # destroy the context behind the wrapper's back, as the collector's order would
+    assert F.lib().b200rt_ctx_destroy(h_ctx) == 0
+    acc = np.zeros((16, 16, 4), np.float32)
+    st = F.Stats()
+    p = rt.copy_params(sb.params, width=16, height=16, spp_count=1)
+    rc = F.lib().b200rt_render(sc._h, C.byref(sb.camera), C.byref(p), acc.ctypes.data_as(C.c_void_p), C.byref(st))
+    assert rc == F.ERR_INVALID and b"context has been destroyed" in F.lib().b200rt_global_error()
+    h_sc, sc._h = sc._h, None
+    assert F.lib().b200rt_scene_destroy(h_sc) == 0
+    # the session context is untouched and sees no stale error
+    a, _ = rt.Scene(ctx, sb).render(sb.camera, p)
+    assert np.isfinite(a).all() and a[..., 3].min() == 1
