@@ -51,6 +51,7 @@ struct b200rt_scene {
   uint32_t n_nodes = 0, n_prims = 0;
 };
 
+namespace { void multi_forget_device(int device); }  // api_multi.cuh
 static thread_local std::string g_global_err;
 // a scene whose context has been destroyed
 #define SCENE_ALIVE(s)                                                                                              \
@@ -126,6 +127,7 @@ int b200rt_ctx_destroy(b200rt_ctx* c) {
   if (!c) return B200RT_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  multi_forget_device(c->device);
   {
     std::lock_guard<std::mutex> lock(c->scenes_mutex);
     for (b200rt_scene* s : c->scenes) s->ctx = nullptr;  // orphaned: b200rt_scene_destroy still frees their tables

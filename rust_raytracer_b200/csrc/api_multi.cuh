@@ -71,6 +71,18 @@ NcclApi& nccl_api() {  // call with g_multi_mutex held
   return g_nccl;
 }
 
+// b200rt_ctx_destroy: the NCCL cliques that include the context's device are destroyed with it (a clique is cached for the
+// calls to come, not for the process exit: communicators left alive there are torn down by NCCL's own exit handlers, after
+// the CUDA context they point into)
+void multi_forget_device(int device) {
+  std::lock_guard<std::mutex> lock(g_multi_mutex);
+  for (auto it = g_nccl_comms.begin(); it != g_nccl_comms.end();) {
+    if (std::find(it->first.begin(), it->first.end(), device) == it->first.end()) { ++it; continue; }
+    if (g_nccl.CommDestroy) for (rt_ncclComm_t c : it->second) if (c) g_nccl.CommDestroy(c);
+    it = g_nccl_comms.erase(it);
+  }
+}
+
 // ---- peer-memory reduce: dst (on the launching device) += sum of the peers' buffers, read over NVLink
 struct PeerSrc { const float4* p[B200RT_MULTI_MAX_DEV]; int n; };
 __global__ void __launch_bounds__(256) k_reduce_peers(float4* __restrict__ dst, PeerSrc src, size_t n4) {

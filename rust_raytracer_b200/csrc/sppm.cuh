@@ -544,6 +544,9 @@ __global__ void __launch_bounds__(128) k_sppm_eye_trace(DevScene S, RenderConst 
 #ifndef SPPM_GATHER_LANES
 #define SPPM_GATHER_LANES 8
 #endif
+#ifndef SPPM_GATHER_CLIP
+#define SPPM_GATHER_CLIP 1
+#endif
 DEV void sppm_gather_map(const SppmGrid& G, bool on, float3 p, float3 bsdf, float radius2, unsigned sub, float3& flux, uint32_t& count) {
   flux = f3(0, 0, 0); count = 0;
   const float r = sqrtf(radius2), rr = r * r;
@@ -555,8 +558,25 @@ DEV void sppm_gather_map(const SppmGrid& G, bool on, float3 p, float3 bsdf, floa
     uint32_t j0 = 0, j1 = 0;
     const int mine = r0 + (int)sub;
     if (mine < rows) {
-      const uint32_t base = (uint32_t)(((a.z + mine / ny) * G.res + a.y + mine % ny) * G.res);
-      j0 = __ldg(&G.cell_start[base + (uint32_t)a.x]); j1 = __ldg(&G.cell_start[base + (uint32_t)b.x + 1u]);
+      // the cells of this row the SPHERE reaches, not the box: the row's distance from the point in y and z leaves
+      // sqrt(r^2 - dy^2 - dz^2) along x (cell faces moved out by 1e-4 cell: a photon is binned with one float rounding)
+      const int y = a.y + mine % ny, z = a.z + mine / ny;
+      const float slack = 1e-4f * G.cell;
+      const float ylo = G.lo.y + (float)y * G.cell, zlo = G.lo.z + (float)z * G.cell;
+      const float dy = fmaxf(0.f, fmaxf(ylo - slack - p.y, p.y - (ylo + G.cell + slack)));
+      const float dz = fmaxf(0.f, fmaxf(zlo - slack - p.z, p.z - (zlo + G.cell + slack)));
+#if SPPM_GATHER_CLIP
+      const float rem = rr - dy * dy - dz * dz;
+#else
+      const float rem = 1e30f + 0.f * (dy + dz);  // A/B: the whole box (tools/dbg/sppm_clip_check.py compares the per-pixel photon counts)
+#endif
+      if (rem >= 0.f) {
+        const float dx = sqrtf(rem) + slack;
+        const int xa = max(a.x, min(G.res - 1, max(0, (int)floorf((p.x - dx - G.lo.x) * G.inv_cell))));
+        const int xb = min(b.x, min(G.res - 1, max(0, (int)floorf((p.x + dx - G.lo.x) * G.inv_cell))));
+        const uint32_t base = (uint32_t)((z * G.res + y) * G.res);
+        if (xa <= xb) { j0 = __ldg(&G.cell_start[base + (uint32_t)xa]); j1 = __ldg(&G.cell_start[base + (uint32_t)xb + 1u]); }
+      }
     }
 #pragma unroll
     for (int k = 0; k < SPPM_GATHER_LANES; ++k) {
@@ -648,6 +668,43 @@ DEV void sppm_for_each_in_cube(const SppmGrid& G, const SppmCube& q, unsigned la
       const uint32_t b0 = __shfl_sync(0xffffffffu, j0, k), b1 = __shfl_sync(0xffffffffu, j1, k);
       for (uint32_t j = b0 + lane; j < b1; j += 32) f(j, __ldg(G.pos + j), run + (j - b0));
       run += b1 - b0;
+    }
+  }
+}
+// The same enumeration restricted to the cells a SPHERE around p reaches (radius^2 = rr): per row, the x-range left by the
+// row's distance from p in y and z (cell faces moved out by 1e-4 cell, as in the radius gather).  The inner loop has a
+// warp-uniform trip count, so f may vote: f(j, position, valid).
+template <class F>
+DEV void sppm_for_each_in_ball(const SppmGrid& G, const SppmCube& q, float3 p, float rr, unsigned lane, F f) {
+  const int ny = q.y1 - q.y0 + 1, rows = ny * (q.z1 - q.z0 + 1);
+  const float slack = 1e-4f * G.cell;
+  for (int r0 = 0; r0 < rows; r0 += 32) {
+    uint32_t j0 = 0, j1 = 0;
+    const int mine = r0 + (int)lane;
+    if (mine < rows) {
+      const int y = q.y0 + mine % ny, z = q.z0 + mine / ny;
+      const float ylo = G.lo.y + (float)y * G.cell, zlo = G.lo.z + (float)z * G.cell;
+      const float dy = fmaxf(0.f, fmaxf(ylo - slack - p.y, p.y - (ylo + G.cell + slack)));
+      const float dz = fmaxf(0.f, fmaxf(zlo - slack - p.z, p.z - (zlo + G.cell + slack)));
+      const float rem = rr - dy * dy - dz * dz;
+      if (rem >= 0.f) {
+        const float dx = sqrtf(rem) + slack;
+        const int xa = max(q.x0, min(G.res - 1, max(0, (int)floorf((p.x - dx - G.lo.x) * G.inv_cell))));
+        const int xb = min(q.x1, min(G.res - 1, max(0, (int)floorf((p.x + dx - G.lo.x) * G.inv_cell))));
+        const uint32_t base = (uint32_t)((z * G.res + y) * G.res);
+        if (xa <= xb) { j0 = __ldg(&G.cell_start[base + (uint32_t)xa]); j1 = __ldg(&G.cell_start[base + (uint32_t)xb + 1u]); }
+      }
+    }
+    unsigned nonempty = __ballot_sync(0xffffffffu, j1 > j0);
+    while (nonempty) {
+      const int k = __ffs((int)nonempty) - 1;
+      nonempty &= nonempty - 1u;
+      const uint32_t b0 = __shfl_sync(0xffffffffu, j0, k), b1 = __shfl_sync(0xffffffffu, j1, k);
+      for (uint32_t jb = b0; jb < b1; jb += 32) {
+        const uint32_t j = jb + lane;
+        const bool valid = j < b1;
+        f(j, valid ? __ldg(G.pos + j) : make_float4(0.f, 0.f, 0.f, 0.f), valid);
+      }
     }
   }
 }
@@ -789,19 +846,34 @@ __global__ void __launch_bounds__(128) k_sppm_knn(SppmGrid Gg, SppmGrid Gc, Sppm
         n_in = sppm_cube_count(G, q, lane, before_me);
         if (n_in >= k || whole) break;
       }
+      // the k-th smallest squared distance inside this cube: the true one if it lies within s cells, else an upper bound of it
+      tau = sppm_select_cube(G, q, p, keys, n_in, before_me, n_in < k ? n_in : k, lane);
       for (;;) {
-        tau = sppm_select_cube(G, q, p, keys, n_in, before_me, n_in < k ? n_in : k, lane);
         const float reach = (float)s * G.cell;
         if (whole || tau <= __float_as_uint(reach * reach)) break;  // no photon outside the cube is nearer than s cells
-        // the k-th of this cube bounds the true one: the cube that reaches that far holds the k nearest of the map
-        const int s_need = (int)ceilf(sqrtf(__uint_as_float(tau)) * G.inv_cell * 1.0001f);
+        // the cube that reaches as far as the bound holds the k nearest of the map, all of them inside the bound's sphere:
+        // only the cells that sphere touches are read, and only the distances up to the bound are kept
+        const float bound = __uint_as_float(tau);
+        const int s_need = (int)ceilf(sqrtf(bound) * G.inv_cell * 1.0001f);
         s = max(s + 1, min(s_need, G.res));
         q = sppm_cube(G, c0, s);
         whole = q.x0 == 0 && q.y0 == 0 && q.z0 == 0 && q.x1 == G.res - 1 && q.y1 == G.res - 1 && q.z1 == G.res - 1;
-        n_in = sppm_cube_count(G, q, lane, before_me);
+        __syncwarp();
+        uint32_t n2 = 0;  // warp-uniform
+        sppm_for_each_in_ball(G, q, p, bound, lane, [&](uint32_t, float4 pos, bool valid) {
+          const uint32_t key = __float_as_uint(sppm_d2(pos, p));
+          const bool keep = valid && key <= tau;
+          const unsigned m = __ballot_sync(0xffffffffu, keep);
+          const uint32_t at = n2 + __popc(m & ((1u << lane) - 1u));
+          if (keep && at < SPPM_KNN_CAP) keys[at] = key;
+          n2 += __popc(m);
+        });
+        __syncwarp();
+        if (n2 <= SPPM_KNN_CAP) tau = sppm_select_smem(keys, n2, k, lane);  // n2 >= k: the k of the smaller cube are among them
+        else { n_in = sppm_cube_count(G, q, lane, before_me); tau = sppm_select_cube(G, q, p, keys, n_in, before_me, k, lane); }
       }
-      sppm_for_each_in_cube(G, q, lane, [&](uint32_t j, float4 pos, uint32_t) {
-        if (__float_as_uint(sppm_d2(pos, p)) <= tau) flux = flux + sppm_photon_flux(G, j, pos, p, bsdf);
+      sppm_for_each_in_ball(G, q, p, __uint_as_float(tau), lane, [&](uint32_t j, float4 pos, bool valid) {
+        if (valid && __float_as_uint(sppm_d2(pos, p)) <= tau) flux = flux + sppm_photon_flux(G, j, pos, p, bsdf);
       });
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) { flux.x += __shfl_xor_sync(0xffffffffu, flux.x, o); flux.y += __shfl_xor_sync(0xffffffffu, flux.y, o); flux.z += __shfl_xor_sync(0xffffffffu, flux.z, o); }
