@@ -33,6 +33,10 @@ struct b200rt_ctx {
   size_t stage_bytes = 0;
   void* spare_block = nullptr;
   size_t spare_bytes = 0;
+  // b200rt_render_sppm's device buffers (photon buffers of the passes in flight, cell-ordered maps, photon queues: GBs) kept
+  // between calls of the same shape, like the wavefront pools above; owned through an opaque pointer (api_sppm.cuh)
+  void* sppm_cache = nullptr;
+  void (*sppm_cache_free)(void*) = nullptr;
   const WfBuffers* static_wf = nullptr;  // set for the duration of b200rt_render_device_static: render_wavefront takes its queues from there
   // the scenes created on this context and not yet destroyed: b200rt_ctx_destroy orphans them (ctx = nullptr), so that a host
   // that releases a context before its scenes (a garbage collector does) gets B200RT_ERR_INVALID from them, not a dangling pointer
@@ -138,6 +142,7 @@ int b200rt_ctx_destroy(b200rt_ctx* c) {
     if (c->wf_shadow_block[k]) cudaFree(c->wf_shadow_block[k]);
     if (c->pipe_stream[k]) cudaStreamDestroy(c->pipe_stream[k]);
   }
+  if (c->sppm_cache && c->sppm_cache_free) c->sppm_cache_free(c->sppm_cache);
   if (c->fork_ev) cudaEventDestroy(c->fork_ev);
   if (c->spare_block) cudaFree(c->spare_block);
   if (c->stage_host) cudaFreeHost(c->stage_host);

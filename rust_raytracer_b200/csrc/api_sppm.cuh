@@ -122,6 +122,19 @@ struct SppmPhotonWf {
   }
 };
 
+// scene-dependent part of a photon queue set: bins, kernel variants, launch sizes (cheap; every call)
+int sppm_photon_wf_configure(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W) {
+  wf_bin_layout(s->n_prims, W.B.n_bins, W.B.bin_mul);
+  W.sms = ctx->prop.multiProcessorCount;
+  W.objf = s->dev.has_objf != 0;
+  int occ_ext = 1, occ_shade = 1;
+  CU_CHECK(ctx, W.objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<false>, 128, 0));
+  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_sppm_ph_shade, 128, 0));
+  W.grid_ext = W.sms * (occ_ext > 0 ? occ_ext : 1);
+  W.grid_shade = W.sms * (occ_shade > 0 ? occ_shade : 1);
+  W.plan = env_int("B200RT_SPPM_PHOTON_ITERS", 12, 1, SppmPhotonWf::MAX_ITERS);
+  return B200RT_OK;
+}
 int sppm_photon_wf_alloc(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W, unsigned int n_photons) {
   const size_t P = ((size_t)n_photons + 31u) & ~(size_t)31u;
   size_t off = 0;
@@ -138,17 +151,8 @@ int sppm_photon_wf_alloc(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W
   W.B.hit = (uint4*)(b + o_hit); W.B.bin_count = (unsigned int*)(b + o_bc); W.B.bin_off = (unsigned int*)(b + o_bo); W.B.cnt = (WfCounters*)(b + o_cnt);
   W.B.sh_o = W.B.sh_d = W.B.sh_c = nullptr; W.B.sh_seed = nullptr;
   W.B.pool = (unsigned int)P;
-  wf_bin_layout(s->n_prims, W.B.n_bins, W.B.bin_mul);
   W.M.tiles_x = 0; W.M.per_sample = n_photons; W.M.total = n_photons;
-  W.sms = ctx->prop.multiProcessorCount;
-  W.objf = s->dev.has_objf != 0;
-  int occ_ext = 1, occ_shade = 1;
-  CU_CHECK(ctx, W.objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<false>, 128, 0));
-  CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_sppm_ph_shade, 128, 0));
-  W.grid_ext = W.sms * (occ_ext > 0 ? occ_ext : 1);
-  W.grid_shade = W.sms * (occ_shade > 0 ? occ_shade : 1);
-  W.plan = env_int("B200RT_SPPM_PHOTON_ITERS", 12, 1, SppmPhotonWf::MAX_ITERS);
-  return B200RT_OK;
+  return sppm_photon_wf_configure(ctx, s, W);
 }
 
 // One photon pass on `qp`: `W.plan` wavefront iterations carry the bulk of the photons (the queue shrinks by a third per bounce),
@@ -194,6 +198,20 @@ void sppm_photon_wf_finish(SppmPhotonWf& W, SppmCounters* cnt_host) {
   W.plan = std::min(std::max(used == W.launched ? used + 4 : used, 2), 64);
 }
 
+// What b200rt_render_sppm keeps on its context between calls of the same shape (the cudaMalloc / cudaFree of these GBs was a
+// third of the call's wall time: 116 ms on the host clock against 81 ms of device time).  Taken out of the context for the
+// duration of a call and put back at its end; a call of another shape, or a failed one, releases it.
+struct SppmCache {
+  SppmBuffers B;
+  SppmPhotonWf PW[SPPM_MAX_NB];
+  unsigned int cap = 0, photons = 0;
+  uint32_t n_pix = 0;
+  int NB = 0;
+  bool mega = false;
+  void release() { B.release(); for (int k = 0; k < SPPM_MAX_NB; ++k) PW[k].release(); }
+  static void destroy(void* p) { SppmCache* c = (SppmCache*)p; c->release(); delete c; }
+};
+
 }  // namespace
 
 extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, const b200rt_params* params, const b200rt_sppm_params* sppm,
@@ -215,23 +233,40 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   const uint32_t n_pix = (uint32_t)params->width * params->height;
   const unsigned int cap = (unsigned int)sppm->photons_per_iter * 16u;  // stored photons per iteration (~1.5 per emitted photon in a Cornell box)
   const uint32_t max_cells = (uint32_t)SPPM_MAX_RES * SPPM_MAX_RES * SPPM_MAX_RES;
-  SppmBuffers B;
   cudaError_t e = cudaSuccess;
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
   // Photon passes in flight: a pass ends in a tail of a few photons that bounce hundreds of times (one dependent traversal after
   // the other: ms), and no pass depends on the pixel statistics (photon_mapper.rs:154-160) — so several run ahead of the eye pass,
   // each on its own stream with its own queues and buffers, and the tail of one hides under the bulk of the next.
-  const int inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 3, 1, SPPM_MAX_NB - 1), sppm->iterations);
+  const int inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 7, 1, SPPM_MAX_NB - 1), sppm->iterations);
   const int NB = inflight + 1;
-  for (int k = 0; k < NB; ++k) { alloc((void**)&B.pg[k], (size_t)cap * 64); alloc((void**)&B.pc[k], (size_t)cap * 64); }
-  if (e == cudaSuccess) e = B.alloc_maps(cap, n_pix);
-  alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
-  alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
-  alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
-  alloc((void**)&B.accum, 16 * (size_t)n_pix);
-  alloc((void**)&B.cnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters));  // [k < NB]: the photon pass into buffer k; [SPPM_MAX_NB]: eye + final pass
-  if (e != cudaSuccess) { B.release(); ctx->err = std::string("sppm: ") + cudaGetErrorString(e); return B200RT_ERR_NOMEM; }
-  auto fail = [&](int code) { B.release(); return code; };
+  const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;  // A/B: the one-thread-per-photon kernel of round 1
+  // the buffers: the context's cached set when it has this call's shape, else a fresh one
+  SppmCache* cache = (SppmCache*)ctx->sppm_cache;
+  ctx->sppm_cache = nullptr;
+  if (cache && !(cache->cap == cap && cache->n_pix == n_pix && cache->NB == NB && cache->photons == (unsigned int)sppm->photons_per_iter && cache->mega == photons_mega)) {
+    SppmCache::destroy(cache);
+    cache = nullptr;
+  }
+  const bool fresh = cache == nullptr;
+  if (fresh) {
+    cache = new (std::nothrow) SppmCache();
+    if (!cache) return B200RT_ERR_NOMEM;
+    cache->cap = cap; cache->n_pix = n_pix; cache->NB = NB; cache->photons = (unsigned int)sppm->photons_per_iter; cache->mega = photons_mega;
+  }
+  SppmBuffers& B = cache->B;
+  SppmPhotonWf* PW = cache->PW;
+  if (fresh) {
+    for (int k = 0; k < NB; ++k) { alloc((void**)&B.pg[k], (size_t)cap * 64); alloc((void**)&B.pc[k], (size_t)cap * 64); }
+    if (e == cudaSuccess) e = B.alloc_maps(cap, n_pix);
+    alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
+    alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
+    alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
+    alloc((void**)&B.accum, 16 * (size_t)n_pix);
+    alloc((void**)&B.cnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters));  // [k < NB]: the photon pass into buffer k; [SPPM_MAX_NB]: eye + final pass
+  }
+  if (e != cudaSuccess) { SppmCache::destroy(cache); ctx->err = std::string("sppm: ") + cudaGetErrorString(e); return B200RT_ERR_NOMEM; }
+  auto fail = [&](int code) { SppmCache::destroy(cache); cache = nullptr; return code; };
 #define SPPM_CHECK(call)                                                                          \
   do {                                                                                            \
     cudaError_t e_ = (call);                                                                      \
@@ -260,10 +295,9 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   // blocks per SM (150 / 128 registers per thread let 3 / 4 blocks of 128 threads reside).  Measured at the reference
   // configuration, serial 339 ms; overlapped with a photon grid of 1 / 2 / 3 / 4 blocks per SM: 303 / 276 / 264 / 253 ms
   const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8);
-  // photon pass: through the wavefront queues (default), or the one-thread-per-photon kernel of round 1 (A/B)
-  const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;
-  SppmPhotonWf PW[SPPM_MAX_NB];
+  // photon pass: through the wavefront queues (default), or the one-thread-per-photon kernel of round 1 (photons_mega, A/B)
   const bool trace = env_int("B200RT_SPPM_TRACE", 0, 0, 1) != 0;
+  const char* dump_prefix = std::getenv("B200RT_SPPM_DUMP");
   cudaStream_t qp[SPPM_MAX_NB] = {};
   cudaEvent_t ev_ph[SPPM_MAX_NB][2] = {}, ev_eye = nullptr, ev_grid = nullptr;  // ev_ph, ev_eye: timing only
   SppmCounters* hcnt = nullptr;  // pinned: [k < NB] photon counters, [SPPM_MAX_NB] eye counters
@@ -275,7 +309,11 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     if (ev_eye) cudaEventDestroy(ev_eye);
     if (ev_grid) cudaEventDestroy(ev_grid);
     if (hcnt) cudaFreeHost(hcnt);
-    for (int k = 0; k < SPPM_MAX_NB; ++k) PW[k].release();
+    if (code == B200RT_OK) {  // the buffers stay with the context for the next call of this shape
+      if (ctx->sppm_cache && ctx->sppm_cache_free) ctx->sppm_cache_free(ctx->sppm_cache);
+      ctx->sppm_cache = cache; ctx->sppm_cache_free = &SppmCache::destroy;
+      return code;
+    }
     return fail(code);
   };
 #undef SPPM_CHECK
@@ -287,7 +325,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   for (int k = 0; k < NB; ++k) {
     SPPM_CHECK(cudaStreamCreateWithFlags(&qp[k], cudaStreamNonBlocking));
     for (int b = 0; b < 2; ++b) SPPM_CHECK(cudaEventCreate(&ev_ph[k][b]));
-    if (!photons_mega && (rc = sppm_photon_wf_alloc(ctx, s, PW[k], (unsigned int)sp.photons_per_iter)) != 0) return fail2(rc);
+    if (!photons_mega && (rc = fresh ? sppm_photon_wf_alloc(ctx, s, PW[k], (unsigned int)sp.photons_per_iter) : sppm_photon_wf_configure(ctx, s, PW[k])) != 0) return fail2(rc);
   }
   SPPM_CHECK(cudaEventCreate(&ev_eye));
   SPPM_CHECK(cudaEventCreate(&ev_grid));
@@ -345,6 +383,22 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     // the grid tables (cell_count, cursor, start, sg, sc) are single-buffered and the stage events are reused:
     // the host lets the eye pass finish before it builds the next grid — the next photon passes are already running
     SPPM_CHECK(cudaStreamSynchronize(q));
+    if (dump_prefix && *dump_prefix && it < 4) {  // test hook: this iteration's cell-ordered maps and visible points, for a brute-force check of the look-ups
+      std::vector<float4> buf;
+      const std::string path = std::string(dump_prefix) + ".it" + std::to_string(it) + ".bin";
+      FILE* f = std::fopen(path.c_str(), "wb");
+      if (f) {
+        const uint32_t head[4] = {h.n_global, h.n_caustic, n_pix, 0u};
+        std::fwrite(head, 4, 4, f);
+        auto put = [&](const float4* dev, size_t n) {
+          buf.resize(n);
+          if (n && cudaMemcpy(buf.data(), dev, 16 * n, cudaMemcpyDeviceToHost) == cudaSuccess) std::fwrite(buf.data(), 16, n, f);
+        };
+        put(Gg.pos, h.n_global); put(Gg.attr, 2 * (size_t)h.n_global); put(Gc.pos, h.n_caustic); put(Gc.attr, 2 * (size_t)h.n_caustic);
+        put(B.vp, n_pix); put(B.vb, n_pix);
+        std::fclose(f);
+      }
+    }
     float ms_g = 0.f, ms_e = 0.f;
     if (cudaEventElapsedTime(&ms_g, ctx->sev[0], ev_grid) == cudaSuccess) local.ms_grid += ms_g;
     if (cudaEventElapsedTime(&ms_e, ev_grid, ev_eye) == cudaSuccess) local.ms_eye += ms_e;
@@ -386,7 +440,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   if (cudaEventElapsedTime(&ms, ctx->sev[0], ctx->sev[1]) == cudaSuccess) local.ms_final = ms;
   if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) local.ms_total = ms;
 #undef SPPM_CHECK
-  fail2(B200RT_OK);  // releases the stream, the events, the pinned counters and the device buffers
+  fail2(B200RT_OK);  // releases the streams, the events and the pinned counters; the device buffers go back to the context
   if (stats) *stats = local;
   return B200RT_OK;
 }

@@ -255,7 +255,7 @@ extern "C" int b200rt_render_sppm_multi(int32_t n_dev, b200rt_scene* const* scen
   const uint32_t n_pix = (uint32_t)params->width * params->height;
   SppmShared sh;
   sh.n_dev = n_dev;
-  sh.inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 3, 1, SPPM_MAX_NB - 1), sppm->iterations);
+  sh.inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 7, 1, SPPM_MAX_NB - 1), sppm->iterations);
   std::memset(sh.pg, 0, sizeof(sh.pg)); std::memset(sh.pc, 0, sizeof(sh.pc)); std::memset(sh.px, 0, sizeof(sh.px)); std::memset(sh.accum, 0, sizeof(sh.accum));
   std::memset(sh.counts, 0, sizeof(sh.counts));
   HostBarrier bar(n_dev + 1);  // the device threads + this one (which does the root's reduce between barriers C and D)

@@ -162,3 +162,82 @@ def test_sppm_multi_argument_errors(ctx):
         rt.render_sppm_multi([scene], sb.camera, p, iterations=0, photons_per_iter=100)
     acc, st = rt.render_sppm_multi([scene], sb.camera, p, iterations=2, photons_per_iter=3000)  # one device: no peers at all
     assert st.global_photons > 1000 and np.all(acc[..., 3] == 1)
+
+
+def _read_sppm_dump(path):
+    raw = np.fromfile(path, dtype=np.uint8)
+    n_g, n_c, n_pix, _ = np.frombuffer(raw[:16].tobytes(), dtype=np.uint32)
+    f = np.frombuffer(raw[16:].tobytes(), dtype=np.float32).reshape(-1, 4)
+    o = 0
+    out = {}
+    for name, n in (("g_pos", n_g), ("g_attr", 2 * n_g), ("c_pos", n_c), ("c_attr", 2 * n_c), ("vp", n_pix), ("vb", n_pix)):
+        out[name] = f[o:o + int(n)]
+        o += int(n)
+    assert o == len(f)
+    return out
+
+
+def _d2(pos, p):
+    """sppm_d2 of sppm.cuh: f32 subtractions, dx*dx rounded, then two fused multiply-adds (exact in f64, rounded once)."""
+    d = (pos[None, :, :3] - p[:, None, :3]).astype(np.float32)
+    t = (d[..., 0] * d[..., 0]).astype(np.float32)
+    t = (d[..., 1].astype(np.float64) ** 2 + t.astype(np.float64)).astype(np.float32)
+    return (d[..., 2].astype(np.float64) ** 2 + t.astype(np.float64)).astype(np.float32), d
+
+
+def _flux(d, d2, sel, attr, bsdf):
+    """sppm_photon_flux summed over the selected photons: bsdf * power * (1 - |n . d/|d||)"""
+    power, nrm = attr[0::2, :3], attr[1::2, :3]
+    dn = np.abs(np.einsum("pnk,nk->pn", d.astype(np.float64), nrm.astype(np.float64)) / np.sqrt(np.maximum(d2.astype(np.float64), 1e-300)))
+    w = np.where(sel, 1.0 - dn, 0.0)
+    return bsdf[:, :3].astype(np.float64) * (w @ power.astype(np.float64))
+
+
+@pytest.mark.gpu
+def test_sppm_lookups_match_brute_force(ctx, tmp_path):
+    """The two look-ups of SPPM::update, pinned photon for photon (B200RT_SPPM_DUMP hands out every iteration's cell-ordered
+    maps and visible points): the k-nearest start (PhotonMap::estimate_flux_by_count, photon_mapper.rs:77-96: radius^2 = the k-th
+    smallest squared distance, flux over those k) of k_sppm_knn against a sort over ALL photons, and the radius gather of the next
+    iteration (estimate_flux_within_radius, 99-114: squared distance < radius^2; N' = N + floor(alpha M), R'^2 = R^2 N' / (N + M),
+    49-64) of k_sppm_gather against a count over ALL photons."""
+    sb = scene_builder("cornell_ref")
+    scene = rt.Scene(ctx, sb)
+    w = h = 32
+    p = rt.copy_params(sb.params, width=w, height=h, spp_count=1, seed=11)
+    prefix = str(tmp_path / "sppm")
+    os.environ["B200RT_SPPM_DUMP"] = prefix
+    try:
+        _, px1, _ = scene.render_sppm(sb.camera, p, iterations=1, photons_per_iter=20000, want_pixel_stats=True)
+        _, px2, _ = scene.render_sppm(sb.camera, p, iterations=2, photons_per_iter=20000, want_pixel_stats=True)
+    finally:
+        del os.environ["B200RT_SPPM_DUMP"]
+    px1, px2 = px1.reshape(-1, 10), px2.reshape(-1, 10)
+    it0, it1 = _read_sppm_dump(prefix + ".it0.bin"), _read_sppm_dump(prefix + ".it1.bin")
+    valid0 = it0["vp"][:, 3] != 0
+    assert valid0.sum() > 0.3 * w * h  # the camera also sees past the box
+    for col, kk, pos, attr in ((0, 100, it0["g_pos"], it0["g_attr"]), (5, 50, it0["c_pos"], it0["c_attr"])):
+        assert len(pos) > kk
+        d2, d = _d2(pos, it0["vp"][valid0])
+        kth = np.partition(d2, kk - 1, axis=1)[:, kk - 1]
+        got_r2 = px1[valid0, col + 3]
+        assert np.array_equal(px1[valid0, col + 4], np.full(valid0.sum(), kk, np.float32))
+        assert np.all(px1[~valid0, col + 4] == 0)
+        np.testing.assert_allclose(got_r2, kth, rtol=3e-7, atol=0)  # the k-th nearest, to the last bit or the one next to it
+        want = _flux(d, d2, d2 <= got_r2[:, None], attr, it0["vb"][valid0])
+        np.testing.assert_allclose(px1[valid0, col:col + 3], want, rtol=2e-4, atol=1e-5 * np.abs(want).max())
+    both = valid0 & (it1["vp"][:, 3] != 0)
+    assert both.sum() > 0.3 * w * h
+    for col, kk, pos, attr in ((0, 100, it1["g_pos"], it1["g_attr"]), (5, 50, it1["c_pos"], it1["c_attr"])):
+        r2 = px1[both, col + 3]
+        rr = (np.sqrt(r2).astype(np.float32) ** 2).astype(np.float32)  # r = sqrtf(radius2); squared distance < r * r
+        d2, d = _d2(pos, it1["vp"][both])
+        inside = d2 < rr[:, None]
+        m = inside.sum(axis=1)
+        n_new = kk + np.floor(0.7 * m.astype(np.float64)).astype(np.int64)
+        off = px2[both, col + 4] != n_new
+        assert off.sum() <= 2, (off.sum(), "pixels whose photon count differs (a distance on the radius, rounded the other way)")
+        frac = (n_new.astype(np.float64) / (kk + m)).astype(np.float32)
+        ok = ~off
+        np.testing.assert_allclose(px2[both, col + 3][ok], (r2 * frac)[ok], rtol=3e-7, atol=0)
+        want = (px1[both, col:col + 3].astype(np.float64) + _flux(d, d2, inside, attr, it1["vb"][both])) * frac[:, None]
+        np.testing.assert_allclose(px2[both, col:col + 3][ok], want[ok], rtol=3e-4, atol=1e-5 * np.abs(want).max())
