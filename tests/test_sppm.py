@@ -241,3 +241,24 @@ def test_sppm_lookups_match_brute_force(ctx, tmp_path):
         np.testing.assert_allclose(px2[both, col + 3][ok], (r2 * frac)[ok], rtol=3e-7, atol=0)
         want = (px1[both, col:col + 3].astype(np.float64) + _flux(d, d2, inside, attr, it1["vb"][both])) * frac[:, None]
         np.testing.assert_allclose(px2[both, col:col + 3][ok], want[ok], rtol=3e-4, atol=1e-5 * np.abs(want).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("photons,iters", [(40, 2), (300, 1), (5000, 9)])
+def test_sppm_small_maps(ctx, photons, iters):
+    """Edge shapes of the look-ups: fewer stored photons than k (the k-nearest start takes them all and the radius is the farthest
+    one: kd_tree.nearests returns what there is), an empty or near-empty caustic map, a one-cell grid, more passes in flight than
+    iterations, more iterations than photon buffers."""
+    sb = scene_builder("cornell_ref")
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=24, height=20, spp_count=2, seed=9)
+    acc, px, st = scene.render_sppm(sb.camera, p, iterations=iters, photons_per_iter=photons, want_pixel_stats=True)
+    px = px.reshape(-1, 10)
+    assert st.global_photons > 0 and st.photon_rays >= photons * iters
+    seen = px[:, 4] > 0
+    assert seen.sum() > 100
+    assert np.all(px[seen, 4] >= 100) and np.all(px[seen, 9] >= 50)      # photons = k after the first look-up (photon_mapper.rs:51-52)
+    assert np.all(np.isfinite(px[seen][:, [0, 1, 2, 3, 5, 6, 7, 8]])) and np.all(px[seen, 3] > 0)
+    if photons * 3 < 100 * 2:  # fewer photons stored per iteration than k: the radius reaches the farthest photon of the first map
+        assert np.all(px[seen, 3] > 1.0)
+    assert np.all(acc[..., 3] == 2)
