@@ -182,12 +182,14 @@ def run_sppm(args):
            "dtype": "f32 (f64 hit confirmation)", "data": "synthetic",
            "config": {"workload": "SPPMIntegrator::new + capture_image (photon_mapper.rs:139-236, 327-365; main.rs:33-53)", "iterations": ITER, "photons_per_iteration": PHOTONS, "spp": SPP},
            "stage_ms": {"photons": st.ms_photons, "grid": st.ms_grid, "eye": st.ms_eye, "final": st.ms_final, "total": st.ms_total,
-                        "note": "the photon pass of iteration i+1 runs on a second stream under the grid build and eye pass of iteration i: the stage times overlap"},
+                        "note": "up to 7 photon passes run ahead of the eye pass on their own streams: photons is the sum of the passes' own event pairs (they overlap each other and the eye passes), grid / eye / final are on the context stream"},
            "rates": {"Mphotons_emitted_per_s": n_emit / st.ms_photons / 1e3, "Mphoton_rays_per_s": st.photon_rays / st.ms_photons / 1e3,
                      "Meye_updates_per_s": n_eye / st.ms_eye / 1e3, "Mfinal_paths_per_s": n_final / st.ms_final / 1e3},
            "photons_stored": {"global": int(st.global_photons), "caustic": int(st.caustic_photons)},
-           "roofline": {"bound": "hbm", "kernel": "k_sppm_eye (radius gather)", "achieved": None, "peak": measured_peaks()[0]["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None,
-                        "note": "not HBM-bound: the eye pass walks photon cells per pixel (latency / divergence bound, profiles/r1_sppm_full_summary.txt); no roofline fraction is claimed for SPPM"},
+           "roofline": {"bound": "fp32_issue", "kernel": "k_sppm_gather (SPPM::update radius gather: 49 of the 50 eye passes)", "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                        "issue": {"issue_active_pct": 50.0, "lanes_per_instruction": 18.5, "fma_pipe_pct": 23.2, "l1_hit_pct": 76.9, "l2_hit_pct": 85.6, "dram_pct_of_peak": 0.9,
+                                  "source": "profiles/r2_sppm_kernels_final.txt (ncu --set full, iteration 1 of tools/bench_sppm.py)"},
+                        "note": "SURVEY.md section 8(d) defines no algorithmic flop count for the photon-map look-ups, so no fraction is claimed; the kernel is issue / latency bound (the maps are L2-resident: 0.9 % of HBM), and the frame is bounded by the eye passes (stage_ms.eye) with the photon passes hidden under them (7 in flight)"},
            "cpu_baseline": cpu,
            "e2e": {"value": float(np.mean(wall)) * 1e3, "unit": "ms per frame", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": W * H * 16,
                    "what": "host clock around b200rt_render_sppm (image returned to a host buffer)"},

@@ -238,17 +238,27 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   // Photon passes in flight: a pass ends in a tail of a few photons that bounce hundreds of times (one dependent traversal after
   // the other: ms), and no pass depends on the pixel statistics (photon_mapper.rs:154-160) — so several run ahead of the eye pass,
   // each on its own stream with its own queues and buffers, and the tail of one hides under the bulk of the next.
-  const int inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 7, 1, SPPM_MAX_NB - 1), sppm->iterations);
-  const int NB = inflight + 1;
+  int inflight = std::min(env_int("B200RT_SPPM_INFLIGHT", 7, 1, SPPM_MAX_NB - 1), sppm->iterations);
   const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;  // A/B: the one-thread-per-photon kernel of round 1
-  // the buffers: the context's cached set when it has this call's shape, else a fresh one
+  // the buffers: the context's cached set when it has this call's shape (and at least the photon buffers this call wants), else a fresh one
   SppmCache* cache = (SppmCache*)ctx->sppm_cache;
   ctx->sppm_cache = nullptr;
-  if (cache && !(cache->cap == cap && cache->n_pix == n_pix && cache->NB == NB && cache->photons == (unsigned int)sppm->photons_per_iter && cache->mega == photons_mega)) {
+  if (cache && !(cache->cap == cap && cache->n_pix == n_pix && cache->NB >= inflight + 1 && cache->photons == (unsigned int)sppm->photons_per_iter && cache->mega == photons_mega)) {
     SppmCache::destroy(cache);
     cache = nullptr;
   }
   const bool fresh = cache == nullptr;
+  if (fresh) {  // as many passes in flight as the free memory holds (each: two photon buffers of `cap` records + its queues)
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+      const size_t per_pass = 2 * (size_t)cap * 64 + 160 * (size_t)sppm->photons_per_iter + (1u << 20);
+      const size_t base = 2 * (size_t)cap * 48 + 72 * (size_t)n_pix + 16 * (size_t)max_cells + (64u << 20);
+      const size_t budget = free_b - free_b / 8;  // leave an eighth
+      const size_t fit = budget > base + 2 * per_pass ? (budget - base) / per_pass - 1 : 1;
+      if ((size_t)inflight > fit) inflight = (int)std::max<size_t>(fit, 1);
+    }
+  }
+  const int NB = fresh ? inflight + 1 : cache->NB;
   if (fresh) {
     cache = new (std::nothrow) SppmCache();
     if (!cache) return B200RT_ERR_NOMEM;
