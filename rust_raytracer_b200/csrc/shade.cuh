@@ -41,9 +41,43 @@ DEV float perlin_turb(const DevScene& S, float3 p) {
   for (int i = 0; i < 7; ++i) { accum += weight * perlin_noise(S, p); weight *= 0.5f; p = p * 2.0f; }
   return fabsf(accum);
 }
+// perlin_turb with the whole (converged) warp on ONE point: 7 octaves x 8 lattice corners = 56 terms, a lane per term (4 octaves
+// per round, 2 rounds), the 8 corners of an octave summed inside their 8-lane segment, the octaves across the segments.  The
+// shade kernel evaluates NOISE textures this way: a warp streams rays in the order of where they STARTED, so the one Perlin
+// sphere of book-2 is hit by ~2 of its 32 lanes at a time, and those two spent ~1000 instructions each while the others
+// waited (16 % of k_wf_shade's instructions at 2.1 lanes).  Same lattice terms as perlin_noise; the sums associate differently
+// (a few ulp).  Every lane returns the value.
+DEV float perlin_turb_warp(const DevScene& S, float3 p, unsigned lane) {
+  const int corner = (int)(lane & 7u), di = corner >> 2, dj = (corner >> 1) & 1, dk = corner & 1;
+  float total = 0.f;
+#pragma unroll
+  for (int round = 0; round < 2; ++round) {
+    const int oct = round * 4 + (int)(lane >> 3);
+    float term = 0.f;
+    if (oct < 7) {
+      const float sc = (float)(1 << oct);
+      const float3 q = p * sc;  // exact: the serial version doubles p per octave
+      const float fx = floorf(q.x), fy = floorf(q.y), fz = floorf(q.z);
+      const float u = q.x - fx, v = q.y - fy, w = q.z - fz;
+      const int i = (int)fx, j = (int)fy, k = (int)fz;
+      const float uu = u * u * (3 - 2 * u), vv = v * v * (3 - 2 * v), ww = w * w * (3 - 2 * w);
+      const int idx = __ldg(&S.perlin_perm[(i + di) & 255]) ^ __ldg(&S.perlin_perm[256 + ((j + dj) & 255)]) ^ __ldg(&S.perlin_perm[512 + ((k + dk) & 255)]);
+      const float3 c = f3(__ldg(&S.perlin_vec[idx]));
+      const float3 wv = f3(u - di, v - dj, w - dk);
+      term = (di ? uu : 1 - uu) * (dj ? vv : 1 - vv) * (dk ? ww : 1 - ww) * dot(c, wv) * (1.0f / sc);
+    }
+    term += __shfl_xor_sync(0xffffffffu, term, 1); term += __shfl_xor_sync(0xffffffffu, term, 2); term += __shfl_xor_sync(0xffffffffu, term, 4);
+    term += __shfl_xor_sync(0xffffffffu, term, 8); term += __shfl_xor_sync(0xffffffffu, term, 16);
+    total += term;
+  }
+  return fabsf(total);
+}
 DEV bool texture_needs_uv(const DevScene& S, int tex) { return __float_as_int(__ldg(&S.textures[3 * tex]).x) == B200RT_TEX_IMAGE; }
 
-DEV float3 texture_color(const DevScene& S, int tex, const HitInfo& h) {
+DEV bool texture_is_noise(const DevScene& S, int tex) { return __float_as_int(__ldg(&S.textures[3 * tex]).x) == B200RT_TEX_NOISE; }
+
+// turb >= 0: the turbulence at h.p, already evaluated (perlin_turb_warp)
+DEV float3 texture_color(const DevScene& S, int tex, const HitInfo& h, float turb = -1.f) {
   const float4 hd = __ldg(&S.textures[3 * tex]);
   const int type = __float_as_int(hd.x);
   DBG_INC(48 + type);
@@ -61,7 +95,7 @@ DEV float3 texture_color(const DevScene& S, int tex, const HitInfo& h) {
     const uint8_t* px = S.image_data + im.x + 3 * ((size_t)y * im.y + x);
     return f3(px[0] * (1.f / 255.f), px[1] * (1.f / 255.f), px[2] * (1.f / 255.f));
   }
-  return f3(1, 1, 1) * (0.5f * (1.f + sinf(hd.z * h.p.z + 10.f * perlin_turb(S, h.p))));  // NOISE
+  return f3(1, 1, 1) * (0.5f * (1.f + sinf(hd.z * h.p.z + 10.f * (turb >= 0.f ? turb : perlin_turb(S, h.p)))));  // NOISE
 }
 
 // ---- light PDFs (book-3 HittablePDF over the marked lights) -----------------------------------------------
@@ -186,10 +220,10 @@ DEV float3 refract3(float3 uv, float3 n, float eta) {                        // 
 // the PATH build carries no light-sampling code: fewer registers, a third of the instructions); -1 reads P.integrator.
 template <int INTEG = -1>
 DEV bool shade_surface(const DevScene& S, const RenderConst& P, Ray& ray, const HitInfo& h, const float4 mat, const float u1, const float u2, const float u3,
-                       const uint32_t next_seed, PathState& ps, ShadowReq& sreq) {
+                       const uint32_t next_seed, PathState& ps, ShadowReq& sreq, const float turb = -1.f) {
   const int integrator = INTEG >= 0 ? INTEG : P.integrator;
   const int mtype = __float_as_int(mat.x), tex = __float_as_int(mat.y);
-  const float3 color = texture_color(S, tex, h);
+  const float3 color = texture_color(S, tex, h, turb);
   DBG_INC(40 + mtype);
 
   if (mtype == B200RT_MAT_DIFFUSE_LIGHT) {  // emitted = emit.get_color(rec), both faces (material.rs:209-211)
@@ -301,14 +335,23 @@ DEV bool shade_surface(const DevScene& S, const RenderConst& P, Ray& ray, const 
 
 // Processes the hit `hr` of `ray`: HitRecord::new, the Philox draws of this bounce, then shade_surface.
 // depth bookkeeping (photon_mapper.rs:334-339) is done by the caller.
-template <int INTEG = -1>
-DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitRaw& hr, PathState& ps, ShadowReq& sreq) {
-  sreq.valid = false;
+// In two halves for the shade kernel, which evaluates NOISE textures between them with the warp converged.
+DEV void shade_hit_begin(const DevScene& S, const Ray& ray, const HitRaw& hr, HitInfo& h, float4& mat) {
   const int4 meta = __ldg(&S.prim_meta[hr.prim]);
-  const float4 mat = __ldg(&S.materials[meta.x >> 8]);
-  HitInfo h;
+  mat = __ldg(&S.materials[meta.x >> 8]);
   finish_hit(S, ray, hr, h, texture_needs_uv(S, __float_as_int(mat.y)));
+}
+template <int INTEG = -1>
+DEV bool shade_hit_end(const DevScene& S, const RenderConst& P, Ray& ray, const HitInfo& h, const float4 mat, PathState& ps, ShadowReq& sreq, const float turb = -1.f) {
+  sreq.valid = false;
   ps.bounce++;
   const uint4 rnd = philox4x32(make_uint4(ps.pixel, ps.sample, (uint32_t)ps.bounce, 0u), P.key);
-  return shade_surface<INTEG>(S, P, ray, h, mat, u01(rnd.x), u01(rnd.y), u01(rnd.z), rnd.w, ps, sreq);
+  return shade_surface<INTEG>(S, P, ray, h, mat, u01(rnd.x), u01(rnd.y), u01(rnd.z), rnd.w, ps, sreq, turb);
+}
+template <int INTEG = -1>
+DEV bool shade_hit(const DevScene& S, const RenderConst& P, Ray& ray, const HitRaw& hr, PathState& ps, ShadowReq& sreq) {
+  HitInfo h;
+  float4 mat;
+  shade_hit_begin(S, ray, hr, h, mat);
+  return shade_hit_end<INTEG>(S, P, ray, h, mat, ps, sreq);
 }

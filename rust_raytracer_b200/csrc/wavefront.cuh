@@ -252,6 +252,9 @@ DEV void mbar_wait(uint32_t bar, uint32_t parity) {
 #ifndef B200RT_SHADE_MINBLOCKS  // ... MIXTURE / NEE need 120 / 126
 #define B200RT_SHADE_MINBLOCKS 4
 #endif
+#ifndef B200RT_SHADE_COOP_PERLIN  // NOISE textures evaluated by the whole warp, one hit at a time (shade.cuh perlin_turb_warp)
+#define B200RT_SHADE_COOP_PERLIN 1
+#endif
 template <int INTEG>
 __global__ void __launch_bounds__(128, INTEG == B200RT_INTEGRATOR_PATH ? B200RT_SHADE_MINBLOCKS_PATH : B200RT_SHADE_MINBLOCKS)
 k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
@@ -349,6 +352,43 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
     PathState ps;
     ShadowReq sr;
     sr.valid = false;
+#if B200RT_SHADE_COOP_PERLIN
+    // hit record per lane, then the NOISE textures of the warp one after the other with all 32 lanes on each (perlin_turb_warp),
+    // then the rest of the shading per lane
+    HitInfo hi;
+    float4 mat = make_float4(0.f, 0.f, 0.f, 0.f);
+    float turb = -1.f;
+    bool surf = false;
+    if (active) {
+      ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
+      ps.throughput = f3(sa); ps.prev_pdf_b = sa.w; ps.radiance = f3(0, 0, 0);
+      ps.pixel = sb.x; ps.sample = sb.y; ps.bounce = (int)sb.z;
+      surf = hprim >= 0 && ps.bounce < P.max_depth;  // photon_mapper.rs:336-339: the depth budget is checked after the hit
+      if (surf) {
+        HitRaw h;
+        h.t = __longlong_as_double((long long)(((unsigned long long)hh.y << 32) | hh.x)); h.prim = hprim; h.aux = wf_unpack_aux(hh.z);
+        shade_hit_begin(S, ray, h, hi, mat);
+      }
+    }
+    {
+      unsigned noisy = __ballot_sync(0xffffffffu, surf && texture_is_noise(S, __float_as_int(mat.y)));
+      while (noisy) {
+        const int src = __ffs((int)noisy) - 1;
+        noisy &= noisy - 1u;
+        const float3 q = f3(__shfl_sync(0xffffffffu, hi.p.x, src), __shfl_sync(0xffffffffu, hi.p.y, src), __shfl_sync(0xffffffffu, hi.p.z, src));
+        const float tb = perlin_turb_warp(S, q, threadIdx.x & 31u);
+        if ((int)(threadIdx.x & 31u) == src) turb = tb;
+      }
+    }
+    if (active) {
+      if (hprim < 0) ps.radiance = ps.throughput * background_color(P, ray.d);  // miss
+      else if (surf) {
+        cont = shade_hit_end<INTEG>(S, P, ray, hi, mat, ps, sr, turb);
+        shadow = sr.valid;
+      }
+      accum_add(accum, ps.pixel, ps.radiance);
+    }
+#else
     if (active) {
       ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
       ps.throughput = f3(sa); ps.prev_pdf_b = sa.w; ps.radiance = f3(0, 0, 0);
@@ -363,6 +403,7 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
       }
       accum_add(accum, ps.pixel, ps.radiance);
     }
+#endif
     if (active && rank != WF_NO_RANK) {  // the place extend reserved in the next set: the new ray, or a dead record
       const unsigned int bin = 1u + __umulhi((unsigned int)hprim, B.bin_mul);  // the bin extend ranked it in
       const size_t dst = 2 * (size_t)((off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank);
