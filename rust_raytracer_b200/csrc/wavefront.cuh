@@ -252,8 +252,8 @@ DEV void mbar_wait(uint32_t bar, uint32_t parity) {
 #ifndef B200RT_SHADE_MINBLOCKS  // ... MIXTURE / NEE need 120 / 126
 #define B200RT_SHADE_MINBLOCKS 4
 #endif
-#ifndef B200RT_SHADE_COOP_PERLIN  // NOISE textures evaluated by the whole warp, one hit at a time (shade.cuh perlin_turb_warp)
-#define B200RT_SHADE_COOP_PERLIN 1
+#ifndef B200RT_SHADE_COOP_PERLIN  // 1: NOISE textures evaluated by the whole warp, one hit at a time (perlin_turb_warp): measured -0.65 %, profiles/r2_experiments.md section 7
+#define B200RT_SHADE_COOP_PERLIN 0
 #endif
 template <int INTEG>
 __global__ void __launch_bounds__(128, INTEG == B200RT_INTEGRATOR_PATH ? B200RT_SHADE_MINBLOCKS_PATH : B200RT_SHADE_MINBLOCKS)
