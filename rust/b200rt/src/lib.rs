@@ -201,6 +201,18 @@ pub fn render_multi(scenes: &[&Scene<'_>], cam: &Camera, params: &Params) -> Res
     Ok((accum, ms))
 }
 
+/// The SPPM integrator (`Scene::render_sppm`) over the devices of `scenes`: photons sharded by id, the photon maps gathered inside
+/// each device's grid build over NVLink peer mappings, pixel statistics sharded by pixel, the final pass by sample index
+/// (`b200rt_render_sppm_multi`).  Needs peer access between the devices.
+pub fn render_sppm_multi(scenes: &[&Scene<'_>], cam: &Camera, params: &Params, sppm: &SppmParams) -> Result<(Vec<f32>, SppmStats)> {
+    assert!(!scenes.is_empty());
+    let raws: Vec<*mut sys::b200rt_scene> = scenes.iter().map(|s| s.raw).collect();
+    let mut accum = vec![0f32; 4 * params.width as usize * params.height as usize];
+    let mut st = SppmStats::default();
+    scenes[0].ctx.check(unsafe { sys::b200rt_render_sppm_multi(raws.len() as i32, raws.as_ptr(), cam, params, sppm, accum.as_mut_ptr(), ptr::null_mut(), &mut st) })?;
+    Ok((accum, st))
+}
+
 /// The reference's defaults: 800x800 (main.rs:33-46), 256 spp (camera.rs:73), depth 50 and t_min 0.001 (photon_mapper.rs:333-339).
 pub fn default_params() -> Params {
     Params { width: 800, height: 800, spp_begin: 0, spp_count: 256, max_depth: 50, integrator: sys::B200RT_INTEGRATOR_PATH,
