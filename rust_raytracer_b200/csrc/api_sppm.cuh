@@ -204,7 +204,8 @@ void sppm_photon_wf_finish(SppmPhotonWf& W, SppmCounters* cnt_host) {
 struct SppmCache {
   SppmBuffers B;
   SppmPhotonWf PW[SPPM_MAX_NB];
-  unsigned int cap = 0, photons = 0;
+  unsigned int cap = 0, photons = 0;   // photon buffers: records each, photons per pass (one device: all of them; several: this device's shard)
+  unsigned int cap_maps = 0;           // records of each cell-ordered map (= cap on one device, the complete map on several)
   uint32_t n_pix = 0;
   int NB = 0;
   bool mega = false;
@@ -243,7 +244,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   // the buffers: the context's cached set when it has this call's shape (and at least the photon buffers this call wants), else a fresh one
   SppmCache* cache = (SppmCache*)ctx->sppm_cache;
   ctx->sppm_cache = nullptr;
-  if (cache && !(cache->cap == cap && cache->n_pix == n_pix && cache->NB >= inflight + 1 && cache->photons == (unsigned int)sppm->photons_per_iter && cache->mega == photons_mega)) {
+  if (cache && !(cache->cap == cap && cache->cap_maps == cap && cache->n_pix == n_pix && cache->NB >= inflight + 1 && cache->photons == (unsigned int)sppm->photons_per_iter && cache->mega == photons_mega)) {
     SppmCache::destroy(cache);
     cache = nullptr;
   }
@@ -262,7 +263,7 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
   if (fresh) {
     cache = new (std::nothrow) SppmCache();
     if (!cache) return B200RT_ERR_NOMEM;
-    cache->cap = cap; cache->n_pix = n_pix; cache->NB = NB; cache->photons = (unsigned int)sppm->photons_per_iter; cache->mega = photons_mega;
+    cache->cap = cap; cache->cap_maps = cap; cache->n_pix = n_pix; cache->NB = NB; cache->photons = (unsigned int)sppm->photons_per_iter; cache->mega = photons_mega;
   }
   SppmBuffers& B = cache->B;
   SppmPhotonWf* PW = cache->PW;

@@ -75,9 +75,25 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   const unsigned int cap_total = (unsigned int)sppm->photons_per_iter * 16u;  // the complete map (cell order) lives on every device
   const unsigned int cap_shard = (id_count + 1u) * 16u;
   const uint32_t max_cells = (uint32_t)SPPM_MAX_RES * SPPM_MAX_RES * SPPM_MAX_RES;
-  SppmBuffers B;
   cudaStream_t q = ctx->stream, qp[SPPM_MAX_NB] = {};
-  const int inflight = sh.inflight, NB = inflight + 1, EYE = SPPM_MAX_NB;  // as in b200rt_render_sppm: buffer / stream / queues k = pass % NB
+  const int inflight = sh.inflight, EYE = SPPM_MAX_NB;  // as in b200rt_render_sppm: buffer / stream / queues k = pass % NB
+  const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;  // as in b200rt_render_sppm
+  // this device's buffers: its context's cached set when it has this call's shape, else a fresh one (b200rt_render_sppm's rule)
+  SppmCache* cache = (SppmCache*)ctx->sppm_cache;
+  ctx->sppm_cache = nullptr;
+  if (cache && !(cache->cap == cap_shard && cache->cap_maps == cap_total && cache->n_pix == n_pix && cache->NB == inflight + 1 && cache->photons == id_count && cache->mega == photons_mega)) {  // NB: the same on every device (peers index each other's buffers by pass % NB)
+    SppmCache::destroy(cache);
+    cache = nullptr;
+  }
+  const bool fresh = cache == nullptr;
+  SppmCache local_cache;  // stands in when the allocation of the cache object itself fails (reported below)
+  if (fresh) {
+    cache = new (std::nothrow) SppmCache();
+    if (cache) { cache->cap = cap_shard; cache->cap_maps = cap_total; cache->n_pix = n_pix; cache->NB = inflight + 1; cache->photons = id_count; cache->mega = photons_mega; }
+  }
+  const int NB = cache ? cache->NB : inflight + 1;
+  SppmBuffers& B = cache ? cache->B : local_cache.B;
+  SppmPhotonWf* PW = cache ? cache->PW : local_cache.PW;
   cudaEvent_t ev_grid = nullptr;
   SppmCounters* hcnt = nullptr;
   auto ok = [&](cudaError_t e, const char* what) {
@@ -88,6 +104,7 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   // ---- set-up: peer mappings, buffers
   bool good = ok(cudaSetDevice(ctx->device), "cudaSetDevice");
   cudaGetLastError();  // as in b200rt_render_sppm: stale non-sticky errors are not this call's
+  if (!cache) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: out of host memory"); good = false; }
   for (int h = 0; good && h < G; ++h) {
     const int peer = scenes[h]->ctx->device;
     if (peer == ctx->device) continue;
@@ -101,13 +118,15 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   if (good) {
     cudaError_t e = cudaSuccess;
     auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
-    for (int k = 0; k < NB; ++k) { alloc((void**)&B.pg[k], (size_t)cap_shard * 64); alloc((void**)&B.pc[k], (size_t)cap_shard * 64); }
-    if (e == cudaSuccess) e = B.alloc_maps(cap_total, n_pix);
-    alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
-    alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
-    alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
-    alloc((void**)&B.accum, 16 * (size_t)n_pix);
-    alloc((void**)&B.cnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters));
+    if (fresh) {
+      for (int k = 0; k < NB; ++k) { alloc((void**)&B.pg[k], (size_t)cap_shard * 64); alloc((void**)&B.pc[k], (size_t)cap_shard * 64); }
+      if (e == cudaSuccess) e = B.alloc_maps(cap_total, n_pix);
+      alloc((void**)&B.tile_sum, 4 * 1024); alloc((void**)&B.cell_count, 4 * (size_t)max_cells); alloc((void**)&B.cursor, 4 * (size_t)max_cells);
+      alloc((void**)&B.start_g, 4 * ((size_t)max_cells + 1)); alloc((void**)&B.start_c, 4 * ((size_t)max_cells + 1));
+      alloc((void**)&B.px_g, 16 * (size_t)n_pix); alloc((void**)&B.px_c, 16 * (size_t)n_pix); alloc((void**)&B.px_n, 8 * (size_t)n_pix);
+      alloc((void**)&B.accum, 16 * (size_t)n_pix);
+      alloc((void**)&B.cnt, (SPPM_MAX_NB + 1) * sizeof(SppmCounters));
+    }
     good = ok(e, "cudaMalloc");
     for (int k = 0; good && k < NB; ++k) good = ok(cudaStreamCreateWithFlags(&qp[k], cudaStreamNonBlocking), "cudaStreamCreate");
     if (good) good = ok(cudaEventCreateWithFlags(&ev_grid, cudaEventDisableTiming), "cudaEventCreate") &&
@@ -129,10 +148,8 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   Peye.key.y ^= 0x5EE05EE0u;  // as in b200rt_render_sppm
   const int sms = ctx->prop.multiProcessorCount;
   const int photon_grid = env_int("B200RT_SPPM_PHOTON_GRID", 4, 1, 8);
-  const bool photons_mega = env_int("B200RT_SPPM_PHOTONS_MEGA", 0, 0, 1) != 0;  // as in b200rt_render_sppm
-  SppmPhotonWf PW[SPPM_MAX_NB];
   for (int k = 0; good && k < NB; ++k)
-    if (!photons_mega && id_count && sppm_photon_wf_alloc(ctx, s, PW[k], id_count)) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon queues: " + ctx->err); good = false; }
+    if (!photons_mega && id_count && (fresh ? sppm_photon_wf_alloc(ctx, s, PW[k], id_count) : sppm_photon_wf_configure(ctx, s, PW[k]))) { sh.fail(B200RT_ERR_NOMEM, "render_sppm_multi: photon queues: " + ctx->err); good = false; }
   auto launch_photons = [&](int it) -> bool {  // on stream / into the buffers it % NB
     const int k = it % NB;
     cudaStream_t qpk = qp[k];
@@ -227,10 +244,15 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
   }
   bar.wait();  // C: every accumulation buffer is complete; the root reduces and reads them in b200rt_render_sppm_multi
   bar.wait();  // D: the root is done with the peers' buffers
-  for (int k = 0; k < SPPM_MAX_NB; ++k) { if (qp[k]) { cudaStreamSynchronize(qp[k]); cudaStreamDestroy(qp[k]); } PW[k].release(); }
+  for (int k = 0; k < SPPM_MAX_NB; ++k) if (qp[k]) { cudaStreamSynchronize(qp[k]); cudaStreamDestroy(qp[k]); }
   if (ev_grid) cudaEventDestroy(ev_grid);
   if (hcnt) cudaFreeHost(hcnt);
-  B.release();
+  cudaStreamSynchronize(q);
+  if (cache && good && !sh.failed) {  // the buffers stay with this device's context for the next call of this shape
+    if (ctx->sppm_cache && ctx->sppm_cache_free) ctx->sppm_cache_free(ctx->sppm_cache);
+    ctx->sppm_cache = cache; ctx->sppm_cache_free = &SppmCache::destroy;
+  } else if (cache) SppmCache::destroy(cache);
+  else local_cache.release();
 }
 
 }  // namespace
