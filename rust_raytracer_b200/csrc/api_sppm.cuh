@@ -381,6 +381,10 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
     if ((rc = sppm_build_grid(ctx, B, Gg, sppm_one_seg(B.pg[k], h.n_global), B.start_g, B.sg)) != 0) return fail2(rc);
     if ((rc = sppm_build_grid(ctx, B, Gc, sppm_one_seg(B.pc[k], h.n_caustic), B.start_c, B.sc)) != 0) return fail2(rc);
     SPPM_CHECK(cudaEventRecord(ev_grid, q));
+    // the eye pass is queued BEFORE the next photon pass: that one is ~60 launches (0.2 ms of host time), which would otherwise
+    // leave the context stream idle between the grid build and the eye pass of every iteration
+    if ((rc = sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + EYE, 0u, n_pix)) != 0) return fail2(rc);
+    SPPM_CHECK(cudaEventRecord(ev_eye, q));
     if (it + inflight < sp.iterations) {
       // pass it + inflight writes the buffer iteration it - 1 used: its grid build read it and has finished (the host
       // synchronised the context stream at the end of that iteration).  It starts after THIS iteration's grid build:
@@ -389,8 +393,6 @@ extern "C" int b200rt_render_sppm(b200rt_scene* s, const b200rt_camera* cam, con
       SPPM_CHECK(cudaStreamWaitEvent(qp[(it + inflight) % NB], ev_grid, 0));
       SPPM_CHECK(launch_photons(it + inflight));
     }
-    if ((rc = sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + EYE, 0u, n_pix)) != 0) return fail2(rc);
-    SPPM_CHECK(cudaEventRecord(ev_eye, q));
     // the grid tables (cell_count, cursor, start, sg, sc) are single-buffered and the stage events are reused:
     // the host lets the eye pass finish before it builds the next grid — the next photon passes are already running
     SPPM_CHECK(cudaStreamSynchronize(q));

@@ -202,15 +202,16 @@ void sppm_multi_worker(int g, SppmShared& sh, HostBarrier& bar, b200rt_scene* co
       sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: grid build: " + ctx->err); good = false; continue;
     }
     good = ok(cudaEventRecord(ev_grid, q), "event");
+    // eye pass first, then the ~60 launches of the next photon pass (as in b200rt_render_sppm)
+    if (good && pix_count) {
+      const SppmPixels px = sh.px[g];
+      if (sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + EYE, pix_first, pix_count)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: eye pass: " + ctx->err); good = false; }
+    }
     if (good && it + inflight < sp.iterations) {
       // pass it + inflight writes the buffers (it - 1) % NB, which every peer's grid build of iteration it - 1 has finished
       // reading: each thread synchronised its stream at the end of that iteration, before it arrived at barrier A of this one.
       // It starts after the local grid build (see b200rt_render_sppm: photon blocks starve the small grid kernels).
       good = ok(cudaStreamWaitEvent(qp[(it + inflight) % NB], ev_grid, 0), "wait") && launch_photons(it + inflight);
-    }
-    if (good && pix_count) {
-      const SppmPixels px = sh.px[g];
-      if (sppm_eye_pass(ctx, s, Peye, sp, it, Gg, Gc, px, B, B.cnt + EYE, pix_first, pix_count)) { sh.fail(B200RT_ERR_CUDA, "render_sppm_multi: eye pass: " + ctx->err); good = false; }
     }
     // grid tables are single-buffered, and the peers may not overwrite the shards this grid build reads before it is done
     if (good) good = ok(cudaStreamSynchronize(q), "eye pass");
