@@ -154,6 +154,9 @@ typedef struct b200rt_scene_desc {
   const b200rt_instance* instances;
   const int32_t* light_prims;  /* prim indices sampled by the light PDF  */
   const b200rt_perlin* perlin; /* may be NULL when no NOISE texture      */
+  const float* light_scales;   /* n_lights, or NULL (all 1): the `scale` of XZRectLight::new / SphereDiffuseLight::new
+                                  (light.rs:71,131) per light, RELATIVE to b200rt_sppm_params.light_scale (photon power and the
+                                  choice between lights; the light PDFs of the path integrators do not use it) */
 } b200rt_scene_desc;
 
 /* camera.rs:11-21 plus a shutter interval (MovingSphere). */
@@ -436,6 +439,9 @@ int b200rt_builder_medium_sphere(b200rt_builder* b, const double center[3], doub
 int b200rt_builder_medium_cube(b200rt_builder* b, const double box_min[3], const double box_max[3], double density,
                                int32_t phase_material);
 int b200rt_builder_mark_light(b200rt_builder* b, int32_t prim);
+/* The same with the light's own `scale` (light.rs:71,131), relative to b200rt_sppm_params.light_scale: a scene whose lights
+ * carry different scales upstream marks each with its scale and renders with light_scale = 1. */
+int b200rt_builder_mark_light_scaled(b200rt_builder* b, int32_t prim, double scale);
 int b200rt_builder_set_flags(b200rt_builder* b, uint32_t flags);
 int b200rt_builder_seed_perlin(b200rt_builder* b, uint64_t seed);
 /* Appendix-B JSON scene (data/scene_*.json): fills the builder and the camera. */

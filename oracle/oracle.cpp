@@ -702,6 +702,7 @@ struct Light {  // book-3 HittablePDF target; absent upstream (nearest analogue 
   HitablePtr shape;
   int prim;
   const Material* shape_material = nullptr;
+  double scale = 1;  // the light's own `scale` (light.rs:71,131), relative to SPPMParams::light_scale
   double pdf_value(Vec3 o, Vec3 dir, double t_min) const {
     HitRecord rec;
     Ray r(o, dir);
@@ -853,6 +854,7 @@ static Scene* build_scene(const b200rt_scene_desc* d, uint64_t bvh_seed) {
     Light l;
     l.prim = pi; l.shape = raw[pi];
     l.shape_material = &sc->materials[p.material];
+    l.scale = d->light_scales ? (double)d->light_scales[i] : 1.0;
     if (p.type == B200RT_PRIM_SPHERE) { l.kind = 0; l.center = v3(p.p); l.radius = p.p[3]; }
     else if (p.type == B200RT_PRIM_XY_RECT || p.type == B200RT_PRIM_XZ_RECT || p.type == B200RT_PRIM_YZ_RECT) {
       l.kind = 1; l.axis = p.type == B200RT_PRIM_XY_RECT ? 2 : (p.type == B200RT_PRIM_XZ_RECT ? 1 : 0);
@@ -994,7 +996,7 @@ static Vec3 random_in_hemisphere(Vec3 n, Stream& rng) {  // vec3.rs:144-151
 static Vec3 light_flux(const Light& L) {  // the DiffuseLight colour the light was built with (light.rs:77, 143)
   HitRecord rec;
   rec.p = L.kind == 0 ? L.center : Vec3::zero(); rec.u = 0; rec.v = 0;
-  return L.shape_material->tex->get_color(rec);
+  return L.shape_material->tex->get_color(rec) * L.scale;
 }
 // AllLights::emit (light.rs:214-219) -> Light::emit (light.rs:97-102, 157-165)
 static void emit_photon(const Scene& sc, const SPPMParams& sp, Stream& rng, Ray& ray, Vec3& power) {

@@ -53,7 +53,7 @@ mod manual {
         pub image_bytes: u64,
         pub prims: *const c_void, pub tri_normals: *const f32, pub materials: *const c_void, pub textures: *const c_void,
         pub images: *const c_void, pub image_rgb8: *const u8, pub instances: *const c_void, pub light_prims: *const i32,
-        pub perlin: *const c_void,
+        pub perlin: *const c_void, pub light_scales: *const f32,
     }
 
     /// camera.rs:11-21 plus a shutter interval.
@@ -163,6 +163,7 @@ mod manual {
         pub fn b200rt_builder_medium_sphere(b: *mut b200rt_builder, center: *const f64, radius: f64, density: f64, phase_material: i32) -> c_int;
         pub fn b200rt_builder_medium_cube(b: *mut b200rt_builder, box_min: *const f64, box_max: *const f64, density: f64, phase_material: i32) -> c_int;
         pub fn b200rt_builder_mark_light(b: *mut b200rt_builder, prim: i32) -> c_int;
+        pub fn b200rt_builder_mark_light_scaled(b: *mut b200rt_builder, prim: i32, scale: f64) -> c_int;
         pub fn b200rt_builder_set_flags(b: *mut b200rt_builder, flags: u32) -> c_int;
         pub fn b200rt_builder_seed_perlin(b: *mut b200rt_builder, seed: u64) -> c_int;
         pub fn b200rt_builder_load_json(b: *mut b200rt_builder, text: *const c_char, len: u64, cam_out: *mut b200rt_camera) -> c_int;

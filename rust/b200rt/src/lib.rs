@@ -136,6 +136,8 @@ impl SceneBuilder {
     }
     /// the `lights` argument of World::new (world.rs:15-25): primitives the light PDF / the photon emitter sample
     pub fn mark_light(&mut self, prim: i32) -> Result<()> { self.ok(unsafe { sys::b200rt_builder_mark_light(self.raw, prim) }) }
+    /// with the light's own `scale` (light.rs:71,131), relative to `SppmParams::light_scale`
+    pub fn mark_light_scaled(&mut self, prim: i32, scale: f64) -> Result<()> { self.ok(unsafe { sys::b200rt_builder_mark_light_scaled(self.raw, prim, scale) }) }
     /// `Vec<Arc<dyn Hitable>>::hit` instead of the BVH (hit.rs:56-67)
     pub fn flat_list(&mut self) -> Result<()> { self.ok(unsafe { sys::b200rt_builder_set_flags(self.raw, sys::B200RT_SCENE_FLAT_LIST) }) }
     /// data/scene_*.json / *.yaml (Appendix B of SURVEY.md)

@@ -77,6 +77,7 @@ class SceneDesc(C.Structure):
         ("prims", C.POINTER(Prim)), ("tri_normals", C.POINTER(C.c_float)), ("materials", C.POINTER(Material)),
         ("textures", C.POINTER(Texture)), ("images", C.POINTER(Image)), ("image_rgb8", C.POINTER(C.c_uint8)),
         ("instances", C.POINTER(Instance)), ("light_prims", C.POINTER(C.c_int32)), ("perlin", C.POINTER(Perlin)),
+        ("light_scales", C.POINTER(C.c_float)),
     ]
 
 
@@ -171,6 +172,7 @@ PROTOTYPES = {
     "b200rt_builder_medium_sphere": (C.c_int, [VP, D3, C.c_double, C.c_double, C.c_int32]),
     "b200rt_builder_medium_cube": (C.c_int, [VP, D3, D3, C.c_double, C.c_int32]),
     "b200rt_builder_mark_light": (C.c_int, [VP, C.c_int32]),
+    "b200rt_builder_mark_light_scaled": (C.c_int, [VP, C.c_int32, C.c_double]),
     "b200rt_builder_set_flags": (C.c_int, [VP, C.c_uint32]),
     "b200rt_builder_seed_perlin": (C.c_int, [VP, C.c_uint64]),
     "b200rt_builder_load_json": (C.c_int, [VP, C.c_char_p, C.c_uint64, C.POINTER(Camera)]),

@@ -307,9 +307,10 @@ class World:
         ids = {}
         for h in hitable_list:
             ids[id(h)] = h.flatten(self.builder)
-        for l in lights:
+        for l in lights:  # a hitable, or (hitable, scale): the `scale` of XZRectLight::new / SphereDiffuseLight::new (light.rs:71,131)
+            l, scale = l if isinstance(l, tuple) else (l, 1.0)
             if id(l) not in ids:
                 raise B200RTError(F.ERR_INVALID, "World::new: a light must also be in the hitable list (scene.rs:86,110)")
-            self.builder._ok(F.lib().b200rt_builder_mark_light(self.builder.handle, ids[id(l)]))
+            self.builder._ok(F.lib().b200rt_builder_mark_light_scaled(self.builder.handle, ids[id(l)], float(scale)))
         self.cam = cam
         self.builder.camera = cam.c

@@ -3,6 +3,7 @@
 // textures; raytracer/src/scene.rs:16-112 is the model usage) into the flat tables of b200rt_scene_desc.
 // Host only; no CUDA.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <map>
 
@@ -209,13 +210,16 @@ int b200rt_builder_medium_cube(b200rt_builder* b, const double mn[3], const doub
   set3(p.p, D3(mn)); set3(p.p + 3, D3(mx)); p.p[6] = (float)density;
   return push_prim(b, p);
 }
-int b200rt_builder_mark_light(b200rt_builder* b, int32_t prim) {
+int b200rt_builder_mark_light(b200rt_builder* b, int32_t prim) { return b200rt_builder_mark_light_scaled(b, prim, 1.0); }
+int b200rt_builder_mark_light_scaled(b200rt_builder* b, int32_t prim, double scale) {
   if (!b) return B200RT_ERR_INVALID;
+  if (!(scale > 0.0) || !std::isfinite(scale)) { b->err = "mark_light: the light's scale must be positive and finite"; return B200RT_ERR_INVALID; }
   if (prim < 0 || (size_t)prim >= b->prims.size()) { b->err = "mark_light: prim out of range"; return B200RT_ERR_INVALID; }
   const b200rt_prim& p = b->prims[prim];
   bool ok = p.instance < 0 && (p.type == B200RT_PRIM_SPHERE || p.type == B200RT_PRIM_XY_RECT || p.type == B200RT_PRIM_XZ_RECT || p.type == B200RT_PRIM_YZ_RECT);
   if (!ok) { b->err = "only untransformed spheres and axis rectangles can be sampled as lights"; return B200RT_ERR_UNSUPPORTED; }
   b->lights.push_back(prim);
+  b->light_scales.push_back((float)scale);
   return B200RT_OK;
 }
 int b200rt_builder_set_flags(b200rt_builder* b, uint32_t flags) {
@@ -244,6 +248,7 @@ int b200rt_builder_finish(b200rt_builder* b, b200rt_scene_desc* out) {
   out->image_rgb8 = b->image_data.data();
   out->instances = b->instances.data();
   out->light_prims = b->lights.data();
+  out->light_scales = b->light_scales.data();
   out->perlin = b->has_perlin ? &b->perlin : nullptr;
   return B200RT_OK;
 }

@@ -27,7 +27,7 @@
 //   textures   : 3 x float4: (type bits, image bits, scale, 0), c0, c1
 //   images     : int4 (offset, w, h, 0) + RGB8 bytes
 //   lights     : 3 x float4 per light: (kind bits [0 sphere, 1 rect], original prim bits, axis bits, material bits),
-//                (a0, b0, a1, b1) or (c, r), (k, area, 0, 0)
+//                (a0, b0, a1, b1) or (c, r), (k, area, own scale, 0) [k, area: rectangles only]
 #pragma once
 #include <stdint.h>
 

@@ -121,6 +121,7 @@ struct b200rt_builder {
   std::vector<uint8_t> image_data;
   std::vector<b200rt_instance> instances;
   std::vector<int32_t> lights;
+  std::vector<float> light_scales;  // one per entry of `lights`
   b200rt_perlin perlin;
   bool has_perlin = false;
   uint32_t flags = 0;

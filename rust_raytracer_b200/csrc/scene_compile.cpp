@@ -431,6 +431,9 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
       put4(cs.lights, at + 4, p.p[0], p.p[1], p.p[2], p.p[3]);
       put4(cs.lights, at + 8, p.p[4], (p.p[2] - p.p[0]) * (p.p[3] - p.p[1]), 0, 0);
     } else { err = "only sphere and axis-rectangle lights are sampled"; return B200RT_ERR_UNSUPPORTED; }
+    const float scale = d->light_scales ? d->light_scales[i] : 1.0f;  // light.rs:71,131, relative to b200rt_sppm_params.light_scale
+    if (!(scale > 0.f) || !std::isfinite(scale)) { err = "light scale must be positive and finite"; return B200RT_ERR_INVALID; }
+    cs.lights[at + 10] = scale;  // row 2, .z (row 2 of a sphere light is otherwise unused; of a rectangle: k, area)
   }
   (void)ubits;
   return B200RT_OK;

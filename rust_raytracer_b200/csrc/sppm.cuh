@@ -113,12 +113,13 @@ DEV float3 sppm_bsdf(const DevScene& S, const float4 mat, const HitInfo& h) {
   return __float_as_int(mat.x) == B200RT_MAT_DIFFUSE_LIGHT ? f3(1, 1, 1) * (1.0f / PI_F) : texture_color(S, __float_as_int(mat.y), h);
 }
 
-DEV float3 sppm_light_flux(const DevScene& S, int li) {  // the DiffuseLight colour (light.rs:77, 143)
+DEV float3 sppm_light_flux(const DevScene& S, int li) {  // the DiffuseLight colour (light.rs:77, 143) x the light's own scale (light.rs:71,131)
   const float4 L0 = __ldg(&S.lights[3 * li]), L1 = __ldg(&S.lights[3 * li + 1]);
+  const float own_scale = __ldg(&S.lights[3 * li + 2]).z;
   const float4 lmat = __ldg(&S.materials[__float_as_int(L0.w)]);
   HitInfo lh;
   lh.p = f3(L1); lh.n = f3(0, 1, 0); lh.u = 0.f; lh.v = 0.f; lh.t = 0.f; lh.front_face = 1;
-  return texture_color(S, __float_as_int(lmat.y), lh);
+  return texture_color(S, __float_as_int(lmat.y), lh) * own_scale;
 }
 // AllLights::emit (light.rs:214-219) -> SphereDiffuseLight::emit (97-102) / XZRectLight::emit (157-165)
 DEV void sppm_emit(const DevScene& S, const SppmConst& sp, uint4 r0, uint4 r1, Ray& ray, float3& power) {

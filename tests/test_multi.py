@@ -177,3 +177,22 @@ def test_context_destroyed_before_its_scene_orphans_the_scene(ctx):
     # the session context is untouched and sees no stale error
     a, _ = rt.Scene(ctx, sb).render(sb.camera, p)
     assert np.isfinite(a).all() and a[..., 3].min() == 1
+
+
+@pytest.mark.gpu
+def test_garbage_collected_context_and_scene_cycle(ctx):
+    """The collector's order, for real: a context and its scene die together inside a reference cycle.  Weak references to
+    unreachable objects are cleared before their finalizers run, so Context.close() no longer finds the scene; whichever
+    finalizer runs first, nothing may crash and no CUDA error may be left for the next call."""
+    import gc
+    sb = scene_builder("cornell_ref")
+    for _ in range(3):
+        c2 = rt.Context(0)
+        sc = rt.Scene(c2, sb)
+        sc.cycle = [sc, c2]  # unreachable only through the cycle collector
+        c2.cycle = sc
+        del c2, sc
+        gc.collect()
+    p = rt.copy_params(sb.params, width=16, height=16, spp_count=1)
+    a, _ = rt.Scene(ctx, sb).render(sb.camera, p)
+    assert np.isfinite(a).all() and a[..., 3].min() == 1

@@ -262,3 +262,59 @@ def test_sppm_small_maps(ctx, photons, iters):
     if photons * 3 < 100 * 2:  # fewer photons stored per iteration than k: the radius reaches the farthest photon of the first map
         assert np.all(px[seen, 3] > 1.0)
     assert np.all(acc[..., 3] == 2)
+
+
+def _two_light_room(scale_right):
+    """A closed white room with two equal XZ rectangle lights in the ceiling; the right one carries `scale_right` (light.rs:131)."""
+    white, emit = rt.Lambertian(rt.ConstantTexture((0.73, 0.73, 0.73))), rt.DiffuseLight(rt.ConstantTexture((1.0, 1.0, 1.0)))
+    left, right = rt.XZRectangle((100, 200), (200, 300), 554, emit), rt.XZRectangle((355, 200), (455, 300), 554, emit)
+    walls = [rt.XZRectangle((0, 0), (555, 555), 0, white), rt.XZRectangle((0, 0), (555, 555), 555, white), rt.XYRectangle((0, 0), (555, 555), 555, white),
+             rt.YZRectangle((0, 0), (555, 555), 0, white), rt.YZRectangle((0, 0), (555, 555), 555, white)]
+    cam = rt.Camera(((278, 278, -800), (278, 278, 0)), (0, 1, 0), 40, 1, 0, 10)
+    return rt.World(rt.HitableList(walls + [left, right]), cam, lights=[left, (right, scale_right)])
+
+
+@pytest.mark.gpu
+def test_sppm_lights_carry_their_own_scale(ctx):
+    """Every upstream light has its own `scale` (SphereDiffuseLight::new / XZRectLight::new, light.rs:71,131): it weighs the choice
+    between the lights (AllLights::emit, light.rs:214-219) and the power of the photons.  Two equal lights, the right one at 4x:
+    the device against the oracle restatement (same tables), and against the equal-scale scene."""
+    from oracle_ffi import OracleScene
+    w = h = 40
+    out = {}
+    for name, sr in (("equal", 1.0), ("right4", 4.0)):
+        world = _two_light_room(sr)
+        sb = world.builder
+        p = rt.copy_params(rt.make_params(w, h, 2), seed=3)
+        scene = rt.Scene(ctx, sb)
+        _, px, st = scene.render_sppm(world.cam.c, p, iterations=4, photons_per_iter=20000, light_scale=1e6, want_pixel_stats=True)
+        flux = px[..., 0:3].astype(np.float64) / np.maximum(px[..., 3:4], 1e-30)  # flux / radius^2: proportional to irradiance
+        out[name] = (flux, st)
+        if name == "right4":
+            o_flux = []
+            for seed in (11, 12):
+                _, o_px, _ = OracleScene(sb).sppm_render(world.cam.c, rt.copy_params(p, seed=seed), iterations=4, photons_per_iter=20000, light_scale=1e6)
+                o_flux.append(o_px[..., 0:3] / np.maximum(o_px[..., 3:4], 1e-30))
+            g, a, b = flux.mean(), o_flux[0].mean(), o_flux[1].mean()
+            print("two lights, right at 4x: flux/r2 mean gpu %.5g oracle %.5g / %.5g" % (g, a, b))
+            assert abs(g - 0.5 * (a + b)) < 0.06 * 0.5 * (a + b) + 3 * abs(a - b)
+    eq, r4 = out["equal"][0], out["right4"][0]
+    assert out["equal"][1].global_photons > 0
+    # AllLights::emit picks a light with probability P_i / sum(P) and gives the photon that light's FULL power (light.rs:214-219:
+    # no division by the pick probability), so the expected power per photon is sum(P_i^2) / sum(P): (16 + 1) / 5 = 3.4 against 1
+    ratio_total = r4.mean() / eq.mean()
+    assert 3.1 < ratio_total < 3.7, ratio_total
+    # ... and one half of the image gains much more than the other (which one: Camera::new's u axis)
+    halves = [r4[:, : w // 2].mean() / eq[:, : w // 2].mean(), r4[:, w // 2:].mean() / eq[:, w // 2:].mean()]
+    assert max(halves) / min(halves) > 1.15, halves
+
+
+def test_mark_light_scaled_rejects_bad_scales():
+    b = rt.SceneBuilder()
+    m = rt.DiffuseLight(rt.ConstantTexture((1, 1, 1))).flatten(b)
+    prim = b._id(F.lib().b200rt_builder_rect(b.handle, 1, 0.0, 0.0, 1.0, 1.0, 5.0, m))
+    for bad in (0.0, -1.0, float("nan"), float("inf")):
+        assert F.lib().b200rt_builder_mark_light_scaled(b.handle, prim, bad) == F.ERR_INVALID
+    assert F.lib().b200rt_builder_mark_light_scaled(b.handle, prim, 2.5) == 0
+    d = b.desc()
+    assert d.n_lights == 1 and abs(d.light_scales[0] - 2.5) < 1e-7
