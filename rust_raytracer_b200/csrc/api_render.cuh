@@ -80,6 +80,7 @@ struct WfPipeState {
   cudaEvent_t* sev;
   WfCounters* host;
   bool done, in_flight;
+  bool tail;  // the tail kernel is in flight: the pipeline is done when it returns
   int set;  // which of the two event sets the batch in flight records into
 };
 
@@ -174,6 +175,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
     W.host = ctx->host_cnt + k;
     W.done = W.M.total == 0;
     W.in_flight = false;
+    W.tail = false;
     std::memset(W.host, 0, sizeof(WfCounters));
   }
   // the other pipelines start after whatever the caller queued on the context stream (the zeroed accumulation buffer);
@@ -270,11 +272,24 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
       }
     }
   };
+  // No new paths left and the queue has run low: ONE launch finishes the stragglers (k_wf_tail) instead of up to max_depth more
+  // near-empty iterations.  0 switches it off.
+  const unsigned int tail_rays = (unsigned int)env_int("B200RT_WF_TAIL", 65536, 0, 1 << 20);
   auto harvest = [&](WfPipeState& W) -> int {
     const int set = W.set;
     W.in_flight = false;
+    if (W.tail) { W.done = true; return B200RT_OK; }  // (its batch was collected when the tail went out)
     if (W.host->n_ext_next == 0 && W.host->next_path >= W.M.total) W.done = true;
-    else {
+    else if (tail_rays && W.host->next_path >= W.M.total && W.host->n_ext_next <= tail_rays) {
+      const int blocks = (int)std::min<unsigned int>((W.host->n_ext_next + 127u) / 128u, (unsigned int)sms * 4u);
+      if (objf) k_wf_tail<true><<<blocks, 128, 0, W.q>>>(s->dev, W.B, W.P, accum);
+      else k_wf_tail<false><<<blocks, 128, 0, W.q>>>(s->dev, W.B, W.P, accum);
+      launches += 1;
+      CU_CHECK(ctx, cudaGetLastError());
+      CU_CHECK(ctx, cudaMemcpyAsync(W.host, W.B.cnt, sizeof(WfCounters), cudaMemcpyDeviceToHost, W.q));
+      W.tail = true;
+      W.in_flight = true;
+    } else {
       W.set ^= 1;
       const int rc_e = enqueue_batch(W);
       if (rc_e) return rc_e;

@@ -451,3 +451,47 @@ __global__ void __launch_bounds__(128) k_wf_shadow(DevScene S, WfBuffers B, floa
     }
   }
 }
+
+// tail: the paths still alive when a render has no new paths left and its queue has run low are finished here, one thread per
+// path, instead of through up to max_depth more near-empty iterations of five launches each (a 400x225x100-spp render is 9 M paths
+// in ~5 ms, of which the last 30 iterations carry < 1000 rays and cost ~1 ms of launch latency and host polling).  The records are
+// the survivors of the last shade pass (the NEXT set); the draws are keyed (pixel, sample, bounce) as everywhere, so the paths are
+// the ones the queue iterations would have traced: the ray statistics and the image do not change.
+template <bool OBJF>
+__global__ void __launch_bounds__(128) k_wf_tail(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
+  const unsigned int n = B.cnt->n_ext_next;
+  unsigned long long n_ext = 0, n_shd = 0;
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 o = WF_LD(B.ray_n + 2 * (size_t)i), d = WF_LD(B.ray_n + 2 * (size_t)i + 1);
+    if (d.x == 0.f && d.y == 0.f && d.z == 0.f) continue;  // a dead record
+    const float4 sa = WF_LD(B.st_n + 2 * (size_t)i), sb = WF_LD(B.st_n + 2 * (size_t)i + 1);
+    Ray ray;
+    ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
+    PathState ps;
+    ps.throughput = f3(sa); ps.prev_pdf_b = sa.w; ps.radiance = f3(0, 0, 0);
+    ps.pixel = __float_as_uint(sb.x); ps.sample = __float_as_uint(sb.y); ps.bounce = (int)__float_as_uint(sb.z);
+    for (;;) {
+      HitRaw h;
+      trace<false, OBJF>(S, ray, P.t_min, h);
+      n_ext++;
+      if (h.prim < 0) { ps.radiance = ps.radiance + ps.throughput * background_color(P, ray.d); break; }
+      if (ps.bounce >= P.max_depth) break;  // photon_mapper.rs:336-339: the depth budget is checked after the hit
+      ShadowReq sr;
+      const bool cont = shade_hit(S, P, ray, h, ps, sr);
+      if (sr.valid) {
+        HitRaw sh;
+        trace<true, OBJF>(S, sr.ray, P.t_min, sh);
+        n_shd++;
+        if (sh.prim < 0) ps.radiance = ps.radiance + sr.contrib;
+      }
+      if (!cont) break;
+      ray.tmax = __int_as_float(0x7f800000);
+    }
+    accum_add(accum, ps.pixel, ps.radiance);
+  }
+  for (int o = 16; o > 0; o >>= 1) { n_ext += __shfl_down_sync(0xffffffffu, n_ext, o); n_shd += __shfl_down_sync(0xffffffffu, n_shd, o); }
+  if ((threadIdx.x & 31) == 0) {
+    if (n_ext) atomicAdd(&B.cnt->extend_rays, n_ext);
+    if (n_shd) atomicAdd(&B.cnt->shadow_rays, n_shd);
+  }
+}

@@ -151,7 +151,7 @@ def test_concurrent_pipelines_render_the_same_paths(ctx, integrator):
     for n in (2, 3, 4):
         a, s = out[n]
         assert (s.paths, s.extend_rays, s.shadow_rays) == (s1.paths, s1.extend_rays, s1.shadow_rays), n
-        assert s.wavefront_iterations > s1.wavefront_iterations  # iterations are counted per pipeline
+        assert s.pipelines == n and s.wavefront_iterations >= s1.wavefront_iterations  # iterations are counted per pipeline (batches of 4, then the tail kernel)
         np.testing.assert_allclose(a, a1, rtol=1e-4, atol=1e-4)
         assert np.all(a[..., 3] == 7)
 
