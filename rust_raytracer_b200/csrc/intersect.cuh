@@ -274,6 +274,23 @@ struct TStack {
   uint2* sm;  // &shared[threadIdx.x]; entry k at sm[k * B200RT_BLOCK]
 #endif
   uint2 loc[B200RT_STACK - B200RT_SSTACK];
+#ifndef B200RT_STACK_TOPREG  // 1: the top entry lives in registers, so a pop's local-memory load feeds the NEXT pop, not this one
+#define B200RT_STACK_TOPREG 0
+#endif
+#if B200RT_STACK_TOPREG && B200RT_SSTACK == 0
+  uint2 top;  // valid iff sp > 0; loc[k] holds entry k for k < sp - 1
+  DEV void push(int& sp, uint2 v) {
+    if (sp > 0) loc[sp - 1] = top;
+    top = v;
+    ++sp;
+  }
+  DEV uint2 pop(int& sp) {
+    --sp;
+    const uint2 r = top;
+    if (sp > 0) top = loc[sp - 1];
+    return r;
+  }
+#else
   DEV void push(int& sp, uint2 v) {
 #if B200RT_SSTACK > 0
     if (sp < B200RT_SSTACK) sm[sp * B200RT_BLOCK] = v; else loc[sp - B200RT_SSTACK] = v;
@@ -290,6 +307,7 @@ struct TStack {
     return loc[sp];
 #endif
   }
+#endif
 };
 
 DEV uint32_t pop_next(TStack& stack, int& sp, float t_best32) {
