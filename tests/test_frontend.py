@@ -39,6 +39,37 @@ def test_cube_obj_loader_matches_tobj_semantics():
     assert np.abs(pos).max() <= 1.000002
 
 
+def test_obj_with_several_models_and_texcoords_loads_like_mesh_rs(tmp_path):
+    """Mesh::load_obj takes `models[0]` only (mesh.rs:159) and Triangle::hit hands HitRecord::new the uv (0.0, 0.0) — the texcoord
+    interpolation is a commented-out todo!() upstream (mesh.rs:66-68, 103-128).  A two-object OBJ with vt lines and v/vt/vn faces:
+    the first object's triangles only, texture coordinates read past."""
+    obj = tmp_path / "two.obj"
+    obj.write_text("""o first
+v 0 0 0
+v 1 0 0
+v 0 1 0
+v 1 1 0
+vt 0 0
+vt 1 0
+vt 0 1
+vt 1 1
+vn 0 0 1
+f 1/1/1 2/2/1 3/3/1
+f 2/2/1 4/4/1 3/3/1
+o second
+v 0 0 5
+v 1 0 5
+v 0 1 5
+f 5//1 6//1 7//1
+""")
+    white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
+    w = rt.World(rt.HitableList([rt.Mesh.load_obj(str(obj), white)]), rt.Camera(((0, 0, 5), (0, 0, 0)), (0, 1, 0), 40, 1, 0, 1))
+    d = w.builder.desc()
+    assert d.n_prims == 2
+    z = np.array([d.prims[i].p[:9] for i in range(2)]).reshape(2, 3, 3)[..., 2]
+    assert np.all(z == 0)  # nothing of the second object
+
+
 def test_obj_without_normals_is_an_error_like_the_reference_panic():
     """bun315.obj has no vn lines: Triangle::hit would index an empty normals Vec (mesh.rs:62-64)."""
     white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
