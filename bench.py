@@ -446,7 +446,7 @@ def main():
                        "spp_per_step_total": step_spp, "spp_per_step_per_gpu": spp, "full_job_spp": FULL_JOB_SPP, "max_depth": 50, "integrator": "path", "pipeline": args.pipeline,
                        "sharding": "spp ranges per rank + NCCL sum-reduce of the accumulation buffer per step",
                        "concurrent_pipelines": n_pipes,
-                       "l2": "256 MB write between timed steps; the wavefront queues (2^26 positions x 144 B of ray/state/hit streams = 9.7 GB) exceed L2"},
+                       "l2": "256 MB write between timed steps; the wavefront queues (2^28 positions x 144 B of ray/state/hit streams = 38.7 GB) exceed L2"},
             "mrays_per_s": mrays, "rays_per_path": rays_per_path,
             "stage_ms_per_step": {k: stats[k] / args.steps for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow", "ms_total")},
             "stage_ms_sum_per_step": {k: stats[k + "_sum"] / args.steps for k in ("ms_generate", "ms_extend", "ms_shade", "ms_shadow")},

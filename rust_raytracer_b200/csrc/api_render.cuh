@@ -128,9 +128,20 @@ static void wf_bin_layout(uint32_t n_prims, unsigned int& n_bins, unsigned int& 
 
 static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMap& M0, float* accum, b200rt_stats* st) {
   b200rt_ctx* ctx = s->ctx;
-  // queue positions in flight: 144 B each (9.7 GB at 2^26 over all pipelines — HBM is plentiful, and a larger pool means
-  // fewer, fuller launches: 2^21 -> 2^24 -> 2^26 is +17 % -> +4 % on book-2, profiles/r1_experiments.md)
-  const int pool_log2 = env_int("B200RT_WF_POOL_LOG2", 26, 12, 28);
+  // queue positions in flight: 144 B each (38.7 GB at 2^28 over all pipelines — HBM is plentiful, and a larger pool means
+  // fewer, fuller launches: 2^21 -> 2^24 -> 2^26 is +17 % -> +4 % on book-2, profiles/r1_experiments.md; 2^26 -> 2^28 -> 2^30
+  // +0.8 % -> +1.1 % on the 10,000-spp job, r2_experiments.md section 10).  A render of fewer paths takes a pool of its size.
+  // At most half of the memory that is free (counting what this context's pools already hold) goes to the queues.
+  int pool_log2 = env_int("B200RT_WF_POOL_LOG2", 28, 12, 30);
+  if (!ctx->static_wf) {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+      size_t held = 0;
+      for (int k = 0; k < WF_MAX_PIPES; ++k) if (ctx->wf_block[k]) held += ctx->wf_bytes;
+      const unsigned long long budget = ((unsigned long long)free_b + held) / 2;
+      while (pool_log2 > 20 && ((unsigned long long)WF_POS_BYTES << pool_log2) > budget) --pool_log2;
+    }
+  }
   // pipelines: 2 by default when each still gets 2^24 paths (same box, 1 -> 2 pipelines: book-2 800x800x128 spp +3.2 %,
   // 318k-triangle mesh +5.1 %, Cornell NEE +2.2 %, scene_500 -1.2 %, Cornell MixturePDF at 23 M paths -3.3 %: deep
   // traversals with long launch tails gain, short renders lose to the halved launches; profiles/r1_experiments.md)
