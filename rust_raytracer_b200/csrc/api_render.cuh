@@ -15,7 +15,7 @@ static int wf_ensure_pool(b200rt_ctx* ctx, int pipe, unsigned int pool, bool sha
     size_t o_ray[2], o_st[2];
     for (int k = 0; k < 2; ++k) { o_ray[k] = take(P * 32); o_st[k] = take(P * 32); }  // the two ray / state sets
     size_t o_hit = take(P * 16);
-    size_t o_bc = take(4 * WF_MAX_BINS), o_bo = take(4 * (WF_MAX_BINS + 1)), o_cnt = take(sizeof(WfCounters));
+    size_t o_bc = take(4 * WF_MAX_BINS), o_bo = take(4 * (WF_MAX_BINS + 1)), o_cnt = take(sizeof(WfCounters)), o_sp = take(8 * WF_MAX_BINS);
     CU_CHECK(ctx, cudaMalloc(&ctx->wf_block[pipe], off));
     char* b = (char*)ctx->wf_block[pipe];
     ctx->wf_bytes = off;  // per pipeline
@@ -24,6 +24,7 @@ static int wf_ensure_pool(b200rt_ctx* ctx, int pipe, unsigned int pool, bool sha
     ctx->wf[pipe].hit = (uint4*)(b + o_hit);
     ctx->wf[pipe].bin_count = (unsigned int*)(b + o_bc); ctx->wf[pipe].bin_off = (unsigned int*)(b + o_bo);
     ctx->wf[pipe].cnt = (WfCounters*)(b + o_cnt);
+    ctx->wf[pipe].split_cnt = (unsigned int*)(b + o_sp);
     ctx->wf[pipe].sh_o = ctx->wf[pipe].sh_d = ctx->wf[pipe].sh_c = nullptr; ctx->wf[pipe].sh_seed = nullptr;
     ctx->wf[pipe].pool = pool;
   }
@@ -158,6 +159,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   const unsigned long long cap = ctx->static_wf ? (unsigned long long)ctx->static_wf->pool : (1ull << pool_log2) / (unsigned long long)n_pipes;
   unsigned int n_bins, bin_mul;
   wf_bin_layout(s->n_prims, n_bins, bin_mul);
+  const bool split_fog = env_int("B200RT_WF_SPLIT", 0, 0, 1) != 0;  // measured: extend -1.7 %, shade +7.5 %, net -2.3 % (profiles/r2_experiments.md section 11)
   const bool nee = P0.integrator == B200RT_INTEGRATOR_NEE;
   WfPipeState pipes[WF_MAX_PIPES];
   for (int k = 0; k < n_pipes; ++k) {
@@ -176,6 +178,9 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
       W.B = ctx->wf[k];
     }
     W.B.n_bins = n_bins; W.B.bin_mul = bin_mul;
+    // bins of the primitives outside the BVH are filled from both ends (wavefront.cuh); not on the static queue block
+    W.B.split_bin = (split_fog && W.B.split_cnt && !s->dev.flat && s->dev.n_bvh_prims < s->dev.n_prims && s->dev.n_bvh_prims > 0)
+                        ? 1u + (unsigned int)(((unsigned long long)(unsigned int)s->dev.n_bvh_prims * bin_mul) >> 32) : n_bins;
     if (k == 0) W.q = ctx->stream;
     else {
       if (!ctx->pipe_stream[k]) CU_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->pipe_stream[k], cudaStreamNonBlocking));

@@ -61,6 +61,11 @@ struct WfBuffers {
   unsigned int* bin_off;    // n_bins + 1: start of every bin in the next set
   unsigned int bin_mul;     // bin = 1 + umulhi(prim, bin_mul)
   unsigned int n_bins;      // multiple of 1024 (the control kernels run one 1024-thread block), <= WF_MAX_BINS
+  // Bins >= split_bin (the primitives OUTSIDE the BVH: book-2's fog) are filled from both ends by shade: rays that hit the BVH root
+  // from the front of the bin's range, rays that miss it (and dead records) from the back (split_cnt[2 bin], [2 bin + 1]).
+  // split_bin == n_bins: off.
+  unsigned int* split_cnt;
+  unsigned int split_bin;
   float4* sh_o; float4* sh_d; float4* sh_c; unsigned int* sh_seed;
   WfCounters* cnt;
   unsigned int pool;
@@ -110,6 +115,7 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfBuffers B, RenderConst P,
 // One block turns the counters over between generate and extend (no host round trip inside an iteration).
 __global__ void k_wf_control(WfBuffers B, PathMap M) {  // <<<1, WF_CTRL_THREADS>>>
   for (unsigned int k = threadIdx.x; k < B.n_bins; k += blockDim.x) B.bin_count[k] = 0;
+  if (B.split_bin < B.n_bins) for (unsigned int k = 2u * B.split_bin + threadIdx.x; k < 2u * B.n_bins; k += blockDim.x) B.split_cnt[k] = 0;
   if (threadIdx.x != 0) return;
   WfCounters* c = B.cnt;
   const unsigned int n_new = wf_new_paths(c, M, B.pool);
@@ -252,6 +258,24 @@ DEV void mbar_wait(uint32_t bar, uint32_t parity) {
 #ifndef B200RT_SHADE_MINBLOCKS  // ... MIXTURE / NEE need 120 / 126
 #define B200RT_SHADE_MINBLOCKS 4
 #endif
+// Does the ray reach any child box of the BVH root within [t_min, inf)?  (The first node step of trace(), without the stack.)
+DEV bool wf_ray_hits_root(const DevScene& S, const Ray& r, float t_min) {
+  const float3 inv = f3(safe_rcp(r.d.x), safe_rcp(r.d.y), safe_rcp(r.d.z));
+  const float4 lox = __ldg(S.nodes + 0), hix = __ldg(S.nodes + 1), loy = __ldg(S.nodes + 2), hiy = __ldg(S.nodes + 3), loz = __ldg(S.nodes + 4), hiz = __ldg(S.nodes + 5);
+  const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, hx[4] = {hix.x, hix.y, hix.z, hix.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w},
+              hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+  bool any = false;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float t0x = (lx[i] - r.o.x) * inv.x, t1x = (hx[i] - r.o.x) * inv.x, t0y = (ly[i] - r.o.y) * inv.y, t1y = (hy[i] - r.o.y) * inv.y;
+    const float t0z = (lz[i] - r.o.z) * inv.z, t1z = (hz[i] - r.o.z) * inv.z;
+    const float n = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), t_min));
+    const float f = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+    any = any || n <= f * 1.00001f;  // an ordering hint, not a decision: empty slots (inverted infinite boxes) never pass
+  }
+  return any;
+}
+
 #ifndef B200RT_SHADE_COOP_PERLIN  // 1: NOISE textures evaluated by the whole warp, one hit at a time (perlin_turb_warp): measured -0.65 %, profiles/r2_experiments.md section 7
 #define B200RT_SHADE_COOP_PERLIN 0
 #endif
@@ -404,9 +428,29 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
       accum_add(accum, ps.pixel, ps.radiance);
     }
 #endif
-    if (active && rank != WF_NO_RANK) {  // the place extend reserved in the next set: the new ray, or a dead record
-      const unsigned int bin = 1u + __umulhi((unsigned int)hprim, B.bin_mul);  // the bin extend ranked it in
-      const size_t dst = 2 * (size_t)((off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank);
+    const bool writes = active && rank != WF_NO_RANK;  // the place extend reserved in the next set: the new ray, or a dead record
+    const unsigned int bin = writes ? 1u + __umulhi((unsigned int)hprim, B.bin_mul) : 0u;  // the bin extend ranked it in
+    unsigned int slot = writes ? (off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank : 0u;
+    if (B.split_bin < B.n_bins) {
+      // A bin of a primitive OUTSIDE the BVH (book-2's fog: half of all rays are born there, anywhere in the scene, in any
+      // direction) is filled from both ends: the rays that will enter the BVH from the front, the ones that miss its root — one
+      // node step, then only the fog again — and the dead records from the back.  Extend's rank is not used there, only its count.
+      const bool split = writes && bin >= B.split_bin;
+      const bool front = split && cont && wf_ray_hits_root(S, ray, P.t_min);
+      const unsigned lane_id = threadIdx.x & 31u;
+      const unsigned int key = split ? 2u * bin + (front ? 0u : 1u) : (0x80000000u | lane_id);
+      const unsigned peers = __match_any_sync(0xffffffffu, key);
+      const int leader = __ffs((int)peers) - 1;
+      unsigned int r2 = 0;
+      if (split && (int)lane_id == leader) r2 = atomicAdd(&B.split_cnt[key], (unsigned)__popc(peers));
+      r2 = __shfl_sync(0xffffffffu, r2, leader) + __popc(peers & ((1u << lane_id) - 1u));
+      if (split) {
+        const unsigned int lo = off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin]), hi = off_in_smem ? s_off[bin + 1] : __ldg(&B.bin_off[bin + 1]);
+        slot = front ? lo + r2 : hi - 1u - r2;
+      }
+    }
+    if (writes) {
+      const size_t dst = 2 * (size_t)slot;
       float4* out = B.ray_n + dst;
       if (cont) {
         float4* out_s = B.st_n + dst;
