@@ -159,7 +159,7 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   const unsigned long long cap = ctx->static_wf ? (unsigned long long)ctx->static_wf->pool : (1ull << pool_log2) / (unsigned long long)n_pipes;
   unsigned int n_bins, bin_mul;
   wf_bin_layout(s->n_prims, n_bins, bin_mul);
-  const bool split_fog = env_int("B200RT_WF_SPLIT", 0, 0, 1) != 0;  // measured: extend -1.7 %, shade +7.5 %, net -2.3 % (profiles/r2_experiments.md section 11)
+  const bool split_fog = B200RT_SHADE_SPLIT && env_int("B200RT_WF_SPLIT", 0, 0, 1) != 0;  // measured: extend -1.7 %, shade +7.5 %, net -2.3 % (profiles/r2_experiments.md section 11)
   const bool nee = P0.integrator == B200RT_INTEGRATOR_NEE;
   WfPipeState pipes[WF_MAX_PIPES];
   for (int k = 0; k < n_pipes; ++k) {

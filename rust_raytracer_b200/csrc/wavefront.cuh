@@ -276,6 +276,9 @@ DEV bool wf_ray_hits_root(const DevScene& S, const Ray& r, float t_min) {
   return any;
 }
 
+#ifndef B200RT_SHADE_SPLIT  // 1 (and B200RT_WF_SPLIT=1 at run time): out-of-BVH bins filled from both ends by root hit: measured -2.3 %, r2_experiments.md section 11
+#define B200RT_SHADE_SPLIT 0
+#endif
 #ifndef B200RT_SHADE_COOP_PERLIN  // 1: NOISE textures evaluated by the whole warp, one hit at a time (perlin_turb_warp): measured -0.65 %, profiles/r2_experiments.md section 7
 #define B200RT_SHADE_COOP_PERLIN 0
 #endif
@@ -431,6 +434,7 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
     const bool writes = active && rank != WF_NO_RANK;  // the place extend reserved in the next set: the new ray, or a dead record
     const unsigned int bin = writes ? 1u + __umulhi((unsigned int)hprim, B.bin_mul) : 0u;  // the bin extend ranked it in
     unsigned int slot = writes ? (off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank : 0u;
+#if B200RT_SHADE_SPLIT
     if (B.split_bin < B.n_bins) {
       // A bin of a primitive OUTSIDE the BVH (book-2's fog: half of all rays are born there, anywhere in the scene, in any
       // direction) is filled from both ends: the rays that will enter the BVH from the front, the ones that miss its root — one
@@ -449,6 +453,7 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
         slot = front ? lo + r2 : hi - 1u - r2;
       }
     }
+#endif
     if (writes) {
       const size_t dst = 2 * (size_t)slot;
       float4* out = B.ray_n + dst;
