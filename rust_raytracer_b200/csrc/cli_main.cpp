@@ -5,7 +5,7 @@
 //                 [--earth earth.ppm] [--width W] [--height H] [--spp N] [--depth D] [--integrator path|mixture|nee|sppm]
 //                 [--iterations 50] [--photons 500000] [--light-scale 1e6] [--seed S] [--gpus G] [--out output/test.png]
 //
-// --integrator sppm is what the reference's main renders (SPPMIntegrator::new + capture_image, main.rs:51-53; one GPU).
+// --integrator sppm is what the reference's main renders (SPPMIntegrator::new + capture_image, main.rs:51-53); with --gpus G through b200rt_render_sppm_multi.
 //
 // --gpus G shards the samples over G devices (b200rt_render_multi: one context and one host thread per device -- the
 // reference's own decomposition is row bands over a thread pool, camera.rs:74-111 -- and one NCCL or peer-memory
@@ -145,28 +145,38 @@ int main(int argc, char** argv) {
   b200rt_scene_desc desc{};
   if (b200rt_builder_finish(b, &desc)) { std::fprintf(stderr, "scene: %s\n", b200rt_builder_error(b)); return 1; }
 
-  if (integ == "sppm") {  // main.rs:51-53: SPPMIntegrator::new(world) then capture_image(integrator)
-    b200rt_ctx* ctx = nullptr;
-    if (b200rt_ctx_create(0, &ctx)) { std::fprintf(stderr, "no CUDA device (there is no CPU fallback)\n"); return 1; }
-    b200rt_scene* sc = nullptr;
-    if (b200rt_scene_create(ctx, &desc, &sc)) { std::fprintf(stderr, "scene: %s\n", b200rt_last_error(ctx)); return 1; }
+  if (integ == "sppm") {  // main.rs:51-53: SPPMIntegrator::new(world) then capture_image(integrator); --gpus G: b200rt_render_sppm_multi
+    std::vector<Shard> shards(gpus);
+    {
+      std::vector<std::thread> threads;
+      for (int g = 0; g < gpus; ++g) { shards[g].device = g; threads.emplace_back(create_shard, &desc, &shards[g]); }
+      for (auto& t : threads) t.join();
+    }
+    std::vector<b200rt_scene*> scenes(gpus);
+    for (int g = 0; g < gpus; ++g) {
+      if (shards[g].rc) { std::fprintf(stderr, "scene on device %d: %s (there is no CPU fallback)\n", g, shards[g].err.c_str()); return 1; }
+      scenes[g] = shards[g].scene;
+    }
+    b200rt_ctx* ctx = shards[0].ctx;
     params.spp_begin = 0; params.spp_count = spp;
     b200rt_sppm_params sp{};
     sp.iterations = iterations; sp.photons_per_iter = photons; sp.k_global = 100; sp.k_caustic = 50; sp.alpha = 0.7; sp.light_scale = light_scale;
     b200rt_sppm_stats st{};
     std::vector<float> accum((size_t)params.width * params.height * 4, 0.f);
-    if (b200rt_render_sppm(sc, &cam, &params, &sp, accum.data(), nullptr, &st)) { std::fprintf(stderr, "sppm: %s\n", b200rt_last_error(ctx)); return 1; }
+    rc = gpus > 1 ? b200rt_render_sppm_multi(gpus, scenes.data(), &cam, &params, &sp, accum.data(), nullptr, &st)
+                  : b200rt_render_sppm(scenes[0], &cam, &params, &sp, accum.data(), nullptr, &st);
+    if (rc) { std::fprintf(stderr, "sppm: %s\n", b200rt_last_error(ctx)); return 1; }
     std::vector<uint8_t> rgb8((size_t)params.width * params.height * 3);
     if (b200rt_tonemap_rgb8(ctx, accum.data(), params.width, params.height, rgb8.data())) { std::fprintf(stderr, "tonemap: %s\n", b200rt_last_error(ctx)); return 1; }
-    b200rt_scene_destroy(sc);
-    b200rt_ctx_destroy(ctx);
+    for (int g = 0; g < gpus; ++g) { b200rt_scene_destroy(shards[g].scene); b200rt_ctx_destroy(shards[g].ctx); }
     b200rt_builder_destroy(b);
     if (b200rt_write_png(out.c_str(), rgb8.data(), params.width, params.height)) { std::fprintf(stderr, "cannot write %s\n", out.c_str()); return 1; }
-    const double sppm_s = (st.ms_photons + st.ms_grid + st.ms_eye) * 1e-3, rt_s = st.ms_final * 1e-3;
+    // one device: CUDA-event stage times (photons overlap the eye passes); several: host clocks of the iterations and of the rest
+    const double sppm_s = gpus > 1 ? st.ms_eye * 1e-3 : (st.ms_total - st.ms_final) * 1e-3, rt_s = st.ms_final * 1e-3;
     std::printf("Total: %.3fs\n\tSPPM: %.3fs\n\tRT: %.3fs\n", seconds_since(t_start), sppm_s, rt_s);
-    std::printf("%dx%d, %d iterations x %d photons (%llu global, %llu caustic stored), %d spp: photons %.1f ms, grid %.1f ms, eye %.1f ms, final %.1f ms -> %s\n",
-                params.width, params.height, iterations, photons, (unsigned long long)st.global_photons, (unsigned long long)st.caustic_photons, spp,
-                st.ms_photons, st.ms_grid, st.ms_eye, st.ms_final, out.c_str());
+    std::printf("%dx%d, %d iterations x %d photons (%llu global, %llu caustic stored), %d spp on %d GPU(s): total %.1f ms (photons %.1f, grid %.1f, eye %.1f, final %.1f) -> %s\n",
+                params.width, params.height, iterations, photons, (unsigned long long)st.global_photons, (unsigned long long)st.caustic_photons, spp, gpus,
+                st.ms_total, st.ms_photons, st.ms_grid, st.ms_eye, st.ms_final, out.c_str());
     return 0;
   }
   const auto t_rt = std::chrono::steady_clock::now();

@@ -318,3 +318,25 @@ def test_mark_light_scaled_rejects_bad_scales():
     assert F.lib().b200rt_builder_mark_light_scaled(b.handle, prim, 2.5) == 0
     d = b.desc()
     assert d.n_lights == 1 and abs(d.light_scales[0] - 2.5) < 1e-7
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gpus", [1, 2])
+def test_cli_renders_sppm(ctx, tmp_path, gpus):
+    """The reference's main() over the C ABI (main.rs:49-72: SPPMIntegrator::new + capture_image + save + the Total / SPPM / RT
+    lines); with --gpus 2 through b200rt_render_sppm_multi."""
+    import ctypes as C
+    import subprocess
+    from PIL import Image
+    from rust_raytracer_b200.build import CLI
+    n = C.c_int(0)
+    F.lib().b200rt_device_count(C.byref(n))
+    if n.value < gpus:
+        pytest.skip("needs %d GPUs" % gpus)
+    out = str(tmp_path / "sppm.png")
+    r = subprocess.run([CLI, "--scene", "cornell_ref", "--integrator", "sppm", "--width", "64", "--height", "64", "--spp", "4", "--iterations", "3", "--photons", "20000",
+                        "--gpus", str(gpus), "--out", out], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Total:" in r.stdout and "SPPM:" in r.stdout and "RT:" in r.stdout and "%d GPU(s)" % gpus in r.stdout
+    img = np.asarray(Image.open(out).convert("RGB"))
+    assert img.shape == (64, 64, 3) and img.mean() > 5  # a lit Cornell box, not a black frame
