@@ -270,6 +270,15 @@ int b200rt_scene_info(const b200rt_scene* scene, uint64_t* h2d_bytes, uint32_t* 
 int b200rt_scene_compile_stats(const b200rt_scene_desc* desc, uint32_t* bvh_nodes, uint32_t* bvh4_depth,
                                uint32_t* stack_needed, uint32_t* stack_capacity);
 
+/* Host only (no CUDA): the surface-area estimate of that BVH — BVH4 node steps and primitive tests a random line through the
+ * scene's box pays (sum of node areas, and of leaf area x leaf size, over the root's area) — and the scene's DENSE BOX if it has
+ * one: a box of at most half of the root's surface holding >= 90 % of the BVH's primitives (a 300,000-triangle mesh in a
+ * room of a dozen walls).  capture_image's wavefront queues then keep the rays that cross it apart from the rest
+ * (DESIGN.md section 4).  No counterpart in the reference (bvh.rs:60-83 splits at the median of a random axis).
+ * Any out pointer may be NULL; dense_lo / dense_hi: 3 floats each, zero when there is no dense box. */
+int b200rt_scene_bvh_quality(const b200rt_scene_desc* desc, float* node_steps, float* prim_tests, int32_t* has_dense_box,
+                             float* dense_lo, float* dense_hi);
+
 /* ---- World::hit as a batch operator (world.rs:27-29) -------------------- */
 /* o_time: n x (ox,oy,oz,time); d_tmax: n x (dx,dy,dz,t_max); medium_seed: n x u32 or NULL (the draw
  * ConstantMedium::hit takes inside `hit`, medium.rs:37-38, derived as u01(hash(seed, prim))).

@@ -120,6 +120,7 @@ mod manual {
         pub fn b200rt_scene_create(ctx: *mut b200rt_ctx, desc: *const b200rt_scene_desc, out: *mut *mut b200rt_scene) -> c_int;
         pub fn b200rt_scene_destroy(scene: *mut b200rt_scene) -> c_int;
         pub fn b200rt_scene_info(scene: *const b200rt_scene, h2d_bytes: *mut u64, bvh_nodes: *mut u32, device_prims: *mut u32) -> c_int;
+    pub fn b200rt_scene_bvh_quality(desc: *const b200rt_scene_desc, node_steps: *mut f32, prim_tests: *mut f32, has_dense_box: *mut i32, dense_lo: *mut f32, dense_hi: *mut f32) -> c_int;
     pub fn b200rt_scene_compile_stats(desc: *const b200rt_scene_desc, bvh_nodes: *mut u32, bvh4_depth: *mut u32, stack_needed: *mut u32, stack_capacity: *mut u32) -> c_int;
     pub fn b200rt_debug_eval(scene: *mut b200rt_scene, cam: *const b200rt_camera, params: *const b200rt_params, kind: i32, n: u64, in_host: *const f32, out_host: *mut f32) -> c_int;
         // ---- World::hit over a batch (world.rs:27-29)

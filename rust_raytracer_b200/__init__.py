@@ -6,4 +6,4 @@ does not load the library; the first call does, and fails loudly if libb200rt.so
 """
 from . import _ffi as ffi  # noqa: F401
 from .api import *  # noqa: F401,F403
-from .engine import Context, Scene, make_params, copy_params, render_multi, render_sppm_multi, compile_stats, HIT_DTYPE  # noqa: F401
+from .engine import Context, Scene, make_params, copy_params, render_multi, render_sppm_multi, compile_stats, bvh_quality, HIT_DTYPE  # noqa: F401

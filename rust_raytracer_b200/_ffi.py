@@ -138,6 +138,7 @@ PROTOTYPES = {
     "b200rt_scene_create": (C.c_int, [VP, C.POINTER(SceneDesc), C.POINTER(VP)]),
     "b200rt_scene_destroy": (C.c_int, [VP]),
     "b200rt_scene_info": (C.c_int, [VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "b200rt_scene_bvh_quality": (C.c_int, [C.POINTER(SceneDesc), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b200rt_scene_compile_stats": (C.c_int, [C.POINTER(SceneDesc), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "b200rt_debug_eval": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(Params), C.c_int32, C.c_uint64, VP, VP]),
     "b200rt_intersect_batch": (C.c_int, [VP, VP, VP, VP, C.c_uint64, C.c_float, VP]),

@@ -53,6 +53,8 @@ struct b200rt_scene {
   size_t block_bytes = 0;
   uint64_t h2d_bytes = 0;
   uint32_t n_nodes = 0, n_prims = 0;
+  bool has_dense_box = false;  // scene_compile.cpp dense_box: the wavefront queues keep the rays that cross it apart from the rest
+  float dense_lo[3] = {0, 0, 0}, dense_hi[3] = {0, 0, 0};
 };
 
 namespace { void multi_forget_device(int device); }  // api_multi.cuh
@@ -234,6 +236,8 @@ int b200rt_scene_create(b200rt_ctx* ctx, const b200rt_scene_desc* desc, b200rt_s
   sc->dev.prim_obj = (const float4*)(base + parts[12].off);
   sc->dev.instances_d = (const double*)(base + parts[13].off);
   sc->dev.inst_eps = (const float*)(base + parts[14].off);
+  sc->has_dense_box = cs.has_dense_box;
+  for (int a = 0; a < 3; ++a) { sc->dense_lo[a] = cs.dense_lo[a]; sc->dense_hi[a] = cs.dense_hi[a]; }
   sc->dev.n_prims = (int)cs.n_prims; sc->dev.n_bvh_prims = (int)cs.n_bvh_prims; sc->dev.n_nodes = (int)cs.n_nodes; sc->dev.n_lights = (int)cs.n_lights; sc->dev.flat = cs.flat ? 1 : 0; sc->dev.has_objf = cs.has_objf ? 1 : 0;
   sc->h2d_bytes = total; sc->n_nodes = cs.n_nodes; sc->n_prims = cs.n_prims;
   sc->device = ctx->device;

@@ -159,7 +159,12 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   const unsigned long long cap = ctx->static_wf ? (unsigned long long)ctx->static_wf->pool : (1ull << pool_log2) / (unsigned long long)n_pipes;
   unsigned int n_bins, bin_mul;
   wf_bin_layout(s->n_prims, n_bins, bin_mul);
-  const bool split_fog = B200RT_SHADE_SPLIT && env_int("B200RT_WF_SPLIT", 0, 0, 1) != 0;  // measured: extend -1.7 %, shade +7.5 %, net -2.3 % (profiles/r2_experiments.md section 11)
+  // Two-ended bins (WfBuffers::split_bin).  -1: every bin by the scene's dense box when it has one and the BVH is large (a mesh in a
+  // room); 0: off; 1: the out-of-BVH bins by root hit (book-2's fog; measured: extend -1.7 %, shade +7.5 %, net -2.3 %,
+  // profiles/r2_experiments.md section 11); 2: the dense box whatever the size of the BVH.
+  const int split_mode = env_int("B200RT_WF_SPLIT", -1, -1, 2);
+  const bool split_box = !s->dev.flat && s->has_dense_box && (split_mode == 2 || (split_mode == -1 && s->dev.n_bvh_prims >= env_int("B200RT_WF_SPLIT_MIN_PRIMS", 8192, 1, 1 << 27)));
+  const bool split_fog = split_mode == 1 && !s->dev.flat && s->dev.n_bvh_prims < s->dev.n_prims && s->dev.n_bvh_prims > 0;
   const bool nee = P0.integrator == B200RT_INTEGRATOR_NEE;
   WfPipeState pipes[WF_MAX_PIPES];
   for (int k = 0; k < n_pipes; ++k) {
@@ -179,8 +184,9 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
     }
     W.B.n_bins = n_bins; W.B.bin_mul = bin_mul;
     // bins of the primitives outside the BVH are filled from both ends (wavefront.cuh); not on the static queue block
-    W.B.split_bin = (split_fog && W.B.split_cnt && !s->dev.flat && s->dev.n_bvh_prims < s->dev.n_prims && s->dev.n_bvh_prims > 0)
-                        ? 1u + (unsigned int)(((unsigned long long)(unsigned int)s->dev.n_bvh_prims * bin_mul) >> 32) : n_bins;
+    W.B.split_bin = !W.B.split_cnt ? n_bins : split_box ? 0u : split_fog ? 1u + (unsigned int)(((unsigned long long)(unsigned int)s->dev.n_bvh_prims * bin_mul) >> 32) : n_bins;
+    W.B.split_box = split_box ? 1 : 0;
+    W.B.split_lo = make_float3(s->dense_lo[0], s->dense_lo[1], s->dense_lo[2]); W.B.split_hi = make_float3(s->dense_hi[0], s->dense_hi[1], s->dense_hi[2]);
     if (k == 0) W.q = ctx->stream;
     else {
       if (!ctx->pipe_stream[k]) CU_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->pipe_stream[k], cudaStreamNonBlocking));
@@ -220,9 +226,13 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   const bool objf = s->dev.has_objf != 0;  // any primitive filtered in object space (rotated Cube / rectangle, ellipsoid)?
   CU_CHECK(ctx, objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<false>, 128, 0));
   CU_CHECK(ctx, objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow<false>, 128, 0));
-  CU_CHECK(ctx, P0.integrator == B200RT_INTEGRATOR_PATH ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_PATH>, 128, 0)
-                : P0.integrator == B200RT_INTEGRATOR_MIXTURE ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_MIXTURE>, 128, 0)
-                                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<B200RT_INTEGRATOR_NEE>, 128, 0));
+  const bool split = pipes[0].B.split_bin < n_bins;  // the same for every pipeline
+  {
+    const void* shade_fn = P0.integrator == B200RT_INTEGRATOR_PATH ? (split ? (const void*)k_wf_shade<B200RT_INTEGRATOR_PATH, true> : (const void*)k_wf_shade<B200RT_INTEGRATOR_PATH, false>)
+                         : P0.integrator == B200RT_INTEGRATOR_MIXTURE ? (split ? (const void*)k_wf_shade<B200RT_INTEGRATOR_MIXTURE, true> : (const void*)k_wf_shade<B200RT_INTEGRATOR_MIXTURE, false>)
+                         : (split ? (const void*)k_wf_shade<B200RT_INTEGRATOR_NEE, true> : (const void*)k_wf_shade<B200RT_INTEGRATOR_NEE, false>);
+    CU_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, shade_fn, 128, 0));
+  }
   const int grid_ext = sms * env_int("B200RT_WF_EXT_GRID", occ_ext > 0 ? occ_ext : 1, 1, occ_ext > 0 ? occ_ext : 1), grid_shadow = sms * (occ_shadow > 0 ? occ_shadow : 1);
   const int grid_gen = sms * 8, grid_shade = sms * env_int("B200RT_WF_SHADE_GRID", occ_shade > 5 ? 5 : (occ_shade > 0 ? occ_shade : 1), 1, 64);
   // (one resident wave of shade blocks: a larger grid widens the window of queue positions in flight, which interleaves
@@ -253,9 +263,11 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
 #endif
       cudaEventRecord(ev[2], q);
       k_wf_control_shade<<<1, WF_CTRL_THREADS, 0, q>>>(B);
-      if (W.P.integrator == B200RT_INTEGRATOR_PATH) k_wf_shade<B200RT_INTEGRATOR_PATH><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
-      else if (W.P.integrator == B200RT_INTEGRATOR_MIXTURE) k_wf_shade<B200RT_INTEGRATOR_MIXTURE><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
-      else k_wf_shade<B200RT_INTEGRATOR_NEE><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum);
+#define B200RT_LAUNCH_SHADE(I) do { if (split) k_wf_shade<I, true><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum); else k_wf_shade<I, false><<<grid_shade, 128, 0, q>>>(s->dev, B, W.P, accum); } while (0)
+      if (W.P.integrator == B200RT_INTEGRATOR_PATH) B200RT_LAUNCH_SHADE(B200RT_INTEGRATOR_PATH);
+      else if (W.P.integrator == B200RT_INTEGRATOR_MIXTURE) B200RT_LAUNCH_SHADE(B200RT_INTEGRATOR_MIXTURE);
+      else B200RT_LAUNCH_SHADE(B200RT_INTEGRATOR_NEE);
+#undef B200RT_LAUNCH_SHADE
       cudaEventRecord(ev[3], q);
       launches += 5;
       if (nee) {

@@ -125,7 +125,7 @@ struct SppmPhotonWf {
 // scene-dependent part of a photon queue set: bins, kernel variants, launch sizes (cheap; every call)
 int sppm_photon_wf_configure(b200rt_ctx* ctx, const b200rt_scene* s, SppmPhotonWf& W) {
   wf_bin_layout(s->n_prims, W.B.n_bins, W.B.bin_mul);
-  W.B.split_cnt = nullptr; W.B.split_bin = W.B.n_bins;  // (the two-ended bins are the path tracer's shade kernel's)
+  W.B.split_cnt = nullptr; W.B.split_bin = W.B.n_bins; W.B.split_box = 0;  // (the two-ended bins are the path tracer's shade kernel's)
   W.sms = ctx->prop.multiProcessorCount;
   W.objf = s->dev.has_objf != 0;
   int occ_ext = 1, occ_shade = 1;

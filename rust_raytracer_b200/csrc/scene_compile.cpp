@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <numeric>
 
@@ -45,10 +46,15 @@ struct BinBuilder {
   std::vector<D3> centroid;
   std::vector<int> order;
   std::vector<BinNode> nodes;
+  std::vector<float> size_key;  // -log2(box area): the fourth split "axis" of build()
+  bool size_split = true;       // B200RT_BVH_SIZE_SPLIT=0 turns the size axis off (A/B of the builder)
   explicit BinBuilder(const std::vector<Box>& boxes) : pb(boxes) {
     order.resize(pb.size());
     std::iota(order.begin(), order.end(), 0);
     centroid.resize(pb.size());
+    size_key.resize(pb.size());
+    for (size_t i = 0; i < pb.size(); ++i) { const float a = pb[i].area(); size_key[i] = -std::log2(a > 1e-30f ? (a < 1e30f ? a : 1e30f) : 1e-30f); }
+    if (const char* e = std::getenv("B200RT_BVH_SIZE_SPLIT")) size_split = std::atoi(e) != 0;
     for (size_t i = 0; i < pb.size(); ++i) centroid[i] = D3(0.5 * ((double)pb[i].lo[0] + pb[i].hi[0]), 0.5 * ((double)pb[i].lo[1] + pb[i].hi[1]), 0.5 * ((double)pb[i].lo[2] + pb[i].hi[2]));
   }
   // depth_left: binary levels this subtree may still use.  While the budget is roomy the split is binned SAH; once
@@ -61,17 +67,27 @@ struct BinBuilder {
     Box box, cbox;
     for (int i = first; i < first + count; ++i) { box.grow(pb[order[i]]); D3 c = centroid[order[i]]; for (int a = 0; a < 3; ++a) { cbox.lo[a] = std::min(cbox.lo[a], (float)c[a]); cbox.hi[a] = std::max(cbox.hi[a], (float)c[a]); } }
     nodes[id].box = box;
+    nodes[id].first = first; nodes[id].count = count;  // inner nodes too: the size of the subtree (dense_box below)
     if (count == 1) { nodes[id].first = first; nodes[id].count = count; return id; }
-    // binned SAH over the three axes
+    // binned SAH over the three centroid axes and, as a fourth "axis", the primitives' size (-log2 of the box area: large first).
+    // A room of a dozen walls around a 300,000-triangle mesh has no good spatial split near the root — every plane through the
+    // mesh leaves walls on both sides, so both halves keep the room's box and every ray descends both — but it has a very good
+    // split by size: the walls | the mesh.  Same cost function, so the size split is only taken where it is the cheaper one.
     const int NB = 16;
+    float klo[4], khi[4];
+    for (int a = 0; a < 3; ++a) { klo[a] = cbox.lo[a]; khi[a] = cbox.hi[a]; }
+    klo[3] = FLT_MAX; khi[3] = -FLT_MAX;
+    if (size_split) for (int i = first; i < first + count; ++i) { klo[3] = std::min(klo[3], size_key[order[i]]); khi[3] = std::max(khi[3], size_key[order[i]]); }
+    auto key_of = [&](int p, int axis) { return axis < 3 ? (float)centroid[p][axis] : size_key[p]; };
     float best_cost = FLT_MAX; int best_axis = -1, best_split = -1;
-    for (int axis = 0; axis < 3; ++axis) {
-      float ext = cbox.hi[axis] - cbox.lo[axis];
+    for (int axis = 0; axis < (size_split ? 4 : 3); ++axis) {
+      float ext = khi[axis] - klo[axis];
       if (!(ext > 0)) continue;
+      if (axis == 3 && ext < 2.f) continue;  // sizes within a factor of four: nothing to separate
       Box bins[NB]; int cnt[NB] = {0};
       float k = NB * (1 - 1e-6f) / ext;
       for (int i = first; i < first + count; ++i) {
-        int bi = std::min(NB - 1, std::max(0, (int)(((float)centroid[order[i]][axis] - cbox.lo[axis]) * k)));
+        int bi = std::min(NB - 1, std::max(0, (int)((key_of(order[i], axis) - klo[axis]) * k)));
         bins[bi].grow(pb[order[i]]); cnt[bi]++;
       }
       float right_area[NB]; int right_cnt[NB];
@@ -97,10 +113,10 @@ struct BinBuilder {
     } else if (best_axis < 0) {  // all centroids coincide: split the range in the middle
       mid = first + count / 2;
     } else {
-      float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
+      float ext = khi[best_axis] - klo[best_axis];
       float k = NB * (1 - 1e-6f) / ext;
       auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](int p) {
-        int bi = std::min(NB - 1, std::max(0, (int)(((float)centroid[p][best_axis] - cbox.lo[best_axis]) * k)));
+        int bi = std::min(NB - 1, std::max(0, (int)((key_of(p, best_axis) - klo[best_axis]) * k)));
         return bi <= best_split;
       });
       mid = (int)(it - order.begin());
@@ -113,18 +129,42 @@ struct BinBuilder {
   }
 };
 
+// The box of the scene's dense part, if it has one: from the root down, follow the child that keeps >= 90 % of the primitives
+// for as long as there is one (the size split of build() puts a room's few large walls on one side of the root and a 300,000-
+// triangle mesh on the other).  Accepted when what is left is at most half of the root's surface: a ray then either crosses that
+// box — a long traversal — or is done after a few node steps, and the wavefront queues keep the two kinds apart
+// (WfBuffers::split_lo, wavefront.cuh).
+bool dense_box(const BinBuilder& bb, int root, Box& out) {
+  const int total = bb.nodes[root].count;
+  int cur = root;
+  for (;;) {
+    const BinNode& n = bb.nodes[cur];
+    if (n.left < 0) break;
+    const int l = bb.nodes[n.left].count, r = bb.nodes[n.right].count;
+    const int next = l >= r ? n.left : n.right;
+    if ((long long)std::max(l, r) * 10 < (long long)total * 9) break;
+    cur = next;
+  }
+  if (cur == root) return false;
+  out = bb.nodes[cur].box;
+  return out.area() <= 0.5f * bb.nodes[root].box.area();
+}
+
 void put4(std::vector<float>& v, size_t at, float a, float b, float c, float d) { v[at] = a; v[at + 1] = b; v[at + 2] = c; v[at + 3] = d; }
 float ibits(int32_t i) { float f; std::memcpy(&f, &i, 4); return f; }
 float ubits(uint32_t i) { float f; std::memcpy(&f, &i, 4); return f; }
 
 // Collapse the binary tree into BVH4 nodes (128 B each); returns the node index.  depth_out: levels of BVH4 nodes below
 // and including this one (the traversal pushes at most 3 entries per level: node_step in intersect.cuh).
-int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out, int& depth_out) {
+// sah[0] += area of this node's box, sah[1] += area x primitives of every leaf child: divided by the root's area these are the node
+// steps and primitive tests a random line through the scene pays (the SAH estimate b200rt_scene_bvh_quality reports).
+int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out, int& depth_out, double* sah) {
   int my = (int)(out.size() / 32);
   int deepest = 0;
   out.resize(out.size() + 32, 0.f);
   int kids[4]; int nk = 0;
   const BinNode& root = bb.nodes[bin_id];
+  sah[0] += root.box.area();
   if (root.left < 0) { kids[nk++] = bin_id; }
   else {
     kids[nk++] = root.left; kids[nk++] = root.right;
@@ -146,8 +186,8 @@ int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out, int& dep
   for (int i = 0; i < nk; ++i) {
     const BinNode& c = bb.nodes[kids[i]];
     for (int a = 0; a < 3; ++a) { lo[a][i] = c.box.lo[a]; hi[a][i] = c.box.hi[a]; }
-    if (c.left < 0) refs[i] = (int32_t)(B200RT_LEAF_BIT | ((uint32_t)(c.count - 1) << 27) | (uint32_t)c.first);
-    else { int dk = 0; refs[i] = collapse(bb, kids[i], out, dk); deepest = std::max(deepest, dk); }
+    if (c.left < 0) { refs[i] = (int32_t)(B200RT_LEAF_BIT | ((uint32_t)(c.count - 1) << 27) | (uint32_t)c.first); sah[1] += (double)c.box.area() * c.count; }
+    else { int dk = 0; refs[i] = collapse(bb, kids[i], out, dk, sah); deepest = std::max(deepest, dk); }
   }
   depth_out = deepest + 1;
   size_t at = (size_t)my * 32;
@@ -344,8 +384,14 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
       cs.nodes.clear();
       cs.nodes.reserve(in_idx.size() * 16);
       int depth4 = 0;
-      collapse(bb, root, cs.nodes, depth4);
+      double sah[2] = {0., 0.};
+      collapse(bb, root, cs.nodes, depth4, sah);
       cs.bvh4_depth = (uint32_t)depth4;
+      const double root_area = std::max((double)bb.nodes[root].box.area(), 1e-300);
+      cs.sah_node_steps = (float)(sah[0] / root_area); cs.sah_prim_tests = (float)(sah[1] / root_area);
+      Box dense;
+      cs.has_dense_box = dense_box(bb, root, dense);
+      for (int a = 0; a < 3; ++a) { cs.dense_lo[a] = cs.has_dense_box ? dense.lo[a] : 0.f; cs.dense_hi[a] = cs.has_dense_box ? dense.hi[a] : 0.f; }
       bb_order.swap(bb.order);
       if (3 * depth4 <= B200RT_STACK) break;
     }
@@ -451,5 +497,17 @@ extern "C" int b200rt_scene_compile_stats(const b200rt_scene_desc* desc, uint32_
   if (bvh4_depth) *bvh4_depth = cs.bvh4_depth;
   if (stack_needed) *stack_needed = 3 * cs.bvh4_depth;
   if (stack_capacity) *stack_capacity = B200RT_STACK;
+  return B200RT_OK;
+}
+
+extern "C" int b200rt_scene_bvh_quality(const b200rt_scene_desc* desc, float* node_steps, float* prim_tests, int32_t* has_dense_box, float* dense_lo, float* dense_hi) {
+  b200rt::CompiledScene cs;
+  std::string err;
+  const int rc = b200rt::compile_scene(desc, cs, err);
+  if (rc) return rc;
+  if (node_steps) *node_steps = cs.sah_node_steps;
+  if (prim_tests) *prim_tests = cs.sah_prim_tests;
+  if (has_dense_box) *has_dense_box = cs.has_dense_box ? 1 : 0;
+  for (int a = 0; a < 3; ++a) { if (dense_lo) dense_lo[a] = cs.dense_lo[a]; if (dense_hi) dense_hi[a] = cs.dense_hi[a]; }
   return B200RT_OK;
 }

@@ -27,6 +27,9 @@ struct CompiledScene {
   uint32_t n_prims = 0, n_bvh_prims = 0, n_nodes = 0, n_lights = 0;
   uint32_t bvh4_depth = 0;  // levels of BVH4 nodes; the traversal stack needs at most 3 entries per level
   bool flat = false;
+  float sah_node_steps = 0.f, sah_prim_tests = 0.f;  // SAH estimate of the BVH: node steps / primitive tests of a random line through the root box
+  bool has_dense_box = false;  // the BVH has a small box holding >= 90 % of its primitives (scene_compile.cpp dense_box)
+  float dense_lo[3] = {0, 0, 0}, dense_hi[3] = {0, 0, 0};
   bool has_objf = false;  // some primitive is filtered in object space (B200RT_PRIM_OBJF)
 };
 

@@ -61,11 +61,15 @@ struct WfBuffers {
   unsigned int* bin_off;    // n_bins + 1: start of every bin in the next set
   unsigned int bin_mul;     // bin = 1 + umulhi(prim, bin_mul)
   unsigned int n_bins;      // multiple of 1024 (the control kernels run one 1024-thread block), <= WF_MAX_BINS
-  // Bins >= split_bin (the primitives OUTSIDE the BVH: book-2's fog) are filled from both ends by shade: rays that hit the BVH root
-  // from the front of the bin's range, rays that miss it (and dead records) from the back (split_cnt[2 bin], [2 bin + 1]).
-  // split_bin == n_bins: off.
+  // Bins >= split_bin are filled from both ends by shade (k_wf_shade<INTEG, true>): the rays expected to traverse for long from the
+  // front of the bin's range, the others and the dead records from the back (split_cnt[2 bin], [2 bin + 1]); extend then meets
+  // warps of one kind.  split_box: every bin, "long" = the ray crosses the scene's dense box [split_lo, split_hi] (a 300,000-
+  // triangle mesh in a room of a dozen walls: scene_compile.cpp dense_box).  Otherwise the bins of the primitives OUTSIDE the BVH
+  // (book-2's fog) by whether the ray reaches the BVH root (measured and left off).  split_bin == n_bins: off.
   unsigned int* split_cnt;
   unsigned int split_bin;
+  int split_box;
+  float3 split_lo, split_hi;
   float4* sh_o; float4* sh_d; float4* sh_c; unsigned int* sh_seed;
   WfCounters* cnt;
   unsigned int pool;
@@ -276,13 +280,21 @@ DEV bool wf_ray_hits_root(const DevScene& S, const Ray& r, float t_min) {
   return any;
 }
 
-#ifndef B200RT_SHADE_SPLIT  // 1 (and B200RT_WF_SPLIT=1 at run time): out-of-BVH bins filled from both ends by root hit: measured -2.3 %, r2_experiments.md section 11
-#define B200RT_SHADE_SPLIT 0
-#endif
+// Does the ray cross the box within [t_min, inf)?  An ordering hint like wf_ray_hits_root, not a decision.
+DEV bool wf_ray_hits_box(const float3 lo, const float3 hi, const Ray& r, float t_min) {
+  const float3 inv = f3(safe_rcp(r.d.x), safe_rcp(r.d.y), safe_rcp(r.d.z));
+  const float t0x = (lo.x - r.o.x) * inv.x, t1x = (hi.x - r.o.x) * inv.x, t0y = (lo.y - r.o.y) * inv.y, t1y = (hi.y - r.o.y) * inv.y;
+  const float t0z = (lo.z - r.o.z) * inv.z, t1z = (hi.z - r.o.z) * inv.z;
+  const float n = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), t_min));
+  const float f = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+  return n <= f * 1.00001f;
+}
+
 #ifndef B200RT_SHADE_COOP_PERLIN  // 1: NOISE textures evaluated by the whole warp, one hit at a time (perlin_turb_warp): measured -0.65 %, profiles/r2_experiments.md section 7
 #define B200RT_SHADE_COOP_PERLIN 0
 #endif
-template <int INTEG>
+// SPLIT: the two-ended bins of WfBuffers::split_bin (a separate instantiation: the plain one is the kernel the book scenes run)
+template <int INTEG, bool SPLIT>
 __global__ void __launch_bounds__(128, INTEG == B200RT_INTEGRATOR_PATH ? B200RT_SHADE_MINBLOCKS_PATH : B200RT_SHADE_MINBLOCKS)
 k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
   __shared__ unsigned int s_off[WF_SMEM_BINS + 1];
@@ -434,13 +446,11 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
     const bool writes = active && rank != WF_NO_RANK;  // the place extend reserved in the next set: the new ray, or a dead record
     const unsigned int bin = writes ? 1u + __umulhi((unsigned int)hprim, B.bin_mul) : 0u;  // the bin extend ranked it in
     unsigned int slot = writes ? (off_in_smem ? s_off[bin] : __ldg(&B.bin_off[bin])) + rank : 0u;
-#if B200RT_SHADE_SPLIT
-    if (B.split_bin < B.n_bins) {
-      // A bin of a primitive OUTSIDE the BVH (book-2's fog: half of all rays are born there, anywhere in the scene, in any
-      // direction) is filled from both ends: the rays that will enter the BVH from the front, the ones that miss its root — one
-      // node step, then only the fog again — and the dead records from the back.  Extend's rank is not used there, only its count.
+    if (SPLIT) {
+      // Extend's rank is not used in a two-ended bin, only its count: the place is taken from the front or the back of the bin's
+      // range by one atomic per (bin, end) present in the warp.
       const bool split = writes && bin >= B.split_bin;
-      const bool front = split && cont && wf_ray_hits_root(S, ray, P.t_min);
+      const bool front = split && cont && (B.split_box ? wf_ray_hits_box(B.split_lo, B.split_hi, ray, P.t_min) : wf_ray_hits_root(S, ray, P.t_min));
       const unsigned lane_id = threadIdx.x & 31u;
       const unsigned int key = split ? 2u * bin + (front ? 0u : 1u) : (0x80000000u | lane_id);
       const unsigned peers = __match_any_sync(0xffffffffu, key);
@@ -453,7 +463,6 @@ k_wf_shade(DevScene S, WfBuffers B, RenderConst P, float* __restrict__ accum) {
         slot = front ? lo + r2 : hi - 1u - r2;
       }
     }
-#endif
     if (writes) {
       const size_t dst = 2 * (size_t)slot;
       float4* out = B.ray_n + dst;

@@ -174,6 +174,18 @@ def compile_stats(builder_or_desc):
     return dict(zip(("bvh_nodes", "bvh4_depth", "stack_needed", "stack_capacity"), [x.value for x in v]))
 
 
+def bvh_quality(builder_or_desc):
+    """Host only: the surface-area estimate of the BVH scene_create would build and the scene's dense box, if any —
+    {"node_steps", "prim_tests", "dense_box": None | (lo[3], hi[3])} (b200rt_scene_bvh_quality)."""
+    desc = builder_or_desc.desc() if hasattr(builder_or_desc, "desc") else builder_or_desc
+    ns, pt, has = C.c_float(), C.c_float(), C.c_int32()
+    lo, hi = (C.c_float * 3)(), (C.c_float * 3)()
+    rc = F.lib().b200rt_scene_bvh_quality(C.byref(desc), C.byref(ns), C.byref(pt), C.byref(has), lo, hi)
+    if rc:
+        raise B200RTError(rc, "scene_bvh_quality")
+    return {"node_steps": ns.value, "prim_tests": pt.value, "dense_box": (tuple(lo), tuple(hi)) if has.value else None}
+
+
 def render_multi(scenes, camera, params):
     """capture_image sharded by sample index over the devices of `scenes` (the same scene created on one Context per GPU) with
     one NCCL / peer-memory sum-reduce onto scenes[0]'s device (b200rt_render_multi).

@@ -207,6 +207,26 @@ def test_bvh_depth_is_bounded_by_the_traversal_stack():
     assert st["bvh4_depth"] <= 10  # the budget never touches an ordinary scene
 
 
+def test_bvh_quality_size_axis_and_dense_box(monkeypatch):
+    """Host only.  A mesh in a room: the builder's size axis puts the walls on one side of the root and the mesh on the other, which
+    lowers the surface-area estimate of the tree and exposes the mesh's box as the scene's dense box; the book scenes have none."""
+    sb = scene_builder("mesh_small")
+    q = rt.bvh_quality(sb)
+    assert q["dense_box"] is not None
+    lo, hi = (np.array(v) for v in q["dense_box"])
+    assert np.all(lo > -1.0) and np.all(hi < 556.0) and np.all(hi > lo)
+    ext = hi - lo
+    assert 2 * (ext[0] * ext[1] + ext[1] * ext[2] + ext[2] * ext[0]) <= 0.5 * 6 * 555.1 ** 2
+    monkeypatch.setenv("B200RT_BVH_SIZE_SPLIT", "0")
+    q0 = rt.bvh_quality(sb)
+    monkeypatch.delenv("B200RT_BVH_SIZE_SPLIT")
+    assert q0["dense_box"] is None and q["node_steps"] < 0.9 * q0["node_steps"] and q["prim_tests"] <= 1.05 * q0["prim_tests"]
+    for name in ("book1", "book2", "cornell_book3", "json:scene_500"):
+        assert rt.bvh_quality(scene_builder(name))["dense_box"] is None, name
+    with pytest.raises(rt.B200RTError):
+        rt.bvh_quality(rt.SceneBuilder())  # BVHNode::new on an empty list
+
+
 def test_scene_500_yaml_builds_the_same_tables_as_its_json_twin():
     """README.md:86-89: data/scene_500.yaml (894 KB, 1,005 spheres, 999 BVHNodes) carries the same objects as scene_500.json."""
     a = rt.SceneBuilder().load_json(open(os.path.join(DATA, "scene_500.json")).read())

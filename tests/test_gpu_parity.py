@@ -309,6 +309,26 @@ def test_wavefront_equals_megakernel(ctx):
     np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)  # float summation order only
 
 
+@pytest.mark.parametrize("name,integrator,mode", [("mesh_small", F.INTEGRATOR_MIXTURE, "2"), ("mesh_small", F.INTEGRATOR_NEE, "2"), ("mesh_small", F.INTEGRATOR_PATH, "2"),
+                                                   ("book2", F.INTEGRATOR_PATH, "1")])
+def test_two_ended_bins_trace_the_same_paths(ctx, name, integrator, mode, monkeypatch):
+    """The queue order is not part of the result: filling the bins from both ends (B200RT_WF_SPLIT: 2 = by the scene's dense box,
+    1 = the out-of-BVH bins by root hit) traces the very same paths as plain bins (0), against the megakernel as well."""
+    sb = scene_builder(name)
+    if mode == "2":
+        assert rt.bvh_quality(sb)["dense_box"] is not None
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=160, height=120, spp_count=32, integrator=integrator)
+    monkeypatch.setenv("B200RT_WF_SPLIT", "0")
+    a, sa = scene.render(sb.camera, p)
+    monkeypatch.setenv("B200RT_WF_SPLIT", mode)
+    b, sbt = scene.render(sb.camera, p)
+    m, sm = scene.render(sb.camera, rt.copy_params(p, pipeline=F.PIPELINE_MEGAKERNEL))
+    assert sa.extend_rays == sbt.extend_rays == sm.extend_rays and sa.shadow_rays == sbt.shadow_rays == sm.shadow_rays
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)  # float summation order only
+    np.testing.assert_allclose(m, b, rtol=1e-4, atol=1e-4)
+
+
 def test_spp_sharding_is_additive(ctx):
     """Multi-GPU sharding rule: samples [0,8) + [8,16) == samples [0,16) (global sample index keys the RNG)."""
     sb = scene_builder("cornell_book3")

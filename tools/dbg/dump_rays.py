@@ -1,6 +1,6 @@
 """Dump a sample of one extend launch (rays, hits, per-ray node / leaf counts) from a -DB200RT_COUNTERS build.
 
-  python -c "from rust_raytracer_b200.build import build_variant; build_variant('counters', ['B200RT_COUNTERS'])"
+  python -c "from rust_raytracer_b200.build import build_counters; build_counters()"
   python tools/dbg/dump_rays.py [scene] [iteration] [out.bin] [spp] [warp stride]
 
 The file is read by tools/dbg/analyze_rays.py (offline: lane occupancy of the traversal under alternative queue orders).
@@ -11,7 +11,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
-os.environ.setdefault("B200RT_LIB", os.path.join(ROOT, "tools", "dbg", "libb200rt_counters.so"))
+os.environ.setdefault("B200RT_LIB", os.path.join(ROOT, "rust_raytracer_b200", "libb200rt_counters.so"))
 name = sys.argv[1] if len(sys.argv) > 1 else "book2"
 it = sys.argv[2] if len(sys.argv) > 2 else "12"
 out = sys.argv[3] if len(sys.argv) > 3 else os.path.join(ROOT, "gpurun_out", "rays_%s_%s.bin" % (name, it))
