@@ -417,6 +417,12 @@ DEV uint32_t node_step(const DevScene& S, const RayF& rf, const RayT& rt, uint32
   if (tn[3] < 3.0e38f) stack.push(sp, make_uint2(rr[3], __float_as_uint(tn[3])));
   if (tn[2] < 3.0e38f) stack.push(sp, make_uint2(rr[2], __float_as_uint(tn[2])));
   if (tn[1] < 3.0e38f) stack.push(sp, make_uint2(rr[1], __float_as_uint(tn[1])));
+#ifndef B200RT_NODE_PREFETCH  // 1: the second-nearest child's node (one 128 B line) is pulled towards L1 when it is pushed
+#define B200RT_NODE_PREFETCH 0
+#endif
+#if B200RT_NODE_PREFETCH
+  if (tn[1] < 3.0e38f && !(rr[1] & B200RT_LEAF_BIT)) asm volatile("prefetch.global.L1 [%0];" ::"l"(rt.nodes + (rr[1] << 3)));
+#endif
   if (tn[0] < 3.0e38f) return rr[0];
   return pop_next(stack, sp, t_best32);
 }
