@@ -49,6 +49,7 @@ struct BinBuilder {
   std::vector<float> size_key;  // -log2(box area): the fourth split "axis" of build()
   bool size_split = true;       // B200RT_BVH_SIZE_SPLIT=0 turns the size axis off (A/B of the builder)
   int n_bins = 16;              // SAH bins per axis (B200RT_BVH_BINS, 4..64)
+  float trav_cost = 0.f;        // cost of a node step in primitive tests when deciding leaf against split (B200RT_BVH_TRAV_COST)
   explicit BinBuilder(const std::vector<Box>& boxes) : pb(boxes) {
     order.resize(pb.size());
     std::iota(order.begin(), order.end(), 0);
@@ -56,6 +57,7 @@ struct BinBuilder {
     size_key.resize(pb.size());
     for (size_t i = 0; i < pb.size(); ++i) { const float a = pb[i].area(); size_key[i] = -std::log2(a > 1e-30f ? (a < 1e30f ? a : 1e30f) : 1e-30f); }
     if (const char* e = std::getenv("B200RT_BVH_SIZE_SPLIT")) size_split = std::atoi(e) != 0;
+    if (const char* e = std::getenv("B200RT_BVH_TRAV_COST")) trav_cost = (float)std::atof(e);
     if (const char* e = std::getenv("B200RT_BVH_BINS")) n_bins = std::min(64, std::max(4, std::atoi(e)));
     for (size_t i = 0; i < pb.size(); ++i) centroid[i] = D3(0.5 * ((double)pb[i].lo[0] + pb[i].hi[0]), 0.5 * ((double)pb[i].lo[1] + pb[i].hi[1]), 0.5 * ((double)pb[i].lo[2] + pb[i].hi[2]));
   }
@@ -105,7 +107,7 @@ struct BinBuilder {
       }
     }
     float leaf_cost = box.area() * count;
-    if (count <= B200RT_MAX_LEAF && (best_axis < 0 || best_cost >= leaf_cost)) { nodes[id].first = first; nodes[id].count = count; return id; }
+    if (count <= B200RT_MAX_LEAF && (best_axis < 0 || best_cost + trav_cost * box.area() >= leaf_cost)) { nodes[id].first = first; nodes[id].count = count; return id; }
     const bool force_median = depth_left < 31 && (long long)count > (1ll << std::max(0, depth_left - 1));
     int mid;
     if (force_median) {
@@ -139,13 +141,15 @@ struct BinBuilder {
 // (WfBuffers::split_lo, wavefront.cuh).
 bool dense_box(const BinBuilder& bb, int root, Box& out) {
   const int total = bb.nodes[root].count;
+  int pct = 90;  // B200RT_BVH_DENSE_PCT: the share of the primitives the box must keep (A/B of the predictor)
+  if (const char* e = std::getenv("B200RT_BVH_DENSE_PCT")) pct = std::min(100, std::max(50, std::atoi(e)));
   int cur = root;
   for (;;) {
     const BinNode& n = bb.nodes[cur];
     if (n.left < 0) break;
     const int l = bb.nodes[n.left].count, r = bb.nodes[n.right].count;
     const int next = l >= r ? n.left : n.right;
-    if ((long long)std::max(l, r) * 10 < (long long)total * 9) break;
+    if ((long long)std::max(l, r) * 100 < (long long)total * pct) break;
     cur = next;
   }
   if (cur == root) return false;
