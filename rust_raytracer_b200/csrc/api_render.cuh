@@ -227,6 +227,13 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
   CU_CHECK(ctx, objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend<false>, 128, 0));
   CU_CHECK(ctx, objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shadow, k_wf_shadow<false>, 128, 0));
   const bool split = pipes[0].B.split_bin < n_bins;  // the same for every pipeline
+  // per-lane ray replacement in extend (k_wf_extend_dyn): scenes with a dense box whose primitives are all inside the BVH
+  bool dyn_extend = env_int("B200RT_WF_DYN", 0, 0, 1) != 0 && split && pipes[0].B.split_box && !s->dev.flat && s->dev.n_bvh_prims == s->dev.n_prims;
+  const int dyn_thresh = env_int("B200RT_WF_DYN_THRESH", 16, 1, 32);
+#ifdef B200RT_COUNTERS
+  if (dump_path && *dump_path) dyn_extend = false;  // the per-ray step dump is k_wf_extend's
+#endif
+  if (dyn_extend) CU_CHECK(ctx, objf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend_dyn<true>, 128, 0) : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_ext, k_wf_extend_dyn<false>, 128, 0));
   {
     const void* shade_fn = P0.integrator == B200RT_INTEGRATOR_PATH ? (split ? (const void*)k_wf_shade<B200RT_INTEGRATOR_PATH, true> : (const void*)k_wf_shade<B200RT_INTEGRATOR_PATH, false>)
                          : P0.integrator == B200RT_INTEGRATOR_MIXTURE ? (split ? (const void*)k_wf_shade<B200RT_INTEGRATOR_MIXTURE, true> : (const void*)k_wf_shade<B200RT_INTEGRATOR_MIXTURE, false>)
@@ -256,7 +263,10 @@ static int render_wavefront(b200rt_scene* s, const RenderConst& P0, const PathMa
       k_wf_generate<<<grid_gen, 256, 0, q>>>(B, W.P, W.M);
       k_wf_control<<<1, WF_CTRL_THREADS, 0, q>>>(B, W.M);
       cudaEventRecord(ev[1], q);
-      if (objf) k_wf_extend<true><<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
+      if (dyn_extend) {
+        if (objf) k_wf_extend_dyn<true><<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters, dyn_thresh);
+        else k_wf_extend_dyn<false><<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters, dyn_thresh);
+      } else if (objf) k_wf_extend<true><<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
       else k_wf_extend<false><<<grid_ext, 128, 0, q>>>(s->dev, B, W.P.t_min, light_scatters);
 #ifdef B200RT_COUNTERS
       if (dump_steps && (int)iters == dump_iter) dbg_dump_iteration(s, B, q, dump_steps, dump_path, dump_stride);

@@ -240,6 +240,117 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
   }
 }
 
+// extend with per-lane ray replacement, for scenes with a dense box (a mesh in a room: WfBuffers::split_box).  There the rays that
+// cross the box take 12 to 40 node steps each and a warp of k_wf_extend runs as long as its deepest lane (6 of 32 lanes per
+// instruction, profiles/r2_mesh_split_extend_shade_full.txt).  Here a lane that has finished its ray waits only until `thresh`
+// lanes of its warp are idle; those lanes then store their hits, take their ranks and fetch the next rays of the queue together,
+// outside the node loop, and start at the root while the others go on.  On book-2 (5 node steps per ray, an out-of-BVH tail that
+// wants the warp converged) the same idea lost 20-80 % twice (profiles/r1_experiments.md); the refill costs ~200 instructions per
+// group of >= thresh rays, which is noise against 2,500 per box-crossing ray and ruin against 700.  Scenes whose primitives are
+// all inside the BVH only (no tail after the traversal); the host falls back to k_wf_extend otherwise.
+#ifndef B200RT_EXTEND_DYN_MINBLOCKS
+#define B200RT_EXTEND_DYN_MINBLOCKS 7
+#endif
+template <bool OBJF>
+__global__ void __launch_bounds__(128, B200RT_EXTEND_DYN_MINBLOCKS) k_wf_extend_dyn(DevScene S, WfBuffers B, float t_min, int light_scatters, int thresh) {
+  const unsigned int n = B.cnt->n_ext;
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu;
+  unsigned int idx = 0xffffffffu;  // queue position of the ray this lane holds; none
+  uint32_t cur = B200RT_TRAV_DONE;
+  bool more = true;                // the queue still has rays (warp-uniform)
+  // the ray, once: RayF plus the two per-ray terms of RayT that are not in it (Ray and RayT are re-assembled from these where
+  // trace()'s callees want them: a second copy of o, d and 1/d kept across the refill branch costs the registers the node step needs)
+  RayF rf;
+  float3 oi = f3(0.f, 0.f, 0.f);
+  float slack = 0.f;
+  unsigned int mseed = 0u;
+  HitRaw h;
+  TStack stack;
+  int sp = 0;
+  float t_best32 = 0.f;
+  rf.o = rf.d = rf.inv = f3(0.f, 0.f, 0.f); rf.a = 0.f; rf.time = 0.f;
+  h.t = 0.; h.prim = -1; h.aux = 0;
+  for (;;) {
+    const unsigned idle = __ballot_sync(FULL, cur == B200RT_TRAV_DONE);
+    if (idle == FULL || (more && (int)__popc(idle) >= thresh)) {
+      bool more_l = more;
+      if (cur == B200RT_TRAV_DONE) {  // exactly the lanes of `idle`
+        // (1) finished rays: will the path go on?  bin, rank inside the bin (one atomic per bin present), hit record
+        const bool has = idx != 0xffffffffu;
+        unsigned int bin = WF_NO_BIN;
+        if (has && h.prim >= 0) {
+          const int4 meta = __ldg(&S.prim_meta[h.prim]);
+          const int mtype = __float_as_int(__ldg(&S.materials[meta.x >> 8]).x);
+          if (mtype != B200RT_MAT_DIFFUSE_LIGHT || light_scatters) bin = 1u + __umulhi((unsigned int)h.prim, B.bin_mul);
+        }
+        const bool goes_on = bin != WF_NO_BIN;
+        const unsigned peers = __match_any_sync(idle, goes_on ? bin : (0x80000000u | lane));
+        const int leader = __ffs((int)peers) - 1;
+        unsigned int rank = 0;
+        if (goes_on && (int)lane == leader) rank = atomicAdd(&B.bin_count[bin], (unsigned)__popc(peers));
+        rank = __shfl_sync(idle, rank, leader) + __popc(peers & ((1u << lane) - 1u));
+        if (has) {
+          const unsigned long long tb = (unsigned long long)__double_as_longlong(h.t);
+          WF_ST(B.hit + idx, make_uint4((unsigned int)tb, (unsigned int)(tb >> 32), wf_pack_prim(h.prim, h.aux), goes_on ? rank : WF_NO_RANK));
+          idx = 0xffffffffu;
+        }
+        // (2) the next rays of the queue, one per idle lane
+        if (more) {
+          const unsigned k = __popc(idle);
+          const int first = __ffs((int)idle) - 1;
+          unsigned int base = 0;
+          if ((int)lane == first) base = atomicAdd(&B.cnt->ext_cursor, k);
+          base = __shfl_sync(idle, base, first);
+          more_l = base + k < n;
+          const unsigned int i = base + __popc(idle & ((1u << lane) - 1u));
+          bool dead = false;
+          if (i < n) {
+            const float4 o = WF_LD(B.ray + 2 * (size_t)i), d = WF_LD(B.ray + 2 * (size_t)i + 1);
+            dead = d.x == 0.f && d.y == 0.f && d.z == 0.f;
+            if (dead) {  // nothing to trace, nothing goes on
+              WF_ST(B.hit + i, make_uint4(0u, 0u, wf_pack_prim(WF_PRIM_DEAD, 0), WF_NO_RANK));
+            } else {
+              idx = i;
+              Ray ray;
+              ray.o = f3(o); ray.time = o.w; ray.d = f3(d); ray.tmax = __int_as_float(0x7f800000); ray.mseed = __float_as_uint(d.w);
+              rf = make_rayf(ray);
+              const RayT rt = make_rayt(S, rf);
+              oi = rt.oi; slack = rt.slack; mseed = ray.mseed;
+              h.t = (double)ray.tmax; h.prim = -1; h.aux = 0;
+              t_best32 = ray.tmax;
+              sp = 0;
+              cur = 0u;  // root
+              DBG_INC(0);
+            }
+          }
+          const unsigned n_dead = __popc(__ballot_sync(idle, dead));
+          if (n_dead && (int)lane == first) atomicAdd(&B.cnt->dead_rays, (unsigned long long)n_dead);
+        }
+      }
+      more = __shfl_sync(FULL, more_l, __ffs((int)idle) - 1) != 0;
+      if (!__any_sync(FULL, cur != B200RT_TRAV_DONE)) {
+        if (!more) break;
+        continue;  // a group of dead records only: fetch again
+      }
+    }
+    {
+      RayT rt;
+      asm("mov.b64 %0, %1;" : "=l"(rt.nodes) : "l"(S.nodes));
+      rt.inv = rf.inv; rt.oi = oi; rt.slack = slack;
+      while (!(cur & B200RT_LEAF_BIT)) cur = node_step(S, rf, rt, cur, t_min, t_best32, stack, sp);
+    }
+    if (cur != B200RT_TRAV_DONE) {
+      Ray ray;
+      ray.o = rf.o; ray.d = rf.d; ray.time = rf.time; ray.tmax = __int_as_float(0x7f800000); ray.mseed = mseed;
+      const int first = (int)(cur & 0x07FFFFFFu), count = (int)((cur >> 27) & 15u) + 1;
+      DBG_INC(2);
+      for (int k = first; k < first + count; ++k) test_prim<OBJF>(S, ray, rf, k, t_min, t_best32, h);
+      cur = pop_next(stack, sp, t_best32);
+    }
+  }
+}
+
 // ---- bulk asynchronous copies (TMA, 1-D): global -> shared memory behind an mbarrier
 #ifndef B200RT_SHADE_BULK  // > 0: stages of the shade kernel's input tiles kept in flight by cp.async.bulk (0: plain loads + L2 prefetch)
 #define B200RT_SHADE_BULK 0

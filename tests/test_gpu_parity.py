@@ -329,6 +329,23 @@ def test_two_ended_bins_trace_the_same_paths(ctx, name, integrator, mode, monkey
     np.testing.assert_allclose(m, b, rtol=1e-4, atol=1e-4)
 
 
+def test_extend_with_ray_replacement_traces_the_same_paths(ctx, monkeypatch):
+    """k_wf_extend_dyn (B200RT_WF_DYN=1, off by default: measured slower, profiles/r2_experiments.md section 12) hands a finished lane the
+    next ray of the queue instead of waiting for its warp: same rays, same hits, same image."""
+    sb = scene_builder("mesh_small")
+    scene = rt.Scene(ctx, sb)
+    p = rt.copy_params(sb.params, width=160, height=120, spp_count=32, integrator=F.INTEGRATOR_MIXTURE)
+    monkeypatch.setenv("B200RT_WF_SPLIT", "2")
+    a, sa = scene.render(sb.camera, p)
+    for thresh in ("1", "16", "32"):
+        monkeypatch.setenv("B200RT_WF_DYN", "1")
+        monkeypatch.setenv("B200RT_WF_DYN_THRESH", thresh)
+        b, sbt = scene.render(sb.camera, p)
+        monkeypatch.setenv("B200RT_WF_DYN", "0")
+        assert sa.extend_rays == sbt.extend_rays and sa.paths == sbt.paths
+        np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)  # float summation order only
+
+
 def test_spp_sharding_is_additive(ctx):
     """Multi-GPU sharding rule: samples [0,8) + [8,16) == samples [0,16) (global sample index keys the RNG)."""
     sb = scene_builder("cornell_book3")
