@@ -164,7 +164,8 @@ __global__ void k_wf_control_shadow(WfBuffers B) { B.cnt->shadow_rays += B.cnt->
 // the ray stream), traverse, store the hit and rank the queue position inside its bin for shade.
 // (Measured and rejected: per-lane ray replacement a la Aila & Laine's dynamic fetch.  Refilling idle lanes from
 // the queue mixes rays of different bins in one warp and loses the converged out-of-BVH tail: 60 ms -> 74..99 ms
-// of extend per step on book-2 for refill thresholds 16..28, profiles/r1_experiments.md.)
+// of extend per step on book-2 for refill thresholds 16..28, profiles/r1_experiments.md.  k_wf_extend_dyn below is the
+// third implementation, for scenes with a dense box: correct, 8 % slower than this kernel there, off by default.)
 #ifndef B200RT_EXTEND_BATCHES  // 32-ray batches a warp takes per cursor atomic (the later ones prefetched into L2)
 #define B200RT_EXTEND_BATCHES 1
 #endif
@@ -248,6 +249,9 @@ __global__ void __launch_bounds__(128, B200RT_EXTEND_MINBLOCKS) k_wf_extend(DevS
 // wants the warp converged) the same idea lost 20-80 % twice (profiles/r1_experiments.md); the refill costs ~200 instructions per
 // group of >= thresh rays, which is noise against 2,500 per box-crossing ray and ruin against 700.  Scenes whose primitives are
 // all inside the BVH only (no tail after the traversal); the host falls back to k_wf_extend otherwise.
+// MEASURED (profiles/r2_experiments.md section 12): 197 ms against k_wf_extend's 182 on the mesh config.  The replacement buys 5 %
+// (209 ms when the same code refills only whole warps) and the per-lane state carried across the refill branch costs 15 %
+// (270 B of spills at 72 registers).  Launched only with B200RT_WF_DYN=1; kept with its parity test as the record of the attempt.
 #ifndef B200RT_EXTEND_DYN_MINBLOCKS
 #define B200RT_EXTEND_DYN_MINBLOCKS 7
 #endif
