@@ -48,7 +48,7 @@ struct BinBuilder {
   std::vector<BinNode> nodes;
   std::vector<float> size_key;  // -log2(box area): the fourth split "axis" of build()
   bool size_split = true;       // B200RT_BVH_SIZE_SPLIT=0 turns the size axis off (A/B of the builder)
-  int n_bins = 16;              // SAH bins per axis (B200RT_BVH_BINS, 4..64)
+  int n_bins = 16;              // SAH bins per axis (B200RT_BVH_BINS, 4..32)
   float trav_cost = 0.f;        // cost of a node step in primitive tests when deciding leaf against split (B200RT_BVH_TRAV_COST)
   explicit BinBuilder(const std::vector<Box>& boxes) : pb(boxes) {
     order.resize(pb.size());
@@ -58,7 +58,7 @@ struct BinBuilder {
     for (size_t i = 0; i < pb.size(); ++i) { const float a = pb[i].area(); size_key[i] = -std::log2(a > 1e-30f ? (a < 1e30f ? a : 1e30f) : 1e-30f); }
     if (const char* e = std::getenv("B200RT_BVH_SIZE_SPLIT")) size_split = std::atoi(e) != 0;
     if (const char* e = std::getenv("B200RT_BVH_TRAV_COST")) trav_cost = (float)std::atof(e);
-    if (const char* e = std::getenv("B200RT_BVH_BINS")) n_bins = std::min(64, std::max(4, std::atoi(e)));
+    if (const char* e = std::getenv("B200RT_BVH_BINS")) n_bins = std::min(32, std::max(4, std::atoi(e)));
     for (size_t i = 0; i < pb.size(); ++i) centroid[i] = D3(0.5 * ((double)pb[i].lo[0] + pb[i].hi[0]), 0.5 * ((double)pb[i].lo[1] + pb[i].hi[1]), 0.5 * ((double)pb[i].lo[2] + pb[i].hi[2]));
   }
   // depth_left: binary levels this subtree may still use.  While the budget is roomy the split is binned SAH; once
@@ -72,12 +72,12 @@ struct BinBuilder {
     for (int i = first; i < first + count; ++i) { box.grow(pb[order[i]]); D3 c = centroid[order[i]]; for (int a = 0; a < 3; ++a) { cbox.lo[a] = std::min(cbox.lo[a], (float)c[a]); cbox.hi[a] = std::max(cbox.hi[a], (float)c[a]); } }
     nodes[id].box = box;
     nodes[id].first = first; nodes[id].count = count;  // inner nodes too: the size of the subtree (dense_box below)
-    if (count == 1) { nodes[id].first = first; nodes[id].count = count; return id; }
+    if (count == 1) return id;
     // binned SAH over the three centroid axes and, as a fourth "axis", the primitives' size (-log2 of the box area: large first).
     // A room of a dozen walls around a 300,000-triangle mesh has no good spatial split near the root — every plane through the
     // mesh leaves walls on both sides, so both halves keep the room's box and every ray descends both — but it has a very good
     // split by size: the walls | the mesh.  Same cost function, so the size split is only taken where it is the cheaper one.
-    const int NBMAX = 64;
+    const int NBMAX = 32;
     const int NB = n_bins;
     float klo[4], khi[4];
     for (int a = 0; a < 3; ++a) { klo[a] = cbox.lo[a]; khi[a] = cbox.hi[a]; }
@@ -85,17 +85,18 @@ struct BinBuilder {
     if (size_split) for (int i = first; i < first + count; ++i) { klo[3] = std::min(klo[3], size_key[order[i]]); khi[3] = std::max(khi[3], size_key[order[i]]); }
     auto key_of = [&](int p, int axis) { return axis < 3 ? (float)centroid[p][axis] : size_key[p]; };
     float best_cost = FLT_MAX; int best_axis = -1, best_split = -1;
+    Box bins[NBMAX]; int cnt[NBMAX];
+    float right_area[NBMAX]; int right_cnt[NBMAX];
     for (int axis = 0; axis < (size_split ? 4 : 3); ++axis) {
       float ext = khi[axis] - klo[axis];
       if (!(ext > 0)) continue;
       if (axis == 3 && ext < 2.f) continue;  // sizes within a factor of four: nothing to separate
-      Box bins[NBMAX]; int cnt[NBMAX] = {0};
+      for (int b = 0; b < NB; ++b) { bins[b] = Box(); cnt[b] = 0; }
       float k = NB * (1 - 1e-6f) / ext;
       for (int i = first; i < first + count; ++i) {
         int bi = std::min(NB - 1, std::max(0, (int)((key_of(order[i], axis) - klo[axis]) * k)));
         bins[bi].grow(pb[order[i]]); cnt[bi]++;
       }
-      float right_area[NBMAX]; int right_cnt[NBMAX];
       Box acc; int c = 0;
       for (int i = NB - 1; i > 0; --i) { acc.grow(bins[i]); c += cnt[i]; right_area[i] = acc.area(); right_cnt[i] = c; }
       Box lacc; int lc = 0;
