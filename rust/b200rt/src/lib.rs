@@ -151,6 +151,16 @@ impl SceneBuilder {
         self.ok(unsafe { sys::b200rt_builder_load_yaml(self.raw, text.as_ptr().cast(), text.len() as u64, &mut cam) })?;
         Ok(cam)
     }
+    /// Host only: the surface-area estimate of the BVH `Scene::new` would build (node steps, primitive tests per random line) and
+    /// the scene's dense box, if it has one (`b200rt_scene_bvh_quality`; no counterpart in the reference).
+    pub fn bvh_quality(&mut self) -> Result<(f32, f32, Option<([f32; 3], [f32; 3])>)> {
+        let mut desc: sys::b200rt_scene_desc = unsafe { std::mem::zeroed() };
+        self.ok(unsafe { sys::b200rt_builder_finish(self.raw, &mut desc) })?;
+        let (mut nodes, mut prims, mut has) = (0f32, 0f32, 0i32);
+        let (mut lo, mut hi) = ([0f32; 3], [0f32; 3]);
+        self.ok(unsafe { sys::b200rt_scene_bvh_quality(&desc, &mut nodes, &mut prims, &mut has, lo.as_mut_ptr(), hi.as_mut_ptr()) })?;
+        Ok((nodes, prims, if has != 0 { Some((lo, hi)) } else { None }))
+    }
 }
 impl Drop for SceneBuilder { fn drop(&mut self) { unsafe { sys::b200rt_builder_destroy(self.raw); } } }
 
