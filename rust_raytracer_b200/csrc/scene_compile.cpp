@@ -5,10 +5,13 @@
 // binned-SAH binary build collapsed to 4-wide nodes; topology does not affect closest-hit results.
 #include <algorithm>
 #include <cfloat>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <future>
 #include <numeric>
+#include <thread>
 
 #include "scene_compile.hpp"
 
@@ -42,34 +45,98 @@ struct BinNode {
 };
 
 struct BinBuilder {
-  const std::vector<Box>& pb;
-  std::vector<D3> centroid;
-  std::vector<int> order;
+  // One record per primitive, kept in BUILD ORDER: every pass over a node's range streams through memory (box, centroid and
+  // size travel with the index when a range is partitioned) instead of gathering through an index array — the top levels of a
+  // 300,000-primitive build are passes over 15 MB and were latency-bound as gathers.
+  struct Item {
+    Box box;
+    float key[4];  // centroid x, y, z; -log2(box area): the fourth split "axis" of build()
+    int id;
+  };
+  std::vector<Item> items;
+  std::vector<int> order;       // filled by build(): the primitives in leaf order
   std::vector<BinNode> nodes;
-  std::vector<float> size_key;  // -log2(box area): the fourth split "axis" of build()
   bool size_split = true;       // B200RT_BVH_SIZE_SPLIT=0 turns the size axis off (A/B of the builder)
   int n_bins = 16;              // SAH bins per axis (B200RT_BVH_BINS, 4..32)
   float trav_cost = 0.f;        // cost of a node step in primitive tests when deciding leaf against split (B200RT_BVH_TRAV_COST)
-  explicit BinBuilder(const std::vector<Box>& boxes) : pb(boxes) {
-    order.resize(pb.size());
-    std::iota(order.begin(), order.end(), 0);
-    centroid.resize(pb.size());
-    size_key.resize(pb.size());
-    for (size_t i = 0; i < pb.size(); ++i) { const float a = pb[i].area(); size_key[i] = -std::log2(a > 1e-30f ? (a < 1e30f ? a : 1e30f) : 1e-30f); }
+  explicit BinBuilder(const std::vector<Box>& boxes) {
+    items.resize(boxes.size());
+    for (size_t i = 0; i < boxes.size(); ++i) {
+      Item& it = items[i];
+      it.box = boxes[i];
+      it.id = (int)i;
+      for (int a = 0; a < 3; ++a) it.key[a] = (float)(0.5 * ((double)boxes[i].lo[a] + boxes[i].hi[a]));
+      const float ar = boxes[i].area();
+      it.key[3] = -std::log2(ar > 1e-30f ? (ar < 1e30f ? ar : 1e30f) : 1e-30f);
+    }
     if (const char* e = std::getenv("B200RT_BVH_SIZE_SPLIT")) size_split = std::atoi(e) != 0;
     if (const char* e = std::getenv("B200RT_BVH_TRAV_COST")) trav_cost = (float)std::atof(e);
     if (const char* e = std::getenv("B200RT_BVH_BINS")) n_bins = std::min(32, std::max(4, std::atoi(e)));
-    for (size_t i = 0; i < pb.size(); ++i) centroid[i] = D3(0.5 * ((double)pb[i].lo[0] + pb[i].hi[0]), 0.5 * ((double)pb[i].lo[1] + pb[i].hi[1]), 0.5 * ((double)pb[i].lo[2] + pb[i].hi[2]));
   }
   // depth_left: binary levels this subtree may still use.  While the budget is roomy the split is binned SAH; once
   // count > 2^(depth_left - 1) only an even split still fits, so the range is halved at the median of its widest
   // centroid axis (a chain of geometrically growing primitives, or a deep mesh, would otherwise give a tree whose
   // BVH4 collapse needs more traversal-stack entries than B200RT_STACK).
+  // Node slots are assigned up front — a subtree over c primitives owns the 2c - 1 slots from its root's, the left child's
+  // subtree starts at the next slot and the right child's 2 * (left count) slots after its root — so the halves of a large node
+  // can be built on two threads without sharing anything but disjoint ranges of `items` and `nodes`, and the tree does not
+  // depend on the thread count (slots a subtree does not need stay unused).  par: thread-doubling levels still available; a
+  // node that still has some of them also bins its four axes on four threads (the top of the tree is where the time is).
   int build(int first, int count, int depth_left = 1 << 20) {
-    int id = (int)nodes.size();
-    nodes.emplace_back();
-    Box box, cbox;
-    for (int i = first; i < first + count; ++i) { box.grow(pb[order[i]]); D3 c = centroid[order[i]]; for (int a = 0; a < 3; ++a) { cbox.lo[a] = std::min(cbox.lo[a], (float)c[a]); cbox.hi[a] = std::max(cbox.hi[a], (float)c[a]); } }
+    unsigned hw = std::thread::hardware_concurrency();
+    if (const char* e = std::getenv("B200RT_BVH_THREADS")) hw = (unsigned)std::max(1, std::atoi(e));
+    int par = 0;
+    while ((1u << par) < std::min(std::max(hw, 1u), 16u)) ++par;
+    nodes.assign((size_t)2 * count, BinNode());
+    const int root = build(first, count, depth_left, par, 0);
+    order.resize(items.size());
+    for (size_t i = 0; i < items.size(); ++i) order[i] = items[i].id;
+    return root;
+  }
+  static const int NBMAX = 32;
+  // best split of [first, first + count) along one axis: cost and bin, or FLT_MAX
+  void best_on_axis(int first, int count, int axis, float klo, float khi, float& cost_out, int& split_out) const {
+    cost_out = FLT_MAX; split_out = -1;
+    const int NB = n_bins;
+    const float ext = khi - klo;
+    if (!(ext > 0)) return;
+    if (axis == 3 && ext < 2.f) return;  // sizes within a factor of four: nothing to separate
+    // (three quarters of a tree's nodes hold <= 8 primitives: bins are created on first touch and the sweeps visit only the
+    //  occupied ones — between two occupied bins every split index gives the same partition and the first of them, the one a
+    //  sweep over all bins would keep under its strict <, is the occupied bin itself)
+    struct RawBox { float lo[3], hi[3]; };
+    RawBox bins[NBMAX];
+    int cnt[NBMAX];
+    for (int b = 0; b < NB; ++b) cnt[b] = 0;
+    const float k = NB * (1 - 1e-6f) / ext;
+    for (int i = first; i < first + count; ++i) {
+      const int bi = std::min(NB - 1, std::max(0, (int)((items[i].key[axis] - klo) * k)));
+      const Box& ib = items[i].box;
+      RawBox& bb = bins[bi];
+      if (cnt[bi]++ == 0) { for (int a = 0; a < 3; ++a) { bb.lo[a] = ib.lo[a]; bb.hi[a] = ib.hi[a]; } }
+      else { for (int a = 0; a < 3; ++a) { bb.lo[a] = std::min(bb.lo[a], ib.lo[a]); bb.hi[a] = std::max(bb.hi[a], ib.hi[a]); } }
+    }
+    int nz[NBMAX], m = 0;
+    for (int b = 0; b < NB; ++b) if (cnt[b]) nz[m++] = b;
+    if (m < 2) return;
+    auto grow_raw = [](Box& acc, const RawBox& r) { for (int a = 0; a < 3; ++a) { acc.lo[a] = std::min(acc.lo[a], r.lo[a]); acc.hi[a] = std::max(acc.hi[a], r.hi[a]); } };
+    float right_area[NBMAX]; int right_cnt[NBMAX];  // of the occupied bins nz[j..m)
+    Box acc; int c = 0;
+    for (int j = m - 1; j > 0; --j) { grow_raw(acc, bins[nz[j]]); c += cnt[nz[j]]; right_area[j] = acc.area(); right_cnt[j] = c; }
+    Box lacc; int lc = 0;
+    for (int j = 0; j < m - 1; ++j) {
+      grow_raw(lacc, bins[nz[j]]); lc += cnt[nz[j]];
+      const float cost = lacc.area() * lc + right_area[j + 1] * right_cnt[j + 1];
+      if (cost < cost_out) { cost_out = cost; split_out = nz[j]; }
+    }
+  }
+  int build(int first, int count, int depth_left, int par, int id) {
+    Box box;
+    float klo[4] = {FLT_MAX, FLT_MAX, FLT_MAX, FLT_MAX}, khi[4] = {-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = first; i < first + count; ++i) {
+      box.grow(items[i].box);
+      for (int a = 0; a < 4; ++a) { klo[a] = std::min(klo[a], items[i].key[a]); khi[a] = std::max(khi[a], items[i].key[a]); }
+    }
     nodes[id].box = box;
     nodes[id].first = first; nodes[id].count = count;  // inner nodes too: the size of the subtree (dense_box below)
     if (count == 1) return id;
@@ -77,59 +144,50 @@ struct BinBuilder {
     // A room of a dozen walls around a 300,000-triangle mesh has no good spatial split near the root — every plane through the
     // mesh leaves walls on both sides, so both halves keep the room's box and every ray descends both — but it has a very good
     // split by size: the walls | the mesh.  Same cost function, so the size split is only taken where it is the cheaper one.
-    const int NBMAX = 32;
     const int NB = n_bins;
-    float klo[4], khi[4];
-    for (int a = 0; a < 3; ++a) { klo[a] = cbox.lo[a]; khi[a] = cbox.hi[a]; }
-    klo[3] = FLT_MAX; khi[3] = -FLT_MAX;
-    if (size_split) for (int i = first; i < first + count; ++i) { klo[3] = std::min(klo[3], size_key[order[i]]); khi[3] = std::max(khi[3], size_key[order[i]]); }
-    auto key_of = [&](int p, int axis) { return axis < 3 ? (float)centroid[p][axis] : size_key[p]; };
-    float best_cost = FLT_MAX; int best_axis = -1, best_split = -1;
-    Box bins[NBMAX]; int cnt[NBMAX];
-    float right_area[NBMAX]; int right_cnt[NBMAX];
-    for (int axis = 0; axis < (size_split ? 4 : 3); ++axis) {
-      float ext = khi[axis] - klo[axis];
-      if (!(ext > 0)) continue;
-      if (axis == 3 && ext < 2.f) continue;  // sizes within a factor of four: nothing to separate
-      for (int b = 0; b < NB; ++b) { bins[b] = Box(); cnt[b] = 0; }
-      float k = NB * (1 - 1e-6f) / ext;
-      for (int i = first; i < first + count; ++i) {
-        int bi = std::min(NB - 1, std::max(0, (int)((key_of(order[i], axis) - klo[axis]) * k)));
-        bins[bi].grow(pb[order[i]]); cnt[bi]++;
-      }
-      Box acc; int c = 0;
-      for (int i = NB - 1; i > 0; --i) { acc.grow(bins[i]); c += cnt[i]; right_area[i] = acc.area(); right_cnt[i] = c; }
-      Box lacc; int lc = 0;
-      for (int i = 0; i < NB - 1; ++i) {
-        lacc.grow(bins[i]); lc += cnt[i];
-        if (lc == 0 || right_cnt[i + 1] == 0) continue;
-        float cost = lacc.area() * lc + right_area[i + 1] * right_cnt[i + 1];
-        if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = i; }
-      }
+    const int n_axes = size_split ? 4 : 3;
+    float axis_cost[4]; int axis_split[4];
+    if (par > 0 && count >= 32768) {
+      std::future<void> f[3];
+      for (int a = 1; a < n_axes; ++a) f[a - 1] = std::async(std::launch::async, [&, a] { best_on_axis(first, count, a, klo[a], khi[a], axis_cost[a], axis_split[a]); });
+      best_on_axis(first, count, 0, klo[0], khi[0], axis_cost[0], axis_split[0]);
+      for (int a = 1; a < n_axes; ++a) f[a - 1].get();
+    } else {
+      for (int a = 0; a < n_axes; ++a) best_on_axis(first, count, a, klo[a], khi[a], axis_cost[a], axis_split[a]);
     }
+    float best_cost = FLT_MAX; int best_axis = -1, best_split = -1;
+    for (int a = 0; a < n_axes; ++a) if (axis_cost[a] < best_cost) { best_cost = axis_cost[a]; best_axis = a; best_split = axis_split[a]; }
     float leaf_cost = box.area() * count;
-    if (count <= B200RT_MAX_LEAF && (best_axis < 0 || best_cost + trav_cost * box.area() >= leaf_cost)) { nodes[id].first = first; nodes[id].count = count; return id; }
+    if (count <= B200RT_MAX_LEAF && (best_axis < 0 || best_cost + trav_cost * box.area() >= leaf_cost)) return id;
     const bool force_median = depth_left < 31 && (long long)count > (1ll << std::max(0, depth_left - 1));
     int mid;
     if (force_median) {
       int axis = 0;
-      for (int a = 1; a < 3; ++a) if (cbox.hi[a] - cbox.lo[a] > cbox.hi[axis] - cbox.lo[axis]) axis = a;
+      for (int a = 1; a < 3; ++a) if (khi[a] - klo[a] > khi[axis] - klo[axis]) axis = a;
       mid = first + count / 2;
-      std::nth_element(order.begin() + first, order.begin() + mid, order.begin() + first + count, [&](int a, int b) { return centroid[a][axis] < centroid[b][axis]; });
+      std::nth_element(items.begin() + first, items.begin() + mid, items.begin() + first + count, [&](const Item& a, const Item& b) { return a.key[axis] < b.key[axis]; });
     } else if (best_axis < 0) {  // all centroids coincide: split the range in the middle
       mid = first + count / 2;
     } else {
-      float ext = khi[best_axis] - klo[best_axis];
-      float k = NB * (1 - 1e-6f) / ext;
-      auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](int p) {
-        int bi = std::min(NB - 1, std::max(0, (int)((key_of(p, best_axis) - klo[best_axis]) * k)));
+      const float ext = khi[best_axis] - klo[best_axis];
+      const float k = NB * (1 - 1e-6f) / ext;
+      auto it = std::partition(items.begin() + first, items.begin() + first + count, [&](const Item& p) {
+        const int bi = std::min(NB - 1, std::max(0, (int)((p.key[best_axis] - klo[best_axis]) * k)));
         return bi <= best_split;
       });
-      mid = (int)(it - order.begin());
+      mid = (int)(it - items.begin());
       if (mid == first || mid == first + count) mid = first + count / 2;
     }
-    int l = build(first, mid - first, depth_left - 1);
-    int r = build(mid, first + count - mid, depth_left - 1);
+    const int nl = mid - first, nr = first + count - mid, lid = id + 1, rid = id + 2 * nl;
+    int l, r;
+    if (par > 0 && std::min(nl, nr) >= 4096) {
+      auto left = std::async(std::launch::async, [&] { return build(first, nl, depth_left - 1, par - 1, lid); });
+      r = build(mid, nr, depth_left - 1, par - 1, rid);
+      l = left.get();
+    } else {  // (a lopsided split — seven walls | the mesh — keeps the thread budget for the levels below)
+      l = build(first, nl, depth_left - 1, par, lid);
+      r = build(mid, nr, depth_left - 1, par, rid);
+    }
     nodes[id].left = l; nodes[id].right = r;
     return id;
   }
@@ -213,6 +271,15 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
   if (d->n_prims >= (1u << 27)) { err = "too many primitives"; return B200RT_ERR_UNSUPPORTED; }
   if (!d->prims || !d->materials || !d->textures) { err = "null table pointer"; return B200RT_ERR_INVALID; }
   const uint32_t n = d->n_prims;
+  // B200RT_COMPILE_TIMING=1: the stages' host times on stderr
+  const bool timing = std::getenv("B200RT_COMPILE_TIMING") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  auto stage = [&](const char* what) {
+    if (!timing) return;
+    const auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "compile_scene: %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+    t_prev = now;
+  };
   // ---- validate tables
   for (uint32_t i = 0; i < d->n_textures; ++i) {
     const b200rt_texture& t = d->textures[i];
@@ -244,6 +311,7 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
       put4(cs.instances, (size_t)i * 24 + 12 + 4 * r, (float)Minv[i].m[4 * r], (float)Minv[i].m[4 * r + 1], (float)Minv[i].m[4 * r + 2], 0);
     }
   }
+  stage("validate + instances");
   // ---- bake primitives to world space
   // Transform::new(rotate, scale: Vec3, translate, obj) (transform.rs:17-148) is accepted in full generality.  Where the
   // shape survives the transform (a sphere under a similarity; an axis rectangle / Cube under a positive diagonal; any
@@ -355,6 +423,7 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     }
     bx.pad();
   }
+  stage("bake primitives");
   // ---- BVH (skipped for the flat-list arm: hit.rs:56-67 scans linearly)
   cs.flat = (d->flags & B200RT_SCENE_FLAT_LIST) != 0;
   std::vector<int> order(n);
@@ -386,9 +455,11 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     std::vector<int> bb_order;
     for (int attempt = 0; attempt < 5; ++attempt) {
       if (attempt > 0 && budgets[attempt] < min_budget) continue;
+      stage("  in / out of the BVH");
       BinBuilder bb(inboxes);
-      bb.nodes.reserve(2 * in_idx.size());
+      stage("  builder records");
       int root = bb.build(0, (int)in_idx.size(), budgets[attempt]);
+      stage("  binary SAH build");
       cs.nodes.clear();
       cs.nodes.reserve(in_idx.size() * 16);
       int depth4 = 0;
@@ -445,6 +516,7 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     cs.prim_meta[(size_t)k * 4 + 2] = p.instance;
     cs.prim_meta[(size_t)k * 4 + 3] = p.aux;
   }
+  stage("BVH build + collapse");
   // ---- the remaining tables
   cs.tri_normals.assign((size_t)std::max(1u, d->n_tri_normals) * 12, 0.f);
   for (uint32_t i = 0; i < d->n_tri_normals; ++i)
@@ -489,6 +561,7 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
     if (!(scale > 0.f) || !std::isfinite(scale)) { err = "light scale must be positive and finite"; return B200RT_ERR_INVALID; }
     cs.lights[at + 10] = scale;  // row 2, .z (row 2 of a sphere light is otherwise unused; of a rectangle: k, area)
   }
+  stage("tables in leaf order");
   (void)ubits;
   return B200RT_OK;
 }
