@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <future>
 #include <numeric>
+#include <system_error>
 #include <thread>
 
 #include "scene_compile.hpp"
@@ -149,9 +150,12 @@ struct BinBuilder {
     float axis_cost[4]; int axis_split[4];
     if (par > 0 && count >= 32768) {
       std::future<void> f[3];
-      for (int a = 1; a < n_axes; ++a) f[a - 1] = std::async(std::launch::async, [&, a] { best_on_axis(first, count, a, klo[a], khi[a], axis_cost[a], axis_split[a]); });
+      for (int a = 1; a < n_axes; ++a) {
+        try { f[a - 1] = std::async(std::launch::async, [&, a] { best_on_axis(first, count, a, klo[a], khi[a], axis_cost[a], axis_split[a]); }); }
+        catch (const std::system_error&) {}  // no thread to be had: this axis on the calling thread, below
+      }
       best_on_axis(first, count, 0, klo[0], khi[0], axis_cost[0], axis_split[0]);
-      for (int a = 1; a < n_axes; ++a) f[a - 1].get();
+      for (int a = 1; a < n_axes; ++a) { if (f[a - 1].valid()) f[a - 1].get(); else best_on_axis(first, count, a, klo[a], khi[a], axis_cost[a], axis_split[a]); }
     } else {
       for (int a = 0; a < n_axes; ++a) best_on_axis(first, count, a, klo[a], khi[a], axis_cost[a], axis_split[a]);
     }
@@ -181,9 +185,11 @@ struct BinBuilder {
     const int nl = mid - first, nr = first + count - mid, lid = id + 1, rid = id + 2 * nl;
     int l, r;
     if (par > 0 && std::min(nl, nr) >= 4096) {
-      auto left = std::async(std::launch::async, [&] { return build(first, nl, depth_left - 1, par - 1, lid); });
+      std::future<int> left;
+      try { left = std::async(std::launch::async, [&] { return build(first, nl, depth_left - 1, par - 1, lid); }); }
+      catch (const std::system_error&) {}
       r = build(mid, nr, depth_left - 1, par - 1, rid);
-      l = left.get();
+      l = left.valid() ? left.get() : build(first, nl, depth_left - 1, 0, lid);
     } else {  // (a lopsided split — seven walls | the mesh — keeps the thread budget for the levels below)
       l = build(first, nl, depth_left - 1, par, lid);
       r = build(mid, nr, depth_left - 1, par, rid);
