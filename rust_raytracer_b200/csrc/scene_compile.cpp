@@ -271,7 +271,7 @@ int collapse(const BinBuilder& bb, int bin_id, std::vector<float>& out, int& dep
 
 }  // namespace
 
-int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& err) {
+static int compile_scene_impl(const b200rt_scene_desc* d, CompiledScene& cs, std::string& err) {
   if (!d) { err = "null scene desc"; return B200RT_ERR_INVALID; }
   if (d->n_prims == 0) { err = "scene has no primitives (BVHNode::new on an empty list)"; return B200RT_ERR_INVALID; }
   if (d->n_prims >= (1u << 27)) { err = "too many primitives"; return B200RT_ERR_UNSUPPORTED; }
@@ -570,6 +570,20 @@ int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& er
   stage("tables in leaf order");
   (void)ubits;
   return B200RT_OK;
+}
+
+// No exception leaves the library: the callers are extern "C" (a scene of 10^8 primitives that does not fit the host's memory
+// is an error code, not a terminate()).
+int compile_scene(const b200rt_scene_desc* d, CompiledScene& cs, std::string& err) {
+  try {
+    return compile_scene_impl(d, cs, err);
+  } catch (const std::bad_alloc&) {
+    err = "out of host memory while compiling the scene";
+    return B200RT_ERR_NOMEM;
+  } catch (const std::exception& e) {
+    err = std::string("scene compile failed: ") + e.what();
+    return B200RT_ERR_INVALID;
+  }
 }
 
 }  // namespace b200rt
