@@ -361,7 +361,7 @@ int json_node(b200rt_builder* b, const JValue* n, int depth) {
 
 extern "C" {
 
-int b200rt_builder_mesh_obj(b200rt_builder* b, const char* path, int32_t material, int32_t make_normals, int32_t subdivide) {
+int b200rt_builder_mesh_obj(b200rt_builder* b, const char* path, int32_t material, int32_t make_normals, int32_t subdivide) try {
   if (!b || !path) return -B200RT_ERR_INVALID;
   std::string text;
   if (!read_file(path, text)) { b->err = std::string("Failed to load OBJ file: ") + path; return -B200RT_ERR_IO; }  // mesh.rs:158
@@ -387,20 +387,32 @@ int b200rt_builder_mesh_obj(b200rt_builder* b, const char* path, int32_t materia
     if (first < 0) first = id;
   }
   return first;
+} catch (const std::bad_alloc&) {  // no exception crosses the C ABI
+  b->err = "out of host memory while loading the OBJ";
+  return -B200RT_ERR_NOMEM;
+} catch (const std::exception& e) {
+  b->err = std::string("OBJ: ") + e.what();
+  return -B200RT_ERR_PARSE;
 }
 
 static int load_scene_tree(b200rt_builder* b, const JValue* root, b200rt_camera* cam_out);
 
-int b200rt_builder_load_json(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out) {
+int b200rt_builder_load_json(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out) try {
   if (!b || !text) return B200RT_ERR_INVALID;
   JParser jp;
   jp.p = text; jp.end = text + len;
   auto root = jp.parse();
   if (!root) { b->err = "JSON: " + jp.err; return B200RT_ERR_PARSE; }
   return load_scene_tree(b, root.get(), cam_out);
+} catch (const std::bad_alloc&) {
+  b->err = "out of host memory while loading the scene file";
+  return B200RT_ERR_NOMEM;
+} catch (const std::exception& e) {
+  b->err = std::string("scene file: ") + e.what();
+  return B200RT_ERR_PARSE;
 }
 
-int b200rt_builder_load_yaml(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out) {
+int b200rt_builder_load_yaml(b200rt_builder* b, const char* text, uint64_t len, b200rt_camera* cam_out) try {
   if (!b || !text) return B200RT_ERR_INVALID;
   YParser yp;
   if (!yp.tokenize(text, text + len)) { b->err = yp.err; return B200RT_ERR_PARSE; }
@@ -408,6 +420,12 @@ int b200rt_builder_load_yaml(b200rt_builder* b, const char* text, uint64_t len, 
   auto root = yp.block(yp.lines[0].indent, 0);
   if (!root || yp.at != yp.lines.size()) { b->err = yp.err.empty() ? "YAML: trailing content / bad indentation" : yp.err; return B200RT_ERR_PARSE; }
   return load_scene_tree(b, root.get(), cam_out);
+} catch (const std::bad_alloc&) {
+  b->err = "out of host memory while loading the scene file";
+  return B200RT_ERR_NOMEM;
+} catch (const std::exception& e) {
+  b->err = std::string("scene file: ") + e.what();
+  return B200RT_ERR_PARSE;
 }
 
 static int load_scene_tree(b200rt_builder* b, const JValue* root, b200rt_camera* cam_out) {
