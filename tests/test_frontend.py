@@ -227,6 +227,18 @@ def test_bvh_quality_size_axis_and_dense_box(monkeypatch):
         rt.bvh_quality(rt.SceneBuilder())  # BVHNode::new on an empty list
 
 
+@pytest.mark.parametrize("name", ["mesh", "book2"])
+def test_bvh_does_not_depend_on_the_builder_threads(name, monkeypatch):
+    """Host only.  The builder assigns node slots up front and builds the halves of a large node on two threads: same tree
+    (node count, depth, surface-area sums, dense box) for 1, 3 and 16 threads."""
+    sb = scene_builder(name)
+    seen = []
+    for threads in ("1", "3", "16"):
+        monkeypatch.setenv("B200RT_BVH_THREADS", threads)
+        seen.append((rt.compile_stats(sb), rt.bvh_quality(sb)))
+    assert seen[0] == seen[1] == seen[2]
+
+
 def test_scene_500_yaml_builds_the_same_tables_as_its_json_twin():
     """README.md:86-89: data/scene_500.yaml (894 KB, 1,005 spheres, 999 BVHNodes) carries the same objects as scene_500.json."""
     a = rt.SceneBuilder().load_json(open(os.path.join(DATA, "scene_500.json")).read())
