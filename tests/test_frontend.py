@@ -227,6 +227,27 @@ def test_bvh_quality_size_axis_and_dense_box(monkeypatch):
         rt.bvh_quality(rt.SceneBuilder())  # BVHNode::new on an empty list
 
 
+def test_dense_box_of_a_cluster_in_a_room():
+    """Host only, through the construction API: five walls around 6,000 small spheres in one corner.  The dense box is the
+    cluster's; a room that the cluster fills has none; neither has a room without a cluster."""
+    white = rt.Lambertian(rt.ConstantTexture((1, 1, 1)))
+    cam = rt.Camera(((50, 50, -150), (50, 50, 50)), (0, 1, 0), 40, 1, 0, 1)
+    walls = [rt.YZRectangle((0, 0), (100, 100), 0, white), rt.YZRectangle((0, 0), (100, 100), 100, white), rt.XZRectangle((0, 0), (100, 100), 0, white),
+             rt.XZRectangle((0, 0), (100, 100), 100, white), rt.XYRectangle((0, 0), (100, 100), 100, white)]
+    rng = np.random.default_rng(5)
+
+    def cluster(lo, hi, n=6000):
+        c = rng.uniform(lo, hi, size=(n, 3))
+        return [rt.Sphere(tuple(map(float, x)), 0.2, white) for x in c]
+
+    q = rt.bvh_quality(rt.World(rt.HitableList(walls + cluster(10, 40)), cam).builder)
+    assert q["dense_box"] is not None
+    lo, hi = (np.array(v) for v in q["dense_box"])
+    assert np.all(lo > 9.5) and np.all(lo < 10.5) and np.all(hi > 39.5) and np.all(hi < 40.5)
+    assert rt.bvh_quality(rt.World(rt.HitableList(walls + cluster(1, 99)), cam).builder)["dense_box"] is None  # 94 % of the room's surface
+    assert rt.bvh_quality(rt.World(rt.HitableList(walls), cam).builder)["dense_box"] is None
+
+
 @pytest.mark.parametrize("name", ["mesh", "book2"])
 def test_bvh_does_not_depend_on_the_builder_threads(name, monkeypatch):
     """Host only.  The builder assigns node slots up front and builds the halves of a large node on two threads: same tree
