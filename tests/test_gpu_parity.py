@@ -329,6 +329,31 @@ def test_two_ended_bins_trace_the_same_paths(ctx, name, integrator, mode, monkey
     np.testing.assert_allclose(m, b, rtol=1e-4, atol=1e-4)
 
 
+def test_two_ended_bins_by_default_on_a_large_clustered_scene(ctx, monkeypatch):
+    """>= 8192 primitives in the BVH and a dense box: the two-ended bins are on without any variable set (the mesh config's path).
+    Same paths as the megakernel and as plain bins."""
+    white = rt.Lambertian(rt.ConstantTexture((0.7, 0.7, 0.7)))
+    light = rt.DiffuseLight(rt.ConstantTexture((8, 8, 8)))
+    cam = rt.Camera(((50, 50, -140), (50, 50, 50)), (0, 1, 0), 40, 1, 0, 1)
+    rng = np.random.default_rng(11)
+    items = [rt.YZRectangle((0, 0), (100, 100), 0, white), rt.YZRectangle((0, 0), (100, 100), 100, white), rt.XZRectangle((0, 0), (100, 100), 0, white),
+             rt.XZRectangle((0, 0), (100, 100), 100, white), rt.XYRectangle((0, 0), (100, 100), 100, white), rt.XZRectangle((35, 35), (65, 65), 99.9, light)]
+    items += [rt.Sphere(tuple(map(float, c)), 0.4, white) for c in rng.uniform(15, 45, size=(9000, 3))]
+    world = rt.World(rt.HitableList(items), cam)
+    assert rt.bvh_quality(world.builder)["dense_box"] is not None
+    for k in ("B200RT_WF_SPLIT", "B200RT_WF_SPLIT_MIN_PRIMS", "B200RT_WF_DYN"):
+        monkeypatch.delenv(k, raising=False)
+    scene = rt.Scene(ctx, world.builder)
+    p = rt.make_params(160, 120, 32)
+    a, sa = scene.render(cam.c, p)
+    m, sm = scene.render(cam.c, rt.copy_params(p, pipeline=F.PIPELINE_MEGAKERNEL))
+    monkeypatch.setenv("B200RT_WF_SPLIT", "0")
+    b, sbt = scene.render(cam.c, p)
+    assert sa.extend_rays == sm.extend_rays == sbt.extend_rays and sa.paths == 160 * 120 * 32
+    np.testing.assert_allclose(a, m, rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)
+
+
 def test_extend_with_ray_replacement_traces_the_same_paths(ctx, monkeypatch):
     """k_wf_extend_dyn (B200RT_WF_DYN=1, off by default: measured slower, profiles/r2_experiments.md section 12) hands a finished lane the
     next ray of the queue instead of waiting for its warp: same rays, same hits, same image."""
